@@ -1,0 +1,112 @@
+/*
+ * kair_b200 C ABI -- sm_100a (B200) kernels for KAIR's image-restoration hot path.
+ *
+ * Every entry point takes plain device pointers, sizes and a CUDA stream handle (cudaStream_t passed as void*),
+ * launches asynchronously on that stream, never synchronises, and returns 0 on success.  A non-zero return is
+ * either a cudaError_t (> 0) or a kair error (< 0); kair_last_error() gives the message for the calling thread.
+ * There is no CPU fallback: calling on a non-sm_100 device is an error.
+ *
+ * The reference (Owen1B/KAIR) has no native interface for this path -- it calls ATen ops from Python
+ * (models/network_swinir.py:114-145, 239-279; models/network_dncnn.py:69-71; models/network_unet.py:59-76).
+ * Its own plugin convention for native code is a torch extension of plain functions wrapped in
+ * torch.autograd.Function (models/op/fused_act.py:10-72, models/op/fused_bias_act.cpp:7-21); this header is the
+ * C-ABI layer under that convention.  Each entry point cites the reference lines whose arithmetic it replaces.
+ *
+ * Internal activation layout ("token layout"): tokens are NHWC pixels, t = (b*H + h)*W + w, channel-padded to a
+ * multiple of 64 (C=180 -> 192), bf16 for GEMM operands and fp32 for the residual stream.  Padded channels are
+ * zero, except an optional "ones column" used to obtain bias gradients from the weight-gradient GEMM.
+ */
+#ifndef KAIR_B200_H
+#define KAIR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* kair_last_error(void);
+int kair_version(void);
+/* 0 if the current CUDA device can run the kernels (compute capability 10.x). */
+int kair_check_device(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * kair_gemm_tn: D[M,N] = epilogue( A[M,K] * B[N,K]^T ) on tcgen05 tensor cores (bf16 in, fp32 accumulate in TMEM).
+ *   conv == 0: A is a row-major bf16 matrix [M][a_pitch]  (nn.Linear: network_swinir.py:25-28, 121, 143)
+ *   conv == 1: A is an NHWC bf16 image [B][H][W][a_pitch]; implicit-GEMM 3x3 stride-1 zero-padded convolution,
+ *              K = 9 taps x Cin_pad, B packed as [N][9*Cin_pad] with k = tap*Cin_pad + ci
+ *              (nn.Conv2d(C,C,3,1,1): network_swinir.py:465, 669, 729; basicblock.py:65)
+ * Epilogue modes (what happens to acc = A*B^T, one row of the tile per thread):
+ *   KAIR_EPI_LINEAR   v = act(acc + bias [+ resid]);                          outB = bf16(v), outF = v
+ *   KAIR_EPI_GELU     u = acc + bias; outB2 = bf16(u); outB = bf16(gelu_erf(u))   (network_swinir.py:25-26)
+ *   KAIR_EPI_RESID_LN v = acc + bias + resid; outF = v; outB = bf16((v-mean)*rstd); rowstat = rstd
+ *                     (residual add + the next LayerNorm, network_swinir.py:245, 276-277)
+ *   KAIR_EPI_DGELU    outB = bf16(acc * gelu_erf'(aux))                        (backward of :26)
+ *   KAIR_EPI_LNBWD    LayerNorm backward fused with the residual gradient:
+ *                     outF = resid + rstd*(acc - mean(acc) - xhat*mean(acc*xhat)), outB = bf16(outF), xhat = aux
+ * ------------------------------------------------------------------------------------------------------------ */
+enum { KAIR_EPI_LINEAR = 0, KAIR_EPI_GELU = 1, KAIR_EPI_RESID_LN = 2, KAIR_EPI_DGELU = 3, KAIR_EPI_LNBWD = 4 };
+enum { KAIR_ACT_NONE = 0, KAIR_ACT_LRELU = 1 /* slope 0 == ReLU */ };
+
+typedef struct kair_gemm_tn_args {
+  const void* A;     /* bf16 */
+  int64_t a_pitch;   /* elements per row / per pixel */
+  const void* B;     /* bf16 [N][K_total], K_total = taps*K */
+  int64_t b_pitch;   /* elements per row of B */
+  int32_t M;         /* rows (tokens); for conv: batch*H*W */
+  int32_t N;         /* output columns, multiple of bn */
+  int32_t K;         /* reduction length per tap, multiple of 64 */
+  int32_t bn;        /* N tile: 64, 128, 192 or 256 */
+  int32_t mode;      /* KAIR_EPI_* */
+  int32_t act;       /* KAIR_ACT_* (LINEAR mode only) */
+  float act_slope;
+  float ln_eps;
+  const float* bias; /* [N] or NULL */
+  const float* resid;
+  int64_t resid_pitch;
+  const void* aux;   /* bf16 */
+  int64_t aux_pitch;
+  float* rowstat;    /* [M] rstd: written by RESID_LN, read by LNBWD */
+  void* outB;        /* bf16 [M][outB_pitch] or NULL */
+  int64_t outB_pitch;
+  void* outB2;       /* bf16, GELU mode pre-activation, or NULL */
+  int64_t outB2_pitch;
+  float* outF;       /* fp32 [M][outF_pitch] or NULL */
+  int64_t outF_pitch;
+  int32_t n_valid;   /* number of real (unpadded) columns, for LayerNorm statistics */
+  int32_t ones_col;  /* column of outB forced to 1.0 (bias-gradient trick), -1 for none */
+  int32_t conv;      /* 0 dense, 1 conv3x3 */
+  int32_t batch, H, W;
+} kair_gemm_tn_args;
+
+int kair_gemm_tn(const kair_gemm_tn_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * kair_gemm_nt: D[n1][taps*n2] += sum_t A[t][n1] * B[t (+tap shift)][n2]   (fp32 accumulate into D, which the
+ * caller zero-fills).  The weight-gradient GEMM of nn.Linear / nn.Conv2d 3x3 (autograd of
+ * network_swinir.py:19-21, 105-107, 465, 729); with a ones column in B it also yields the bias gradient.
+ *   conv == 0: A, B are [T][pitch] bf16 token matrices.
+ *   conv == 1: A, B are NHWC images; column block `tap` of D holds sum_p A[p] * B[p + (dy-1, dx-1)].
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_gemm_nt_args {
+  const void* A;    /* bf16 [T][a_pitch] (output gradient) */
+  int64_t a_pitch;
+  const void* B;    /* bf16 [T][b_pitch] (layer input) */
+  int64_t b_pitch;
+  float* D;         /* fp32 [n1][d_pitch] */
+  int64_t d_pitch;
+  int32_t T;
+  int32_t n1;       /* rows of D (multiple of 64) */
+  int32_t n2;       /* columns of D per tap (multiple of bn) */
+  int32_t bn;       /* 64, 128, 192, 256 */
+  int32_t splits;   /* token-range splits, 0 = auto */
+  int32_t conv;
+  int32_t batch, H, W;
+} kair_gemm_nt_args;
+
+int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KAIR_B200_H */

@@ -1,0 +1,317 @@
+// kair_gemm_nt: weight-gradient GEMM  D[n1, n2] += sum_t A[t, n1] * B[t, n2]   (contraction over tokens)
+//
+// Both operands are read in their natural token-major layout, i.e. "MN-major" UMMA operands: TMA brings
+// [64 tokens x 64 channels] SWIZZLE_128B atoms and tcgen05.mma consumes them with a_major = b_major = MN.
+// The token range is split across CTAs; every CTA keeps one 128 x BN accumulator tile in TMEM for its whole token
+// range and finally adds it into the fp32 result with a TMA reduce-add (cp.reduce.async.bulk.tensor ... .add).
+// Conv mode: B is an NHWC image read through 9 shifted 4-D boxes (TMA zero fill = zero padding), the result column
+// block is tap*K2.
+//
+// Replaces (reference file:line): autograd's weight gradients for nn.Linear (models/network_swinir.py:19-21,
+// 105-107) and nn.Conv2d 3x3 (:465, :729; models/basicblock.py:65).
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+constexpr int NT_THREADS = 320;
+constexpr int NT_BKT = 64;                    // tokens per pipeline stage
+constexpr int NT_A_STAGE = 128 * NT_BKT * 2;  // 16 KiB: two [64 tok x 64 ch] atoms
+constexpr int NT_STG_PER_WARP = 8192;         // 2 x 4 KiB fp32 chunks
+constexpr int NT_STG_BYTES = 8 * NT_STG_PER_WARP;
+constexpr int NT_MAX_STAGES = 8;
+constexpr int NT_MISC_BYTES = 1024;
+
+struct NtParams {
+  CUtensorMap tmA, tmB, tmD;
+  int T, kb_total, kb_per_split, splits, tiles1, tiles2, taps, stages;
+  int H, W, TW, TH, tiles_w, tiles_h;  // conv: a k-block is a TW x TH pixel patch (TW*TH = 64)
+  int k2;                              // channels of B per tap (conv: column block stride in D)
+};
+
+template <int BN, bool kConv>
+__global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_constant__ NtParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  constexpr int B_STAGE = BN * NT_BKT * 2;
+  uint8_t* stg_base = smem;
+  uint8_t* a_base = smem + NT_STG_BYTES;
+  uint8_t* b_base = a_base + p.stages * NT_A_STAGE;
+  uint8_t* misc = b_base + p.stages * B_STAGE;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
+  uint64_t* empty_bar = full_bar + NT_MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + NT_MAX_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmD);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < p.stages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      mbar_init(tfull_bar, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // work item: (tile1, tile2, tap, split)
+  int w = blockIdx.x;
+  const int split = w % p.splits;
+  w /= p.splits;
+  const int tap = w % p.taps;
+  w /= p.taps;
+  const int tile2 = w % p.tiles2;
+  const int tile1 = w / p.tiles2;
+  const int kb0 = split * p.kb_per_split;
+  int kb1 = kb0 + p.kb_per_split;
+  if (kb1 > p.kb_total) kb1 = p.kb_total;
+  const int nkb = kb1 - kb0;  // may be <= 0 for trailing splits
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int dy = tap / 3, dx = tap - dy * 3;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
+        uint8_t* a_s = a_base + stage * NT_A_STAGE;
+        uint8_t* b_s = b_base + stage * B_STAGE;
+        if (kConv) {
+          int per_img = p.tiles_w * p.tiles_h;
+          int b = kb / per_img;
+          int r = kb - b * per_img;
+          int th = r / p.tiles_w;
+          int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * 128 + i * 64, w0, h0, b);
+#pragma unroll
+          for (int i = 0; i < BN / 64; ++i)
+            tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0 + dx - 1, h0 + dy - 1, b);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            tma_load_2d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * 128 + i * 64, kb * NT_BKT);
+#pragma unroll
+          for (int i = 0; i < BN / 64; ++i)
+            tma_load_2d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, kb * NT_BKT);
+        }
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0 && nkb > 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tcgen05_fence_after();
+        const uint32_t a_addr = smem_u32(a_base + stage * NT_A_STAGE);
+        const uint32_t b_addr = smem_u32(b_base + stage * B_STAGE);
+#pragma unroll
+        for (int k = 0; k < NT_BKT / 16; ++k) {
+          umma_f16_ss(tmem_base, make_desc_mnmajor_sw128(a_addr + k * 2048, NT_BKT),
+                      make_desc_mnmajor_sw128(b_addr + k * 2048, NT_BKT), idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tfull_bar);
+    }
+    __syncwarp();
+  } else if (nkb > 0) {
+    const int ew = warp - 2;
+    const int q = warp & 3;
+    const int hf = ew >> 2;
+    constexpr int HALF = BN / 2;
+    constexpr int NCH = HALF / 32;
+    uint8_t* stg = stg_base + ew * NT_STG_PER_WARP;
+    mbar_wait(tfull_bar, 0);
+    tcgen05_fence_after();
+    const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + hf * HALF;
+    const int col_base = tap * p.k2 + tile2 * BN + hf * HALF;
+    int sbuf = 0;
+#pragma unroll 1
+    for (int c = 0; c < NCH; ++c) {
+      uint32_t r[32];
+      tmem_ld32(tacc + c * 32, r);
+      tmem_ld_wait();
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+      uint8_t* buf = stg + sbuf * 4096;
+      uint32_t base = smem_u32(buf) + lane * 128;
+      uint32_t sw = lane & 7;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        uint32_t a = base + ((j ^ sw) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(r[4 * j]), "r"(r[4 * j + 1]),
+                     "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                     : "memory");
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_reduce_add_2d(&p.tmD, buf, col_base + c * 32, tile1 * 128 + q * 32);
+        tma_store_commit();
+      }
+      sbuf ^= 1;
+    }
+    if (lane == 0) tma_store_wait_all<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int BN, bool kConv>
+static int nt_launch_cfg(const NtParams& p, int grid, size_t smem, cudaStream_t st) {
+  auto kern = gemm_nt_kernel<BN, kConv>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set[dev & 63] = true;
+  }
+  kern<<<grid, NT_THREADS, smem, st>>>(p);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
+  KB_CHECK(a.A && a.B && a.D, "kair_gemm_nt: null pointer");
+  KB_CHECK(a.bn == 64 || a.bn == 128 || a.bn == 192 || a.bn == 256, "kair_gemm_nt: bn=%d unsupported", a.bn);
+  KB_CHECK(a.n2 > 0 && a.n2 % a.bn == 0, "kair_gemm_nt: n2=%d must be a multiple of bn=%d", a.n2, a.bn);
+  KB_CHECK(a.n1 > 0 && a.n1 % 64 == 0, "kair_gemm_nt: n1=%d must be a multiple of 64", a.n1);
+  KB_CHECK(a.a_pitch % 8 == 0 && a.b_pitch % 8 == 0 && a.d_pitch % 4 == 0, "kair_gemm_nt: misaligned pitch");
+  KB_CHECK(a.T > 0, "kair_gemm_nt: empty token range");
+  if (check_device() != 0) return -3;
+
+  NtParams p;
+  memset(&p, 0, sizeof(p));
+  p.T = a.T;
+  p.taps = a.conv ? 9 : 1;
+  p.tiles1 = (a.n1 + 127) / 128;
+  p.tiles2 = a.n2 / a.bn;
+  p.k2 = a.n2;
+  if (a.conv) {
+    KB_CHECK((long long)a.batch * a.H * a.W == a.T, "kair_gemm_nt: conv geometry does not match T");
+    p.H = a.H;
+    p.W = a.W;
+    int tw = 64;
+    while (tw > 8 && tw > a.W) tw >>= 1;
+    p.TW = tw;
+    p.TH = 64 / tw;
+    p.tiles_w = (a.W + p.TW - 1) / p.TW;
+    p.tiles_h = (a.H + p.TH - 1) / p.TH;
+    p.kb_total = a.batch * p.tiles_w * p.tiles_h;
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH, 1};
+    {
+      uint64_t dims[4] = {(uint64_t)a.n1, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+      uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.a_pitch * 2 * a.W, (uint64_t)a.a_pitch * 2 * a.W * a.H};
+      if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.A, dims, str, box, nullptr,
+                    CU_TENSOR_MAP_SWIZZLE_128B))
+        return -2;
+    }
+    {
+      uint64_t dims[4] = {(uint64_t)a.n2, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+      uint64_t str[3] = {(uint64_t)a.b_pitch * 2, (uint64_t)a.b_pitch * 2 * a.W, (uint64_t)a.b_pitch * 2 * a.W * a.H};
+      if (make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.B, dims, str, box, nullptr,
+                    CU_TENSOR_MAP_SWIZZLE_128B))
+        return -2;
+    }
+  } else {
+    p.kb_total = (a.T + NT_BKT - 1) / NT_BKT;
+    uint32_t box[2] = {64, 64};
+    {
+      uint64_t dims[2] = {(uint64_t)a.n1, (uint64_t)a.T};
+      uint64_t str[1] = {(uint64_t)a.a_pitch * 2};
+      if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.A, dims, str, box, nullptr,
+                    CU_TENSOR_MAP_SWIZZLE_128B))
+        return -2;
+    }
+    {
+      uint64_t dims[2] = {(uint64_t)a.n2, (uint64_t)a.T};
+      uint64_t str[1] = {(uint64_t)a.b_pitch * 2};
+      if (make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.B, dims, str, box, nullptr,
+                    CU_TENSOR_MAP_SWIZZLE_128B))
+        return -2;
+    }
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)a.n2 * p.taps, (uint64_t)a.n1};
+    uint64_t str[1] = {(uint64_t)a.d_pitch * 4};
+    uint32_t box[2] = {32, 32};
+    if (make_tmap(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, a.D, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+
+  const int b_stage = a.bn * NT_BKT * 2;
+  int stages = (232448 - 1024 - NT_STG_BYTES - NT_MISC_BYTES) / (NT_A_STAGE + b_stage);
+  if (stages > NT_MAX_STAGES) stages = NT_MAX_STAGES;
+  KB_CHECK(stages >= 2, "kair_gemm_nt: not enough shared memory");
+  p.stages = stages;
+  size_t smem = 1024 + NT_STG_BYTES + (size_t)stages * (NT_A_STAGE + b_stage) + NT_MISC_BYTES;
+
+  const int items = p.tiles1 * p.tiles2 * p.taps;
+  int splits = a.splits > 0 ? a.splits : sm_count() / items;
+  if (splits < 1) splits = 1;
+  if (splits > p.kb_total) splits = p.kb_total;
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.splits = splits;
+  const int grid = items * splits;
+
+  if (a.conv) {
+    switch (a.bn) {
+      case 64: return nt_launch_cfg<64, true>(p, grid, smem, st);
+      case 128: return nt_launch_cfg<128, true>(p, grid, smem, st);
+      case 192: return nt_launch_cfg<192, true>(p, grid, smem, st);
+      case 256: return nt_launch_cfg<256, true>(p, grid, smem, st);
+    }
+  } else {
+    switch (a.bn) {
+      case 64: return nt_launch_cfg<64, false>(p, grid, smem, st);
+      case 128: return nt_launch_cfg<128, false>(p, grid, smem, st);
+      case 192: return nt_launch_cfg<192, false>(p, grid, smem, st);
+      case 256: return nt_launch_cfg<256, false>(p, grid, smem, st);
+    }
+  }
+  return -1;
+}
+
+}  // namespace kb

@@ -1,0 +1,779 @@
+// kair_gemm_tn: persistent, warp-specialised tcgen05 GEMM  D[M,N] = epilogue(A[M,K] * B[N,K]^T)
+//
+//   warp 0      TMA producer   (A tiles [128 x 64] bf16, SWIZZLE_128B; conv mode: 9 shifted 4-D boxes per k-slice,
+//                                zero padding comes from TMA out-of-bounds fill)
+//   warp 1      MMA issuer     (one lane issues tcgen05.mma 128 x BN x 16, accumulators double-buffered in TMEM)
+//   warps 2..9  epilogue       (tcgen05.ld -> registers -> fused bias / GELU / residual / LayerNorm /
+//                                LayerNorm-backward -> swizzled smem staging -> TMA store)
+//
+// One thread of the epilogue owns one row of the 128-row tile (TMEM lane == row), split in two column halves across
+// two warps, so LayerNorm statistics are thread-local plus one smem exchange.
+//
+// Replaces (reference file:line): nn.Linear qkv/proj/fc1/fc2 and their input-gradient GEMMs
+// (models/network_swinir.py:25-28, 121, 143), LayerNorm norm1/norm2 (:245, :277), the residual adds (:276-277) and
+// nn.Conv2d 3x3 (:465, :729; models/basicblock.py:65).
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+constexpr int TN_THREADS = 320;       // 10 warps
+constexpr int TN_BM = 128;
+constexpr int TN_BK = 64;
+constexpr int TN_A_STAGE = TN_BM * TN_BK * 2;  // 16 KiB
+constexpr int TN_STG_PER_WARP = 12288;         // 2 x (4 KiB fp32 chunk + 2 KiB bf16 chunk)
+constexpr int TN_STG_BYTES = 8 * TN_STG_PER_WARP;
+constexpr int TN_MAX_STAGES = 8;
+constexpr int TN_MISC_BYTES = 6144;            // 1 KiB barriers + tmem ptr, 4 KiB row-exchange buffer
+
+struct TnParams {
+  CUtensorMap tmA, tmB, tmOutB, tmOutB2, tmOutF;
+  const float* bias;
+  const float* resid;
+  const bf16* aux;
+  float* rowstat;
+  long long resid_pitch, aux_pitch;
+  int M, m_tiles, n_tiles, kc, taps, stages;
+  int n_valid, ones_col, act;
+  float act_slope, ln_eps;
+  int has_outB, has_outB2, has_outF;
+  // conv geometry
+  int H, W, TW, TH, tiles_w, tiles_h;
+};
+
+struct TileCoord {
+  int b, h0, w0;
+};
+
+template <bool kConv>
+__device__ __forceinline__ TileCoord tile_coord(const TnParams& p, int m_tile) {
+  TileCoord t;
+  if (kConv) {
+    int per_img = p.tiles_w * p.tiles_h;
+    t.b = m_tile / per_img;
+    int r = m_tile - t.b * per_img;
+    int th = r / p.tiles_w;
+    t.h0 = th * p.TH;
+    t.w0 = (r - th * p.tiles_w) * p.TW;
+  } else {
+    t.b = 0;
+    t.h0 = 0;
+    t.w0 = m_tile * TN_BM;
+  }
+  return t;
+}
+
+// global token index of tile row `row` (or -1 when the row falls outside the tensor)
+template <bool kConv>
+__device__ __forceinline__ long long row_token(const TnParams& p, const TileCoord& t, int row) {
+  if (kConv) {
+    int h = t.h0 + row / p.TW;
+    int w = t.w0 + row % p.TW;
+    if (h >= p.H || w >= p.W) return -1;
+    return ((long long)t.b * p.H + h) * p.W + w;
+  } else {
+    long long tok = (long long)t.w0 + row;
+    return tok < p.M ? tok : -1;
+  }
+}
+
+// ---- staging + TMA store of one 32-row x 32-col chunk owned by a warp --------------------------------------
+__device__ __forceinline__ void stage_bf16(uint8_t* buf, int lane, const float (&v)[32]) {
+  // 64-byte rows, SWIZZLE_64B: 16-byte unit j of row r lives at unit j ^ ((r >> 1) & 3)
+  uint32_t base = smem_u32(buf) + lane * 64;
+  uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t a = base + ((j ^ sw) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(v[8 * j + 0], v[8 * j + 1])),
+                 "r"(pack_bf16x2(v[8 * j + 2], v[8 * j + 3])), "r"(pack_bf16x2(v[8 * j + 4], v[8 * j + 5])),
+                 "r"(pack_bf16x2(v[8 * j + 6], v[8 * j + 7]))
+                 : "memory");
+  }
+}
+__device__ __forceinline__ void stage_f32(uint8_t* buf, int lane, const float (&v)[32]) {
+  // 128-byte rows, SWIZZLE_128B: 16-byte unit j of row r lives at unit j ^ (r & 7)
+  uint32_t base = smem_u32(buf) + lane * 128;
+  uint32_t sw = lane & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint32_t a = base + ((j ^ sw) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(v[4 * j + 0])),
+                 "r"(__float_as_uint(v[4 * j + 1])), "r"(__float_as_uint(v[4 * j + 2])),
+                 "r"(__float_as_uint(v[4 * j + 3]))
+                 : "memory");
+  }
+}
+template <bool kConv>
+__device__ __forceinline__ void tma_store_chunk(const TnParams& p, const CUtensorMap* tm, const uint8_t* buf,
+                                                const TileCoord& t, int q, int col) {
+  if (kConv) {
+    int r0 = q * 32;
+    tma_store_4d(tm, buf, col, t.w0 + r0 % p.TW, t.h0 + r0 / p.TW, t.b);
+  } else {
+    tma_store_2d(tm, buf, col, t.w0 + q * 32);
+  }
+}
+
+template <int BN, int EPI, bool kConv, bool kBRes>
+__global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_constant__ TnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+
+  constexpr int B_STAGE = BN * TN_BK * 2;
+  const int k_total = p.kc * p.taps;
+  uint8_t* stg_base = smem;
+  uint8_t* a_base = smem + TN_STG_BYTES;
+  uint8_t* b_base = a_base + p.stages * TN_A_STAGE;
+  uint8_t* misc = b_base + (kBRes ? k_total : p.stages) * B_STAGE;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
+  uint64_t* empty_bar = full_bar + TN_MAX_STAGES;
+  uint64_t* tfull_bar = empty_bar + TN_MAX_STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint64_t* bres_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
+  float* xch = reinterpret_cast<float*>(misc + 1024);  // [2 slots][2 halves][2 values][128 rows] fp32 = 4 KiB
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  constexpr uint32_t TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    if (p.has_outB) tma_prefetch_desc(&p.tmOutB);
+    if (p.has_outB2) tma_prefetch_desc(&p.tmOutB2);
+    if (p.has_outF) tma_prefetch_desc(&p.tmOutF);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < p.stages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull_bar[i], 1);
+        mbar_init(&tempty_bar[i], 8);
+      }
+      mbar_init(bres_bar, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // static persistent schedule: this CTA keeps one n-tile and walks m-tiles with a fixed stride
+  const int n_tile = blockIdx.x % p.n_tiles;
+  const int m_first = blockIdx.x / p.n_tiles;
+  const int m_stride = gridDim.x / p.n_tiles;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      if (kBRes) {
+        mbar_arrive_expect_tx(bres_bar, (uint32_t)(k_total * B_STAGE));
+        for (int kb = 0; kb < k_total; ++kb)
+          tma_load_2d(b_base + kb * B_STAGE, &p.tmB, bres_bar, kb * TN_BK, n_tile * BN);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride) {
+        const TileCoord t = tile_coord<kConv>(p, m_tile);
+        for (int kb = 0; kb < k_total; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
+          if (kConv) {
+            int tap = kb / p.kc;
+            int kcc = kb - tap * p.kc;
+            int dy = tap / 3, dx = tap - dy * 3;
+            tma_load_4d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + dx - 1,
+                        t.h0 + dy - 1, t.b);
+          } else {
+            tma_load_2d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kb * TN_BK, t.w0);
+          }
+          if (!kBRes) tma_load_2d(b_base + stage * B_STAGE, &p.tmB, &full_bar[stage], kb * TN_BK, n_tile * BN);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TN_BM, BN, 0, 0);
+      if (kBRes) {
+        mbar_wait(bres_bar, 0);
+        tcgen05_fence_after();
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&tempty_bar[as], aphase ^ 1);
+        tcgen05_fence_after();
+        const uint32_t tacc = tmem_base + as * BN;
+        for (int kb = 0; kb < k_total; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tcgen05_fence_after();
+          const uint32_t a_addr = smem_u32(a_base + stage * TN_A_STAGE);
+          const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : stage) * B_STAGE);
+#pragma unroll
+          for (int k = 0; k < TN_BK / 16; ++k) {
+            umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
+                        (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull_bar[as]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================================ epilogue ================================
+    const int ew = warp - 2;
+    const int q = warp & 3;    // TMEM lane quarter this warp may access
+    const int hf = ew >> 2;    // column half
+    const int row = q * 32 + lane;
+    constexpr int HALF = BN / 2;
+    constexpr int NCH = HALF / 32;
+    uint8_t* stg = stg_base + ew * TN_STG_PER_WARP;
+    int sbuf = 0;
+    int xslot = 0;
+    const float inv_n = 1.0f / (float)p.n_valid;
+
+    // two-value exchange between the two threads that share a row
+    auto exchange2 = [&](float a, float b, float& oa, float& ob) {
+      float* s = xch + xslot * 512;
+      s[(hf * 2 + 0) * 128 + row] = a;
+      s[(hf * 2 + 1) * 128 + row] = b;
+      named_bar_sync(1, 256);
+      oa = a + s[((hf ^ 1) * 2 + 0) * 128 + row];
+      ob = b + s[((hf ^ 1) * 2 + 1) * 128 + row];
+      xslot ^= 1;
+    };
+    // acquire a staging buffer set: fp32 chunk (or first bf16 chunk) at +0, bf16 chunk at +4096
+    auto stage_begin = [&]() -> uint8_t* {
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+      return stg + sbuf * 6144;
+    };
+    auto stage_end = [&]() {
+      if (lane == 0) tma_store_commit();
+      sbuf ^= 1;
+    };
+
+    int it = 0;
+    for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      const TileCoord t = tile_coord<kConv>(p, m_tile);
+      const long long tok = row_token<kConv>(p, t, row);
+      mbar_wait(&tfull_bar[as], aphase);
+      tcgen05_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * HALF;
+      const int col_half = n_tile * BN + hf * HALF;
+
+      if (EPI == KAIR_EPI_LINEAR) {
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+            }
+          }
+          if (p.resid && tok >= 0) {
+            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 r4 = __ldg(rp + i);
+              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
+            }
+          }
+          if (p.act == KAIR_ACT_LRELU) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
+          }
+          uint8_t* buf = stage_begin();
+          if (p.has_outF) stage_f32(buf, lane, v);
+          if (p.has_outB) {
+            if (p.ones_col >= col && p.ones_col < col + 32) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (col + i == p.ones_col) v[i] = 1.0f;
+            }
+            stage_bf16(buf + 4096, lane, v);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
+            if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+          }
+          stage_end();
+        }
+      } else if (EPI == KAIR_EPI_GELU) {
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+            }
+          }
+          uint8_t* buf = stage_begin();
+          if (p.has_outB2) stage_bf16(buf, lane, v);  // pre-activation u
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+          if (p.ones_col >= col && p.ones_col < col + 32) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col + i == p.ones_col) v[i] = 1.0f;
+          }
+          stage_bf16(buf + 4096, lane, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.has_outB2) tma_store_chunk<kConv>(p, &p.tmOutB2, buf, t, q, col);
+            tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+          }
+          stage_end();
+        }
+      } else if (EPI == KAIR_EPI_RESID_LN) {
+        // pass A: v = acc + bias + resid -> outF, keep v in TMEM, accumulate row sum
+        float s1 = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
+              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+            }
+          }
+          if (p.resid && tok >= 0) {
+            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 r4 = __ldg(rp + i);
+              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) s1 += v[i];
+          {
+            uint32_t r[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+            tmem_st32(tacc + c * 32, r);
+          }
+          if (p.has_outF) {
+            uint8_t* buf = stage_begin();
+            stage_f32(buf, lane, v);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
+            stage_end();
+          }
+        }
+        tmem_st_wait();
+        float tot, dummy;
+        exchange2(s1, 0.f, tot, dummy);
+        const float mean = tot * inv_n;
+        // pass B: centred second moment (padding columns hold exact zeros -> subtract their mean^2 contribution)
+        float s2 = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          uint32_t r[32];
+          tmem_ld32(tacc + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float d = __uint_as_float(r[i]) - mean;
+            s2 += d * d;
+          }
+        }
+        float tot2;
+        exchange2(s2, 0.f, tot2, dummy);
+        tot2 -= (float)(p.n_tiles * BN - p.n_valid) * mean * mean;
+        const float rstd = rsqrtf(fmaxf(tot2, 0.f) * inv_n + p.ln_eps);
+        if (hf == 0 && tok >= 0 && p.rowstat) p.rowstat[tok] = rstd;
+        // pass C: xhat -> bf16
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float x = (__uint_as_float(r[i]) - mean) * rstd;
+              int cg = col + i;
+              v[i] = cg < p.n_valid ? x : (cg == p.ones_col ? 1.0f : 0.0f);
+            }
+          }
+          uint8_t* buf = stage_begin();
+          stage_bf16(buf + 4096, lane, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+          stage_end();
+        }
+      } else if (EPI == KAIR_EPI_DGELU) {
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          uint4 u4[4];
+          if (tok >= 0) {
+            const uint4* up = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) u4[i] = __ldg(up + i);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) u4[i] = make_uint4(0, 0, 0, 0);
+          }
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          }
+          const __nv_bfloat162* ub = reinterpret_cast<const __nv_bfloat162*>(u4);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float2 u2 = __bfloat1622float2(ub[i]);
+            v[2 * i] *= gelu_erf_grad(u2.x);
+            v[2 * i + 1] *= gelu_erf_grad(u2.y);
+          }
+          uint8_t* buf = stage_begin();
+          stage_bf16(buf + 4096, lane, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+          stage_end();
+        }
+      } else if (EPI == KAIR_EPI_LNBWD) {
+        // pass A: s1 = sum(acc), s2 = sum(acc * xhat)
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          uint4 x4[4];
+          if (tok >= 0) {
+            const uint4* xp = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x4[i] = __ldg(xp + i);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x4[i] = make_uint4(0, 0, 0, 0);
+          }
+          uint32_t r[32];
+          tmem_ld32(tacc + c * 32, r);
+          tmem_ld_wait();
+          const __nv_bfloat162* xb = reinterpret_cast<const __nv_bfloat162*>(x4);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float2 x2 = __bfloat1622float2(xb[i]);
+            float a0 = __uint_as_float(r[2 * i]), a1 = __uint_as_float(r[2 * i + 1]);
+            s1 += a0 + a1;
+            s2 += a0 * x2.x + a1 * x2.y;
+          }
+        }
+        float t1, t2;
+        exchange2(s1, s2, t1, t2);
+        const float m1 = t1 * inv_n, m2 = t2 * inv_n;
+        const float rstd = (tok >= 0) ? p.rowstat[tok] : 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int col = col_half + c * 32;
+          float v[32];
+          uint4 x4[4];
+          if (tok >= 0) {
+            const uint4* xp = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x4[i] = __ldg(xp + i);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x4[i] = make_uint4(0, 0, 0, 0);
+          }
+          {
+            uint32_t r[32];
+            tmem_ld32(tacc + c * 32, r);
+            tmem_ld_wait();
+            const __nv_bfloat162* xb = reinterpret_cast<const __nv_bfloat162*>(x4);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              float2 x2 = __bfloat1622float2(xb[i]);
+              v[2 * i] = rstd * (__uint_as_float(r[2 * i]) - m1 - x2.x * m2);
+              v[2 * i + 1] = rstd * (__uint_as_float(r[2 * i + 1]) - m1 - x2.y * m2);
+            }
+          }
+          if (p.resid && tok >= 0) {
+            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 r4 = __ldg(rp + i);
+              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (col + i >= p.n_valid) v[i] = 0.f;
+          uint8_t* buf = stage_begin();
+          if (p.has_outF) stage_f32(buf, lane, v);
+          if (p.has_outB) stage_bf16(buf + 4096, lane, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
+            if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+          }
+          stage_end();
+        }
+      }
+      // release the accumulator stage back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+    }
+    if (lane == 0) tma_store_wait_all<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+
+template <int BN, int EPI, bool kConv, bool kBRes>
+static int launch_cfg(const TnParams& p, int grid, size_t smem, cudaStream_t st) {
+  auto kern = gemm_tn_kernel<BN, EPI, kConv, kBRes>;
+  static bool attr_set[64] = {false};  // per instantiation and device; benign race (idempotent)
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set[dev & 63] = true;
+  }
+  kern<<<grid, TN_THREADS, smem, st>>>(p);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int BN, int EPI, bool kConv>
+static int launch_res(const TnParams& p, bool bres, int grid, size_t smem, cudaStream_t st) {
+  if (bres) return launch_cfg<BN, EPI, kConv, true>(p, grid, smem, st);
+  return launch_cfg<BN, EPI, kConv, false>(p, grid, smem, st);
+}
+
+// Instantiated configurations (kept explicit to bound compile time):
+//   dense: every epilogue at BN=192 (SwinIR-M, C=180 padded to 192); LINEAR at BN 64/128/256
+//   conv : LINEAR at BN 64/128/192/256; RESID_LN at BN=192
+static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool bres, int grid, size_t smem,
+                           cudaStream_t st) {
+#define KB_CASE(BN_, EPI_, CONV_) \
+  if (bn == BN_ && epi == EPI_ && conv == CONV_) return launch_res<BN_, EPI_, CONV_>(p, bres, grid, smem, st);
+  KB_CASE(192, KAIR_EPI_LINEAR, false)
+  KB_CASE(192, KAIR_EPI_GELU, false)
+  KB_CASE(192, KAIR_EPI_RESID_LN, false)
+  KB_CASE(192, KAIR_EPI_DGELU, false)
+  KB_CASE(192, KAIR_EPI_LNBWD, false)
+  KB_CASE(64, KAIR_EPI_LINEAR, false)
+  KB_CASE(128, KAIR_EPI_LINEAR, false)
+  KB_CASE(256, KAIR_EPI_LINEAR, false)
+  KB_CASE(64, KAIR_EPI_LINEAR, true)
+  KB_CASE(128, KAIR_EPI_LINEAR, true)
+  KB_CASE(192, KAIR_EPI_LINEAR, true)
+  KB_CASE(256, KAIR_EPI_LINEAR, true)
+  KB_CASE(192, KAIR_EPI_RESID_LN, true)
+#undef KB_CASE
+  set_error("kair_gemm_tn: configuration bn=%d mode=%d conv=%d is not instantiated", bn, epi, (int)conv);
+  return -1;
+}
+
+static int conv_tile_w(int W) {
+  // widest power-of-two tile row <= min(W, 128); the tile is TW x (128/TW) pixels
+  int tw = 128;
+  while (tw > 8 && tw > W) tw >>= 1;
+  return tw;
+}
+
+int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
+  KB_CHECK(a.A && a.B, "kair_gemm_tn: null operand");
+  KB_CHECK(a.K > 0 && a.K % 64 == 0, "kair_gemm_tn: K=%d must be a positive multiple of 64", a.K);
+  KB_CHECK(a.bn == 64 || a.bn == 128 || a.bn == 192 || a.bn == 256, "kair_gemm_tn: bn=%d unsupported", a.bn);
+  KB_CHECK(a.N > 0 && a.N % a.bn == 0, "kair_gemm_tn: N=%d must be a multiple of bn=%d", a.N, a.bn);
+  KB_CHECK(a.a_pitch % 8 == 0 && a.b_pitch % 8 == 0, "kair_gemm_tn: operand pitches must be multiples of 8 elements");
+  KB_CHECK(a.M > 0, "kair_gemm_tn: empty M");
+  if (a.mode == KAIR_EPI_RESID_LN || a.mode == KAIR_EPI_LNBWD)
+    KB_CHECK(a.N == a.bn, "kair_gemm_tn: LayerNorm epilogues need the whole row in one tile (N == bn)");
+  if (a.mode == KAIR_EPI_LNBWD || a.mode == KAIR_EPI_DGELU) KB_CHECK(a.aux != nullptr, "kair_gemm_tn: aux required");
+  if (a.mode == KAIR_EPI_LNBWD) KB_CHECK(a.rowstat != nullptr, "kair_gemm_tn: rowstat required");
+  if (check_device() != 0) return -3;
+
+  TnParams p;
+  memset(&p, 0, sizeof(p));
+  const int taps = a.conv ? 9 : 1;
+  p.bias = a.bias;
+  p.resid = a.resid;
+  p.aux = (const bf16*)a.aux;
+  p.rowstat = a.rowstat;
+  p.resid_pitch = a.resid_pitch;
+  p.aux_pitch = a.aux_pitch;
+  p.M = a.M;
+  p.n_tiles = a.N / a.bn;
+  p.kc = a.K / 64;
+  p.taps = taps;
+  p.n_valid = a.n_valid > 0 ? a.n_valid : a.N;
+  p.ones_col = a.ones_col;
+  p.act = a.act;
+  p.act_slope = a.act_slope;
+  p.ln_eps = a.ln_eps;
+  p.has_outB = a.outB != nullptr;
+  p.has_outB2 = a.outB2 != nullptr;
+  p.has_outF = a.outF != nullptr;
+
+  if (a.conv) {
+    KB_CHECK(a.batch > 0 && a.H > 0 && a.W > 0 && (long long)a.batch * a.H * a.W == a.M,
+             "kair_gemm_tn: conv geometry %dx%dx%d does not match M=%d", a.batch, a.H, a.W, a.M);
+    p.H = a.H;
+    p.W = a.W;
+    p.TW = conv_tile_w(a.W);
+    p.TH = 128 / p.TW;
+    p.tiles_w = (a.W + p.TW - 1) / p.TW;
+    p.tiles_h = (a.H + p.TH - 1) / p.TH;
+    p.m_tiles = a.batch * p.tiles_w * p.tiles_h;
+    uint64_t dims[4] = {(uint64_t)a.K, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.a_pitch * 2 * a.W, (uint64_t)a.a_pitch * 2 * a.W * a.H};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH, 1};
+    if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.A, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  } else {
+    p.m_tiles = (a.M + TN_BM - 1) / TN_BM;
+    uint64_t dims[2] = {(uint64_t)a.K, (uint64_t)a.M};
+    uint64_t str[1] = {(uint64_t)a.a_pitch * 2};
+    uint32_t box[2] = {64, 128};
+    if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.A, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)a.K * taps, (uint64_t)a.N};
+    uint64_t str[1] = {(uint64_t)a.b_pitch * 2};
+    uint32_t box[2] = {64, (uint32_t)a.bn};
+    if (make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a.B, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+  // output maps: per-warp 32-row x 32-col boxes
+  auto make_out = [&](CUtensorMap* tm, const void* ptr, long long pitch, bool f32) -> int {
+    const int esz = f32 ? 4 : 2;
+    KB_CHECK((pitch * esz) % 16 == 0, "kair_gemm_tn: output pitch must be a multiple of 16 bytes");
+    CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    CUtensorMapSwizzle sw = f32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if (a.conv) {
+      uint64_t dims[4] = {(uint64_t)a.N, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+      uint64_t str[3] = {(uint64_t)pitch * esz, (uint64_t)pitch * esz * a.W, (uint64_t)pitch * esz * a.W * a.H};
+      uint32_t bw = p.TW >= 32 ? 32 : p.TW;
+      uint32_t box[4] = {32, bw, 32 / bw, 1};
+      return make_tmap(tm, dt, 4, ptr, dims, str, box, nullptr, sw);
+    } else {
+      uint64_t dims[2] = {(uint64_t)a.N, (uint64_t)a.M};
+      uint64_t str[1] = {(uint64_t)pitch * esz};
+      uint32_t box[2] = {32, 32};
+      return make_tmap(tm, dt, 2, ptr, dims, str, box, nullptr, sw);
+    }
+  };
+  if (a.outB && make_out(&p.tmOutB, a.outB, a.outB_pitch, false)) return -2;
+  if (a.outB2 && make_out(&p.tmOutB2, a.outB2, a.outB2_pitch, false)) return -2;
+  if (a.outF && make_out(&p.tmOutF, a.outF, a.outF_pitch, true)) return -2;
+
+  // shared memory plan
+  const int k_total = p.kc * taps;
+  const int b_stage = a.bn * 64 * 2;
+  const int budget = 232448 - 1024 - TN_STG_BYTES - TN_MISC_BYTES;
+  bool bres = false;
+  int stages = 0;
+  {
+    long long bres_bytes = (long long)k_total * b_stage;
+    int st_res = (int)((budget - bres_bytes) / TN_A_STAGE);
+    if (bres_bytes < budget && st_res >= 3) {
+      bres = true;
+      stages = st_res;
+    } else {
+      stages = budget / (TN_A_STAGE + b_stage);
+    }
+  }
+  if (stages > TN_MAX_STAGES) stages = TN_MAX_STAGES;
+  KB_CHECK(stages >= 2, "kair_gemm_tn: not enough shared memory for bn=%d", a.bn);
+  p.stages = stages;
+  size_t smem = 1024 + TN_STG_BYTES + (size_t)stages * TN_A_STAGE +
+                (size_t)(bres ? k_total : stages) * b_stage + TN_MISC_BYTES;
+
+  int nsm = sm_count();
+  long long total_tiles = (long long)p.m_tiles * p.n_tiles;
+  int grid = (int)(total_tiles < nsm ? total_tiles : nsm);
+  grid = (grid / p.n_tiles) * p.n_tiles;
+  KB_CHECK(grid >= p.n_tiles, "kair_gemm_tn: n_tiles=%d exceeds the SM count", p.n_tiles);
+
+  return launch_dispatch(p, a.bn, a.mode, a.conv != 0, bres, grid, smem, st);
+}
+
+}  // namespace kb

@@ -1,0 +1,41 @@
+// Host-side helpers shared by the launchers: error reporting and TMA tensor-map encoding.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+namespace kb {
+
+// thread-local last error string (returned through kair_last_error())
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define KB_CHECK(cond, ...)          \
+  do {                               \
+    if (!(cond)) {                   \
+      kb::set_error(__VA_ARGS__);    \
+      return -1;                     \
+    }                                \
+  } while (0)
+
+#define KB_CUDA(expr)                                                                   \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      kb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return (int)_e;                                                                   \
+    }                                                                                   \
+  } while (0)
+
+// Encode a tiled tensor map. dims/box are innermost-first; strides_bytes has rank-1 entries (dims 1..rank-1).
+// elem_strides may be null (all 1). Returns 0 on success.
+int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
+              CUtensorMapSwizzle swizzle);
+
+int sm_count();
+int check_device();  // 0 if current device is sm_100; error otherwise
+
+}  // namespace kb
