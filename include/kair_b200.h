@@ -106,6 +106,31 @@ typedef struct kair_gemm_nt_args {
 
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * kair_window_attn_fwd / _bwd: shifted-window multi-head attention core (8x8 windows, head_dim padded to 32).
+ *   out[t, h*32+d] = sum_j softmax_j(q_i.k_j + table[rel(i,j)][h] + mask(i,j)) v_j
+ * qkv holds [q | k | v] per token with columns [3][nH][32]; q is already multiplied by head_dim^-0.5.
+ * Window partition / reverse (network_swinir.py:33-62), the cyclic shift (:249-252, 269-272) and the shifted-window
+ * mask (:216-237, values {0,-100}) are index arithmetic inside the kernel; `table` is relative_position_bias_table
+ * (:89-90, 127-130) in its state_dict layout.  Backward returns d(qkv) and accumulates d(table) (fp32, caller zeroes).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_window_attn_args {
+  const void* qkv;   /* bf16 [B*H*W][qkv_pitch] */
+  int64_t qkv_pitch;
+  void* out;         /* bf16 [B*H*W][out_pitch] (forward output) */
+  int64_t out_pitch;
+  const float* table; /* fp32 [(2*window-1)^2][num_heads] */
+  const void* dout;  /* bf16, backward only */
+  int64_t dout_pitch;
+  void* dqkv;        /* bf16, backward only */
+  int64_t dqkv_pitch;
+  float* dtable;     /* fp32 [(2*window-1)^2][num_heads], backward only, accumulated */
+  int32_t batch, H, W;
+  int32_t num_heads, window, shift;
+} kair_window_attn_args;
+
+int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,19 @@ class GemmNtArgs(ctypes.Structure):
     ]
 
 
+class WindowAttnArgs(ctypes.Structure):
+    _fields_ = [
+        ("qkv", c_ptr), ("qkv_pitch", c_i64),
+        ("out", c_ptr), ("out_pitch", c_i64),
+        ("table", c_ptr),
+        ("dout", c_ptr), ("dout_pitch", c_i64),
+        ("dqkv", c_ptr), ("dqkv_pitch", c_i64),
+        ("dtable", c_ptr),
+        ("batch", c_i32), ("H", c_i32), ("W", c_i32),
+        ("num_heads", c_i32), ("window", c_i32), ("shift", c_i32),
+    ]
+
+
 # name -> (restype, argtypes); every symbol of include/kair_b200.h must be listed here (tests check it)
 SIGNATURES = {
     "kair_last_error": (ctypes.c_char_p, []),
@@ -50,6 +63,7 @@ SIGNATURES = {
     "kair_check_device": (ctypes.c_int, []),
     "kair_gemm_tn": (ctypes.c_int, [ctypes.POINTER(GemmTnArgs), c_ptr]),
     "kair_gemm_nt": (ctypes.c_int, [ctypes.POINTER(GemmNtArgs), c_ptr]),
+    "kair_window_attn_fwd": (ctypes.c_int, [ctypes.POINTER(WindowAttnArgs), c_ptr]),
 }
 
 _lib = None

@@ -1,0 +1,402 @@
+// kair_window_attn_fwd: fused shifted-window attention core on tcgen05 / TMEM.
+//
+//   out[t, h*32+d] = sum_j softmax_j( q_i . k_j + bias[h][rel(i,j)] + mask(i,j) ) * v_j        (q pre-scaled)
+//
+// One CTA iteration handles a PAIR of 8x8 windows (128 tokens = one UMMA M tile).  Window partition, the cyclic
+// shift (torch.roll) and window reverse are pure TMA coordinates: each window is fetched / written as four 4x4-pixel
+// quadrant boxes at ((wi*8 + qy*4 + shift) mod H, (wj*8 + qx*4 + shift) mod W), which never straddle the image
+// border.  The shifted-window mask is evaluated in closed form (regions are constant per quadrant) and the
+// relative-position bias is gathered from the (2ws-1)^2 x nH table held in shared memory.
+//
+//   warp 0       TMA producer: per head pair, Q/K/V tiles [128 tok x 64 ch] (SWIZZLE_128B), double buffered
+//   warp 1       MMA issuer:   per window S_h = Q_h K_h^T (UMMA 64x64x32) and O_h = P_h V_h (64x32x64); the two windows
+//                              of the pair are interleaved in TMEM lanes (M=64 atoms use 16 lanes per sub-partition,
+//                              the second window is issued at lane offset 16)
+//   warps 2..9   softmax:      two groups (even / odd heads); thread == query row; TMEM -> regs, bias + mask, exp2,
+//                              P (bf16) -> swizzled smem; final 1/rowsum scaling, bf16 conversion, TMA scatter
+//
+// Replaces models/network_swinir.py:124-142 (q@k^T, bias gather :127-130, mask :132-135, softmax :136-138, attn@v)
+// together with window_partition/window_reverse (:33-62), torch.roll (:249-252, :269-272) and calculate_mask
+// (:216-237).
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+constexpr int AF_THREADS = 320;
+constexpr int AF_STAGE = 3 * 16384;     // Q, K, V tiles of one head pair
+constexpr int AF_P_BYTES = 16384;       // [2 windows x 64 rows][64 keys] bf16, SWIZZLE_128B
+constexpr int AF_MAX_HEADS = 8;
+
+struct AttnFwdParams {
+  CUtensorMap tmQKV, tmOut;
+  const float* table;  // [(2*8-1)^2][nH]
+  int nH, H, W, nWh, nWw, shift, total_windows, pairs;
+};
+
+__device__ __forceinline__ void window_origin(const AttnFwdParams& p, int gw, int& b, int& wi, int& wj) {
+  int nW = p.nWh * p.nWw;
+  b = gw / nW;
+  int r = gw - b * nW;
+  wi = r / p.nWw;
+  wj = r - wi * p.nWw;
+}
+
+__global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __grid_constant__ AttnFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* qkv_s = smem;                        // 2 stages x 48 KiB
+  uint8_t* p_s = qkv_s + 2 * AF_STAGE;          // 2 x 32 KiB
+  uint8_t* out_s = p_s + 2 * AF_P_BYTES;        // [128 x nH*32] bf16 as nH/2 atoms of 16 KiB
+  uint8_t* misc = out_s + (p.nH / 2) * 16384;
+  uint64_t* qkv_full = reinterpret_cast<uint64_t*>(misc);
+  uint64_t* qkv_empty = qkv_full + 2;
+  uint64_t* s_full = qkv_empty + 2;
+  uint64_t* s_empty = s_full + 2;
+  uint64_t* p_full = s_empty + 2;
+  uint64_t* p_empty = p_full + 2;
+  uint64_t* o_full = p_empty + 2;
+  uint64_t* o_empty = o_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 1);
+  float* table_s = reinterpret_cast<float*>(misc + 256);  // [nH][225]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nH = p.nH;
+  const int hpairs = nH / 2;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmQKV);
+    tma_prefetch_desc(&p.tmOut);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&qkv_full[i], 1);
+        mbar_init(&qkv_empty[i], 1);
+        mbar_init(&s_full[i], 1);
+        mbar_init(&s_empty[i], 4);
+        mbar_init(&p_full[i], 4);
+        mbar_init(&p_empty[i], 1);
+      }
+      mbar_init(o_full, 1);
+      mbar_init(o_empty, 8);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  // bias table -> smem as [h][idx]
+  for (int i = threadIdx.x; i < 225 * nH; i += AF_THREADS) {
+    int idx = i / nH, h = i - idx * nH;
+    table_s[h * 225 + idx] = p.table[i];
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_S = tmem_base;         // 2 x 64 columns
+  const uint32_t tmem_O = tmem_base + 128;   // nH x 32 columns
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x) {
+        int gw0 = pair * 2;
+        int gw1 = gw0 + 1 < p.total_windows ? gw0 + 1 : gw0;
+        int wb[2], wi[2], wj[2];
+        window_origin(p, gw0, wb[0], wi[0], wj[0]);
+        window_origin(p, gw1, wb[1], wi[1], wj[1]);
+        for (int hp = 0; hp < hpairs; ++hp) {
+          mbar_wait(&qkv_empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&qkv_full[stage], AF_STAGE);
+          uint8_t* st = qkv_s + stage * AF_STAGE;
+#pragma unroll
+          for (int t3 = 0; t3 < 3; ++t3) {
+            const int col = t3 * nH * 32 + hp * 64;
+#pragma unroll
+            for (int wq = 0; wq < 8; ++wq) {
+              const int wsel = wq >> 2, quad = wq & 3;
+              const int hh = (wi[wsel] * 8 + (quad >> 1) * 4 + p.shift) % p.H;
+              const int ww = (wj[wsel] * 8 + (quad & 1) * 4 + p.shift) % p.W;
+              tma_load_4d(st + t3 * 16384 + wq * 2048, &p.tmQKV, &qkv_full[stage], col, ww, hh, wb[wsel]);
+            }
+          }
+          if (++stage == 2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(64, 32, 0, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t use[2] = {0, 0};  // per S/P buffer use counters
+      uint32_t pair_it = 0;
+      for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
+        for (int hp = 0; hp < hpairs; ++hp) {
+          mbar_wait(&qkv_full[stage], phase);
+          tcgen05_fence_after();
+          const uint32_t q_addr = smem_u32(qkv_s + stage * AF_STAGE);
+          const uint32_t k_addr = q_addr + 16384;
+          const uint32_t v_addr = q_addr + 32768;
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            mbar_wait(&s_empty[b], (use[b] & 1) ^ 1);
+            tcgen05_fence_after();
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+#pragma unroll
+              for (int k = 0; k < 2; ++k) {
+                umma_f16_ss(tmem_S + b * 64 + ((uint32_t)(w * 16) << 16),
+                            make_desc_kmajor_sw128(q_addr + w * 8192 + b * 64 + k * 32),
+                            make_desc_kmajor_sw128(k_addr + w * 8192 + b * 64 + k * 32), idesc_s, k);
+              }
+            }
+            umma_commit(&s_full[b]);
+          }
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            const int h = hp * 2 + b;
+            mbar_wait(&p_full[b], use[b] & 1);
+            tcgen05_fence_after();
+            if (h == 0) {
+              mbar_wait(o_empty, (pair_it & 1) ^ 1);
+              tcgen05_fence_after();
+            }
+            const uint32_t pa = smem_u32(p_s + b * AF_P_BYTES);
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {
+                umma_f16_ss(tmem_O + h * 32 + ((uint32_t)(w * 16) << 16),
+                            make_desc_kmajor_sw128(pa + w * 8192 + kk * 32),
+                            make_desc_mnmajor_sw128(v_addr + w * 8192 + kk * 2048 + b * 64, 64), idesc_pv, kk);
+              }
+            }
+            umma_commit(&p_empty[b]);
+            use[b]++;
+          }
+          umma_commit(&qkv_empty[stage]);
+          if (++stage == 2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(o_full);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================================ softmax / epilogue ================================
+    const int q = warp & 3;
+    const int g = (warp - 2) >> 2;  // head parity handled by this group
+    // M=64 accumulators: TMEM lane 32q + l holds row 16q + (l & 15) of window (l >> 4)
+    const int wsel = lane >> 4;
+    const int i = q * 16 + (lane & 15);  // in-window index, quadrant-major (== quadrant q)
+    const int row = wsel * 64 + i;       // row of the 128-row smem tiles
+    const int quad_i = i >> 4;
+    const int ry = (quad_i >> 1) * 4 + ((i & 15) >> 2);
+    const int rx = (quad_i & 1) * 4 + (i & 3);
+    const int base_i = ry * 15 + rx;
+    const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
+    uint32_t use = 0;
+    uint32_t pair_it = 0;
+    const float LOG2E = 1.4426950408889634f;
+
+    for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
+      const int gw0 = pair * 2;
+      const bool second_valid = gw0 + 1 < p.total_windows;
+      const int gw = (wsel && second_valid) ? gw0 + 1 : gw0;
+      int wb, wi, wj;
+      window_origin(p, gw, wb, wi, wj);
+      const bool lastrow = p.shift > 0 && wi == p.nWh - 1;
+      const bool lastcol = p.shift > 0 && wj == p.nWw - 1;
+      float madd[4];
+#pragma unroll
+      for (int qj = 0; qj < 4; ++qj) {
+        bool m = (lastrow && ((qj >> 1) != (quad_i >> 1))) || (lastcol && ((qj & 1) != (quad_i & 1)));
+        madd[qj] = m ? -100.0f : 0.0f;
+      }
+      float inv_sum[AF_MAX_HEADS / 2];
+
+      for (int hh = 0; hh < nH / 2; ++hh, ++use) {
+        const int h = hh * 2 + g;
+        const float* tb = table_s + h * 225 + base_i;
+        mbar_wait(&s_full[g], use & 1);
+        tcgen05_fence_after();
+        float s[64];
+        {
+          uint32_t r0[32], r1[32];
+          tmem_ld32(tmem_S + lane_sel + g * 64, r0);
+          tmem_ld32(tmem_S + lane_sel + g * 64 + 32, r1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            s[j] = __uint_as_float(r0[j]);
+            s[32 + j] = __uint_as_float(r1[j]);
+          }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[g]);
+        float mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          const int qj = j >> 4;
+          const int jy = (qj >> 1) * 4 + ((j & 15) >> 2);
+          const int jx = (qj & 1) * 4 + (j & 3);
+          s[j] = s[j] + tb[(7 - jy) * 15 + (7 - jx)] + madd[qj];
+          mx = fmaxf(mx, s[j]);
+        }
+        float sum = 0.f;
+        uint32_t pk[32];
+        const float mb = mx * LOG2E;
+#pragma unroll
+        for (int j = 0; j < 64; j += 2) {
+          float e0 = exp2f(s[j] * LOG2E - mb);
+          float e1 = exp2f(s[j + 1] * LOG2E - mb);
+          __nv_bfloat162 b2 = __floats2bfloat162_rn(e0, e1);
+          float2 f2 = __bfloat1622float2(b2);
+          sum += f2.x + f2.y;  // normalise by the sum of the values the tensor core will actually see
+          pk[j >> 1] = *reinterpret_cast<uint32_t*>(&b2);
+        }
+        inv_sum[hh] = 1.0f / sum;
+        mbar_wait(&p_empty[g], (use & 1) ^ 1);
+        {
+          const uint32_t base = smem_u32(p_s + g * AF_P_BYTES) + row * 128;
+          const uint32_t sw = row & 7;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint32_t a = base + ((c ^ sw) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pk[4 * c]), "r"(pk[4 * c + 1]),
+                         "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
+                         : "memory");
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[g]);
+      }
+
+      // ---- epilogue: O * 1/rowsum -> bf16 -> staging -> TMA scatter to the windows' pixels
+      mbar_wait(o_full, pair_it & 1);
+      tcgen05_fence_after();
+      if (warp == 2 && lane == 0) tma_store_wait_read<0>();
+      named_bar_sync(2, 256);
+      for (int hh = 0; hh < nH / 2; ++hh) {
+        const int h = hh * 2 + g;
+        uint32_t r[32];
+        tmem_ld32(tmem_O + lane_sel + h * 32, r);
+        tmem_ld_wait();
+        const float sc = inv_sum[hh];
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * sc;
+        const uint32_t base = smem_u32(out_s + (h >> 1) * 16384) + row * 128;
+        const uint32_t sw = row & 7;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t a = base + ((((h & 1) * 4 + c) ^ sw) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(v[8 * c], v[8 * c + 1])),
+                       "r"(pack_bf16x2(v[8 * c + 2], v[8 * c + 3])), "r"(pack_bf16x2(v[8 * c + 4], v[8 * c + 5])),
+                       "r"(pack_bf16x2(v[8 * c + 6], v[8 * c + 7]))
+                       : "memory");
+        }
+      }
+      fence_proxy_async_smem();
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_empty);
+      named_bar_sync(2, 256);
+      if (warp == 2 && lane == 0) {
+        for (int ws2 = 0; ws2 < (second_valid ? 2 : 1); ++ws2) {
+          int b2, wi2, wj2;
+          window_origin(p, gw0 + ws2, b2, wi2, wj2);
+          for (int quad = 0; quad < 4; ++quad) {
+            const int hh2 = (wi2 * 8 + (quad >> 1) * 4 + p.shift) % p.H;
+            const int ww2 = (wj2 * 8 + (quad & 1) * 4 + p.shift) % p.W;
+            for (int a = 0; a < hpairs; ++a)
+              tma_store_4d(&p.tmOut, out_s + a * 16384 + (ws2 * 4 + quad) * 2048, a * 64, ww2, hh2, b2);
+          }
+        }
+        tma_store_commit();
+      }
+    }
+    if (warp == 2 && lane == 0) tma_store_wait_all<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
+  KB_CHECK(a.qkv && a.out && a.table, "kair_window_attn_fwd: null pointer");
+  KB_CHECK(a.window == 8, "kair_window_attn_fwd: only 8x8 windows are supported by the tcgen05 path (got %d)", a.window);
+  KB_CHECK(a.num_heads >= 2 && a.num_heads <= AF_MAX_HEADS && a.num_heads % 2 == 0,
+           "kair_window_attn_fwd: num_heads=%d must be even and <= %d", a.num_heads, AF_MAX_HEADS);
+  KB_CHECK(a.H % 8 == 0 && a.W % 8 == 0 && a.H > 0 && a.W > 0, "kair_window_attn_fwd: H,W must be multiples of 8");
+  KB_CHECK(a.shift == 0 || a.shift == 4, "kair_window_attn_fwd: shift must be 0 or 4");
+  KB_CHECK(a.qkv_pitch % 8 == 0 && a.out_pitch % 8 == 0, "kair_window_attn_fwd: pitches must be multiples of 8");
+  KB_CHECK(a.qkv_pitch >= 3 * a.num_heads * 32 && a.out_pitch >= a.num_heads * 32, "kair_window_attn_fwd: pitch too small");
+  if (check_device() != 0) return -3;
+
+  AttnFwdParams p;
+  memset(&p, 0, sizeof(p));
+  p.table = a.table;
+  p.nH = a.num_heads;
+  p.H = a.H;
+  p.W = a.W;
+  p.nWh = a.H / 8;
+  p.nWw = a.W / 8;
+  p.shift = a.shift;
+  p.total_windows = a.batch * p.nWh * p.nWw;
+  p.pairs = (p.total_windows + 1) / 2;
+  uint32_t box[4] = {64, 4, 4, 1};
+  {
+    uint64_t dims[4] = {(uint64_t)3 * a.num_heads * 32, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)a.qkv_pitch * 2, (uint64_t)a.qkv_pitch * 2 * a.W, (uint64_t)a.qkv_pitch * 2 * a.W * a.H};
+    if (make_tmap(&p.tmQKV, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.qkv, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)a.num_heads * 32, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)a.out_pitch * 2, (uint64_t)a.out_pitch * 2 * a.W, (uint64_t)a.out_pitch * 2 * a.W * a.H};
+    if (make_tmap(&p.tmOut, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.out, dims, str, box, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+  const size_t smem = 1024 + 2 * AF_STAGE + 2 * AF_P_BYTES + (size_t)(a.num_heads / 2) * 16384 + 256 + (size_t)a.num_heads * 225 * 4 + 64;
+  KB_CHECK(smem <= 232448, "kair_window_attn_fwd: shared memory plan exceeds 227 KiB (num_heads=%d)", a.num_heads);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(window_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set[dev & 63] = true;
+  }
+  int grid = p.pairs < sm_count() ? p.pairs : sm_count();
+  window_attn_fwd_kernel<<<grid, AF_THREADS, smem, st>>>(p);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace kb

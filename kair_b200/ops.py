@@ -79,3 +79,23 @@ def gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
         a.conv = 0
         a.T = A.shape[0]
     _lib.check(_lib.load().kair_gemm_nt(ctypes.byref(a), _stream()), "gemm_nt")
+
+
+def _attn_args(qkv, table, batch, H, W, num_heads, window, shift):
+    _req(qkv, torch.bfloat16, "qkv"); _req(table, torch.float32, "table")
+    if not table.is_contiguous():
+        raise RuntimeError("kair_b200: relative_position_bias_table must be contiguous")
+    a = _lib.WindowAttnArgs()
+    a.qkv = _ptr(qkv); a.qkv_pitch = _pitch(qkv)
+    a.table = _ptr(table)
+    a.batch, a.H, a.W = batch, H, W
+    a.num_heads, a.window, a.shift = num_heads, window, shift
+    return a
+
+
+def window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
+    """out[t, h*32:(h+1)*32] = windowed softmax attention; qkv: bf16 [B*H*W, >=3*nH*32] in [3][nH][32] layout."""
+    _req(out, torch.bfloat16, "out")
+    a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
+    a.out = _ptr(out); a.out_pitch = _pitch(out)
+    _lib.check(_lib.load().kair_window_attn_fwd(ctypes.byref(a), _stream()), "window_attn_fwd")

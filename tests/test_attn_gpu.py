@@ -1,0 +1,62 @@
+"""Fused tcgen05 window attention vs a plain PyTorch fp32 evaluation of network_swinir.py:124-142 (+ roll/partition)."""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def _ref_attention(qkv, table, B, H, W, nH, shift, hd=32):
+    """qkv: fp32 [B*H*W, 3*nH*hd] (q pre-scaled). Returns ([B*H*W, nH*hd], P) computed window by window."""
+    from oracle import swinir_oracle as so
+    ws = 8
+    N = ws * ws
+    idx = so.window_token_index(H, W, ws, shift).to(qkv.device)            # (nW, N)
+    nW = idx.shape[0]
+    x = qkv.view(B, H * W, 3, nH, hd)[:, idx.reshape(-1)]                    # (B, nW*N, 3, nH, hd)
+    x = x.view(B * nW, N, 3, nH, hd).permute(2, 0, 3, 1, 4)                  # (3, B_, nH, N, hd)
+    q, k, v = x[0], x[1], x[2]
+    attn = q @ k.transpose(-2, -1)
+    rpi = so.relative_position_index(ws).to(qkv.device).reshape(-1)
+    bias = table[rpi].view(N, N, nH).permute(2, 0, 1)
+    attn = attn + bias.unsqueeze(0)
+    if shift > 0:
+        mask = so.shift_mask(H, W, ws, shift).to(qkv.device)
+        attn = attn.view(B, nW, nH, N, N) + mask[None, :, None]
+        attn = attn.view(-1, nH, N, N)
+    attn = attn.softmax(-1)
+    o = (attn @ v).transpose(1, 2).reshape(B, nW * N, nH * hd)               # windows order
+    out = torch.empty(B, H * W, nH * hd, device=qkv.device)
+    out[:, idx.reshape(-1)] = o
+    return out.view(B * H * W, nH * hd)
+
+
+def _make_qkv(B, H, W, nH, seed, dev):
+    g = torch.Generator().manual_seed(seed)
+    T = B * H * W
+    qkv = torch.randn(T, 3 * nH * 32, generator=g) * 0.8
+    qkv = qkv.view(T, 3, nH, 32)
+    qkv[..., 30:] = 0          # head_dim 30 padded to 32
+    qkv[:, 2, 0, 30] = 1.0     # ones column of v (head 0) used for the proj bias gradient
+    qkv = qkv.view(T, -1)
+    table = torch.randn(225, nH, generator=g) * 0.5
+    return qkv.to(dev).bfloat16(), table.to(dev)
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 16, 24), (1, 24, 24), (1, 8, 8), (3, 32, 16)])
+@pytest.mark.parametrize("shift", [0, 4])
+def test_window_attn_fwd(B, H, W, shift):
+    from kair_b200 import ops
+    dev = torch.device("cuda:0")
+    nH = 6
+    qkv, table = _make_qkv(B, H, W, nH, 100 + H + W + shift, dev)
+    out = torch.zeros(B * H * W, nH * 32, dtype=torch.bfloat16, device=dev)
+    ops.window_attn_fwd(qkv, table, out, batch=B, H=H, W=W, num_heads=nH, shift=shift)
+    torch.cuda.synchronize()
+    ref = _ref_attention(qkv.float(), table, B, H, W, nH, shift)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 3e-2, err
+    assert (out.view(-1, nH, 32)[:, 0, 30].float() - 1.0).abs().max().item() < 2e-2
