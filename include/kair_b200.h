@@ -130,6 +130,7 @@ typedef struct kair_window_attn_args {
 } kair_window_attn_args;
 
 int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream);
+int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream);
 
 #ifdef __cplusplus
 }

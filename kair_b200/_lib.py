@@ -64,6 +64,7 @@ SIGNATURES = {
     "kair_gemm_tn": (ctypes.c_int, [ctypes.POINTER(GemmTnArgs), c_ptr]),
     "kair_gemm_nt": (ctypes.c_int, [ctypes.POINTER(GemmNtArgs), c_ptr]),
     "kair_window_attn_fwd": (ctypes.c_int, [ctypes.POINTER(WindowAttnArgs), c_ptr]),
+    "kair_window_attn_bwd": (ctypes.c_int, [ctypes.POINTER(WindowAttnArgs), c_ptr]),
 }
 
 _lib = None

@@ -7,6 +7,7 @@ namespace kb {
 int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st);
 int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st);
 int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st);
+int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st);
 }
 
 extern "C" {
@@ -37,6 +38,14 @@ int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream) {
     return -1;
   }
   return kb::window_attn_fwd_launch(*args, (cudaStream_t)stream);
+}
+
+int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream) {
+  if (!args) {
+    kb::set_error("kair_window_attn_bwd: null args");
+    return -1;
+  }
+  return kb::window_attn_bwd_launch(*args, (cudaStream_t)stream);
 }
 
 }  // extern "C"

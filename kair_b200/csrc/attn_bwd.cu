@@ -1,0 +1,475 @@
+// kair_window_attn_bwd: backward of the fused shifted-window attention core on tcgen05 / TMEM.
+//
+// Per window and head (q pre-scaled, P = softmax(q k^T + bias + mask) recomputed, nothing but q,k,v was saved):
+//   dP = dO V^T,  delta_i = sum_j P_ij dP_ij,  dS = P o (dP - delta)
+//   dV = P^T dO,  dQ = dS K,  dK = dS^T Q,  d_table[rel(i,j), h] += dS_ij
+// Every transposed product reads the SAME shared-memory tile through an MN-major UMMA descriptor (P and dS are
+// written once, K-major, and consumed both as K-major and as MN-major operands), so no transposes are materialised.
+//
+//   warp 0      TMA producer: Q, K, V, dO tiles [2 windows x 64 tok][64 ch = 2 heads] per (window pair, head pair)
+//   warp 1      MMA issuer (UMMA M=64 per window; the two windows of a pair interleave in TMEM lanes)
+//   warps 2..9  two groups (even / odd head of the pair), thread == query row: softmax recompute, delta, dS,
+//               P/dS -> swizzled smem, d_table partial sums kept in TMEM, dQ/dK/dV -> bf16 -> TMA scatter
+//
+// Loop order is head-pair outermost so the per-row d_table partial sums (64 columns per head) stay resident in
+// TMEM for the whole pass over the windows.
+//
+// Replaces autograd's backward of models/network_swinir.py:124-142 (+ :33-62, :249-252, :269-272, :216-237).
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+constexpr int AB_THREADS = 320;
+constexpr int AB_STAGE = 4 * 16384;   // Q, K, V, dO tiles of one head pair
+constexpr int AB_PDS = 32768;         // per group: P (16 KiB) + dS (16 KiB); reused as dq/dk/dv staging (24 KiB)
+
+struct AttnBwdParams {
+  CUtensorMap tmQKV, tmDO, tmDQKV;
+  const float* table;
+  float* dtable;
+  int nH, H, W, nWh, nWw, shift, total_windows, pairs;
+};
+
+__device__ __forceinline__ void ab_window_origin(const AttnBwdParams& p, int gw, int& b, int& wi, int& wj) {
+  int nW = p.nWh * p.nWw;
+  b = gw / nW;
+  int r = gw - b * nW;
+  wi = r / p.nWw;
+  wj = r - wi * p.nWw;
+}
+
+__global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __grid_constant__ AttnBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* stage_s = smem;                   // 2 x 64 KiB
+  uint8_t* pds_s = stage_s + 2 * AB_STAGE;   // 2 groups x 32 KiB
+  uint8_t* misc = pds_s + 2 * AB_PDS;
+  uint64_t* st_full = reinterpret_cast<uint64_t*>(misc);
+  uint64_t* st_empty = st_full + 2;
+  uint64_t* sdp_full = st_empty + 2;
+  uint64_t* pds_full = sdp_full + 2;
+  uint64_t* grad_full = pds_full + 2;
+  uint64_t* w_free = grad_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_free + 2);
+  float* table_s = reinterpret_cast<float*>(misc + 256);   // [nH][225]
+  float* dtab_s = table_s + p.nH * 225;                     // [2][225]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nH = p.nH;
+  const int hpairs = nH / 2;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmQKV);
+    tma_prefetch_desc(&p.tmDO);
+    tma_prefetch_desc(&p.tmDQKV);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&st_full[i], 1);
+        mbar_init(&st_empty[i], 1);
+        mbar_init(&sdp_full[i], 1);
+        mbar_init(&pds_full[i], 4);
+        mbar_init(&grad_full[i], 1);
+        mbar_init(&w_free[i], 4);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  for (int i = threadIdx.x; i < 225 * nH; i += AB_THREADS) {
+    int idx = i / nH, h = i - idx * nH;
+    table_s[h * 225 + idx] = p.table[i];
+  }
+  for (int i = threadIdx.x; i < 2 * 225; i += AB_THREADS) dtab_s[i] = 0.f;
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  // per group g: W_g = tmem_base + g*128 (S | dP, later dV | dQ | dK), ACC_g = tmem_base + 256 + g*64
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int hp = 0; hp < hpairs; ++hp) {
+        for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x) {
+          int gw0 = pair * 2;
+          int gw1 = gw0 + 1 < p.total_windows ? gw0 + 1 : gw0;
+          int wb[2], wi[2], wj[2];
+          ab_window_origin(p, gw0, wb[0], wi[0], wj[0]);
+          ab_window_origin(p, gw1, wb[1], wi[1], wj[1]);
+          mbar_wait(&st_empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&st_full[stage], AB_STAGE);
+          uint8_t* st = stage_s + stage * AB_STAGE;
+#pragma unroll
+          for (int wq = 0; wq < 8; ++wq) {
+            const int wsel = wq >> 2, quad = wq & 3;
+            const int hh = (wi[wsel] * 8 + (quad >> 1) * 4 + p.shift) % p.H;
+            const int ww = (wj[wsel] * 8 + (quad & 1) * 4 + p.shift) % p.W;
+#pragma unroll
+            for (int t3 = 0; t3 < 3; ++t3)
+              tma_load_4d(st + t3 * 16384 + wq * 2048, &p.tmQKV, &st_full[stage], t3 * nH * 32 + hp * 64, ww, hh,
+                          wb[wsel]);
+            tma_load_4d(st + 3 * 16384 + wq * 2048, &p.tmDO, &st_full[stage], hp * 64, ww, hh, wb[wsel]);
+          }
+          if (++stage == 2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);    // S, dP
+      constexpr uint32_t idesc_dv = make_idesc_bf16(64, 32, 1, 1);   // P^T dO, dS^T Q
+      constexpr uint32_t idesc_dq = make_idesc_bf16(64, 32, 0, 1);   // dS K
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t it = 0;
+      for (int hp = 0; hp < hpairs; ++hp) {
+        for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++it) {
+          mbar_wait(&st_full[stage], phase);
+          tcgen05_fence_after();
+          const uint32_t q_addr = smem_u32(stage_s + stage * AB_STAGE);
+          const uint32_t k_addr = q_addr + 16384;
+          const uint32_t v_addr = q_addr + 32768;
+          const uint32_t do_addr = q_addr + 49152;
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            mbar_wait(&w_free[g], (it & 1) ^ 1);
+            tcgen05_fence_after();
+            const uint32_t tw = tmem_base + g * 128;
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+              const uint32_t lo = (uint32_t)(w * 16) << 16;
+#pragma unroll
+              for (int k = 0; k < 2; ++k) {
+                umma_f16_ss(tw + lo, make_desc_kmajor_sw128(q_addr + w * 8192 + g * 64 + k * 32),
+                            make_desc_kmajor_sw128(k_addr + w * 8192 + g * 64 + k * 32), idesc_s, k);
+              }
+#pragma unroll
+              for (int k = 0; k < 2; ++k) {
+                umma_f16_ss(tw + 64 + lo, make_desc_kmajor_sw128(do_addr + w * 8192 + g * 64 + k * 32),
+                            make_desc_kmajor_sw128(v_addr + w * 8192 + g * 64 + k * 32), idesc_s, k);
+              }
+            }
+            umma_commit(&sdp_full[g]);
+          }
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            mbar_wait(&pds_full[g], it & 1);
+            tcgen05_fence_after();
+            const uint32_t tw = tmem_base + g * 128;
+            const uint32_t p_addr = smem_u32(pds_s + g * AB_PDS);
+            const uint32_t ds_addr = p_addr + 16384;
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+              const uint32_t lo = (uint32_t)(w * 16) << 16;
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {  // dV[j,d] = sum_i P[i,j] dO[i,d]
+                umma_f16_ss(tw + lo, make_desc_mnmajor_sw128(p_addr + w * 8192 + kk * 2048, 64),
+                            make_desc_mnmajor_sw128(do_addr + w * 8192 + kk * 2048 + g * 64, 64), idesc_dv, kk);
+              }
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {  // dQ[i,d] = sum_j dS[i,j] K[j,d]
+                umma_f16_ss(tw + 32 + lo, make_desc_kmajor_sw128(ds_addr + w * 8192 + kk * 32),
+                            make_desc_mnmajor_sw128(k_addr + w * 8192 + kk * 2048 + g * 64, 64), idesc_dq, kk);
+              }
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {  // dK[j,d] = sum_i dS[i,j] Q[i,d]
+                umma_f16_ss(tw + 64 + lo, make_desc_mnmajor_sw128(ds_addr + w * 8192 + kk * 2048, 64),
+                            make_desc_mnmajor_sw128(q_addr + w * 8192 + kk * 2048 + g * 64, 64), idesc_dv, kk);
+              }
+            }
+            umma_commit(&grad_full[g]);
+          }
+          umma_commit(&st_empty[stage]);
+          if (++stage == 2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================================ softmax-recompute / gradient warps ================================
+    const int q = warp & 3;
+    const int g = (warp - 2) >> 2;
+    const int gtid = ((warp - 2) & 3) * 32 + lane;  // thread index inside the group
+    const int wsel = lane >> 4;
+    const int i = q * 16 + (lane & 15);
+    const int row = wsel * 64 + i;
+    const int quad_i = q;
+    const int ry = (quad_i >> 1) * 4 + ((i & 15) >> 2);
+    const int rx = (quad_i & 1) * 4 + (i & 3);
+    const int base_i = ry * 15 + rx;
+    const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
+    const uint32_t tW = tmem_base + lane_sel + g * 128;
+    const uint32_t tACC = tmem_base + lane_sel + 256 + g * 64;
+    uint8_t* pds = pds_s + g * AB_PDS;
+    const float LOG2E = 1.4426950408889634f;
+    uint32_t it = 0;
+
+    for (int hp = 0; hp < hpairs; ++hp) {
+      const int h = hp * 2 + g;
+      const float* tb = table_s + h * 225 + base_i;
+      {  // zero the d_table partial sums of this pass
+        uint32_t z[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) z[j] = 0u;
+        tmem_st32(tACC, z);
+        tmem_st32(tACC + 32, z);
+        tmem_st_wait();
+      }
+      for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++it) {
+        const int gw0 = pair * 2;
+        const bool second_valid = gw0 + 1 < p.total_windows;
+        const bool my_valid = (wsel == 0) || second_valid;
+        const int gw = (wsel && second_valid) ? gw0 + 1 : gw0;
+        int wb, wi, wj;
+        ab_window_origin(p, gw, wb, wi, wj);
+        const bool lastrow = p.shift > 0 && wi == p.nWh - 1;
+        const bool lastcol = p.shift > 0 && wj == p.nWw - 1;
+        float madd[4];
+#pragma unroll
+        for (int qj = 0; qj < 4; ++qj) {
+          bool m = (lastrow && ((qj >> 1) != (quad_i >> 1))) || (lastcol && ((qj & 1) != (quad_i & 1)));
+          madd[qj] = m ? -100.0f : 0.0f;
+        }
+
+        // ---- A/B: S -> normalised P (fp32 registers)
+        mbar_wait(&sdp_full[g], it & 1);
+        tcgen05_fence_after();
+        float pr[64];
+        {
+          uint32_t r0[32], r1[32];
+          tmem_ld32(tW, r0);
+          tmem_ld32(tW + 32, r1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            pr[j] = __uint_as_float(r0[j]);
+            pr[32 + j] = __uint_as_float(r1[j]);
+          }
+        }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          const int qj = j >> 4;
+          const int jy = (qj >> 1) * 4 + ((j & 15) >> 2);
+          const int jx = (qj & 1) * 4 + (j & 3);
+          pr[j] = pr[j] + tb[(7 - jy) * 15 + (7 - jx)] + madd[qj];
+          mx = fmaxf(mx, pr[j]);
+        }
+        float sum = 0.f;
+        const float mb = mx * LOG2E;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          pr[j] = exp2f(pr[j] * LOG2E - mb);
+          sum += pr[j];
+        }
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) pr[j] *= inv;
+
+        // ---- C: delta = sum_j P_ij dP_ij
+        float delta = 0.f;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32];
+          tmem_ld32(tW + 64 + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) delta += pr[c * 32 + j] * __uint_as_float(r[j]);
+        }
+
+        // ---- D: the P/dS tiles double as the previous iteration's output staging: wait for its TMA reads
+        if (gtid == 0) tma_store_wait_read<0>();
+        named_bar_sync(2 + g, 128);
+
+        // ---- E: dS, d_table partial sums, P/dS -> smem
+        const float vmask = my_valid ? 1.0f : 0.0f;
+        const uint32_t prow = smem_u32(pds) + row * 128;
+        const uint32_t dsrow = prow + 16384;
+        const uint32_t sw = row & 7;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32], a[32];
+          tmem_ld32(tW + 64 + c * 32, r);
+          tmem_ld32(tACC + c * 32, a);
+          tmem_ld_wait();
+          float ds[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            ds[j] = pr[c * 32 + j] * (__uint_as_float(r[j]) - delta) * vmask;
+            a[j] = __float_as_uint(__uint_as_float(a[j]) + ds[j]);
+          }
+          tmem_st32(tACC + c * 32, a);
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc) {
+            const uint32_t off = (((c * 4 + cc) ^ sw) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dsrow + off),
+                         "r"(pack_bf16x2(ds[8 * cc], ds[8 * cc + 1])), "r"(pack_bf16x2(ds[8 * cc + 2], ds[8 * cc + 3])),
+                         "r"(pack_bf16x2(ds[8 * cc + 4], ds[8 * cc + 5])), "r"(pack_bf16x2(ds[8 * cc + 6], ds[8 * cc + 7]))
+                         : "memory");
+            const int o = c * 32 + cc * 8;
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + off),
+                         "r"(pack_bf16x2(pr[o], pr[o + 1])), "r"(pack_bf16x2(pr[o + 2], pr[o + 3])),
+                         "r"(pack_bf16x2(pr[o + 4], pr[o + 5])), "r"(pack_bf16x2(pr[o + 6], pr[o + 7]))
+                         : "memory");
+          }
+        }
+        // ---- F
+        tmem_st_wait();
+        fence_proxy_async_smem();
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pds_full[g]);
+
+        // ---- G: dV | dQ | dK -> bf16 -> staging (64-byte rows, SWIZZLE_64B), tensor order dq, dk, dv
+        mbar_wait(&grad_full[g], it & 1);
+        tcgen05_fence_after();
+        {
+          const uint32_t sw64 = (row >> 1) & 3;
+#pragma unroll
+          for (int t3 = 0; t3 < 3; ++t3) {
+            // TMEM column blocks: 0 = dV, 32 = dQ, 64 = dK ; staging tensors: 0 = dq, 1 = dk, 2 = dv
+            const int tcol = t3 == 0 ? 32 : (t3 == 1 ? 64 : 0);
+            uint32_t r[32];
+            tmem_ld32(tW + tcol, r);
+            tmem_ld_wait();
+            const uint32_t base = smem_u32(pds) + t3 * 8192 + row * 64;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + ((cc ^ sw64) << 4)),
+                           "r"(pack_bf16x2(__uint_as_float(r[8 * cc]), __uint_as_float(r[8 * cc + 1]))),
+                           "r"(pack_bf16x2(__uint_as_float(r[8 * cc + 2]), __uint_as_float(r[8 * cc + 3]))),
+                           "r"(pack_bf16x2(__uint_as_float(r[8 * cc + 4]), __uint_as_float(r[8 * cc + 5]))),
+                           "r"(pack_bf16x2(__uint_as_float(r[8 * cc + 6]), __uint_as_float(r[8 * cc + 7])))
+                           : "memory");
+            }
+          }
+        }
+        // ---- H
+        fence_proxy_async_smem();
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&w_free[g]);
+        named_bar_sync(2 + g, 128);
+        if (gtid == 0) {
+          for (int ws2 = 0; ws2 < (second_valid ? 2 : 1); ++ws2) {
+            int b2, wi2, wj2;
+            ab_window_origin(p, gw0 + ws2, b2, wi2, wj2);
+            for (int quad = 0; quad < 4; ++quad) {
+              const int hh2 = (wi2 * 8 + (quad >> 1) * 4 + p.shift) % p.H;
+              const int ww2 = (wj2 * 8 + (quad & 1) * 4 + p.shift) % p.W;
+#pragma unroll
+              for (int t3 = 0; t3 < 3; ++t3)
+                tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws2 * 4 + quad) * 1024, t3 * nH * 32 + h * 32, ww2, hh2,
+                             b2);
+            }
+          }
+          tma_store_commit();
+        }
+      }
+
+      // ---- end of pass: fold the per-row partial sums into d_table[:, h]
+      {
+        float* dt = dtab_s + g * 225;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t a[32];
+          tmem_ld32(tACC + c * 32, a);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int jj = c * 32 + j;
+            const int qj = jj >> 4;
+            const int jy = (qj >> 1) * 4 + ((jj & 15) >> 2);
+            const int jx = (qj & 1) * 4 + (jj & 3);
+            atomicAdd(&dt[base_i + (7 - jy) * 15 + (7 - jx)], __uint_as_float(a[j]));
+          }
+        }
+        named_bar_sync(2 + g, 128);
+        for (int idx = gtid; idx < 225; idx += 128) {
+          float v = dt[idx];
+          if (v != 0.f) atomicAdd(&p.dtable[idx * nH + h], v);
+          dt[idx] = 0.f;
+        }
+        named_bar_sync(2 + g, 128);
+      }
+    }
+    if (gtid == 0) tma_store_wait_all<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
+  KB_CHECK(a.qkv && a.dout && a.dqkv && a.table && a.dtable, "kair_window_attn_bwd: null pointer");
+  KB_CHECK(a.window == 8, "kair_window_attn_bwd: only 8x8 windows are supported by the tcgen05 path (got %d)", a.window);
+  KB_CHECK(a.num_heads >= 2 && a.num_heads <= 8 && a.num_heads % 2 == 0,
+           "kair_window_attn_bwd: num_heads=%d must be even and <= 8", a.num_heads);
+  KB_CHECK(a.H % 8 == 0 && a.W % 8 == 0 && a.H > 0 && a.W > 0, "kair_window_attn_bwd: H,W must be multiples of 8");
+  KB_CHECK(a.shift == 0 || a.shift == 4, "kair_window_attn_bwd: shift must be 0 or 4");
+  KB_CHECK(a.qkv_pitch % 8 == 0 && a.dout_pitch % 8 == 0 && a.dqkv_pitch % 8 == 0,
+           "kair_window_attn_bwd: pitches must be multiples of 8");
+  if (check_device() != 0) return -3;
+
+  AttnBwdParams p;
+  memset(&p, 0, sizeof(p));
+  p.table = a.table;
+  p.dtable = a.dtable;
+  p.nH = a.num_heads;
+  p.H = a.H;
+  p.W = a.W;
+  p.nWh = a.H / 8;
+  p.nWw = a.W / 8;
+  p.shift = a.shift;
+  p.total_windows = a.batch * p.nWh * p.nWw;
+  p.pairs = (p.total_windows + 1) / 2;
+  auto map4 = [&](CUtensorMap* tm, const void* ptr, long long pitch, int cols, uint32_t boxc, CUtensorMapSwizzle sw) {
+    uint64_t dims[4] = {(uint64_t)cols, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)pitch * 2, (uint64_t)pitch * 2 * a.W, (uint64_t)pitch * 2 * a.W * a.H};
+    uint32_t box[4] = {boxc, 4, 4, 1};
+    return make_tmap(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, str, box, nullptr, sw);
+  };
+  if (map4(&p.tmQKV, a.qkv, a.qkv_pitch, 3 * a.num_heads * 32, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return -2;
+  if (map4(&p.tmDO, a.dout, a.dout_pitch, a.num_heads * 32, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return -2;
+  if (map4(&p.tmDQKV, a.dqkv, a.dqkv_pitch, 3 * a.num_heads * 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return -2;
+
+  const size_t smem = 1024 + 2 * AB_STAGE + 2 * AB_PDS + 256 + (size_t)a.num_heads * 225 * 4 + 2 * 225 * 4 + 64;
+  KB_CHECK(smem <= 232448, "kair_window_attn_bwd: shared memory plan exceeds 227 KiB");
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(window_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    attr_set[dev & 63] = true;
+  }
+  int grid = p.pairs < sm_count() ? p.pairs : sm_count();
+  window_attn_bwd_kernel<<<grid, AB_THREADS, smem, st>>>(p);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace kb

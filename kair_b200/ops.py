@@ -99,3 +99,13 @@ def window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.out = _ptr(out); a.out_pitch = _pitch(out)
     _lib.check(_lib.load().kair_window_attn_fwd(ctypes.byref(a), _stream()), "window_attn_fwd")
+
+
+def window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
+    """Backward of window_attn_fwd: writes dqkv (bf16) and accumulates into dtable (fp32, caller zeroes)."""
+    _req(dout, torch.bfloat16, "dout"); _req(dqkv, torch.bfloat16, "dqkv"); _req(dtable, torch.float32, "dtable")
+    a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
+    a.dout = _ptr(dout); a.dout_pitch = _pitch(dout)
+    a.dqkv = _ptr(dqkv); a.dqkv_pitch = _pitch(dqkv)
+    a.dtable = _ptr(dtable)
+    _lib.check(_lib.load().kair_window_attn_bwd(ctypes.byref(a), _stream()), "window_attn_bwd")

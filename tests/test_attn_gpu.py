@@ -60,3 +60,27 @@ def test_window_attn_fwd(B, H, W, shift):
     err = (out.float() - ref).abs().max().item()
     assert err < 3e-2, err
     assert (out.view(-1, nH, 32)[:, 0, 30].float() - 1.0).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 16, 24), (1, 24, 24), (1, 8, 8), (2, 64, 64)])
+@pytest.mark.parametrize("shift", [0, 4])
+def test_window_attn_bwd(B, H, W, shift):
+    from kair_b200 import ops
+    dev = torch.device("cuda:0")
+    nH = 6
+    qkv, table = _make_qkv(B, H, W, nH, 300 + H + W + shift, dev)
+    g = torch.Generator().manual_seed(17)
+    dout = (torch.randn(B * H * W, nH * 32, generator=g) * 0.5).to(dev).bfloat16()
+    dqkv = torch.zeros_like(qkv)
+    dtable = torch.zeros_like(table)
+    ops.window_attn_bwd(qkv, table, dout, dqkv, dtable, batch=B, H=H, W=W, num_heads=nH, shift=shift)
+    torch.cuda.synchronize()
+    qf = qkv.float().requires_grad_(True)
+    tf = table.clone().requires_grad_(True)
+    ref = _ref_attention(qf, tf, B, H, W, nH, shift)
+    (ref * dout.float()).sum().backward()
+    gq = qf.grad
+    e1 = (dqkv.float() - gq).abs().max().item() / (gq.abs().max().item() + 1e-9)
+    e2 = (dtable - tf.grad).abs().max().item() / (tf.grad.abs().max().item() + 1e-9)
+    assert e1 < 2e-2, ("dqkv", e1)
+    assert e2 < 2e-2, ("dtable", e2)
