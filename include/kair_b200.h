@@ -77,6 +77,12 @@ typedef struct kair_gemm_tn_args {
   int32_t ones_col;  /* column of outB forced to 1.0 (bias-gradient trick), -1 for none */
   int32_t conv;      /* 0 dense, 1 conv3x3 */
   int32_t batch, H, W;
+  /* DropPath (network_swinir.py:204, 276-277; per-sample Bernoulli / keep_prob): sample = token / tokens_per_sample.
+   * acc_scale[sample] multiplies (acc + bias) before the residual is added (LINEAR, RESID_LN);
+   * outB_scale[sample] multiplies only the bf16 copy outB (LINEAR, LNBWD) -- the gradient entering the next branch. */
+  const float* acc_scale;
+  const float* outB_scale;
+  int32_t tokens_per_sample;
 } kair_gemm_tn_args;
 
 int kair_gemm_tn(const kair_gemm_tn_args* args, void* stream);
@@ -131,6 +137,153 @@ typedef struct kair_window_attn_args {
 
 int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream);
 int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Weight packing.  fp32 master parameters (state_dict layout) -> padded bf16 GEMM operands, batched over L layers
+ * of identical shape (device arrays of L pointers).
+ *   Wp[l][r][c] = row_scale[r] * W[l][row_map[r]][col_map[c]] * gamma[l][col_map[c]]      (0 where a map is -1)
+ *   bp[l][r]    = row_scale[r] * (b[l][row_map[r]] + sum_k W[l][row_map[r]][k] * beta[l][k]) + bias_const[r]
+ * i.e. the LayerNorm affine (network_swinir.py:199,205) that precedes qkv / fc1 and the q scale (:124) are folded
+ * into the weights, so the GEMM consumes the un-affine normalised activations directly.  WpT is the transpose used
+ * by the input-gradient GEMM.  kair_unpack_linear_grad maps d(Wp) (with d(bp) in column ones_col) back to
+ * dW, db, d(gamma), d(beta) in the parameters' own layouts (overwrites).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_pack_linear_args {
+  const void* const* W;      /* [L] -> fp32 (out_f, in_f) */
+  const void* const* b;      /* [L] -> fp32 (out_f), or NULL */
+  const void* const* gamma;  /* [L] -> fp32 (in_f), or NULL */
+  const void* const* beta;   /* [L] -> fp32 (in_f), or NULL */
+  const int32_t* row_map;    /* [N_pad] */
+  const int32_t* col_map;    /* [K_pad] */
+  const float* row_scale;    /* [N_pad] or NULL */
+  const float* bias_const;   /* [N_pad] or NULL */
+  void* Wp;                  /* bf16 [L][N_pad][K_pad] */
+  void* WpT;                 /* bf16 [L][K_pad][N_pad] or NULL */
+  float* bp;                 /* fp32 [L][N_pad] or NULL */
+  int32_t L, N_pad, K_pad, out_f, in_f;
+} kair_pack_linear_args;
+int kair_pack_linear(const kair_pack_linear_args* args, void* stream);
+
+typedef struct kair_unpack_linear_args {
+  const float* dWp;          /* fp32 [L][N_pad][K_pad] */
+  const void* const* W;
+  const void* const* gamma;
+  const void* const* beta;
+  void* const* dW;           /* [L] -> fp32 (out_f, in_f) */
+  void* const* db;           /* [L] -> fp32 (out_f) or NULL */
+  void* const* dgamma;       /* [L] -> fp32 (in_f) or NULL */
+  void* const* dbeta;
+  const int32_t* row_map;
+  const int32_t* col_map;
+  const float* row_scale;
+  int32_t L, N_pad, K_pad, out_f, in_f, ones_col;
+} kair_unpack_linear_args;
+int kair_unpack_linear_grad(const kair_unpack_linear_args* args, void* stream);
+
+/* conv weights (O, I, kh, kw) -> Wp [L][O_pad][taps*I_pad] (k = tap*I_pad + i) and the flipped / channel-swapped
+ * WpT [L][I_pad][taps*O_pad] used by the input-gradient convolution; bp is the zero-padded bias. */
+typedef struct kair_pack_conv_args {
+  const void* const* W;
+  const void* const* b;      /* or NULL */
+  void* Wp;
+  void* WpT;                 /* or NULL */
+  float* bp;                 /* fp32 [L][O_pad] or NULL */
+  int32_t L, O, I, O_pad, I_pad, taps;
+} kair_pack_conv_args;
+int kair_pack_conv(const kair_pack_conv_args* args, void* stream);
+
+typedef struct kair_unpack_conv_args {
+  const float* dWp;          /* fp32 [L][O_pad][taps*I_pad] */
+  void* const* dW;           /* [L] -> fp32 (O, I, kh, kw) */
+  void* const* db;           /* [L] -> fp32 (O) or NULL; taken from column ones_col of the centre tap */
+  int32_t L, O, I, O_pad, I_pad, taps, ones_col, center_tap;
+} kair_unpack_conv_args;
+int kair_unpack_conv_grad(const kair_unpack_conv_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Standalone LayerNorm over C channels of fp32 token rows (nn.LayerNorm(C, eps): network_swinir.py:683, 725).
+ * Outputs are optional: affine result in fp32 / bf16, un-affine xhat in bf16, per-row mean and rstd.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_layernorm_args {
+  const float* x;
+  const float* gamma;
+  const float* beta;
+  float* y_f32;
+  void* y_bf16;
+  void* xhat_bf16;
+  float* mean;
+  float* rstd;
+  int64_t T;
+  int32_t C, pitch, ones_col;
+  float eps;
+} kair_layernorm_args;
+int kair_layernorm_fwd(const kair_layernorm_args* args, void* stream);
+
+typedef struct kair_layernorm_bwd_args {
+  const float* dy_f32;   /* either or both; summed */
+  const void* dy_bf16;
+  const float* x;
+  const float* mean;
+  const float* rstd;
+  const float* gamma;
+  const float* dx_add;   /* optional residual gradient added to dx */
+  float* dx_f32;
+  void* dx_bf16;
+  float* dgamma;         /* accumulated (caller zeroes) */
+  float* dbeta;
+  int64_t T;
+  int32_t C, pitch;
+} kair_layernorm_bwd_args;
+int kair_layernorm_bwd(const kair_layernorm_bwd_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Thin 3x3 convolutions between NCHW fp32 images (<= 4 channels) and token features.
+ *   conv_in : feat[t][o] = act(b[o] + sum W[o][c][tap] * ((img[c][p+tap] - mean[c]) * range))
+ *             (SwinIR.conv_first with the (x - mean) * img_range of network_swinir.py:809-810, :669;
+ *              DnCNN / DRUNet head: basicblock.py:65, network_dncnn.py:63, network_unet.py:25)
+ *   conv_out: out[c][p] = (b[c] + sum W[c][k][tap] * feat[p+tap][k] + skip_scale*(skip[c][p]-skip_mean[c]))
+ *                          * out_scale + out_mean[c]
+ *             (conv_last + "x + ..." + "/ img_range + mean": network_swinir.py:762, :835-837; DnCNN tail + x - n)
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_conv_in_args {
+  const float* img;      /* (B, ci, H, W) */
+  const float* W;        /* weights (O, ci, 3, 3) */
+  const float* b;        /* (O) or NULL */
+  const float* mean;     /* (ci) */
+  float* out_f32;        /* [T][pitch] or NULL */
+  void* out_bf16;        /* [T][pitch] or NULL */
+  const float* dy_f32;   /* wgrad only */
+  const void* dy_bf16;   /* wgrad only */
+  float* dW;             /* wgrad only, accumulated (caller zeroes) */
+  float* db;
+  float range, act_slope;
+  int32_t batch, ci, H, Wd /* width */, O, O_pad, pitch, act, ones_col;
+} kair_conv_in_args;
+int kair_conv_in_fwd(const kair_conv_in_args* args, void* stream);
+int kair_conv_in_wgrad(const kair_conv_in_args* args, void* stream);
+
+typedef struct kair_conv_out_args {
+  const void* feat;      /* bf16 [T][pitch] */
+  const float* W;        /* weights (co, C, 3, 3) */
+  const float* b;        /* (co) or NULL */
+  const float* skip;     /* (B, co, H, W) or NULL */
+  const float* skip_mean;/* (co) */
+  const float* out_mean; /* (co) */
+  float* out;            /* (B, co, H, W) */
+  const float* dout;     /* backward: d(out) */
+  float* dfeat_f32;      /* dgrad outputs [T][pitch] */
+  void* dfeat_bf16;
+  float* dW;             /* wgrad, accumulated (caller zeroes) */
+  float* db;
+  float skip_scale, out_scale;
+  int32_t batch, co, H, Wd /* width */, C, pitch;
+} kair_conv_out_args;
+int kair_conv_out_fwd(const kair_conv_out_args* args, void* stream);
+int kair_conv_out_dgrad(const kair_conv_out_args* args, void* stream);
+int kair_conv_out_wgrad(const kair_conv_out_args* args, void* stream);
+
+/* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
+int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,71 +1,66 @@
-"""ctypes binding of the C-ABI library (include/kair_b200.h).
+"""ctypes binding of the C-ABI library, generated from include/kair_b200.h.
 
-The library is built in-tree by kair_b200/build.py (nvcc, sm_100a).  There is no fallback: if the shared object is
-missing or a call fails, a RuntimeError is raised.
+The header is the single source of truth: argument structs and function prototypes are parsed from it, so the
+Python side cannot drift from the C side.  The library itself is built in-tree by kair_b200/build.py (nvcc,
+sm_100a).  There is no fallback: a missing library or a failing call raises RuntimeError.
 """
 import ctypes
 import os
+import re
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libkair_b200.so")
+HEADER_PATH = os.path.join(_HERE, "..", "include", "kair_b200.h")
 
-c_i32 = ctypes.c_int32
-c_i64 = ctypes.c_int64
-c_f32 = ctypes.c_float
-c_ptr = ctypes.c_void_p
-
-
-class GemmTnArgs(ctypes.Structure):
-    _fields_ = [
-        ("A", c_ptr), ("a_pitch", c_i64),
-        ("B", c_ptr), ("b_pitch", c_i64),
-        ("M", c_i32), ("N", c_i32), ("K", c_i32), ("bn", c_i32),
-        ("mode", c_i32), ("act", c_i32), ("act_slope", c_f32), ("ln_eps", c_f32),
-        ("bias", c_ptr), ("resid", c_ptr), ("resid_pitch", c_i64),
-        ("aux", c_ptr), ("aux_pitch", c_i64),
-        ("rowstat", c_ptr),
-        ("outB", c_ptr), ("outB_pitch", c_i64),
-        ("outB2", c_ptr), ("outB2_pitch", c_i64),
-        ("outF", c_ptr), ("outF_pitch", c_i64),
-        ("n_valid", c_i32), ("ones_col", c_i32), ("conv", c_i32),
-        ("batch", c_i32), ("H", c_i32), ("W", c_i32),
-    ]
-
-
-class GemmNtArgs(ctypes.Structure):
-    _fields_ = [
-        ("A", c_ptr), ("a_pitch", c_i64),
-        ("B", c_ptr), ("b_pitch", c_i64),
-        ("D", c_ptr), ("d_pitch", c_i64),
-        ("T", c_i32), ("n1", c_i32), ("n2", c_i32), ("bn", c_i32), ("splits", c_i32),
-        ("conv", c_i32), ("batch", c_i32), ("H", c_i32), ("W", c_i32),
-    ]
-
-
-class WindowAttnArgs(ctypes.Structure):
-    _fields_ = [
-        ("qkv", c_ptr), ("qkv_pitch", c_i64),
-        ("out", c_ptr), ("out_pitch", c_i64),
-        ("table", c_ptr),
-        ("dout", c_ptr), ("dout_pitch", c_i64),
-        ("dqkv", c_ptr), ("dqkv_pitch", c_i64),
-        ("dtable", c_ptr),
-        ("batch", c_i32), ("H", c_i32), ("W", c_i32),
-        ("num_heads", c_i32), ("window", c_i32), ("shift", c_i32),
-    ]
-
-
-# name -> (restype, argtypes); every symbol of include/kair_b200.h must be listed here (tests check it)
-SIGNATURES = {
-    "kair_last_error": (ctypes.c_char_p, []),
-    "kair_version": (ctypes.c_int, []),
-    "kair_check_device": (ctypes.c_int, []),
-    "kair_gemm_tn": (ctypes.c_int, [ctypes.POINTER(GemmTnArgs), c_ptr]),
-    "kair_gemm_nt": (ctypes.c_int, [ctypes.POINTER(GemmNtArgs), c_ptr]),
-    "kair_window_attn_fwd": (ctypes.c_int, [ctypes.POINTER(WindowAttnArgs), c_ptr]),
-    "kair_window_attn_bwd": (ctypes.c_int, [ctypes.POINTER(WindowAttnArgs), c_ptr]),
+_SCALARS = {
+    "int32_t": ctypes.c_int32, "int64_t": ctypes.c_int64, "float": ctypes.c_float, "int": ctypes.c_int,
+    "double": ctypes.c_double, "uint32_t": ctypes.c_uint32,
 }
+
+
+def _strip_comments(src):
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    return re.sub(r"//[^\n]*", " ", src)
+
+
+def _parse_header(path):
+    src = _strip_comments(open(path).read())
+    structs = {}
+    for m in re.finditer(r"typedef\s+struct\s+(\w+)\s*\{(.*?)\}\s*(\w+)\s*;", src, flags=re.S):
+        name, body = m.group(3), m.group(2)
+        fields = []
+        for decl in body.split(";"):
+            decl = " ".join(decl.split())
+            if not decl:
+                continue
+            if "*" in decl:
+                # every pointer flavour is passed as an opaque address
+                fname = decl.rsplit("*", 1)[1].strip()
+                fields.append((fname, ctypes.c_void_p))
+            else:
+                tname, rest = decl.split(" ", 1)
+                for fname in rest.split(","):
+                    fields.append((fname.strip(), _SCALARS[tname]))
+        structs[name] = type(name, (ctypes.Structure,), {"_fields_": fields})
+    protos = {}
+    for m in re.finditer(r"(const\s+char\s*\*|int)\s+(kair_\w+)\s*\(([^)]*)\)\s*;", src):
+        ret = ctypes.c_char_p if "char" in m.group(1) else ctypes.c_int
+        args = []
+        params = m.group(3).strip()
+        if params and params != "void":
+            for prm in params.split(","):
+                prm = " ".join(prm.split())
+                if "*" in prm:
+                    base = prm.split("*")[0].replace("const", "").strip()
+                    args.append(ctypes.POINTER(structs[base]) if base in structs else ctypes.c_void_p)
+                else:
+                    args.append(_SCALARS[prm.split(" ")[0]])
+        protos[m.group(2)] = (ret, args)
+    return structs, protos
+
+
+STRUCTS, SIGNATURES = _parse_header(HEADER_PATH)
 
 _lib = None
 _lock = threading.Lock()
@@ -96,3 +91,8 @@ def check(rc, what):
     if rc != 0:
         msg = load().kair_last_error()
         raise RuntimeError("kair_b200.%s failed (rc=%d): %s" % (what, rc, msg.decode() if msg else "?"))
+
+
+def call(name, args_struct, stream):
+    """Invoke `int name(const args*, void* stream)` and raise on error."""
+    check(getattr(load(), name)(ctypes.byref(args_struct), stream), name)

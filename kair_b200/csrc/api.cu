@@ -8,6 +8,18 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st);
 int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st);
 int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st);
 int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st);
+int pack_linear_launch(const kair_pack_linear_args& a, cudaStream_t st);
+int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st);
+int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st);
+int unpack_conv_launch(const kair_unpack_conv_args& a, cudaStream_t st);
+int layernorm_fwd_launch(const kair_layernorm_args& a, cudaStream_t st);
+int layernorm_bwd_launch(const kair_layernorm_bwd_args& a, cudaStream_t st);
+int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st);
+int conv_in_wgrad_launch(const kair_conv_in_args& a, cudaStream_t st);
+int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st);
+int conv_out_dgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
+int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
+int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 }
 
 extern "C" {
@@ -46,6 +58,31 @@ int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream) {
     return -1;
   }
   return kb::window_attn_bwd_launch(*args, (cudaStream_t)stream);
+}
+
+#define KB_WRAP(NAME, TYPE, FN)                                  \
+  int NAME(const TYPE* args, void* stream) {                     \
+    if (!args) {                                                 \
+      kb::set_error(#NAME ": null args");                        \
+      return -1;                                                 \
+    }                                                            \
+    return kb::FN(*args, (cudaStream_t)stream);                  \
+  }
+KB_WRAP(kair_pack_linear, kair_pack_linear_args, pack_linear_launch)
+KB_WRAP(kair_unpack_linear_grad, kair_unpack_linear_args, unpack_linear_launch)
+KB_WRAP(kair_pack_conv, kair_pack_conv_args, pack_conv_launch)
+KB_WRAP(kair_unpack_conv_grad, kair_unpack_conv_args, unpack_conv_launch)
+KB_WRAP(kair_layernorm_fwd, kair_layernorm_args, layernorm_fwd_launch)
+KB_WRAP(kair_layernorm_bwd, kair_layernorm_bwd_args, layernorm_bwd_launch)
+KB_WRAP(kair_conv_in_fwd, kair_conv_in_args, conv_in_fwd_launch)
+KB_WRAP(kair_conv_in_wgrad, kair_conv_in_args, conv_in_wgrad_launch)
+KB_WRAP(kair_conv_out_fwd, kair_conv_out_args, conv_out_fwd_launch)
+KB_WRAP(kair_conv_out_dgrad, kair_conv_out_args, conv_out_dgrad_launch)
+KB_WRAP(kair_conv_out_wgrad, kair_conv_out_args, conv_out_wgrad_launch)
+#undef KB_WRAP
+
+int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {
+  return kb::add_inplace_launch(y, x, yb, (long long)n, (cudaStream_t)stream);
 }
 
 }  // extern "C"

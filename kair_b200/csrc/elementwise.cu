@@ -1,0 +1,618 @@
+// Memory-bound helper kernels around the tensor-core path (warp-shuffle reductions, vectorised coalesced access):
+//   * weight packing: fp32 master weights -> padded bf16 GEMM operands (LayerNorm gamma/beta and the q scale folded
+//     in), and the inverse mapping of the packed weight gradients back onto the parameters' own layouts
+//   * standalone LayerNorm forward / backward (patch_embed.norm and the final norm of SwinIR)
+//   * the thin first / last convolutions (1..4 image channels <-> C feature channels), forward and backward
+//   * residual-stream helpers
+// Reference arithmetic: models/network_swinir.py:199,205,683,725 (LayerNorm eps=1e-5), :669 (conv_first),
+// :762 (conv_last), :809-810,:837 (mean / img_range), models/network_dncnn.py:63-71, models/network_unet.py:25,57.
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+// ------------------------------------------------------------------------------------------------ pack linear
+__global__ void pack_linear_kernel(const kair_pack_linear_args a) {
+  const int r = blockIdx.x, l = blockIdx.y;
+  const float* W = reinterpret_cast<const float*>(a.W[l]);
+  const float* b = a.b ? reinterpret_cast<const float*>(a.b[l]) : nullptr;
+  const float* gamma = a.gamma ? reinterpret_cast<const float*>(a.gamma[l]) : nullptr;
+  const float* beta = a.beta ? reinterpret_cast<const float*>(a.beta[l]) : nullptr;
+  const int src = a.row_map[r];
+  const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
+  bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + ((size_t)l * a.N_pad + r) * a.K_pad;
+  bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * a.K_pad * a.N_pad : nullptr;
+  float bacc = 0.f;
+  for (int c = threadIdx.x; c < a.K_pad; c += blockDim.x) {
+    const int k = a.col_map[c];
+    float v = 0.f;
+    if (src >= 0 && k >= 0) {
+      const float w = W[(size_t)src * a.in_f + k];
+      v = w * rs * (gamma ? gamma[k] : 1.0f);
+      if (beta) bacc += w * beta[k];
+    }
+    Wp[c] = __float2bfloat16(v);
+    if (WpT) WpT[(size_t)c * a.N_pad + r] = __float2bfloat16(v);
+  }
+  if (a.bp) {
+    __shared__ float red[32];
+    bacc = warp_sum(bacc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = bacc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < (blockDim.x + 31) / 32; ++i) t += red[i];
+      float bias = 0.f;
+      if (src >= 0) bias = ((b ? b[src] : 0.f) + t) * rs;
+      if (a.bias_const) bias += a.bias_const[r];
+      a.bp[(size_t)l * a.N_pad + r] = bias;
+    }
+  }
+}
+
+int pack_linear_launch(const kair_pack_linear_args& a, cudaStream_t st) {
+  KB_CHECK(a.W && a.row_map && a.col_map && a.Wp, "kair_pack_linear: null pointer");
+  KB_CHECK(a.L > 0 && a.N_pad > 0 && a.K_pad > 0, "kair_pack_linear: bad sizes");
+  pack_linear_kernel<<<dim3(a.N_pad, a.L), 128, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ unpack linear grads
+// dWp = d(loss)/d(Wp) with Wp[r][c] = rs[r] * W[row_map[r]][col_map[c]] * gamma[col_map[c]] and
+// bp[r] = rs[r] * (b[src] + sum_k W[src][k] beta[k]); column `ones_col` of dWp is d(loss)/d(bp).
+__global__ void unpack_linear_dw_kernel(const kair_unpack_linear_args a) {
+  const int r = blockIdx.x, l = blockIdx.y;
+  const int src = a.row_map[r];
+  if (src < 0) return;
+  const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
+  const float* dWp = a.dWp + ((size_t)l * a.N_pad + r) * a.K_pad;
+  const float* gamma = a.gamma ? reinterpret_cast<const float*>(a.gamma[l]) : nullptr;
+  float* dW = reinterpret_cast<float*>(a.dW[l]) + (size_t)src * a.in_f;
+  for (int c = threadIdx.x; c < a.K_pad; c += blockDim.x) {
+    const int k = a.col_map[c];
+    if (k >= 0) dW[k] = dWp[c] * rs * (gamma ? gamma[k] : 1.0f);
+  }
+  if (threadIdx.x == 0 && a.db && a.ones_col >= 0) reinterpret_cast<float*>(a.db[l])[src] = dWp[a.ones_col] * rs;
+}
+
+__global__ void unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, l = blockIdx.y;
+  if (c >= a.K_pad) return;
+  const int k = a.col_map[c];
+  if (k < 0) return;
+  const float* W = reinterpret_cast<const float*>(a.W[l]);
+  const float* dWp = a.dWp + (size_t)l * a.N_pad * a.K_pad;
+  float dg = 0.f, db = 0.f;
+  for (int r = 0; r < a.N_pad; ++r) {
+    const int src = a.row_map[r];
+    if (src < 0) continue;
+    const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
+    const float w = W[(size_t)src * a.in_f + k] * rs;
+    dg += w * dWp[(size_t)r * a.K_pad + c];
+    db += w * dWp[(size_t)r * a.K_pad + a.ones_col];
+  }
+  reinterpret_cast<float*>(a.dgamma[l])[k] = dg;
+  reinterpret_cast<float*>(a.dbeta[l])[k] = db;
+}
+
+int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st) {
+  KB_CHECK(a.dWp && a.dW && a.row_map && a.col_map, "kair_unpack_linear_grad: null pointer");
+  unpack_linear_dw_kernel<<<dim3(a.N_pad, a.L), 128, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  if (a.dgamma && a.dbeta) {
+    KB_CHECK(a.W && a.ones_col >= 0, "kair_unpack_linear_grad: LayerNorm gradients need W and ones_col");
+    unpack_linear_dln_kernel<<<dim3((a.K_pad + 63) / 64, a.L), 64, 0, st>>>(a);
+    KB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ pack conv3x3
+// W (O, I, kh, kw) fp32 -> Wp [O_pad][taps*I_pad] (k = tap*I_pad + i) and, for the input-gradient convolution,
+// WpT [I_pad][taps*O_pad] with WpT[i][tap*O_pad + o] = W[o][i][taps-1-tap] (spatially flipped, channels swapped).
+__global__ void pack_conv_kernel(const kair_pack_conv_args a) {
+  const int l = blockIdx.y;
+  const float* W = reinterpret_cast<const float*>(a.W[l]);
+  const int taps = a.taps;
+  const size_t n = (size_t)a.O_pad * taps * a.I_pad;
+  bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + (size_t)l * n;
+  bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * n : nullptr;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e % a.I_pad);
+    const int tap = (int)((e / a.I_pad) % taps);
+    const int o = (int)(e / ((size_t)a.I_pad * taps));
+    float v = 0.f;
+    if (o < a.O && i < a.I) v = W[((size_t)o * a.I + i) * taps + tap];
+    Wp[e] = __float2bfloat16(v);
+    if (WpT) WpT[((size_t)i * taps + (taps - 1 - tap)) * a.O_pad + o] = __float2bfloat16(v);
+  }
+  if (a.bp && blockIdx.x == 0) {
+    const float* b = a.b ? reinterpret_cast<const float*>(a.b[l]) : nullptr;
+    for (int o = threadIdx.x; o < a.O_pad; o += blockDim.x) a.bp[(size_t)l * a.O_pad + o] = (b && o < a.O) ? b[o] : 0.f;
+  }
+}
+
+int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st) {
+  KB_CHECK(a.W && a.Wp, "kair_pack_conv: null pointer");
+  size_t n = (size_t)a.O_pad * a.taps * a.I_pad;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 1024) blocks = 1024;
+  pack_conv_kernel<<<dim3(blocks, a.L), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
+  const int l = blockIdx.y;
+  const int taps = a.taps;
+  const float* dWp = a.dWp + (size_t)l * a.O_pad * taps * a.I_pad;
+  float* dW = reinterpret_cast<float*>(a.dW[l]);
+  const size_t n = (size_t)a.O * a.I * taps;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    const int tap = (int)(e % taps);
+    const int i = (int)((e / taps) % a.I);
+    const int o = (int)(e / ((size_t)taps * a.I));
+    dW[e] = dWp[((size_t)o * taps + tap) * a.I_pad + i];
+  }
+  if (a.db && a.ones_col >= 0 && blockIdx.x == 0) {
+    float* db = reinterpret_cast<float*>(a.db[l]);
+    for (int o = threadIdx.x; o < a.O; o += blockDim.x)
+      db[o] = dWp[((size_t)o * taps + a.center_tap) * a.I_pad + a.ones_col];
+  }
+}
+
+int unpack_conv_launch(const kair_unpack_conv_args& a, cudaStream_t st) {
+  KB_CHECK(a.dWp && a.dW, "kair_unpack_conv_grad: null pointer");
+  size_t n = (size_t)a.O * a.I * a.taps;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 1024) blocks = 1024;
+  unpack_conv_kernel<<<dim3(blocks, a.L), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm
+// One warp per token row.  x fp32 [T][pitch]; C real channels, padded channels of every output are written as 0
+// (xhat gets 1.0 in `ones_col`).
+__global__ void layernorm_fwd_kernel(const kair_layernorm_args a) {
+  const int warps = blockDim.x >> 5;
+  const long long row = (long long)blockIdx.x * warps + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= a.T) return;
+  const float* x = a.x + row * a.pitch;
+  float v[8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + 32 * i;
+    v[i] = (c < a.C) ? x[c] : 0.f;
+    s += v[i];
+  }
+  const float mean = warp_sum(s) / a.C;
+  float s2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + 32 * i;
+    const float d = (c < a.C) ? v[i] - mean : 0.f;
+    s2 += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(s2) / a.C + a.eps);
+  if (lane == 0) {
+    if (a.mean) a.mean[row] = mean;
+    if (a.rstd) a.rstd[row] = rstd;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + 32 * i;
+    if (c >= a.pitch) continue;
+    const float xh = (c < a.C) ? (v[i] - mean) * rstd : 0.f;
+    const float y = (c < a.C) ? xh * a.gamma[c] + a.beta[c] : 0.f;
+    if (a.y_f32) a.y_f32[row * a.pitch + c] = y;
+    if (a.y_bf16) reinterpret_cast<bf16*>(a.y_bf16)[row * a.pitch + c] = __float2bfloat16(c == a.ones_col ? 1.0f : y);
+    if (a.xhat_bf16)
+      reinterpret_cast<bf16*>(a.xhat_bf16)[row * a.pitch + c] = __float2bfloat16(c == a.ones_col ? 1.0f : xh);
+  }
+}
+
+int layernorm_fwd_launch(const kair_layernorm_args& a, cudaStream_t st) {
+  KB_CHECK(a.x && a.T > 0 && a.C > 0 && a.pitch >= a.C && a.pitch <= 256, "kair_layernorm_fwd: bad arguments");
+  KB_CHECK((a.y_f32 == nullptr && a.y_bf16 == nullptr) || (a.gamma && a.beta), "kair_layernorm_fwd: affine output needs gamma/beta");
+  const int warps = 8;
+  layernorm_fwd_kernel<<<(unsigned)((a.T + warps - 1) / warps), warps * 32, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  dgamma += dy * xhat;  dbeta += dy
+// dy is given as fp32 and/or bf16 (summed when both are present); dx_out = dx (+ dx_add).
+__global__ void layernorm_bwd_kernel(const kair_layernorm_bwd_args a) {
+  __shared__ float sg[256], sb[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+    sg[i] = 0.f;
+    sb[i] = 0.f;
+  }
+  __syncthreads();
+  const int warps = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  float pg[8], pb[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) pg[i] = pb[i] = 0.f;
+  for (long long row = (long long)blockIdx.x * warps + (threadIdx.x >> 5); row < a.T;
+       row += (long long)gridDim.x * warps) {
+    const float mean = a.mean[row], rstd = a.rstd[row];
+    float xh[8], g[8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = lane + 32 * i;
+      xh[i] = 0.f;
+      g[i] = 0.f;
+      if (c < a.C) {
+        float dy = 0.f;
+        if (a.dy_f32) dy += a.dy_f32[row * a.pitch + c];
+        if (a.dy_bf16) dy += __bfloat162float(reinterpret_cast<const bf16*>(a.dy_bf16)[row * a.pitch + c]);
+        xh[i] = (a.x[row * a.pitch + c] - mean) * rstd;
+        pg[i] += dy * xh[i];
+        pb[i] += dy;
+        g[i] = dy * a.gamma[c];
+        s1 += g[i];
+        s2 += g[i] * xh[i];
+      }
+    }
+    const float m1 = warp_sum(s1) / a.C, m2 = warp_sum(s2) / a.C;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = lane + 32 * i;
+      if (c >= a.pitch) continue;
+      float dx = (c < a.C) ? rstd * (g[i] - m1 - xh[i] * m2) : 0.f;
+      if (a.dx_add && c < a.C) dx += a.dx_add[row * a.pitch + c];
+      if (a.dx_f32) a.dx_f32[row * a.pitch + c] = dx;
+      if (a.dx_bf16) reinterpret_cast<bf16*>(a.dx_bf16)[row * a.pitch + c] = __float2bfloat16(dx);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane + 32 * i;
+    if (c < a.C) {
+      atomicAdd(&sg[c], pg[i]);
+      atomicAdd(&sb[c], pb[i]);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+    atomicAdd(&a.dgamma[c], sg[c]);
+    atomicAdd(&a.dbeta[c], sb[c]);
+  }
+}
+
+int layernorm_bwd_launch(const kair_layernorm_bwd_args& a, cudaStream_t st) {
+  KB_CHECK(a.x && a.mean && a.rstd && a.gamma && a.dgamma && a.dbeta && (a.dy_f32 || a.dy_bf16),
+           "kair_layernorm_bwd: null pointer");
+  KB_CHECK(a.pitch <= 256 && a.pitch >= a.C, "kair_layernorm_bwd: bad pitch");
+  int blocks = sm_count() * 4;
+  long long need = (a.T + 7) / 8;
+  if (blocks > need) blocks = (int)need;
+  layernorm_bwd_kernel<<<blocks, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ thin convolutions
+constexpr int CI_MAX = 4;  // image-side channel count handled by the SIMT convolutions
+
+// conv_in: NCHW fp32 image (B, ci, H, W) -> token features [T][pitch]; one warp per pixel, lanes over outputs.
+//   feat[t][o] = act( b[o] + sum_{c,tap} W[o][c][tap] * ((img[c][p+tap] - mean[c]) * range) )
+__global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
+  extern __shared__ float sw[];  // [ci*9][O_pad] weights, then [O_pad] bias
+  const int K = a.ci * 9;
+  for (int e = threadIdx.x; e < K * a.O_pad; e += blockDim.x) {
+    const int o = e % a.O_pad, k = e / a.O_pad;
+    sw[e] = o < a.O ? a.W[(size_t)o * K + k] : 0.f;
+  }
+  float* sbias = sw + K * a.O_pad;
+  for (int o = threadIdx.x; o < a.O_pad; o += blockDim.x) sbias[o] = (o < a.O && a.b) ? a.b[o] : 0.f;
+  __syncthreads();
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+    float in[CI_MAX * 9];
+#pragma unroll
+    for (int c = 0; c < CI_MAX; ++c) {
+      if (c >= a.ci) break;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+        float v = 0.f;
+        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+          v = a.img[(((size_t)b * a.ci + c) * a.H + hh) * a.Wd + ww];
+          v = (v - a.mean[c]) * a.range;
+        }
+        in[c * 9 + tap] = v;
+      }
+    }
+    for (int o = lane; o < a.pitch; o += 32) {
+      float acc = 0.f;
+      if (o < a.O) {
+        acc = sbias[o];
+        for (int k = 0; k < K; ++k) acc += sw[k * a.O_pad + o] * in[k];
+        if (a.act == KAIR_ACT_LRELU) acc = acc > 0.f ? acc : acc * a.act_slope;
+      }
+      if (a.out_f32) a.out_f32[t * a.pitch + o] = acc;
+      if (a.out_bf16) reinterpret_cast<bf16*>(a.out_bf16)[t * a.pitch + o] = __float2bfloat16(o == a.ones_col ? 1.0f : acc);
+    }
+  }
+}
+
+int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st) {
+  KB_CHECK(a.img && a.W && a.mean, "kair_conv_in_fwd: null pointer");
+  KB_CHECK(a.ci >= 1 && a.ci <= CI_MAX, "kair_conv_in_fwd: ci=%d unsupported (max %d)", a.ci, CI_MAX);
+  KB_CHECK(a.O_pad >= a.O && a.pitch >= a.O, "kair_conv_in_fwd: bad padding");
+  size_t smem = ((size_t)a.ci * 9 * a.O_pad + a.O_pad) * 4;
+  KB_CHECK(smem <= 48 * 1024, "kair_conv_in_fwd: weights do not fit in shared memory");
+  conv_in_fwd_kernel<<<sm_count() * 4, 256, smem, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// conv_in weight gradient: dW[o][c][tap] = sum_t dy[t][o] * in(t, c, tap), db[o] = sum_t dy[t][o]
+__global__ void conv_in_wgrad_kernel(const kair_conv_in_args a) {
+  const int K = a.ci * 9;
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  // each lane owns outputs o = lane + 32*j ; accumulators acc[j][k]
+  constexpr int JMAX = 8;
+  const int nj = (a.O + 31) / 32;
+  for (int j0 = 0; j0 < nj; ++j0) {
+    const int o = lane + 32 * j0;
+    float acc[CI_MAX * 9 + 1];
+#pragma unroll
+    for (int k = 0; k <= CI_MAX * 9; ++k) acc[k] = 0.f;
+    for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+      const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+      float dy = 0.f;
+      if (o < a.O) {
+        if (a.dy_f32) dy += a.dy_f32[t * a.pitch + o];
+        if (a.dy_bf16) dy += __bfloat162float(reinterpret_cast<const bf16*>(a.dy_bf16)[t * a.pitch + o]);
+      }
+#pragma unroll
+      for (int c = 0; c < CI_MAX; ++c) {
+        if (c >= a.ci) break;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+          float v = 0.f;
+          if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+            v = a.img[(((size_t)b * a.ci + c) * a.H + hh) * a.Wd + ww];
+            v = (v - a.mean[c]) * a.range;
+          }
+          acc[c * 9 + tap] += dy * v;
+        }
+      }
+      acc[CI_MAX * 9] += dy;
+    }
+    if (o < a.O) {
+      for (int k = 0; k < K; ++k) atomicAdd(&a.dW[(size_t)o * K + k], acc[k]);
+      if (a.db) atomicAdd(&a.db[o], acc[CI_MAX * 9]);
+    }
+  }
+  (void)JMAX;
+}
+
+int conv_in_wgrad_launch(const kair_conv_in_args& a, cudaStream_t st) {
+  KB_CHECK(a.img && a.dW && a.mean && (a.dy_f32 || a.dy_bf16), "kair_conv_in_wgrad: null pointer");
+  KB_CHECK(a.ci >= 1 && a.ci <= CI_MAX, "kair_conv_in_wgrad: ci=%d unsupported", a.ci);
+  conv_in_wgrad_kernel<<<sm_count() * 2, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// conv_out: token features bf16 [T][pitch] (C channels) -> NCHW fp32 image (B, co, H, W); one warp per pixel.
+//   out[c][p] = (b[c] + sum_{tap,k} W[c][k][tap] * feat[p+tap][k] + skip_scale * skip[c][p]) * out_scale + out_mean[c]
+__global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
+  extern __shared__ float sw[];  // [co][9][C_pad]
+  const int Cp = a.pitch;
+  for (int e = threadIdx.x; e < a.co * 9 * Cp; e += blockDim.x) {
+    const int k = e % Cp, tap = (e / Cp) % 9, c = e / (9 * Cp);
+    sw[e] = k < a.C ? a.W[((size_t)c * a.C + k) * 9 + tap] : 0.f;
+  }
+  __syncthreads();
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  const bf16* feat = reinterpret_cast<const bf16*>(a.feat);
+  for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+    float acc[CI_MAX];
+#pragma unroll
+    for (int c = 0; c < CI_MAX; ++c) acc[c] = 0.f;
+    for (int tap = 0; tap < 9; ++tap) {
+      const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+      if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.Wd) continue;
+      const bf16* row = feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp;
+      for (int k = lane * 2; k < a.C; k += 64) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + k));
+#pragma unroll
+        for (int c = 0; c < CI_MAX; ++c) {
+          if (c >= a.co) break;
+          const float* wr = sw + (c * 9 + tap) * Cp + k;
+          acc[c] += wr[0] * f.x + wr[1] * f.y;
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CI_MAX; ++c) {
+      if (c >= a.co) break;
+      float v = warp_sum(acc[c]);
+      if (lane == 0) {
+        v += a.b ? a.b[c] : 0.f;
+        const size_t oi = (((size_t)b * a.co + c) * a.H + h) * a.Wd + w;
+        if (a.skip) v += a.skip_scale * (a.skip[oi] - a.skip_mean[c]);
+        a.out[oi] = v * a.out_scale + a.out_mean[c];
+      }
+    }
+  }
+}
+
+int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
+  KB_CHECK(a.feat && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
+  KB_CHECK(a.co >= 1 && a.co <= CI_MAX, "kair_conv_out_fwd: co=%d unsupported (max %d)", a.co, CI_MAX);
+  KB_CHECK(a.pitch % 2 == 0 && a.C % 2 == 0, "kair_conv_out_fwd: channel count must be even");
+  size_t smem = (size_t)a.co * 9 * a.pitch * 4;
+  KB_CHECK(smem <= 96 * 1024, "kair_conv_out_fwd: weights do not fit in shared memory");
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  conv_out_fwd_kernel<<<sm_count() * 4, 256, smem, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// conv_out input gradient: dfeat[t][k] = sum_{c,tap} dout[c][p - off(tap)] * W[c][k][tap]   (dout already scaled)
+__global__ void conv_out_dgrad_kernel(const kair_conv_out_args a) {
+  extern __shared__ float sw[];  // [co][9][C_pad]
+  const int Cp = a.pitch;
+  for (int e = threadIdx.x; e < a.co * 9 * Cp; e += blockDim.x) {
+    const int k = e % Cp, tap = (e / Cp) % 9, c = e / (9 * Cp);
+    sw[e] = k < a.C ? a.W[((size_t)c * a.C + k) * 9 + tap] : 0.f;
+  }
+  __syncthreads();
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+    float g[CI_MAX * 9];
+#pragma unroll
+    for (int c = 0; c < CI_MAX; ++c) {
+      if (c >= a.co) break;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const int hh = h - (tap / 3 - 1), ww = w - (tap % 3 - 1);
+        g[c * 9 + tap] = (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd)
+                             ? a.dout[(((size_t)b * a.co + c) * a.H + hh) * a.Wd + ww] * a.out_scale
+                             : 0.f;
+      }
+    }
+    for (int k = lane; k < Cp; k += 32) {
+      float acc = 0.f;
+      if (k < a.C) {
+#pragma unroll
+        for (int c = 0; c < CI_MAX; ++c) {
+          if (c >= a.co) break;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) acc += g[c * 9 + tap] * sw[(c * 9 + tap) * Cp + k];
+        }
+      }
+      if (a.dfeat_f32) a.dfeat_f32[t * Cp + k] = acc;
+      if (a.dfeat_bf16) reinterpret_cast<bf16*>(a.dfeat_bf16)[t * Cp + k] = __float2bfloat16(acc);
+    }
+  }
+}
+
+int conv_out_dgrad_launch(const kair_conv_out_args& a, cudaStream_t st) {
+  KB_CHECK(a.dout && a.W && (a.dfeat_f32 || a.dfeat_bf16), "kair_conv_out_dgrad: null pointer");
+  KB_CHECK(a.co >= 1 && a.co <= CI_MAX, "kair_conv_out_dgrad: co=%d unsupported", a.co);
+  size_t smem = (size_t)a.co * 9 * a.pitch * 4;
+  KB_CHECK(smem <= 96 * 1024, "kair_conv_out_dgrad: weights do not fit in shared memory");
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  KB_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    KB_CUDA(cudaFuncSetAttribute(conv_out_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  conv_out_dgrad_kernel<<<sm_count() * 4, 256, smem, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// conv_out weight gradient: dW[c][k][tap] = sum_t dout[c][t] * feat[t + off(tap)][k],  db[c] = sum_t dout[c][t]
+__global__ void conv_out_wgrad_kernel(const kair_conv_out_args a) {
+  const int Cp = a.pitch;
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  const bf16* feat = reinterpret_cast<const bf16*>(a.feat);
+  for (int c = 0; c < a.co; ++c) {
+    float acc[9][8];  // lane owns channels k = lane*2 + 64*j (+1)
+#pragma unroll
+    for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[tap][j] = 0.f;
+    float accb = 0.f;
+    for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+      const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+      const float d = a.dout[(((size_t)b * a.co + c) * a.H + h) * a.Wd + w] * a.out_scale;
+      accb += d;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+        if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.Wd) continue;
+        const bf16* row = feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = lane * 2 + 64 * j;
+          if (k < a.C) {
+            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + k));
+            acc[tap][2 * j] += d * f.x;
+            acc[tap][2 * j + 1] += d * f.y;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = lane * 2 + 64 * j;
+        if (k < a.C) {
+          atomicAdd(&a.dW[((size_t)c * a.C + k) * 9 + tap], acc[tap][2 * j]);
+          if (k + 1 < a.C) atomicAdd(&a.dW[((size_t)c * a.C + k + 1) * 9 + tap], acc[tap][2 * j + 1]);
+        }
+      }
+    if (a.db) {
+      accb = (lane == 0) ? accb : 0.f;
+      if (lane == 0) atomicAdd(&a.db[c], accb);
+    }
+  }
+}
+
+int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st) {
+  KB_CHECK(a.dout && a.feat && a.dW, "kair_conv_out_wgrad: null pointer");
+  KB_CHECK(a.C <= 256, "kair_conv_out_wgrad: C=%d unsupported (max 256)", a.C);
+  conv_out_wgrad_kernel<<<sm_count(), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ residual helpers
+// y += x (fp32, in place) and refresh the bf16 shadow copy of y
+__global__ void add_inplace_kernel(float* y, const float* x, bf16* yb, size_t n4) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 a = reinterpret_cast<float4*>(y)[i];
+    const float4 b = reinterpret_cast<const float4*>(x)[i];
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    reinterpret_cast<float4*>(y)[i] = a;
+    if (yb) {
+      uint2 o;
+      o.x = pack_bf16x2(a.x, a.y);
+      o.y = pack_bf16x2(a.z, a.w);
+      reinterpret_cast<uint2*>(yb)[i] = o;
+    }
+  }
+}
+
+int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st) {
+  KB_CHECK(y && x && n > 0 && n % 4 == 0, "kair_add_inplace: bad arguments");
+  add_inplace_kernel<<<sm_count() * 8, 256, 0, st>>>(y, x, reinterpret_cast<bf16*>(yb), (size_t)n / 4);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace kb

@@ -35,7 +35,10 @@ struct TnParams {
   const float* resid;
   const bf16* aux;
   float* rowstat;
+  const float* acc_scale;
+  const float* outB_scale;
   long long resid_pitch, aux_pitch;
+  int tokens_per_sample;
   int M, m_tiles, n_tiles, kc, taps, stages;
   int n_valid, ones_col, act;
   float act_slope, ln_eps;
@@ -290,6 +293,11 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       tcgen05_fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * HALF;
       const int col_half = n_tile * BN + hf * HALF;
+      float sa = 1.0f, sb = 1.0f;  // DropPath per-sample scales
+      if (tok >= 0) {
+        if (p.acc_scale) sa = __ldg(p.acc_scale + tok / p.tokens_per_sample);
+        if (p.outB_scale) sb = __ldg(p.outB_scale + tok / p.tokens_per_sample);
+      }
 
       if (EPI == KAIR_EPI_LINEAR) {
 #pragma unroll 1
@@ -310,6 +318,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
               v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
             }
           }
+          if (p.acc_scale) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= sa;
+          }
           if (p.resid && tok >= 0) {
             const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
 #pragma unroll
@@ -325,6 +337,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           uint8_t* buf = stage_begin();
           if (p.has_outF) stage_f32(buf, lane, v);
           if (p.has_outB) {
+            if (p.outB_scale) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] *= sb;
+            }
             if (p.ones_col >= col && p.ones_col < col + 32) {
 #pragma unroll
               for (int i = 0; i < 32; ++i)
@@ -397,6 +413,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
               float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
               v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
             }
+          }
+          if (p.acc_scale) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= sa;
           }
           if (p.resid && tok >= 0) {
             const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
@@ -572,7 +592,13 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             if (col + i >= p.n_valid) v[i] = 0.f;
           uint8_t* buf = stage_begin();
           if (p.has_outF) stage_f32(buf, lane, v);
-          if (p.has_outB) stage_bf16(buf + 4096, lane, v);
+          if (p.has_outB) {
+            if (p.outB_scale) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] *= sb;
+            }
+            stage_bf16(buf + 4096, lane, v);
+          }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
@@ -665,6 +691,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
     KB_CHECK(a.N == a.bn, "kair_gemm_tn: LayerNorm epilogues need the whole row in one tile (N == bn)");
   if (a.mode == KAIR_EPI_LNBWD || a.mode == KAIR_EPI_DGELU) KB_CHECK(a.aux != nullptr, "kair_gemm_tn: aux required");
   if (a.mode == KAIR_EPI_LNBWD) KB_CHECK(a.rowstat != nullptr, "kair_gemm_tn: rowstat required");
+  if (a.acc_scale || a.outB_scale) KB_CHECK(a.tokens_per_sample > 0, "kair_gemm_tn: tokens_per_sample required");
   if (check_device() != 0) return -3;
 
   TnParams p;
@@ -674,6 +701,9 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   p.resid = a.resid;
   p.aux = (const bf16*)a.aux;
   p.rowstat = a.rowstat;
+  p.acc_scale = a.acc_scale;
+  p.outB_scale = a.outB_scale;
+  p.tokens_per_sample = a.tokens_per_sample > 0 ? a.tokens_per_sample : 1;
   p.resid_pitch = a.resid_pitch;
   p.aux_pitch = a.aux_pitch;
   p.M = a.M;

@@ -8,9 +8,11 @@ from . import _lib
 EPI_LINEAR, EPI_GELU, EPI_RESID_LN, EPI_DGELU, EPI_LNBWD = range(5)
 ACT_NONE, ACT_LRELU = 0, 1
 
+_S = _lib.STRUCTS
+
 
 def _ptr(t):
-    return None if t is None else ctypes.c_void_p(t.data_ptr())
+    return None if t is None else t.data_ptr()
 
 
 def _stream():
@@ -24,7 +26,7 @@ def _req(t, dtype, name):
         raise RuntimeError("kair_b200: %s must be a CUDA tensor (no CPU fallback)" % name)
     if t.dtype != dtype:
         raise RuntimeError("kair_b200: %s must be %s, got %s" % (name, dtype, t.dtype))
-    if t.stride(-1) != 1:
+    if t.dim() > 0 and t.stride(-1) != 1:
         raise RuntimeError("kair_b200: %s must be contiguous in its last dimension" % name)
 
 
@@ -33,14 +35,22 @@ def _pitch(t):
     return 0 if t is None else t.stride(-2)
 
 
+def ptr_array(tensors, device):
+    """int64 device tensor holding the data pointers of `tensors` (a `const void* const*` argument)."""
+    return torch.tensor([t.data_ptr() for t in tensors], dtype=torch.int64, device=device)
+
+
+# ------------------------------------------------------------------------------------------------ GEMMs
+
 def gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
-            aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None):
+            aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None,
+            acc_scale=None, outB_scale=None, tokens_per_sample=0):
     """D = epilogue(A @ B^T).  A: bf16 [M, >=K] (or NHWC [B,H,W,>=K] with conv=(B,H,W)); B: bf16 [N, taps*K]."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
     _req(bias, torch.float32, "bias"); _req(resid, torch.float32, "resid")
     _req(aux, torch.bfloat16, "aux"); _req(rowstat, torch.float32, "rowstat")
     _req(outB, torch.bfloat16, "outB"); _req(outB2, torch.bfloat16, "outB2"); _req(outF, torch.float32, "outF")
-    a = _lib.GemmTnArgs()
+    a = _S["kair_gemm_tn_args"]()
     a.A = _ptr(A); a.a_pitch = _pitch(A)
     a.B = _ptr(B); a.b_pitch = _pitch(B)
     if conv is not None:
@@ -60,13 +70,14 @@ def gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_
     a.outB2 = _ptr(outB2); a.outB2_pitch = _pitch(outB2)
     a.outF = _ptr(outF); a.outF_pitch = _pitch(outF)
     a.n_valid = n_valid; a.ones_col = ones_col
-    _lib.check(_lib.load().kair_gemm_tn(ctypes.byref(a), _stream()), "gemm_tn")
+    a.acc_scale = _ptr(acc_scale); a.outB_scale = _ptr(outB_scale); a.tokens_per_sample = tokens_per_sample
+    _lib.call("kair_gemm_tn", a, _stream())
 
 
 def gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B"); _req(D, torch.float32, "D")
-    a = _lib.GemmNtArgs()
+    a = _S["kair_gemm_nt_args"]()
     a.A = _ptr(A); a.a_pitch = _pitch(A)
     a.B = _ptr(B); a.b_pitch = _pitch(B)
     a.D = _ptr(D); a.d_pitch = _pitch(D)
@@ -78,14 +89,16 @@ def gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     else:
         a.conv = 0
         a.T = A.shape[0]
-    _lib.check(_lib.load().kair_gemm_nt(ctypes.byref(a), _stream()), "gemm_nt")
+    _lib.call("kair_gemm_nt", a, _stream())
 
+
+# ------------------------------------------------------------------------------------------------ window attention
 
 def _attn_args(qkv, table, batch, H, W, num_heads, window, shift):
     _req(qkv, torch.bfloat16, "qkv"); _req(table, torch.float32, "table")
     if not table.is_contiguous():
         raise RuntimeError("kair_b200: relative_position_bias_table must be contiguous")
-    a = _lib.WindowAttnArgs()
+    a = _S["kair_window_attn_args"]()
     a.qkv = _ptr(qkv); a.qkv_pitch = _pitch(qkv)
     a.table = _ptr(table)
     a.batch, a.H, a.W = batch, H, W
@@ -98,7 +111,7 @@ def window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=
     _req(out, torch.bfloat16, "out")
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.out = _ptr(out); a.out_pitch = _pitch(out)
-    _lib.check(_lib.load().kair_window_attn_fwd(ctypes.byref(a), _stream()), "window_attn_fwd")
+    _lib.call("kair_window_attn_fwd", a, _stream())
 
 
 def window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
@@ -108,4 +121,130 @@ def window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, w
     a.dout = _ptr(dout); a.dout_pitch = _pitch(dout)
     a.dqkv = _ptr(dqkv); a.dqkv_pitch = _pitch(dqkv)
     a.dtable = _ptr(dtable)
-    _lib.check(_lib.load().kair_window_attn_bwd(ctypes.byref(a), _stream()), "window_attn_bwd")
+    _lib.call("kair_window_attn_bwd", a, _stream())
+
+
+# ------------------------------------------------------------------------------------------------ packing
+
+def pack_linear(W_ptrs, b_ptrs, gamma_ptrs, beta_ptrs, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *,
+                L, N_pad, K_pad, out_f, in_f):
+    a = _S["kair_pack_linear_args"]()
+    a.W = _ptr(W_ptrs); a.b = _ptr(b_ptrs); a.gamma = _ptr(gamma_ptrs); a.beta = _ptr(beta_ptrs)
+    a.row_map = _ptr(row_map); a.col_map = _ptr(col_map)
+    a.row_scale = _ptr(row_scale); a.bias_const = _ptr(bias_const)
+    a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
+    a.L, a.N_pad, a.K_pad, a.out_f, a.in_f = L, N_pad, K_pad, out_f, in_f
+    _lib.call("kair_pack_linear", a, _stream())
+
+
+def unpack_linear_grad(dWp, W_ptrs, gamma_ptrs, beta_ptrs, dW_ptrs, db_ptrs, dgamma_ptrs, dbeta_ptrs, row_map,
+                       col_map, row_scale, *, L, N_pad, K_pad, out_f, in_f, ones_col):
+    a = _S["kair_unpack_linear_args"]()
+    a.dWp = _ptr(dWp)
+    a.W = _ptr(W_ptrs); a.gamma = _ptr(gamma_ptrs); a.beta = _ptr(beta_ptrs)
+    a.dW = _ptr(dW_ptrs); a.db = _ptr(db_ptrs); a.dgamma = _ptr(dgamma_ptrs); a.dbeta = _ptr(dbeta_ptrs)
+    a.row_map = _ptr(row_map); a.col_map = _ptr(col_map); a.row_scale = _ptr(row_scale)
+    a.L, a.N_pad, a.K_pad, a.out_f, a.in_f, a.ones_col = L, N_pad, K_pad, out_f, in_f, ones_col
+    _lib.call("kair_unpack_linear_grad", a, _stream())
+
+
+def pack_conv(W_ptrs, b_ptrs, Wp, WpT, bp, *, L, O, I, O_pad, I_pad, taps=9):
+    a = _S["kair_pack_conv_args"]()
+    a.W = _ptr(W_ptrs); a.b = _ptr(b_ptrs); a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
+    a.L, a.O, a.I, a.O_pad, a.I_pad, a.taps = L, O, I, O_pad, I_pad, taps
+    _lib.call("kair_pack_conv", a, _stream())
+
+
+def unpack_conv_grad(dWp, dW_ptrs, db_ptrs, *, L, O, I, O_pad, I_pad, taps=9, ones_col=-1, center_tap=4):
+    a = _S["kair_unpack_conv_args"]()
+    a.dWp = _ptr(dWp); a.dW = _ptr(dW_ptrs); a.db = _ptr(db_ptrs)
+    a.L, a.O, a.I, a.O_pad, a.I_pad, a.taps, a.ones_col, a.center_tap = L, O, I, O_pad, I_pad, taps, ones_col, center_tap
+    _lib.call("kair_unpack_conv_grad", a, _stream())
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+
+def layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
+                  ones_col=-1):
+    _req(x, torch.float32, "x")
+    a = _S["kair_layernorm_args"]()
+    a.x = _ptr(x); a.gamma = _ptr(gamma); a.beta = _ptr(beta)
+    a.y_f32 = _ptr(y_f32); a.y_bf16 = _ptr(y_bf16); a.xhat_bf16 = _ptr(xhat_bf16)
+    a.mean = _ptr(mean); a.rstd = _ptr(rstd)
+    a.T = x.shape[0]; a.C = C; a.pitch = x.stride(0); a.ones_col = ones_col; a.eps = eps
+    _lib.call("kair_layernorm_fwd", a, _stream())
+
+
+def layernorm_bwd(x, mean, rstd, gamma, dgamma, dbeta, *, C, dy_f32=None, dy_bf16=None, dx_add=None, dx_f32=None,
+                  dx_bf16=None):
+    a = _S["kair_layernorm_bwd_args"]()
+    a.dy_f32 = _ptr(dy_f32); a.dy_bf16 = _ptr(dy_bf16)
+    a.x = _ptr(x); a.mean = _ptr(mean); a.rstd = _ptr(rstd); a.gamma = _ptr(gamma)
+    a.dx_add = _ptr(dx_add); a.dx_f32 = _ptr(dx_f32); a.dx_bf16 = _ptr(dx_bf16)
+    a.dgamma = _ptr(dgamma); a.dbeta = _ptr(dbeta)
+    a.T = x.shape[0]; a.C = C; a.pitch = x.stride(0)
+    _lib.call("kair_layernorm_bwd", a, _stream())
+
+
+# ------------------------------------------------------------------------------------------------ thin convolutions
+
+def _conv_in_args(img, W, b, mean, rng, O, O_pad, pitch):
+    _req(img, torch.float32, "img"); _req(W, torch.float32, "W"); _req(mean, torch.float32, "mean")
+    if not img.is_contiguous() or not W.is_contiguous():
+        raise RuntimeError("kair_b200: conv_in needs contiguous NCHW image and weights")
+    a = _S["kair_conv_in_args"]()
+    a.img = _ptr(img); a.W = _ptr(W); a.b = _ptr(b); a.mean = _ptr(mean); a.range = rng
+    a.batch, a.ci, a.H, a.Wd = img.shape
+    a.O, a.O_pad, a.pitch = O, O_pad, pitch
+    a.ones_col = -1
+    return a
+
+
+def conv_in_fwd(img, W, b, mean, rng, *, O, O_pad, pitch, out_f32=None, out_bf16=None, act=ACT_NONE, act_slope=0.0,
+                ones_col=-1):
+    a = _conv_in_args(img, W, b, mean, rng, O, O_pad, pitch)
+    a.out_f32 = _ptr(out_f32); a.out_bf16 = _ptr(out_bf16)
+    a.act, a.act_slope, a.ones_col = act, act_slope, ones_col
+    _lib.call("kair_conv_in_fwd", a, _stream())
+
+
+def conv_in_wgrad(img, W, mean, rng, dW, db, *, O, O_pad, pitch, dy_f32=None, dy_bf16=None):
+    a = _conv_in_args(img, W, None, mean, rng, O, O_pad, pitch)
+    a.dy_f32 = _ptr(dy_f32); a.dy_bf16 = _ptr(dy_bf16); a.dW = _ptr(dW); a.db = _ptr(db)
+    _lib.call("kair_conv_in_wgrad", a, _stream())
+
+
+def _conv_out_args(W, shape, C, pitch, out_scale):
+    _req(W, torch.float32, "W")
+    a = _S["kair_conv_out_args"]()
+    a.W = _ptr(W)
+    a.batch, a.co, a.H, a.Wd = shape
+    a.C, a.pitch, a.out_scale = C, pitch, out_scale
+    return a
+
+
+def conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, skip=None, skip_mean=None, skip_scale=0.0):
+    _req(feat, torch.bfloat16, "feat"); _req(out, torch.float32, "out")
+    a = _conv_out_args(W, out.shape, C, pitch, out_scale)
+    a.feat = _ptr(feat); a.b = _ptr(b); a.out = _ptr(out); a.out_mean = _ptr(out_mean)
+    a.skip = _ptr(skip); a.skip_mean = _ptr(skip_mean); a.skip_scale = skip_scale
+    _lib.call("kair_conv_out_fwd", a, _stream())
+
+
+def conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
+    _req(dout, torch.float32, "dout")
+    a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
+    a.dout = _ptr(dout); a.dfeat_f32 = _ptr(dfeat_f32); a.dfeat_bf16 = _ptr(dfeat_bf16)
+    _lib.call("kair_conv_out_dgrad", a, _stream())
+
+
+def conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
+    _req(dout, torch.float32, "dout"); _req(feat, torch.bfloat16, "feat")
+    a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
+    a.dout = _ptr(dout); a.feat = _ptr(feat); a.dW = _ptr(dW); a.db = _ptr(db)
+    _lib.call("kair_conv_out_wgrad", a, _stream())
+
+
+def add_inplace(y, x, yb=None):
+    _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")
+    _lib.check(_lib.load().kair_add_inplace(_ptr(y), _ptr(x), _ptr(yb), y.numel(), _stream()), "add_inplace")
