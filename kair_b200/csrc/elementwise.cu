@@ -71,10 +71,13 @@ __global__ void unpack_linear_dw_kernel(const kair_unpack_linear_args a) {
   const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
   const float* dWp = a.dWp + ((size_t)l * a.N_pad + r) * a.K_pad;
   const float* gamma = a.gamma ? reinterpret_cast<const float*>(a.gamma[l]) : nullptr;
+  const float* beta = a.beta ? reinterpret_cast<const float*>(a.beta[l]) : nullptr;
   float* dW = reinterpret_cast<float*>(a.dW[l]) + (size_t)src * a.in_f;
+  // W enters twice: Wp = rs * W * gamma and bp = rs * (b + W . beta)
+  const float dbp = (beta && a.ones_col >= 0) ? dWp[a.ones_col] : 0.f;
   for (int c = threadIdx.x; c < a.K_pad; c += blockDim.x) {
     const int k = a.col_map[c];
-    if (k >= 0) dW[k] = dWp[c] * rs * (gamma ? gamma[k] : 1.0f);
+    if (k >= 0) dW[k] = rs * (dWp[c] * (gamma ? gamma[k] : 1.0f) + (beta ? dbp * beta[k] : 0.f));
   }
   if (threadIdx.x == 0 && a.db && a.ones_col >= 0) reinterpret_cast<float*>(a.db[l])[src] = dWp[a.ones_col] * rs;
 }

@@ -1,0 +1,312 @@
+"""Drop-in `SwinIR` for models/network_swinir.py:618-850 of the reference, computed by the sm_100a kernels.
+
+The module tree below exists only as a *parameter container*: it reproduces the reference's child names, parameter
+and buffer names, shapes, dtypes and registration order, so `state_dict()` / `load_state_dict()` / positional
+non-strict loading (models/model_base.py:209-215), `init_weights` by class name (models/select_network.py:385-433),
+EMA over `named_parameters()` (models/model_base.py:247-252), DDP and `torch.optim` all work unchanged.  None of the
+sub-modules has a forward(): the whole network is evaluated by `SwinIREngine` (fused CUDA kernels), and there is no
+PyTorch / CPU fallback -- a CPU tensor or a missing extension raises.
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .swinir_engine import SwinIREngine, SwinIRFunction, SwinIRSpec
+
+
+def _pair(v):
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+
+
+def _no_forward(self, *a, **k):
+    raise RuntimeError("kair_b200: %s is a parameter container; the computation is fused into SwinIR.forward"
+                       % type(self).__name__)
+
+
+def _rel_index(ws):
+    """relative_position_index buffer (network_swinir.py:92-103), closed form (dy+ws-1)*(2ws-1) + (dx+ws-1)."""
+    ys, xs = torch.meshgrid(torch.arange(ws[0]), torch.arange(ws[1]), indexing="ij")
+    ys, xs = ys.reshape(-1), xs.reshape(-1)
+    return (ys[:, None] - ys[None, :] + ws[0] - 1) * (2 * ws[1] - 1) + (xs[:, None] - xs[None, :] + ws[1] - 1)
+
+
+def _shift_mask(H, W, ws, shift):
+    """attn_mask buffer (network_swinir.py:216-237), closed form: region id r(p,L) = [p >= L-ws] + [p >= L-shift]
+    per axis in the shifted frame; mask = -100 where the ids of two tokens of a window differ."""
+    def rid(n):
+        p = torch.arange(n)
+        return (p >= n - ws).long() + (p >= n - shift).long()
+    ids = (3 * rid(H)[:, None] + rid(W)[None, :]).float()
+    ids = ids.view(H // ws, ws, W // ws, ws).permute(0, 2, 1, 3).reshape(-1, ws * ws)
+    d = ids[:, None, :] - ids[:, :, None]
+    return torch.where(d != 0, torch.full_like(d, -100.0), torch.zeros_like(d))
+
+
+class DropPath(nn.Module):
+    """Holder of the stochastic-depth rate (the per-sample scaling happens inside the GEMM epilogues)."""
+
+    def __init__(self, drop_prob=0.0):
+        super().__init__()
+        self.drop_prob = float(drop_prob)
+
+    forward = _no_forward
+
+
+class Mlp(nn.Module):
+    def __init__(self, in_features, hidden_features, drop=0.0):
+        super().__init__()
+        self.fc1 = nn.Linear(in_features, hidden_features)
+        self.act = nn.GELU()
+        self.fc2 = nn.Linear(hidden_features, in_features)
+        self.drop = nn.Dropout(drop)
+
+    forward = _no_forward
+
+
+class WindowAttention(nn.Module):
+    def __init__(self, dim, window_size, num_heads, qkv_bias=True, qk_scale=None, attn_drop=0.0, proj_drop=0.0):
+        super().__init__()
+        self.dim, self.window_size, self.num_heads = dim, window_size, num_heads
+        self.scale = qk_scale or (dim // num_heads) ** -0.5
+        self.relative_position_bias_table = nn.Parameter(
+            torch.zeros((2 * window_size[0] - 1) * (2 * window_size[1] - 1), num_heads))
+        self.register_buffer("relative_position_index", _rel_index(window_size))
+        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        self.attn_drop = nn.Dropout(attn_drop)
+        self.proj = nn.Linear(dim, dim)
+        self.proj_drop = nn.Dropout(proj_drop)
+        nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
+        self.softmax = nn.Softmax(dim=-1)
+
+    forward = _no_forward
+
+
+class SwinTransformerBlock(nn.Module):
+    def __init__(self, dim, input_resolution, num_heads, window_size, shift_size, mlp_ratio, qkv_bias, qk_scale, drop,
+                 attn_drop, drop_path):
+        super().__init__()
+        self.dim, self.input_resolution, self.num_heads = dim, input_resolution, num_heads
+        self.window_size, self.shift_size, self.mlp_ratio = window_size, shift_size, mlp_ratio
+        if min(input_resolution) <= window_size:
+            self.shift_size, self.window_size = 0, min(input_resolution)
+        self.norm1 = nn.LayerNorm(dim)
+        self.attn = WindowAttention(dim, _pair(self.window_size), num_heads, qkv_bias, qk_scale, attn_drop, drop)
+        self.drop_path = DropPath(drop_path) if drop_path > 0.0 else nn.Identity()
+        self.norm2 = nn.LayerNorm(dim)
+        self.mlp = Mlp(dim, int(dim * mlp_ratio), drop)
+        mask = None
+        if self.shift_size > 0:
+            mask = _shift_mask(input_resolution[0], input_resolution[1], self.window_size, self.shift_size)
+        self.register_buffer("attn_mask", mask)  # kept for state_dict parity; the kernel uses the closed form
+
+    forward = _no_forward
+
+
+class BasicLayer(nn.Module):
+    def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias, qk_scale, drop,
+                 attn_drop, drop_path, use_checkpoint):
+        super().__init__()
+        self.dim, self.input_resolution, self.depth, self.use_checkpoint = dim, input_resolution, depth, use_checkpoint
+        self.blocks = nn.ModuleList([
+            SwinTransformerBlock(dim, input_resolution, num_heads, window_size, 0 if j % 2 == 0 else window_size // 2,
+                                 mlp_ratio, qkv_bias, qk_scale, drop, attn_drop,
+                                 drop_path[j] if isinstance(drop_path, list) else drop_path)
+            for j in range(depth)])
+        self.downsample = None
+
+    forward = _no_forward
+
+
+class PatchEmbed(nn.Module):
+    def __init__(self, img_size, patch_size, in_chans, embed_dim, norm):
+        super().__init__()
+        img_size, patch_size = _pair(img_size), _pair(patch_size)
+        self.img_size, self.patch_size = img_size, patch_size
+        self.patches_resolution = [img_size[0] // patch_size[0], img_size[1] // patch_size[1]]
+        self.num_patches = self.patches_resolution[0] * self.patches_resolution[1]
+        self.in_chans, self.embed_dim = in_chans, embed_dim
+        self.norm = nn.LayerNorm(embed_dim) if norm else None
+
+    forward = _no_forward
+
+
+class PatchUnEmbed(PatchEmbed):
+    def __init__(self, img_size, patch_size, in_chans, embed_dim):
+        super().__init__(img_size, patch_size, in_chans, embed_dim, False)
+
+
+class RSTB(nn.Module):
+    def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias, qk_scale, drop,
+                 attn_drop, drop_path, use_checkpoint, img_size, patch_size, resi_connection):
+        super().__init__()
+        self.dim, self.input_resolution = dim, input_resolution
+        self.residual_group = BasicLayer(dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias,
+                                         qk_scale, drop, attn_drop, drop_path, use_checkpoint)
+        if resi_connection == "1conv":
+            self.conv = nn.Conv2d(dim, dim, 3, 1, 1)
+        elif resi_connection == "3conv":
+            self.conv = nn.Sequential(nn.Conv2d(dim, dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, inplace=True),
+                                      nn.Conv2d(dim // 4, dim // 4, 1, 1, 0), nn.LeakyReLU(0.2, inplace=True),
+                                      nn.Conv2d(dim // 4, dim, 3, 1, 1))
+        self.patch_embed = PatchEmbed(img_size, patch_size, 0, dim, False)
+        self.patch_unembed = PatchUnEmbed(img_size, patch_size, 0, dim)
+
+    forward = _no_forward
+
+
+class Upsample(nn.Sequential):
+    """conv(nf -> 4nf) + PixelShuffle(2) per factor of two, or conv(nf -> 9nf) + PixelShuffle(3)
+    (network_swinir.py:572-591)."""
+
+    def __init__(self, scale, num_feat):
+        m = []
+        if (scale & (scale - 1)) == 0:
+            for _ in range(int(math.log2(scale))):
+                m += [nn.Conv2d(num_feat, 4 * num_feat, 3, 1, 1), nn.PixelShuffle(2)]
+        elif scale == 3:
+            m += [nn.Conv2d(num_feat, 9 * num_feat, 3, 1, 1), nn.PixelShuffle(3)]
+        else:
+            raise ValueError("scale %d is not supported. Supported scales: 2^n and 3." % scale)
+        super().__init__(*m)
+
+
+class UpsampleOneStep(nn.Sequential):
+    def __init__(self, scale, num_feat, num_out_ch, input_resolution=None):
+        self.num_feat, self.input_resolution = num_feat, input_resolution
+        super().__init__(nn.Conv2d(num_feat, (scale ** 2) * num_out_ch, 3, 1, 1), nn.PixelShuffle(scale))
+
+
+class SwinIR(nn.Module):
+    """Same constructor, forward() contract and state_dict layout as the reference's SwinIR."""
+
+    def __init__(self, img_size=64, patch_size=1, in_chans=3, embed_dim=96, depths=[6, 6, 6, 6],
+                 num_heads=[6, 6, 6, 6], window_size=7, mlp_ratio=4., qkv_bias=True, qk_scale=None, drop_rate=0.,
+                 attn_drop_rate=0., drop_path_rate=0.1, norm_layer=nn.LayerNorm, ape=False, patch_norm=True,
+                 use_checkpoint=False, upscale=2, img_range=1., upsampler='', resi_connection='1conv', **kwargs):
+        super().__init__()
+        if norm_layer is not nn.LayerNorm:
+            raise NotImplementedError("kair_b200 SwinIR: only nn.LayerNorm is fused")
+        if ape or drop_rate or attn_drop_rate or patch_size != 1:
+            raise NotImplementedError("kair_b200 SwinIR: ape / dropout / patch_size != 1 are not used by any KAIR "
+                                      "config and are not implemented")
+        num_feat = 64
+        self.img_range = img_range
+        self.mean = torch.Tensor((0.4488, 0.4371, 0.4040)).view(1, 3, 1, 1) if in_chans == 3 else torch.zeros(1, 1, 1, 1)
+        self.upscale, self.upsampler, self.window_size = upscale, upsampler, window_size
+        self.conv_first = nn.Conv2d(in_chans, embed_dim, 3, 1, 1)
+        self.num_layers, self.embed_dim, self.ape, self.patch_norm = len(depths), embed_dim, ape, patch_norm
+        self.num_features, self.mlp_ratio = embed_dim, mlp_ratio
+        self.patch_embed = PatchEmbed(img_size, patch_size, embed_dim, embed_dim, patch_norm)
+        self.patches_resolution = self.patch_embed.patches_resolution
+        self.patch_unembed = PatchUnEmbed(img_size, patch_size, embed_dim, embed_dim)
+        self.pos_drop = nn.Dropout(p=drop_rate)
+        dpr = [v.item() for v in torch.linspace(0, drop_path_rate, sum(depths))]
+        res = (self.patches_resolution[0], self.patches_resolution[1])
+        self.layers = nn.ModuleList()
+        for i in range(self.num_layers):
+            self.layers.append(RSTB(embed_dim, res, depths[i], num_heads[i], window_size, mlp_ratio, qkv_bias, qk_scale,
+                                    drop_rate, attn_drop_rate, dpr[sum(depths[:i]):sum(depths[:i + 1])],
+                                    use_checkpoint, img_size, patch_size, resi_connection))
+        self.norm = nn.LayerNorm(embed_dim)
+        if resi_connection == '1conv':
+            self.conv_after_body = nn.Conv2d(embed_dim, embed_dim, 3, 1, 1)
+        elif resi_connection == '3conv':
+            self.conv_after_body = nn.Sequential(
+                nn.Conv2d(embed_dim, embed_dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, inplace=True),
+                nn.Conv2d(embed_dim // 4, embed_dim // 4, 1, 1, 0), nn.LeakyReLU(0.2, inplace=True),
+                nn.Conv2d(embed_dim // 4, embed_dim, 3, 1, 1))
+        if upsampler == 'pixelshuffle':
+            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.upsample = Upsample(upscale, num_feat)
+            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+        elif upsampler == 'pixelshuffledirect':
+            self.upsample = UpsampleOneStep(upscale, embed_dim, in_chans, res)
+        elif upsampler == 'nearest+conv':
+            assert upscale == 4, 'only support x4 now.'
+            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.conv_up1 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_up2 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_hr = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+            self.lrelu = nn.LeakyReLU(negative_slope=0.2, inplace=True)
+        else:
+            self.conv_last = nn.Conv2d(embed_dim, in_chans, 3, 1, 1)
+        self.apply(self._init_weights)
+        self._spec = SwinIRSpec(in_chans=in_chans, embed_dim=embed_dim, depths=depths, num_heads=num_heads,
+                                window_size=window_size, mlp_ratio=mlp_ratio, qk_scale=qk_scale, img_range=img_range,
+                                upscale=upscale, upsampler=upsampler, resi_connection=resi_connection,
+                                patch_norm=patch_norm, qkv_bias=qkv_bias)
+        self._drop_rates = dpr
+        self._engine = None
+        self._engine_key = None
+
+    def _init_weights(self, m):
+        if isinstance(m, nn.Linear):
+            nn.init.trunc_normal_(m.weight, std=.02)
+            if m.bias is not None:
+                nn.init.constant_(m.bias, 0)
+        elif isinstance(m, nn.LayerNorm):
+            nn.init.constant_(m.bias, 0)
+            nn.init.constant_(m.weight, 1.0)
+
+    @torch.jit.ignore
+    def no_weight_decay(self):
+        return {'absolute_pos_embed'}
+
+    @torch.jit.ignore
+    def no_weight_decay_keywords(self):
+        return {'relative_position_bias_table'}
+
+    def check_image_size(self, x):
+        _, _, h, w = x.size()
+        ph = (self.window_size - h % self.window_size) % self.window_size
+        pw = (self.window_size - w % self.window_size) % self.window_size
+        return F.pad(x, (0, pw, 0, ph), 'reflect') if (ph or pw) else x
+
+    # ---------------------------------------------------------------------------------------------- engine
+    def engine(self, device):
+        """The kernel engine bound to the current parameter storage (rebuilt if parameters were re-allocated)."""
+        params = dict(self.named_parameters())
+        key = (str(device),) + tuple(p.data_ptr() for p in params.values())
+        if self._engine is None or self._engine_key != key:
+            self._engine = SwinIREngine(self._spec, params, device)
+            self._engine_key = key
+        return self._engine
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("kair_b200 SwinIR runs on sm_100a GPUs only; got a %s tensor (there is no CPU fallback)"
+                               % x.device.type)
+        H, W = x.shape[2:]
+        x = self.check_image_size(x.float()).contiguous()
+        self.mean = self.mean.type_as(x)
+        eng = self.engine(x.device)
+        params = list(eng.P.values())
+        train = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        plan = eng.plan(x.shape[0], x.shape[2], x.shape[3], train)
+        if train:
+            plan.set_drop_path(self._drop_rates if self.training else [0.0] * len(self._drop_rates))
+            out = SwinIRFunction.apply(x, plan, *params)
+        else:
+            out = plan.run_forward(x)
+        return out[:, :, :H * self.upscale, :W * self.upscale]
+
+    def flops(self):
+        """Analytic forward FLOPs in the reference's convention (network_swinir.py:841-850 and callees)."""
+        H, W = self.patches_resolution
+        C, s = self.embed_dim, self._spec
+        flops = H * W * 3 * C * 9
+        if self.patch_norm:
+            flops += H * W * C
+        ws = self.window_size
+        N, nW = ws * ws, H * W / ws / ws
+        for depth, nh in zip(s.depths, s.num_heads):
+            attn = N * C * 3 * C + 2 * nh * N * N * (C // nh) + N * C * C
+            blk = 2 * C * H * W + nW * attn + 2 * H * W * C * C * self.mlp_ratio
+            flops += depth * blk + H * W * C * C * 9 + H * W * C  # blocks + conv + patch_embed norm term
+        flops += H * W * 3 * C * C
+        if hasattr(self, "upsample") and hasattr(self.upsample, "flops"):
+            flops += self.upsample.flops()
+        return flops

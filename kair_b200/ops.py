@@ -11,6 +11,48 @@ ACT_NONE, ACT_LRELU = 0, 1
 _S = _lib.STRUCTS
 
 
+class Launch:
+    """One recorded kernel launch: a bound C entry point plus its filled argument struct.
+
+    Engines build these once per plan (all pointers are static workspace / parameter addresses) and replay them
+    every step, so the per-step host cost is one ctypes call per kernel."""
+
+    __slots__ = ("name", "fn", "args", "keep")
+
+    def __init__(self, name, args, keep=()):
+        self.name = name
+        self.fn = getattr(_lib.load(), name)
+        self.args = args
+        self.keep = keep  # tensors whose storage the struct points into
+
+    def run(self, stream):
+        rc = self.fn(ctypes.byref(self.args), stream)
+        if rc != 0:
+            _lib.check(rc, self.name)
+
+
+class _RawLaunch:
+    """Launch of an entry point that takes scalars instead of an argument struct."""
+
+    __slots__ = ("name", "call", "keep")
+
+    def __init__(self, name, call, keep=()):
+        self.name, self.call, self.keep = name, call, keep
+
+    def run(self, stream):
+        rc = self.call(stream)
+        if rc != 0:
+            _lib.check(rc, self.name)
+
+
+def stream_handle():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def zeros(shape, dtype, device):
+    return torch.zeros(shape, dtype=dtype, device=device)
+
+
 def _ptr(t):
     return None if t is None else t.data_ptr()
 
@@ -42,7 +84,7 @@ def ptr_array(tensors, device):
 
 # ------------------------------------------------------------------------------------------------ GEMMs
 
-def gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
+def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
             aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None,
             acc_scale=None, outB_scale=None, tokens_per_sample=0):
     """D = epilogue(A @ B^T).  A: bf16 [M, >=K] (or NHWC [B,H,W,>=K] with conv=(B,H,W)); B: bf16 [N, taps*K]."""
@@ -71,10 +113,10 @@ def gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_
     a.outF = _ptr(outF); a.outF_pitch = _pitch(outF)
     a.n_valid = n_valid; a.ones_col = ones_col
     a.acc_scale = _ptr(acc_scale); a.outB_scale = _ptr(outB_scale); a.tokens_per_sample = tokens_per_sample
-    _lib.call("kair_gemm_tn", a, _stream())
+    return Launch("kair_gemm_tn", a)
 
 
-def gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B"); _req(D, torch.float32, "D")
     a = _S["kair_gemm_nt_args"]()
@@ -89,7 +131,7 @@ def gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     else:
         a.conv = 0
         a.T = A.shape[0]
-    _lib.call("kair_gemm_nt", a, _stream())
+    return Launch("kair_gemm_nt", a)
 
 
 # ------------------------------------------------------------------------------------------------ window attention
@@ -106,65 +148,92 @@ def _attn_args(qkv, table, batch, H, W, num_heads, window, shift):
     return a
 
 
-def window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
+def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
     """out[t, h*32:(h+1)*32] = windowed softmax attention; qkv: bf16 [B*H*W, >=3*nH*32] in [3][nH][32] layout."""
     _req(out, torch.bfloat16, "out")
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.out = _ptr(out); a.out_pitch = _pitch(out)
-    _lib.call("kair_window_attn_fwd", a, _stream())
+    return Launch("kair_window_attn_fwd", a)
 
 
-def window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
+def build_window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
     """Backward of window_attn_fwd: writes dqkv (bf16) and accumulates into dtable (fp32, caller zeroes)."""
     _req(dout, torch.bfloat16, "dout"); _req(dqkv, torch.bfloat16, "dqkv"); _req(dtable, torch.float32, "dtable")
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.dout = _ptr(dout); a.dout_pitch = _pitch(dout)
     a.dqkv = _ptr(dqkv); a.dqkv_pitch = _pitch(dqkv)
     a.dtable = _ptr(dtable)
-    _lib.call("kair_window_attn_bwd", a, _stream())
+    return Launch("kair_window_attn_bwd", a)
 
 
 # ------------------------------------------------------------------------------------------------ packing
 
-def pack_linear(W_ptrs, b_ptrs, gamma_ptrs, beta_ptrs, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *,
-                L, N_pad, K_pad, out_f, in_f):
+def _plist(tensors, like, keep):
+    """device array of data pointers (`const void* const*`) for a list of same-shaped fp32 tensors, or None"""
+    if tensors is None:
+        return None
+    for t in tensors:
+        _req(t, torch.float32, "parameter")
+        if not t.is_contiguous():
+            raise RuntimeError("kair_b200: parameters / gradient buffers must be contiguous")
+    arr = ptr_array(tensors, like.device)
+    keep.append(arr)
+    keep.extend(tensors)
+    return arr.data_ptr()
+
+
+def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f):
+    """Pack L same-shaped nn.Linear layers (lists of fp32 tensors) into Wp [L,N_pad,K_pad] (+ WpT, bp)."""
+    keep = []
     a = _S["kair_pack_linear_args"]()
-    a.W = _ptr(W_ptrs); a.b = _ptr(b_ptrs); a.gamma = _ptr(gamma_ptrs); a.beta = _ptr(beta_ptrs)
+    a.W = _plist(W, Wp, keep); a.b = _plist(b, Wp, keep)
+    a.gamma = _plist(gamma, Wp, keep); a.beta = _plist(beta, Wp, keep)
     a.row_map = _ptr(row_map); a.col_map = _ptr(col_map)
     a.row_scale = _ptr(row_scale); a.bias_const = _ptr(bias_const)
     a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
-    a.L, a.N_pad, a.K_pad, a.out_f, a.in_f = L, N_pad, K_pad, out_f, in_f
-    _lib.call("kair_pack_linear", a, _stream())
+    a.L, a.N_pad, a.K_pad = Wp.shape
+    a.out_f, a.in_f = out_f, in_f
+    return Launch("kair_pack_linear", a, keep)
 
 
-def unpack_linear_grad(dWp, W_ptrs, gamma_ptrs, beta_ptrs, dW_ptrs, db_ptrs, dgamma_ptrs, dbeta_ptrs, row_map,
-                       col_map, row_scale, *, L, N_pad, K_pad, out_f, in_f, ones_col):
+def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map, col_map, row_scale, *, out_f, in_f,
+                             ones_col):
+    """Map packed weight gradients dWp [L,N_pad,K_pad] back onto dW / db / dgamma / dbeta (lists of fp32 tensors)."""
+    keep = []
     a = _S["kair_unpack_linear_args"]()
     a.dWp = _ptr(dWp)
-    a.W = _ptr(W_ptrs); a.gamma = _ptr(gamma_ptrs); a.beta = _ptr(beta_ptrs)
-    a.dW = _ptr(dW_ptrs); a.db = _ptr(db_ptrs); a.dgamma = _ptr(dgamma_ptrs); a.dbeta = _ptr(dbeta_ptrs)
+    a.W = _plist(W, dWp, keep); a.gamma = _plist(gamma, dWp, keep); a.beta = _plist(beta, dWp, keep)
+    a.dW = _plist(dW, dWp, keep); a.db = _plist(db, dWp, keep)
+    a.dgamma = _plist(dgamma, dWp, keep); a.dbeta = _plist(dbeta, dWp, keep)
     a.row_map = _ptr(row_map); a.col_map = _ptr(col_map); a.row_scale = _ptr(row_scale)
-    a.L, a.N_pad, a.K_pad, a.out_f, a.in_f, a.ones_col = L, N_pad, K_pad, out_f, in_f, ones_col
-    _lib.call("kair_unpack_linear_grad", a, _stream())
+    a.L, a.N_pad, a.K_pad = dWp.shape
+    a.out_f, a.in_f, a.ones_col = out_f, in_f, ones_col
+    return Launch("kair_unpack_linear_grad", a, keep)
 
 
-def pack_conv(W_ptrs, b_ptrs, Wp, WpT, bp, *, L, O, I, O_pad, I_pad, taps=9):
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
+    """Pack L same-shaped conv weights (O,I,kh,kw) into Wp [L,O_pad,taps*I_pad] (+ flipped WpT [L,I_pad,taps*O_pad])."""
+    keep = []
     a = _S["kair_pack_conv_args"]()
-    a.W = _ptr(W_ptrs); a.b = _ptr(b_ptrs); a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
-    a.L, a.O, a.I, a.O_pad, a.I_pad, a.taps = L, O, I, O_pad, I_pad, taps
-    _lib.call("kair_pack_conv", a, _stream())
+    a.W = _plist(W, Wp, keep); a.b = _plist(b, Wp, keep)
+    a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
+    a.L, a.O_pad = Wp.shape[0], Wp.shape[1]
+    a.O, a.I, a.I_pad, a.taps = O, I, I_pad, taps
+    return Launch("kair_pack_conv", a, keep)
 
 
-def unpack_conv_grad(dWp, dW_ptrs, db_ptrs, *, L, O, I, O_pad, I_pad, taps=9, ones_col=-1, center_tap=4):
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4):
+    keep = []
     a = _S["kair_unpack_conv_args"]()
-    a.dWp = _ptr(dWp); a.dW = _ptr(dW_ptrs); a.db = _ptr(db_ptrs)
-    a.L, a.O, a.I, a.O_pad, a.I_pad, a.taps, a.ones_col, a.center_tap = L, O, I, O_pad, I_pad, taps, ones_col, center_tap
-    _lib.call("kair_unpack_conv_grad", a, _stream())
+    a.dWp = _ptr(dWp); a.dW = _plist(dW, dWp, keep); a.db = _plist(db, dWp, keep)
+    a.L, a.O_pad = dWp.shape[0], dWp.shape[1]
+    a.O, a.I, a.I_pad, a.taps, a.ones_col, a.center_tap = O, I, I_pad, taps, ones_col, center_tap
+    return Launch("kair_unpack_conv_grad", a, keep)
 
 
 # ------------------------------------------------------------------------------------------------ LayerNorm
 
-def layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
+def build_layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
                   ones_col=-1):
     _req(x, torch.float32, "x")
     a = _S["kair_layernorm_args"]()
@@ -172,10 +241,10 @@ def layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_
     a.y_f32 = _ptr(y_f32); a.y_bf16 = _ptr(y_bf16); a.xhat_bf16 = _ptr(xhat_bf16)
     a.mean = _ptr(mean); a.rstd = _ptr(rstd)
     a.T = x.shape[0]; a.C = C; a.pitch = x.stride(0); a.ones_col = ones_col; a.eps = eps
-    _lib.call("kair_layernorm_fwd", a, _stream())
+    return Launch("kair_layernorm_fwd", a)
 
 
-def layernorm_bwd(x, mean, rstd, gamma, dgamma, dbeta, *, C, dy_f32=None, dy_bf16=None, dx_add=None, dx_f32=None,
+def build_layernorm_bwd(x, mean, rstd, gamma, dgamma, dbeta, *, C, dy_f32=None, dy_bf16=None, dx_add=None, dx_f32=None,
                   dx_bf16=None):
     a = _S["kair_layernorm_bwd_args"]()
     a.dy_f32 = _ptr(dy_f32); a.dy_bf16 = _ptr(dy_bf16)
@@ -183,7 +252,7 @@ def layernorm_bwd(x, mean, rstd, gamma, dgamma, dbeta, *, C, dy_f32=None, dy_bf1
     a.dx_add = _ptr(dx_add); a.dx_f32 = _ptr(dx_f32); a.dx_bf16 = _ptr(dx_bf16)
     a.dgamma = _ptr(dgamma); a.dbeta = _ptr(dbeta)
     a.T = x.shape[0]; a.C = C; a.pitch = x.stride(0)
-    _lib.call("kair_layernorm_bwd", a, _stream())
+    return Launch("kair_layernorm_bwd", a)
 
 
 # ------------------------------------------------------------------------------------------------ thin convolutions
@@ -200,18 +269,18 @@ def _conv_in_args(img, W, b, mean, rng, O, O_pad, pitch):
     return a
 
 
-def conv_in_fwd(img, W, b, mean, rng, *, O, O_pad, pitch, out_f32=None, out_bf16=None, act=ACT_NONE, act_slope=0.0,
+def build_conv_in_fwd(img, W, b, mean, rng, *, O, O_pad, pitch, out_f32=None, out_bf16=None, act=ACT_NONE, act_slope=0.0,
                 ones_col=-1):
     a = _conv_in_args(img, W, b, mean, rng, O, O_pad, pitch)
     a.out_f32 = _ptr(out_f32); a.out_bf16 = _ptr(out_bf16)
     a.act, a.act_slope, a.ones_col = act, act_slope, ones_col
-    _lib.call("kair_conv_in_fwd", a, _stream())
+    return Launch("kair_conv_in_fwd", a)
 
 
-def conv_in_wgrad(img, W, mean, rng, dW, db, *, O, O_pad, pitch, dy_f32=None, dy_bf16=None):
+def build_conv_in_wgrad(img, W, mean, rng, dW, db, *, O, O_pad, pitch, dy_f32=None, dy_bf16=None):
     a = _conv_in_args(img, W, None, mean, rng, O, O_pad, pitch)
     a.dy_f32 = _ptr(dy_f32); a.dy_bf16 = _ptr(dy_bf16); a.dW = _ptr(dW); a.db = _ptr(db)
-    _lib.call("kair_conv_in_wgrad", a, _stream())
+    return Launch("kair_conv_in_wgrad", a)
 
 
 def _conv_out_args(W, shape, C, pitch, out_scale):
@@ -223,28 +292,47 @@ def _conv_out_args(W, shape, C, pitch, out_scale):
     return a
 
 
-def conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, skip=None, skip_mean=None, skip_scale=0.0):
+def build_conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, skip=None, skip_mean=None, skip_scale=0.0):
     _req(feat, torch.bfloat16, "feat"); _req(out, torch.float32, "out")
     a = _conv_out_args(W, out.shape, C, pitch, out_scale)
     a.feat = _ptr(feat); a.b = _ptr(b); a.out = _ptr(out); a.out_mean = _ptr(out_mean)
     a.skip = _ptr(skip); a.skip_mean = _ptr(skip_mean); a.skip_scale = skip_scale
-    _lib.call("kair_conv_out_fwd", a, _stream())
+    return Launch("kair_conv_out_fwd", a)
 
 
-def conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
+def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
     _req(dout, torch.float32, "dout")
     a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
     a.dout = _ptr(dout); a.dfeat_f32 = _ptr(dfeat_f32); a.dfeat_bf16 = _ptr(dfeat_bf16)
-    _lib.call("kair_conv_out_dgrad", a, _stream())
+    return Launch("kair_conv_out_dgrad", a)
 
 
-def conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
+def build_conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
     _req(dout, torch.float32, "dout"); _req(feat, torch.bfloat16, "feat")
     a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
     a.dout = _ptr(dout); a.feat = _ptr(feat); a.dW = _ptr(dW); a.db = _ptr(db)
-    _lib.call("kair_conv_out_wgrad", a, _stream())
+    return Launch("kair_conv_out_wgrad", a)
 
 
-def add_inplace(y, x, yb=None):
+def build_add_inplace(y, x, yb=None):
+    """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")
-    _lib.check(_lib.load().kair_add_inplace(_ptr(y), _ptr(x), _ptr(yb), y.numel(), _stream()), "add_inplace")
+    fn = _lib.load().kair_add_inplace
+    py, px, pyb, n = _ptr(y), _ptr(x), _ptr(yb), y.numel()
+    return _RawLaunch("kair_add_inplace", lambda stream: fn(py, px, pyb, n, stream), keep=(y, x, yb))
+
+
+# ------------------------------------------------------------------------------------------------ eager forms
+# `name(...)` == `build_name(...).run(current stream)`: used by the unit tests and one-off calls.
+
+def _eager(builder):
+    def run(*args, **kwargs):
+        builder(*args, **kwargs).run(_stream())
+    run.__name__ = builder.__name__[len("build_"):]
+    run.__doc__ = builder.__doc__
+    return run
+
+
+for _n in [k for k in list(globals()) if k.startswith("build_")]:
+    globals()[_n[len("build_"):]] = _eager(globals()[_n])
+del _n

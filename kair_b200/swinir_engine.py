@@ -1,0 +1,468 @@
+"""Launch-list engine for SwinIR (forward and backward) on the sm_100a kernels.
+
+The engine turns one (batch, H, W) problem into a *plan*: a statically allocated HBM workspace plus two ordered
+lists of pre-built kernel launches (forward, backward).  Running a step is replaying a list -- one ctypes call per
+kernel, no tensor allocation, no host synchronisation -- so the plan is also CUDA-graph capturable.
+
+Data layout in HBM: activations are token-major NHWC, t = (b*H + h)*W + w, channels padded
+C -> Cp (180 -> 192); bf16 for every tensor-core operand, fp32 for the residual stream and all statistics.
+q/k/v and the attention output use a per-head pitch of 32 (head_dim 30 -> 32).  Spare padded columns carry a
+constant 1.0 ("ones column") so that each weight-gradient GEMM also produces the bias gradient.
+
+Reference arithmetic replaced (file:line in /root/reference): models/network_swinir.py:805-839 (SwinIR.forward),
+:790-803 (forward_features), :481-482 (RSTB.forward), :239-279 (SwinTransformerBlock.forward), :114-145
+(WindowAttention.forward), :24-30 (Mlp.forward), and autograd's backward of all of them.
+"""
+import math
+
+import torch
+
+from . import ops as _real_ops
+
+_BN = 192  # N tile of the instantiated GEMM epilogues for SwinIR-M
+
+
+def _round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+class SwinIRSpec:
+    """The constructor arguments of models/network_swinir.py:646-652 that shape the computation."""
+
+    def __init__(self, *, in_chans, embed_dim, depths, num_heads, window_size, mlp_ratio, qk_scale, img_range,
+                 upscale, upsampler, resi_connection, patch_norm, qkv_bias):
+        self.in_chans = in_chans
+        self.C = embed_dim
+        self.depths = tuple(depths)
+        self.num_heads = tuple(num_heads)
+        self.ws = window_size
+        self.hidden = int(embed_dim * mlp_ratio)
+        self.qk_scale = qk_scale
+        self.img_range = float(img_range)
+        self.upscale = upscale
+        self.upsampler = upsampler or ""
+        self.resi_connection = resi_connection
+        self.patch_norm = patch_norm
+        self.qkv_bias = qkv_bias
+
+    def check_supported(self):
+        """Loud errors for configurations the sm_100a kernels do not cover yet (no fallback path exists)."""
+        def bad(msg):
+            raise NotImplementedError("kair_b200 SwinIR: " + msg + " (see DESIGN.md, 'coverage')")
+        if self.ws != 8:
+            bad("window_size=%d; the tcgen05 window-attention kernel is built for 8x8 windows" % self.ws)
+        if len(set(self.num_heads)) != 1:
+            bad("num_heads must be the same in every RSTB")
+        nH = self.num_heads[0]
+        if nH % 2 or nH > 8 or self.C % nH:
+            bad("num_heads=%d must be even, <= 8 and divide embed_dim" % nH)
+        hd = self.C // nH
+        if hd >= 32:
+            bad("head_dim=%d must be < 32 (one padded column carries the proj bias gradient)" % hd)
+        if _round_up(self.C + 1, 64) != _BN or _round_up(self.hidden + 1, 64) % _BN:
+            bad("embed_dim=%d / mlp hidden=%d: only the C=180 tile configuration (Cp=192) is instantiated"
+                % (self.C, self.hidden))
+        if self.resi_connection != "1conv":
+            bad("resi_connection='%s'" % self.resi_connection)
+        if self.upsampler not in ("",):
+            bad("upsampler='%s'" % self.upsampler)
+        if self.in_chans > 4:
+            bad("in_chans=%d > 4" % self.in_chans)
+
+
+class _Blk:
+    """Activations of one Swin block kept for the backward pass (shared across blocks when not training)."""
+
+    def __init__(self, T, g, dev):
+        bf = lambda n: torch.zeros(T, n, dtype=torch.bfloat16, device=dev)
+        self.xh1 = bf(g.Cp)
+        self.r1 = torch.zeros(T, dtype=torch.float32, device=dev)
+        self.qkv = bf(g.QP)
+        self.att = bf(g.HP)
+        self.xh2 = bf(g.Cp)
+        self.r2 = torch.zeros(T, dtype=torch.float32, device=dev)
+        self.u = bf(g.Fp)
+        self.g = bf(g.Fp)
+
+
+class SwinIREngine:
+    def __init__(self, spec, params, device, ops=None):
+        """params: ordered {state_dict key: nn.Parameter} of the (reference-layout) module."""
+        spec.check_supported()
+        self.spec = spec
+        self.ops = ops or _real_ops
+        self.device = torch.device(device)
+        self.P = params
+        s = spec
+        self.C, self.nH = s.C, s.num_heads[0]
+        self.hd = s.C // self.nH
+        self.Cp = _round_up(s.C + 1, 64)
+        self.HP = self.nH * 32
+        self.QP = 3 * self.HP
+        self.Fp = _round_up(s.hidden + 1, 64)
+        self.L = sum(s.depths)
+        self.nl = len(s.depths)
+        self.scale = s.qk_scale or self.hd ** -0.5
+        self.mean = torch.tensor((0.4488, 0.4371, 0.4040) if s.in_chans == 3 else (0.0,) * s.in_chans,
+                                 dtype=torch.float32, device=self.device)
+        self._plans = {}
+        self._weights = None
+        self._build_maps()
+
+    # ------------------------------------------------------------------------------------------ packing maps
+    def _build_maps(self):
+        C, Cp, nH, hd, HP, QP, Fp, hid = self.C, self.Cp, self.nH, self.hd, self.HP, self.QP, self.Fp, self.spec.hidden
+        dev = self.device
+        i32 = lambda v: torch.tensor(v, dtype=torch.int32, device=dev)
+        f32 = lambda v: torch.tensor(v, dtype=torch.float32, device=dev)
+        self.map_c = i32([c if c < C else -1 for c in range(Cp)])
+        self.map_f = i32([c if c < hid else -1 for c in range(Fp)])
+        head = [(c // 32) * hd + c % 32 if c % 32 < hd else -1 for c in range(HP)]
+        self.map_h = i32(head)
+        qkv_rows, qkv_scale, qkv_const = [], [], []
+        for t3 in range(3):
+            for c in range(HP):
+                src = head[c]
+                qkv_rows.append(t3 * C + src if src >= 0 else -1)
+                qkv_scale.append(self.scale if t3 == 0 else 1.0)
+                # v of head 0 carries a constant 1.0 in its first padded column: softmax rows sum to one, so the
+                # attention output holds 1.0 there and the proj weight-gradient GEMM yields d(proj.bias)
+                qkv_const.append(1.0 if (t3 == 2 and c == hd) else 0.0)
+        self.map_qkv, self.scale_qkv, self.const_qkv = i32(qkv_rows), f32(qkv_scale), f32(qkv_const)
+
+    # ------------------------------------------------------------------------------------------ packed weights
+    def _block_names(self):
+        names = []
+        for i, d in enumerate(self.spec.depths):
+            for j in range(d):
+                names.append("layers.%d.residual_group.blocks.%d." % (i, j))
+        return names
+
+    def _weight_state(self, train):
+        """Packed bf16 operands (+ the launches that refresh them from the fp32 master parameters)."""
+        if self._weights is not None and (self._weights["train"] or not train):
+            return self._weights
+        o, P, dev = self.ops, self.P, self.device
+        L, nl, Cp, HP, QP, Fp, C = self.L, self.nl, self.Cp, self.HP, self.QP, self.Fp, self.C
+        bf = lambda *s: torch.zeros(s, dtype=torch.bfloat16, device=dev)
+        f32 = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+        blk = self._block_names()
+        W = {"train": train}
+        W["qkv"], W["qkvT"], W["bqkv"] = bf(L, QP, Cp), (bf(L, Cp, QP) if train else None), f32(L, QP)
+        W["proj"], W["projT"], W["bproj"] = bf(L, Cp, HP), (bf(L, HP, Cp) if train else None), f32(L, Cp)
+        W["fc1"], W["fc1T"], W["bfc1"] = bf(L, Fp, Cp), (bf(L, Cp, Fp) if train else None), f32(L, Fp)
+        W["fc2"], W["fc2T"], W["bfc2"] = bf(L, Cp, Fp), (bf(L, Fp, Cp) if train else None), f32(L, Cp)
+        W["conv"], W["convT"], W["bconv"] = bf(nl + 1, Cp, 9 * Cp), (bf(nl + 1, Cp, 9 * Cp) if train else None), \
+            f32(nl + 1, Cp)
+        get = lambda suffix: [P[b + suffix] for b in blk]
+        qb = get("attn.qkv.bias") if self.spec.qkv_bias else None
+        conv_names = ["layers.%d.conv" % i for i in range(nl)] + ["conv_after_body"]
+        W["conv_names"] = conv_names
+        W["pack"] = [
+            o.build_pack_linear(get("attn.qkv.weight"), qb, get("norm1.weight"), get("norm1.bias"), self.map_qkv,
+                                self.map_c, self.scale_qkv, self.const_qkv, W["qkv"], W["qkvT"], W["bqkv"],
+                                out_f=3 * C, in_f=C),
+            o.build_pack_linear(get("attn.proj.weight"), get("attn.proj.bias"), None, None, self.map_c, self.map_h,
+                                None, None, W["proj"], W["projT"], W["bproj"], out_f=C, in_f=C),
+            o.build_pack_linear(get("mlp.fc1.weight"), get("mlp.fc1.bias"), get("norm2.weight"), get("norm2.bias"),
+                                self.map_f, self.map_c, None, None, W["fc1"], W["fc1T"], W["bfc1"],
+                                out_f=self.spec.hidden, in_f=C),
+            o.build_pack_linear(get("mlp.fc2.weight"), get("mlp.fc2.bias"), None, None, self.map_c, self.map_f,
+                                None, None, W["fc2"], W["fc2T"], W["bfc2"], out_f=C, in_f=self.spec.hidden),
+            o.build_pack_conv([P[n + ".weight"] for n in conv_names], [P[n + ".bias"] for n in conv_names],
+                              W["conv"], W["convT"], W["bconv"], O=C, I=C, I_pad=Cp),
+        ]
+        W["versions"] = None
+        self._weights = W
+        self._plans = {}  # plans hold pointers into the packed operands
+        return W
+
+    def _param_versions(self):
+        return tuple(p._version for p in self.P.values())
+
+    def refresh_weights(self, W, stream):
+        """Re-pack when any master parameter changed (optimizer step, load_state_dict)."""
+        v = self._param_versions()
+        if W["versions"] != v:
+            for l in W["pack"]:
+                l.run(stream)
+            W["versions"] = v
+
+    # ------------------------------------------------------------------------------------------ plans
+    def plan(self, B, H, W, train):
+        key = (B, H, W, bool(train))
+        Wt = self._weight_state(train)
+        p = self._plans.get(key)
+        if p is None:
+            if len(self._plans) >= 4:  # bound the workspace kept alive by stale shapes
+                self._plans.pop(next(iter(self._plans)))
+            p = _Plan(self, Wt, B, H, W, bool(train))
+            self._plans[key] = p
+        return p
+
+
+class _Plan:
+    def __init__(self, eng, Wt, B, H, W, train):
+        s, o, dev = eng.spec, eng.ops, eng.device
+        if H % s.ws or W % s.ws or min(H, W) <= s.ws:
+            raise NotImplementedError("kair_b200 SwinIR: feature map %dx%d must be a multiple of and larger than the "
+                                      "window (%d)" % (H, W, s.ws))
+        self.eng, self.Wt, self.B, self.H, self.W, self.train = eng, Wt, B, H, W, train
+        self.generation = 0
+        T = B * H * W
+        C, Cp, HP, QP, Fp, L, nl = eng.C, eng.Cp, eng.HP, eng.QP, eng.Fp, eng.L, eng.nl
+        P = eng.P
+        f32 = lambda *sh: torch.zeros(sh, dtype=torch.float32, device=dev)
+        bf = lambda *sh: torch.zeros(sh, dtype=torch.bfloat16, device=dev)
+        geo = (B, H, W)
+        tps = H * W
+
+        self.img = f32(B, s.in_chans, H, W)
+        self.out = f32(B, s.in_chans, H, W)
+        first = f32(T, Cp)
+        mean0, rstd0 = f32(T), f32(T)
+        xs = [f32(T, Cp), f32(T, Cp)]
+        tin = [f32(T, Cp), f32(T, Cp)]
+        tfin = f32(T, Cp)
+        meanF, rstdF = f32(T), f32(T)
+        yb, resb = bf(T, Cp), bf(T, Cp)
+        if train:
+            blocks = [_Blk(T, eng, dev) for _ in range(L)]
+            x2b = [bf(T, Cp) for _ in range(nl)]
+        else:
+            shared = _Blk(T, eng, dev)
+            alt = _Blk.__new__(_Blk)  # the next block's xh1 / r1 must not alias the current one's
+            alt.__dict__.update(shared.__dict__)
+            alt.xh1, alt.r1 = bf(T, Cp), f32(T)
+            blocks = [shared if l % 2 == 0 else alt for l in range(L)]
+            x2b = [bf(T, Cp)] * nl
+        # DropPath per-sample scales: rows [0, L) attention branch, [L, 2L) MLP branch
+        self.dp = torch.ones(2 * L, B, dtype=torch.float32, device=dev)
+        self.dp_active = False
+        dpa = lambda l: self.dp[l] if train else None
+        dpm = lambda l: self.dp[L + l] if train else None
+
+        cf_w, cf_b = P["conv_first.weight"], P["conv_first.bias"]
+        cl_w, cl_b = P["conv_last.weight"], P["conv_last.bias"]
+        tables = [P[b + "attn.relative_position_bias_table"] for b in eng._block_names()]
+        mean_t = eng.mean
+        rng = s.img_range
+
+        # ================================================================================ forward
+        fwd = []
+        fwd.append(o.build_conv_in_fwd(self.img, cf_w, cf_b, mean_t, rng, O=C, O_pad=Cp, pitch=Cp, out_f32=first))
+        if s.patch_norm:
+            fwd.append(o.build_layernorm_fwd(first, P["patch_embed.norm.weight"], P["patch_embed.norm.bias"], C=C,
+                                             y_f32=tin[0], mean=mean0, rstd=rstd0))
+            t0 = tin[0]
+        else:
+            t0 = first
+        fwd.append(o.build_layernorm_fwd(t0, None, None, C=C, xhat_bf16=blocks[0].xh1, rstd=blocks[0].r1, ones_col=C))
+        l = 0
+        t_cur = t0
+        for i, depth in enumerate(s.depths):
+            xin = t_cur
+            for j in range(depth):
+                S = blocks[l]
+                shift = s.ws // 2 if j % 2 == 1 else 0
+                fwd.append(o.build_gemm_tn(S.xh1, Wt["qkv"][l], N=QP, K=Cp, bn=_BN, bias=Wt["bqkv"][l], outB=S.qkv))
+                fwd.append(o.build_window_attn_fwd(S.qkv, tables[l], S.att, batch=B, H=H, W=W, num_heads=eng.nH,
+                                                   window=s.ws, shift=shift))
+                fwd.append(o.build_gemm_tn(S.att, Wt["proj"][l], N=Cp, K=HP, bn=_BN, mode=o.EPI_RESID_LN,
+                                           bias=Wt["bproj"][l], resid=xin, outF=xs[0], outB=S.xh2, rowstat=S.r2,
+                                           n_valid=C, ones_col=C, acc_scale=dpa(l), tokens_per_sample=tps))
+                fwd.append(o.build_gemm_tn(S.xh2, Wt["fc1"][l], N=Fp, K=Cp, bn=_BN, mode=o.EPI_GELU,
+                                           bias=Wt["bfc1"][l], outB=S.g, outB2=S.u, ones_col=s.hidden))
+                if j < depth - 1:
+                    nxt = blocks[l + 1]
+                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_RESID_LN,
+                                               bias=Wt["bfc2"][l], resid=xs[0], outF=xs[1], outB=nxt.xh1,
+                                               rowstat=nxt.r1, n_valid=C, ones_col=C, acc_scale=dpm(l),
+                                               tokens_per_sample=tps))
+                    xin = xs[1]
+                else:
+                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_LINEAR,
+                                               bias=Wt["bfc2"][l], resid=xs[0], outB=x2b[i], ones_col=C,
+                                               acc_scale=dpm(l), tokens_per_sample=tps))
+                l += 1
+            if i < nl - 1:
+                nxt = blocks[l]
+                t_next = tin[1] if t_cur is tin[0] else tin[0]
+                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_RESID_LN,
+                                           bias=Wt["bconv"][i], resid=t_cur, outF=t_next, outB=nxt.xh1,
+                                           rowstat=nxt.r1, n_valid=C, ones_col=C))
+                t_cur = t_next
+            else:
+                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
+                                           bias=Wt["bconv"][i], resid=t_cur, outF=tfin))
+        fwd.append(o.build_layernorm_fwd(tfin, P["norm.weight"], P["norm.bias"], C=C, y_bf16=yb, mean=meanF,
+                                         rstd=rstdF, ones_col=C))
+        fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
+                                   bias=Wt["bconv"][nl], resid=first, outB=resb))
+        fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
+                                        skip=self.img, skip_mean=mean_t, skip_scale=rng))
+        self.fwd = fwd
+        self.bwd = None
+        if not train:
+            return
+
+        # ================================================================================ backward
+        self.dout = f32(B, s.in_chans, H, W)
+        # gradients in the parameters' own layouts: one flat fp32 buffer, views per parameter
+        sizes = [p.numel() for p in P.values()]
+        self.gflat = f32(sum(sizes))
+        G, off = {}, 0
+        for (k, p), n in zip(P.items(), sizes):
+            G[k] = self.gflat[off:off + n].view(p.shape)
+            off += n
+        self.G = G
+        # packed weight gradients (fp32, accumulated by the token-contraction GEMMs)
+        n_qkv, n_proj, n_fc = L * QP * Cp, L * Cp * HP, L * Fp * Cp
+        n_conv = (nl + 1) * Cp * 9 * Cp
+        self.dwflat = f32(n_qkv + n_proj + 2 * n_fc + n_conv)
+        o0 = 0
+        dWqkv = self.dwflat[o0:o0 + n_qkv].view(L, QP, Cp); o0 += n_qkv
+        dWproj = self.dwflat[o0:o0 + n_proj].view(L, Cp, HP); o0 += n_proj
+        dWfc1 = self.dwflat[o0:o0 + n_fc].view(L, Fp, Cp); o0 += n_fc
+        dWfc2 = self.dwflat[o0:o0 + n_fc].view(L, Cp, Fp); o0 += n_fc
+        dWconv = self.dwflat[o0:o0 + n_conv].view(nl + 1, Cp, 9 * Cp)
+        dresf, dresb, dyb = f32(T, Cp), bf(T, Cp), bf(T, Cp)
+        R = [(f32(T, Cp), bf(T, Cp)) for _ in range(3)]  # rotating (fp32, bf16) gradient buffers
+        du, datt, dqkv = bf(T, Fp), bf(T, HP), bf(T, QP)
+        blk_names = eng._block_names()
+
+        bwd = []
+        inv = 1.0 / rng
+        bwd.append(o.build_conv_out_dgrad(self.dout, cl_w, C=C, pitch=Cp, out_scale=inv, dfeat_f32=dresf,
+                                          dfeat_bf16=dresb))
+        bwd.append(o.build_conv_out_wgrad(self.dout, resb, cl_w, G["conv_last.weight"], G["conv_last.bias"], C=C,
+                                          pitch=Cp, out_scale=inv))
+        bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_BN, conv=geo))
+        bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, outB=dyb))
+        dt = 2
+        bwd.append(o.build_layernorm_bwd(tfin, meanF, rstdF, P["norm.weight"], G["norm.weight"], G["norm.bias"], C=C,
+                                         dy_bf16=dyb, dx_f32=R[dt][0], dx_bf16=R[dt][1]))
+        l_end = L
+        for i in reversed(range(nl)):
+            depth = s.depths[i]
+            a, b = [k for k in range(3) if k != dt]
+            bwd.append(o.build_gemm_nt(R[dt][1], x2b[i], dWconv[i], n1=Cp, n2=Cp, bn=_BN, conv=geo))
+            bwd.append(o.build_gemm_tn(R[dt][1], Wt["convT"][i], N=Cp, K=Cp, bn=_BN, conv=geo, outF=R[a][0],
+                                       outB=R[a][1], outB_scale=dpm(l_end - 1), tokens_per_sample=tps))
+            cur, oth = a, b
+            for j in reversed(range(depth)):
+                l = l_end - depth + j
+                S = blocks[l]
+                bwd.append(o.build_gemm_nt(R[cur][1], S.g, dWfc2[l], n1=Cp, n2=Fp, bn=_BN))
+                bwd.append(o.build_gemm_tn(R[cur][1], Wt["fc2T"][l], N=Fp, K=Cp, bn=_BN, mode=o.EPI_DGELU, aux=S.u,
+                                           outB=du))
+                bwd.append(o.build_gemm_nt(du, S.xh2, dWfc1[l], n1=Fp, n2=Cp, bn=_BN))
+                bwd.append(o.build_gemm_tn(du, Wt["fc1T"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_LNBWD, aux=S.xh2,
+                                           rowstat=S.r2, resid=R[cur][0], outF=R[oth][0], outB=R[oth][1], n_valid=C,
+                                           outB_scale=dpa(l), tokens_per_sample=tps))
+                cur, oth = oth, cur
+                bwd.append(o.build_gemm_nt(R[cur][1], S.att, dWproj[l], n1=Cp, n2=HP, bn=_BN))
+                bwd.append(o.build_gemm_tn(R[cur][1], Wt["projT"][l], N=HP, K=Cp, bn=_BN, outB=datt))
+                shift = s.ws // 2 if j % 2 == 1 else 0
+                bwd.append(o.build_window_attn_bwd(S.qkv, tables[l], datt, dqkv,
+                                                   G[blk_names[l] + "attn.relative_position_bias_table"], batch=B,
+                                                   H=H, W=W, num_heads=eng.nH, window=s.ws, shift=shift))
+                bwd.append(o.build_gemm_nt(dqkv, S.xh1, dWqkv[l], n1=QP, n2=Cp, bn=_BN))
+                bwd.append(o.build_gemm_tn(dqkv, Wt["qkvT"][l], N=Cp, K=QP, bn=_BN, mode=o.EPI_LNBWD, aux=S.xh1,
+                                           rowstat=S.r1, resid=R[cur][0], outF=R[oth][0], outB=R[oth][1], n_valid=C,
+                                           outB_scale=(dpm(l - 1) if j > 0 else None), tokens_per_sample=tps))
+                cur, oth = oth, cur
+            # RSTB skip: d(t_in) = d(block path) + d(t_out)
+            bwd.append(o.build_add_inplace(R[cur][0], R[dt][0], R[cur][1]))
+            dt = cur
+            l_end -= depth
+        if s.patch_norm:
+            dfirst = R[(dt + 1) % 3][0]
+            bwd.append(o.build_layernorm_bwd(first, mean0, rstd0, P["patch_embed.norm.weight"],
+                                             G["patch_embed.norm.weight"], G["patch_embed.norm.bias"], C=C,
+                                             dy_f32=R[dt][0], dx_add=dresf, dx_f32=dfirst))
+        else:
+            bwd.append(o.build_add_inplace(R[dt][0], dresf, None))
+            dfirst = R[dt][0]
+        bwd.append(o.build_conv_in_wgrad(self.img, cf_w, mean_t, rng, G["conv_first.weight"], G["conv_first.bias"],
+                                         O=C, O_pad=Cp, pitch=Cp, dy_f32=dfirst))
+        gl = lambda suffix: [G[bn_ + suffix] for bn_ in blk_names]
+        pl = lambda suffix: [P[bn_ + suffix] for bn_ in blk_names]
+        bwd.append(o.build_unpack_linear_grad(dWqkv, pl("attn.qkv.weight"), pl("norm1.weight"), pl("norm1.bias"),
+                                              gl("attn.qkv.weight"),
+                                              gl("attn.qkv.bias") if s.qkv_bias else None,
+                                              gl("norm1.weight"), gl("norm1.bias"), eng.map_qkv, eng.map_c,
+                                              eng.scale_qkv, out_f=3 * C, in_f=C, ones_col=C))
+        bwd.append(o.build_unpack_linear_grad(dWproj, pl("attn.proj.weight"), None, None, gl("attn.proj.weight"),
+                                              gl("attn.proj.bias"), None, None, eng.map_c, eng.map_h, None,
+                                              out_f=C, in_f=C, ones_col=eng.hd))
+        bwd.append(o.build_unpack_linear_grad(dWfc1, pl("mlp.fc1.weight"), pl("norm2.weight"), pl("norm2.bias"),
+                                              gl("mlp.fc1.weight"), gl("mlp.fc1.bias"), gl("norm2.weight"),
+                                              gl("norm2.bias"), eng.map_f, eng.map_c, None, out_f=s.hidden, in_f=C,
+                                              ones_col=C))
+        bwd.append(o.build_unpack_linear_grad(dWfc2, pl("mlp.fc2.weight"), None, None, gl("mlp.fc2.weight"),
+                                              gl("mlp.fc2.bias"), None, None, eng.map_c, eng.map_f, None, out_f=C,
+                                              in_f=s.hidden, ones_col=s.hidden))
+        cn = Wt["conv_names"]
+        bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
+                                            O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
+        self.bwd = bwd
+
+    # ------------------------------------------------------------------------------------------ execution
+    def set_drop_path(self, rates, generator=None):
+        """Draw the per-sample Bernoulli(keep)/keep DropPath scales of this step (network_swinir.py:204, 276-277).
+        rates: per-block drop probability (len L); all-zero rates leave the scales at 1."""
+        L = self.eng.L
+        if not any(r > 0 for r in rates):
+            if self.dp_active:
+                self.dp.fill_(1.0)
+                self.dp_active = False
+            return
+        keep = torch.tensor([1.0 - r for r in rates] * 2, dtype=torch.float32, device=self.dp.device).unsqueeze(1)
+        u = torch.rand(2 * L, self.B, device=self.dp.device, generator=generator)
+        self.dp.copy_((u < keep).float() / keep)
+        self.dp_active = True
+
+    def run_forward(self, x):
+        st = self.eng.ops.stream_handle()
+        self.eng.refresh_weights(self.Wt, st)
+        self.img.copy_(x)
+        for l in self.fwd:
+            l.run(st)
+        self.generation += 1
+        return self.out.clone()
+
+    def run_backward(self, dout):
+        st = self.eng.ops.stream_handle()
+        self.dout.copy_(dout)
+        self.gflat.zero_()
+        self.dwflat.zero_()
+        for l in self.bwd:
+            l.run(st)
+        flat = self.gflat.clone()
+        grads, off = [], 0
+        for p in self.eng.P.values():
+            n = p.numel()
+            grads.append(flat[off:off + n].view(p.shape))
+            off += n
+        return grads
+
+
+class SwinIRFunction(torch.autograd.Function):
+    """forward/backward pair over the whole network (the reference's plugin convention, models/op/fused_act.py:21-72)."""
+
+    @staticmethod
+    def forward(ctx, x, plan, *params):
+        out = plan.run_forward(x)
+        ctx.plan = plan
+        ctx.generation = plan.generation
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        plan = ctx.plan
+        if plan.generation != ctx.generation:
+            raise RuntimeError("kair_b200 SwinIR: backward() called after another forward() of the same shape "
+                               "overwrote the saved activations; run forward and backward in pairs")
+        grads = plan.run_backward(dout.contiguous())
+        return (None, None) + tuple(grads)

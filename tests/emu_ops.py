@@ -1,0 +1,463 @@
+"""TEST INFRASTRUCTURE: a PyTorch (CPU) emulation of every kair_b200.ops launch builder.
+
+It mirrors the *documented semantics* of the C-ABI kernels (include/kair_b200.h) -- padding, ones columns, bf16
+rounding points, accumulate-vs-overwrite -- so that (i) the host-side engines (launch-list construction, weight
+packing maps, gradient routing) can be checked on a machine without a GPU against the oracle / the reference, and
+(ii) the GPU unit tests have a second, independent statement of what each kernel must produce.
+
+It is never imported by the product package: tests inject it with `Engine(..., ops=emu_ops)`.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+EPI_LINEAR, EPI_GELU, EPI_RESID_LN, EPI_DGELU, EPI_LNBWD = range(5)
+ACT_NONE, ACT_LRELU = 0, 1
+
+
+class EmuLaunch:
+    def __init__(self, name, fn):
+        self.name, self.fn = name, fn
+
+    def run(self, stream=None):
+        self.fn()
+
+
+def stream_handle():
+    return None
+
+
+def zeros(shape, dtype, device):
+    return torch.zeros(shape, dtype=dtype, device=device)
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+def _gelu_grad(x):
+    return 0.5 * (1.0 + torch.erf(x * 0.7071067811865476)) + x * torch.exp(-0.5 * x * x) * 0.3989422804014327
+
+
+def _conv_acc(A, Bw, conv, K, N):
+    """implicit-GEMM 3x3: A NHWC [B,H,W,>=K] bf16, Bw [N, 9*K] with k = tap*K + ci."""
+    Bn, H, W = conv
+    x = A.reshape(Bn, H, W, -1)[..., :K].float().permute(0, 3, 1, 2)
+    w = Bw[:N, :9 * K].float().reshape(N, 9, K).permute(0, 2, 1).reshape(N, K, 3, 3)
+    y = F.conv2d(x, w, padding=1)
+    return y.permute(0, 2, 3, 1).reshape(Bn * H * W, N)
+
+
+def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
+                  aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None,
+                  acc_scale=None, outB_scale=None, tokens_per_sample=0):
+    assert K % 64 == 0 and N % bn == 0 and bn in (64, 128, 192, 256)
+    if mode in (EPI_RESID_LN, EPI_LNBWD):
+        assert N == bn
+
+    def run():
+        M = conv[0] * conv[1] * conv[2] if conv is not None else A.shape[0]
+        if conv is not None:
+            acc = _conv_acc(A, B, conv, K, N)
+        else:
+            acc = A[:, :K].float() @ B[:N, :K].float().t()
+        nv = n_valid if n_valid > 0 else N
+        cols = torch.arange(N)
+
+        def flat(t, width):
+            return t.reshape(M, -1)[:, :width]
+
+        def per_sample(s):
+            return s.repeat_interleave(tokens_per_sample)[:M].unsqueeze(1)
+
+        def put_bf(dst, v, ones=True):
+            v = v.clone()
+            if ones and 0 <= ones_col < N:
+                v[:, ones_col] = 1.0
+            flat(dst, N).copy_(_bf(v))
+
+        if mode == EPI_LINEAR:
+            v = acc + (bias[:N] if bias is not None else 0.0)
+            if acc_scale is not None:
+                v = v * per_sample(acc_scale)
+            if resid is not None:
+                v = v + flat(resid, N)
+            if act == ACT_LRELU:
+                v = torch.where(v > 0, v, v * act_slope)
+            if outF is not None:
+                flat(outF, N).copy_(v)
+            if outB is not None:
+                vb = v * per_sample(outB_scale) if outB_scale is not None else v
+                put_bf(outB, vb)
+        elif mode == EPI_GELU:
+            u = acc + (bias[:N] if bias is not None else 0.0)
+            if outB2 is not None:
+                flat(outB2, N).copy_(_bf(u))
+            put_bf(outB, F.gelu(u))
+        elif mode == EPI_RESID_LN:
+            v = acc + (bias[:N] if bias is not None else 0.0)
+            if acc_scale is not None:
+                v = v * per_sample(acc_scale)
+            if resid is not None:
+                v = v + flat(resid, N)
+            if outF is not None:
+                flat(outF, N).copy_(v)
+            mean = v.sum(1, keepdim=True) / nv
+            var = (((v - mean) ** 2).sum(1, keepdim=True) - (N - nv) * mean * mean).clamp_min(0) / nv
+            rstd = torch.rsqrt(var + ln_eps)
+            if rowstat is not None:
+                rowstat[:M].copy_(rstd[:, 0])
+            xh = (v - mean) * rstd
+            xh[:, nv:] = 0.0
+            put_bf(outB, xh)
+        elif mode == EPI_DGELU:
+            put_bf(outB, acc * _gelu_grad(flat(aux, N).float()), ones=False)
+        elif mode == EPI_LNBWD:
+            xh = flat(aux, N).float()
+            m1 = acc.sum(1, keepdim=True) / nv
+            m2 = (acc * xh).sum(1, keepdim=True) / nv
+            v = rowstat[:M].unsqueeze(1) * (acc - m1 - xh * m2)
+            if resid is not None:
+                v = v + flat(resid, N)
+            v[:, nv:] = 0.0
+            if outF is not None:
+                flat(outF, N).copy_(v)
+            if outB is not None:
+                vb = v * per_sample(outB_scale) if outB_scale is not None else v
+                put_bf(outB, vb, ones=False)
+        else:
+            raise AssertionError(mode)
+        del cols
+
+    return EmuLaunch("kair_gemm_tn", run)
+
+
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
+    assert n1 % 64 == 0 and n2 % bn == 0
+
+    def run():
+        if conv is None:
+            D[:n1, :n2] += A[:, :n1].float().t() @ B[:, :n2].float()
+            return
+        Bn, H, W = conv
+        a = A.reshape(Bn, H, W, -1)[..., :n1].float()
+        b = B.reshape(Bn, H, W, -1)[..., :n2].float()
+        bp = F.pad(b, (0, 0, 1, 1, 1, 1))
+        for tap in range(9):
+            dy, dx = tap // 3, tap % 3
+            bs = bp[:, dy:dy + H, dx:dx + W, :]
+            D[:n1, tap * n2:(tap + 1) * n2] += torch.einsum("bhwi,bhwj->ij", a, bs)
+
+    return EmuLaunch("kair_gemm_nt", run)
+
+
+# ------------------------------------------------------------------------------------------------ window attention
+
+def _win_index(H, W, ws, shift):
+    wi, wj = torch.meshgrid(torch.arange(H // ws), torch.arange(W // ws), indexing="ij")
+    r, c = torch.meshgrid(torch.arange(ws), torch.arange(ws), indexing="ij")
+    h = (wi.reshape(-1, 1) * ws + r.reshape(1, -1) + shift) % H
+    w = (wj.reshape(-1, 1) * ws + c.reshape(1, -1) + shift) % W
+    return h * W + w
+
+
+def _rel_index(ws):
+    ys, xs = torch.meshgrid(torch.arange(ws), torch.arange(ws), indexing="ij")
+    ys, xs = ys.reshape(-1), xs.reshape(-1)
+    return (ys[:, None] - ys[None, :] + ws - 1) * (2 * ws - 1) + (xs[:, None] - xs[None, :] + ws - 1)
+
+
+def _mask(H, W, ws, shift):
+    def rid(n):
+        p = torch.arange(n)
+        return (p >= n - ws).long() + (p >= n - shift).long()
+    ids = (3 * rid(H)[:, None] + rid(W)[None, :]).float()
+    ids = ids.view(H // ws, ws, W // ws, ws).permute(0, 2, 1, 3).reshape(-1, ws * ws)
+    d = ids[:, None, :] - ids[:, :, None]
+    return torch.where(d != 0, torch.full_like(d, -100.0), torch.zeros_like(d))
+
+
+def _attn_core(qkv, table, batch, H, W, nH, ws, shift):
+    """qkv fp32 [T, 3*nH*32] -> out [T, nH*32] (autograd-capable)."""
+    N = ws * ws
+    idx = _win_index(H, W, ws, shift)
+    nW = idx.shape[0]
+    x = qkv.view(batch, H * W, 3, nH, 32)[:, idx.reshape(-1)]
+    x = x.view(batch * nW, N, 3, nH, 32).permute(2, 0, 3, 1, 4)
+    q, k, v = x[0], x[1], x[2]
+    attn = q @ k.transpose(-2, -1)
+    bias = table[_rel_index(ws).reshape(-1)].view(N, N, nH).permute(2, 0, 1)
+    attn = attn + bias.unsqueeze(0)
+    if shift > 0:
+        attn = attn.view(batch, nW, nH, N, N) + _mask(H, W, ws, shift)[None, :, None]
+        attn = attn.view(-1, nH, N, N)
+    attn = attn.softmax(-1)
+    o = (attn @ v).transpose(1, 2).reshape(batch, nW * N, nH * 32)
+    out = torch.zeros(batch, H * W, nH * 32)
+    out = out.index_copy(1, idx.reshape(-1), o)
+    return out.view(batch * H * W, nH * 32)
+
+
+def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
+    assert window == 8 and shift in (0, 4)
+
+    def run():
+        w = 3 * num_heads * 32
+        o = _attn_core(qkv.reshape(batch * H * W, -1)[:, :w].float(), table.float(), batch, H, W, num_heads, window, shift)
+        out.reshape(batch * H * W, -1)[:, :num_heads * 32].copy_(_bf(o))
+
+    return EmuLaunch("kair_window_attn_fwd", run)
+
+
+def build_window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
+    def run():
+        T = batch * H * W
+        w = 3 * num_heads * 32
+        with torch.enable_grad():
+            q = qkv.reshape(T, -1)[:, :w].float().detach().requires_grad_(True)
+            t = table.float().detach().requires_grad_(True)
+            o = _attn_core(q, t, batch, H, W, num_heads, window, shift)
+            (o * dout.reshape(T, -1)[:, :num_heads * 32].float()).sum().backward()
+        dqkv.reshape(T, -1)[:, :w].copy_(_bf(q.grad))
+        dtable.add_(t.grad)
+
+    return EmuLaunch("kair_window_attn_bwd", run)
+
+
+# ------------------------------------------------------------------------------------------------ packing
+
+def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f):
+    def run():
+        L, N_pad, K_pad = Wp.shape
+        rm, cm = row_map.long(), col_map.long()
+        for l in range(L):
+            w = W[l].detach()
+            rs = row_scale if row_scale is not None else torch.ones(N_pad)
+            g = gamma[l].detach() if gamma is not None else torch.ones(in_f)
+            full = torch.zeros(N_pad, K_pad)
+            rv, cv = rm >= 0, cm >= 0
+            sub = w[rm[rv]][:, cm[cv]] * g[cm[cv]][None, :] * rs[rv][:, None]
+            full[rv.nonzero()[:, 0][:, None], cv.nonzero()[:, 0][None, :]] = sub
+            Wp[l].copy_(_bf(full))
+            if WpT is not None:
+                WpT[l].copy_(_bf(full.t()))
+            if bp is not None:
+                bias = torch.zeros(N_pad)
+                base = b[l].detach()[rm[rv]] if b is not None else torch.zeros(int(rv.sum()))
+                if beta is not None:
+                    base = base + w[rm[rv]] @ beta[l].detach()
+                bias[rv] = base * rs[rv]
+                if bias_const is not None:
+                    bias = bias + bias_const
+                bp[l].copy_(bias)
+
+    return EmuLaunch("kair_pack_linear", run)
+
+
+def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map, col_map, row_scale, *, out_f, in_f,
+                             ones_col):
+    def run():
+        L, N_pad, K_pad = dWp.shape
+        rm, cm = row_map.long(), col_map.long()
+        rv, cv = rm >= 0, cm >= 0
+        rs = row_scale if row_scale is not None else torch.ones(N_pad)
+        for l in range(L):
+            g = gamma[l].detach() if gamma is not None else torch.ones(in_f)
+            d = dWp[l]
+            sub = d[rv][:, cv] * rs[rv][:, None]          # d loss / d (W*gamma) at (src row, src col)
+            dWl = sub * g[cm[cv]][None, :]
+            if beta is not None:  # W also enters bp = rs * (b + W . beta)
+                dWl = dWl + (d[rv, ones_col] * rs[rv])[:, None] * beta[l].detach()[cm[cv]][None, :]
+            dW[l][rm[rv][:, None], cm[cv][None, :]] = dWl
+            if db is not None:
+                db[l][rm[rv]] = d[rv, ones_col] * rs[rv]
+            if dgamma is not None:
+                w = W[l].detach()[rm[rv]][:, cm[cv]] * rs[rv][:, None]
+                dgamma[l][cm[cv]] = (w * d[rv][:, cv]).sum(0)
+                dbeta[l][cm[cv]] = (w * d[rv, ones_col][:, None]).sum(0)
+
+    return EmuLaunch("kair_unpack_linear_grad", run)
+
+
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
+    def run():
+        L, O_pad = Wp.shape[0], Wp.shape[1]
+        for l in range(L):
+            w = W[l].detach().reshape(O, I, taps)
+            full = torch.zeros(O_pad, taps, I_pad)
+            full[:O, :, :I] = w.permute(0, 2, 1)
+            Wp[l].copy_(_bf(full.reshape(O_pad, taps * I_pad)))
+            if WpT is not None:
+                t = torch.zeros(I_pad, taps, O_pad)
+                t[:I, :, :O] = w.flip(2).permute(1, 2, 0)
+                WpT[l].copy_(_bf(t.reshape(I_pad, taps * O_pad)))
+            if bp is not None:
+                bias = torch.zeros(O_pad)
+                if b is not None:
+                    bias[:O] = b[l].detach()
+                bp[l].copy_(bias)
+
+    return EmuLaunch("kair_pack_conv", run)
+
+
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4):
+    def run():
+        L, O_pad = dWp.shape[0], dWp.shape[1]
+        for l in range(L):
+            d = dWp[l].reshape(O_pad, taps, I_pad)
+            dW[l].copy_(d[:O, :, :I].permute(0, 2, 1).reshape(dW[l].shape))
+            if db is not None and ones_col >= 0:
+                db[l].copy_(d[:O, center_tap, ones_col])
+
+    return EmuLaunch("kair_unpack_conv_grad", run)
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+
+def build_layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
+                        ones_col=-1):
+    def run():
+        v = x[:, :C]
+        m = v.mean(1, keepdim=True)
+        r = torch.rsqrt(((v - m) ** 2).mean(1, keepdim=True) + eps)
+        xh = (v - m) * r
+        if mean is not None:
+            mean.copy_(m[:, 0])
+        if rstd is not None:
+            rstd.copy_(r[:, 0])
+        pitch = x.shape[1]
+
+        def padded(t):
+            o = torch.zeros(x.shape[0], pitch)
+            o[:, :C] = t
+            return o
+        if y_f32 is not None or y_bf16 is not None:
+            y = padded(xh * gamma.detach() + beta.detach())
+            if y_f32 is not None:
+                y_f32.copy_(y)
+            if y_bf16 is not None:
+                if ones_col >= 0:
+                    y[:, ones_col] = 1.0
+                y_bf16.copy_(_bf(y))
+        if xhat_bf16 is not None:
+            h = padded(xh)
+            if ones_col >= 0:
+                h[:, ones_col] = 1.0
+            xhat_bf16.copy_(_bf(h))
+
+    return EmuLaunch("kair_layernorm_fwd", run)
+
+
+def build_layernorm_bwd(x, mean, rstd, gamma, dgamma, dbeta, *, C, dy_f32=None, dy_bf16=None, dx_add=None, dx_f32=None,
+                        dx_bf16=None):
+    def run():
+        dy = torch.zeros(x.shape[0], C)
+        if dy_f32 is not None:
+            dy = dy + dy_f32[:, :C]
+        if dy_bf16 is not None:
+            dy = dy + dy_bf16[:, :C].float()
+        xh = (x[:, :C] - mean[:, None]) * rstd[:, None]
+        g = dy * gamma.detach()
+        dx = rstd[:, None] * (g - g.mean(1, keepdim=True) - xh * (g * xh).mean(1, keepdim=True))
+        if dx_add is not None:
+            dx = dx + dx_add[:, :C]
+        full = torch.zeros_like(x)
+        full[:, :C] = dx
+        if dx_f32 is not None:
+            dx_f32.copy_(full)
+        if dx_bf16 is not None:
+            dx_bf16.copy_(_bf(full))
+        dgamma.add_((dy * xh).sum(0))
+        dbeta.add_(dy.sum(0))
+
+    return EmuLaunch("kair_layernorm_bwd", run)
+
+
+# ------------------------------------------------------------------------------------------------ thin convolutions
+
+def _tokens_to_nchw(t, B, H, W, C):
+    return t.reshape(B, H, W, -1)[..., :C].permute(0, 3, 1, 2)
+
+
+def build_conv_in_fwd(img, W, b, mean, rng, *, O, O_pad, pitch, out_f32=None, out_bf16=None, act=ACT_NONE, act_slope=0.0,
+                      ones_col=-1):
+    def run():
+        Bn, ci, H, Wd = img.shape
+        xin = (img - mean.view(1, ci, 1, 1)) * rng
+        y = F.conv2d(xin, W.detach(), b.detach() if b is not None else None, padding=1)
+        if act == ACT_LRELU:
+            y = torch.where(y > 0, y, y * act_slope)
+        full = torch.zeros(Bn * H * Wd, pitch)
+        full[:, :O] = y.permute(0, 2, 3, 1).reshape(-1, O)
+        if out_f32 is not None:
+            out_f32.copy_(full)
+        if out_bf16 is not None:
+            if ones_col >= 0:
+                full[:, ones_col] = 1.0
+            out_bf16.copy_(_bf(full))
+
+    return EmuLaunch("kair_conv_in_fwd", run)
+
+
+def build_conv_in_wgrad(img, W, mean, rng, dW, db, *, O, O_pad, pitch, dy_f32=None, dy_bf16=None):
+    def run():
+        Bn, ci, H, Wd = img.shape
+        dy = torch.zeros(Bn * H * Wd, O)
+        if dy_f32 is not None:
+            dy = dy + dy_f32[:, :O]
+        if dy_bf16 is not None:
+            dy = dy + dy_bf16[:, :O].float()
+        dyi = _tokens_to_nchw(dy, Bn, H, Wd, O)
+        xin = (img - mean.view(1, ci, 1, 1)) * rng
+        dW.add_(torch.nn.grad.conv2d_weight(xin, W.shape, dyi.contiguous(), padding=1))
+        if db is not None:
+            db.add_(dyi.sum((0, 2, 3)))
+
+    return EmuLaunch("kair_conv_in_wgrad", run)
+
+
+def build_conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, skip=None, skip_mean=None, skip_scale=0.0):
+    def run():
+        Bn, co, H, Wd = out.shape
+        x = _tokens_to_nchw(feat.float(), Bn, H, Wd, C)
+        y = F.conv2d(x, W.detach(), b.detach() if b is not None else None, padding=1)
+        if skip is not None:
+            y = y + skip_scale * (skip - skip_mean.view(1, co, 1, 1))
+        out.copy_(y * out_scale + out_mean.view(1, co, 1, 1))
+
+    return EmuLaunch("kair_conv_out_fwd", run)
+
+
+def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
+    def run():
+        Bn, co, H, Wd = dout.shape
+        dx = torch.nn.grad.conv2d_input((Bn, C, H, Wd), W.detach(), dout * out_scale, padding=1)
+        full = torch.zeros(Bn * H * Wd, pitch)
+        full[:, :C] = dx.permute(0, 2, 3, 1).reshape(-1, C)
+        if dfeat_f32 is not None:
+            dfeat_f32.copy_(full)
+        if dfeat_bf16 is not None:
+            dfeat_bf16.copy_(_bf(full))
+
+    return EmuLaunch("kair_conv_out_dgrad", run)
+
+
+def build_conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
+    def run():
+        Bn, co, H, Wd = dout.shape
+        x = _tokens_to_nchw(feat.float(), Bn, H, Wd, C).contiguous()
+        dW.add_(torch.nn.grad.conv2d_weight(x, W.shape, (dout * out_scale).contiguous(), padding=1))
+        if db is not None:
+            db.add_((dout * out_scale).sum((0, 2, 3)))
+
+    return EmuLaunch("kair_conv_out_wgrad", run)
+
+
+def build_add_inplace(y, x, yb=None):
+    def run():
+        y.add_(x)
+        if yb is not None:
+            yb.copy_(_bf(y))
+
+    return EmuLaunch("kair_add_inplace", run)
