@@ -218,7 +218,8 @@ def window_attention(xw, sd, p, nh, ws, mask, qk_scale=None):
 
 
 def swin_block(x, x_size, sd, p, nh, ws, shift, cfg, drop_mask=None):
-    """SwinTransformerBlock.forward (network_swinir.py:239-279). drop_mask: per-sample DropPath scale or None."""
+    """SwinTransformerBlock.forward (network_swinir.py:239-279). drop_mask: None, or the pair of per-sample DropPath
+    scales (attention branch, MLP branch) -- the reference draws them independently (:276 and :277)."""
     H, W = x_size
     B, L, C = x.shape
     if min(x_size) <= ws:  # (:193-196) is decided at construction from img_size; tests use matching sizes
@@ -232,13 +233,13 @@ def swin_block(x, x_size, sd, p, nh, ws, shift, cfg, drop_mask=None):
     out = torch.empty_like(xn)
     out[:, idx, :] = aw.reshape(B, -1, C)                            # window_reverse + roll(+shift)
     if drop_mask is not None:
-        out = out * drop_mask.view(B, 1, 1)
+        out = out * drop_mask[0].view(B, 1, 1)
     x = shortcut + out
     y = F.layer_norm(x, (C,), sd[p + "norm2.weight"], sd[p + "norm2.bias"], 1e-5)
     y = F.linear(F.gelu(F.linear(y, sd[p + "mlp.fc1.weight"], sd[p + "mlp.fc1.bias"])),
                  sd[p + "mlp.fc2.weight"], sd[p + "mlp.fc2.bias"])
     if drop_mask is not None:
-        y = y * drop_mask.view(B, 1, 1)
+        y = y * drop_mask[1].view(B, 1, 1)
     return x + y
 
 

@@ -12,6 +12,11 @@ CFG = dict(upscale=1, in_chans=1, img_size=16, window_size=8, img_range=1.0, dep
            num_heads=[6, 6], mlp_ratio=2, upsampler="", resi_connection="1conv")
 
 
+def _rel_l2(a, b):
+    """bf16 tensor-core path vs fp32 reference: relative L2 error of a gradient tensor"""
+    return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+
 def _loss(out, target):
     # smooth loss: with Charbonnier(eps=1e-9) dL/dy = sign(y - t)/n, whose sign flips under bf16 rounding
     return torch.mean((out - target) ** 2)
@@ -69,8 +74,7 @@ def test_engine_matches_reference_module(in_chans, H, W):
     assert (y - y_ref.detach()).abs().max().item() < 2e-2
     for k, p in ref.named_parameters():
         gr = p.grad
-        rel = (grads[k] - gr).abs().max().item() / (gr.abs().max().item() + 1e-12)
-        assert rel < 5e-2, (k, rel)
+        assert _rel_l2(grads[k], gr) < 3e-2, (k, _rel_l2(grads[k], gr))
 
 
 def test_engine_matches_oracle_with_drop_path():
@@ -91,5 +95,4 @@ def test_engine_matches_oracle_with_drop_path():
     assert (y - y_ref.detach()).abs().max().item() < 2e-2
     for k, p in mine.named_parameters():
         gr = sd[k].grad
-        rel = (grads[k] - gr).abs().max().item() / (gr.abs().max().item() + 1e-12)
-        assert rel < 5e-2, (k, rel)
+        assert _rel_l2(grads[k], gr) < 3e-2, (k, _rel_l2(grads[k], gr))
