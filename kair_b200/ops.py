@@ -322,6 +322,35 @@ def build_add_inplace(y, x, yb=None):
     return _RawLaunch("kair_add_inplace", lambda stream: fn(py, px, pyb, n, stream), keep=(y, x, yb))
 
 
+# ------------------------------------------------------------------------------------------------ lifetimes
+# A Launch stores raw device addresses, so it must own a reference to every tensor it points into: the plan's
+# workspace tensors are otherwise free to be garbage-collected (and their memory reused) once the builder returns.
+
+def _tensors_of(args, kwargs):
+    out = []
+    for v in list(args) + list(kwargs.values()):
+        if isinstance(v, torch.Tensor):
+            out.append(v)
+        elif isinstance(v, (list, tuple)):
+            out.extend(t for t in v if isinstance(t, torch.Tensor))
+    return out
+
+
+def _owning(builder):
+    def build(*args, **kwargs):
+        launch = builder(*args, **kwargs)
+        launch.keep = tuple(launch.keep) + tuple(_tensors_of(args, kwargs))
+        return launch
+    build.__name__ = builder.__name__
+    build.__doc__ = builder.__doc__
+    return build
+
+
+for _n in [k for k in list(globals()) if k.startswith("build_")]:
+    globals()[_n] = _owning(globals()[_n])
+del _n
+
+
 # ------------------------------------------------------------------------------------------------ eager forms
 # `name(...)` == `build_name(...).run(current stream)`: used by the unit tests and one-off calls.
 

@@ -1,0 +1,143 @@
+"""Parity of the drop-in SwinIR module (CUDA path, through the C ABI) against the CPU oracle on the same seeded
+inputs and weights.  Tolerances: bf16 tensor-core mode, |out - ref|_max <= 2e-2 on [0,1] images (north_star);
+gradients are compared in relative L2 (<= 3e-2) because the fp32-mode 1e-3 bound does not apply to bf16 operands."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+CFG = dict(upscale=1, in_chans=1, img_size=32, window_size=8, img_range=1.0, depths=[2, 2], embed_dim=180,
+           num_heads=[6, 6], mlp_ratio=2, upsampler="", resi_connection="1conv")
+
+
+def _oracle_cfg(cfg):
+    from oracle import swinir_oracle as so
+    return so.SwinIRConfig(img_size=cfg["img_size"], in_chans=cfg["in_chans"], embed_dim=cfg["embed_dim"],
+                           depths=tuple(cfg["depths"]), num_heads=tuple(cfg["num_heads"]),
+                           window_size=cfg["window_size"], mlp_ratio=cfg["mlp_ratio"], upscale=cfg["upscale"],
+                           img_range=cfg["img_range"], upsampler=cfg["upsampler"])
+
+
+def _randomize(model, seed):
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for k, p in model.named_parameters():
+            if "norm" in k and k.endswith("weight"):
+                p.copy_(1.0 + 0.2 * torch.randn(p.shape, generator=g))
+            elif k.endswith("bias"):
+                p.copy_(0.1 * torch.randn(p.shape, generator=g))
+            elif k.endswith("relative_position_bias_table"):
+                p.copy_(0.3 * torch.randn(p.shape, generator=g))
+            else:
+                p.mul_(1.5)
+
+
+def _rel_l2(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+
+@pytest.mark.parametrize("in_chans,B,H,W", [(1, 2, 32, 32), (3, 1, 24, 40), (2, 3, 16, 16)])
+def test_forward_backward_vs_oracle(in_chans, B, H, W):
+    from kair_b200.network_swinir import SwinIR
+    from oracle import swinir_oracle as so
+    cfg = dict(CFG, in_chans=in_chans)
+    torch.manual_seed(0)
+    model = SwinIR(drop_path_rate=0.0, **cfg)
+    _randomize(model, 11)
+    sd = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point) for k, v in model.state_dict().items()}
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(B, in_chans, H, W, generator=g)
+    tgt = torch.rand(B, in_chans, H, W, generator=g)
+    y_ref = so.swinir_forward(sd, x, _oracle_cfg(cfg))
+    torch.mean((y_ref - tgt) ** 2).backward()
+
+    model = model.cuda().train()
+    y = model(x.cuda())
+    torch.mean((y - tgt.cuda()) ** 2).backward()
+    torch.cuda.synchronize()
+    err = (y.detach().cpu() - y_ref.detach()).abs().max().item()
+    assert err < 2e-2, err
+    bad = []
+    for k, p in model.named_parameters():
+        r = _rel_l2(p.grad.cpu(), sd[k].grad)
+        if not r < 3e-2:
+            bad.append((k, r))
+    assert not bad, bad[:8]
+
+
+def test_eval_matches_train_forward_and_pads():
+    """no_grad/eval plan (shared activation buffers) == training plan; odd sizes are reflect-padded and cropped."""
+    from kair_b200.network_swinir import SwinIR
+    from oracle import swinir_oracle as so
+    torch.manual_seed(0)
+    model = SwinIR(drop_path_rate=0.1, **CFG)
+    _randomize(model, 12)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    x = torch.rand(2, 1, 27, 35, generator=torch.Generator().manual_seed(6))
+    y_ref = so.swinir_forward(sd, x, _oracle_cfg(CFG))
+    model = model.cuda().eval()
+    with torch.no_grad():
+        y_eval = model(x.cuda())
+    y_train = model(x.cuda())          # grad enabled, eval mode: DropPath off
+    assert y_eval.shape == (2, 1, 27, 35)
+    assert (y_eval.cpu() - y_ref).abs().max().item() < 2e-2
+    assert torch.equal(y_eval, y_train.detach())
+
+
+def test_drop_path_scales_replayed():
+    """DropPath: inject the per-sample scales, compare with the oracle replaying the same masks."""
+    from kair_b200.network_swinir import SwinIR
+    from oracle import swinir_oracle as so
+    torch.manual_seed(0)
+    model = SwinIR(drop_path_rate=0.1, **CFG)
+    _randomize(model, 13)
+    sd = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point) for k, v in model.state_dict().items()}
+    g = torch.Generator().manual_seed(7)
+    B, L = 4, 4
+    x = torch.rand(B, 1, 32, 32, generator=g)
+    drop = (torch.rand(2 * L, B, generator=g) < 0.8).float() / 0.8
+    y_ref = so.swinir_forward(sd, x, _oracle_cfg(CFG), drop_masks=[(drop[l], drop[L + l]) for l in range(L)])
+    y_ref.square().mean().backward()
+    model = model.cuda().train()
+    eng = model.engine(torch.device("cuda:0"))
+    plan = eng.plan(B, 32, 32, True)
+    from kair_b200.swinir_engine import SwinIRFunction
+    plan.dp.copy_(drop.cuda())
+    y = SwinIRFunction.apply(x.cuda(), plan, *eng.P.values())
+    y.square().mean().backward()
+    assert (y.detach().cpu() - y_ref.detach()).abs().max().item() < 2e-2
+    bad = [(k, _rel_l2(p.grad.cpu(), sd[k].grad)) for k, p in model.named_parameters()
+           if not _rel_l2(p.grad.cpu(), sd[k].grad) < 5e-2]
+    assert not bad, bad[:8]
+
+
+def test_cpu_tensor_is_rejected():
+    from kair_b200.network_swinir import SwinIR
+    model = SwinIR(drop_path_rate=0.0, **CFG)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        model(torch.rand(1, 1, 32, 32))
+
+
+def test_full_size_properties():
+    """cfg2 shape (B=8, 1x128x128, SwinIR-M): finite outputs, identity-at-zero-weights property, determinism."""
+    from kair_b200.network_swinir import SwinIR
+    torch.manual_seed(0)
+    model = SwinIR(upscale=1, in_chans=1, img_size=128, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                   num_heads=[6] * 6, mlp_ratio=2, upsampler="", resi_connection="1conv").cuda().train()
+    x = torch.rand(8, 1, 128, 128, device="cuda")
+    y1 = model(x)
+    y1.square().mean().backward()
+    g1 = model.conv_first.weight.grad.clone()
+    assert torch.isfinite(y1).all() and all(torch.isfinite(p.grad).all() for p in model.parameters())
+    model.zero_grad()
+    model.eval()
+    with torch.no_grad():
+        y2 = model(x)
+    # conv_last zeroed => network output == input (x + conv_last(res) with zero weights), exactly
+    with torch.no_grad():
+        model.conv_last.weight.zero_(); model.conv_last.bias.zero_()
+        y3 = model(x)
+    assert torch.equal(y3, x)
+    assert torch.isfinite(y2).all() and g1.abs().sum().item() > 0
