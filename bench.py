@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""Headline benchmark: SwinIR-M gray-denoising TRAINING step (BASELINE.json configs[1], "cfg2") on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K --warmup W # the reference arithmetic on the host CPU cores
+
+One step = zero_grad -> forward -> Charbonnier loss -> backward -> Adam (models/model_plain.py:270-302 of the
+reference) on 8 patches of 1x128x128 per GPU.  `value` is patches/s over all ranks with inputs resident in HBM;
+`e2e` is the same step fed from pinned host memory with the loss read back every step.  The roofline object
+describes the kernel group that takes the largest share of the step, timed per launch with CUDA events on the
+launching stream in an instrumented replay of the same launch lists right after the timed region.
+
+/root/reference does not exist on the GPU box: the reference arm and the cpu_baseline leg time the oracle
+(oracle/swinir_oracle.py, a functional restatement of the reference modules pinned against them by tests/).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CFG2 = dict(upscale=1, in_chans=1, img_size=128, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+            num_heads=[6] * 6, mlp_ratio=2, upsampler=None, resi_connection="1conv")
+BATCH_PER_GPU = 8
+PATCH = 128
+FWD_GFLOP_PER_PATCH = 399.94          # SURVEY.md section 8(d), measured with hooks on the reference modules
+REAL_DIMS = {192: 180, 576: 540, 384: 360, "head_dim": 30}
+WORKLOAD = "cfg2: SwinIR-M gray-DN training (ws8, C180, 6x6 RSTB), SPECT-shaped 1x128x128 patches, batch 8/GPU"
+
+
+# ------------------------------------------------------------------------------------------------ synthetic data
+
+def spect_batch(batch, size, seed):
+    """SPECT-shaped synthetic pair: lambda = smooth positive field of Gaussian blobs (mean ~5
+    counts), H = Poisson(lambda)/150, L = 8*Binomial(Poisson(lambda), 1/8)/150 (linear /150 normalisation,
+    utils/utils_spect.py:15-16 of the reference)."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    yy, xx = torch.meshgrid(torch.arange(size, dtype=torch.float32), torch.arange(size, dtype=torch.float32),
+                            indexing="ij")
+    lam = torch.full((batch, 1, size, size), 0.8)
+    for b in range(batch):
+        for _ in range(6):
+            cy, cx = (torch.rand(2, generator=g) * size).tolist()
+            sig = 6.0 + 20.0 * torch.rand(1, generator=g).item()
+            amp = 4.0 + 36.0 * torch.rand(1, generator=g).item() ** 2
+            lam[b, 0] += amp * torch.exp(-((yy - cy) ** 2 + (xx - cx) ** 2) / (2 * sig * sig))
+    counts = torch.poisson(lam, generator=g)
+    low = torch.binomial(counts, torch.full_like(counts, 0.125), generator=g) * 8.0
+    return (low / 150.0).contiguous(), (counts / 150.0).contiguous()
+
+
+def charbonnier(x, y, eps=1e-9):
+    """models/loss.py:208-218 of the reference."""
+    import torch
+    d = x - y
+    return torch.mean(torch.sqrt(d * d + eps))
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.mask, self.max_mhz = [], 0, None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001 - reported in the JSON line
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    self.mask |= nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    self.mask |= nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self.is_alive():
+            self.join()
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "samples": len(s),
+                "reasons": sorted(v for k, v in self.REASONS.items() if self.mask & k)}
+
+
+def _physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except (ValueError, IndexError):
+            return local_rank
+    return local_rank
+
+
+# ------------------------------------------------------------------------------------------------ oracle legs (CPU)
+
+def oracle_train_steps(steps, warmup, batch, seed=0, budget_s=240.0):
+    """The reference's training step restated on the oracle (CPU, fp32, all host threads).  Returns
+    (seconds per step, steps actually timed, threads)."""
+    import torch
+    from oracle import swinir_oracle as so
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    cfg = so.SwinIRConfig(img_size=CFG2["img_size"], in_chans=1, embed_dim=180, depths=(6,) * 6, num_heads=(6,) * 6,
+                          window_size=8, mlp_ratio=2, upscale=1, img_range=1.0, upsampler="")
+    sd = so.deterministic_state(so.state_spec(cfg), seed, cfg)
+    params = [v for k, v in sd.items() if v.dtype.is_floating_point and not k.endswith("attn_mask")]
+    for p in params:
+        p.requires_grad_(True)
+    opt = torch.optim.Adam(params, lr=2e-4, betas=(0.9, 0.999), weight_decay=0)
+    low, high = spect_batch(batch, PATCH, 1234)
+    times = []
+    t_begin = time.perf_counter()
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        out = so.swinir_forward(sd, low, cfg)
+        loss = so.charbonnier(out, high)
+        loss.backward()
+        opt.step()
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+        if time.perf_counter() - t_begin > budget_s and times:
+            break
+    return sum(times) / len(times), len(times), threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_batch = 1
+    sec, done, threads = oracle_train_steps(args.steps, args.warmup, sample_batch)
+    value = sample_batch / sec
+    sample = "%d patch(es) of the 8-patch batch per step, %d timed steps, fp32, oracle port of the reference " \
+             "modules (reference tree is not on the GPU box)" % (sample_batch, done)
+    line = {
+        "impl": "reference", "metric": "SwinIR-M gray-DN train patches/s", "value": value, "unit": "patches/s",
+        "n_gpus": args.gpus, "steps": done, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "patches/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "patches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from kair_b200 import profiling
+    from kair_b200.network_swinir import SwinIR
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device; the sm_100a path has no CPU fallback "
+                           "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    torch.manual_seed(0)
+    model = SwinIR(**CFG2).to(dev).train()           # drop_path_rate: constructor default 0.1, as define_G leaves it
+    net = model
+    if world > 1:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        net = DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
+    opt = torch.optim.Adam(model.parameters(), lr=2e-4, betas=(0.9, 0.999), weight_decay=0, fused=True)
+
+    low_h, high_h = spect_batch(BATCH_PER_GPU, PATCH, 1234 + rank)
+    low_h, high_h = low_h.pin_memory(), high_h.pin_memory()
+    low, high = low_h.to(dev), high_h.to(dev)
+
+    def step(lo, hi):
+        opt.zero_grad(set_to_none=True)
+        out = net(lo)
+        loss = charbonnier(out, hi)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    for _ in range(max(args.warmup, 3)):
+        step(low, high)
+    sampler = ClockSampler(_physical_gpu_index(local_rank))
+    sampler.start()
+    ms_total = timed(lambda: step(low, high), args.steps)
+    clocks = sampler.stop()
+
+    # end-to-end: inputs come from pinned host memory every step, the loss goes back to the host every step
+    def e2e_step():
+        low.copy_(low_h, non_blocking=True)
+        high.copy_(high_h, non_blocking=True)
+        return step(low, high).item()
+
+    for _ in range(2):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+
+    patches = BATCH_PER_GPU * world
+    ms_step = ms_total / args.steps
+    value = patches / (ms_step * 1e-3)
+    e2e_value = patches / (ms_e2e / args.steps * 1e-3)
+
+    # ---- per-launch instrumented replay (rank 0): which kernel group dominates, and its achieved TFLOP/s
+    plan = model.engine(dev).plan(BATCH_PER_GPU, PATCH, PATCH, True)
+    launches = list(plan.fwd) + list(plan.bwd)
+    n_pack = len(plan.Wt["pack"])
+    roof, groups = None, None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:  # noqa: BLE001
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained")
+        peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        if not peak_tf:
+            peak_tf, peak_src = 1400.0, "fallback (B200_PROFILING.md sustained ~1.4 PFLOP/s)"
+        import ctypes
+        sth = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        plan.gflat.zero_(); plan.dwflat.zero_()
+        per = profiling.time_launches(launches, sth, reps=3)
+        groups = profiling.summarize(launches, per, REAL_DIMS)
+        tot = sum(d["ms"] for d in groups.values())
+        top_tag, top = max(groups.items(), key=lambda kv: kv[1]["ms"])
+        ach = top["flops"] / (top["ms"] * 1e-3) / 1e12 if top["ms"] > 0 else 0.0
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                "traffic": None, "kernel": top_tag, "launches_per_step": top["count"],
+                "avg_launch_ms": top["ms"] / top["count"], "share_of_kernel_time": top["ms"] / tot,
+                "peak_source": peak_src,
+                "whole_step": {"tflops": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step,
+                               "frac": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step / peak_tf,
+                               "sum_kernel_ms": tot},
+                "groups": {k: {"n": v["count"], "ms": round(v["ms"], 4),
+                               "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0}
+                           for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sec, done, threads = oracle_train_steps(3, 1, 1, budget_s=60.0)
+        cpu = {"value": 1.0 / sec, "unit": "patches/s", "cores": threads, "kind": "port",
+               "sample": "1 patch (1x128x128) per step, %d timed steps after 1 warm-up, fp32 oracle port of the "
+                         "reference modules incl. Adam" % done}
+
+    if rank == 0:
+        line = {
+            "metric": "SwinIR-M gray-DN train patches/s", "value": value, "unit": "patches/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": patches, "parallelism": "dp%d" % world,
+                       "drop_path_rate": 0.1, "optimizer": "Adam lr 2e-4", "loss": "Charbonnier eps 1e-9",
+                       "l2": "per-step working set (~13 GB of activations) far exceeds the 126 MB L2; no flush needed"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "patches/s",
+                    "h2d_bytes_per_step": (low_h.numel() + high_h.numel()) * 4 * world,
+                    "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": (len(launches) + n_pack) * args.steps,
+            "roofline": roof, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
