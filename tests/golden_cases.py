@@ -1,0 +1,117 @@
+"""TEST INFRASTRUCTURE: the seeded cases shared by tests/golden/make_golden.py (reference side) and the parity tests
+(oracle side / CUDA side).  Weights come from oracle.swinir_oracle.deterministic_state (one CPU generator per key),
+inputs and targets from a seeded CPU generator, so both sides rebuild identical tensors without storing them."""
+import math
+
+import torch
+
+from oracle import convnets_oracle as co
+from oracle import swinir_oracle as so
+
+_SW = dict(net="swinir", patch_norm=True, qkv_bias=True)
+CASES = {
+    # SwinIR-M shaped (C=180, 6 heads, ws 8, mlp 2) gray denoiser, the cfg2 architecture at reduced depth / size
+    "swinir_m_gray32": dict(_SW, kw=dict(img_size=32, in_chans=1, embed_dim=180, depths=[2, 2], num_heads=[6, 6],
+                                         window_size=8, mlp_ratio=2, upscale=1, img_range=1.0, upsampler="",
+                                         resi_connection="1conv"), x=(2, 1, 32, 32), seed=3, loss="charbonnier"),
+    # colour, input not a multiple of the window and != img_size: reflect pad + dynamic mask (network_swinir.py:262)
+    "swinir_m_rgb_pad": dict(_SW, kw=dict(img_size=32, in_chans=3, embed_dim=180, depths=[2], num_heads=[6],
+                                          window_size=8, mlp_ratio=2, upscale=1, img_range=1.0, upsampler="",
+                                          resi_connection="1conv"), x=(1, 3, 27, 35), seed=4, loss="l1"),
+    # classical SR x4 head (cfg3 architecture, reduced): pixelshuffle
+    "swinir_sr_ps4": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=180, depths=[2], num_heads=[6],
+                                       window_size=8, mlp_ratio=2, upscale=4, img_range=1.0,
+                                       upsampler="pixelshuffle", resi_connection="1conv"), x=(2, 3, 16, 16), seed=5,
+                          loss="l1"),
+    # real-world SR x4 head (cfg5 architecture, reduced): nearest+conv
+    "swinir_sr_nearest4": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=180, depths=[2], num_heads=[6],
+                                            window_size=8, mlp_ratio=2, upscale=4, img_range=1.0,
+                                            upsampler="nearest+conv", resi_connection="1conv"), x=(1, 3, 16, 24),
+                               seed=6, loss="l1"),
+    # lightweight SR: pixelshuffledirect, C=60 (head_dim 10)
+    "swinir_s_psd2": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=60, depths=[2], num_heads=[6],
+                                       window_size=8, mlp_ratio=2, upscale=2, img_range=1.0,
+                                       upsampler="pixelshuffledirect", resi_connection="1conv"), x=(1, 3, 16, 16),
+                          seed=7, loss="l1"),
+    # '3conv' residual connection (SwinIR-L style), C=48
+    "swinir_3conv": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=48, depths=[2], num_heads=[6],
+                                      window_size=8, mlp_ratio=2, upscale=1, img_range=1.0, upsampler="",
+                                      resi_connection="3conv"), x=(1, 3, 16, 16), seed=8, loss="l1"),
+    # JPEG-artifact model geometry: window 7, img_range 255
+    "swinir_jpeg_ws7": dict(_SW, kw=dict(img_size=28, in_chans=1, embed_dim=180, depths=[2], num_heads=[6],
+                                         window_size=7, mlp_ratio=2, upscale=1, img_range=255.0, upsampler="",
+                                         resi_connection="1conv"), x=(1, 1, 28, 28), seed=9, loss="charbonnier"),
+    # DnCNN-17 'R' (the inference checkpoint's architecture, cfg1)
+    "dncnn_r17": dict(net="dncnn", kw=dict(in_nc=1, out_nc=1, nc=64, nb=17, act_mode="R"), x=(1, 1, 40, 40), seed=10,
+                      loss="l1"),
+    # DnCNN 'BR' in training mode: batch-statistics BN (momentum 0.9, eps 1e-4) + running-stat update
+    "dncnn_br_train": dict(net="dncnn", kw=dict(in_nc=1, out_nc=1, nc=64, nb=5, act_mode="BR"), x=(4, 1, 24, 24),
+                           seed=11, loss="l1", train_mode=True),
+    "dncnn_br_eval": dict(net="dncnn", kw=dict(in_nc=3, out_nc=3, nc=64, nb=5, act_mode="BR"), x=(2, 3, 24, 24),
+                          seed=12, loss="l1"),
+    # DRUNet (cfg4 architecture, nb reduced to 2)
+    "unetres_nb2": dict(net="unetres", kw=dict(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=2, act_mode="R",
+                                               downsample_mode="strideconv", upsample_mode="convtranspose",
+                                               bias=False), x=(1, 4, 32, 32), seed=13, loss="l1"),
+}
+
+
+def loss_fn(case):
+    if case["loss"] == "charbonnier":
+        return so.charbonnier
+    return lambda a, b: torch.mean(torch.abs(a - b))
+
+
+def swinir_cfg(kw):
+    return so.SwinIRConfig(img_size=kw["img_size"], in_chans=kw["in_chans"], embed_dim=kw["embed_dim"],
+                           depths=tuple(kw["depths"]), num_heads=tuple(kw["num_heads"]),
+                           window_size=kw["window_size"], mlp_ratio=kw["mlp_ratio"], upscale=kw["upscale"],
+                           img_range=kw["img_range"], upsampler=kw["upsampler"],
+                           resi_connection=kw["resi_connection"])
+
+
+def state_and_io(case):
+    """(state_dict, x, target) of a case -- identical on every machine."""
+    kw, net = case["kw"], case["net"]
+    if net == "swinir":
+        cfg = swinir_cfg(kw)
+        sd = so.deterministic_state(so.state_spec(cfg), case["seed"], cfg)
+        up = kw["upscale"]
+    elif net == "dncnn":
+        sd = so.deterministic_state(co.dncnn_state_spec(**kw), case["seed"])
+        up = 1
+    else:
+        sd = so.deterministic_state(co.unetres_state_spec(kw["in_nc"], kw["out_nc"], tuple(kw["nc"]), kw["nb"],
+                                                          kw["bias"]), case["seed"])
+        up = 1
+    g = torch.Generator().manual_seed(1000 + case["seed"])
+    B, c, H, W = case["x"]
+    x = torch.rand(B, c, H, W, generator=g)
+    co_ = kw.get("out_nc", c)
+    tgt = torch.rand(B, co_, H * up, W * up, generator=g)
+    return sd, x, tgt
+
+
+def oracle_forward(case, sd, x, new_stats=None):
+    kw, net = case["kw"], case["net"]
+    if net == "swinir":
+        return so.swinir_forward(sd, x, swinir_cfg(kw))
+    if net == "dncnn":
+        return co.dncnn_forward(sd, x, nb=kw["nb"], act_mode=kw["act_mode"], training=case.get("train_mode", False),
+                                new_stats=new_stats)
+    return co.unetres_forward(sd, x, nb=kw["nb"])
+
+
+def build_reference(case, ref_loader):
+    """The real reference module with the case's weights loaded (needs /root/reference)."""
+    kw, net = case["kw"], case["net"]
+    sd, x, tgt = state_and_io(case)
+    if net == "swinir":
+        model = ref_loader.load("network_swinir").SwinIR(drop_path_rate=0.0, **kw)
+    elif net == "dncnn":
+        model = ref_loader.load("network_dncnn").DnCNN(**kw)
+    else:
+        model = ref_loader.load("network_unet").UNetRes(**kw)
+    missing = model.load_state_dict(sd, strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    return model, sd, x, tgt
