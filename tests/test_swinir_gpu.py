@@ -141,3 +141,30 @@ def test_full_size_properties():
         y3 = model(x)
     assert torch.equal(y3, x)
     assert torch.isfinite(y2).all() and g1.abs().sum().item() > 0
+
+
+def test_golden_fixture_swinir_m_gray32():
+    """CUDA path vs the committed golden vector produced by the real reference module (tests/golden/)."""
+    import json
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_swinir import SwinIR
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "swinir_m_gray32.npz"))
+    case = gc.CASES["swinir_m_gray32"]
+    sd, x, tgt = gc.state_and_io(case)
+    model = SwinIR(drop_path_rate=0.0, **case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().train()
+    y = model(x.cuda())
+    loss = gc.loss_fn(case)(y, tgt.cuda())
+    loss.backward()
+    assert np.abs(y.detach().cpu().numpy() - z["y"]).max() < 2e-2
+    assert abs(loss.item() - float(z["loss"])) < 2e-3
+    grads = json.loads(str(z["grads"]))
+    bad = []
+    for k, p in model.named_parameters():
+        n = p.grad.double().norm().item()
+        if abs(n - grads[k][0]) > 3e-2 * grads[k][0] + 1e-6:
+            bad.append((k, n, grads[k][0]))
+    assert not bad, bad[:6]
