@@ -30,7 +30,7 @@ constexpr int TN_MAX_STAGES = 8;
 constexpr int TN_MISC_BYTES = 6144;            // 1 KiB barriers + tmem ptr, 4 KiB row-exchange buffer
 
 struct TnParams {
-  CUtensorMap tmA, tmB, tmOutB, tmOutB2, tmOutF;
+  CUtensorMap tmA, tmB, tmOutB, tmOutB2, tmOutF, tmResid, tmAux;
   const float* bias;
   const float* resid;
   const bf16* aux;
@@ -137,8 +137,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
   uint64_t* tfull_bar = empty_bar + TN_MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* bres_bar = tempty_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
+  uint64_t* ld_bar = bres_bar + 1;  // [8 epilogue warps][up to 6 ring buffers]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ld_bar + 48);
   float* xch = reinterpret_cast<float*>(misc + 1024);  // [2 slots][2 halves][2 values][128 rows] fp32 = 4 KiB
+  float* bias_s = reinterpret_cast<float*>(misc + 5120);  // this CTA's BN bias values (1 KiB)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -151,6 +153,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     if (p.has_outB) tma_prefetch_desc(&p.tmOutB);
     if (p.has_outB2) tma_prefetch_desc(&p.tmOutB2);
     if (p.has_outF) tma_prefetch_desc(&p.tmOutF);
+    if (p.resid) tma_prefetch_desc(&p.tmResid);
+    if (p.aux) tma_prefetch_desc(&p.tmAux);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -163,11 +167,15 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         mbar_init(&tempty_bar[i], 8);
       }
       mbar_init(bres_bar, 1);
+      for (int i = 0; i < 48; ++i) mbar_init(&ld_bar[i], 1);
       fence_barrier_init();
     }
     __syncwarp();
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
+  }
+  if (p.bias != nullptr && threadIdx.x >= 64 && threadIdx.x < 64 + BN) {
+    bias_s[threadIdx.x - 64] = __ldg(p.bias + (blockIdx.x % p.n_tiles) * BN + (threadIdx.x - 64));
   }
   tcgen05_fence_before();
   __syncthreads();
@@ -251,6 +259,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     __syncwarp();
   } else {
     // ================================ epilogue ================================
+    // Each epilogue warp owns two 6 KiB staging sets (4 KiB fp32 chunk + 2 KiB bf16 chunk of 32 rows x 32 columns).
+    // Global operands of the epilogue (fp32 residual rows, bf16 aux rows) are TMA-loaded into the set one chunk
+    // ("slot") ahead -- across tile boundaries too --, consumed from shared memory, overwritten in place with the
+    // results and TMA-stored from the same set.  `resid` / `aux` must not alias any output of this launch.
     const int ew = warp - 2;
     const int q = warp & 3;    // TMEM lane quarter this warp may access
     const int hf = ew >> 2;    // column half
@@ -258,9 +270,31 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 32;
     uint8_t* stg = stg_base + ew * TN_STG_PER_WARP;
-    int sbuf = 0;
+    uint64_t* ldbar = ld_bar + ew * 6;
+    uint32_t ldphase = 0;      // bit b: parity the next wait on ring buffer b expects
+    int ridx = 0;              // ring buffer of the current slot
     int xslot = 0;
     const float inv_n = 1.0f / (float)p.n_valid;
+    const int col_half = n_tile * BN + hf * HALF;
+    const bool use_r = p.resid != nullptr && (EPI == KAIR_EPI_LINEAR || EPI == KAIR_EPI_RESID_LN || EPI == KAIR_EPI_LNBWD);
+    const bool use_a = (EPI == KAIR_EPI_DGELU || EPI == KAIR_EPI_LNBWD);
+    const bool has_ld = use_r || use_a;
+    // The warp's 12 KiB of staging memory is a ring of ringD buffers of ringS bytes; slot k uses buffer k % ringD and
+    // its operands are TMA-prefetched ringDist slots ahead.
+    //   6 KiB x 2: fp32 chunk at +0 (residual in / outF out), bf16 chunk at +4096 (aux in / outB out)
+    //   4 KiB x 3: GELU, u at +0 and gelu(u) at +2048          2 KiB x 6: a single bf16 chunk (store-only or in place)
+    int ringD = 2, ringS = 6144, ringDist = has_ld ? 1 : 0;
+    if (EPI == KAIR_EPI_GELU) { ringD = 3; ringS = 4096; ringDist = 0; }
+    if (EPI == KAIR_EPI_DGELU) { ringD = 6; ringS = 2048; ringDist = NCH; }
+    if (EPI == KAIR_EPI_LINEAR && !use_r && !p.has_outF) { ringD = 6; ringS = 2048; ringDist = 0; }
+    const int boff = (ringS == 6144) ? 4096 : 0;  // offset of the bf16 chunk inside a ring buffer
+    auto ring_at = [&](int d) { int i = ridx + d; return i >= ringD ? i - ringD : i; };
+    auto wait_stores = [&](int n) {  // at most n of this thread's latest TMA-store groups may still be reading smem
+      if (n <= 0) tma_store_wait_read<0>();
+      else if (n == 1) tma_store_wait_read<1>();
+      else if (n == 2) tma_store_wait_read<2>();
+      else tma_store_wait_read<5>();
+    };
 
     // two-value exchange between the two threads that share a row
     auto exchange2 = [&](float a, float b, float& oa, float& ob) {
@@ -272,69 +306,137 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       ob = b + s[((hf ^ 1) * 2 + 1) * 128 + row];
       xslot ^= 1;
     };
-    // acquire a staging buffer set: fp32 chunk (or first bf16 chunk) at +0, bf16 chunk at +4096
-    auto stage_begin = [&]() -> uint8_t* {
-      if (lane == 0) tma_store_wait_read<1>();
-      __syncwarp();
-      return stg + sbuf * 6144;
+    auto load_acc = [&](uint32_t taddr, float (&v)[32]) {
+      uint32_t r[32];
+      tmem_ld32(taddr, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
     };
-    auto stage_end = [&]() {
-      if (lane == 0) tma_store_commit();
-      sbuf ^= 1;
+    auto add_bias = [&](float (&v)[32], int col) {
+      if (p.bias) {
+        const float4* bp = reinterpret_cast<const float4*>(bias_s + (col - n_tile * BN));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float4 b4 = bp[i];  // warp-uniform address: shared-memory broadcast
+          v[4 * i] += b4.x; v[4 * i + 1] += b4.y; v[4 * i + 2] += b4.z; v[4 * i + 3] += b4.w;
+        }
+      }
+    };
+    // lane 0: TMA-load the operands of one slot into staging set `set` (fp32 residual at +0, bf16 aux at +4096)
+    auto issue_load = [&](int bi, bool want_r, bool want_a, const TileCoord& tt, int col) {
+      uint8_t* b = stg + bi * ringS;
+      mbar_arrive_expect_tx(&ldbar[bi], (want_r ? 4096u : 0u) + (want_a ? 2048u : 0u));
+      if (kConv) {
+        const int r0 = q * 32;
+        if (want_r) tma_load_4d(b, &p.tmResid, &ldbar[bi], col, tt.w0 + r0 % p.TW, tt.h0 + r0 / p.TW, tt.b);
+        if (want_a) tma_load_4d(b + boff, &p.tmAux, &ldbar[bi], col, tt.w0 + r0 % p.TW, tt.h0 + r0 / p.TW, tt.b);
+      } else {
+        if (want_r) tma_load_2d(b, &p.tmResid, &ldbar[bi], col, tt.w0 + q * 32);
+        if (want_a) tma_load_2d(b + boff, &p.tmAux, &ldbar[bi], col, tt.w0 + q * 32);
+      }
+    };
+    // Begin a slot: make sure the buffer that is about to be (re)filled is free (the TMA store that last used it has
+    // been read out), prefetch the slot ringDist ahead into it, then wait for this slot's operands.
+    auto slot_begin = [&](bool have_next, bool nr, bool na, const TileCoord& nt, int ncol, bool wait_mine) -> uint8_t* {
+      if (lane == 0) {
+        if (have_next && (nr || na)) {
+          wait_stores(ringD - ringDist - 1);
+          issue_load(ring_at(ringDist), nr, na, nt, ncol);
+        } else {
+          wait_stores(ringD - 1);
+        }
+      }
+      __syncwarp();
+      if (wait_mine) {
+        mbar_wait(&ldbar[ridx], (ldphase >> ridx) & 1u);
+        ldphase ^= 1u << ridx;
+      }
+      return stg + ridx * ringS;
+    };
+    auto slot_end = [&](bool stored) {
+      if (stored && lane == 0) tma_store_commit();
+      ridx = ring_at(1);
+    };
+    // this thread's row of a landed fp32 / bf16 chunk (same swizzles as stage_f32 / stage_bf16)
+    auto add_row_f32 = [&](float (&v)[32], const uint8_t* buf) {
+      const uint32_t base = smem_u32(buf) + lane * 128;
+      const uint32_t sw = lane & 7;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 r4;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(r4.x), "=f"(r4.y), "=f"(r4.z), "=f"(r4.w)
+                     : "r"(base + ((j ^ sw) << 4)));
+        v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+      }
+    };
+    auto read_row_bf16 = [&](float (&x)[32], const uint8_t* buf) {
+      const uint32_t base = smem_u32(buf) + lane * 64;
+      const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t w0, w1, w2, w3;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3)
+                     : "r"(base + ((j ^ sw) << 4)));
+        const uint32_t w[4] = {w0, w1, w2, w3};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+          x[8 * j + 2 * e] = f2.x;
+          x[8 * j + 2 * e + 1] = f2.y;
+        }
+      }
     };
 
     int it = 0;
-    for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
+    int m_tile = m_first;
+    if (has_ld && lane == 0 && m_tile < p.m_tiles) {
+      const TileCoord t0 = tile_coord<kConv>(p, m_tile);
+      if (EPI == KAIR_EPI_DGELU) {
+        for (int c = 0; c < NCH; ++c) issue_load(c, false, true, t0, col_half + c * 32);  // the whole first tile
+      } else {
+        issue_load(0, use_r && EPI != KAIR_EPI_LNBWD, use_a, t0, col_half);              // slot 0 of the first tile
+      }
+    }
+    __syncwarp();
+
+    for (; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       const TileCoord t = tile_coord<kConv>(p, m_tile);
       const long long tok = row_token<kConv>(p, t, row);
-      mbar_wait(&tfull_bar[as], aphase);
-      tcgen05_fence_after();
-      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * HALF;
-      const int col_half = n_tile * BN + hf * HALF;
+      const bool more_tiles = (m_tile + m_stride) < p.m_tiles;
+      const TileCoord t_next = tile_coord<kConv>(p, more_tiles ? m_tile + m_stride : m_tile);
       float sa = 1.0f, sb = 1.0f;  // DropPath per-sample scales
       if (tok >= 0) {
         if (p.acc_scale) sa = __ldg(p.acc_scale + tok / p.tokens_per_sample);
         if (p.outB_scale) sb = __ldg(p.outB_scale + tok / p.tokens_per_sample);
       }
+      mbar_wait(&tfull_bar[as], aphase);
+      tcgen05_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * HALF;
 
       if (EPI == KAIR_EPI_LINEAR) {
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
+          const bool last = (c == NCH - 1);
+          uint8_t* buf = slot_begin(!last || more_tiles, use_r, false, last ? t_next : t, last ? col_half : col + 32,
+                                    use_r);
           float v[32];
-          {
-            uint32_t r[32];
-            tmem_ld32(tacc + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-          }
-          if (p.bias) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
-              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
-            }
-          }
+          load_acc(tacc + c * 32, v);
+          add_bias(v, col);
           if (p.acc_scale) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= sa;
           }
-          if (p.resid && tok >= 0) {
-            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              float4 r4 = __ldg(rp + i);
-              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
-            }
-          }
+          if (use_r) add_row_f32(v, buf);
           if (p.act == KAIR_ACT_LRELU) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
           }
-          uint8_t* buf = stage_begin();
           if (p.has_outF) stage_f32(buf, lane, v);
           if (p.has_outB) {
             if (p.outB_scale) {
@@ -346,36 +448,24 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
               for (int i = 0; i < 32; ++i)
                 if (col + i == p.ones_col) v[i] = 1.0f;
             }
-            stage_bf16(buf + 4096, lane, v);
+            stage_bf16(buf + boff, lane, v);
           }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
             if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
-            if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+            if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + boff, t, q, col);
           }
-          stage_end();
+          slot_end(true);
         }
       } else if (EPI == KAIR_EPI_GELU) {
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
+          uint8_t* buf = slot_begin(false, false, false, t, 0, false);
           float v[32];
-          {
-            uint32_t r[32];
-            tmem_ld32(tacc + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-          }
-          if (p.bias) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
-              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
-            }
-          }
-          uint8_t* buf = stage_begin();
+          load_acc(tacc + c * 32, v);
+          add_bias(v, col);
           if (p.has_outB2) stage_bf16(buf, lane, v);  // pre-activation u
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
@@ -384,48 +474,32 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             for (int i = 0; i < 32; ++i)
               if (col + i == p.ones_col) v[i] = 1.0f;
           }
-          stage_bf16(buf + 4096, lane, v);
+          stage_bf16(buf + 2048, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
             if (p.has_outB2) tma_store_chunk<kConv>(p, &p.tmOutB2, buf, t, q, col);
-            tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
+            tma_store_chunk<kConv>(p, &p.tmOutB, buf + 2048, t, q, col);
           }
-          stage_end();
+          slot_end(true);
         }
       } else if (EPI == KAIR_EPI_RESID_LN) {
-        // pass A: v = acc + bias + resid -> outF, keep v in TMEM, accumulate row sum
+        // pass A: v = acc + bias + resid -> outF (in place over the landed residual chunk), keep v in TMEM
         float s1 = 0.f;
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
+          const bool last = (c == NCH - 1);
+          uint8_t* buf = slot_begin(!last || more_tiles, use_r, false, last ? t_next : t, last ? col_half : col + 32,
+                                    use_r);
           float v[32];
-          {
-            uint32_t r[32];
-            tmem_ld32(tacc + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-          }
-          if (p.bias) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + i));
-              v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
-            }
-          }
+          load_acc(tacc + c * 32, v);
+          add_bias(v, col);
           if (p.acc_scale) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= sa;
           }
-          if (p.resid && tok >= 0) {
-            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              float4 r4 = __ldg(rp + i);
-              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
-            }
-          }
+          if (use_r) add_row_f32(v, buf);
 #pragma unroll
           for (int i = 0; i < 32; ++i) s1 += v[i];
           {
@@ -435,13 +509,12 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             tmem_st32(tacc + c * 32, r);
           }
           if (p.has_outF) {
-            uint8_t* buf = stage_begin();
             stage_f32(buf, lane, v);
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
-            stage_end();
           }
+          slot_end(p.has_outF);
         }
         tmem_st_wait();
         float tot, dummy;
@@ -465,7 +538,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         tot2 -= (float)(p.n_tiles * BN - p.n_valid) * mean * mean;
         const float rstd = rsqrtf(fmaxf(tot2, 0.f) * inv_n + p.ln_eps);
         if (hf == 0 && tok >= 0 && p.rowstat) p.rowstat[tok] = rstd;
-        // pass C: xhat -> bf16
+        // pass C: xhat -> bf16, staged in the bf16 halves of the two sets (the fp32 halves may already be receiving
+        // the next tile's residual chunk, so the slot counter is left alone)
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
@@ -481,74 +555,53 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
               v[i] = cg < p.n_valid ? x : (cg == p.ones_col ? 1.0f : 0.0f);
             }
           }
-          uint8_t* buf = stage_begin();
-          stage_bf16(buf + 4096, lane, v);
+          uint8_t* bb = stg + (c & 1) * 6144 + 4096;
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          stage_bf16(bb, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
-          stage_end();
+          if (lane == 0) {
+            tma_store_chunk<kConv>(p, &p.tmOutB, bb, t, q, col);
+            tma_store_commit();
+          }
         }
       } else if (EPI == KAIR_EPI_DGELU) {
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
-          float v[32];
-          uint4 u4[4];
-          if (tok >= 0) {
-            const uint4* up = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
+          uint8_t* buf = slot_begin(more_tiles, false, true, t_next, col, true);  // same chunk of the next tile
+          float v[32], u[32];
+          load_acc(tacc + c * 32, v);
+          read_row_bf16(u, buf);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) u4[i] = __ldg(up + i);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) u4[i] = make_uint4(0, 0, 0, 0);
-          }
-          {
-            uint32_t r[32];
-            tmem_ld32(tacc + c * 32, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-          }
-          const __nv_bfloat162* ub = reinterpret_cast<const __nv_bfloat162*>(u4);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float2 u2 = __bfloat1622float2(ub[i]);
-            v[2 * i] *= gelu_erf_grad(u2.x);
-            v[2 * i + 1] *= gelu_erf_grad(u2.y);
-          }
-          uint8_t* buf = stage_begin();
-          stage_bf16(buf + 4096, lane, v);
+          for (int i = 0; i < 32; ++i) v[i] *= gelu_erf_grad(u[i]);
+          stage_bf16(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
-          stage_end();
+          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf, t, q, col);
+          slot_end(true);
         }
       } else if (EPI == KAIR_EPI_LNBWD) {
-        // pass A: s1 = sum(acc), s2 = sum(acc * xhat)
+        // slots of a tile: A0..A(NCH-1) need xhat (aux); B0..B(NCH-1) need xhat and the residual gradient
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
-          uint4 x4[4];
-          if (tok >= 0) {
-            const uint4* xp = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x4[i] = __ldg(xp + i);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x4[i] = make_uint4(0, 0, 0, 0);
-          }
+          const bool last = (c == NCH - 1);
+          uint8_t* buf = slot_begin(true, last ? use_r : false, true, t, last ? col_half : col + 32, true);
+          float x[32];
+          read_row_bf16(x, buf + 4096);
           uint32_t r[32];
           tmem_ld32(tacc + c * 32, r);
           tmem_ld_wait();
-          const __nv_bfloat162* xb = reinterpret_cast<const __nv_bfloat162*>(x4);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float2 x2 = __bfloat1622float2(xb[i]);
-            float a0 = __uint_as_float(r[2 * i]), a1 = __uint_as_float(r[2 * i + 1]);
-            s1 += a0 + a1;
-            s2 += a0 * x2.x + a1 * x2.y;
+          for (int i = 0; i < 32; ++i) {
+            float a0 = __uint_as_float(r[i]);
+            s1 += a0;
+            s2 += a0 * x[i];
           }
+          slot_end(false);
         }
         float t1, t2;
         exchange2(s1, s2, t1, t2);
@@ -557,40 +610,23 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
+          const bool last = (c == NCH - 1);
+          uint8_t* buf = slot_begin(!last || more_tiles, last ? false : use_r, true, last ? t_next : t,
+                                    last ? col_half : col + 32, true);
           float v[32];
-          uint4 x4[4];
-          if (tok >= 0) {
-            const uint4* xp = reinterpret_cast<const uint4*>(p.aux + tok * p.aux_pitch + col);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x4[i] = __ldg(xp + i);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x4[i] = make_uint4(0, 0, 0, 0);
-          }
           {
+            float x[32];
+            read_row_bf16(x, buf + 4096);
             uint32_t r[32];
             tmem_ld32(tacc + c * 32, r);
             tmem_ld_wait();
-            const __nv_bfloat162* xb = reinterpret_cast<const __nv_bfloat162*>(x4);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              float2 x2 = __bfloat1622float2(xb[i]);
-              v[2 * i] = rstd * (__uint_as_float(r[2 * i]) - m1 - x2.x * m2);
-              v[2 * i + 1] = rstd * (__uint_as_float(r[2 * i + 1]) - m1 - x2.y * m2);
-            }
+            for (int i = 0; i < 32; ++i) v[i] = rstd * (__uint_as_float(r[i]) - m1 - x[i] * m2);
           }
-          if (p.resid && tok >= 0) {
-            const float4* rp = reinterpret_cast<const float4*>(p.resid + tok * p.resid_pitch + col);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              float4 r4 = __ldg(rp + i);
-              v[4 * i] += r4.x; v[4 * i + 1] += r4.y; v[4 * i + 2] += r4.z; v[4 * i + 3] += r4.w;
-            }
-          }
+          if (use_r) add_row_f32(v, buf);
 #pragma unroll
           for (int i = 0; i < 32; ++i)
             if (col + i >= p.n_valid) v[i] = 0.f;
-          uint8_t* buf = stage_begin();
           if (p.has_outF) stage_f32(buf, lane, v);
           if (p.has_outB) {
             if (p.outB_scale) {
@@ -605,7 +641,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
             if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
           }
-          stage_end();
+          slot_end(true);
         }
       }
       // release the accumulator stage back to the MMA warp
@@ -774,6 +810,8 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   if (a.outB && make_out(&p.tmOutB, a.outB, a.outB_pitch, false)) return -2;
   if (a.outB2 && make_out(&p.tmOutB2, a.outB2, a.outB2_pitch, false)) return -2;
   if (a.outF && make_out(&p.tmOutF, a.outF, a.outF_pitch, true)) return -2;
+  if (a.resid && make_out(&p.tmResid, a.resid, a.resid_pitch, true)) return -2;
+  if (a.aux && make_out(&p.tmAux, a.aux, a.aux_pitch, false)) return -2;
 
   // shared memory plan
   const int k_total = p.kc * taps;
