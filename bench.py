@@ -294,6 +294,8 @@ def run_b200(args):
         import ctypes
         sth = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
         plan.gflat.zero_(); plan.dwflat.zero_()
+        for t_ in plan._thin:
+            t_.zero_()
         per = profiling.time_launches(launches, sth, reps=3)
         groups = profiling.summarize(launches, per, REAL_DIMS)
         tot = sum(d["ms"] for d in groups.values())

@@ -197,6 +197,7 @@ typedef struct kair_unpack_conv_args {
   void* const* dW;           /* [L] -> fp32 (O, I, kh, kw) */
   void* const* db;           /* [L] -> fp32 (O) or NULL; taken from column ones_col of the centre tap */
   int32_t L, O, I, O_pad, I_pad, taps, ones_col, center_tap;
+  int32_t dwp_pitch;         /* row pitch of dWp in elements; 0 = taps*I_pad */
 } kair_unpack_conv_args;
 int kair_unpack_conv_grad(const kair_unpack_conv_args* args, void* stream);
 
@@ -281,6 +282,37 @@ typedef struct kair_conv_out_args {
 int kair_conv_out_fwd(const kair_conv_out_args* args, void* stream);
 int kair_conv_out_dgrad(const kair_conv_out_args* args, void* stream);
 int kair_conv_out_wgrad(const kair_conv_out_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Thin (<= 4 channel) convolutions expressed as GEMMs.  kair_im2col3x3 expands an NCHW fp32 image into a bf16 token
+ * matrix  out[t][tap*cpad + ch] = (img[ch][p(t) + dir*off(tap)] - mean[ch]) * scale  (0 outside the image, 1.0 in
+ * column ones_col, 0 in the other padding columns), off(tap) = (tap/3 - 1, tap%3 - 1).
+ *   dir = +1: input patches of conv_first  -> weight gradient = kair_gemm_nt(dY, patches)   (autograd of
+ *             network_swinir.py:669, :811; network_dncnn.py:63; network_unet.py:25)
+ *   dir = -1: shifted output gradients of conv_last -> input gradient = kair_gemm_tn(shifted, packed W) and weight
+ *             gradient = kair_gemm_nt(features, shifted)   (autograd of network_swinir.py:762, :835)
+ * kair_conv_out_pack converts between conv_last's (co, C, 3, 3) fp32 layout and those GEMM operands:
+ *   mode 0: Wt[k][tap*cpad + c] = W[c][k][tap]  (bf16 [C_pad][pitch])
+ *   mode 1: dW[c][k][tap] = D[k][tap*cpad + c], db[c] = D[ones_row][4*cpad + c]  (D fp32 [C_pad][pitch])
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_im2col_args {
+  const float* img;      /* (B, c, H, W) */
+  const float* mean;     /* (c) or NULL */
+  void* out;             /* bf16 [B*H*W][pitch] */
+  float scale;
+  int32_t batch, c, H, Wd, cpad, pitch, dir, ones_col;
+} kair_im2col_args;
+int kair_im2col3x3(const kair_im2col_args* args, void* stream);
+
+typedef struct kair_conv_out_pack_args {
+  const float* W;        /* mode 0: (co, C, 3, 3) */
+  void* Wt;              /* mode 0: bf16 [C_pad][pitch] */
+  const float* D;        /* mode 1: fp32 [C_pad][pitch] */
+  float* dW;             /* mode 1: (co, C, 3, 3) */
+  float* db;             /* mode 1: (co) or NULL */
+  int32_t mode, co, C, C_pad, cpad, pitch, ones_row;
+} kair_conv_out_pack_args;
+int kair_conv_out_pack(const kair_conv_out_pack_args* args, void* stream);
 
 /* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);

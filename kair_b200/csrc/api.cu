@@ -19,6 +19,8 @@ int conv_in_wgrad_launch(const kair_conv_in_args& a, cudaStream_t st);
 int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st);
 int conv_out_dgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
 int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
+int im2col3x3_launch(const kair_im2col_args& a, cudaStream_t st);
+int conv_out_pack_launch(const kair_conv_out_pack_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 }
 
@@ -79,6 +81,8 @@ KB_WRAP(kair_conv_in_wgrad, kair_conv_in_args, conv_in_wgrad_launch)
 KB_WRAP(kair_conv_out_fwd, kair_conv_out_args, conv_out_fwd_launch)
 KB_WRAP(kair_conv_out_dgrad, kair_conv_out_args, conv_out_dgrad_launch)
 KB_WRAP(kair_conv_out_wgrad, kair_conv_out_args, conv_out_wgrad_launch)
+KB_WRAP(kair_im2col3x3, kair_im2col_args, im2col3x3_launch)
+KB_WRAP(kair_conv_out_pack, kair_conv_out_pack_args, conv_out_pack_launch)
 #undef KB_WRAP
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {

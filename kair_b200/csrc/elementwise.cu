@@ -83,23 +83,36 @@ __global__ void unpack_linear_dw_kernel(const kair_unpack_linear_args a) {
 }
 
 __global__ void unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x, l = blockIdx.y;
-  if (c >= a.K_pad) return;
-  const int k = a.col_map[c];
-  if (k < 0) return;
+  // block = 32 columns x 8 row groups; dgamma[k] = sum_r rs*W[src][k] * dWp[r][c], dbeta[k] = sum_r rs*W[src][k] * dbp[r]
+  __shared__ float sg[8][33], sb[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5, l = blockIdx.y;
+  const int c = blockIdx.x * 32 + cx;
+  const int k = c < a.K_pad ? a.col_map[c] : -1;
   const float* W = reinterpret_cast<const float*>(a.W[l]);
   const float* dWp = a.dWp + (size_t)l * a.N_pad * a.K_pad;
   float dg = 0.f, db = 0.f;
-  for (int r = 0; r < a.N_pad; ++r) {
-    const int src = a.row_map[r];
-    if (src < 0) continue;
-    const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
-    const float w = W[(size_t)src * a.in_f + k] * rs;
-    dg += w * dWp[(size_t)r * a.K_pad + c];
-    db += w * dWp[(size_t)r * a.K_pad + a.ones_col];
+  if (k >= 0) {
+    for (int r = ry; r < a.N_pad; r += 8) {
+      const int src = a.row_map[r];
+      if (src < 0) continue;
+      const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
+      const float w = W[(size_t)src * a.in_f + k] * rs;
+      dg += w * dWp[(size_t)r * a.K_pad + c];
+      db += w * dWp[(size_t)r * a.K_pad + a.ones_col];
+    }
   }
-  reinterpret_cast<float*>(a.dgamma[l])[k] = dg;
-  reinterpret_cast<float*>(a.dbeta[l])[k] = db;
+  sg[ry][cx] = dg;
+  sb[ry][cx] = db;
+  __syncthreads();
+  if (ry == 0 && k >= 0) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+      dg += sg[i][cx];
+      db += sb[i][cx];
+    }
+    reinterpret_cast<float*>(a.dgamma[l])[k] = dg;
+    reinterpret_cast<float*>(a.dbeta[l])[k] = db;
+  }
 }
 
 int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st) {
@@ -108,7 +121,7 @@ int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st) {
   KB_CUDA(cudaGetLastError());
   if (a.dgamma && a.dbeta) {
     KB_CHECK(a.W && a.ones_col >= 0, "kair_unpack_linear_grad: LayerNorm gradients need W and ones_col");
-    unpack_linear_dln_kernel<<<dim3((a.K_pad + 63) / 64, a.L), 64, 0, st>>>(a);
+    unpack_linear_dln_kernel<<<dim3((a.K_pad + 31) / 32, a.L), 256, 0, st>>>(a);
     KB_CUDA(cudaGetLastError());
   }
   return 0;
@@ -152,19 +165,20 @@ int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st) {
 __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
   const int l = blockIdx.y;
   const int taps = a.taps;
-  const float* dWp = a.dWp + (size_t)l * a.O_pad * taps * a.I_pad;
+  const int rp = a.dwp_pitch > 0 ? a.dwp_pitch : taps * a.I_pad;  // row pitch of the packed gradient
+  const float* dWp = a.dWp + (size_t)l * a.O_pad * rp;
   float* dW = reinterpret_cast<float*>(a.dW[l]);
   const size_t n = (size_t)a.O * a.I * taps;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
     const int tap = (int)(e % taps);
     const int i = (int)((e / taps) % a.I);
     const int o = (int)(e / ((size_t)taps * a.I));
-    dW[e] = dWp[((size_t)o * taps + tap) * a.I_pad + i];
+    dW[e] = dWp[(size_t)o * rp + tap * a.I_pad + i];
   }
   if (a.db && a.ones_col >= 0 && blockIdx.x == 0) {
     float* db = reinterpret_cast<float*>(a.db[l]);
     for (int o = threadIdx.x; o < a.O; o += blockDim.x)
-      db[o] = dWp[((size_t)o * taps + a.center_tap) * a.I_pad + a.ones_col];
+      db[o] = dWp[(size_t)o * rp + a.center_tap * a.I_pad + a.ones_col];
   }
 }
 
@@ -233,6 +247,7 @@ int layernorm_fwd_launch(const kair_layernorm_args& a, cudaStream_t st) {
 // dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  dgamma += dy * xhat;  dbeta += dy
 // dy is given as fp32 and/or bf16 (summed when both are present); dx_out = dx (+ dx_add).
 __global__ void layernorm_bwd_kernel(const kair_layernorm_bwd_args a) {
+  // one warp per row; lane owns column pairs c = 2*lane + 64*i (8-byte coalesced accesses), pitch <= 256, pitch % 64 == 0
   __shared__ float sg[256], sb[256];
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
     sg[i] = 0.f;
@@ -241,48 +256,83 @@ __global__ void layernorm_bwd_kernel(const kair_layernorm_bwd_args a) {
   __syncthreads();
   const int warps = blockDim.x >> 5;
   const int lane = threadIdx.x & 31;
-  float pg[8], pb[8];
+  const int nv = a.pitch >> 6;  // float2 per lane
+  const float inv_c = 1.0f / (float)a.C;
+  float2 pg[4], pb[4], gam[4];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) pg[i] = pb[i] = 0.f;
+  for (int i = 0; i < 4; ++i) {
+    pg[i] = pb[i] = make_float2(0.f, 0.f);
+    const int c = 2 * lane + 64 * i;
+    gam[i].x = (i < nv && c < a.C) ? a.gamma[c] : 0.f;
+    gam[i].y = (i < nv && c + 1 < a.C) ? a.gamma[c + 1] : 0.f;
+  }
+  const bf16* dyb = reinterpret_cast<const bf16*>(a.dy_bf16);
+  bf16* dxb = reinterpret_cast<bf16*>(a.dx_bf16);
   for (long long row = (long long)blockIdx.x * warps + (threadIdx.x >> 5); row < a.T;
        row += (long long)gridDim.x * warps) {
-    const float mean = a.mean[row], rstd = a.rstd[row];
-    float xh[8], g[8];
-    float s1 = 0.f, s2 = 0.f;
+    const size_t base = (size_t)row * a.pitch;
+    float2 dy[4], xv[4], ad[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = lane + 32 * i;
-      xh[i] = 0.f;
-      g[i] = 0.f;
-      if (c < a.C) {
-        float dy = 0.f;
-        if (a.dy_f32) dy += a.dy_f32[row * a.pitch + c];
-        if (a.dy_bf16) dy += __bfloat162float(reinterpret_cast<const bf16*>(a.dy_bf16)[row * a.pitch + c]);
-        xh[i] = (a.x[row * a.pitch + c] - mean) * rstd;
-        pg[i] += dy * xh[i];
-        pb[i] += dy;
-        g[i] = dy * a.gamma[c];
-        s1 += g[i];
-        s2 += g[i] * xh[i];
+    for (int i = 0; i < 4; ++i) {
+      if (i < nv) {
+        const int c = 2 * lane + 64 * i;
+        xv[i] = *reinterpret_cast<const float2*>(a.x + base + c);
+        dy[i] = a.dy_f32 ? *reinterpret_cast<const float2*>(a.dy_f32 + base + c) : make_float2(0.f, 0.f);
+        if (dyb) {
+          float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dyb + base + c));
+          dy[i].x += t.x;
+          dy[i].y += t.y;
+        }
+        ad[i] = a.dx_add ? *reinterpret_cast<const float2*>(a.dx_add + base + c) : make_float2(0.f, 0.f);
       }
     }
-    const float m1 = warp_sum(s1) / a.C, m2 = warp_sum(s2) / a.C;
+    const float mean = a.mean[row], rstd = a.rstd[row];
+    float s1 = 0.f, s2 = 0.f;
+    float2 xh[4], g[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = lane + 32 * i;
-      if (c >= a.pitch) continue;
-      float dx = (c < a.C) ? rstd * (g[i] - m1 - xh[i] * m2) : 0.f;
-      if (a.dx_add && c < a.C) dx += a.dx_add[row * a.pitch + c];
-      if (a.dx_f32) a.dx_f32[row * a.pitch + c] = dx;
-      if (a.dx_bf16) reinterpret_cast<bf16*>(a.dx_bf16)[row * a.pitch + c] = __float2bfloat16(dx);
+    for (int i = 0; i < 4; ++i) {
+      xh[i] = g[i] = make_float2(0.f, 0.f);
+      if (i < nv) {
+        const int c = 2 * lane + 64 * i;
+        if (c < a.C) {
+          xh[i].x = (xv[i].x - mean) * rstd;
+          pg[i].x += dy[i].x * xh[i].x;
+          pb[i].x += dy[i].x;
+          g[i].x = dy[i].x * gam[i].x;
+        }
+        if (c + 1 < a.C) {
+          xh[i].y = (xv[i].y - mean) * rstd;
+          pg[i].y += dy[i].y * xh[i].y;
+          pb[i].y += dy[i].y;
+          g[i].y = dy[i].y * gam[i].y;
+        }
+        s1 += g[i].x + g[i].y;
+        s2 += g[i].x * xh[i].x + g[i].y * xh[i].y;
+      }
+    }
+    const float m1 = warp_sum(s1) * inv_c, m2 = warp_sum(s2) * inv_c;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (i < nv) {
+        const int c = 2 * lane + 64 * i;
+        float2 dx;
+        dx.x = (c < a.C) ? rstd * (g[i].x - m1 - xh[i].x * m2) + ad[i].x : 0.f;
+        dx.y = (c + 1 < a.C) ? rstd * (g[i].y - m1 - xh[i].y * m2) + ad[i].y : 0.f;
+        if (a.dx_f32) *reinterpret_cast<float2*>(a.dx_f32 + base + c) = dx;
+        if (dxb) *reinterpret_cast<__nv_bfloat162*>(dxb + base + c) = __floats2bfloat162_rn(dx.x, dx.y);
+      }
     }
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int c = lane + 32 * i;
-    if (c < a.C) {
-      atomicAdd(&sg[c], pg[i]);
-      atomicAdd(&sb[c], pb[i]);
+  for (int i = 0; i < 4; ++i) {
+    const int c = 2 * lane + 64 * i;
+    if (i < nv && c < a.C) {
+      atomicAdd(&sg[c], pg[i].x);
+      atomicAdd(&sb[c], pb[i].x);
+      if (c + 1 < a.C) {
+        atomicAdd(&sg[c + 1], pg[i].y);
+        atomicAdd(&sb[c + 1], pb[i].y);
+      }
     }
   }
   __syncthreads();
@@ -295,8 +345,8 @@ __global__ void layernorm_bwd_kernel(const kair_layernorm_bwd_args a) {
 int layernorm_bwd_launch(const kair_layernorm_bwd_args& a, cudaStream_t st) {
   KB_CHECK(a.x && a.mean && a.rstd && a.gamma && a.dgamma && a.dbeta && (a.dy_f32 || a.dy_bf16),
            "kair_layernorm_bwd: null pointer");
-  KB_CHECK(a.pitch <= 256 && a.pitch >= a.C, "kair_layernorm_bwd: bad pitch");
-  int blocks = sm_count() * 4;
+  KB_CHECK(a.pitch <= 256 && a.pitch >= a.C && a.pitch % 64 == 0, "kair_layernorm_bwd: pitch must be a multiple of 64, <= 256");
+  int blocks = sm_count() * 8;
   long long need = (a.T + 7) / 8;
   if (blocks > need) blocks = (int)need;
   layernorm_bwd_kernel<<<blocks, 256, 0, st>>>(a);
@@ -595,6 +645,78 @@ int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------------ residual helpers
+// ------------------------------------------------------------------------------------------------ thin convs as GEMMs
+// im2col for <= 4-channel images: one thread per (token, 8-column group); see include/kair_b200.h
+__global__ void im2col3x3_kernel(const kair_im2col_args a) {
+  const long long T = (long long)a.batch * a.H * a.Wd;
+  const int groups = a.pitch >> 3;
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < T * groups;
+       e += (long long)gridDim.x * blockDim.x) {
+    const long long t = e / groups;
+    const int g = (int)(e - t * groups);
+    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int col = g * 8 + i;
+      const int tap = col / a.cpad, ch = col - tap * a.cpad;
+      float x = 0.f;
+      if (tap < 9 && ch < a.c) {
+        const int hh = h + a.dir * (tap / 3 - 1), ww = w + a.dir * (tap % 3 - 1);
+        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+          x = a.img[(((size_t)b * a.c + ch) * a.H + hh) * a.Wd + ww];
+          x = (x - (a.mean ? a.mean[ch] : 0.f)) * a.scale;
+        }
+      }
+      if (col == a.ones_col) x = 1.0f;
+      v[i] = x;
+    }
+    uint4 pk = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                          pack_bf16x2(v[6], v[7]));
+    *reinterpret_cast<uint4*>(out + t * a.pitch + g * 8) = pk;
+  }
+}
+
+int im2col3x3_launch(const kair_im2col_args& a, cudaStream_t st) {
+  KB_CHECK(a.img && a.out, "kair_im2col3x3: null pointer");
+  KB_CHECK(a.c >= 1 && a.cpad >= a.c && 9 * a.cpad <= a.pitch && a.pitch % 8 == 0 && (a.dir == 1 || a.dir == -1),
+           "kair_im2col3x3: bad geometry c=%d cpad=%d pitch=%d dir=%d", a.c, a.cpad, a.pitch, a.dir);
+  im2col3x3_kernel<<<sm_count() * 8, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void conv_out_pack_kernel(const kair_conv_out_pack_args a) {
+  const int n = a.C_pad * a.pitch;
+  if (a.mode == 0) {
+    bf16* Wt = reinterpret_cast<bf16*>(a.Wt);
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+      const int k = e / a.pitch, col = e - k * a.pitch;
+      const int tap = col / a.cpad, c = col - tap * a.cpad;
+      float v = 0.f;
+      if (k < a.C && tap < 9 && c < a.co) v = a.W[((size_t)c * a.C + k) * 9 + tap];
+      Wt[e] = __float2bfloat16(v);
+    }
+  } else {
+    const int m = a.co * a.C * 9;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < m; e += gridDim.x * blockDim.x) {
+      const int tap = e % 9, k = (e / 9) % a.C, c = e / (9 * a.C);
+      a.dW[e] = a.D[(size_t)k * a.pitch + tap * a.cpad + c];
+    }
+    if (a.db && blockIdx.x == 0 && threadIdx.x < a.co)
+      a.db[threadIdx.x] = a.D[(size_t)a.ones_row * a.pitch + 4 * a.cpad + threadIdx.x];
+  }
+}
+
+int conv_out_pack_launch(const kair_conv_out_pack_args& a, cudaStream_t st) {
+  KB_CHECK(a.mode == 0 ? (a.W && a.Wt) : (a.D && a.dW), "kair_conv_out_pack: null pointer");
+  KB_CHECK(a.co >= 1 && a.cpad >= a.co && 9 * a.cpad <= a.pitch && a.C <= a.C_pad, "kair_conv_out_pack: bad geometry");
+  conv_out_pack_kernel<<<64, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // y += x (fp32, in place) and refresh the bf16 shadow copy of y
 __global__ void add_inplace_kernel(float* y, const float* x, bf16* yb, size_t n4) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {

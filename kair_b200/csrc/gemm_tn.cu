@@ -12,6 +12,7 @@
 // Replaces (reference file:line): nn.Linear qkv/proj/fc1/fc2 and their input-gradient GEMMs
 // (models/network_swinir.py:25-28, 121, 143), LayerNorm norm1/norm2 (:245, :277), the residual adds (:276-277) and
 // nn.Conv2d 3x3 (:465, :729; models/basicblock.py:65).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -24,8 +25,8 @@ constexpr int TN_THREADS = 320;       // 10 warps
 constexpr int TN_BM = 128;
 constexpr int TN_BK = 64;
 constexpr int TN_A_STAGE = TN_BM * TN_BK * 2;  // 16 KiB
-constexpr int TN_STG_PER_WARP = 12288;         // 2 x (4 KiB fp32 chunk + 2 KiB bf16 chunk)
-constexpr int TN_STG_BYTES = 8 * TN_STG_PER_WARP;
+// per-epilogue-warp staging ring (runtime, TnParams::stg_warp): 12 KiB = 2 x (4 KiB fp32 + 2 KiB bf16 chunk) for the
+// epilogues with in-place residual traffic, 6-8 KiB for the light ones so that more A stages fit
 constexpr int TN_MAX_STAGES = 8;
 constexpr int TN_MISC_BYTES = 6144;            // 1 KiB barriers + tmem ptr, 4 KiB row-exchange buffer
 
@@ -41,6 +42,8 @@ struct TnParams {
   int tokens_per_sample;
   int M, m_tiles, n_tiles, kc, taps, stages;
   int n_valid, ones_col, act;
+  int stg_warp, ringD, ringS, ringDist;
+  int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs
   float act_slope, ln_eps;
   int has_outB, has_outB2, has_outF;
   // conv geometry
@@ -129,7 +132,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
   constexpr int B_STAGE = BN * TN_BK * 2;
   const int k_total = p.kc * p.taps;
   uint8_t* stg_base = smem;
-  uint8_t* a_base = smem + TN_STG_BYTES;
+  uint8_t* a_base = smem + 8 * p.stg_warp;
   uint8_t* b_base = a_base + p.stages * TN_A_STAGE;
   uint8_t* misc = b_base + (kBRes ? k_total : p.stages) * B_STAGE;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
@@ -244,6 +247,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : stage) * B_STAGE);
 #pragma unroll
           for (int k = 0; k < TN_BK / 16; ++k) {
+            if (p.dbg & 2) continue;
             umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
                         (kb | k) != 0 ? 1u : 0u);
           }
@@ -269,7 +273,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     const int row = q * 32 + lane;
     constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 32;
-    uint8_t* stg = stg_base + ew * TN_STG_PER_WARP;
+    uint8_t* stg = stg_base + ew * p.stg_warp;
     uint64_t* ldbar = ld_bar + ew * 6;
     uint32_t ldphase = 0;      // bit b: parity the next wait on ring buffer b expects
     int ridx = 0;              // ring buffer of the current slot
@@ -283,17 +287,14 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     // its operands are TMA-prefetched ringDist slots ahead.
     //   6 KiB x 2: fp32 chunk at +0 (residual in / outF out), bf16 chunk at +4096 (aux in / outB out)
     //   4 KiB x 3: GELU, u at +0 and gelu(u) at +2048          2 KiB x 6: a single bf16 chunk (store-only or in place)
-    int ringD = 2, ringS = 6144, ringDist = has_ld ? 1 : 0;
-    if (EPI == KAIR_EPI_GELU) { ringD = 3; ringS = 4096; ringDist = 0; }
-    if (EPI == KAIR_EPI_DGELU) { ringD = 6; ringS = 2048; ringDist = NCH; }
-    if (EPI == KAIR_EPI_LINEAR && !use_r && !p.has_outF) { ringD = 6; ringS = 2048; ringDist = 0; }
+    const int ringD = p.ringD, ringS = p.ringS, ringDist = p.ringDist;
     const int boff = (ringS == 6144) ? 4096 : 0;  // offset of the bf16 chunk inside a ring buffer
     auto ring_at = [&](int d) { int i = ridx + d; return i >= ringD ? i - ringD : i; };
     auto wait_stores = [&](int n) {  // at most n of this thread's latest TMA-store groups may still be reading smem
       if (n <= 0) tma_store_wait_read<0>();
       else if (n == 1) tma_store_wait_read<1>();
       else if (n == 2) tma_store_wait_read<2>();
-      else tma_store_wait_read<5>();
+      else tma_store_wait_read<2>();  // n >= 2 (stricter than needed for deeper rings)
     };
 
     // two-value exchange between the two threads that share a row
@@ -395,7 +396,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     if (has_ld && lane == 0 && m_tile < p.m_tiles) {
       const TileCoord t0 = tile_coord<kConv>(p, m_tile);
       if (EPI == KAIR_EPI_DGELU) {
-        for (int c = 0; c < NCH; ++c) issue_load(c, false, true, t0, col_half + c * 32);  // the whole first tile
+        for (int c = 0; c < ringDist; ++c) issue_load(c, false, true, t0, col_half + c * 32);  // needs ringDist <= NCH
       } else {
         issue_load(0, use_r && EPI != KAIR_EPI_LNBWD, use_a, t0, col_half);              // slot 0 of the first tile
       }
@@ -426,7 +427,12 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           uint8_t* buf = slot_begin(!last || more_tiles, use_r, false, last ? t_next : t, last ? col_half : col + 32,
                                     use_r);
           float v[32];
-          load_acc(tacc + c * 32, v);
+          if (p.dbg & 1) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+          } else {
+            load_acc(tacc + c * 32, v);
+          }
           add_bias(v, col);
           if (p.acc_scale) {
 #pragma unroll
@@ -570,7 +576,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
-          uint8_t* buf = slot_begin(more_tiles, false, true, t_next, col, true);  // same chunk of the next tile
+          const int cn = c + ringDist;  // chunk prefetched now: ringDist slots ahead, possibly in the next tile
+          const bool wrap = cn >= NCH;
+          uint8_t* buf = slot_begin(!wrap || more_tiles, false, true, wrap ? t_next : t,
+                                    col_half + (wrap ? cn - NCH : cn) * 32, true);
           float v[32], u[32];
           load_acc(tacc + c * 32, v);
           read_row_bf16(u, buf);
@@ -754,6 +763,10 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   p.has_outB = a.outB != nullptr;
   p.has_outB2 = a.outB2 != nullptr;
   p.has_outF = a.outF != nullptr;
+  {
+    const char* e = getenv("KB_TN_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
 
   if (a.conv) {
     KB_CHECK(a.batch > 0 && a.H > 0 && a.W > 0 && (long long)a.batch * a.H * a.W == a.M,
@@ -816,7 +829,15 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   // shared memory plan
   const int k_total = p.kc * taps;
   const int b_stage = a.bn * 64 * 2;
-  const int budget = 232448 - 1024 - TN_STG_BYTES - TN_MISC_BYTES;
+  // staging ring per epilogue warp (see the kernel's epilogue comment)
+  const bool loads_r = a.resid && (a.mode == KAIR_EPI_LINEAR || a.mode == KAIR_EPI_RESID_LN || a.mode == KAIR_EPI_LNBWD);
+  p.stg_warp = 12288; p.ringD = 2; p.ringS = 6144;
+  p.ringDist = (loads_r || a.mode == KAIR_EPI_DGELU || a.mode == KAIR_EPI_LNBWD) ? 1 : 0;
+  if (a.mode == KAIR_EPI_GELU) { p.stg_warp = 8192; p.ringD = 2; p.ringS = 4096; p.ringDist = 0; }
+  if (a.mode == KAIR_EPI_DGELU) { p.stg_warp = 8192; p.ringD = 4; p.ringS = 2048; p.ringDist = 2; }
+  if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
+  const int stg_bytes = 8 * p.stg_warp;
+  const int budget = 232448 - 1024 - stg_bytes - TN_MISC_BYTES;
   bool bres = false;
   int stages = 0;
   {
@@ -832,7 +853,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   if (stages > TN_MAX_STAGES) stages = TN_MAX_STAGES;
   KB_CHECK(stages >= 2, "kair_gemm_tn: not enough shared memory for bn=%d", a.bn);
   p.stages = stages;
-  size_t smem = 1024 + TN_STG_BYTES + (size_t)stages * TN_A_STAGE +
+  size_t smem = 1024 + stg_bytes + (size_t)stages * TN_A_STAGE +
                 (size_t)(bres ? k_total : stages) * b_stage + TN_MISC_BYTES;
 
   int nsm = sm_count();

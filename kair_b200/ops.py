@@ -222,12 +222,13 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
     return Launch("kair_pack_conv", a, keep)
 
 
-def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4):
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0):
     keep = []
     a = _S["kair_unpack_conv_args"]()
     a.dWp = _ptr(dWp); a.dW = _plist(dW, dWp, keep); a.db = _plist(db, dWp, keep)
     a.L, a.O_pad = dWp.shape[0], dWp.shape[1]
     a.O, a.I, a.I_pad, a.taps, a.ones_col, a.center_tap = O, I, I_pad, taps, ones_col, center_tap
+    a.dwp_pitch = dwp_pitch
     return Launch("kair_unpack_conv_grad", a, keep)
 
 
@@ -312,6 +313,29 @@ def build_conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
     a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
     a.dout = _ptr(dout); a.feat = _ptr(feat); a.dW = _ptr(dW); a.db = _ptr(db)
     return Launch("kair_conv_out_wgrad", a)
+
+
+def build_im2col3x3(img, out, *, cpad, direction, mean=None, scale=1.0, ones_col=-1):
+    """out[t, tap*cpad + ch] = (img[ch, p(t) + direction*off(tap)] - mean[ch]) * scale as bf16 (see kair_b200.h)."""
+    _req(img, torch.float32, "img"); _req(out, torch.bfloat16, "out"); _req(mean, torch.float32, "mean")
+    if not img.is_contiguous():
+        raise RuntimeError("kair_b200: im2col3x3 needs a contiguous NCHW image")
+    a = _S["kair_im2col_args"]()
+    a.img = _ptr(img); a.mean = _ptr(mean); a.out = _ptr(out); a.scale = scale
+    a.batch, a.c, a.H, a.Wd = img.shape
+    a.cpad, a.pitch, a.dir, a.ones_col = cpad, out.stride(0), direction, ones_col
+    return Launch("kair_im2col3x3", a)
+
+
+def build_conv_out_pack(*, mode, co, C, cpad, W=None, Wt=None, D=None, dW=None, db=None, ones_row=-1):
+    """mode 0: Wt[k, tap*cpad + c] = W[c, k, tap] (bf16); mode 1: dW[c, k, tap] = D[k, tap*cpad + c], db from ones_row."""
+    _req(W, torch.float32, "W"); _req(Wt, torch.bfloat16, "Wt"); _req(D, torch.float32, "D")
+    _req(dW, torch.float32, "dW"); _req(db, torch.float32, "db")
+    a = _S["kair_conv_out_pack_args"]()
+    a.W = _ptr(W); a.Wt = _ptr(Wt); a.D = _ptr(D); a.dW = _ptr(dW); a.db = _ptr(db)
+    ref = Wt if mode == 0 else D
+    a.mode, a.co, a.C, a.C_pad, a.cpad, a.pitch, a.ones_row = mode, co, C, ref.shape[0], cpad, ref.stride(0), ones_row
+    return Launch("kair_conv_out_pack", a)
 
 
 def build_add_inplace(y, x, yb=None):

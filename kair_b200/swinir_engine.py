@@ -298,7 +298,7 @@ class _Plan:
         fwd.append(o.build_layernorm_fwd(tfin, P["norm.weight"], P["norm.bias"], C=C, y_bf16=yb, mean=meanF,
                                          rstd=rstdF, ones_col=C))
         fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
-                                   bias=Wt["bconv"][nl], resid=first, outB=resb))
+                                   bias=Wt["bconv"][nl], resid=first, outB=resb, ones_col=C))
         fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
                                         skip=self.img, skip_mean=mean_t, skip_scale=rng))
         self.fwd = fwd
@@ -333,10 +333,16 @@ class _Plan:
 
         bwd = []
         inv = 1.0 / rng
-        bwd.append(o.build_conv_out_dgrad(self.dout, cl_w, C=C, pitch=Cp, out_scale=inv, dfeat_f32=dresf,
-                                          dfeat_bf16=dresb))
-        bwd.append(o.build_conv_out_wgrad(self.dout, resb, cl_w, G["conv_last.weight"], G["conv_last.bias"], C=C,
-                                          pitch=Cp, out_scale=inv))
+        # conv_last backward as GEMMs over the 9-tap expansion of d(out) (columns tap*7 + c, K padded to 64)
+        ci = s.in_chans
+        dsh, clT, dWcl = bf(T, 64), bf(Cp, 64), f32(Cp, 64)
+        self._thin = (dWcl,)
+        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=inv))
+        bwd.append(o.build_conv_out_pack(mode=0, co=ci, C=C, cpad=7, W=cl_w, Wt=clT))
+        bwd.append(o.build_gemm_tn(dsh, clT, N=Cp, K=64, bn=_BN, outF=dresf, outB=dresb))
+        bwd.append(o.build_gemm_nt(resb, dsh, dWcl, n1=Cp, n2=64, bn=64))
+        bwd.append(o.build_conv_out_pack(mode=1, co=ci, C=C, cpad=7, D=dWcl, dW=G["conv_last.weight"],
+                                         db=G["conv_last.bias"], ones_row=C))
         bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_BN, conv=geo))
         bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, outB=dyb))
         dt = 2
@@ -377,15 +383,20 @@ class _Plan:
             dt = cur
             l_end -= depth
         if s.patch_norm:
-            dfirst = R[(dt + 1) % 3][0]
+            dfirst_b = R[(dt + 1) % 3][1]
             bwd.append(o.build_layernorm_bwd(first, mean0, rstd0, P["patch_embed.norm.weight"],
                                              G["patch_embed.norm.weight"], G["patch_embed.norm.bias"], C=C,
-                                             dy_f32=R[dt][0], dx_add=dresf, dx_f32=dfirst))
+                                             dy_f32=R[dt][0], dx_add=dresf, dx_bf16=dfirst_b))
         else:
-            bwd.append(o.build_add_inplace(R[dt][0], dresf, None))
-            dfirst = R[dt][0]
-        bwd.append(o.build_conv_in_wgrad(self.img, cf_w, mean_t, rng, G["conv_first.weight"], G["conv_first.bias"],
-                                         O=C, O_pad=Cp, pitch=Cp, dy_f32=dfirst))
+            bwd.append(o.build_add_inplace(R[dt][0], dresf, R[dt][1]))
+            dfirst_b = R[dt][1]
+        # conv_first weight gradient = d(first)^T . im2col(input) on the tensor cores (columns tap*7 + c, ones -> bias)
+        xcol, dWcf = bf(T, 64), f32(1, Cp, 64)
+        self._thin += (dWcf,)
+        bwd.append(o.build_im2col3x3(self.img, xcol, cpad=7, direction=1, mean=mean_t, scale=rng, ones_col=4 * 7 + ci))
+        bwd.append(o.build_gemm_nt(dfirst_b, xcol, dWcf[0], n1=Cp, n2=64, bn=64))
+        bwd.append(o.build_unpack_conv_grad(dWcf, [G["conv_first.weight"]], [G["conv_first.bias"]], O=C, I=ci, I_pad=7,
+                                            ones_col=ci, center_tap=4, dwp_pitch=64))
         gl = lambda suffix: [G[bn_ + suffix] for bn_ in blk_names]
         pl = lambda suffix: [P[bn_ + suffix] for bn_ in blk_names]
         bwd.append(o.build_unpack_linear_grad(dWqkv, pl("attn.qkv.weight"), pl("norm1.weight"), pl("norm1.bias"),
@@ -437,6 +448,8 @@ class _Plan:
         self.dout.copy_(dout)
         self.gflat.zero_()
         self.dwflat.zero_()
+        for t in self._thin:
+            t.zero_()
         for l in self.bwd:
             l.run(st)
         flat = self.gflat.clone()

@@ -301,11 +301,11 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
     return EmuLaunch("kair_pack_conv", run)
 
 
-def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4):
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0):
     def run():
         L, O_pad = dWp.shape[0], dWp.shape[1]
         for l in range(L):
-            d = dWp[l].reshape(O_pad, taps, I_pad)
+            d = dWp[l].reshape(O_pad, -1)[:, :taps * I_pad].reshape(O_pad, taps, I_pad)
             dW[l].copy_(d[:O, :, :I].permute(0, 2, 1).reshape(dW[l].shape))
             if db is not None and ones_col >= 0:
                 db[l].copy_(d[:O, center_tap, ones_col])
@@ -452,6 +452,37 @@ def build_conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
             db.add_((dout * out_scale).sum((0, 2, 3)))
 
     return EmuLaunch("kair_conv_out_wgrad", run)
+
+
+def build_im2col3x3(img, out, *, cpad, direction, mean=None, scale=1.0, ones_col=-1):
+    def run():
+        B, c, H, W = img.shape
+        x = img if mean is None else img - mean.view(1, -1, 1, 1)
+        x = F.pad(x * scale, (1, 1, 1, 1))
+        res = torch.zeros(B * H * W, out.shape[1])
+        for tap in range(9):
+            dy, dx = direction * (tap // 3 - 1), direction * (tap % 3 - 1)
+            sh = x[:, :, 1 + dy:1 + dy + H, 1 + dx:1 + dx + W]
+            res[:, tap * cpad:tap * cpad + c] = sh.permute(0, 2, 3, 1).reshape(-1, c)
+        if ones_col >= 0:
+            res[:, ones_col] = 1.0
+        out.copy_(_bf(res))
+    return EmuLaunch("kair_im2col3x3", run)
+
+
+def build_conv_out_pack(*, mode, co, C, cpad, W=None, Wt=None, D=None, dW=None, db=None, ones_row=-1):
+    def run():
+        if mode == 0:
+            res = torch.zeros(Wt.shape, dtype=torch.float32)
+            for tap in range(9):
+                res[:C, tap * cpad:tap * cpad + co] = W.reshape(co, C, 9)[:, :, tap].t()
+            Wt.copy_(_bf(res))
+        else:
+            g = torch.stack([D[:C, tap * cpad:tap * cpad + co] for tap in range(9)], dim=2)  # [C, co, 9]
+            dW.copy_(g.permute(1, 0, 2).reshape(dW.shape))
+            if db is not None:
+                db.copy_(D[ones_row, 4 * cpad:4 * cpad + co])
+    return EmuLaunch("kair_conv_out_pack", run)
 
 
 def build_add_inplace(y, x, yb=None):

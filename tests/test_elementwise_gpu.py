@@ -145,3 +145,22 @@ def test_add_inplace():
     y, x = torch.randn(1000, 192, generator=g), torch.randn(1000, 192, generator=g)
     kw = dict(y=y, x=x, yb=torch.zeros(1000, 192).bfloat16())
     _run_both("add_inplace", kw, ["y"], 1e-6)
+
+
+@pytest.mark.parametrize("c,direction", [(1, 1), (3, -1), (4, 1)])
+def test_im2col3x3(c, direction):
+    g = _g(6)
+    img = torch.randn(2, c, 24, 40, generator=g)
+    kw = dict(img=img, out=torch.zeros(2 * 24 * 40, 64).bfloat16(), cpad=7, direction=direction,
+              mean=torch.randn(c, generator=g), scale=1.7, ones_col=4 * 7 + c)
+    _run_both("im2col3x3", kw, ["out"], 1e-2)
+
+
+def test_conv_out_pack_roundtrip():
+    g = _g(7)
+    co, C = 3, 180
+    W = torch.randn(co, C, 3, 3, generator=g)
+    _run_both("conv_out_pack", dict(mode=0, co=co, C=C, cpad=7, W=W, Wt=torch.zeros(192, 64).bfloat16()), ["Wt"], 1e-2)
+    D = torch.randn(192, 64, generator=g)
+    _run_both("conv_out_pack", dict(mode=1, co=co, C=C, cpad=7, D=D, dW=torch.zeros(co, C, 3, 3), db=torch.zeros(co),
+                                    ones_row=C), ["dW", "db"], 1e-6)

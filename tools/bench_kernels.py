@@ -12,9 +12,23 @@ f32 = lambda *s: torch.randn(*s, device=dev)
 
 
 def timeit(fn, n=20):
+    """GPU time per call: the n calls are captured in a CUDA graph so host launch cost is excluded."""
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
+    if os.environ.get("KB_NO_GRAPH") != "1":
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(n):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n * 1e3
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(n):
@@ -36,6 +50,10 @@ def main():
     def add(name, **kw):
         cases[name] = kw
     add("qkv linear N576 K192", A=A192, B=W[(576, 192)], N=576, K=192, bias=bias[576], outB=OB576)
+    add("qkv linear N576 K192 no-out", A=A192, B=W[(576, 192)], N=576, K=192, bias=bias[576])
+    add("qkv linear N576 K192 no-bias", A=A192, B=W[(576, 192)], N=576, K=192, outB=OB576)
+    add("linear N192 K192 no-out", A=A192, B=W[(192, 192)], N=192, K=192)
+    add("linear N192 K576 no-out", A=A576, B=W[(192, 576)], N=192, K=576)
     add("resid_ln N192 K192 full", A=A192, B=W[(192, 192)], N=192, K=192, mode=ops.EPI_RESID_LN, bias=bias[192], resid=R, outF=OF, outB=OB, rowstat=rs, n_valid=180, ones_col=180)
     add("resid_ln N192 K192 no-resid", A=A192, B=W[(192, 192)], N=192, K=192, mode=ops.EPI_RESID_LN, bias=bias[192], outF=OF, outB=OB, rowstat=rs, n_valid=180, ones_col=180)
     add("resid_ln N192 K192 no-outF", A=A192, B=W[(192, 192)], N=192, K=192, mode=ops.EPI_RESID_LN, bias=bias[192], resid=R, outB=OB, rowstat=rs, n_valid=180, ones_col=180)
@@ -55,8 +73,7 @@ def main():
         kw = dict(kw)
         A, B = kw.pop("A"), kw.pop("B")
         l = ops.build_gemm_tn(A, B, bn=192, **kw)
-        st = ops.stream_handle()
-        us = timeit(lambda: l.run(st))
+        us = timeit(lambda: l.run(ops.stream_handle()))
         by = A.shape[0] * (kw["K"] * 2 + sum(v.element_size() * v.shape[-1] for k, v in kw.items() if isinstance(v, torch.Tensor) and v.dim() == 2))
         print("%-40s %8.1f us   %6.0f MB  %5.0f GB/s" % (name, us, by / 1e6, by / us / 1e3))
     # attention
@@ -66,10 +83,9 @@ def main():
         dout = bf(T, 192); dqkv = bf(T, 576); dtable = torch.zeros(225, 6, device=dev)
         for shift in (0, 4):
             l = ops.build_window_attn_fwd(qkv, table, out, batch=B_, H=H, W=Wd, num_heads=nH, window=8, shift=shift)
-            st = ops.stream_handle()
-            print("attn fwd shift %d  %8.1f us" % (shift, timeit(lambda: l.run(st))))
+            print("attn fwd shift %d  %8.1f us" % (shift, timeit(lambda: l.run(ops.stream_handle()))))
             l2 = ops.build_window_attn_bwd(qkv, table, dout, dqkv, dtable, batch=B_, H=H, W=Wd, num_heads=nH, window=8, shift=shift)
-            print("attn bwd shift %d  %8.1f us" % (shift, timeit(lambda: l2.run(st))))
+            print("attn bwd shift %d  %8.1f us" % (shift, timeit(lambda: l2.run(ops.stream_handle()))))
 
 
 if __name__ == "__main__":
