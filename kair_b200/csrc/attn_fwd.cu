@@ -18,6 +18,7 @@
 // Replaces models/network_swinir.py:124-142 (q@k^T, bias gather :127-130, mask :132-135, softmax :136-138, attn@v)
 // together with window_partition/window_reverse (:33-62), torch.roll (:249-252, :269-272) and calculate_mask
 // (:216-237).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -26,15 +27,24 @@
 
 namespace kb {
 
+// timeline stamps: role r (0 producer, 1 mma, 2 softmax warp 2 lane 0), up to 256 events each
+#define AF_TS(role, cnt)                                                              \
+  do {                                                                                \
+    if (p.ts && blockIdx.x == 0 && (cnt) < 256) p.ts[(role) * 256 + (cnt)++] = clock64(); \
+  } while (0)
+
 constexpr int AF_THREADS = 320;
 constexpr int AF_STAGE = 3 * 16384;     // Q, K, V tiles of one head pair
 constexpr int AF_P_BYTES = 16384;       // [2 windows x 64 rows][64 keys] bf16, SWIZZLE_128B
 constexpr int AF_MAX_HEADS = 8;
 
 struct AttnFwdParams {
-  CUtensorMap tmQKV, tmOut;
+  CUtensorMap tmQKV, tmOut;      // 4x4-pixel quadrant boxes
+  CUtensorMap tmQKV2, tmOut2;    // 4-wide x 8-tall half-window boxes (two quadrants per TMA operation)
   const float* table;  // [(2*8-1)^2][nH]
   int nH, H, W, nWh, nWw, shift, total_windows, pairs;
+  long long* ts;  // development timeline buffer (env KB_AF_TS): [role][event] clock64 stamps of CTA 0
+  int dbg;  // development ablations (env KB_AF_DBG): 1 no bias/mask/exp, 2 no output TMA stores, 4 no epilogue math
 };
 
 __device__ __forceinline__ void window_origin(const AttnFwdParams& p, int gw, int& b, int& wi, int& wj) {
@@ -52,9 +62,11 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
   uint8_t* p_s = qkv_s + 2 * AF_STAGE;          // 2 x 32 KiB
   uint8_t* out_s = p_s + 2 * AF_P_BYTES;        // [128 x nH*32] bf16 as nH/2 atoms of 16 KiB
   uint8_t* misc = out_s + (p.nH / 2) * 16384;
-  uint64_t* qkv_full = reinterpret_cast<uint64_t*>(misc);
-  uint64_t* qkv_empty = qkv_full + 2;
-  uint64_t* s_full = qkv_empty + 2;
+  uint64_t* qk_full = reinterpret_cast<uint64_t*>(misc);  // Q,K tiles of a stage (dead once S is computed)
+  uint64_t* qk_empty = qk_full + 2;
+  uint64_t* v_full = qk_empty + 2;                        // V tile of a stage (dead once O is accumulated)
+  uint64_t* v_empty = v_full + 2;
+  uint64_t* s_full = v_empty + 2;
   uint64_t* s_empty = s_full + 2;
   uint64_t* p_full = s_empty + 2;
   uint64_t* p_empty = p_full + 2;
@@ -71,12 +83,16 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmQKV);
     tma_prefetch_desc(&p.tmOut);
+    tma_prefetch_desc(&p.tmQKV2);
+    tma_prefetch_desc(&p.tmOut2);
   }
   if (warp == 1) {
     if (lane == 0) {
       for (int i = 0; i < 2; ++i) {
-        mbar_init(&qkv_full[i], 1);
-        mbar_init(&qkv_empty[i], 1);
+        mbar_init(&qk_full[i], 1);
+        mbar_init(&qk_empty[i], 1);
+        mbar_init(&v_full[i], 1);
+        mbar_init(&v_empty[i], 1);
         mbar_init(&s_full[i], 1);
         mbar_init(&s_empty[i], 4);
         mbar_init(&p_full[i], 4);
@@ -91,9 +107,23 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     tmem_relinquish();
   }
   // bias table -> smem as [h][idx]
-  for (int i = threadIdx.x; i < 225 * nH; i += AF_THREADS) {
-    int idx = i / nH, h = i - idx * nH;
-    table_s[h * 225 + idx] = p.table[i];
+  {
+    // all loads of a thread are issued before the first store; values are pre-multiplied by log2(e) so that the
+    // softmax works in the exp2 domain with a single FFMA per score
+    float tv[6];
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int i = threadIdx.x + u * AF_THREADS;
+      tv[u] = i < 225 * nH ? __ldg(p.table + i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int i = threadIdx.x + u * AF_THREADS;
+      if (i < 225 * nH) {
+        const int idx = i / nH, h = i - idx * nH;
+        table_s[h * 225 + idx] = tv[u] * 1.4426950408889634f;
+      }
+    }
   }
   tcgen05_fence_before();
   __syncthreads();
@@ -107,27 +137,50 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      int tsn = 0;
       for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x) {
-        int gw0 = pair * 2;
-        int gw1 = gw0 + 1 < p.total_windows ? gw0 + 1 : gw0;
-        int wb[2], wi[2], wj[2];
-        window_origin(p, gw0, wb[0], wi[0], wj[0]);
-        window_origin(p, gw1, wb[1], wi[1], wj[1]);
-        for (int hp = 0; hp < hpairs; ++hp) {
-          mbar_wait(&qkv_empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&qkv_full[stage], AF_STAGE);
-          uint8_t* st = qkv_s + stage * AF_STAGE;
+        const int gw0 = pair * 2;
+        const int gw1 = gw0 + 1 < p.total_windows ? gw0 + 1 : gw0;
+        // box coordinates of the pair's four half windows (in-window order is quadrant-major with quad = qx*2 + qy, so
+        // the two quadrants of a half window are adjacent in shared memory: one 4x8 box per half unless the window
+        // wraps around the bottom edge, then two 4x4 boxes)
+        int wb[2], hw[2], h0[2], h1[2], ww[2][2];
 #pragma unroll
-          for (int t3 = 0; t3 < 3; ++t3) {
-            const int col = t3 * nH * 32 + hp * 64;
+        for (int wsel = 0; wsel < 2; ++wsel) {
+          int wi, wj;
+          window_origin(p, wsel ? gw1 : gw0, wb[wsel], wi, wj);
+          hw[wsel] = p.shift > 0 && wi == p.nWh - 1;
+          h0[wsel] = (wi * 8 + p.shift) % p.H;
+          h1[wsel] = (h0[wsel] + 4) % p.H;
+          ww[wsel][0] = (wj * 8 + p.shift) % p.W;
+          ww[wsel][1] = (wj * 8 + 4 + p.shift) % p.W;
+        }
+        auto load_tile = [&](uint8_t* dst, uint64_t* bar, int col) {
 #pragma unroll
-            for (int wq = 0; wq < 8; ++wq) {
-              const int wsel = wq >> 2, quad = wq & 3;
-              const int hh = (wi[wsel] * 8 + (quad >> 1) * 4 + p.shift) % p.H;
-              const int ww = (wj[wsel] * 8 + (quad & 1) * 4 + p.shift) % p.W;
-              tma_load_4d(st + t3 * 16384 + wq * 2048, &p.tmQKV, &qkv_full[stage], col, ww, hh, wb[wsel]);
+          for (int wsel = 0; wsel < 2; ++wsel) {
+#pragma unroll
+            for (int qx = 0; qx < 2; ++qx) {
+              uint8_t* d = dst + (wsel * 4 + qx * 2) * 2048;
+              if (!hw[wsel]) {
+                tma_load_4d(d, &p.tmQKV2, bar, col, ww[wsel][qx], h0[wsel], wb[wsel]);
+              } else {
+                tma_load_4d(d, &p.tmQKV, bar, col, ww[wsel][qx], h0[wsel], wb[wsel]);
+                tma_load_4d(d + 2048, &p.tmQKV, bar, col, ww[wsel][qx], h1[wsel], wb[wsel]);
+              }
             }
           }
+        };
+        for (int hp = 0; hp < hpairs; ++hp) {
+          uint8_t* st = qkv_s + stage * AF_STAGE;
+          mbar_wait(&qk_empty[stage], phase ^ 1);
+          AF_TS(0, tsn);
+          mbar_arrive_expect_tx(&qk_full[stage], 32768);
+          load_tile(st, &qk_full[stage], hp * 64);
+          load_tile(st + 16384, &qk_full[stage], nH * 32 + hp * 64);
+          mbar_wait(&v_empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&v_full[stage], 16384);
+          load_tile(st + 32768, &v_full[stage], 2 * nH * 32 + hp * 64);
+          AF_TS(0, tsn);
           if (++stage == 2) {
             stage = 0;
             phase ^= 1;
@@ -138,39 +191,66 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     __syncwarp();
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
+    // Software-pipelined by one head-pair step: S(n+1) = Q K^T is issued before waiting for the probabilities of step
+    // n, so the softmax warps always find their next score tile ready while O(n) = P V is still being accumulated.
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(64, 32, 0, 1);
-      int stage = 0;
-      uint32_t phase = 0;
-      uint32_t use[2] = {0, 0};  // per S/P buffer use counters
-      uint32_t pair_it = 0;
-      for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
-        for (int hp = 0; hp < hpairs; ++hp) {
-          mbar_wait(&qkv_full[stage], phase);
+      uint32_t s_use[2] = {0, 0}, p_use[2] = {0, 0};  // per S / P buffer use counters
+      int s_stage = 0;
+      uint32_t s_phase = 0;
+      int tsn = 0;
+      auto issue_S = [&]() {
+        mbar_wait(&qk_full[s_stage], s_phase);
+        AF_TS(1, tsn);
+        tcgen05_fence_after();
+        const uint32_t q_addr = smem_u32(qkv_s + s_stage * AF_STAGE);
+        const uint32_t k_addr = q_addr + 16384;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          mbar_wait(&s_empty[b], (s_use[b] & 1) ^ 1);
           tcgen05_fence_after();
-          const uint32_t q_addr = smem_u32(qkv_s + stage * AF_STAGE);
-          const uint32_t k_addr = q_addr + 16384;
-          const uint32_t v_addr = q_addr + 32768;
 #pragma unroll
-          for (int b = 0; b < 2; ++b) {
-            mbar_wait(&s_empty[b], (use[b] & 1) ^ 1);
-            tcgen05_fence_after();
+          for (int w = 0; w < 2; ++w) {
 #pragma unroll
-            for (int w = 0; w < 2; ++w) {
-#pragma unroll
-              for (int k = 0; k < 2; ++k) {
-                umma_f16_ss(tmem_S + b * 64 + ((uint32_t)(w * 16) << 16),
-                            make_desc_kmajor_sw128(q_addr + w * 8192 + b * 64 + k * 32),
-                            make_desc_kmajor_sw128(k_addr + w * 8192 + b * 64 + k * 32), idesc_s, k);
-              }
+            for (int k = 0; k < 2; ++k) {
+              umma_f16_ss(tmem_S + b * 64 + ((uint32_t)(w * 16) << 16),
+                          make_desc_kmajor_sw128(q_addr + w * 8192 + b * 64 + k * 32),
+                          make_desc_kmajor_sw128(k_addr + w * 8192 + b * 64 + k * 32), idesc_s, k);
             }
-            umma_commit(&s_full[b]);
           }
+          umma_commit(&s_full[b]);
+          s_use[b]++;
+        }
+        umma_commit(&qk_empty[s_stage]);  // Q and K of this stage may be overwritten as soon as S is done
+        AF_TS(1, tsn);
+        if (++s_stage == 2) {
+          s_stage = 0;
+          s_phase ^= 1;
+        }
+      };
+      int stage = 0;
+      uint32_t v_phase = 0;
+      uint32_t pair_it = 0;
+      if (blockIdx.x < p.pairs) issue_S();
+      for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
+        const bool last_pair = pair + (int)gridDim.x >= p.pairs;
+        for (int hp = 0; hp < hpairs; ++hp) {
+          // issue the next step's S now if its Q/K have landed, otherwise after this step's P V
+          const bool more = !(last_pair && hp == hpairs - 1);
+          bool s_done = !more;
+          if (more && mbar_try_wait(&qk_full[s_stage], s_phase)) {
+            issue_S();
+            s_done = true;
+          }
+          const uint32_t v_addr = smem_u32(qkv_s + stage * AF_STAGE) + 32768;
+          mbar_wait(&v_full[stage], v_phase);
+          tcgen05_fence_after();
 #pragma unroll
           for (int b = 0; b < 2; ++b) {
             const int h = hp * 2 + b;
-            mbar_wait(&p_full[b], use[b] & 1);
+            mbar_wait(&p_full[b], p_use[b] & 1);
+            AF_TS(1, tsn);
             tcgen05_fence_after();
             if (h == 0) {
               mbar_wait(o_empty, (pair_it & 1) ^ 1);
@@ -187,15 +267,17 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
               }
             }
             umma_commit(&p_empty[b]);
-            use[b]++;
+            p_use[b]++;
           }
-          umma_commit(&qkv_empty[stage]);
+          umma_commit(&v_empty[stage]);
+          if (hp == hpairs - 1) umma_commit(o_full);  // before a possibly blocking wait for the next pair's Q/K
+          AF_TS(1, tsn);
+          if (!s_done) issue_S();
           if (++stage == 2) {
             stage = 0;
-            phase ^= 1;
+            v_phase ^= 1;
           }
         }
-        umma_commit(o_full);
       }
     }
     __syncwarp();
@@ -207,13 +289,15 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     const int wsel = lane >> 4;
     const int i = q * 16 + (lane & 15);  // in-window index, quadrant-major (== quadrant q)
     const int row = wsel * 64 + i;       // row of the 128-row smem tiles
-    const int quad_i = i >> 4;
-    const int ry = (quad_i >> 1) * 4 + ((i & 15) >> 2);
-    const int rx = (quad_i & 1) * 4 + (i & 3);
+    const int quad_i = i >> 4;           // = qx*2 + qy
+    const int ry = (quad_i & 1) * 4 + ((i & 15) >> 2);
+    const int rx = (quad_i >> 1) * 4 + (i & 3);
     const int base_i = ry * 15 + rx;
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
     uint32_t use = 0;
     uint32_t pair_it = 0;
+    int tsn = 0;
+    const bool tsw = (warp == 2 && lane == 0);
     const float LOG2E = 1.4426950408889634f;
 
     for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
@@ -227,8 +311,8 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       float madd[4];
 #pragma unroll
       for (int qj = 0; qj < 4; ++qj) {
-        bool m = (lastrow && ((qj >> 1) != (quad_i >> 1))) || (lastcol && ((qj & 1) != (quad_i & 1)));
-        madd[qj] = m ? -100.0f : 0.0f;
+        bool m = (lastrow && ((qj & 1) != (quad_i & 1))) || (lastcol && ((qj >> 1) != (quad_i >> 1)));
+        madd[qj] = m ? -100.0f * 1.4426950408889634f : 0.0f;
       }
       float inv_sum[AF_MAX_HEADS / 2];
 
@@ -236,6 +320,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         const int h = hh * 2 + g;
         const float* tb = table_s + h * 225 + base_i;
         mbar_wait(&s_full[g], use & 1);
+        if (tsw) AF_TS(2, tsn);
         tcgen05_fence_after();
         float s[64];
         {
@@ -252,29 +337,37 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_empty[g]);
-        float mx = -INFINITY;
+        if (tsw) AF_TS(2, tsn);
+        // scores in the exp2 domain: t = s*log2(e) + bias*log2(e) (+ mask); 4-way split max / sum chains for ILP
+        const bool masked = lastrow || lastcol;
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int j = 0; j < 64; ++j) {
           const int qj = j >> 4;
-          const int jy = (qj >> 1) * 4 + ((j & 15) >> 2);
-          const int jx = (qj & 1) * 4 + (j & 3);
-          s[j] = s[j] + tb[(7 - jy) * 15 + (7 - jx)] + madd[qj];
-          mx = fmaxf(mx, s[j]);
+          const int jy = (qj & 1) * 4 + ((j & 15) >> 2);
+          const int jx = (qj >> 1) * 4 + (j & 3);
+          s[j] = fmaf(s[j], LOG2E, tb[(7 - jy) * 15 + (7 - jx)]);
+          if (masked) s[j] += madd[qj];
+          mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
         }
-        float sum = 0.f;
+        const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        float sum4[4] = {0.f, 0.f, 0.f, 0.f};
         uint32_t pk[32];
-        const float mb = mx * LOG2E;
 #pragma unroll
         for (int j = 0; j < 64; j += 2) {
-          float e0 = exp2f(s[j] * LOG2E - mb);
-          float e1 = exp2f(s[j + 1] * LOG2E - mb);
+          float e0, e1;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(s[j] - mb));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(s[j + 1] - mb));
           __nv_bfloat162 b2 = __floats2bfloat162_rn(e0, e1);
           float2 f2 = __bfloat1622float2(b2);
-          sum += f2.x + f2.y;  // normalise by the sum of the values the tensor core will actually see
+          sum4[(j >> 1) & 3] += f2.x + f2.y;  // normalise by the sum of the values the tensor core will actually see
           pk[j >> 1] = *reinterpret_cast<uint32_t*>(&b2);
         }
+        const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
         inv_sum[hh] = 1.0f / sum;
+        if (tsw) AF_TS(2, tsn);
         mbar_wait(&p_empty[g], (use & 1) ^ 1);
+        if (tsw) AF_TS(2, tsn);
         {
           const uint32_t base = smem_u32(p_s + g * AF_P_BYTES) + row * 128;
           const uint32_t sw = row & 7;
@@ -289,14 +382,17 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[g]);
+        if (tsw) AF_TS(2, tsn);
       }
 
       // ---- epilogue: O * 1/rowsum -> bf16 -> staging -> TMA scatter to the windows' pixels
       mbar_wait(o_full, pair_it & 1);
+      if (tsw) AF_TS(2, tsn);
       tcgen05_fence_after();
-      if (warp == 2 && lane == 0) tma_store_wait_read<0>();
+      if (lane == 0) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
       named_bar_sync(2, 256);
       for (int hh = 0; hh < nH / 2; ++hh) {
+        if (p.dbg & 4) break;
         const int h = hh * 2 + g;
         uint32_t r[32];
         tmem_ld32(tmem_O + lane_sel + h * 32, r);
@@ -321,21 +417,31 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       __syncwarp();
       if (lane == 0) mbar_arrive(o_empty);
       named_bar_sync(2, 256);
-      if (warp == 2 && lane == 0) {
-        for (int ws2 = 0; ws2 < (second_valid ? 2 : 1); ++ws2) {
+      if (lane == 0) {
+        // the pair's (window, half, head-pair) output boxes are spread over the eight epilogue warps
+        const int ew = warp - 2;
+        const int nops = (second_valid ? 2 : 1) * 2 * hpairs;
+        for (int op = ew; op < nops; op += 8) {
+          const int a = op % hpairs, hq = op / hpairs;
+          const int ws2 = hq >> 1, qx = hq & 1;
           int b2, wi2, wj2;
           window_origin(p, gw0 + ws2, b2, wi2, wj2);
-          for (int quad = 0; quad < 4; ++quad) {
-            const int hh2 = (wi2 * 8 + (quad >> 1) * 4 + p.shift) % p.H;
-            const int ww2 = (wj2 * 8 + (quad & 1) * 4 + p.shift) % p.W;
-            for (int a = 0; a < hpairs; ++a)
-              tma_store_4d(&p.tmOut, out_s + a * 16384 + (ws2 * 4 + quad) * 2048, a * 64, ww2, hh2, b2);
+          const bool hwrap = p.shift > 0 && wi2 == p.nWh - 1;
+          const int h0 = (wi2 * 8 + p.shift) % p.H;
+          const int ww2 = (wj2 * 8 + qx * 4 + p.shift) % p.W;
+          const uint8_t* src = out_s + a * 16384 + (ws2 * 4 + qx * 2) * 2048;
+          if (!hwrap) {
+            tma_store_4d(&p.tmOut2, src, a * 64, ww2, h0, b2);
+          } else {
+            tma_store_4d(&p.tmOut, src, a * 64, ww2, h0, b2);
+            tma_store_4d(&p.tmOut, src + 2048, a * 64, ww2, (h0 + 4) % p.H, b2);
           }
         }
         tma_store_commit();
       }
+      if (tsw) AF_TS(2, tsn);
     }
-    if (warp == 2 && lane == 0) tma_store_wait_all<0>();
+    if (lane == 0) tma_store_wait_all<0>();
     __syncwarp();
   }
 
@@ -369,6 +475,10 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
   p.shift = a.shift;
   p.total_windows = a.batch * p.nWh * p.nWw;
   p.pairs = (p.total_windows + 1) / 2;
+  {
+    const char* e = getenv("KB_AF_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
   uint32_t box[4] = {64, 4, 4, 1};
   {
     uint64_t dims[4] = {(uint64_t)3 * a.num_heads * 32, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
@@ -384,6 +494,21 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
                   CU_TENSOR_MAP_SWIZZLE_128B))
       return -2;
   }
+  uint32_t box2[4] = {64, 4, 8, 1};
+  {
+    uint64_t dims[4] = {(uint64_t)3 * a.num_heads * 32, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)a.qkv_pitch * 2, (uint64_t)a.qkv_pitch * 2 * a.W, (uint64_t)a.qkv_pitch * 2 * a.W * a.H};
+    if (make_tmap(&p.tmQKV2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.qkv, dims, str, box2, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)a.num_heads * 32, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+    uint64_t str[3] = {(uint64_t)a.out_pitch * 2, (uint64_t)a.out_pitch * 2 * a.W, (uint64_t)a.out_pitch * 2 * a.W * a.H};
+    if (make_tmap(&p.tmOut2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.out, dims, str, box2, nullptr,
+                  CU_TENSOR_MAP_SWIZZLE_128B))
+      return -2;
+  }
   const size_t smem = 1024 + 2 * AF_STAGE + 2 * AF_P_BYTES + (size_t)(a.num_heads / 2) * 16384 + 256 + (size_t)a.num_heads * 225 * 4 + 64;
   KB_CHECK(smem <= 232448, "kair_window_attn_fwd: shared memory plan exceeds 227 KiB (num_heads=%d)", a.num_heads);
   static bool attr_set[64] = {false};
@@ -394,8 +519,26 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
     attr_set[dev & 63] = true;
   }
   int grid = p.pairs < sm_count() ? p.pairs : sm_count();
+  static long long* ts_dev = nullptr;
+  const bool want_ts = getenv("KB_AF_TS") != nullptr;
+  if (want_ts) {
+    if (!ts_dev) cudaMalloc(&ts_dev, 3 * 256 * 8);
+    cudaMemset(ts_dev, 0, 3 * 256 * 8);
+    p.ts = ts_dev;
+  }
   window_attn_fwd_kernel<<<grid, AF_THREADS, smem, st>>>(p);
   KB_CUDA(cudaGetLastError());
+  if (want_ts) {
+    static long long h[3 * 256];
+    cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    long long t0 = h[0];
+    const char* names[3] = {"producer", "mma", "softmax"};
+    for (int r = 0; r < 3; ++r) {
+      fprintf(stderr, "%s:", names[r]);
+      for (int i = 0; i < 64 && h[r * 256 + i]; ++i) fprintf(stderr, " %lld", h[r * 256 + i] - t0);
+      fprintf(stderr, "\n");
+    }
+  }
   return 0;
 }
 
