@@ -38,6 +38,8 @@ int kair_check_device(void);
  *              (nn.Conv2d(C,C,3,1,1): network_swinir.py:465, 669, 729; basicblock.py:65)
  * Epilogue modes (what happens to acc = A*B^T, one row of the tile per thread):
  *   KAIR_EPI_LINEAR   v = act(acc + bias [+ resid]);                          outB = bf16(v), outF = v
+ *                     with aux (and act == NONE): activation backward, v = (acc + bias) * (aux > 0 ? 1 : act_slope)
+ *                     [+ resid], aux = the saved ReLU / LeakyReLU output (basicblock.py:70-77, :211-223)
  *   KAIR_EPI_GELU     u = acc + bias; outB2 = bf16(u); outB = bf16(gelu_erf(u))   (network_swinir.py:25-26)
  *   KAIR_EPI_RESID_LN v = acc + bias + resid; outF = v; outB = bf16((v-mean)*rstd); rowstat = rstd
  *                     (residual add + the next LayerNorm, network_swinir.py:245, 276-277)
@@ -189,6 +191,10 @@ typedef struct kair_pack_conv_args {
   void* WpT;                 /* or NULL */
   float* bp;                 /* fp32 [L][O_pad] or NULL */
   int32_t L, O, I, O_pad, I_pad, taps;
+  /* optional per-output-channel affine folded into the packed operands (eval-mode BatchNorm after the conv,
+   * basicblock.py:68-69; the arithmetic of utils/utils_bnorm.py:44-58): Wp = W * oscale[o], bp = b * oscale[o] + oshift[o] */
+  const void* const* oscale; /* [L] -> fp32 (O) or NULL */
+  const void* const* oshift; /* [L] -> fp32 (O) or NULL */
 } kair_pack_conv_args;
 int kair_pack_conv(const kair_pack_conv_args* args, void* stream);
 
@@ -278,6 +284,10 @@ typedef struct kair_conv_out_args {
   float* db;
   float skip_scale, out_scale;
   int32_t batch, co, H, Wd /* width */, C, pitch;
+  /* dgrad only, optional: feat = act(u) was produced by ReLU / LeakyReLU (network_dncnn.py:63-65); the gradient is
+   * multiplied by act'(u) = (mask > 0 ? 1 : mask_slope), mask = the saved bf16 feat */
+  const void* mask;
+  float mask_slope;
 } kair_conv_out_args;
 int kair_conv_out_fwd(const kair_conv_out_args* args, void* stream);
 int kair_conv_out_dgrad(const kair_conv_out_args* args, void* stream);
@@ -313,6 +323,99 @@ typedef struct kair_conv_out_pack_args {
   int32_t mode, co, C, C_pad, cpad, pitch, ones_row;
 } kair_conv_out_pack_args;
 int kair_conv_out_pack(const kair_conv_out_pack_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Conv-net helpers (DnCNN: models/network_dncnn.py:40-71; DRUNet / UNetRes: models/network_unet.py:21-76).
+ *
+ * kair_space_to_depth / kair_depth_to_space: the 2x2 stride-2 pixel regrouping that turns
+ *   nn.Conv2d(Cin, Cout, 2, 2, 0) (basicblock.py:495-501) into a dense GEMM over [T/4][4*Cin] rows, and
+ *   nn.ConvTranspose2d(Cin, Cout, 2, 2, 0) (basicblock.py:471-477) into a dense GEMM producing [T/4][4*Cout] rows:
+ *     coarse[(b*H/2 + h)*W/2 + w][tap*C + c] <-> fine[(b*H + 2h+dy)*W + 2w+dx][c],  tap = dy*2 + dx
+ *   (H, W are the FINE resolution; both must be even).  s2d reads bf16 and writes bf16; d2s reads fp32 or bf16 and
+ *   writes fp32 and/or bf16.  They are also each other's adjoints, so they serve the backward passes.
+ * kair_colsum: out[c] += sum_t x[t][c]  (bias gradients: autograd of basicblock.py:65 with bias=True).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_regroup_args {
+  const void* fine_bf16;   /* s2d input  [B*H*W][fine_pitch] */
+  void* coarse_bf16;       /* s2d output [B*H/2*W/2][coarse_pitch] */
+  const float* coarse_in_f32;  /* d2s input (either) */
+  const void* coarse_in_bf16;
+  float* fine_out_f32;     /* d2s outputs (either or both) */
+  void* fine_out_bf16;
+  int64_t fine_pitch, coarse_pitch;
+  int32_t batch, H, W, C;  /* C % 8 == 0 */
+} kair_regroup_args;
+int kair_space_to_depth(const kair_regroup_args* args, void* stream);
+int kair_depth_to_space(const kair_regroup_args* args, void* stream);
+
+typedef struct kair_colsum_args {
+  const void* x_bf16;      /* either */
+  const float* x_f32;
+  float* out;              /* [C], accumulated (caller zeroes) */
+  int64_t T, pitch;
+  int32_t C;               /* even */
+  float scale;
+} kair_colsum_args;
+int kair_colsum(const kair_colsum_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * BatchNorm2d over NHWC token rows (B.conv mode 'B': nn.BatchNorm2d(C, momentum=0.9, eps=1e-4, affine=True),
+ * basicblock.py:68-69), training mode: biased batch statistics over all T = B*H*W tokens.
+ *   kair_bn_stats       acc[0][c] += sum_t z, acc[1][c] += sum_t z^2            (double accumulators, caller zeroes once)
+ *   kair_bn_finalize    mean, rstd = 1/sqrt(var_biased + eps); running_mean/var <- (1-m)*running + m*batch (unbiased
+ *                       variance), num_batches_tracked += 1; acc is reset to zero
+ *   kair_bn_apply       y = act(gamma * (z - mean) * rstd + beta)  -> bf16 (and/or fp32)
+ *   kair_bn_bwd_reduce  g = dy * act'(y);  dbeta[c] += sum_t g,  dgamma[c] += sum_t g * xhat      (caller zeroes)
+ *   kair_bn_bwd_apply   dz = gamma * rstd * (g - dbeta/T - xhat * dgamma/T) -> bf16;  dbias[c] += sum_t dz (optional)
+ *   kair_bn_fold        eval mode: scale = gamma / sqrt(running_var + eps), shift = beta - running_mean * scale
+ *                       (consumed by kair_pack_conv's oscale / oshift)
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_bn_args {
+  const float* z;          /* fp32 [T][pitch] conv output (pre-BN) */
+  const void* y;           /* bf16 [T][pitch] activated output (backward: activation mask) */
+  const void* dy;          /* bf16 [T][pitch] gradient w.r.t. the activated output (or dy_f32) */
+  const float* dy_f32;     /* fp32 alternative: the BN backward subtracts projections of dy, which amplifies bf16 rounding */
+  void* out_bf16;          /* apply: y;  bwd_apply: dz */
+  float* out_f32;          /* apply only, optional */
+  const float* gamma;
+  const float* beta;
+  float* mean;             /* [C] */
+  float* rstd;             /* [C] */
+  double* acc;             /* [2][C] */
+  float* running_mean;     /* finalize / fold */
+  float* running_var;
+  int64_t* num_batches_tracked; /* finalize, optional */
+  float* dgamma;           /* [C] */
+  float* dbeta;            /* [C] */
+  float* dbias;            /* [C] optional (bwd_apply) */
+  float* scale;            /* fold outputs [C] */
+  float* shift;
+  int64_t T, pitch;
+  int32_t C;               /* C % 4 == 0, C <= 512 */
+  int32_t act;             /* KAIR_ACT_* applied after the affine (slope 0 == ReLU) */
+  float act_slope, eps, momentum;
+} kair_bn_args;
+int kair_bn_stats(const kair_bn_args* args, void* stream);
+int kair_bn_finalize(const kair_bn_args* args, void* stream);
+int kair_bn_apply(const kair_bn_args* args, void* stream);
+int kair_bn_bwd_reduce(const kair_bn_args* args, void* stream);
+int kair_bn_bwd_apply(const kair_bn_args* args, void* stream);
+int kair_bn_fold(const kair_bn_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * SwinIR reconstruction heads (network_swinir.py:572-615, 740-762, 816-831).
+ *   kair_pixel_shuffle  nn.PixelShuffle(r) on token features: in [B*H*W][r*r*C] with channel c*r*r + dy*r + dx
+ *                       -> out [B*(rH)*(rW)][C] at pixel (r*h+dy, r*w+dx); bf16 in / bf16 out  (r = 2, 3, 4)
+ *   kair_upsample_nearest2  torch.nn.functional.interpolate(scale_factor=2, mode='nearest') on token features
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_shuffle_args {
+  const void* in;          /* bf16 */
+  void* out;               /* bf16 */
+  int64_t in_pitch, out_pitch;
+  int32_t batch, H, W, C, r; /* H, W = INPUT resolution; C = output channels */
+} kair_shuffle_args;
+int kair_pixel_shuffle(const kair_shuffle_args* args, void* stream);
+int kair_upsample_nearest2(const kair_shuffle_args* args, void* stream);
 
 /* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);

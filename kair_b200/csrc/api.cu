@@ -21,6 +21,17 @@ int conv_out_dgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
 int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st);
 int im2col3x3_launch(const kair_im2col_args& a, cudaStream_t st);
 int conv_out_pack_launch(const kair_conv_out_pack_args& a, cudaStream_t st);
+int s2d_launch(const kair_regroup_args& a, cudaStream_t st);
+int d2s_launch(const kair_regroup_args& a, cudaStream_t st);
+int colsum_launch(const kair_colsum_args& a, cudaStream_t st);
+int bn_stats_launch(const kair_bn_args& a, cudaStream_t st);
+int bn_finalize_launch(const kair_bn_args& a, cudaStream_t st);
+int bn_apply_launch(const kair_bn_args& a, cudaStream_t st);
+int bn_bwd_reduce_launch(const kair_bn_args& a, cudaStream_t st);
+int bn_bwd_apply_launch(const kair_bn_args& a, cudaStream_t st);
+int bn_fold_launch(const kair_bn_args& a, cudaStream_t st);
+int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st);
+int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 }
 
@@ -83,6 +94,17 @@ KB_WRAP(kair_conv_out_dgrad, kair_conv_out_args, conv_out_dgrad_launch)
 KB_WRAP(kair_conv_out_wgrad, kair_conv_out_args, conv_out_wgrad_launch)
 KB_WRAP(kair_im2col3x3, kair_im2col_args, im2col3x3_launch)
 KB_WRAP(kair_conv_out_pack, kair_conv_out_pack_args, conv_out_pack_launch)
+KB_WRAP(kair_space_to_depth, kair_regroup_args, s2d_launch)
+KB_WRAP(kair_depth_to_space, kair_regroup_args, d2s_launch)
+KB_WRAP(kair_colsum, kair_colsum_args, colsum_launch)
+KB_WRAP(kair_bn_stats, kair_bn_args, bn_stats_launch)
+KB_WRAP(kair_bn_finalize, kair_bn_args, bn_finalize_launch)
+KB_WRAP(kair_bn_apply, kair_bn_args, bn_apply_launch)
+KB_WRAP(kair_bn_bwd_reduce, kair_bn_args, bn_bwd_reduce_launch)
+KB_WRAP(kair_bn_bwd_apply, kair_bn_args, bn_bwd_apply_launch)
+KB_WRAP(kair_bn_fold, kair_bn_args, bn_fold_launch)
+KB_WRAP(kair_pixel_shuffle, kair_shuffle_args, pixel_shuffle_launch)
+KB_WRAP(kair_upsample_nearest2, kair_shuffle_args, upsample_nearest2_launch)
 #undef KB_WRAP
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {

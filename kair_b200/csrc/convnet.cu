@@ -1,0 +1,474 @@
+// Memory-bound kernels of the conv-net paths (DnCNN, DRUNet / UNetRes) and of SwinIR's reconstruction heads:
+//   * 2x2 stride-2 pixel regrouping (space-to-depth / depth-to-space) that turns the strided convolution and the
+//     transposed convolution into dense tcgen05 GEMMs (models/basicblock.py:471-477, 495-501)
+//   * per-channel column sums (bias gradients)
+//   * training-mode BatchNorm2d on NHWC token rows: statistics, apply (+ReLU), backward reduce / apply, and the
+//     eval-mode fold into the preceding convolution (models/basicblock.py:68-69; utils/utils_bnorm.py:44-58)
+//   * PixelShuffle / nearest-neighbour x2 of token features (models/network_swinir.py:572-615, 823-826)
+// All of them are HBM-bound: 16-byte vector accesses, consecutive threads on consecutive addresses, grids sized in
+// multiples of the SM count, warp/block partial sums before any atomic.
+#include <string.h>
+
+#include "common.cuh"
+#include "host.h"
+#include "../../include/kair_b200.h"
+
+namespace kb {
+
+static inline int grid_for(long long items, int per_block, int max_mult) {
+  long long b = (items + per_block - 1) / per_block;
+  long long cap = (long long)sm_count() * max_mult;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+// ------------------------------------------------------------------------------------------------ regrouping
+__global__ void s2d_kernel(const kair_regroup_args a) {
+  const int Hc = a.H >> 1, Wc = a.W >> 1, vc = a.C >> 3;  // 8 bf16 per vector
+  const long long nvec = (long long)a.batch * Hc * Wc * 4 * vc;
+  const uint4* src = reinterpret_cast<const uint4*>(a.fine_bf16);
+  uint4* dst = reinterpret_cast<uint4*>(a.coarse_bf16);
+  const long long fp = a.fine_pitch >> 3, cp = a.coarse_pitch >> 3;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nvec; e += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(e % vc);
+    const int tap = (int)((e / vc) & 3);
+    const long long tc = e / (4 * vc);
+    const int w = (int)(tc % Wc), h = (int)((tc / Wc) % Hc);
+    const long long b = tc / ((long long)Wc * Hc);
+    const long long tf = (b * a.H + 2 * h + (tap >> 1)) * a.W + 2 * w + (tap & 1);
+    dst[tc * cp + tap * vc + v] = __ldg(src + tf * fp + v);
+  }
+}
+
+__global__ void d2s_kernel(const kair_regroup_args a) {
+  const int Hc = a.H >> 1, Wc = a.W >> 1, vc = a.C >> 3;
+  const long long nvec = (long long)a.batch * a.H * a.W * vc;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nvec; e += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(e % vc);
+    const long long tf = e / vc;
+    const int w = (int)(tf % a.W), h = (int)((tf / a.W) % a.H);
+    const long long b = tf / ((long long)a.W * a.H);
+    const long long tc = (b * Hc + (h >> 1)) * Wc + (w >> 1);
+    const int tap = ((h & 1) << 1) | (w & 1);
+    const long long ci = tc * a.coarse_pitch + (long long)tap * a.C + v * 8;
+    float f[8];
+    if (a.coarse_in_f32) {
+      const float4 p = __ldg(reinterpret_cast<const float4*>(a.coarse_in_f32 + ci));
+      const float4 q = __ldg(reinterpret_cast<const float4*>(a.coarse_in_f32 + ci + 4));
+      f[0] = p.x; f[1] = p.y; f[2] = p.z; f[3] = p.w; f[4] = q.x; f[5] = q.y; f[6] = q.z; f[7] = q.w;
+    } else {
+      const uint4 p = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(a.coarse_in_bf16) + ci));
+      const uint32_t w4[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w4[i]));
+        f[2 * i] = f2.x;
+        f[2 * i + 1] = f2.y;
+      }
+    }
+    const long long fo = tf * a.fine_pitch + v * 8;
+    if (a.fine_out_f32) {
+      reinterpret_cast<float4*>(a.fine_out_f32 + fo)[0] = make_float4(f[0], f[1], f[2], f[3]);
+      reinterpret_cast<float4*>(a.fine_out_f32 + fo)[1] = make_float4(f[4], f[5], f[6], f[7]);
+    }
+    if (a.fine_out_bf16) {
+      uint4 o;
+      o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+      o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.fine_out_bf16) + fo) = o;
+    }
+  }
+}
+
+static int regroup_check(const kair_regroup_args& a, const char* who) {
+  KB_CHECK(a.batch > 0 && a.H > 0 && a.W > 0 && a.H % 2 == 0 && a.W % 2 == 0, "%s: H=%d, W=%d must be even", who, a.H, a.W);
+  KB_CHECK(a.C > 0 && a.C % 8 == 0 && a.fine_pitch % 8 == 0 && a.coarse_pitch % 8 == 0 && a.fine_pitch >= a.C &&
+               a.coarse_pitch >= 4 * a.C,
+           "%s: C=%d and the pitches must be multiples of 8 elements", who, a.C);
+  return 0;
+}
+
+int s2d_launch(const kair_regroup_args& a, cudaStream_t st) {
+  if (regroup_check(a, "kair_space_to_depth")) return -1;
+  KB_CHECK(a.fine_bf16 && a.coarse_bf16, "kair_space_to_depth: null pointer");
+  const long long nvec = (long long)a.batch * a.H * a.W * (a.C >> 3);
+  s2d_kernel<<<grid_for(nvec, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int d2s_launch(const kair_regroup_args& a, cudaStream_t st) {
+  if (regroup_check(a, "kair_depth_to_space")) return -1;
+  KB_CHECK((a.coarse_in_f32 != nullptr) != (a.coarse_in_bf16 != nullptr), "kair_depth_to_space: exactly one input");
+  KB_CHECK(a.fine_out_f32 || a.fine_out_bf16, "kair_depth_to_space: no output");
+  const long long nvec = (long long)a.batch * a.H * a.W * (a.C >> 3);
+  d2s_kernel<<<grid_for(nvec, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ column sums
+// Shared shape of the per-channel reductions below: a block of 256 threads covers `rows` token rows per iteration,
+// thread (r, g) owns channel group g (VEC channels) of row r; per-thread fp32 partials, then one shared-memory
+// reduction over r and one atomic per channel and block.
+struct ColGeom {
+  int groups, gp, rows;  // channel groups, groups rounded up to a power of two (<= 256), rows per iteration
+};
+static inline ColGeom col_geom(int C, int vec) {
+  ColGeom g;
+  g.groups = C / vec;
+  g.gp = 1;
+  while (g.gp < g.groups) g.gp <<= 1;
+  g.rows = 256 / g.gp;
+  return g;
+}
+
+template <int NV>
+__device__ __forceinline__ void block_reduce_cols(float (&v)[NV], float* sh, int r, int g, int gp, int rows) {
+  // sh: [NV][256]
+#pragma unroll
+  for (int i = 0; i < NV; ++i) sh[i * 256 + r * gp + g] = v[i];
+  __syncthreads();
+  if (r == 0) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      float s = 0.f;
+      for (int rr = 0; rr < rows; ++rr) s += sh[i * 256 + rr * gp + g];
+      v[i] = s;
+    }
+  }
+}
+
+__global__ void colsum_kernel(const kair_colsum_args a, int groups, int gp, int rows) {
+  __shared__ float sh[2 * 256];
+  const int g = threadIdx.x % gp, r = threadIdx.x / gp;
+  float acc[2] = {0.f, 0.f};
+  if (g < groups) {
+    for (long long t = (long long)blockIdx.x * rows + r; t < a.T; t += (long long)gridDim.x * rows) {
+      if (a.x_bf16) {
+        const float2 f = __bfloat1622float2(
+            *reinterpret_cast<const __nv_bfloat162*>(reinterpret_cast<const bf16*>(a.x_bf16) + t * a.pitch + 2 * g));
+        acc[0] += f.x;
+        acc[1] += f.y;
+      } else {
+        const float2 f = *reinterpret_cast<const float2*>(a.x_f32 + t * a.pitch + 2 * g);
+        acc[0] += f.x;
+        acc[1] += f.y;
+      }
+    }
+  }
+  block_reduce_cols<2>(acc, sh, r, g, gp, rows);
+  if (r == 0 && g < groups) {
+    atomicAdd(a.out + 2 * g, acc[0] * a.scale);
+    atomicAdd(a.out + 2 * g + 1, acc[1] * a.scale);
+  }
+}
+
+int colsum_launch(const kair_colsum_args& a, cudaStream_t st) {
+  KB_CHECK((a.x_bf16 != nullptr) != (a.x_f32 != nullptr) && a.out, "kair_colsum: exactly one input and an output");
+  KB_CHECK(a.C > 0 && a.C % 2 == 0 && a.C <= 512 && a.pitch >= a.C && a.pitch % 2 == 0 && a.T > 0, "kair_colsum: bad shape");
+  const ColGeom g = col_geom(a.C, 2);
+  colsum_kernel<<<grid_for(a.T, g.rows * 16, 4), 256, 0, st>>>(a, g.groups, g.gp, g.rows);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ BatchNorm
+__device__ __forceinline__ void ld_bf16x4(const void* base, long long idx, float (&f)[4]) {
+  const uint2 p = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(base) + idx);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&p.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&p.y));
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+__device__ __forceinline__ void st_bf16x4(void* base, long long idx, const float (&f)[4]) {
+  uint2 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(base) + idx) = o;
+}
+
+__device__ __forceinline__ void ld_dy4(const kair_bn_args& a, long long idx, float (&f)[4]) {
+  if (a.dy_f32) {
+    const float4 v = *reinterpret_cast<const float4*>(a.dy_f32 + idx);
+    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+  } else {
+    ld_bf16x4(a.dy, idx, f);
+  }
+}
+
+__global__ void bn_stats_kernel(const kair_bn_args a, int groups, int gp, int rows) {
+  __shared__ float sh[8 * 256];
+  const int g = threadIdx.x % gp, r = threadIdx.x / gp;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (g < groups) {
+    for (long long t = (long long)blockIdx.x * rows + r; t < a.T; t += (long long)gridDim.x * rows) {
+      const float4 z = *reinterpret_cast<const float4*>(a.z + t * a.pitch + 4 * g);
+      acc[0] += z.x; acc[1] += z.y; acc[2] += z.z; acc[3] += z.w;
+      acc[4] += z.x * z.x; acc[5] += z.y * z.y; acc[6] += z.z * z.z; acc[7] += z.w * z.w;
+    }
+  }
+  block_reduce_cols<8>(acc, sh, r, g, gp, rows);
+  if (r == 0 && g < groups) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      atomicAdd(a.acc + 4 * g + i, (double)acc[i]);
+      atomicAdd(a.acc + a.C + 4 * g + i, (double)acc[4 + i]);
+    }
+  }
+}
+
+__global__ void bn_finalize_kernel(const kair_bn_args a) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < a.C) {
+    const double n = (double)a.T;
+    const double mean = a.acc[c] / n;
+    double var = a.acc[a.C + c] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    a.mean[c] = (float)mean;
+    a.rstd[c] = (float)(1.0 / sqrt(var + (double)a.eps));
+    if (a.running_mean) a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * (float)mean;
+    if (a.running_var) {
+      const double unbiased = var * n / (n > 1.0 ? n - 1.0 : 1.0);
+      a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (float)unbiased;
+    }
+    a.acc[c] = 0.0;
+    a.acc[a.C + c] = 0.0;
+  }
+  if (c == 0 && a.num_batches_tracked) *a.num_batches_tracked += 1;
+}
+
+__global__ void bn_apply_kernel(const kair_bn_args a) {
+  const int groups = a.C >> 2;
+  const long long n = a.T * groups;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(e % groups);
+    const long long t = e / groups;
+    const float4 z = *reinterpret_cast<const float4*>(a.z + t * a.pitch + 4 * g);
+    const float zz[4] = {z.x, z.y, z.z, z.w};
+    float y[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = 4 * g + i;
+      const float sc = __ldg(a.gamma + c) * __ldg(a.rstd + c);
+      float v = (zz[i] - __ldg(a.mean + c)) * sc + __ldg(a.beta + c);
+      if (a.act == KAIR_ACT_LRELU) v = v > 0.f ? v : v * a.act_slope;
+      y[i] = v;
+    }
+    if (a.out_bf16) st_bf16x4(a.out_bf16, t * a.pitch + 4 * g, y);
+    if (a.out_f32) *reinterpret_cast<float4*>(a.out_f32 + t * a.pitch + 4 * g) = make_float4(y[0], y[1], y[2], y[3]);
+  }
+}
+
+__global__ void bn_bwd_reduce_kernel(const kair_bn_args a, int groups, int gp, int rows) {
+  __shared__ float sh[8 * 256];
+  const int g = threadIdx.x % gp, r = threadIdx.x / gp;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (g < groups) {
+    float mu[4], rs[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      mu[i] = a.mean[4 * g + i];
+      rs[i] = a.rstd[4 * g + i];
+    }
+    for (long long t = (long long)blockIdx.x * rows + r; t < a.T; t += (long long)gridDim.x * rows) {
+      const long long idx = t * a.pitch + 4 * g;
+      const float4 z = *reinterpret_cast<const float4*>(a.z + idx);
+      const float zz[4] = {z.x, z.y, z.z, z.w};
+      float dy[4], y[4];
+      ld_dy4(a, idx, dy);
+      if (a.act == KAIR_ACT_LRELU) ld_bf16x4(a.y, idx, y);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float gq = dy[i];
+        if (a.act == KAIR_ACT_LRELU && !(y[i] > 0.f)) gq *= a.act_slope;
+        acc[i] += gq;
+        acc[4 + i] += gq * (zz[i] - mu[i]) * rs[i];
+      }
+    }
+  }
+  block_reduce_cols<8>(acc, sh, r, g, gp, rows);
+  if (r == 0 && g < groups) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      atomicAdd(a.dbeta + 4 * g + i, acc[i]);
+      atomicAdd(a.dgamma + 4 * g + i, acc[4 + i]);
+    }
+  }
+}
+
+__global__ void bn_bwd_apply_kernel(const kair_bn_args a, int groups, int gp, int rows) {
+  __shared__ float sh[4 * 256];
+  const int g = threadIdx.x % gp, r = threadIdx.x / gp;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  if (g < groups) {
+    const float inv_n = 1.0f / (float)a.T;
+    float mu[4], rs[4], k0[4], k1[4], k2[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = 4 * g + i;
+      mu[i] = a.mean[c];
+      rs[i] = a.rstd[c];
+      k0[i] = a.gamma[c] * rs[i];
+      k1[i] = a.dbeta[c] * inv_n;
+      k2[i] = a.dgamma[c] * inv_n;
+    }
+    for (long long t = (long long)blockIdx.x * rows + r; t < a.T; t += (long long)gridDim.x * rows) {
+      const long long idx = t * a.pitch + 4 * g;
+      const float4 z = *reinterpret_cast<const float4*>(a.z + idx);
+      const float zz[4] = {z.x, z.y, z.z, z.w};
+      float dy[4], y[4], dz[4];
+      ld_dy4(a, idx, dy);
+      if (a.act == KAIR_ACT_LRELU) ld_bf16x4(a.y, idx, y);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float gq = dy[i];
+        if (a.act == KAIR_ACT_LRELU && !(y[i] > 0.f)) gq *= a.act_slope;
+        dz[i] = k0[i] * (gq - k1[i] - (zz[i] - mu[i]) * rs[i] * k2[i]);
+        acc[i] += dz[i];
+      }
+      st_bf16x4(a.out_bf16, idx, dz);
+    }
+  }
+  if (a.dbias) {
+    block_reduce_cols<4>(acc, sh, r, g, gp, rows);
+    if (r == 0 && g < groups) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) atomicAdd(a.dbias + 4 * g + i, acc[i]);
+    }
+  }
+}
+
+__global__ void bn_fold_kernel(const kair_bn_args a) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < a.C) {
+    const float sc = a.gamma[c] * rsqrtf(a.running_var[c] + a.eps);
+    a.scale[c] = sc;
+    a.shift[c] = a.beta[c] - a.running_mean[c] * sc;
+  }
+}
+
+static int bn_check(const kair_bn_args& a, const char* who) {
+  KB_CHECK(a.C > 0 && a.C % 4 == 0 && a.C <= 512, "%s: C=%d must be a multiple of 4, <= 512", who, a.C);
+  return 0;
+}
+static int bn_check_rows(const kair_bn_args& a, const char* who) {
+  if (bn_check(a, who)) return -1;
+  KB_CHECK(a.T > 0 && a.pitch >= a.C && a.pitch % 4 == 0 && a.z, "%s: bad token matrix", who);
+  return 0;
+}
+
+int bn_stats_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check_rows(a, "kair_bn_stats")) return -1;
+  KB_CHECK(a.acc, "kair_bn_stats: null accumulator");
+  const ColGeom g = col_geom(a.C, 4);
+  bn_stats_kernel<<<grid_for(a.T, g.rows * 8, 4), 256, 0, st>>>(a, g.groups, g.gp, g.rows);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int bn_finalize_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check(a, "kair_bn_finalize")) return -1;
+  KB_CHECK(a.acc && a.mean && a.rstd && a.T > 0, "kair_bn_finalize: null pointer");
+  bn_finalize_kernel<<<(a.C + 127) / 128, 128, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int bn_apply_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check_rows(a, "kair_bn_apply")) return -1;
+  KB_CHECK(a.mean && a.rstd && a.gamma && a.beta && (a.out_bf16 || a.out_f32), "kair_bn_apply: null pointer");
+  bn_apply_kernel<<<grid_for(a.T * (a.C >> 2), 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int bn_bwd_reduce_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check_rows(a, "kair_bn_bwd_reduce")) return -1;
+  KB_CHECK((a.dy || a.dy_f32) && a.mean && a.rstd && a.dgamma && a.dbeta && (a.act == KAIR_ACT_NONE || a.y),
+           "kair_bn_bwd_reduce: null pointer");
+  const ColGeom g = col_geom(a.C, 4);
+  bn_bwd_reduce_kernel<<<grid_for(a.T, g.rows * 8, 4), 256, 0, st>>>(a, g.groups, g.gp, g.rows);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int bn_bwd_apply_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check_rows(a, "kair_bn_bwd_apply")) return -1;
+  KB_CHECK((a.dy || a.dy_f32) && a.mean && a.rstd && a.gamma && a.dgamma && a.dbeta && a.out_bf16 &&
+               (a.act == KAIR_ACT_NONE || a.y),
+           "kair_bn_bwd_apply: null pointer");
+  const ColGeom g = col_geom(a.C, 4);
+  bn_bwd_apply_kernel<<<grid_for(a.T, g.rows * 8, 4), 256, 0, st>>>(a, g.groups, g.gp, g.rows);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int bn_fold_launch(const kair_bn_args& a, cudaStream_t st) {
+  if (bn_check(a, "kair_bn_fold")) return -1;
+  KB_CHECK(a.gamma && a.beta && a.running_mean && a.running_var && a.scale && a.shift, "kair_bn_fold: null pointer");
+  bn_fold_kernel<<<(a.C + 127) / 128, 128, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ SR heads
+// PixelShuffle(r): out[(b, r*h+dy, r*w+dx)][c] = in[(b,h,w)][c*r*r + dy*r + dx]; one thread per output channel pair.
+__global__ void pixel_shuffle_kernel(const kair_shuffle_args a) {
+  const int r = a.r, Ho = a.H * r, Wo = a.W * r, rr = r * r;
+  const bf16* in = reinterpret_cast<const bf16*>(a.in);
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  const int pc = a.C >> 1;
+  const long long n = (long long)a.batch * Ho * Wo * pc;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(e % pc) * 2;
+    const long long to = e / pc;
+    const int wo = (int)(to % Wo), ho = (int)((to / Wo) % Ho);
+    const long long b = to / ((long long)Wo * Ho);
+    const long long ti = (b * a.H + ho / r) * a.W + wo / r;
+    const int sub = (ho % r) * r + (wo % r);
+    __nv_bfloat162 v;
+    v.x = in[ti * a.in_pitch + (long long)c * rr + sub];
+    v.y = in[ti * a.in_pitch + (long long)(c + 1) * rr + sub];
+    *reinterpret_cast<__nv_bfloat162*>(out + to * a.out_pitch + c) = v;
+  }
+}
+
+__global__ void upsample_nearest2_kernel(const kair_shuffle_args a) {
+  const int Ho = a.H * 2, Wo = a.W * 2, vc = a.C >> 3;
+  const uint4* in = reinterpret_cast<const uint4*>(a.in);
+  uint4* out = reinterpret_cast<uint4*>(a.out);
+  const long long ip = a.in_pitch >> 3, op = a.out_pitch >> 3;
+  const long long n = (long long)a.batch * Ho * Wo * vc;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(e % vc);
+    const long long to = e / vc;
+    const int wo = (int)(to % Wo), ho = (int)((to / Wo) % Ho);
+    const long long b = to / ((long long)Wo * Ho);
+    const long long ti = (b * a.H + (ho >> 1)) * a.W + (wo >> 1);
+    out[to * op + v] = __ldg(in + ti * ip + v);
+  }
+}
+
+int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle: null pointer / empty");
+  KB_CHECK(a.r >= 2 && a.r <= 4 && a.C % 2 == 0 && a.out_pitch % 2 == 0 && a.in_pitch >= (long long)a.C * a.r * a.r &&
+               a.out_pitch >= a.C,
+           "kair_pixel_shuffle: bad geometry (r=%d, C=%d)", a.r, a.C);
+  const long long n = (long long)a.batch * a.H * a.W * a.r * a.r * (a.C >> 1);
+  pixel_shuffle_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_upsample_nearest2: null pointer / empty");
+  KB_CHECK(a.C % 8 == 0 && a.in_pitch % 8 == 0 && a.out_pitch % 8 == 0 && a.in_pitch >= a.C && a.out_pitch >= a.C,
+           "kair_upsample_nearest2: C and pitches must be multiples of 8");
+  const long long n = (long long)a.batch * a.H * a.W * 4 * (a.C >> 3);
+  upsample_nearest2_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace kb

@@ -137,18 +137,24 @@ __global__ void pack_conv_kernel(const kair_pack_conv_args a) {
   const size_t n = (size_t)a.O_pad * taps * a.I_pad;
   bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + (size_t)l * n;
   bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * n : nullptr;
+  const float* osc = a.oscale ? reinterpret_cast<const float*>(a.oscale[l]) : nullptr;
+  const float* osh = a.oshift ? reinterpret_cast<const float*>(a.oshift[l]) : nullptr;
   for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
     const int i = (int)(e % a.I_pad);
     const int tap = (int)((e / a.I_pad) % taps);
     const int o = (int)(e / ((size_t)a.I_pad * taps));
     float v = 0.f;
-    if (o < a.O && i < a.I) v = W[((size_t)o * a.I + i) * taps + tap];
+    if (o < a.O && i < a.I) v = W[((size_t)o * a.I + i) * taps + tap] * (osc ? osc[o] : 1.f);
     Wp[e] = __float2bfloat16(v);
     if (WpT) WpT[((size_t)i * taps + (taps - 1 - tap)) * a.O_pad + o] = __float2bfloat16(v);
   }
   if (a.bp && blockIdx.x == 0) {
     const float* b = a.b ? reinterpret_cast<const float*>(a.b[l]) : nullptr;
-    for (int o = threadIdx.x; o < a.O_pad; o += blockDim.x) a.bp[(size_t)l * a.O_pad + o] = (b && o < a.O) ? b[o] : 0.f;
+    for (int o = threadIdx.x; o < a.O_pad; o += blockDim.x) {
+      float v = (b && o < a.O) ? b[o] : 0.f;
+      if (o < a.O) v = v * (osc ? osc[o] : 1.f) + (osh ? osh[o] : 0.f);
+      a.bp[(size_t)l * a.O_pad + o] = v;
+    }
   }
 }
 
@@ -562,6 +568,7 @@ __global__ void conv_out_dgrad_kernel(const kair_conv_out_args a) {
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) acc += g[c * 9 + tap] * sw[(c * 9 + tap) * Cp + k];
         }
+        if (a.mask && !(__bfloat162float(reinterpret_cast<const bf16*>(a.mask)[t * Cp + k]) > 0.f)) acc *= a.mask_slope;
       }
       if (a.dfeat_f32) a.dfeat_f32[t * Cp + k] = acc;
       if (a.dfeat_bf16) reinterpret_cast<bf16*>(a.dfeat_bf16)[t * Cp + k] = __float2bfloat16(acc);

@@ -281,7 +281,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     const float inv_n = 1.0f / (float)p.n_valid;
     const int col_half = n_tile * BN + hf * HALF;
     const bool use_r = p.resid != nullptr && (EPI == KAIR_EPI_LINEAR || EPI == KAIR_EPI_RESID_LN || EPI == KAIR_EPI_LNBWD);
-    const bool use_a = (EPI == KAIR_EPI_DGELU || EPI == KAIR_EPI_LNBWD);
+    // LINEAR with aux: activation backward, v *= (aux > 0 ? 1 : act_slope) with aux = the saved activation output
+    const bool use_a = (EPI == KAIR_EPI_DGELU || EPI == KAIR_EPI_LNBWD || (EPI == KAIR_EPI_LINEAR && p.aux != nullptr));
     const bool has_ld = use_r || use_a;
     // The warp's 12 KiB of staging memory is a ring of ringD buffers of ringS bytes; slot k uses buffer k % ringD and
     // its operands are TMA-prefetched ringDist slots ahead.
@@ -424,8 +425,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         for (int c = 0; c < NCH; ++c) {
           const int col = col_half + c * 32;
           const bool last = (c == NCH - 1);
-          uint8_t* buf = slot_begin(!last || more_tiles, use_r, false, last ? t_next : t, last ? col_half : col + 32,
-                                    use_r);
+          uint8_t* buf = slot_begin(!last || more_tiles, use_r, use_a, last ? t_next : t, last ? col_half : col + 32,
+                                    use_r || use_a);
           float v[32];
           if (p.dbg & 1) {
 #pragma unroll
@@ -437,6 +438,12 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           if (p.acc_scale) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= sa;
+          }
+          if (use_a) {
+            float u[32];
+            read_row_bf16(u, buf + boff);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = u[i] > 0.f ? v[i] : v[i] * p.act_slope;
           }
           if (use_r) add_row_f32(v, buf);
           if (p.act == KAIR_ACT_LRELU) {
@@ -736,6 +743,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
     KB_CHECK(a.N == a.bn, "kair_gemm_tn: LayerNorm epilogues need the whole row in one tile (N == bn)");
   if (a.mode == KAIR_EPI_LNBWD || a.mode == KAIR_EPI_DGELU) KB_CHECK(a.aux != nullptr, "kair_gemm_tn: aux required");
   if (a.mode == KAIR_EPI_LNBWD) KB_CHECK(a.rowstat != nullptr, "kair_gemm_tn: rowstat required");
+  if (a.mode == KAIR_EPI_LINEAR && a.aux) KB_CHECK(a.act == KAIR_ACT_NONE, "kair_gemm_tn: aux (activation backward) excludes act");
   if (a.acc_scale || a.outB_scale) KB_CHECK(a.tokens_per_sample > 0, "kair_gemm_tn: tokens_per_sample required");
   if (check_device() != 0) return -3;
 
@@ -832,10 +840,11 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   // staging ring per epilogue warp (see the kernel's epilogue comment)
   const bool loads_r = a.resid && (a.mode == KAIR_EPI_LINEAR || a.mode == KAIR_EPI_RESID_LN || a.mode == KAIR_EPI_LNBWD);
   p.stg_warp = 12288; p.ringD = 2; p.ringS = 6144;
-  p.ringDist = (loads_r || a.mode == KAIR_EPI_DGELU || a.mode == KAIR_EPI_LNBWD) ? 1 : 0;
+  const bool lin_aux = a.mode == KAIR_EPI_LINEAR && a.aux != nullptr;
+  p.ringDist = (loads_r || lin_aux || a.mode == KAIR_EPI_DGELU || a.mode == KAIR_EPI_LNBWD) ? 1 : 0;
   if (a.mode == KAIR_EPI_GELU) { p.stg_warp = 8192; p.ringD = 2; p.ringS = 4096; p.ringDist = 0; }
   if (a.mode == KAIR_EPI_DGELU) { p.stg_warp = 8192; p.ringD = 4; p.ringS = 2048; p.ringDist = 2; }
-  if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
+  if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF && !lin_aux) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
   const int stg_bytes = 8 * p.stg_warp;
   const int budget = 232448 - 1024 - stg_bytes - TN_MISC_BYTES;
   bool bres = false;

@@ -211,11 +211,13 @@ def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map
     return Launch("kair_unpack_linear_grad", a, keep)
 
 
-def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
-    """Pack L same-shaped conv weights (O,I,kh,kw) into Wp [L,O_pad,taps*I_pad] (+ flipped WpT [L,I_pad,taps*O_pad])."""
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None):
+    """Pack L same-shaped conv weights (O,I,kh,kw) into Wp [L,O_pad,taps*I_pad] (+ flipped WpT [L,I_pad,taps*O_pad]).
+    oscale / oshift: optional per-layer (O,) fp32 tensors folded in (Wp = W*oscale[o], bp = b*oscale[o] + oshift[o])."""
     keep = []
     a = _S["kair_pack_conv_args"]()
     a.W = _plist(W, Wp, keep); a.b = _plist(b, Wp, keep)
+    a.oscale = _plist(oscale, Wp, keep); a.oshift = _plist(oshift, Wp, keep)
     a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
     a.L, a.O_pad = Wp.shape[0], Wp.shape[1]
     a.O, a.I, a.I_pad, a.taps = O, I, I_pad, taps
@@ -301,10 +303,12 @@ def build_conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, sk
     return Launch("kair_conv_out_fwd", a)
 
 
-def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
-    _req(dout, torch.float32, "dout")
+def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None, mask=None,
+                         mask_slope=0.0):
+    _req(dout, torch.float32, "dout"); _req(mask, torch.bfloat16, "mask")
     a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
     a.dout = _ptr(dout); a.dfeat_f32 = _ptr(dfeat_f32); a.dfeat_bf16 = _ptr(dfeat_bf16)
+    a.mask = _ptr(mask); a.mask_slope = mask_slope
     return Launch("kair_conv_out_dgrad", a)
 
 
@@ -344,6 +348,146 @@ def build_add_inplace(y, x, yb=None):
     fn = _lib.load().kair_add_inplace
     py, px, pyb, n = _ptr(y), _ptr(x), _ptr(yb), y.numel()
     return _RawLaunch("kair_add_inplace", lambda stream: fn(py, px, pyb, n, stream), keep=(y, x, yb))
+
+
+# ------------------------------------------------------------------------------------------------ conv-net helpers
+
+def _regroup_args(batch, H, W, C, fine_pitch, coarse_pitch):
+    a = _S["kair_regroup_args"]()
+    a.batch, a.H, a.W, a.C = batch, H, W, C
+    a.fine_pitch, a.coarse_pitch = fine_pitch, coarse_pitch
+    return a
+
+
+def build_space_to_depth(fine, coarse, *, batch, H, W, C):
+    """coarse[(b,h,w)][tap*C + c] = fine[(b,2h+dy,2w+dx)][c], tap = dy*2+dx; (H, W) is the fine resolution."""
+    _req(fine, torch.bfloat16, "fine"); _req(coarse, torch.bfloat16, "coarse")
+    a = _regroup_args(batch, H, W, C, _pitch(fine), _pitch(coarse))
+    a.fine_bf16 = _ptr(fine); a.coarse_bf16 = _ptr(coarse)
+    return Launch("kair_space_to_depth", a)
+
+
+def build_depth_to_space(coarse, *, batch, H, W, C, out_f32=None, out_bf16=None):
+    """inverse regrouping; coarse is fp32 or bf16 [T/4, >=4C], outputs fp32 and/or bf16 [T, >=C]."""
+    if coarse.dtype not in (torch.float32, torch.bfloat16):
+        raise RuntimeError("kair_b200: depth_to_space input must be fp32 or bf16")
+    _req(coarse, coarse.dtype, "coarse"); _req(out_f32, torch.float32, "out_f32"); _req(out_bf16, torch.bfloat16, "out_bf16")
+    ref = out_f32 if out_f32 is not None else out_bf16
+    a = _regroup_args(batch, H, W, C, _pitch(ref), _pitch(coarse))
+    if out_f32 is not None and out_bf16 is not None and _pitch(out_f32) != _pitch(out_bf16):
+        raise RuntimeError("kair_b200: depth_to_space outputs must share one pitch")
+    if coarse.dtype == torch.float32:
+        a.coarse_in_f32 = _ptr(coarse)
+    else:
+        a.coarse_in_bf16 = _ptr(coarse)
+    a.fine_out_f32 = _ptr(out_f32); a.fine_out_bf16 = _ptr(out_bf16)
+    return Launch("kair_depth_to_space", a)
+
+
+def build_colsum(x, out, *, C, scale=1.0):
+    """out[c] += scale * sum_t x[t, c]; x fp32 or bf16 [T, >=C], out fp32 (caller zeroes)."""
+    _req(out, torch.float32, "out")
+    a = _S["kair_colsum_args"]()
+    if x.dtype == torch.bfloat16:
+        a.x_bf16 = _ptr(x)
+    elif x.dtype == torch.float32:
+        a.x_f32 = _ptr(x)
+    else:
+        raise RuntimeError("kair_b200: colsum input must be fp32 or bf16")
+    _req(x, x.dtype, "x")
+    a.out = _ptr(out); a.T = x.shape[0]; a.pitch = _pitch(x); a.C = C; a.scale = scale
+    return Launch("kair_colsum", a)
+
+
+def _bn_args(C, T, pitch, eps, momentum, act, act_slope):
+    a = _S["kair_bn_args"]()
+    a.C, a.T, a.pitch, a.eps, a.momentum, a.act, a.act_slope = C, T, pitch, eps, momentum, act, act_slope
+    return a
+
+
+def _set_dy(a, dy):
+    """dy of the BatchNorm backward kernels: bf16 or fp32 [T, pitch] with the pitch of z"""
+    if dy.dtype == torch.float32:
+        a.dy_f32 = _ptr(dy)
+    elif dy.dtype == torch.bfloat16:
+        a.dy = _ptr(dy)
+    else:
+        raise RuntimeError("kair_b200: BatchNorm dy must be fp32 or bf16")
+    if _pitch(dy) != a.pitch:
+        raise RuntimeError("kair_b200: BatchNorm dy must share the pitch of z")
+
+
+def build_bn_stats(z, acc, *, C):
+    _req(z, torch.float32, "z"); _req(acc, torch.float64, "acc")
+    a = _bn_args(C, z.shape[0], _pitch(z), 0.0, 0.0, 0, 0.0)
+    a.z = _ptr(z); a.acc = _ptr(acc)
+    return Launch("kair_bn_stats", a)
+
+
+def build_bn_finalize(acc, mean, rstd, running_mean, running_var, num_batches_tracked, *, C, T, eps, momentum):
+    _req(acc, torch.float64, "acc"); _req(mean, torch.float32, "mean"); _req(rstd, torch.float32, "rstd")
+    _req(running_mean, torch.float32, "running_mean"); _req(running_var, torch.float32, "running_var")
+    _req(num_batches_tracked, torch.int64, "num_batches_tracked")
+    a = _bn_args(C, T, C, eps, momentum, 0, 0.0)
+    a.acc = _ptr(acc); a.mean = _ptr(mean); a.rstd = _ptr(rstd)
+    a.running_mean = _ptr(running_mean); a.running_var = _ptr(running_var)
+    a.num_batches_tracked = _ptr(num_batches_tracked)
+    return Launch("kair_bn_finalize", a)
+
+
+def build_bn_apply(z, mean, rstd, gamma, beta, *, C, act=ACT_NONE, act_slope=0.0, out_bf16=None, out_f32=None):
+    _req(z, torch.float32, "z"); _req(out_bf16, torch.bfloat16, "out_bf16"); _req(out_f32, torch.float32, "out_f32")
+    a = _bn_args(C, z.shape[0], _pitch(z), 0.0, 0.0, act, act_slope)
+    a.z = _ptr(z); a.mean = _ptr(mean); a.rstd = _ptr(rstd); a.gamma = _ptr(gamma); a.beta = _ptr(beta)
+    a.out_bf16 = _ptr(out_bf16); a.out_f32 = _ptr(out_f32)
+    return Launch("kair_bn_apply", a)
+
+
+def build_bn_bwd_reduce(z, y, dy, mean, rstd, dgamma, dbeta, *, C, act=ACT_NONE, act_slope=0.0):
+    _req(z, torch.float32, "z"); _req(y, torch.bfloat16, "y"); _req(dy, dy.dtype, "dy")
+    _req(dgamma, torch.float32, "dgamma"); _req(dbeta, torch.float32, "dbeta")
+    a = _bn_args(C, z.shape[0], _pitch(z), 0.0, 0.0, act, act_slope)
+    a.z = _ptr(z); a.y = _ptr(y); _set_dy(a, dy); a.mean = _ptr(mean); a.rstd = _ptr(rstd)
+    a.dgamma = _ptr(dgamma); a.dbeta = _ptr(dbeta)
+    return Launch("kair_bn_bwd_reduce", a)
+
+
+def build_bn_bwd_apply(z, y, dy, mean, rstd, gamma, dgamma, dbeta, dz, *, C, act=ACT_NONE, act_slope=0.0, dbias=None):
+    _req(z, torch.float32, "z"); _req(y, torch.bfloat16, "y"); _req(dy, dy.dtype, "dy")
+    _req(dz, torch.bfloat16, "dz"); _req(dbias, torch.float32, "dbias")
+    a = _bn_args(C, z.shape[0], _pitch(z), 0.0, 0.0, act, act_slope)
+    a.z = _ptr(z); a.y = _ptr(y); _set_dy(a, dy); a.mean = _ptr(mean); a.rstd = _ptr(rstd); a.gamma = _ptr(gamma)
+    a.dgamma = _ptr(dgamma); a.dbeta = _ptr(dbeta); a.out_bf16 = _ptr(dz); a.dbias = _ptr(dbias)
+    return Launch("kair_bn_bwd_apply", a)
+
+
+def build_bn_fold(gamma, beta, running_mean, running_var, scale, shift, *, C, eps):
+    for t, n in ((gamma, "gamma"), (beta, "beta"), (running_mean, "running_mean"), (running_var, "running_var"),
+                 (scale, "scale"), (shift, "shift")):
+        _req(t, torch.float32, n)
+    a = _bn_args(C, 1, C, eps, 0.0, 0, 0.0)
+    a.gamma = _ptr(gamma); a.beta = _ptr(beta); a.running_mean = _ptr(running_mean); a.running_var = _ptr(running_var)
+    a.scale = _ptr(scale); a.shift = _ptr(shift)
+    return Launch("kair_bn_fold", a)
+
+
+def _shuffle_args(x, out, batch, H, W, C, r):
+    _req(x, torch.bfloat16, "in"); _req(out, torch.bfloat16, "out")
+    a = _S["kair_shuffle_args"]()
+    setattr(a, "in", _ptr(x)); a.out = _ptr(out)
+    a.in_pitch, a.out_pitch = _pitch(x), _pitch(out)
+    a.batch, a.H, a.W, a.C, a.r = batch, H, W, C, r
+    return a
+
+
+def build_pixel_shuffle(x, out, *, batch, H, W, C, r):
+    """nn.PixelShuffle(r) on token features: x [B*H*W, >= r*r*C] -> out [B*rH*rW, >= C] (bf16)."""
+    return Launch("kair_pixel_shuffle", _shuffle_args(x, out, batch, H, W, C, r))
+
+
+def build_upsample_nearest2(x, out, *, batch, H, W, C):
+    """nearest-neighbour x2 of token features: x [B*H*W, >= C] -> out [B*2H*2W, >= C] (bf16)."""
+    return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2))
 
 
 # ------------------------------------------------------------------------------------------------ lifetimes

@@ -81,6 +81,9 @@ def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.
             v = acc + (bias[:N] if bias is not None else 0.0)
             if acc_scale is not None:
                 v = v * per_sample(acc_scale)
+            if aux is not None:
+                assert act == ACT_NONE
+                v = torch.where(flat(aux, N).float() > 0, v, v * act_slope)
             if resid is not None:
                 v = v + flat(resid, N)
             if act == ACT_LRELU:
@@ -280,11 +283,13 @@ def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map
     return EmuLaunch("kair_unpack_linear_grad", run)
 
 
-def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None):
     def run():
         L, O_pad = Wp.shape[0], Wp.shape[1]
         for l in range(L):
             w = W[l].detach().reshape(O, I, taps)
+            if oscale is not None:
+                w = w * oscale[l].view(O, 1, 1)
             full = torch.zeros(O_pad, taps, I_pad)
             full[:O, :, :I] = w.permute(0, 2, 1)
             Wp[l].copy_(_bf(full.reshape(O_pad, taps * I_pad)))
@@ -296,6 +301,10 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9):
                 bias = torch.zeros(O_pad)
                 if b is not None:
                     bias[:O] = b[l].detach()
+                if oscale is not None:
+                    bias[:O] = bias[:O] * oscale[l]
+                if oshift is not None:
+                    bias[:O] = bias[:O] + oshift[l]
                 bp[l].copy_(bias)
 
     return EmuLaunch("kair_pack_conv", run)
@@ -429,12 +438,15 @@ def build_conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, sk
     return EmuLaunch("kair_conv_out_fwd", run)
 
 
-def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None):
+def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, dfeat_bf16=None, mask=None,
+                         mask_slope=0.0):
     def run():
         Bn, co, H, Wd = dout.shape
         dx = torch.nn.grad.conv2d_input((Bn, C, H, Wd), W.detach(), dout * out_scale, padding=1)
         full = torch.zeros(Bn * H * Wd, pitch)
         full[:, :C] = dx.permute(0, 2, 3, 1).reshape(-1, C)
+        if mask is not None:
+            full = torch.where(mask.reshape(-1, pitch).float() > 0, full, full * mask_slope)
         if dfeat_f32 is not None:
             dfeat_f32.copy_(full)
         if dfeat_bf16 is not None:
@@ -492,3 +504,127 @@ def build_add_inplace(y, x, yb=None):
             yb.copy_(_bf(y))
 
     return EmuLaunch("kair_add_inplace", run)
+
+
+# ------------------------------------------------------------------------------------------------ conv-net helpers
+
+def build_space_to_depth(fine, coarse, *, batch, H, W, C):
+    def run():
+        x = fine.reshape(batch, H // 2, 2, W // 2, 2, -1)[..., :C]
+        coarse.reshape(batch * (H // 2) * (W // 2), -1)[:, :4 * C].copy_(
+            x.permute(0, 1, 3, 2, 4, 5).reshape(-1, 4 * C))
+
+    return EmuLaunch("kair_space_to_depth", run)
+
+
+def build_depth_to_space(coarse, *, batch, H, W, C, out_f32=None, out_bf16=None):
+    def run():
+        x = coarse.reshape(batch, H // 2, W // 2, -1)[..., :4 * C].float().reshape(batch, H // 2, W // 2, 2, 2, C)
+        y = x.permute(0, 1, 3, 2, 4, 5).reshape(batch * H * W, C)
+        if out_f32 is not None:
+            out_f32.reshape(batch * H * W, -1)[:, :C].copy_(y)
+        if out_bf16 is not None:
+            out_bf16.reshape(batch * H * W, -1)[:, :C].copy_(_bf(y))
+
+    return EmuLaunch("kair_depth_to_space", run)
+
+
+def build_colsum(x, out, *, C, scale=1.0):
+    def run():
+        out[:C].add_(scale * x[:, :C].float().sum(0))
+
+    return EmuLaunch("kair_colsum", run)
+
+
+def build_bn_stats(z, acc, *, C):
+    def run():
+        acc[0, :C] += z[:, :C].double().sum(0)
+        acc[1, :C] += (z[:, :C].double() ** 2).sum(0)
+
+    return EmuLaunch("kair_bn_stats", run)
+
+
+def build_bn_finalize(acc, mean, rstd, running_mean, running_var, num_batches_tracked, *, C, T, eps, momentum):
+    def run():
+        m = acc[0, :C] / T
+        var = (acc[1, :C] / T - m * m).clamp_min(0)
+        mean[:C].copy_(m.float())
+        rstd[:C].copy_((1.0 / torch.sqrt(var + eps)).float())
+        with torch.no_grad():
+            if running_mean is not None:
+                running_mean.mul_(1 - momentum).add_(momentum * m.float())
+            if running_var is not None:
+                running_var.mul_(1 - momentum).add_(momentum * (var * T / max(T - 1, 1)).float())
+            if num_batches_tracked is not None:
+                num_batches_tracked.add_(1)
+        acc.zero_()
+
+    return EmuLaunch("kair_bn_finalize", run)
+
+
+def _act_mask(y, act, slope):
+    if act != ACT_LRELU:
+        return 1.0
+    return torch.where(y.float() > 0, torch.ones(()), torch.full((), float(slope)))
+
+
+def build_bn_apply(z, mean, rstd, gamma, beta, *, C, act=ACT_NONE, act_slope=0.0, out_bf16=None, out_f32=None):
+    def run():
+        v = (z[:, :C] - mean[:C]) * (gamma.detach() * rstd[:C]) + beta.detach()
+        if act == ACT_LRELU:
+            v = torch.where(v > 0, v, v * act_slope)
+        if out_bf16 is not None:
+            out_bf16[:, :C].copy_(_bf(v))
+        if out_f32 is not None:
+            out_f32[:, :C].copy_(v)
+
+    return EmuLaunch("kair_bn_apply", run)
+
+
+def build_bn_bwd_reduce(z, y, dy, mean, rstd, dgamma, dbeta, *, C, act=ACT_NONE, act_slope=0.0):
+    def run():
+        g = dy[:, :C].float() * _act_mask(y[:, :C], act, act_slope)
+        xh = (z[:, :C] - mean[:C]) * rstd[:C]
+        dbeta.add_(g.sum(0))
+        dgamma.add_((g * xh).sum(0))
+
+    return EmuLaunch("kair_bn_bwd_reduce", run)
+
+
+def build_bn_bwd_apply(z, y, dy, mean, rstd, gamma, dgamma, dbeta, dz, *, C, act=ACT_NONE, act_slope=0.0, dbias=None):
+    def run():
+        T = z.shape[0]
+        g = dy[:, :C].float() * _act_mask(y[:, :C], act, act_slope)
+        xh = (z[:, :C] - mean[:C]) * rstd[:C]
+        d = gamma.detach() * rstd[:C] * (g - dbeta / T - xh * dgamma / T)
+        dz[:, :C].copy_(_bf(d))
+        if dbias is not None:
+            dbias.add_(d.sum(0))
+
+    return EmuLaunch("kair_bn_bwd_apply", run)
+
+
+def build_bn_fold(gamma, beta, running_mean, running_var, scale, shift, *, C, eps):
+    def run():
+        sc = gamma.detach() * torch.rsqrt(running_var + eps)
+        scale.copy_(sc)
+        shift.copy_(beta.detach() - running_mean * sc)
+
+    return EmuLaunch("kair_bn_fold", run)
+
+
+def build_pixel_shuffle(x, out, *, batch, H, W, C, r):
+    def run():
+        v = x.reshape(batch, H, W, -1)[..., :C * r * r].reshape(batch, H, W, C, r, r)
+        y = v.permute(0, 1, 4, 2, 5, 3).reshape(batch * H * r * W * r, C)
+        out.reshape(batch * H * r * W * r, -1)[:, :C].copy_(y)
+
+    return EmuLaunch("kair_pixel_shuffle", run)
+
+
+def build_upsample_nearest2(x, out, *, batch, H, W, C):
+    def run():
+        v = x.reshape(batch, H, 1, W, 1, -1)[..., :C].expand(batch, H, 2, W, 2, C)
+        out.reshape(batch * 4 * H * W, -1)[:, :C].copy_(v.reshape(-1, C))
+
+    return EmuLaunch("kair_upsample_nearest2", run)

@@ -115,3 +115,25 @@ def build_reference(case, ref_loader):
     missing = model.load_state_dict(sd, strict=True)
     assert not missing.missing_keys and not missing.unexpected_keys
     return model, sd, x, tgt
+
+
+def dncnn_cfg1_images(size=256, sigma=25.0):
+    """cfg1 protocol (main_test_dncnn.py:151-152 of the reference): a clean synthetic image in [0,1] (sum of sinusoids
+    and an edge), plus np.random.seed(0) Gaussian noise of level sigma/255.  Returns (clean, noisy) as (1,1,H,W) fp32."""
+    import numpy as np
+    yy, xx = np.meshgrid(np.arange(size, dtype=np.float64), np.arange(size, dtype=np.float64), indexing="ij")
+    clean = 0.5 + 0.2 * np.sin(2 * np.pi * xx / 64.0) * np.cos(2 * np.pi * yy / 48.0) + 0.15 * np.sin(2 * np.pi * (xx + yy) / 23.0)
+    clean += 0.1 * ((xx > size * 0.6) & (yy > size * 0.3))
+    clean = np.clip(clean, 0.0, 1.0)
+    np.random.seed(seed=0)
+    noisy = clean + np.random.normal(0, sigma / 255.0, clean.shape)
+    to_t = lambda a: torch.from_numpy(a.astype(np.float32))[None, None]
+    return to_t(clean), to_t(noisy)
+
+
+def psnr_uint8(a, b):
+    """utils/utils_image.py:296-300, 629-645 of the reference: PSNR on round(clip(x,0,1)*255) uint8 images."""
+    qa = (a.clamp(0, 1) * 255.0).round()
+    qb = (b.clamp(0, 1) * 255.0).round()
+    mse = torch.mean((qa - qb) ** 2).item()
+    return float("inf") if mse == 0 else 20.0 * math.log10(255.0 / math.sqrt(mse))

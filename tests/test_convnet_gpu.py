@@ -1,0 +1,297 @@
+"""GPU parity of the conv-net path (through the C ABI): the new helper kernels vs their PyTorch statements in
+tests/emu_ops.py, and the drop-in DnCNN / UNetRes modules vs the CPU oracle, the committed golden fixtures (made from
+the real reference modules) and the model_zoo/dncnn_25.pth known-answer fixture.
+Tolerances: bf16 tensor-core mode, 2e-2 max-abs on [0,1]-range outputs (north_star); gradients in relative L2."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import emu_ops
+import golden_cases as gc
+from test_elementwise_gpu import _g, _run_both
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+# ------------------------------------------------------------------------------------------------ kernels
+
+@pytest.mark.parametrize("B,H,W,C", [(2, 8, 12, 64), (1, 16, 16, 256), (3, 4, 4, 512)])
+def test_regroup(B, H, W, C):
+    g = _g(C + H)
+    fine = torch.randn(B * H * W, C, generator=g).bfloat16()
+    kw = dict(fine=fine, coarse=torch.zeros(B * H * W // 4, 4 * C).bfloat16(), batch=B, H=H, W=W, C=C)
+    _run_both("space_to_depth", kw, ["coarse"], 1e-6)
+    for src in (torch.randn(B * H * W // 4, 4 * C, generator=g), kw["coarse"]):
+        kw2 = dict(coarse=src, batch=B, H=H, W=W, C=C, out_f32=torch.zeros(B * H * W, C),
+                   out_bf16=torch.zeros(B * H * W, C).bfloat16())
+        _run_both("depth_to_space", kw2, ["out_f32"], 1e-6)
+        _run_both("depth_to_space", kw2, ["out_bf16"], 1e-2)
+    # round trip
+    from kair_b200 import ops
+    f = fine.cuda(); c = torch.zeros(B * H * W // 4, 4 * C, device="cuda", dtype=torch.bfloat16)
+    back = torch.zeros_like(f)
+    ops.space_to_depth(f, c, batch=B, H=H, W=W, C=C)
+    ops.depth_to_space(c, batch=B, H=H, W=W, C=C, out_bf16=back)
+    assert torch.equal(back, f)
+
+
+@pytest.mark.parametrize("T,C,dt", [(1000, 64, torch.bfloat16), (4096, 512, torch.bfloat16), (777, 128, torch.float32)])
+def test_colsum(T, C, dt):
+    x = torch.randn(T, C, generator=_g(T)).to(dt)
+    _run_both("colsum", dict(x=x, out=torch.zeros(C), C=C, scale=0.5), ["out"], 1e-4)
+
+
+@pytest.mark.parametrize("T,C,slope", [(2 * 24 * 24, 64, 0.0), (1000, 128, 0.2)])
+def test_batchnorm_kernels(T, C, slope):
+    g = _g(T + C)
+    z = torch.randn(T, C, generator=g) * 1.7 + 0.3 * torch.randn(C, generator=g)
+    gamma, beta = 1 + 0.2 * torch.randn(C, generator=g), 0.1 * torch.randn(C, generator=g)
+    rm, rv = 0.1 * torch.randn(C, generator=g), 0.5 + torch.rand(C, generator=g)
+    acc = torch.zeros(2, C, dtype=torch.float64)
+    _run_both("bn_stats", dict(z=z, acc=acc, C=C), ["acc"], 1e-5)
+    mean, rstd = torch.zeros(C), torch.zeros(C)
+    nbt = torch.zeros((), dtype=torch.int64)
+    kw = dict(acc=acc, mean=mean, rstd=rstd, running_mean=rm, running_var=rv, num_batches_tracked=nbt, C=C, T=T,
+              eps=1e-4, momentum=0.9)
+    _run_both("bn_finalize", kw, ["mean", "rstd", "running_mean", "running_var", "num_batches_tracked", "acc"], 1e-5)
+    assert int(nbt) == 1
+    y = torch.zeros(T, C).bfloat16()
+    kwa = dict(z=z, mean=mean, rstd=rstd, gamma=gamma, beta=beta, C=C, act=emu_ops.ACT_LRELU, act_slope=slope,
+               out_bf16=y, out_f32=torch.zeros(T, C))
+    _run_both("bn_apply", kwa, ["out_f32"], 1e-5)
+    _run_both("bn_apply", kwa, ["out_bf16"], 1e-2)
+    for dy in (torch.randn(T, C, generator=g), torch.randn(T, C, generator=g).bfloat16()):
+        dgamma, dbeta = torch.zeros(C), torch.zeros(C)
+        kwr = dict(z=z, y=y, dy=dy, mean=mean, rstd=rstd, dgamma=dgamma, dbeta=dbeta, C=C, act=emu_ops.ACT_LRELU,
+                   act_slope=slope)
+        _run_both("bn_bwd_reduce", kwr, ["dgamma", "dbeta"], 1e-4)
+        kwb = dict(z=z, y=y, dy=dy, mean=mean, rstd=rstd, gamma=gamma, dgamma=dgamma, dbeta=dbeta,
+                   dz=torch.zeros(T, C).bfloat16(), C=C, act=emu_ops.ACT_LRELU, act_slope=slope, dbias=torch.zeros(C))
+        _run_both("bn_bwd_apply", kwb, ["dz"], 1e-2)
+    sc, sh = torch.zeros(C), torch.zeros(C)
+    _run_both("bn_fold", dict(gamma=gamma, beta=beta, running_mean=rm, running_var=rv, scale=sc, shift=sh, C=C,
+                              eps=1e-4), ["scale", "shift"], 1e-5)
+
+
+@pytest.mark.parametrize("r,C", [(2, 64), (3, 64), (4, 4)])
+def test_pixel_shuffle_and_nearest(r, C):
+    B, H, W = 2, 6, 10
+    x = torch.randn(B * H * W, C * r * r, generator=_g(r)).bfloat16()
+    _run_both("pixel_shuffle", dict(x=x, out=torch.zeros(B * H * r * W * r, C).bfloat16(), batch=B, H=H, W=W, C=C, r=r),
+              ["out"], 1e-6)
+    # the emulation follows torch.nn.PixelShuffle's channel order
+    ref = torch.nn.functional.pixel_shuffle(x.float().view(B, H, W, -1).permute(0, 3, 1, 2), r)
+    out = torch.zeros(B * H * r * W * r, C).bfloat16()
+    emu_ops.build_pixel_shuffle(x, out, batch=B, H=H, W=W, C=C, r=r).run()
+    assert torch.equal(out.float().view(B, H * r, W * r, C).permute(0, 3, 1, 2), ref)
+    if r == 2:
+        x8 = torch.randn(B * H * W, 64, generator=_g(5)).bfloat16()
+        _run_both("upsample_nearest2", dict(x=x8, out=torch.zeros(B * 4 * H * W, 64).bfloat16(), batch=B, H=H, W=W, C=64),
+                  ["out"], 1e-6)
+
+
+@pytest.mark.parametrize("conv,N,K", [(True, 64, 64), (True, 128, 128), (False, 256, 128), (True, 512, 512)])
+def test_gemm_tn_activation_backward_mask(conv, N, K):
+    """LINEAR epilogue with aux: (acc + bias) * (aux > 0 ? 1 : slope) [+ resid] -- the ReLU backward fused into dgrad."""
+    B, H, W = 2, 12, 20
+    M = B * H * W
+    g = _g(N + K)
+    A = torch.randn(M, K, generator=g).bfloat16()
+    taps = 9 if conv else 1
+    Bw = (torch.randn(N, taps * K, generator=g) * 0.05).bfloat16()
+    aux = torch.randn(M, N, generator=g).bfloat16()
+    resid = torch.randn(M, N, generator=g)
+    bn = 256 if N % 256 == 0 else (128 if N % 128 == 0 else 64)
+    for use_resid, slope in ((False, 0.0), (True, 0.2)):
+        kw = dict(A=A, B=Bw, N=N, K=K, bn=bn, aux=aux, act_slope=slope, resid=resid if use_resid else None,
+                  outB=torch.zeros(M, N).bfloat16(), outF=torch.zeros(M, N), conv=(B, H, W) if conv else None)
+        _run_both("gemm_tn", kw, ["outF"], 2e-3)
+        _run_both("gemm_tn", kw, ["outB"], 1e-2)
+
+
+def test_conv_out_dgrad_mask_and_pack_conv_fold():
+    B, co, H, W, C = 2, 1, 10, 14, 64
+    g = _g(3)
+    dout = torch.randn(B, co, H, W, generator=g)
+    Wt = torch.randn(co, C, 3, 3, generator=g) * 0.1
+    mask = torch.randn(B * H * W, C, generator=g).bfloat16()
+    kw = dict(dout=dout, W=Wt, C=C, pitch=C, out_scale=-1.0, dfeat_f32=torch.zeros(B * H * W, C), mask=mask,
+              mask_slope=0.1)
+    _run_both("conv_out_dgrad", kw, ["dfeat_f32"], 1e-5)
+    L = 3
+    Ws = [torch.randn(C, C, 3, 3, generator=g) * 0.05 for _ in range(L)]
+    bs = [torch.randn(C, generator=g) for _ in range(L)]
+    osc = [1 + 0.3 * torch.randn(C, generator=g) for _ in range(L)]
+    osh = [torch.randn(C, generator=g) for _ in range(L)]
+    kwp = dict(W=Ws, b=bs, Wp=torch.zeros(L, C, 9 * C).bfloat16(), WpT=torch.zeros(L, C, 9 * C).bfloat16(),
+               bp=torch.zeros(L, C), O=C, I=C, I_pad=C, oscale=osc, oshift=osh)
+    _run_both("pack_conv", kwp, ["bp"], 1e-6)
+    _run_both("pack_conv", kwp, ["Wp", "WpT"], 1e-2)
+
+
+# ------------------------------------------------------------------------------------------------ networks
+
+def _rel_l2(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+
+def _build(case):
+    from kair_b200.network_dncnn import DnCNN
+    from kair_b200.network_unet import UNetRes
+    kw = case["kw"]
+    model = DnCNN(**kw) if case["net"] == "dncnn" else UNetRes(**kw)
+    sd, x, tgt = gc.state_and_io(case)
+    model.load_state_dict(sd, strict=True)
+    return model, sd, x, tgt
+
+
+def _check_against_golden(name, grad_tol, out_tol=2e-2):
+    case = gc.CASES[name]
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    model, sd, x, tgt = _build(case)
+    model = model.cuda().train(case.get("train_mode", False))
+    y = model(x.cuda())
+    loss = gc.loss_fn(case)(y, tgt.cuda())
+    loss.backward()
+    torch.cuda.synchronize()
+    yr = z["y"]
+    assert np.abs(y.detach().cpu().numpy() - yr).max() < out_tol * max(1.0, np.abs(yr).max())
+    grads = json.loads(str(z["grads"]))
+    gmax = max(v[0] for v in grads.values())
+    bad, e2, r2 = [], 0.0, 0.0
+    for k, p in model.named_parameters():
+        n = p.grad.double().norm().item()
+        e2, r2 = e2 + (n - grads[k][0]) ** 2, r2 + grads[k][0] ** 2
+        if abs(n - grads[k][0]) > 3 * grad_tol * grads[k][0] + 2e-3 * gmax:
+            bad.append((k, n, grads[k][0]))
+    assert not bad, bad[:6]
+    assert (e2 / r2) ** 0.5 < grad_tol
+    return model, z
+
+
+def test_golden_dncnn_r17():
+    _check_against_golden("dncnn_r17", 4e-2)
+
+
+def test_golden_dncnn_br_train():
+    model, z = _check_against_golden("dncnn_br_train", 0.1)
+    sd = model.state_dict()
+    for k in z.files:
+        if k.startswith("stat:"):
+            assert np.allclose(sd[k[5:]].cpu().numpy(), z[k], rtol=2e-2, atol=1e-2), k
+    assert int(sd["model.3.num_batches_tracked"]) == 1
+
+
+def test_golden_dncnn_br_eval_forward():
+    """eval-mode BN: running statistics folded into the packed conv weights (no_grad path)."""
+    case = gc.CASES["dncnn_br_eval"]
+    z = np.load(os.path.join(GOLDEN, "dncnn_br_eval.npz"))
+    model, sd, x, tgt = _build(case)
+    model = model.cuda().eval()
+    with torch.no_grad():
+        y = model(x.cuda())
+    assert np.abs(y.cpu().numpy() - z["y"]).max() < 2e-2 * max(1.0, np.abs(z["y"]).max())
+    with pytest.raises(NotImplementedError, match="eval-mode BatchNorm"):
+        model(x.cuda())
+
+
+def test_golden_unetres_nb2():
+    _check_against_golden("unetres_nb2", 6e-2)
+
+
+@pytest.mark.parametrize("net,shape", [("dncnn", (2, 1, 33, 47)), ("dncnn_bn", (3, 3, 24, 40)), ("unet", (2, 4, 40, 24))])
+def test_networks_vs_oracle_all_gradients(net, shape):
+    """Every parameter gradient (full tensors, not fingerprints) vs the oracle on odd / non-square sizes."""
+    from kair_b200.network_dncnn import DnCNN
+    from kair_b200.network_unet import UNetRes
+    from oracle import convnets_oracle as co
+    from test_convnet_engine_cpu import _check_grads, _sd, _seed_params
+    torch.manual_seed(0)
+    B, c, H, W = shape
+    if net == "unet":
+        model = UNetRes(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=2, act_mode="R", bias=False)
+        _seed_params(model, 61, scale=0.7)
+        fwd = lambda sd, x: co.unetres_forward(sd, x, nb=2)
+        co_ = 3
+    else:
+        act = "BR" if net == "dncnn_bn" else "R"
+        model = DnCNN(in_nc=c, out_nc=c, nc=64, nb=6, act_mode=act)
+        _seed_params(model, 62)
+        model.train(True)
+        fwd = lambda sd, x: co.dncnn_forward(sd, x, nb=6, act_mode=act, training=True)
+        co_ = c
+    sd = _sd(model)
+    g = torch.Generator().manual_seed(8)
+    x, tgt = torch.rand(B, c, H, W, generator=g), torch.rand(B, co_, H, W, generator=g)
+    y_ref = fwd(sd, x)
+    torch.mean((y_ref - tgt) ** 2).backward()
+    model = model.cuda()
+    y = model(x.cuda())
+    torch.mean((y - tgt.cuda()) ** 2).backward()
+    torch.cuda.synchronize()
+    assert (y.detach().cpu() - y_ref.detach()).abs().max().item() < 2e-2 * max(1.0, y_ref.detach().abs().max().item())
+    _check_grads(model, sd, {k: p.grad.cpu() for k, p in model.named_parameters()}, 0.1 if net == "dncnn_bn" else 6e-2)
+
+
+def test_dncnn25_known_answer_cfg1():
+    """BASELINE configs[0]: DnCNN-17 'R' + model_zoo/dncnn_25.pth on the seeded 256x256 image; y from the real reference."""
+    from kair_b200.network_dncnn import DnCNN
+    z = np.load(os.path.join(GOLDEN, "kat", "dncnn_25.npz"))
+    sd = {str(k): torch.from_numpy(z["w:" + str(k)]) for k in z["keys"]}
+    model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=17, act_mode="R")
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().eval()
+    for p in model.parameters():
+        p.requires_grad = False            # main_test_dncnn.py:123-124
+    torch.manual_seed(0)
+    x = torch.rand(1, 1, 256, 256)
+    y = model(x.cuda()).cpu()
+    yr = torch.from_numpy(z["y"])
+    err = (y - yr).abs().max().item()
+    assert err < 2e-2, err
+    # cfg1 denoising protocol: sigma=25 noise on a clean synthetic image, PSNR (uint8) within 0.02 dB of the reference
+    clean, noisy = gc.dncnn_cfg1_images()
+    y_dn = model(noisy.cuda()).cpu()
+    assert (y_dn - torch.from_numpy(z["y_denoise"])).abs().max().item() < 2e-2
+    assert abs(gc.psnr_uint8(noisy, clean) - float(z["psnr_in"])) < 1e-6
+    assert abs(gc.psnr_uint8(y_dn, clean) - float(z["psnr_out"])) < 0.02, (gc.psnr_uint8(y_dn, clean), float(z["psnr_out"]))
+    assert abs(y.mean().item() - 0.5027428) < 2e-3
+    # batch of 5 odd-sized images: same weights, per-image equality with the batch-1 result of the same image
+    xb = torch.rand(5, 1, 63, 97, generator=torch.Generator().manual_seed(3)).cuda()
+    yb = model(xb)
+    y1 = model(xb[2:3])
+    assert torch.equal(yb[2:3], y1)
+
+
+def test_full_size_properties_drunet_cfg4():
+    """cfg4 shape (B=16, 4x128x128, DRUNet nb=4): finite outputs and gradients, linearity of the bias-free net in its
+    last layer (tail weights zeroed => exact zeros), determinism of two identical steps."""
+    from kair_b200.network_unet import UNetRes
+    torch.manual_seed(0)
+    model = UNetRes(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=4, act_mode="R", downsample_mode="strideconv",
+                    upsample_mode="convtranspose", bias=False).cuda().train()
+    x = torch.rand(16, 4, 128, 128, device="cuda")
+    y1 = model(x)
+    y1.abs().mean().backward()
+    g1 = [p.grad.clone() for p in model.parameters()]
+    assert y1.shape == (16, 3, 128, 128) and torch.isfinite(y1).all() and all(torch.isfinite(g).all() for g in g1)
+    model.zero_grad()
+    y2 = model(x)
+    y2.abs().mean().backward()
+    assert torch.equal(y1, y2) or (y1 - y2).abs().max().item() < 1e-6
+    with torch.no_grad():
+        model.m_tail.weight.zero_()
+        assert torch.count_nonzero(model(x)).item() == 0
+
+
+def test_cpu_tensor_is_rejected():
+    from kair_b200.network_dncnn import DnCNN
+    from kair_b200.network_unet import UNetRes
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        DnCNN()(torch.rand(1, 1, 16, 16))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        UNetRes()(torch.rand(1, 3, 16, 16))
