@@ -176,6 +176,13 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _group_table(groups):
+    return {k: {"n": v["count"], "ms": round(v["ms"], 4),
+                "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0,
+                "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 0) if v["ms"] > 0 else 0.0}
+            for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])}
+
+
 # ------------------------------------------------------------------------------------------------ B200 arm
 
 def run_b200(args):
@@ -300,17 +307,18 @@ def run_b200(args):
         groups = profiling.summarize(launches, per, REAL_DIMS)
         tot = sum(d["ms"] for d in groups.values())
         top_tag, top = max(groups.items(), key=lambda kv: kv[1]["ms"])
-        ach = top["flops"] / (top["ms"] * 1e-3) / 1e12 if top["ms"] > 0 else 0.0
-        roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+        peak_gbs = peaks.get("hbm_gbs") or 6500.0
+        roof = profiling.roofline_of(top, peak_tf, peak_gbs)
+        roof.update({
                 "traffic": None, "kernel": top_tag, "launches_per_step": top["count"],
                 "avg_launch_ms": top["ms"] / top["count"], "share_of_kernel_time": top["ms"] / tot,
-                "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": top["bytes"] / top["count"],
+                "algorithmic_flops_per_launch": top["flops"] / top["count"],
+                "peak_source": peak_src + " / hbm_gbs",
                 "whole_step": {"tflops": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step,
                                "frac": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step / peak_tf,
                                "sum_kernel_ms": tot},
-                "groups": {k: {"n": v["count"], "ms": round(v["ms"], 4),
-                               "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0}
-                           for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])}}
+                "groups": _group_table(groups)})
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -339,6 +347,302 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------ other configs
+# BASELINE.json configs[0], [2], [3], [4] (cfg1, cfg3, cfg4, cfg5 of SURVEY.md section 8(d)): `--workload cfgN`.
+# The default line (no flag) stays cfg2, the config the headline metric is quoted on.
+
+SWIN_SR = dict(upscale=4, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+               num_heads=[6] * 6, mlp_ratio=2, resi_connection="1conv")
+WORKLOADS = {
+    "cfg1": "cfg1: DnCNN-17 'R' gray sigma=25 inference (dncnn_25.pth architecture), synthetic 1x256x256 images, batch %d/GPU",
+    "cfg3": "cfg3: SwinIR-M classical SR x4 (pixelshuffle) inference, synthetic 3x64x64 LR patches, batch %d/GPU",
+    "cfg4": "cfg4: DRUNet (UNetRes 64-128-256-512, nb=4) training, 4-channel 128x128 patches (RGB + sigma map), batch %d/GPU, L1 + Adam 1e-4",
+    "cfg5": "cfg5: SwinIR-M real-world SR x4 (nearest+conv) tiled inference, synthetic 3x2048x2048 image, tile 256 overlap 32 (100 tiles), %d tiles per forward, tiles sharded over ranks",
+}
+DEFAULT_BATCH = {"cfg1": 1, "cfg3": 32, "cfg4": 16, "cfg5": 4}
+
+
+def _dncnn_weights(model):
+    """dncnn_25.pth tensors from the committed known-answer fixture when present (data, not oracle code)."""
+    import numpy as np
+    import torch
+    path = os.path.join(ROOT, "tests", "golden", "kat", "dncnn_25.npz")
+    if os.path.exists(path):
+        z = np.load(path)
+        model.load_state_dict({str(k): torch.from_numpy(z["w:" + str(k)]) for k in z["keys"]}, strict=True)
+        return "model_zoo/dncnn_25.pth (from tests/golden/kat)"
+    return "random init"
+
+
+def oracle_workload(name, batch, steps, warmup, budget_s=60.0):
+    """CPU leg of a workload on the oracle port (fp32, all host threads), on a bounded sample; returns
+    (units per second, timed steps, threads, sample description)."""
+    import torch
+    from oracle import convnets_oracle as co
+    from oracle import swinir_oracle as so
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(0)
+    if name == "cfg1":
+        sd = so.deterministic_state(co.dncnn_state_spec(1, 1, 64, 17, "R"), 0)
+        x = torch.rand(1, 1, 256, 256, generator=g)
+        units, sample = 256 * 256 / 1e6, "1 image of 1x256x256 per step"
+        def fn():
+            with torch.no_grad():
+                co.dncnn_forward(sd, x, nb=17, act_mode="R")
+    elif name in ("cfg3", "cfg5"):
+        up = "pixelshuffle" if name == "cfg3" else "nearest+conv"
+        cfg = so.SwinIRConfig(img_size=64, in_chans=3, embed_dim=180, depths=(6,) * 6, num_heads=(6,) * 6, window_size=8,
+                              mlp_ratio=2, upscale=4, img_range=1.0, upsampler=up)
+        sd = so.deterministic_state(so.state_spec(cfg), 0, cfg)
+        side = 64 if name == "cfg3" else 128
+        x = torch.rand(1, 3, side, side, generator=g)
+        units = side * side / 1e6
+        sample = "1 LR patch of 3x%dx%d per step%s" % (side, side, "" if name == "cfg3" else
+                                                      " (a quarter of one 256x256 tile; cost is linear in pixels)")
+        def fn():
+            with torch.no_grad():
+                so.swinir_forward(sd, x, cfg)
+    elif name == "cfg4":
+        sd = so.deterministic_state(co.unetres_state_spec(4, 3, (64, 128, 256, 512), 4, False), 0)
+        params = [v.requires_grad_(True) for v in sd.values()]
+        opt = torch.optim.Adam(params, lr=1e-4)
+        x, tgt = torch.rand(1, 4, 128, 128, generator=g), torch.rand(1, 3, 128, 128, generator=g)
+        units, sample = 1.0, "1 patch of 4x128x128 per step (forward + backward + Adam)"
+        def fn():
+            opt.zero_grad(set_to_none=True)
+            torch.mean(torch.abs(co.unetres_forward(sd, x, nb=4) - tgt)).backward()
+            opt.step()
+    else:
+        raise SystemExit("unknown workload " + name)
+    times, t_begin = [], time.perf_counter()
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        fn()
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_begin > budget_s and times:
+            break
+    sec = sum(times) / len(times)
+    return units / sec, len(times), threads, sample + ", %d timed steps, fp32 oracle port of the reference modules" % len(times)
+
+
+_W_METRIC = {"cfg1": ("DnCNN-17 inference MPix/s", "MPix/s"), "cfg3": ("SwinIR-M SR x4 inference LR-MPix/s", "MPix/s"),
+             "cfg4": ("DRUNet train patches/s", "patches/s"), "cfg5": ("SwinIR-M SR x4 tiled inference LR-MPix/s", "MPix/s")}
+
+
+def run_reference_workload(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    name = args.workload
+    batch = args.batch or DEFAULT_BATCH[name]
+    value, done, threads, sample = oracle_workload(name, batch, args.steps, min(args.warmup, 1), budget_s=200.0)
+    metric, unit = _W_METRIC[name]
+    print(json.dumps({
+        "impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": done,
+        "warmup": min(args.warmup, 1), "ms_per_step": None, "higher_is_better": True,
+        "scaling": "strong" if name == "cfg5" else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOADS[name] % batch, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": unit, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+    }), flush=True)
+
+
+def run_b200_workload(args):
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    from kair_b200 import profiling, tiling
+    name = args.workload
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device; the sm_100a path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    batch = args.batch or DEFAULT_BATCH[name]
+    torch.manual_seed(0)
+    g = torch.Generator().manual_seed(1234 + rank)
+    real_dims = dict(REAL_DIMS)
+    weights = "random init (reference default initialisation, seed 0)"
+    extra_cfg = {}
+    n_tiles_rank = None
+
+    if name == "cfg1":
+        from kair_b200.network_dncnn import DnCNN
+        model = DnCNN(1, 1, 64, 17, "R")
+        weights = _dncnn_weights(model)
+        model = model.to(dev).eval()
+        for p_ in model.parameters():
+            p_.requires_grad = False
+        clean = torch.rand(batch, 1, 256, 256, generator=g)
+        host = [(clean + torch.randn(clean.shape, generator=g) * (25.0 / 255.0)).pin_memory()]
+        units = batch * 256 * 256 / 1e6
+        plan_of = lambda: model.engine(dev).plan(batch, 256, 256, False, False)
+        def step(x):
+            with torch.no_grad():
+                return model(x)
+        fwd_gflop = 72.63 * batch
+        real_dims = {}
+    elif name == "cfg3":
+        from kair_b200.network_swinir import SwinIR
+        model = SwinIR(upsampler="pixelshuffle", **SWIN_SR).to(dev).eval()
+        host = [torch.rand(batch, 3, 64, 64, generator=g).pin_memory()]
+        units = batch * 64 * 64 / 1e6
+        plan_of = lambda: model.engine(dev).plan(batch, 64, 64, False)
+        def step(x):
+            with torch.no_grad():
+                return model(x)
+        fwd_gflop = 107.11 * batch
+    elif name == "cfg4":
+        from kair_b200.network_unet import UNetRes
+        model = UNetRes(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=4, act_mode="R", downsample_mode="strideconv",
+                        upsample_mode="convtranspose", bias=False).to(dev).train()
+        net = model
+        if world > 1:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            net = DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)
+        high = torch.rand(batch, 3, 128, 128, generator=g)
+        sigma = torch.rand(batch, 1, 1, 1, generator=g) * 50.0 / 255.0
+        low = torch.cat([high + torch.randn(high.shape, generator=g) * sigma, sigma.expand(batch, 1, 128, 128)], 1)
+        host = [low.contiguous().pin_memory(), high.pin_memory()]
+        units = float(batch)
+        plan_of = lambda: model.engine(dev).plan(batch, 128, 128, True)
+        def step(lo, hi):
+            opt.zero_grad(set_to_none=True)
+            loss = torch.mean(torch.abs(net(lo) - hi))
+            loss.backward()
+            opt.step()
+            return loss
+        fwd_gflop = 3 * 69.39 * batch
+        real_dims = {}
+    elif name == "cfg5":
+        from kair_b200.network_swinir import SwinIR
+        model = SwinIR(upsampler="nearest+conv", **SWIN_SR).to(dev).eval()
+        side = args.image or 2048
+        img = tiling.pad_to_window(torch.rand(1, 3, side, side, generator=torch.Generator().manual_seed(1234)), 8)
+        host = [img.pin_memory()]
+        units = side * side / 1e6 / world          # whole job = one image; each rank does its share of the tiles
+        n_tiles = len(tiling.tile_origins(img.shape[2], img.shape[3], 256, 32))
+        n_tiles_rank = len([i for i in range(n_tiles) if i % world == rank])
+        extra_cfg = {"tiles": n_tiles, "tiles_on_rank0": n_tiles_rank, "padded": list(img.shape[2:])}
+        plan_of = lambda: model.engine(dev).plan(batch, 256, 256, False)
+        def step(x):
+            with torch.no_grad():
+                E, Wt, _ = tiling.tiled_partial(model, x, 256, 32, 4, 8, tile_batch=batch, rank=rank, world=world)
+                if world > 1:      # merge of the per-rank partial sums on rank 0 (the only exchange; after the compute)
+                    dist.reduce(E, 0)
+                    dist.reduce(Wt, 0)
+                return E.div_(Wt) if rank == 0 else E
+        fwd_gflop = 1791.1 * n_tiles_rank
+    else:
+        raise SystemExit("unknown workload " + name)
+
+    devin = [h.to(dev) for h in host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        out = step(*devin)
+    sampler = ClockSampler(_physical_gpu_index(local_rank))
+    sampler.start()
+    ms_total = timed(lambda: step(*devin), args.steps)
+    clocks = sampler.stop()
+    out_bytes = out.numel() * out.element_size() if out.dim() > 0 else 4
+    host_out = torch.empty(out.shape, dtype=out.dtype).pin_memory() if out.dim() > 0 else None
+
+    def e2e_step():
+        for d_, h_ in zip(devin, host):
+            d_.copy_(h_, non_blocking=True)
+        o_ = step(*devin)
+        if host_out is None:
+            return o_.item()
+        if name != "cfg5" or rank == 0:
+            host_out.copy_(o_, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    ms_step = ms_total / args.steps
+    value = units * world / (ms_step * 1e-3)
+    e2e_value = units * world / (ms_e2e / args.steps * 1e-3)
+
+    roof, cpu = None, None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:  # noqa: BLE001
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained") or 1400.0
+        peak_gbs = peaks.get("hbm_gbs") or 6500.0
+        plan = plan_of()
+        launches = list(plan.fwd) + list(plan.bwd or [])
+        if plan.bwd:
+            plan.grads.flat.zero_()
+            for t_ in plan.zero_before_bwd:
+                t_.zero_()
+        sth = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        per = profiling.time_launches(launches, sth, reps=3)
+        groups = profiling.summarize(launches, per, real_dims)
+        tot = sum(d["ms"] for d in groups.values())
+        top_tag, top = max(groups.items(), key=lambda kv: kv[1]["ms"])
+        roof = profiling.roofline_of(top, peak_tf, peak_gbs)
+        passes = 1 if name != "cfg5" else -(-n_tiles_rank // batch)
+        roof.update({"traffic": None, "kernel": top_tag, "launches_per_step": top["count"] * passes,
+                     "avg_launch_ms": top["ms"] / top["count"], "share_of_kernel_time": top["ms"] / tot,
+                     "algorithmic_bytes_per_launch": top["bytes"] / top["count"],
+                     "algorithmic_flops_per_launch": top["flops"] / top["count"],
+                     "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)",
+                     "whole_step": {"tflops": fwd_gflop / ms_step, "frac": fwd_gflop / ms_step / peak_tf,
+                                    "sum_kernel_ms": tot * passes},
+                     "groups": _group_table(groups)})
+        n_launch = len(launches) * passes
+        if world == 1 and not args.no_cpu_baseline:
+            v, done, threads, sample = oracle_workload(name, batch, 3, 1, budget_s=40.0)
+            cpu = {"value": v, "unit": _W_METRIC[name][1], "cores": threads, "kind": "port", "sample": sample}
+        metric, unit = _W_METRIC[name]
+        line = {
+            "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if name == "cfg5" else "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": dict({"workload": WORKLOADS[name] % batch, "parallelism": "dp%d" % world, "weights": weights,
+                            "l2": "inputs/activations of a step exceed the 126 MB L2 except cfg1 at batch 1 "
+                                  "(whole net L2-resident by design); no flush"}, **extra_cfg),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": sum(h.numel() * 4 for h in host) * world,
+                    "d2h_bytes_per_step": out_bytes * (1 if name == "cfg5" else world),
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": n_launch * args.steps, "roofline": roof, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -346,10 +650,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"],
+                    help="BASELINE.json config to run; cfg2 (SwinIR training) is the headline and the default")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override for cfg1/3/4, tiles per forward for cfg5")
+    ap.add_argument("--image", type=int, default=0, help="cfg5: image side (default 2048)")
     ap.add_argument("--ncu-slice", action="store_true", help="profiling aid: one launch per kernel group in a "
                     "cudaProfilerStart/Stop range")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.workload != "cfg2":
+        (run_reference_workload if args.impl == "reference" else run_b200_workload)(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

@@ -18,7 +18,14 @@ def describe(launch, real_dims):
     if name == "gemm_tn":
         taps = 9 if a.conv else 1
         tag = "gemm_tn[%s N%d K%d %s]" % ("conv3x3" if a.conv else "dense", a.N, a.K * taps, _EPI[a.mode])
-        return tag, 2.0 * a.M * r(a.N) * r(a.K) * taps, 2.0 * a.M * (r(a.K) + r(a.N))
+        if a.mode == 0 and a.aux:
+            tag = tag[:-1] + "+actbwd]"
+        # operand traffic of this launch on the unpadded extents: A once (the 9 taps re-read it from L2 / smem),
+        # fp32 residual in, bf16 aux in, every output once; weights are L2-resident
+        by = 2.0 * a.M * r(a.K)
+        by += 4.0 * a.M * r(a.N) * (1 if a.resid else 0) + 2.0 * a.M * r(a.N) * (1 if a.aux else 0)
+        by += 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
+        return tag, 2.0 * a.M * r(a.N) * r(a.K) * taps, by
     if name == "gemm_nt":
         taps = 9 if a.conv else 1
         tag = "gemm_nt[%s n1=%d n2=%d]" % ("conv3x3" if a.conv else "dense", a.n1, a.n2 * taps)
@@ -28,10 +35,49 @@ def describe(launch, real_dims):
         N = a.window * a.window
         hd = real_dims.get("head_dim", 30)
         f = 4.0 * (T // N) * a.num_heads * N * N * hd          # QK^T + PV
-        by = 4.0 * T * a.num_heads * hd * 2                    # q, k, v, o in bf16
+        by = 4.0 * T * a.num_heads * hd * 2                    # q, k, v, o in bf16 (15 360 B / window-head)
         if name.endswith("bwd"):
-            return "window_attn_bwd", 2.0 * f, 2.0 * by        # dV, dP, dQ, dK; + dO, dq, dk, dv traffic
+            # autograd's dV, dP, dQ, dK contractions (the kernel's recomputation of S is not algorithmic work);
+            # reads q, k, v, dO, writes dq, dk, dv
+            return "window_attn_bwd", 2.0 * f, 7.0 * T * a.num_heads * hd * 2
         return "window_attn_fwd", f, by
+    T_ = lambda: int(a.T)
+    if name in ("bn_stats",):
+        return name, 0.0, 4.0 * T_() * a.C
+    if name == "bn_apply":
+        return name, 0.0, T_() * a.C * (4.0 + (2.0 if a.out_bf16 else 0) + (4.0 if a.out_f32 else 0))
+    if name == "bn_bwd_reduce":
+        return name, 0.0, T_() * a.C * (4.0 + 2.0 + (4.0 if a.dy_f32 else 2.0))
+    if name == "bn_bwd_apply":
+        return name, 0.0, T_() * a.C * (4.0 + 2.0 + (4.0 if a.dy_f32 else 2.0) + 2.0)
+    if name == "colsum":
+        return name, 0.0, T_() * a.C * (2.0 if a.x_bf16 else 4.0)
+    if name in ("space_to_depth", "depth_to_space"):
+        n = float(a.batch) * a.H * a.W * a.C
+        if name == "space_to_depth":
+            return name, 0.0, 4.0 * n
+        return name, 0.0, n * ((4.0 if a.coarse_in_f32 else 2.0) + (4.0 if a.fine_out_f32 else 0) + (2.0 if a.fine_out_bf16 else 0))
+    if name in ("pixel_shuffle", "upsample_nearest2"):
+        rr = a.r * a.r if name == "pixel_shuffle" else 4
+        n = float(a.batch) * a.H * a.W * a.C * rr
+        return name, 0.0, 2.0 * n + (2.0 * n if name == "pixel_shuffle" else 2.0 * n / 4)
+    if name in ("conv_in_fwd", "conv_out_fwd", "conv_out_dgrad", "conv_out_wgrad", "conv_in_wgrad"):
+        Tn = float(a.batch) * a.H * a.Wd
+        if name.startswith("conv_in"):
+            ch, img_c = a.O, a.ci
+        else:
+            ch, img_c = a.C, a.co
+        fl = 2.0 * Tn * 9 * ch * img_c
+        feat_b = Tn * ch * 2.0
+        if name == "conv_in_fwd":
+            feat_b = Tn * ch * ((4.0 if a.out_f32 else 0) + (2.0 if a.out_bf16 else 0))
+        elif name == "conv_in_wgrad":
+            feat_b = Tn * ch * ((4.0 if a.dy_f32 else 0) + (2.0 if a.dy_bf16 else 0))
+        elif name == "conv_out_dgrad":
+            feat_b = Tn * ch * ((4.0 if a.dfeat_f32 else 0) + (2.0 if a.dfeat_bf16 else 0) + (2.0 if a.mask else 0))
+        return name, fl, feat_b + Tn * img_c * 4.0
+    if name == "add_inplace":
+        return name, 0.0, 0.0
     return name, 0.0, 0.0
 
 
@@ -63,3 +109,16 @@ def summarize(launches, ms, real_dims):
         d["flops"] += fl
         d["bytes"] += by
     return out
+
+
+def roofline_of(group, peak_tflops, peak_gbs):
+    """roofline object fields for one kernel group dict(count, ms, flops, bytes): the bound is chosen by arithmetic
+    intensity against the ridge peak_tflops / peak_gbs."""
+    sec = group["ms"] * 1e-3
+    ai = group["flops"] / group["bytes"] if group["bytes"] > 0 else float("inf")
+    ridge = peak_tflops * 1e12 / (peak_gbs * 1e9)
+    if group["flops"] > 0 and ai >= ridge:
+        ach = group["flops"] / sec / 1e12 if sec > 0 else 0.0
+        return {"bound": "tensor", "achieved": ach, "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach / peak_tflops}
+    ach = group["bytes"] / sec / 1e9 if sec > 0 else 0.0
+    return {"bound": "hbm", "achieved": ach, "peak": peak_gbs, "unit": "GB/s", "frac": ach / peak_gbs}

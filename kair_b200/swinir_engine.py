@@ -64,8 +64,10 @@ class SwinIRSpec:
                 % (self.C, self.hidden))
         if self.resi_connection != "1conv":
             bad("resi_connection='%s'" % self.resi_connection)
-        if self.upsampler not in ("",):
+        if self.upsampler not in ("", "pixelshuffle", "nearest+conv"):
             bad("upsampler='%s'" % self.upsampler)
+        if self.upsampler == "pixelshuffle" and not (self.upscale in (2, 3, 4, 8)):
+            bad("pixelshuffle upscale=%d" % self.upscale)
         if self.in_chans > 4:
             bad("in_chans=%d > 4" % self.in_chans)
 
@@ -172,6 +174,24 @@ class SwinIREngine:
             o.build_pack_conv([P[n + ".weight"] for n in conv_names], [P[n + ".bias"] for n in conv_names],
                               W["conv"], W["convT"], W["bconv"], O=C, I=C, I_pad=Cp),
         ]
+        # reconstruction heads (network_swinir.py:740-760): num_feat = 64
+        up = self.spec.upsampler
+        if up:
+            nf = 64
+            W["cbu"], W["bcbu"] = bf(1, nf, 9 * Cp), f32(1, nf)
+            W["pack"].append(o.build_pack_conv([P["conv_before_upsample.0.weight"]], [P["conv_before_upsample.0.bias"]],
+                                               W["cbu"], None, W["bcbu"], O=nf, I=C, I_pad=Cp))
+            if up == "pixelshuffle":
+                s = self.spec.upscale
+                r = 3 if s == 3 else 2
+                n = 1 if s == 3 else int(math.log2(s))
+                names = ["upsample.%d" % (2 * i) for i in range(n)]
+                W["ups"], W["bups"], W["ups_r"] = bf(n, r * r * nf, 9 * nf), f32(n, r * r * nf), r
+            else:
+                names = ["conv_up1", "conv_up2", "conv_hr"]
+                W["ups"], W["bups"] = bf(3, nf, 9 * nf), f32(3, nf)
+            W["pack"].append(o.build_pack_conv([P[n_ + ".weight"] for n_ in names], [P[n_ + ".bias"] for n_ in names],
+                                               W["ups"], None, W["bups"], O=W["ups"].shape[1], I=nf, I_pad=nf))
         W["versions"] = None
         self._weights = W
         self._plans = {}  # plans hold pointers into the packed operands
@@ -217,8 +237,13 @@ class _Plan:
         geo = (B, H, W)
         tps = H * W
 
+        up = s.upsampler
+        if up and train:
+            raise NotImplementedError("kair_b200 SwinIR: autograd through the '%s' reconstruction head is not built yet "
+                                      "(inference under torch.no_grad() is); see DESIGN.md, 'coverage'" % up)
+        sc = s.upscale if up else 1
         self.img = f32(B, s.in_chans, H, W)
-        self.out = f32(B, s.in_chans, H, W)
+        self.out = f32(B, s.in_chans, H * sc, W * sc)
         first = f32(T, Cp)
         mean0, rstd0 = f32(T), f32(T)
         xs = [f32(T, Cp), f32(T, Cp)]
@@ -299,8 +324,38 @@ class _Plan:
                                          rstd=rstdF, ones_col=C))
         fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
                                    bias=Wt["bconv"][nl], resid=first, outB=resb, ones_col=C))
-        fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
-                                        skip=self.img, skip_mean=mean_t, skip_scale=rng))
+        if not up:
+            fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
+                                            skip=self.img, skip_mean=mean_t, skip_scale=rng))
+        else:
+            # conv_before_upsample + LeakyReLU(0.01), then the upsampling convolutions on 64 features
+            nf = 64
+            f = bf(T, nf)
+            fwd.append(o.build_gemm_tn(resb, Wt["cbu"][0], N=nf, K=Cp, bn=64, conv=geo, bias=Wt["bcbu"][0],
+                                       act=o.ACT_LRELU, act_slope=0.01, outB=f))
+            h, w = H, W
+            if up == "pixelshuffle":
+                r = Wt["ups_r"]
+                for i in range(Wt["ups"].shape[0]):
+                    u = bf(B * h * w, r * r * nf)
+                    fwd.append(o.build_gemm_tn(f, Wt["ups"][i], N=r * r * nf, K=nf, bn=(192 if r == 3 else 256),
+                                               conv=(B, h, w), bias=Wt["bups"][i], outB=u))
+                    f = bf(B * h * r * w * r, nf)
+                    fwd.append(o.build_pixel_shuffle(u, f, batch=B, H=h, W=w, C=nf, r=r))
+                    h, w = h * r, w * r
+            else:
+                for i in range(2):
+                    n_ = bf(B * 4 * h * w, nf)
+                    fwd.append(o.build_upsample_nearest2(f, n_, batch=B, H=h, W=w, C=nf))
+                    h, w = 2 * h, 2 * w
+                    f = bf(B * h * w, nf)
+                    fwd.append(o.build_gemm_tn(n_, Wt["ups"][i], N=nf, K=nf, bn=64, conv=(B, h, w), bias=Wt["bups"][i],
+                                               act=o.ACT_LRELU, act_slope=0.2, outB=f))
+                f2 = bf(B * h * w, nf)
+                fwd.append(o.build_gemm_tn(f, Wt["ups"][2], N=nf, K=nf, bn=64, conv=(B, h, w), bias=Wt["bups"][2],
+                                           act=o.ACT_LRELU, act_slope=0.2, outB=f2))
+                f = f2
+            fwd.append(o.build_conv_out_fwd(f, cl_w, cl_b, self.out, mean_t, C=nf, pitch=nf, out_scale=1.0 / rng))
         self.fwd = fwd
         self.bwd = None
         if not train:

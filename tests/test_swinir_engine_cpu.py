@@ -96,3 +96,22 @@ def test_engine_matches_oracle_with_drop_path():
     for k, p in mine.named_parameters():
         gr = sd[k].grad
         assert _rel_l2(grads[k], gr) < 5e-2, (k, _rel_l2(grads[k], gr))
+
+
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4"])
+def test_sr_heads_forward_vs_oracle(name):
+    """Reconstruction heads (network_swinir.py:740-760, 816-831): pixelshuffle x4 and nearest+conv x4, inference plan."""
+    import golden_cases as gc
+    case = gc.CASES[name]
+    sd, x, _ = gc.state_and_io(case)
+    mine = SwinIR(drop_path_rate=0.0, **case["kw"])
+    mine.load_state_dict(sd, strict=True)
+    y_ref = gc.oracle_forward(case, sd, x)
+    params = dict(mine.named_parameters())
+    eng = SwinIREngine(mine._spec, params, "cpu", ops=emu_ops)
+    B, _, H, W = x.shape
+    y = eng.plan(B, H, W, False).run_forward(x)
+    assert y.shape == y_ref.shape
+    assert (y - y_ref).abs().max().item() < 2e-2
+    with pytest.raises(NotImplementedError, match="reconstruction head"):
+        eng.plan(B, H, W, True)

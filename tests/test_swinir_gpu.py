@@ -168,3 +168,39 @@ def test_golden_fixture_swinir_m_gray32():
         if abs(n - grads[k][0]) > 3e-2 * grads[k][0] + 1e-6:
             bad.append((k, n, grads[k][0]))
     assert not bad, bad[:6]
+
+
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4"])
+def test_golden_fixture_sr_heads(name):
+    """cfg3 / cfg5 architectures (reduced depth): x4 pixelshuffle and nearest+conv heads under no_grad vs the golden
+    output of the real reference module; bf16 result vs fp32 reference: 2e-2 max-abs and 0.02 dB PSNR (north_star)."""
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_swinir import SwinIR
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    case = gc.CASES[name]
+    sd, x, tgt = gc.state_and_io(case)
+    model = SwinIR(drop_path_rate=0.0, **case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().eval()
+    with torch.no_grad():
+        y = model(x.cuda()).cpu()
+    yr = torch.from_numpy(z["y"])
+    assert y.shape == yr.shape
+    assert (y - yr).abs().max().item() < 2e-2
+    assert abs(gc.psnr_uint8(y, tgt) - gc.psnr_uint8(yr, tgt)) < 0.02
+
+
+def test_sr_x4_full_size_cfg3():
+    """cfg3 shape: SwinIR-M x4 pixelshuffle, batch 32 of 3x64x64 LR patches, no_grad; batch-split invariance."""
+    from kair_b200.network_swinir import SwinIR
+    torch.manual_seed(0)
+    model = SwinIR(upscale=4, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                   num_heads=[6] * 6, mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv").cuda().eval()
+    x = torch.rand(32, 3, 64, 64, device="cuda")
+    with torch.no_grad():
+        y = model(x)
+        y4 = model(x[4:8])
+    assert y.shape == (32, 3, 256, 256) and torch.isfinite(y).all()
+    assert torch.equal(y[4:8], y4)
