@@ -24,6 +24,12 @@ import torch.nn as nn
 from . import ops as _real_ops
 
 
+def _conv_tile(n):
+    """N tile of the 3x3 implicit GEMMs: weights of >= 128-channel layers are streamed through a shared-memory ring,
+    where 128-wide tiles leave room for a deep enough ring"""
+    return _bn_tile(n) if n < 256 else (128 if n % 128 == 0 else _bn_tile(n))
+
+
 def _bn_tile(n):
     """N tile of the tcgen05 GEMMs for an n-column output (n is a multiple of 64)."""
     for bn in (256, 192, 128, 64):
@@ -315,17 +321,25 @@ class _DnCNNPlan(_PlanBase):
         df = f32(T, nc) if bn_live else None
         live = lambda s: s.bn is not None and bn_live
         bwd = []
-        bwd.append(o.build_conv_out_wgrad(self.dout, A(Lb), tail.conv.weight, G(tail.conv.weight),
-                                          G(tail.conv.bias) if tail.conv.bias is not None else None, C=nc, pitch=nc,
-                                          out_scale=-1.0))
+        # thin tail / head convolutions as tensor-core GEMMs over the 9-tap expansion of the <= 4 image channels
+        # (columns tap*7 + c, K padded to 64): d(out) expanded with dir=-1 serves the tail's dgrad and wgrad
+        dsh, clT, dWcl, csum = bf(T, 64), bf(nc, 64), f32(nc, 64), f32(64)
+        xcol, dWcf = bf(T, 64), f32(1, nc, 64)
+        self.zero_before_bwd += [dWcl, csum, dWcf]
+        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=-1.0))   # out = x - n
+        bwd.append(o.build_conv_out_pack(mode=0, co=cout, C=nc, cpad=7, W=tail.conv.weight, Wt=clT))
+        bwd.append(o.build_gemm_nt(A(Lb), dsh, dWcl, n1=nc, n2=64, bn=64))
+        bwd.append(o.build_conv_out_pack(mode=1, co=cout, C=nc, cpad=7, D=dWcl, dW=G(tail.conv.weight)))
+        if tail.conv.bias is not None:
+            bwd.append(o.build_colsum(dsh, csum, C=64))
+            bwd.append(o.build_copy(G(tail.conv.bias), csum[4 * 7:4 * 7 + cout]))
         # gradient w.r.t. the last body output; the activation mask is applied here unless that stage has a live BN
         last = body[-1]
         if live(last):
-            bwd.append(o.build_conv_out_dgrad(self.dout, tail.conv.weight, C=nc, pitch=nc, out_scale=-1.0, dfeat_f32=df))
+            bwd.append(o.build_gemm_tn(dsh, clT, N=nc, K=64, bn=bn, outF=df))
         else:
-            bwd.append(o.build_conv_out_dgrad(self.dout, tail.conv.weight, C=nc, pitch=nc, out_scale=-1.0,
-                                              dfeat_bf16=d[0], mask=A(Lb) if last.slope is not None else None,
-                                              mask_slope=last.slope or 0.0))
+            bwd.append(o.build_gemm_tn(dsh, clT, N=nc, K=64, bn=bn, outB=d[0],
+                                       aux=A(Lb) if last.slope is not None else None, act_slope=last.slope or 0.0))
         cur = 0
         for i in reversed(range(Lb)):
             s = body[i]
@@ -349,9 +363,11 @@ class _DnCNNPlan(_PlanBase):
                 bwd.append(o.build_gemm_tn(g, Wt["WpT"][i], N=nc, K=nc, bn=bn, conv=geo, outB=d[cur ^ 1],
                                            aux=A(i) if prev.slope is not None else None, act_slope=prev.slope or 0.0))
             cur ^= 1
-        bwd.append(o.build_conv_in_wgrad(self.img, head.conv.weight, zc_in, 1.0, G(head.conv.weight),
-                                         G(head.conv.bias) if head.conv.bias is not None else None, O=nc, O_pad=nc,
-                                         pitch=nc, dy_bf16=d[cur]))
+        bwd.append(o.build_im2col3x3(self.img, xcol, cpad=7, direction=1, mean=zc_in, scale=1.0, ones_col=4 * 7 + cin))
+        bwd.append(o.build_gemm_nt(d[cur], xcol, dWcf[0], n1=nc, n2=64, bn=64))
+        bwd.append(o.build_unpack_conv_grad(dWcf, [G(head.conv.weight)],
+                                            [G(head.conv.bias)] if head.conv.bias is not None else None, O=nc, I=cin,
+                                            I_pad=7, ones_col=cin, center_tap=4, dwp_pitch=64))
         bwd.append(o.build_unpack_conv_grad(dWp, [G(s.conv.weight) for s in body], None, O=nc, I=nc, I_pad=nc))
         self.bwd = bwd
         self._finish(eng)
@@ -500,7 +516,7 @@ class _UNetResPlan(_PlanBase):
         zc, zc_out = f32(cin), f32(cout)
         geos = [(B, H >> l, W >> l) for l in range(4)]
         Ts = [g[0] * g[1] * g[2] for g in geos]
-        bns = [_bn_tile(c) for c in nc]
+        bns = [_conv_tile(c) for c in nc]
 
         # fp32 residual streams: two rotating buffers per level + the skip features kept for the up path
         rot = [[f32(Ts[l], nc[l]), f32(Ts[l], nc[l])] for l in range(4)]
@@ -601,12 +617,12 @@ class _UNetResPlan(_PlanBase):
             c1, c2 = R["convs"][k], R["convs"][k + 1]
             nf = gf[l][0] if cf is not gf[l][0] else gf[l][1]
             nb2 = gb[l][0] if cb is not gb[l][0] else gb[l][1]
-            bwd.append(o.build_gemm_nt(cb, hb_, dWres[l][k + 1], n1=nc[l], n2=nc[l], bn=bns[l], conv=geos[l]))
+            bwd.append(o.build_gemm_nt(cb, hb_, dWres[l][k + 1], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l]))
             if c2.bias is not None:
                 bwd.append(o.build_colsum(cb, G(c2.bias), C=nc[l]))
             bwd.append(o.build_gemm_tn(cb, R["WpT"][k + 1], N=nc[l], K=nc[l], bn=bns[l], conv=geos[l], outB=dh[l],
                                        aux=hb_, act_slope=spec.slope))
-            bwd.append(o.build_gemm_nt(dh[l], xb_, dWres[l][k], n1=nc[l], n2=nc[l], bn=bns[l], conv=geos[l]))
+            bwd.append(o.build_gemm_nt(dh[l], xb_, dWres[l][k], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l]))
             if c1.bias is not None:
                 bwd.append(o.build_colsum(dh[l], G(c1.bias), C=nc[l]))
             bwd.append(o.build_gemm_tn(dh[l], R["WpT"][k], N=nc[l], K=nc[l], bn=bns[l], conv=geos[l], resid=cf, outF=nf,
@@ -614,10 +630,17 @@ class _UNetResPlan(_PlanBase):
             return nf, nb2
 
         # tail: d(tail_in) feeds both the up-path output and the head feature (skip)
-        bwd.append(o.build_conv_out_wgrad(self.dout, tail_in, tail.weight, G(tail.weight), G(tail.bias), C=nc[0],
-                                          pitch=nc[0]))
-        bwd.append(o.build_conv_out_dgrad(self.dout, tail.weight, C=nc[0], pitch=nc[0], dfeat_f32=gskip[0],
-                                          dfeat_bf16=gskip_b))
+        dsh, clT, dWcl, csum = bf(Ts[0], 64), bf(nc[0], 64), f32(nc[0], 64), f32(64)
+        xcol, dWcf = bf(Ts[0], 64), f32(1, nc[0], 64)
+        self.zero_before_bwd += [dWcl, csum, dWcf]
+        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=1.0))
+        bwd.append(o.build_conv_out_pack(mode=0, co=cout, C=nc[0], cpad=7, W=tail.weight, Wt=clT))
+        bwd.append(o.build_gemm_nt(tail_in, dsh, dWcl, n1=nc[0], n2=64, bn=64))
+        bwd.append(o.build_conv_out_pack(mode=1, co=cout, C=nc[0], cpad=7, D=dWcl, dW=G(tail.weight)))
+        if tail.bias is not None:
+            bwd.append(o.build_colsum(dsh, csum, C=64))
+            bwd.append(o.build_copy(G(tail.bias), csum[4 * 7:4 * 7 + cout]))
+        bwd.append(o.build_gemm_tn(dsh, clT, N=nc[0], K=64, bn=bns[0], outF=gskip[0], outB=gskip_b))
         cf, cb = gskip[0], gskip_b
         entries = list(saved)
         # index ranges of `saved`: down path blocks per level, body, up path blocks per level (3 -> 1)
@@ -656,9 +679,11 @@ class _UNetResPlan(_PlanBase):
                 cf, cb = res_block_bwd(e, cf, cb)
             pos -= n_dn
         assert pos == 0
-        bwd.append(o.build_add_inplace(cf, gskip[0], None))
-        bwd.append(o.build_conv_in_wgrad(self.img, head.weight, zc, 1.0, G(head.weight), G(head.bias), O=nc[0],
-                                         O_pad=nc[0], pitch=nc[0], dy_f32=cf))
+        bwd.append(o.build_add_inplace(cf, gskip[0], cb))
+        bwd.append(o.build_im2col3x3(self.img, xcol, cpad=7, direction=1, mean=zc, scale=1.0, ones_col=4 * 7 + cin))
+        bwd.append(o.build_gemm_nt(cb, xcol, dWcf[0], n1=nc[0], n2=64, bn=64))
+        bwd.append(o.build_unpack_conv_grad(dWcf, [G(head.weight)], [G(head.bias)] if head.bias is not None else None,
+                                            O=nc[0], I=cin, I_pad=7, ones_col=cin, center_tap=4, dwp_pitch=64))
         for l in range(4):
             convs = Wt["res"][l]["convs"]
             if convs:

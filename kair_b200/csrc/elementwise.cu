@@ -363,46 +363,80 @@ int layernorm_bwd_launch(const kair_layernorm_bwd_args& a, cudaStream_t st) {
 // ------------------------------------------------------------------------------------------------ thin convolutions
 constexpr int CI_MAX = 4;  // image-side channel count handled by the SIMT convolutions
 
-// conv_in: NCHW fp32 image (B, ci, H, W) -> token features [T][pitch]; one warp per pixel, lanes over outputs.
+// conv_in: NCHW fp32 image (B, ci, H, W) -> token features [T][pitch]; one thread per (pixel, 8 consecutive outputs):
+// every thread is independent (no reductions), its 9*ci image loads are issued together, the weights are read from
+// shared memory as float4 pairs and the result leaves as one 16-byte bf16 / two 16-byte fp32 stores.
 //   feat[t][o] = act( b[o] + sum_{c,tap} W[o][c][tap] * ((img[c][p+tap] - mean[c]) * range) )
 __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
-  extern __shared__ float sw[];  // [ci*9][O_pad] weights, then [O_pad] bias
+  extern __shared__ float sw[];  // [ci*9][P8] weights, then [P8] bias; P8 = pitch rounded to 8
   const int K = a.ci * 9;
-  for (int e = threadIdx.x; e < K * a.O_pad; e += blockDim.x) {
-    const int o = e % a.O_pad, k = e / a.O_pad;
+  const int P8 = a.pitch;        // launcher guarantees pitch % 8 == 0
+  for (int e = threadIdx.x; e < K * P8; e += blockDim.x) {
+    const int o = e % P8, k = e / P8;
     sw[e] = o < a.O ? a.W[(size_t)o * K + k] : 0.f;
   }
-  float* sbias = sw + K * a.O_pad;
-  for (int o = threadIdx.x; o < a.O_pad; o += blockDim.x) sbias[o] = (o < a.O && a.b) ? a.b[o] : 0.f;
+  float* sbias = sw + K * P8;
+  for (int o = threadIdx.x; o < P8; o += blockDim.x) sbias[o] = (o < a.O && a.b) ? a.b[o] : 0.f;
   __syncthreads();
-  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const int og = P8 >> 3;  // output groups per pixel
   const long long T = (long long)a.batch * a.H * a.Wd;
-  for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
+  const long long n = T * og;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(e % og);
+    const long long t = e / og;
     const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
     float in[CI_MAX * 9];
 #pragma unroll
     for (int c = 0; c < CI_MAX; ++c) {
-      if (c >= a.ci) break;
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
         float v = 0.f;
-        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
-          v = a.img[(((size_t)b * a.ci + c) * a.H + hh) * a.Wd + ww];
+        if (c < a.ci && hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+          v = __ldg(a.img + (((size_t)b * a.ci + c) * a.H + hh) * a.Wd + ww);
           v = (v - a.mean[c]) * a.range;
         }
         in[c * 9 + tap] = v;
       }
     }
-    for (int o = lane; o < a.pitch; o += 32) {
-      float acc = 0.f;
-      if (o < a.O) {
-        acc = sbias[o];
-        for (int k = 0; k < K; ++k) acc += sw[k * a.O_pad + o] * in[k];
-        if (a.act == KAIR_ACT_LRELU) acc = acc > 0.f ? acc : acc * a.act_slope;
+    float acc[8];
+    {
+      const float4 b0 = *reinterpret_cast<const float4*>(sbias + 8 * g);
+      const float4 b1 = *reinterpret_cast<const float4*>(sbias + 8 * g + 4);
+      acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+    }
+#pragma unroll
+    for (int c = 0; c < CI_MAX; ++c) {
+      if (c >= a.ci) break;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const float x = in[c * 9 + tap];
+        const float* wr = sw + (c * 9 + tap) * P8 + 8 * g;
+        const float4 w0 = *reinterpret_cast<const float4*>(wr);
+        const float4 w1 = *reinterpret_cast<const float4*>(wr + 4);
+        acc[0] += w0.x * x; acc[1] += w0.y * x; acc[2] += w0.z * x; acc[3] += w0.w * x;
+        acc[4] += w1.x * x; acc[5] += w1.y * x; acc[6] += w1.z * x; acc[7] += w1.w * x;
       }
-      if (a.out_f32) a.out_f32[t * a.pitch + o] = acc;
-      if (a.out_bf16) reinterpret_cast<bf16*>(a.out_bf16)[t * a.pitch + o] = __float2bfloat16(o == a.ones_col ? 1.0f : acc);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int o = 8 * g + i;
+      if (o >= a.O) acc[i] = 0.f;
+      else if (a.act == KAIR_ACT_LRELU) acc[i] = acc[i] > 0.f ? acc[i] : acc[i] * a.act_slope;
+    }
+    const long long off = t * a.pitch + 8 * g;
+    if (a.out_f32) {
+      reinterpret_cast<float4*>(a.out_f32 + off)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      reinterpret_cast<float4*>(a.out_f32 + off)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+    if (a.out_bf16) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (8 * g + i == a.ones_col) acc[i] = 1.0f;
+      uint4 o4;
+      o4.x = pack_bf16x2(acc[0], acc[1]); o4.y = pack_bf16x2(acc[2], acc[3]);
+      o4.z = pack_bf16x2(acc[4], acc[5]); o4.w = pack_bf16x2(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.out_bf16) + off) = o4;
     }
   }
 }
@@ -410,10 +444,13 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
 int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st) {
   KB_CHECK(a.img && a.W && a.mean, "kair_conv_in_fwd: null pointer");
   KB_CHECK(a.ci >= 1 && a.ci <= CI_MAX, "kair_conv_in_fwd: ci=%d unsupported (max %d)", a.ci, CI_MAX);
-  KB_CHECK(a.O_pad >= a.O && a.pitch >= a.O, "kair_conv_in_fwd: bad padding");
-  size_t smem = ((size_t)a.ci * 9 * a.O_pad + a.O_pad) * 4;
+  KB_CHECK(a.O_pad >= a.O && a.pitch >= a.O && a.pitch % 8 == 0, "kair_conv_in_fwd: pitch must be a multiple of 8, >= O");
+  size_t smem = ((size_t)a.ci * 9 * a.pitch + a.pitch) * 4;
   KB_CHECK(smem <= 48 * 1024, "kair_conv_in_fwd: weights do not fit in shared memory");
-  conv_in_fwd_kernel<<<sm_count() * 4, 256, smem, st>>>(a);
+  const long long n = (long long)a.batch * a.H * a.Wd * (a.pitch >> 3);
+  long long blocks = (n + 255) / 256;
+  if (blocks > (long long)sm_count() * 8) blocks = (long long)sm_count() * 8;
+  conv_in_fwd_kernel<<<(int)blocks, 256, smem, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -470,7 +507,10 @@ int conv_in_wgrad_launch(const kair_conv_in_args& a, cudaStream_t st) {
   return 0;
 }
 
-// conv_out: token features bf16 [T][pitch] (C channels) -> NCHW fp32 image (B, co, H, W); one warp per pixel.
+// conv_out: token features bf16 [T][pitch] (C channels) -> NCHW fp32 image (B, co, H, W).
+// 8 lanes per pixel (a warp covers 4 consecutive pixels): lane j of a pixel owns the 16-byte channel chunks
+// j, j+8, ...; the 9 tap rows of a pixel are fetched with independent 16-byte loads issued before any arithmetic
+// (memory-level parallelism instead of one dependent load chain per warp), partial sums meet in 3 shuffle steps.
 //   out[c][p] = (b[c] + sum_{tap,k} W[c][k][tap] * feat[p+tap][k] + skip_scale * skip[c][p]) * out_scale + out_mean[c]
 __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
   extern __shared__ float sw[];  // [co][9][C_pad]
@@ -480,33 +520,58 @@ __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
     sw[e] = k < a.C ? a.W[((size_t)c * a.C + k) * 9 + tap] : 0.f;
   }
   __syncthreads();
-  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const int sub = threadIdx.x & 7;
   const long long T = (long long)a.batch * a.H * a.Wd;
+  const long long groups = (T + 3) / 4;  // 4 pixels per warp iteration
+  const int warps = blockDim.x >> 5;
   const bf16* feat = reinterpret_cast<const bf16*>(a.feat);
-  for (long long t = (long long)blockIdx.x * warps + (threadIdx.x >> 5); t < T; t += (long long)gridDim.x * warps) {
-    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+  const int chunks = (a.C + 7) >> 3;     // 16-byte chunks per row that hold real channels
+  for (long long gidx = (long long)blockIdx.x * warps + (threadIdx.x >> 5); gidx < groups; gidx += (long long)gridDim.x * warps) {
+    const long long t = gidx * 4 + ((threadIdx.x & 31) >> 3);
+    const bool live = t < T;
+    const long long tt = live ? t : T - 1;
+    const int w = (int)(tt % a.Wd), h = (int)((tt / a.Wd) % a.H), b = (int)(tt / ((long long)a.Wd * a.H));
     float acc[CI_MAX];
 #pragma unroll
     for (int c = 0; c < CI_MAX; ++c) acc[c] = 0.f;
-    for (int tap = 0; tap < 9; ++tap) {
-      const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
-      if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.Wd) continue;
-      const bf16* row = feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp;
-      for (int k = lane * 2; k < a.C; k += 64) {
-        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + k));
+    for (int ch = sub; ch < chunks; ch += 8) {
+      uint4 v[9];
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+        v[tap] = make_uint4(0u, 0u, 0u, 0u);
+        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd)
+          v[tap] = __ldg(reinterpret_cast<const uint4*>(feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp + ch * 8));
+      }
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const uint32_t wd[4] = {v[tap].x, v[tap].y, v[tap].z, v[tap].w};
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wd[i]));
+          f[2 * i] = f2.x;
+          f[2 * i + 1] = f2.y;
+        }
 #pragma unroll
         for (int c = 0; c < CI_MAX; ++c) {
           if (c >= a.co) break;
-          const float* wr = sw + (c * 9 + tap) * Cp + k;
-          acc[c] += wr[0] * f.x + wr[1] * f.y;
+          const float* wr = sw + (c * 9 + tap) * Cp + ch * 8;
+          const float4 w0 = *reinterpret_cast<const float4*>(wr);
+          const float4 w1 = *reinterpret_cast<const float4*>(wr + 4);
+          acc[c] += w0.x * f[0] + w0.y * f[1] + w0.z * f[2] + w0.w * f[3] + w1.x * f[4] + w1.y * f[5] + w1.z * f[6] +
+                    w1.w * f[7];
         }
       }
     }
 #pragma unroll
     for (int c = 0; c < CI_MAX; ++c) {
       if (c >= a.co) break;
-      float v = warp_sum(acc[c]);
-      if (lane == 0) {
+      float v = acc[c];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      if (sub == 0 && live) {
         v += a.b ? a.b[c] : 0.f;
         const size_t oi = (((size_t)b * a.co + c) * a.H + h) * a.Wd + w;
         if (a.skip) v += a.skip_scale * (a.skip[oi] - a.skip_mean[c]);
@@ -519,7 +584,7 @@ __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
 int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
   KB_CHECK(a.feat && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
   KB_CHECK(a.co >= 1 && a.co <= CI_MAX, "kair_conv_out_fwd: co=%d unsupported (max %d)", a.co, CI_MAX);
-  KB_CHECK(a.pitch % 2 == 0 && a.C % 2 == 0, "kair_conv_out_fwd: channel count must be even");
+  KB_CHECK(a.pitch % 8 == 0 && a.C <= a.pitch, "kair_conv_out_fwd: pitch must be a multiple of 8 channels, >= C");
   size_t smem = (size_t)a.co * 9 * a.pitch * 4;
   KB_CHECK(smem <= 96 * 1024, "kair_conv_out_fwd: weights do not fit in shared memory");
   static bool attr_set[64] = {false};
@@ -529,7 +594,11 @@ int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
     KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
     attr_set[dev & 63] = true;
   }
-  conv_out_fwd_kernel<<<sm_count() * 4, 256, smem, st>>>(a);
+  const long long groups = ((long long)a.batch * a.H * a.Wd + 3) / 4;
+  long long blocks = (groups + 7) / 8;
+  const long long cap = (long long)sm_count() * (smem > 32 * 1024 ? 2 : 6);
+  if (blocks > cap) blocks = cap;
+  conv_out_fwd_kernel<<<(int)blocks, 256, smem, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
 }

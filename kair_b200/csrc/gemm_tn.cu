@@ -41,6 +41,8 @@ struct TnParams {
   long long resid_pitch, aux_pitch;
   int tokens_per_sample;
   int M, m_tiles, n_tiles, kc, taps, stages;
+  int stages_b;  // conv with streamed weights: depth of the separate B ring
+  int a_stage;  // bytes of one A stage: 16 KiB (dense), 18 KiB (conv: 8 x 18 pixel halo column of one 64-channel slice)
   int n_valid, ones_col, act;
   int stg_warp, ringD, ringS, ringDist;
   int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs
@@ -132,16 +134,23 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
   constexpr int B_STAGE = BN * TN_BK * 2;
   const int k_total = p.kc * p.taps;
   uint8_t* stg_base = smem;
+  // conv mode: a stage is one x-shifted halo column [18 rows][8 px][64 ch] of the 8 x 16 pixel tile; its three
+  // y-shifted 128-row windows (start + dy * 1024 B) feed the taps (dy, dx), so every input element is brought into
+  // shared memory 3 times instead of 9 (the 64-channel-wide layers were bound by that fill rate)
+  // Streamed (non-resident) weights in conv mode travel through their own ring of single [BN x 64] tiles, so the A
+  // ring (stages x 18 KiB) and the B ring (stages_b x B_STAGE) are sized independently.
   uint8_t* a_base = smem + 8 * p.stg_warp;
-  uint8_t* b_base = a_base + p.stages * TN_A_STAGE;
-  uint8_t* misc = b_base + (kBRes ? k_total : p.stages) * B_STAGE;
+  uint8_t* b_base = a_base + p.stages * p.a_stage;
+  uint8_t* misc = b_base + (kBRes ? k_total : (kConv ? p.stages_b : p.stages)) * B_STAGE;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
   uint64_t* empty_bar = full_bar + TN_MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + TN_MAX_STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* bres_bar = tempty_bar + 2;
   uint64_t* ld_bar = bres_bar + 1;  // [8 epilogue warps][up to 6 ring buffers]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ld_bar + 48);
+  uint64_t* fullb_bar = ld_bar + 48;
+  uint64_t* emptyb_bar = fullb_bar + TN_MAX_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(emptyb_bar + TN_MAX_STAGES);
   float* xch = reinterpret_cast<float*>(misc + 1024);  // [2 slots][2 halves][2 values][128 rows] fp32 = 4 KiB
   float* bias_s = reinterpret_cast<float*>(misc + 5120);  // this CTA's BN bias values (1 KiB)
 
@@ -164,6 +173,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       for (int i = 0; i < p.stages; ++i) {
         mbar_init(&full_bar[i], 1);
         mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < TN_MAX_STAGES; ++i) {
+        mbar_init(&fullb_bar[i], 1);
+        mbar_init(&emptyb_bar[i], 1);
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull_bar[i], 1);
@@ -198,26 +211,43 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         for (int kb = 0; kb < k_total; ++kb)
           tma_load_2d(b_base + kb * B_STAGE, &p.tmB, bres_bar, kb * TN_BK, n_tile * BN);
       }
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, stage_b = 0;
+      uint32_t phase = 0, phase_b = 0;
       for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride) {
         const TileCoord t = tile_coord<kConv>(p, m_tile);
-        for (int kb = 0; kb < k_total; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
-          if (kConv) {
-            int tap = kb / p.kc;
-            int kcc = kb - tap * p.kc;
-            int dy = tap / 3, dx = tap - dy * 3;
-            tma_load_4d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + dx - 1,
-                        t.h0 + dy - 1, t.b);
-          } else {
-            tma_load_2d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kb * TN_BK, t.w0);
+        if (kConv) {
+          for (int kb = 0; kb < p.kc * 3; ++kb) {
+            const int kcc = kb / 3, dx = kb - kcc * 3;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)p.a_stage);
+            tma_load_4d(a_base + stage * p.a_stage, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + dx - 1, t.h0 - 1, t.b);
+            if (!kBRes) {
+              for (int dy = 0; dy < 3; ++dy) {
+                mbar_wait(&emptyb_bar[stage_b], phase_b ^ 1);
+                mbar_arrive_expect_tx(&fullb_bar[stage_b], (uint32_t)B_STAGE);
+                tma_load_2d(b_base + stage_b * B_STAGE, &p.tmB, &fullb_bar[stage_b],
+                            ((dy * 3 + dx) * p.kc + kcc) * TN_BK, n_tile * BN);
+                if (++stage_b == p.stages_b) {
+                  stage_b = 0;
+                  phase_b ^= 1;
+                }
+              }
+            }
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
-          if (!kBRes) tma_load_2d(b_base + stage * B_STAGE, &p.tmB, &full_bar[stage], kb * TN_BK, n_tile * BN);
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1;
+        } else {
+          for (int kb = 0; kb < k_total; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
+            tma_load_2d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kb * TN_BK, t.w0);
+            if (!kBRes) tma_load_2d(b_base + stage * B_STAGE, &p.tmB, &full_bar[stage], kb * TN_BK, n_tile * BN);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
       }
@@ -231,8 +261,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         mbar_wait(bres_bar, 0);
         tcgen05_fence_after();
       }
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, stage_b = 0;
+      uint32_t phase = 0, phase_b = 0;
       int it = 0;
       for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
         const int as = it & 1;
@@ -240,21 +270,58 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         mbar_wait(&tempty_bar[as], aphase ^ 1);
         tcgen05_fence_after();
         const uint32_t tacc = tmem_base + as * BN;
-        for (int kb = 0; kb < k_total; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tcgen05_fence_after();
-          const uint32_t a_addr = smem_u32(a_base + stage * TN_A_STAGE);
-          const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : stage) * B_STAGE);
+        if (kConv) {
+          for (int kb = 0; kb < p.kc * 3; ++kb) {
+            const int kcc = kb / 3, dx = kb - kcc * 3;
+            mbar_wait(&full_bar[stage], phase);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(a_base + stage * p.a_stage);
+            for (int dy = 0; dy < 3; ++dy) {
+              uint32_t b_addr;
+              if (kBRes) {
+                b_addr = smem_u32(b_base + ((dy * 3 + dx) * p.kc + kcc) * B_STAGE);
+              } else {
+                mbar_wait(&fullb_bar[stage_b], phase_b);
+                tcgen05_fence_after();
+                b_addr = smem_u32(b_base + stage_b * B_STAGE);
+              }
 #pragma unroll
-          for (int k = 0; k < TN_BK / 16; ++k) {
-            if (p.dbg & 2) continue;
-            umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
-                        (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < TN_BK / 16; ++k) {
+                if (p.dbg & 2) continue;
+                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + dy * 1024 + k * 32),
+                            make_desc_kmajor_sw128(b_addr + k * 32), idesc, (kb | dy | k) != 0 ? 1u : 0u);
+              }
+              if (!kBRes) {
+                umma_commit(&emptyb_bar[stage_b]);
+                if (++stage_b == p.stages_b) {
+                  stage_b = 0;
+                  phase_b ^= 1;
+                }
+              }
+            }
+            umma_commit(&empty_bar[stage]);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
-          umma_commit(&empty_bar[stage]);
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1;
+        } else {
+          for (int kb = 0; kb < k_total; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(a_base + stage * TN_A_STAGE);
+            const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : stage) * B_STAGE);
+#pragma unroll
+            for (int k = 0; k < TN_BK / 16; ++k) {
+              if (p.dbg & 2) continue;
+              umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
+                          (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[stage]);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
         umma_commit(&tfull_bar[as]);
@@ -725,13 +792,6 @@ static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool b
   return -1;
 }
 
-static int conv_tile_w(int W) {
-  // widest power-of-two tile row <= min(W, 128); the tile is TW x (128/TW) pixels
-  int tw = 128;
-  while (tw > 8 && tw > W) tw >>= 1;
-  return tw;
-}
-
 int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   KB_CHECK(a.A && a.B, "kair_gemm_tn: null operand");
   KB_CHECK(a.K > 0 && a.K % 64 == 0, "kair_gemm_tn: K=%d must be a positive multiple of 64", a.K);
@@ -781,14 +841,14 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
              "kair_gemm_tn: conv geometry %dx%dx%d does not match M=%d", a.batch, a.H, a.W, a.M);
     p.H = a.H;
     p.W = a.W;
-    p.TW = conv_tile_w(a.W);
-    p.TH = 128 / p.TW;
+    p.TW = 8;    // 8 x 16 pixel tiles: each 8-row UMMA atom is one tile row, so y shifts are whole-atom offsets
+    p.TH = 16;
     p.tiles_w = (a.W + p.TW - 1) / p.TW;
     p.tiles_h = (a.H + p.TH - 1) / p.TH;
     p.m_tiles = a.batch * p.tiles_w * p.tiles_h;
     uint64_t dims[4] = {(uint64_t)a.K, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
     uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.a_pitch * 2 * a.W, (uint64_t)a.a_pitch * 2 * a.W * a.H};
-    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH, 1};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH + 2, 1};
     if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.A, dims, str, box, nullptr,
                   CU_TENSOR_MAP_SWIZZLE_128B))
       return -2;
@@ -847,23 +907,35 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF && !lin_aux) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
   const int stg_bytes = 8 * p.stg_warp;
   const int budget = 232448 - 1024 - stg_bytes - TN_MISC_BYTES;
+  p.a_stage = a.conv ? (p.TH + 2) * p.TW * 128 : TN_A_STAGE;
   bool bres = false;
-  int stages = 0;
+  int stages = 0, stages_b = 0;
   {
     long long bres_bytes = (long long)k_total * b_stage;
-    int st_res = (int)((budget - bres_bytes) / TN_A_STAGE);
+    int st_res = (int)((budget - bres_bytes) / p.a_stage);
     if (bres_bytes < budget && st_res >= 3) {
       bres = true;
       stages = st_res;
+    } else if (a.conv) {
+      // separate rings: 2-3 halo stages, the rest of the budget for streamed weight tiles
+      stages = 3;
+      stages_b = (budget - stages * p.a_stage) / b_stage;
+      if (stages_b < 3) {
+        stages = 2;
+        stages_b = (budget - stages * p.a_stage) / b_stage;
+      }
+      if (stages_b > TN_MAX_STAGES) stages_b = TN_MAX_STAGES;
+      KB_CHECK(stages_b >= 2, "kair_gemm_tn: not enough shared memory for streamed conv weights at bn=%d", a.bn);
     } else {
-      stages = budget / (TN_A_STAGE + b_stage);
+      stages = budget / (p.a_stage + b_stage);
     }
   }
   if (stages > TN_MAX_STAGES) stages = TN_MAX_STAGES;
   KB_CHECK(stages >= 2, "kair_gemm_tn: not enough shared memory for bn=%d", a.bn);
   p.stages = stages;
-  size_t smem = 1024 + stg_bytes + (size_t)stages * TN_A_STAGE +
-                (size_t)(bres ? k_total : stages) * b_stage + TN_MISC_BYTES;
+  p.stages_b = stages_b;
+  size_t smem = 1024 + stg_bytes + (size_t)stages * p.a_stage +
+                (size_t)(bres ? k_total : (a.conv ? stages_b : stages)) * b_stage + TN_MISC_BYTES;
 
   int nsm = sm_count();
   long long total_tiles = (long long)p.m_tiles * p.n_tiles;

@@ -490,6 +490,12 @@ def build_upsample_nearest2(x, out, *, batch, H, W, C):
     return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2))
 
 
+def build_copy(dst, src):
+    """dst <- src on the current stream (device-to-device plumbing for a handful of values, e.g. a bias gradient
+    picked out of a column-sum vector); no kernel of ours is involved."""
+    return _RawLaunch("copy", lambda stream: (dst.copy_(src), 0)[1], keep=(dst, src))
+
+
 # ------------------------------------------------------------------------------------------------ lifetimes
 # A Launch stores raw device addresses, so it must own a reference to every tensor it points into: the plan's
 # workspace tensors are otherwise free to be garbage-collected (and their memory reused) once the builder returns.

@@ -628,3 +628,7 @@ def build_upsample_nearest2(x, out, *, batch, H, W, C):
         out.reshape(batch * 4 * H * W, -1)[:, :C].copy_(v.reshape(-1, C))
 
     return EmuLaunch("kair_upsample_nearest2", run)
+
+
+def build_copy(dst, src):
+    return EmuLaunch("copy", lambda: dst.copy_(src))
