@@ -241,6 +241,7 @@ class SwinIR(nn.Module):
         self._drop_rates = dpr
         self._engine = None
         self._engine_key = None
+        self._ops = None   # test hook: tests/emu_ops.py replays the launch lists on CPU (host-logic / DDP tests)
 
     def _init_weights(self, m):
         if isinstance(m, nn.Linear):
@@ -271,12 +272,12 @@ class SwinIR(nn.Module):
         params = dict(self.named_parameters())
         key = (str(device),) + tuple(p.data_ptr() for p in params.values())
         if self._engine is None or self._engine_key != key:
-            self._engine = SwinIREngine(self._spec, params, device)
+            self._engine = SwinIREngine(self._spec, params, device, ops=self._ops)
             self._engine_key = key
         return self._engine
 
     def forward(self, x):
-        if not x.is_cuda:
+        if not x.is_cuda and self._ops is None:
             raise RuntimeError("kair_b200 SwinIR runs on sm_100a GPUs only; got a %s tensor (there is no CPU fallback)"
                                % x.device.type)
         H, W = x.shape[2:]

@@ -40,16 +40,17 @@ class UNetRes(nn.Module):
         self.m_tail = B.conv(nc[0], out_nc, bias=bias, mode="C")
         self._engine = None
         self._engine_key = None
+        self._ops = None   # test hook: tests/emu_ops.py replays the launch lists on CPU (host-logic / DDP tests)
 
     def engine(self, device):
         key = _tree_key(self, device)
         if self._engine is None or self._engine_key != key:
-            self._engine = UNetResEngine(parse_unetres(self), dict(self.named_parameters()), device)
+            self._engine = UNetResEngine(parse_unetres(self), dict(self.named_parameters()), device, ops=self._ops)
             self._engine_key = key
         return self._engine
 
     def forward(self, x0):
-        if not x0.is_cuda:
+        if not x0.is_cuda and self._ops is None:
             raise RuntimeError("kair_b200 UNetRes runs on sm_100a GPUs only; got a %s tensor (there is no CPU fallback)"
                                % x0.device.type)
         x0 = x0.float().contiguous()

@@ -2,6 +2,8 @@
 routing, BatchNorm bookkeeping), checked on CPU by replaying the launch lists through tests/emu_ops.py and comparing
 with the oracle (oracle/convnets_oracle.py, pinned against the reference modules) and, where the reference tree is
 mounted, with the unmodified reference modules themselves."""
+import os
+
 import pytest
 import torch
 
@@ -216,3 +218,24 @@ def test_dncnn_checkpoint_loads_strict():
     model.load_state_dict(torch.load(path, map_location="cpu"), strict=True)
     stages = parse_dncnn(model.model)
     assert len(stages) == 17 and all(s.bn is None for s in stages)
+
+
+@pytest.mark.skipif(not ref_loader.have_reference(), reason="reference tree not mounted")
+def test_install_routes_define_G_lookups():
+    """kair_b200.install(): the classes models/select_network.py:define_G imports at call time become the drop-ins
+    (run in a subprocess: it mutates sys.modules)."""
+    import subprocess
+    import sys
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import kair_b200\n"
+        "print(kair_b200.install())\n"
+        "from models.network_dncnn import DnCNN as a\n"
+        "from models.network_unet import UNetRes as b\n"
+        "from models.network_swinir import SwinIR as c\n"
+        "assert a.__module__ == 'kair_b200.network_dncnn' and b.__module__ == 'kair_b200.network_unet'\n"
+        "assert c.__module__ == 'kair_b200.network_swinir'\n"
+        "from models.network_dncnn import IRCNN\n"            # the rest of the reference module is untouched
+        "print('ok')\n") % (ref_loader.REF, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
