@@ -176,6 +176,22 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _wrap_dp(model, local_rank, use_ddp):
+    """Patch-batch data parallelism (models/model_base.py:113-119): torch DDP (--ddp) or the single flat all-reduce."""
+    if use_ddp:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        return DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
+    from kair_b200.parallel import FlatDataParallel
+    return FlatDataParallel(model)
+
+
+def _dp_name(world, use_ddp):
+    if world == 1:
+        return "dp1"
+    return "dp%d (%s)" % (world, "torch DDP" if use_ddp else "FlatDataParallel: one NCCL all-reduce of the flat "
+                          "gradient buffer per step")
+
+
 def _group_table(groups):
     return {k: {"n": v["count"], "ms": round(v["ms"], 4),
                 "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0,
@@ -207,8 +223,7 @@ def run_b200(args):
     model = SwinIR(**CFG2).to(dev).train()           # drop_path_rate: constructor default 0.1, as define_G leaves it
     net = model
     if world > 1:
-        from torch.nn.parallel import DistributedDataParallel as DDP
-        net = DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
+        net = _wrap_dp(model, local_rank, args.ddp)
     opt = torch.optim.Adam(model.parameters(), lr=2e-4, betas=(0.9, 0.999), weight_decay=0, fused=True)
 
     low_h, high_h = spect_batch(BATCH_PER_GPU, PATCH, 1234 + rank)
@@ -332,7 +347,7 @@ def run_b200(args):
             "metric": "SwinIR-M gray-DN train patches/s", "value": value, "unit": "patches/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "global_batch": patches, "parallelism": "dp%d" % world,
+            "config": {"workload": WORKLOAD, "global_batch": patches, "parallelism": _dp_name(world, args.ddp),
                        "drop_path_rate": 0.1, "optimizer": "Adam lr 2e-4", "loss": "Charbonnier eps 1e-9",
                        "l2": "per-step working set (~13 GB of activations) far exceeds the 126 MB L2; no flush needed"},
             "clocks": clocks,
@@ -505,8 +520,7 @@ def run_b200_workload(args):
                         upsample_mode="convtranspose", bias=False).to(dev).train()
         net = model
         if world > 1:
-            from torch.nn.parallel import DistributedDataParallel as DDP
-            net = DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
+            net = _wrap_dp(model, local_rank, args.ddp)
         opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)
         high = torch.rand(batch, 3, 128, 128, generator=g)
         sigma = torch.rand(batch, 1, 1, 1, generator=g) * 50.0 / 255.0
@@ -629,7 +643,9 @@ def run_b200_workload(args):
             "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if name == "cfg5" else "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": dict({"workload": WORKLOADS[name] % batch, "parallelism": "dp%d" % world, "weights": weights,
+            "config": dict({"workload": WORKLOADS[name] % batch, "parallelism": _dp_name(world, args.ddp) if name == "cfg4" else "replicas x%d, no collective" % world
+                            if name != "cfg5" else "tiles sharded over %d ranks, one reduce of the partial sums" % world,
+                            "weights": weights,
                             "l2": "inputs/activations of a step exceed the 126 MB L2 except cfg1 at batch 1 "
                                   "(whole net L2-resident by design); no flush"}, **extra_cfg),
             "clocks": clocks,
@@ -654,6 +670,8 @@ def main():
                     help="BASELINE.json config to run; cfg2 (SwinIR training) is the headline and the default")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override for cfg1/3/4, tiles per forward for cfg5")
     ap.add_argument("--image", type=int, default=0, help="cfg5: image side (default 2048)")
+    ap.add_argument("--ddp", action="store_true", help="N>1 training: wrap in torch DistributedDataParallel (the "
+                    "reference's wrapper) instead of kair_b200.parallel.FlatDataParallel")
     ap.add_argument("--ncu-slice", action="store_true", help="profiling aid: one launch per kernel group in a "
                     "cudaProfilerStart/Stop range")
     args = ap.parse_args()

@@ -84,6 +84,7 @@ class _EngineBase:
         self.ops = ops or _real_ops
         self._plans = {}
         self._names = {id(p): k for k, p in P.items()}
+        self.grad_hook = None   # callable(flat fp32 gradient buffer), e.g. parallel.allreduce_flat bound to the module
 
     def name_of(self, p):
         return self._names[id(p)]
@@ -125,6 +126,8 @@ class _PlanBase:
             t.zero_()
         for l in self.bwd:
             l.run(st)
+        if self.eng.grad_hook is not None:
+            self.eng.grad_hook(self.grads.flat)
         return self.grads.snapshot()
 
 

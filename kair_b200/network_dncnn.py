@@ -10,6 +10,8 @@ working.  The children never run: forward() re-reads the tree (it may have been 
 import torch
 import torch.nn as nn
 
+from . import parallel as _parallel
+
 from . import basicblock as B
 from .convnet_engine import ConvNetFunction, DnCNNEngine, parse_dncnn
 
@@ -42,6 +44,7 @@ class DnCNN(nn.Module):
         if self._engine is None or self._engine_key != key:
             self._engine = DnCNNEngine(parse_dncnn(self.model), dict(self.named_parameters()), device, ops=self._ops)
             self._engine_key = key
+        self._engine.grad_hook = (lambda flat: _parallel.allreduce_flat(self, flat))
         return self._engine
 
     def forward(self, x):

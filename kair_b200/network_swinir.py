@@ -11,6 +11,8 @@ import math
 
 import torch
 import torch.nn as nn
+
+from . import parallel as _parallel
 import torch.nn.functional as F
 
 from .swinir_engine import SwinIREngine, SwinIRFunction, SwinIRSpec
@@ -274,6 +276,7 @@ class SwinIR(nn.Module):
         if self._engine is None or self._engine_key != key:
             self._engine = SwinIREngine(self._spec, params, device, ops=self._ops)
             self._engine_key = key
+        self._engine.grad_hook = (lambda flat: _parallel.allreduce_flat(self, flat))
         return self._engine
 
     def forward(self, x):

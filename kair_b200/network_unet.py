@@ -9,6 +9,8 @@ There is no CPU / PyTorch fallback.
 import torch
 import torch.nn as nn
 
+from . import parallel as _parallel
+
 from . import basicblock as B
 from .convnet_engine import ConvNetFunction, UNetResEngine, parse_unetres
 from .network_dncnn import _tree_key
@@ -47,6 +49,7 @@ class UNetRes(nn.Module):
         if self._engine is None or self._engine_key != key:
             self._engine = UNetResEngine(parse_unetres(self), dict(self.named_parameters()), device, ops=self._ops)
             self._engine_key = key
+        self._engine.grad_hook = (lambda flat: _parallel.allreduce_flat(self, flat))
         return self._engine
 
     def forward(self, x0):

@@ -109,6 +109,7 @@ class SwinIREngine:
                                  dtype=torch.float32, device=self.device)
         self._plans = {}
         self._weights = None
+        self.grad_hook = None   # callable(flat fp32 gradient buffer), e.g. parallel.allreduce_flat bound to the module
         self._build_maps()
 
     # ------------------------------------------------------------------------------------------ packing maps
@@ -507,6 +508,8 @@ class _Plan:
             t.zero_()
         for l in self.bwd:
             l.run(st)
+        if self.eng.grad_hook is not None:
+            self.eng.grad_hook(self.gflat)
         flat = self.gflat.clone()
         grads, off = [], 0
         for p in self.eng.P.values():

@@ -44,12 +44,16 @@ def _build(net):
     return model, x, tgt
 
 
-def _worker(rank, world, port, net, out_dir):
+def _worker(rank, world, port, net, out_dir, flat):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.set_num_threads(2)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     model, x, tgt = _build(net)
-    ddp = torch.nn.parallel.DistributedDataParallel(model, broadcast_buffers=False)
+    if flat:
+        from kair_b200.parallel import FlatDataParallel
+        ddp = FlatDataParallel(model)
+    else:
+        ddp = torch.nn.parallel.DistributedDataParallel(model, broadcast_buffers=False)
     n = x.shape[0] // world
     xs, ts = x[rank * n:(rank + 1) * n], tgt[rank * n:(rank + 1) * n]
     opt = torch.optim.SGD(model.parameters(), lr=0.1)
@@ -63,10 +67,12 @@ def _worker(rank, world, port, net, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("net", ["dncnn", "swinir"])
-def test_ddp_world2_matches_full_batch(net, tmp_path):
+@pytest.mark.parametrize("net,flat", [("dncnn", False), ("swinir", False), ("dncnn", True), ("swinir", True)])
+def test_ddp_world2_matches_full_batch(net, flat, tmp_path):
+    """flat=False: torch DistributedDataParallel (the reference's wrapper); flat=True: kair_b200.parallel
+    .FlatDataParallel (one all-reduce of the engine's flat gradient buffer)."""
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), net, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), net, str(tmp_path), flat), nprocs=world, join=True)
     r0, r1 = (torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r)) for r in range(world))
     for k in r0["grads"]:
         assert torch.equal(r0["grads"][k], r1["grads"][k]), k          # all-reduced: identical on both ranks
