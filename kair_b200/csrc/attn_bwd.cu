@@ -265,36 +265,40 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
             pr[32 + j] = __uint_as_float(r1[j]);
           }
         }
-        float mx = -INFINITY;
+        // four independent max / sum / delta chains (a 64-long dependent chain costs 64 x 4 cycles per row)
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int j = 0; j < 64; ++j) {
           const int qj = j >> 4;
           const int jy = (qj >> 1) * 4 + ((j & 15) >> 2);
           const int jx = (qj & 1) * 4 + (j & 3);
           pr[j] = pr[j] + tb[(7 - jy) * 15 + (7 - jx)] + madd[qj];
-          mx = fmaxf(mx, pr[j]);
+          mx4[j & 3] = fmaxf(mx4[j & 3], pr[j]);
         }
-        float sum = 0.f;
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        float sum4[4] = {0.f, 0.f, 0.f, 0.f};
         const float mb = mx * LOG2E;
 #pragma unroll
         for (int j = 0; j < 64; ++j) {
-          pr[j] = exp2f(pr[j] * LOG2E - mb);
-          sum += pr[j];
+          pr[j] = ex2_approx(fmaf(pr[j], LOG2E, -mb));
+          sum4[j & 3] += pr[j];
         }
+        const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
         const float inv = 1.0f / sum;
 #pragma unroll
         for (int j = 0; j < 64; ++j) pr[j] *= inv;
 
         // ---- C: delta = sum_j P_ij dP_ij
-        float delta = 0.f;
+        float dl4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t r[32];
           tmem_ld32(tW + 64 + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) delta += pr[c * 32 + j] * __uint_as_float(r[j]);
+          for (int j = 0; j < 32; ++j) dl4[j & 3] = fmaf(pr[c * 32 + j], __uint_as_float(r[j]), dl4[j & 3]);
         }
+        const float delta = (dl4[0] + dl4[1]) + (dl4[2] + dl4[3]);
 
         // ---- D: the P/dS tiles double as the previous iteration's output staging: wait for its TMA reads
         if (gtid == 0) tma_store_wait_read<0>();

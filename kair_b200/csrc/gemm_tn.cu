@@ -580,8 +580,14 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             for (int i = 0; i < 32; ++i) v[i] *= sa;
           }
           if (use_r) add_row_f32(v, buf);
+          {  // four independent partial sums: a single 32-long FADD chain costs 32 x 4 dependent cycles
+            float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) s1 += v[i];
+            for (int i = 0; i < 32; i += 4) {
+              p0 += v[i]; p1 += v[i + 1]; p2 += v[i + 2]; p3 += v[i + 3];
+            }
+            s1 += (p0 + p1) + (p2 + p3);
+          }
           {
             uint32_t r[32];
 #pragma unroll
@@ -607,11 +613,14 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           uint32_t r[32];
           tmem_ld32(tacc + c * 32, r);
           tmem_ld_wait();
+          float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float d = __uint_as_float(r[i]) - mean;
-            s2 += d * d;
+          for (int i = 0; i < 32; i += 4) {
+            const float d0 = __uint_as_float(r[i]) - mean, d1 = __uint_as_float(r[i + 1]) - mean;
+            const float d2 = __uint_as_float(r[i + 2]) - mean, d3 = __uint_as_float(r[i + 3]) - mean;
+            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2); q3 = fmaf(d3, d3, q3);
           }
+          s2 += (q0 + q1) + (q2 + q3);
         }
         float tot2;
         exchange2(s2, 0.f, tot2, dummy);
@@ -678,12 +687,15 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           uint32_t r[32];
           tmem_ld32(tacc + c * 32, r);
           tmem_ld_wait();
+          float p0 = 0.f, p1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float a0 = __uint_as_float(r[i]);
-            s1 += a0;
-            s2 += a0 * x[i];
+          for (int i = 0; i < 32; i += 2) {
+            const float a0 = __uint_as_float(r[i]), a1 = __uint_as_float(r[i + 1]);
+            p0 += a0; p1 += a1;
+            q0 = fmaf(a0, x[i], q0); q1 = fmaf(a1, x[i + 1], q1);
           }
+          s1 += p0 + p1;
+          s2 += q0 + q1;
           slot_end(false);
         }
         float t1, t2;
