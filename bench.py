@@ -192,6 +192,16 @@ def _dp_name(world, use_ddp):
                           "gradient buffer per step")
 
 
+def _ncu_traffic(tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of kernel group `tag`, from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json, written by tools/ncu_summary.py); None if not captured."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return d["bytes_per_launch"].get(tag)
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def _group_table(groups):
     return {k: {"n": v["count"], "ms": round(v["ms"], 4),
                 "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0,
@@ -325,7 +335,7 @@ def run_b200(args):
         peak_gbs = peaks.get("hbm_gbs") or 6500.0
         roof = profiling.roofline_of(top, peak_tf, peak_gbs)
         roof.update({
-                "traffic": None, "kernel": top_tag, "launches_per_step": top["count"],
+                "traffic": _ncu_traffic(top_tag), "kernel": top_tag, "launches_per_step": top["count"],
                 "avg_launch_ms": top["ms"] / top["count"], "share_of_kernel_time": top["ms"] / tot,
                 "algorithmic_bytes_per_launch": top["bytes"] / top["count"],
                 "algorithmic_flops_per_launch": top["flops"] / top["count"],
