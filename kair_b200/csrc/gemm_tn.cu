@@ -45,7 +45,8 @@ struct TnParams {
   int a_stage;  // bytes of one A stage: 16 KiB (dense), 18 KiB (conv: 8 x 18 pixel halo column of one 64-channel slice)
   int n_valid, ones_col, act;
   int stg_warp, ringD, ringS, ringDist;
-  int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs
+  int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs,
+            // 4 = LINEAR epilogue does the barrier handshake only, 8 = dense producer moves no A tiles
   float act_slope, ln_eps;
   int has_outB, has_outB2, has_outF;
   // conv geometry
@@ -241,6 +242,14 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         } else {
           for (int kb = 0; kb < k_total; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (p.dbg & 8) {  // ablation: no A traffic
+              mbar_arrive(&full_bar[stage]);
+              if (++stage == p.stages) {
+                stage = 0;
+                phase ^= 1;
+              }
+              continue;
+            }
             mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
             tma_load_2d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kb * TN_BK, t.w0);
             if (!kBRes) tma_load_2d(b_base + stage * B_STAGE, &p.tmB, &full_bar[stage], kb * TN_BK, n_tile * BN);
@@ -489,7 +498,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 
       if (EPI == KAIR_EPI_LINEAR) {
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        for (int c = 0; c < ((p.dbg & 4) ? 0 : NCH); ++c) {  // dbg 4: ablation, epilogue = barrier handshake only
           const int col = col_half + c * 32;
           const bool last = (c == NCH - 1);
           uint8_t* buf = slot_begin(!last || more_tiles, use_r, use_a, last ? t_next : t, last ? col_half : col + 32,
