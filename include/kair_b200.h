@@ -417,6 +417,19 @@ typedef struct kair_shuffle_args {
 int kair_pixel_shuffle(const kair_shuffle_args* args, void* stream);
 int kair_upsample_nearest2(const kair_shuffle_args* args, void* stream);
 
+/* UpsampleOneStep ('pixelshuffledirect', network_swinir.py:594-615, 819-822) tail: PixelShuffle(r) of the conv output
+ * straight into the NCHW fp32 image with the final affine of SwinIR.forward (:837):
+ *   out[b][c][r*h+dy][r*w+dx] = in[(b,h,w)][c*r*r + dy*r + dx] * scale + mean[c] */
+typedef struct kair_shuffle_out_args {
+  const void* in;          /* bf16 [B*H*W][in_pitch] */
+  float* out;              /* fp32 (B, co, r*H, r*W) */
+  const float* mean;       /* (co) */
+  int64_t in_pitch;
+  float scale;
+  int32_t batch, H, W, co, r;
+} kair_shuffle_out_args;
+int kair_pixel_shuffle_out(const kair_shuffle_out_args* args, void* stream);
+
 /* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);
 

@@ -32,6 +32,7 @@ int bn_bwd_apply_launch(const kair_bn_args& a, cudaStream_t st);
 int bn_fold_launch(const kair_bn_args& a, cudaStream_t st);
 int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st);
+int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 }
 
@@ -105,6 +106,7 @@ KB_WRAP(kair_bn_bwd_apply, kair_bn_args, bn_bwd_apply_launch)
 KB_WRAP(kair_bn_fold, kair_bn_args, bn_fold_launch)
 KB_WRAP(kair_pixel_shuffle, kair_shuffle_args, pixel_shuffle_launch)
 KB_WRAP(kair_upsample_nearest2, kair_shuffle_args, upsample_nearest2_launch)
+KB_WRAP(kair_pixel_shuffle_out, kair_shuffle_out_args, pixel_shuffle_out_launch)
 #undef KB_WRAP
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {

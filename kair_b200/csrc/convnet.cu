@@ -450,6 +450,31 @@ __global__ void upsample_nearest2_kernel(const kair_shuffle_args a) {
   }
 }
 
+// one thread per output pixel pair along x (coalesced fp32 stores; the bf16 row of an input pixel is L1-resident)
+__global__ void pixel_shuffle_out_kernel(const kair_shuffle_out_args a) {
+  const int r = a.r, Ho = a.H * r, Wo = a.W * r, rr = r * r;
+  const bf16* in = reinterpret_cast<const bf16*>(a.in);
+  const long long n = (long long)a.batch * a.co * Ho * Wo;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int wo = (int)(e % Wo), ho = (int)((e / Wo) % Ho);
+    const int c = (int)((e / ((long long)Wo * Ho)) % a.co);
+    const long long b = e / ((long long)Wo * Ho * a.co);
+    const long long ti = (b * a.H + ho / r) * a.W + wo / r;
+    const float v = __bfloat162float(in[ti * a.in_pitch + (long long)c * rr + (ho % r) * r + (wo % r)]);
+    a.out[e] = v * a.scale + a.mean[c];
+  }
+}
+
+int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.mean && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle_out: null pointer / empty");
+  KB_CHECK(a.r >= 1 && a.r <= 8 && a.co >= 1 && a.in_pitch >= (long long)a.co * a.r * a.r,
+           "kair_pixel_shuffle_out: bad geometry (r=%d, co=%d)", a.r, a.co);
+  const long long n = (long long)a.batch * a.co * a.H * a.W * a.r * a.r;
+  pixel_shuffle_out_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st) {
   KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle: null pointer / empty");
   KB_CHECK(a.r >= 2 && a.r <= 4 && a.C % 2 == 0 && a.out_pitch % 2 == 0 && a.in_pitch >= (long long)a.C * a.r * a.r &&

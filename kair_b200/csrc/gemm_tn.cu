@@ -789,8 +789,8 @@ static int launch_res(const TnParams& p, bool bres, int grid, size_t smem, cudaS
 }
 
 // Instantiated configurations (kept explicit to bound compile time):
-//   dense: every epilogue at BN=192 (SwinIR-M, C=180 padded to 192); LINEAR at BN 64/128/256
-//   conv : LINEAR at BN 64/128/192/256; RESID_LN at BN=192
+//   dense: every epilogue at BN=192 (SwinIR-M, C=180 padded to 192) and BN=64 (SwinIR-S, C=60); LINEAR at BN 64/128/256
+//   conv : LINEAR at BN 64/128/192/256; RESID_LN at BN=192 and 64
 static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool bres, int grid, size_t smem,
                            cudaStream_t st) {
 #define KB_CASE(BN_, EPI_, CONV_) \
@@ -808,6 +808,12 @@ static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool b
   KB_CASE(192, KAIR_EPI_LINEAR, true)
   KB_CASE(256, KAIR_EPI_LINEAR, true)
   KB_CASE(192, KAIR_EPI_RESID_LN, true)
+  // SwinIR-S (lightweight SR, embed_dim 60 -> 64 padded channels)
+  KB_CASE(64, KAIR_EPI_GELU, false)
+  KB_CASE(64, KAIR_EPI_RESID_LN, false)
+  KB_CASE(64, KAIR_EPI_DGELU, false)
+  KB_CASE(64, KAIR_EPI_LNBWD, false)
+  KB_CASE(64, KAIR_EPI_RESID_LN, true)
 #undef KB_CASE
   set_error("kair_gemm_tn: configuration bn=%d mode=%d conv=%d is not instantiated", bn, epi, (int)conv);
   return -1;
@@ -924,7 +930,9 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   const bool lin_aux = a.mode == KAIR_EPI_LINEAR && a.aux != nullptr;
   p.ringDist = (loads_r || lin_aux || a.mode == KAIR_EPI_DGELU || a.mode == KAIR_EPI_LNBWD) ? 1 : 0;
   if (a.mode == KAIR_EPI_GELU) { p.stg_warp = 8192; p.ringD = 2; p.ringS = 4096; p.ringDist = 0; }
-  if (a.mode == KAIR_EPI_DGELU) { p.stg_warp = 8192; p.ringD = 4; p.ringS = 2048; p.ringDist = 2; }
+  if (a.mode == KAIR_EPI_DGELU) {  // prefetch distance must not exceed the chunks per thread (bn / 64)
+    p.stg_warp = 8192; p.ringD = 4; p.ringS = 2048; p.ringDist = a.bn >= 128 ? 2 : 1;
+  }
   if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF && !lin_aux) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
   const int stg_bytes = 8 * p.stg_warp;
   const int budget = 232448 - 1024 - stg_bytes - TN_MISC_BYTES;

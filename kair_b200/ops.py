@@ -490,6 +490,19 @@ def build_upsample_nearest2(x, out, *, batch, H, W, C):
     return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2))
 
 
+def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
+    """out (B, co, r*H, r*W) fp32 = PixelShuffle(r)(x) * scale + mean[c]; x bf16 [B*H*W, >= co*r*r]."""
+    _req(x, torch.bfloat16, "in"); _req(out, torch.float32, "out"); _req(mean, torch.float32, "mean")
+    if not out.is_contiguous():
+        raise RuntimeError("kair_b200: pixel_shuffle_out needs a contiguous NCHW output")
+    a = _S["kair_shuffle_out_args"]()
+    setattr(a, "in", _ptr(x)); a.out = _ptr(out); a.mean = _ptr(mean)
+    a.in_pitch = _pitch(x); a.scale = scale
+    a.batch, a.co = out.shape[0], out.shape[1]
+    a.H, a.W, a.r = out.shape[2] // r, out.shape[3] // r, r
+    return Launch("kair_pixel_shuffle_out", a)
+
+
 def build_copy(dst, src):
     """dst <- src on the current stream (device-to-device plumbing for a handful of values, e.g. a bias gradient
     picked out of a column-sum vector); no kernel of ours is involved."""

@@ -19,7 +19,14 @@ import torch
 
 from . import ops as _real_ops
 
-_BN = 192  # N tile of the instantiated GEMM epilogues for SwinIR-M
+def _tile(n, fused=False):
+    """N tile of a GEMM with n output columns.  The fused epilogues (GELU, GELU', LayerNorm forward / backward) are
+    instantiated at 192 (SwinIR-M, C=180) and 64 (SwinIR-S, C=60); plain LINEAR and the weight-gradient GEMMs at
+    64 / 128 / 192 / 256."""
+    for bn in ((192, 64) if fused else (256, 192, 128, 64)):
+        if n % bn == 0:
+            return bn
+    raise NotImplementedError("kair_b200 SwinIR: no GEMM tile for %d columns" % n)
 
 
 def _round_up(x, m):
@@ -59,13 +66,15 @@ class SwinIRSpec:
         hd = self.C // nH
         if hd >= 32:
             bad("head_dim=%d must be < 32 (one padded column carries the proj bias gradient)" % hd)
-        if _round_up(self.C + 1, 64) != _BN or _round_up(self.hidden + 1, 64) % _BN:
-            bad("embed_dim=%d / mlp hidden=%d: only the C=180 tile configuration (Cp=192) is instantiated"
-                % (self.C, self.hidden))
+        if _round_up(self.C + 1, 64) not in (64, 192):
+            bad("embed_dim=%d: the LayerNorm epilogues are instantiated for 64 and 192 padded channels "
+                "(embed_dim 1..63 and 128..191, e.g. SwinIR-S 60 and SwinIR-M 180)" % self.C)
         if self.resi_connection != "1conv":
             bad("resi_connection='%s'" % self.resi_connection)
-        if self.upsampler not in ("", "pixelshuffle", "nearest+conv"):
+        if self.upsampler not in ("", "pixelshuffle", "pixelshuffledirect", "nearest+conv"):
             bad("upsampler='%s'" % self.upsampler)
+        if self.upsampler == "pixelshuffledirect" and not (1 <= self.upscale <= 8):
+            bad("pixelshuffledirect upscale=%d" % self.upscale)
         if self.upsampler == "pixelshuffle" and not (self.upscale in (2, 3, 4, 8)):
             bad("pixelshuffle upscale=%d" % self.upscale)
         if self.in_chans > 4:
@@ -177,7 +186,13 @@ class SwinIREngine:
         ]
         # reconstruction heads (network_swinir.py:740-760): num_feat = 64
         up = self.spec.upsampler
-        if up:
+        if up == "pixelshuffledirect":
+            # UpsampleOneStep (network_swinir.py:594-609): one conv embed_dim -> upscale^2 * num_out_ch, rows padded to 64
+            no = self.spec.upscale ** 2 * self.spec.in_chans
+            W["psd"], W["bpsd"] = bf(1, _round_up(no, 64), 9 * Cp), f32(1, _round_up(no, 64))
+            W["pack"].append(o.build_pack_conv([P["upsample.0.weight"]], [P["upsample.0.bias"]],
+                                               W["psd"], None, W["bpsd"], O=no, I=C, I_pad=Cp))
+        elif up:
             nf = 64
             W["cbu"], W["bcbu"] = bf(1, nf, 9 * Cp), f32(1, nf)
             W["pack"].append(o.build_pack_conv([P["conv_before_upsample.0.weight"]], [P["conv_before_upsample.0.bias"]],
@@ -269,7 +284,7 @@ class _Plan:
         dpm = lambda l: self.dp[L + l] if train else None
 
         cf_w, cf_b = P["conv_first.weight"], P["conv_first.bias"]
-        cl_w, cl_b = P["conv_last.weight"], P["conv_last.bias"]
+        cl_w, cl_b = (P["conv_last.weight"], P["conv_last.bias"]) if up != "pixelshuffledirect" else (None, None)
         tables = [P[b + "attn.relative_position_bias_table"] for b in eng._block_names()]
         mean_t = eng.mean
         rng = s.img_range
@@ -291,43 +306,48 @@ class _Plan:
             for j in range(depth):
                 S = blocks[l]
                 shift = s.ws // 2 if j % 2 == 1 else 0
-                fwd.append(o.build_gemm_tn(S.xh1, Wt["qkv"][l], N=QP, K=Cp, bn=_BN, bias=Wt["bqkv"][l], outB=S.qkv))
+                fwd.append(o.build_gemm_tn(S.xh1, Wt["qkv"][l], N=QP, K=Cp, bn=_tile(QP), bias=Wt["bqkv"][l], outB=S.qkv))
                 fwd.append(o.build_window_attn_fwd(S.qkv, tables[l], S.att, batch=B, H=H, W=W, num_heads=eng.nH,
                                                    window=s.ws, shift=shift))
-                fwd.append(o.build_gemm_tn(S.att, Wt["proj"][l], N=Cp, K=HP, bn=_BN, mode=o.EPI_RESID_LN,
+                fwd.append(o.build_gemm_tn(S.att, Wt["proj"][l], N=Cp, K=HP, bn=_tile(Cp, True), mode=o.EPI_RESID_LN,
                                            bias=Wt["bproj"][l], resid=xin, outF=xs[0], outB=S.xh2, rowstat=S.r2,
                                            n_valid=C, ones_col=C, acc_scale=dpa(l), tokens_per_sample=tps))
-                fwd.append(o.build_gemm_tn(S.xh2, Wt["fc1"][l], N=Fp, K=Cp, bn=_BN, mode=o.EPI_GELU,
+                fwd.append(o.build_gemm_tn(S.xh2, Wt["fc1"][l], N=Fp, K=Cp, bn=_tile(Fp, True), mode=o.EPI_GELU,
                                            bias=Wt["bfc1"][l], outB=S.g, outB2=S.u, ones_col=s.hidden))
                 if j < depth - 1:
                     nxt = blocks[l + 1]
-                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_RESID_LN,
+                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_tile(Cp, True), mode=o.EPI_RESID_LN,
                                                bias=Wt["bfc2"][l], resid=xs[0], outF=xs[1], outB=nxt.xh1,
                                                rowstat=nxt.r1, n_valid=C, ones_col=C, acc_scale=dpm(l),
                                                tokens_per_sample=tps))
                     xin = xs[1]
                 else:
-                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_LINEAR,
+                    fwd.append(o.build_gemm_tn(S.g, Wt["fc2"][l], N=Cp, K=Fp, bn=_tile(Cp), mode=o.EPI_LINEAR,
                                                bias=Wt["bfc2"][l], resid=xs[0], outB=x2b[i], ones_col=C,
                                                acc_scale=dpm(l), tokens_per_sample=tps))
                 l += 1
             if i < nl - 1:
                 nxt = blocks[l]
                 t_next = tin[1] if t_cur is tin[0] else tin[0]
-                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_RESID_LN,
+                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_tile(Cp, True), conv=geo, mode=o.EPI_RESID_LN,
                                            bias=Wt["bconv"][i], resid=t_cur, outF=t_next, outB=nxt.xh1,
                                            rowstat=nxt.r1, n_valid=C, ones_col=C))
                 t_cur = t_next
             else:
-                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
+                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
                                            bias=Wt["bconv"][i], resid=t_cur, outF=tfin))
         fwd.append(o.build_layernorm_fwd(tfin, P["norm.weight"], P["norm.bias"], C=C, y_bf16=yb, mean=meanF,
                                          rstd=rstdF, ones_col=C))
-        fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, mode=o.EPI_LINEAR,
+        fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
                                    bias=Wt["bconv"][nl], resid=first, outB=resb, ones_col=C))
         if not up:
             fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
                                             skip=self.img, skip_mean=mean_t, skip_scale=rng))
+        elif up == "pixelshuffledirect":
+            no = Wt["psd"].shape[1]
+            u = bf(T, no)
+            fwd.append(o.build_gemm_tn(resb, Wt["psd"][0], N=no, K=Cp, bn=_tile(no), conv=geo, bias=Wt["bpsd"][0], outB=u))
+            fwd.append(o.build_pixel_shuffle_out(u, self.out, mean_t, r=s.upscale, scale=1.0 / rng))
         else:
             # conv_before_upsample + LeakyReLU(0.01), then the upsampling convolutions on 64 features
             nf = 64
@@ -395,12 +415,12 @@ class _Plan:
         self._thin = (dWcl,)
         bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=inv))
         bwd.append(o.build_conv_out_pack(mode=0, co=ci, C=C, cpad=7, W=cl_w, Wt=clT))
-        bwd.append(o.build_gemm_tn(dsh, clT, N=Cp, K=64, bn=_BN, outF=dresf, outB=dresb))
+        bwd.append(o.build_gemm_tn(dsh, clT, N=Cp, K=64, bn=_tile(Cp), outF=dresf, outB=dresb))
         bwd.append(o.build_gemm_nt(resb, dsh, dWcl, n1=Cp, n2=64, bn=64))
         bwd.append(o.build_conv_out_pack(mode=1, co=ci, C=C, cpad=7, D=dWcl, dW=G["conv_last.weight"],
                                          db=G["conv_last.bias"], ones_row=C))
-        bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_BN, conv=geo))
-        bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_BN, conv=geo, outB=dyb))
+        bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
+        bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, outB=dyb))
         dt = 2
         bwd.append(o.build_layernorm_bwd(tfin, meanF, rstdF, P["norm.weight"], G["norm.weight"], G["norm.bias"], C=C,
                                          dy_bf16=dyb, dx_f32=R[dt][0], dx_bf16=R[dt][1]))
@@ -408,29 +428,29 @@ class _Plan:
         for i in reversed(range(nl)):
             depth = s.depths[i]
             a, b = [k for k in range(3) if k != dt]
-            bwd.append(o.build_gemm_nt(R[dt][1], x2b[i], dWconv[i], n1=Cp, n2=Cp, bn=_BN, conv=geo))
-            bwd.append(o.build_gemm_tn(R[dt][1], Wt["convT"][i], N=Cp, K=Cp, bn=_BN, conv=geo, outF=R[a][0],
+            bwd.append(o.build_gemm_nt(R[dt][1], x2b[i], dWconv[i], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
+            bwd.append(o.build_gemm_tn(R[dt][1], Wt["convT"][i], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, outF=R[a][0],
                                        outB=R[a][1], outB_scale=dpm(l_end - 1), tokens_per_sample=tps))
             cur, oth = a, b
             for j in reversed(range(depth)):
                 l = l_end - depth + j
                 S = blocks[l]
-                bwd.append(o.build_gemm_nt(R[cur][1], S.g, dWfc2[l], n1=Cp, n2=Fp, bn=_BN))
-                bwd.append(o.build_gemm_tn(R[cur][1], Wt["fc2T"][l], N=Fp, K=Cp, bn=_BN, mode=o.EPI_DGELU, aux=S.u,
+                bwd.append(o.build_gemm_nt(R[cur][1], S.g, dWfc2[l], n1=Cp, n2=Fp, bn=_tile(Fp)))
+                bwd.append(o.build_gemm_tn(R[cur][1], Wt["fc2T"][l], N=Fp, K=Cp, bn=_tile(Fp, True), mode=o.EPI_DGELU, aux=S.u,
                                            outB=du))
-                bwd.append(o.build_gemm_nt(du, S.xh2, dWfc1[l], n1=Fp, n2=Cp, bn=_BN))
-                bwd.append(o.build_gemm_tn(du, Wt["fc1T"][l], N=Cp, K=Fp, bn=_BN, mode=o.EPI_LNBWD, aux=S.xh2,
+                bwd.append(o.build_gemm_nt(du, S.xh2, dWfc1[l], n1=Fp, n2=Cp, bn=_tile(Cp)))
+                bwd.append(o.build_gemm_tn(du, Wt["fc1T"][l], N=Cp, K=Fp, bn=_tile(Cp, True), mode=o.EPI_LNBWD, aux=S.xh2,
                                            rowstat=S.r2, resid=R[cur][0], outF=R[oth][0], outB=R[oth][1], n_valid=C,
                                            outB_scale=dpa(l), tokens_per_sample=tps))
                 cur, oth = oth, cur
-                bwd.append(o.build_gemm_nt(R[cur][1], S.att, dWproj[l], n1=Cp, n2=HP, bn=_BN))
-                bwd.append(o.build_gemm_tn(R[cur][1], Wt["projT"][l], N=HP, K=Cp, bn=_BN, outB=datt))
+                bwd.append(o.build_gemm_nt(R[cur][1], S.att, dWproj[l], n1=Cp, n2=HP, bn=_tile(HP)))
+                bwd.append(o.build_gemm_tn(R[cur][1], Wt["projT"][l], N=HP, K=Cp, bn=_tile(HP), outB=datt))
                 shift = s.ws // 2 if j % 2 == 1 else 0
                 bwd.append(o.build_window_attn_bwd(S.qkv, tables[l], datt, dqkv,
                                                    G[blk_names[l] + "attn.relative_position_bias_table"], batch=B,
                                                    H=H, W=W, num_heads=eng.nH, window=s.ws, shift=shift))
-                bwd.append(o.build_gemm_nt(dqkv, S.xh1, dWqkv[l], n1=QP, n2=Cp, bn=_BN))
-                bwd.append(o.build_gemm_tn(dqkv, Wt["qkvT"][l], N=Cp, K=QP, bn=_BN, mode=o.EPI_LNBWD, aux=S.xh1,
+                bwd.append(o.build_gemm_nt(dqkv, S.xh1, dWqkv[l], n1=QP, n2=Cp, bn=_tile(Cp)))
+                bwd.append(o.build_gemm_tn(dqkv, Wt["qkvT"][l], N=Cp, K=QP, bn=_tile(Cp, True), mode=o.EPI_LNBWD, aux=S.xh1,
                                            rowstat=S.r1, resid=R[cur][0], outF=R[oth][0], outB=R[oth][1], n_valid=C,
                                            outB_scale=(dpm(l - 1) if j > 0 else None), tokens_per_sample=tps))
                 cur, oth = oth, cur

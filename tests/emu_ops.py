@@ -632,3 +632,13 @@ def build_upsample_nearest2(x, out, *, batch, H, W, C):
 
 def build_copy(dst, src):
     return EmuLaunch("copy", lambda: dst.copy_(src))
+
+
+def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
+    def run():
+        Bn, co, Ho, Wo = out.shape
+        H, W = Ho // r, Wo // r
+        v = x.reshape(Bn, H, W, -1)[..., :co * r * r].float().permute(0, 3, 1, 2)
+        out.copy_(F.pixel_shuffle(v, r) * scale + mean.view(1, co, 1, 1))
+
+    return EmuLaunch("kair_pixel_shuffle_out", run)

@@ -50,10 +50,10 @@ def _engine_step(model, x, target, drop=None):
 
 
 @pytest.mark.skipif(not ref_loader.have_reference(), reason="reference tree not mounted")
-@pytest.mark.parametrize("in_chans,H,W", [(1, 16, 16), (3, 16, 24)])
-def test_engine_matches_reference_module(in_chans, H, W):
+@pytest.mark.parametrize("in_chans,H,W,C", [(1, 16, 16, 180), (3, 16, 24, 180), (3, 16, 16, 60)])
+def test_engine_matches_reference_module(in_chans, H, W, C):
     ref_mod = ref_loader.load("network_swinir")
-    cfg = dict(CFG, in_chans=in_chans)
+    cfg = dict(CFG, in_chans=in_chans, embed_dim=C)   # C=60: SwinIR-S (lightweight SR) geometry, head_dim 10
     torch.manual_seed(0)
     ref = ref_mod.SwinIR(drop_path_rate=0.0, **cfg)
     mine = SwinIR(drop_path_rate=0.0, **cfg)
@@ -98,9 +98,10 @@ def test_engine_matches_oracle_with_drop_path():
         assert _rel_l2(grads[k], gr) < 5e-2, (k, _rel_l2(grads[k], gr))
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4"])
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2"])
 def test_sr_heads_forward_vs_oracle(name):
-    """Reconstruction heads (network_swinir.py:740-760, 816-831): pixelshuffle x4 and nearest+conv x4, inference plan."""
+    """Reconstruction heads (network_swinir.py:740-760, 816-831): pixelshuffle x4, nearest+conv x4 and the lightweight
+    pixelshuffledirect x2 (embed_dim 60), inference plan."""
     import golden_cases as gc
     case = gc.CASES[name]
     sd, x, _ = gc.state_and_io(case)

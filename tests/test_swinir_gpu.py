@@ -38,11 +38,12 @@ def _rel_l2(a, b):
     return ((a - b).norm() / (b.norm() + 1e-20)).item()
 
 
-@pytest.mark.parametrize("in_chans,B,H,W", [(1, 2, 32, 32), (3, 1, 24, 40), (2, 3, 16, 16)])
-def test_forward_backward_vs_oracle(in_chans, B, H, W):
+@pytest.mark.parametrize("in_chans,B,H,W,C", [(1, 2, 32, 32, 180), (3, 1, 24, 40, 180), (2, 3, 16, 16, 180),
+                                              (3, 2, 32, 32, 60), (1, 1, 16, 24, 60)])
+def test_forward_backward_vs_oracle(in_chans, B, H, W, C):
     from kair_b200.network_swinir import SwinIR
     from oracle import swinir_oracle as so
-    cfg = dict(CFG, in_chans=in_chans)
+    cfg = dict(CFG, in_chans=in_chans, embed_dim=C)   # C=60: SwinIR-S geometry (64 padded channels, 64-wide tiles)
     torch.manual_seed(0)
     model = SwinIR(drop_path_rate=0.0, **cfg)
     _randomize(model, 11)
@@ -170,7 +171,7 @@ def test_golden_fixture_swinir_m_gray32():
     assert not bad, bad[:6]
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4"])
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2"])
 def test_golden_fixture_sr_heads(name):
     """cfg3 / cfg5 architectures (reduced depth): x4 pixelshuffle and nearest+conv heads under no_grad vs the golden
     output of the real reference module; bf16 result vs fp32 reference: 2e-2 max-abs and 0.02 dB PSNR (north_star)."""
