@@ -412,10 +412,19 @@ typedef struct kair_shuffle_args {
   const void* in;          /* bf16 */
   void* out;               /* bf16 */
   int64_t in_pitch, out_pitch;
-  int32_t batch, H, W, C, r; /* H, W = INPUT resolution; C = output channels */
+  int32_t batch, H, W, C, r; /* H, W = LOW resolution; C = channels at the HIGH resolution */
+  /* backward entry points only: the gradient written is multiplied by (mask > 0 ? 1 : mask_slope), mask being the
+   * LeakyReLU output that fed the forward op (network_swinir.py:747, 829-830); NULL = no activation */
+  const void* mask;        /* bf16, shaped like the backward output, or NULL */
+  int64_t mask_pitch;
+  float mask_slope;
 } kair_shuffle_args;
 int kair_pixel_shuffle(const kair_shuffle_args* args, void* stream);
 int kair_upsample_nearest2(const kair_shuffle_args* args, void* stream);
+/* adjoints: `in` is the HIGH-resolution gradient [B*rH*rW][C], `out` the LOW-resolution one
+ * ([B*H*W][r*r*C] for the shuffle; [B*H*W][C] = sum over the 2x2 footprint for nearest x2) */
+int kair_pixel_shuffle_bwd(const kair_shuffle_args* args, void* stream);
+int kair_upsample_nearest2_bwd(const kair_shuffle_args* args, void* stream);
 
 /* UpsampleOneStep ('pixelshuffledirect', network_swinir.py:594-615, 819-822) tail: PixelShuffle(r) of the conv output
  * straight into the NCHW fp32 image with the final affine of SwinIR.forward (:837):
@@ -429,6 +438,10 @@ typedef struct kair_shuffle_out_args {
   int32_t batch, H, W, co, r;
 } kair_shuffle_out_args;
 int kair_pixel_shuffle_out(const kair_shuffle_out_args* args, void* stream);
+/* adjoint of kair_pixel_shuffle_out: roles swap, `out` (the fp32 NCHW gradient of the image) is READ and `in`
+ * (bf16 [B*H*W][in_pitch]) is WRITTEN: in[(b,h,w)][c*r*r + dy*r + dx] = out[b][c][r*h+dy][r*w+dx] * scale; columns
+ * >= co*r*r are left untouched (they are the zero padding of the GEMM operand).  mean is ignored. */
+int kair_pixel_shuffle_out_bwd(const kair_shuffle_out_args* args, void* stream);
 
 /* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);

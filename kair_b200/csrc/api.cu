@@ -33,6 +33,9 @@ int bn_fold_launch(const kair_bn_args& a, cudaStream_t st);
 int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st);
 int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st);
+int pixel_shuffle_out_bwd_launch(const kair_shuffle_out_args& a, cudaStream_t st);
+int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
+int upsample_nearest2_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 }
 
@@ -107,6 +110,9 @@ KB_WRAP(kair_bn_fold, kair_bn_args, bn_fold_launch)
 KB_WRAP(kair_pixel_shuffle, kair_shuffle_args, pixel_shuffle_launch)
 KB_WRAP(kair_upsample_nearest2, kair_shuffle_args, upsample_nearest2_launch)
 KB_WRAP(kair_pixel_shuffle_out, kair_shuffle_out_args, pixel_shuffle_out_launch)
+KB_WRAP(kair_pixel_shuffle_out_bwd, kair_shuffle_out_args, pixel_shuffle_out_bwd_launch)
+KB_WRAP(kair_pixel_shuffle_bwd, kair_shuffle_args, pixel_shuffle_bwd_launch)
+KB_WRAP(kair_upsample_nearest2_bwd, kair_shuffle_args, upsample_nearest2_bwd_launch)
 #undef KB_WRAP
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {

@@ -475,6 +475,121 @@ int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st) {
   return 0;
 }
 
+// adjoint of pixel_shuffle_kernel: a thread reads one bf16 pair of the high-resolution gradient (coalesced) and
+// scatters it to the two channel groups of the low-resolution pixel
+__global__ void pixel_shuffle_bwd_kernel(const kair_shuffle_args a) {
+  const int r = a.r, Ho = a.H * r, Wo = a.W * r, rr = r * r;
+  const bf16* in = reinterpret_cast<const bf16*>(a.in);
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  const int pc = a.C >> 1;
+  const long long n = (long long)a.batch * Ho * Wo * pc;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(e % pc) * 2;
+    const long long to = e / pc;
+    const int wo = (int)(to % Wo), ho = (int)((to / Wo) % Ho);
+    const long long b = to / ((long long)Wo * Ho);
+    const long long ti = (b * a.H + ho / r) * a.W + wo / r;
+    const int sub = (ho % r) * r + (wo % r);
+    const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(in + to * a.in_pitch + c);
+    out[ti * a.out_pitch + (long long)c * rr + sub] = v.x;
+    out[ti * a.out_pitch + (long long)(c + 1) * rr + sub] = v.y;
+  }
+}
+
+// adjoint of nearest x2: low-resolution gradient = sum of the 2x2 footprint (fp32), then the LeakyReLU mask
+__global__ void upsample_nearest2_bwd_kernel(const kair_shuffle_args a) {
+  const int Wo = a.W * 2, vc = a.C >> 3;
+  const uint4* in = reinterpret_cast<const uint4*>(a.in);
+  uint4* out = reinterpret_cast<uint4*>(a.out);
+  const uint4* mask = reinterpret_cast<const uint4*>(a.mask);
+  const long long ip = a.in_pitch >> 3, op = a.out_pitch >> 3, mp = a.mask_pitch >> 3;
+  const long long n = (long long)a.batch * a.H * a.W * vc;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(e % vc);
+    const long long ti = e / vc;
+    const int w = (int)(ti % a.W), h = (int)((ti / a.W) % a.H);
+    const long long b = ti / ((long long)a.W * a.H);
+    const long long t00 = (b * 2 * a.H + 2 * h) * Wo + 2 * w;
+    uint4 q[4];
+    q[0] = __ldg(in + t00 * ip + v);
+    q[1] = __ldg(in + (t00 + 1) * ip + v);
+    q[2] = __ldg(in + (t00 + Wo) * ip + v);
+    q[3] = __ldg(in + (t00 + Wo + 1) * ip + v);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q[k]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(h2[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+    if (mask) {
+      const uint4 m = __ldg(mask + ti * mp + v);
+      const __nv_bfloat162* m2 = reinterpret_cast<const __nv_bfloat162*>(&m);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(m2[j]);
+        if (!(f.x > 0.f)) acc[2 * j] *= a.mask_slope;
+        if (!(f.y > 0.f)) acc[2 * j + 1] *= a.mask_slope;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(acc[0], acc[1]);
+    o.y = pack_bf16x2(acc[2], acc[3]);
+    o.z = pack_bf16x2(acc[4], acc[5]);
+    o.w = pack_bf16x2(acc[6], acc[7]);
+    out[ti * op + v] = o;
+  }
+}
+
+__global__ void pixel_shuffle_out_bwd_kernel(const kair_shuffle_out_args a) {
+  const int r = a.r, Ho = a.H * r, Wo = a.W * r, rr = r * r;
+  bf16* in = reinterpret_cast<bf16*>(const_cast<void*>(a.in));
+  const long long n = (long long)a.batch * a.co * Ho * Wo;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const int wo = (int)(e % Wo), ho = (int)((e / Wo) % Ho);
+    const int c = (int)((e / ((long long)Wo * Ho)) % a.co);
+    const long long b = e / ((long long)Wo * Ho * a.co);
+    const long long ti = (b * a.H + ho / r) * a.W + wo / r;
+    in[ti * a.in_pitch + (long long)c * rr + (ho % r) * r + (wo % r)] = __float2bfloat16(a.out[e] * a.scale);
+  }
+}
+
+int pixel_shuffle_out_bwd_launch(const kair_shuffle_out_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle_out_bwd: null pointer / empty");
+  KB_CHECK(a.r >= 1 && a.r <= 8 && a.co >= 1 && a.in_pitch >= (long long)a.co * a.r * a.r,
+           "kair_pixel_shuffle_out_bwd: bad geometry (r=%d, co=%d)", a.r, a.co);
+  const long long n = (long long)a.batch * a.co * a.H * a.W * a.r * a.r;
+  pixel_shuffle_out_bwd_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle_bwd: null pointer / empty");
+  KB_CHECK(a.r >= 2 && a.r <= 4 && a.C % 2 == 0 && a.in_pitch % 2 == 0 && a.out_pitch >= (long long)a.C * a.r * a.r &&
+               a.in_pitch >= a.C && !a.mask,
+           "kair_pixel_shuffle_bwd: bad geometry (r=%d, C=%d) or mask given", a.r, a.C);
+  const long long n = (long long)a.batch * a.H * a.W * a.r * a.r * (a.C >> 1);
+  pixel_shuffle_bwd_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int upsample_nearest2_bwd_launch(const kair_shuffle_args& a, cudaStream_t st) {
+  KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_upsample_nearest2_bwd: null pointer / empty");
+  KB_CHECK(a.C % 8 == 0 && a.in_pitch % 8 == 0 && a.out_pitch % 8 == 0 && a.in_pitch >= a.C && a.out_pitch >= a.C &&
+               (!a.mask || (a.mask_pitch % 8 == 0 && a.mask_pitch >= a.C)),
+           "kair_upsample_nearest2_bwd: C and pitches must be multiples of 8");
+  const long long n = (long long)a.batch * a.H * a.W * (a.C >> 3);
+  upsample_nearest2_bwd_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st) {
   KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_pixel_shuffle: null pointer / empty");
   KB_CHECK(a.r >= 2 && a.r <= 4 && a.C % 2 == 0 && a.out_pitch % 2 == 0 && a.in_pitch >= (long long)a.C * a.r * a.r &&

@@ -490,6 +490,33 @@ def build_upsample_nearest2(x, out, *, batch, H, W, C):
     return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2))
 
 
+def build_pixel_shuffle_bwd(dy, dx, *, batch, H, W, C, r):
+    """adjoint of build_pixel_shuffle: dy [B*rH*rW, >= C] -> dx [B*H*W, >= r*r*C] (bf16)."""
+    return Launch("kair_pixel_shuffle_bwd", _shuffle_args(dy, dx, batch, H, W, C, r))
+
+
+def build_upsample_nearest2_bwd(dy, dx, *, batch, H, W, C, mask=None, mask_slope=0.0):
+    """adjoint of build_upsample_nearest2 (2x2 sums), times the LeakyReLU mask of the low-resolution activation."""
+    a = _shuffle_args(dy, dx, batch, H, W, C, 2)
+    if mask is not None:
+        _req(mask, torch.bfloat16, "mask")
+        a.mask = _ptr(mask); a.mask_pitch = _pitch(mask); a.mask_slope = mask_slope
+    return Launch("kair_upsample_nearest2_bwd", a)
+
+
+def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
+    """adjoint of build_pixel_shuffle_out: dout (B, co, r*H, r*W) fp32 -> dx bf16 [B*H*W, >= co*r*r] (* scale)."""
+    _req(dx, torch.bfloat16, "in"); _req(dout, torch.float32, "out")
+    if not dout.is_contiguous():
+        raise RuntimeError("kair_b200: pixel_shuffle_out_bwd needs a contiguous NCHW gradient")
+    a = _S["kair_shuffle_out_args"]()
+    setattr(a, "in", _ptr(dx)); a.out = _ptr(dout); a.mean = None
+    a.in_pitch = _pitch(dx); a.scale = scale
+    a.batch, a.co = dout.shape[0], co
+    a.H, a.W, a.r = dout.shape[2] // r, dout.shape[3] // r, r
+    return Launch("kair_pixel_shuffle_out_bwd", a)
+
+
 def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
     """out (B, co, r*H, r*W) fp32 = PixelShuffle(r)(x) * scale + mean[c]; x bf16 [B*H*W, >= co*r*r]."""
     _req(x, torch.bfloat16, "in"); _req(out, torch.float32, "out"); _req(mean, torch.float32, "mean")

@@ -189,14 +189,15 @@ class SwinIREngine:
         if up == "pixelshuffledirect":
             # UpsampleOneStep (network_swinir.py:594-609): one conv embed_dim -> upscale^2 * num_out_ch, rows padded to 64
             no = self.spec.upscale ** 2 * self.spec.in_chans
-            W["psd"], W["bpsd"] = bf(1, _round_up(no, 64), 9 * Cp), f32(1, _round_up(no, 64))
+            nop = _round_up(no, 64)
+            W["psd"], W["bpsd"], W["psdT"] = bf(1, nop, 9 * Cp), f32(1, nop), (bf(1, Cp, 9 * nop) if train else None)
             W["pack"].append(o.build_pack_conv([P["upsample.0.weight"]], [P["upsample.0.bias"]],
-                                               W["psd"], None, W["bpsd"], O=no, I=C, I_pad=Cp))
+                                               W["psd"], W["psdT"], W["bpsd"], O=no, I=C, I_pad=Cp))
         elif up:
             nf = 64
-            W["cbu"], W["bcbu"] = bf(1, nf, 9 * Cp), f32(1, nf)
+            W["cbu"], W["bcbu"], W["cbuT"] = bf(1, nf, 9 * Cp), f32(1, nf), (bf(1, Cp, 9 * nf) if train else None)
             W["pack"].append(o.build_pack_conv([P["conv_before_upsample.0.weight"]], [P["conv_before_upsample.0.bias"]],
-                                               W["cbu"], None, W["bcbu"], O=nf, I=C, I_pad=Cp))
+                                               W["cbu"], W["cbuT"], W["bcbu"], O=nf, I=C, I_pad=Cp))
             if up == "pixelshuffle":
                 s = self.spec.upscale
                 r = 3 if s == 3 else 2
@@ -206,8 +207,10 @@ class SwinIREngine:
             else:
                 names = ["conv_up1", "conv_up2", "conv_hr"]
                 W["ups"], W["bups"] = bf(3, nf, 9 * nf), f32(3, nf)
+            W["ups_names"] = names
+            W["upsT"] = bf(W["ups"].shape[0], nf, 9 * W["ups"].shape[1]) if train else None
             W["pack"].append(o.build_pack_conv([P[n_ + ".weight"] for n_ in names], [P[n_ + ".bias"] for n_ in names],
-                                               W["ups"], None, W["bups"], O=W["ups"].shape[1], I=nf, I_pad=nf))
+                                               W["ups"], W["upsT"], W["bups"], O=W["ups"].shape[1], I=nf, I_pad=nf))
         W["versions"] = None
         self._weights = W
         self._plans = {}  # plans hold pointers into the packed operands
@@ -254,9 +257,6 @@ class _Plan:
         tps = H * W
 
         up = s.upsampler
-        if up and train:
-            raise NotImplementedError("kair_b200 SwinIR: autograd through the '%s' reconstruction head is not built yet "
-                                      "(inference under torch.no_grad() is); see DESIGN.md, 'coverage'" % up)
         sc = s.upscale if up else 1
         self.img = f32(B, s.in_chans, H, W)
         self.out = f32(B, s.in_chans, H * sc, W * sc)
@@ -346,19 +346,22 @@ class _Plan:
         elif up == "pixelshuffledirect":
             no = Wt["psd"].shape[1]
             u = bf(T, no)
+            head = None
             fwd.append(o.build_gemm_tn(resb, Wt["psd"][0], N=no, K=Cp, bn=_tile(no), conv=geo, bias=Wt["bpsd"][0], outB=u))
             fwd.append(o.build_pixel_shuffle_out(u, self.out, mean_t, r=s.upscale, scale=1.0 / rng))
         else:
             # conv_before_upsample + LeakyReLU(0.01), then the upsampling convolutions on 64 features
             nf = 64
-            f = bf(T, nf)
+            f = f0 = bf(T, nf)
             fwd.append(o.build_gemm_tn(resb, Wt["cbu"][0], N=nf, K=Cp, bn=64, conv=geo, bias=Wt["bcbu"][0],
                                        act=o.ACT_LRELU, act_slope=0.01, outB=f))
             h, w = H, W
+            head = []   # per upsampling conv: (conv input, its (B, h, w), activation output feeding the resampler)
             if up == "pixelshuffle":
                 r = Wt["ups_r"]
                 for i in range(Wt["ups"].shape[0]):
                     u = bf(B * h * w, r * r * nf)
+                    head.append((f, (B, h, w), None))
                     fwd.append(o.build_gemm_tn(f, Wt["ups"][i], N=r * r * nf, K=nf, bn=(192 if r == 3 else 256),
                                                conv=(B, h, w), bias=Wt["bups"][i], outB=u))
                     f = bf(B * h * r * w * r, nf)
@@ -369,10 +372,12 @@ class _Plan:
                     n_ = bf(B * 4 * h * w, nf)
                     fwd.append(o.build_upsample_nearest2(f, n_, batch=B, H=h, W=w, C=nf))
                     h, w = 2 * h, 2 * w
+                    head.append((n_, (B, h, w), f))
                     f = bf(B * h * w, nf)
                     fwd.append(o.build_gemm_tn(n_, Wt["ups"][i], N=nf, K=nf, bn=64, conv=(B, h, w), bias=Wt["bups"][i],
                                                act=o.ACT_LRELU, act_slope=0.2, outB=f))
                 f2 = bf(B * h * w, nf)
+                head.append((f, (B, h, w), None))
                 fwd.append(o.build_gemm_tn(f, Wt["ups"][2], N=nf, K=nf, bn=64, conv=(B, h, w), bias=Wt["bups"][2],
                                            act=o.ACT_LRELU, act_slope=0.2, outB=f2))
                 f = f2
@@ -383,7 +388,7 @@ class _Plan:
             return
 
         # ================================================================================ backward
-        self.dout = f32(B, s.in_chans, H, W)
+        self.dout = f32(B, s.in_chans, H * sc, W * sc)
         # gradients in the parameters' own layouts: one flat fp32 buffer, views per parameter
         sizes = [p.numel() for p in P.values()]
         self.gflat = f32(sum(sizes))
@@ -409,16 +414,83 @@ class _Plan:
 
         bwd = []
         inv = 1.0 / rng
-        # conv_last backward as GEMMs over the 9-tap expansion of d(out) (columns tap*7 + c, K padded to 64)
         ci = s.in_chans
-        dsh, clT, dWcl = bf(T, 64), bf(Cp, 64), f32(Cp, 64)
-        self._thin = (dWcl,)
-        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=inv))
-        bwd.append(o.build_conv_out_pack(mode=0, co=ci, C=C, cpad=7, W=cl_w, Wt=clT))
-        bwd.append(o.build_gemm_tn(dsh, clT, N=Cp, K=64, bn=_tile(Cp), outF=dresf, outB=dresb))
-        bwd.append(o.build_gemm_nt(resb, dsh, dWcl, n1=Cp, n2=64, bn=64))
-        bwd.append(o.build_conv_out_pack(mode=1, co=ci, C=C, cpad=7, D=dWcl, dW=G["conv_last.weight"],
-                                         db=G["conv_last.bias"], ones_row=C))
+        unpack_head = []
+        colsum = lambda x, out, n: [o.build_colsum(x[:, c0:min(c0 + 512, n)], out[c0:min(c0 + 512, n)],
+                                                   C=min(c0 + 512, n) - c0) for c0 in range(0, n, 512)]
+        if not up:
+            # conv_last backward as GEMMs over the 9-tap expansion of d(out) (columns tap*7 + c, K padded to 64)
+            dsh, clT, dWcl = bf(T, 64), bf(Cp, 64), f32(Cp, 64)
+            self._thin = (dWcl,)
+            bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=inv))
+            bwd.append(o.build_conv_out_pack(mode=0, co=ci, C=C, cpad=7, W=cl_w, Wt=clT))
+            bwd.append(o.build_gemm_tn(dsh, clT, N=Cp, K=64, bn=_tile(Cp), outF=dresf, outB=dresb))
+            bwd.append(o.build_gemm_nt(resb, dsh, dWcl, n1=Cp, n2=64, bn=64))
+            bwd.append(o.build_conv_out_pack(mode=1, co=ci, C=C, cpad=7, D=dWcl, dW=G["conv_last.weight"],
+                                             db=G["conv_last.bias"], ones_row=C))
+        elif up == "pixelshuffledirect":
+            # d(out) un-shuffled into the conv's output channels; bias gradient from the ones column of `res`
+            nop = Wt["psd"].shape[1]
+            dps, dWpsd = bf(T, nop), f32(1, nop, 9 * Cp)
+            self._thin = (dWpsd,)
+            bwd.append(o.build_pixel_shuffle_out_bwd(self.dout, dps, r=s.upscale, co=ci, scale=inv))
+            bwd.append(o.build_gemm_nt(dps, resb, dWpsd[0], n1=nop, n2=Cp, bn=_tile(Cp), conv=geo))
+            bwd.append(o.build_gemm_tn(dps, Wt["psdT"][0], N=Cp, K=nop, bn=_tile(Cp), conv=geo, outF=dresf, outB=dresb))
+            unpack_head.append(o.build_unpack_conv_grad(dWpsd, [G["upsample.0.weight"]], [G["upsample.0.bias"]],
+                                                        O=s.upscale ** 2 * ci, I=C, I_pad=Cp, ones_col=C, center_tap=4))
+        else:
+            # conv_last on 64 features at the output resolution (thin: 9-tap expansion of d(out)), then the upsampling
+            # convolutions in reverse; LeakyReLU masks ride on the dgrad epilogues / the nearest-x2 adjoint
+            nf = 64
+            names = Wt["ups_names"]
+            Th = B * H * sc * W * sc
+            dsh, clT, dWcl, csum = bf(Th, 64), bf(nf, 64), f32(nf, 64), f32(64)
+            n_up, O_up = Wt["ups"].shape[0], Wt["ups"].shape[1]
+            dWups, dWcbu = f32(n_up, O_up, 9 * nf), f32(1, nf, 9 * Cp)
+            self._thin = (dWcl, csum, dWups, dWcbu)
+            bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=inv))
+            bwd.append(o.build_conv_out_pack(mode=0, co=ci, C=nf, cpad=7, W=cl_w, Wt=clT))
+            bwd.append(o.build_gemm_nt(f, dsh, dWcl, n1=nf, n2=64, bn=64))
+            bwd.append(o.build_conv_out_pack(mode=1, co=ci, C=nf, cpad=7, D=dWcl, dW=G["conv_last.weight"]))
+            bwd.append(o.build_colsum(dsh, csum, C=64))
+            bwd.append(o.build_copy(G["conv_last.bias"], csum[4 * 7:4 * 7 + ci]))
+            g = bf(Th, nf)
+            lrelu_out = up == "nearest+conv"   # conv_last reads lrelu(conv_hr(.)) there, a bare PixelShuffle otherwise
+            bwd.append(o.build_gemm_tn(dsh, clT, N=nf, K=64, bn=64, outB=g, aux=f if lrelu_out else None,
+                                       act_slope=0.2 if lrelu_out else 0.0))
+            for i in reversed(range(n_up)):
+                xin, (_, h_, w_), pre = head[i]
+                if up == "pixelshuffle":
+                    r = Wt["ups_r"]
+                    du_ = bf(B * h_ * w_, O_up)
+                    bwd.append(o.build_pixel_shuffle_bwd(g, du_, batch=B, H=h_, W=w_, C=nf, r=r))
+                    g = du_
+                bwd += colsum(g, G[names[i] + ".bias"], O_up)
+                bwd.append(o.build_gemm_nt(g, xin, dWups[i], n1=O_up, n2=nf, bn=64, conv=(B, h_, w_)))
+                gin = bf(B * h_ * w_, nf)
+                if up == "pixelshuffle":
+                    # the first conv reads f0 = LeakyReLU(0.01)(conv_before_upsample), later ones a bare PixelShuffle
+                    bwd.append(o.build_gemm_tn(g, Wt["upsT"][i], N=nf, K=O_up, bn=64, conv=(B, h_, w_), outB=gin,
+                                               aux=f0 if i == 0 else None, act_slope=0.01 if i == 0 else 0.0))
+                    g = gin
+                elif pre is None:
+                    # conv_hr reads lrelu(conv_up2(.)) directly
+                    bwd.append(o.build_gemm_tn(g, Wt["upsT"][i], N=nf, K=O_up, bn=64, conv=(B, h_, w_), outB=gin,
+                                               aux=xin, act_slope=0.2))
+                    g = gin
+                else:
+                    bwd.append(o.build_gemm_tn(g, Wt["upsT"][i], N=nf, K=O_up, bn=64, conv=(B, h_, w_), outB=gin))
+                    g = bf(B * (h_ // 2) * (w_ // 2), nf)
+                    bwd.append(o.build_upsample_nearest2_bwd(gin, g, batch=B, H=h_ // 2, W=w_ // 2, C=nf, mask=pre,
+                                                             mask_slope=0.01 if i == 0 else 0.2))
+            # g = d(f0), masked; conv_before_upsample
+            bwd.append(o.build_gemm_nt(g, resb, dWcbu[0], n1=nf, n2=Cp, bn=_tile(Cp), conv=geo))
+            bwd.append(o.build_gemm_tn(g, Wt["cbuT"][0], N=Cp, K=nf, bn=_tile(Cp), conv=geo, outF=dresf, outB=dresb))
+            unpack_head.append(o.build_unpack_conv_grad(dWcbu, [G["conv_before_upsample.0.weight"]],
+                                                        [G["conv_before_upsample.0.bias"]], O=nf, I=C, I_pad=Cp,
+                                                        ones_col=C, center_tap=4))
+            unpack_head.append(o.build_unpack_conv_grad(dWups, [G[n_ + ".weight"] for n_ in names], None, O=O_up, I=nf,
+                                                        I_pad=nf))
         bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
         bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, outB=dyb))
         dt = 2
@@ -493,7 +565,7 @@ class _Plan:
         cn = Wt["conv_names"]
         bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
                                             O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
-        self.bwd = bwd
+        self.bwd = bwd + unpack_head
 
     # ------------------------------------------------------------------------------------------ execution
     def set_drop_path(self, rates, generator=None):

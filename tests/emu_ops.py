@@ -642,3 +642,30 @@ def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
         out.copy_(F.pixel_shuffle(v, r) * scale + mean.view(1, co, 1, 1))
 
     return EmuLaunch("kair_pixel_shuffle_out", run)
+
+
+def build_pixel_shuffle_bwd(dy, dx, *, batch, H, W, C, r):
+    def run():
+        g = dy.reshape(batch, H * r, W * r, -1)[..., :C].float().permute(0, 3, 1, 2)
+        dx[:, :C * r * r] = _bf(F.pixel_unshuffle(g, r).permute(0, 2, 3, 1).reshape(batch * H * W, C * r * r))
+
+    return EmuLaunch("kair_pixel_shuffle_bwd", run)
+
+
+def build_upsample_nearest2_bwd(dy, dx, *, batch, H, W, C, mask=None, mask_slope=0.0):
+    def run():
+        g = dy.reshape(batch, H, 2, W, 2, -1)[..., :C].float().sum(dim=(2, 4)).reshape(batch * H * W, C)
+        if mask is not None:
+            g = torch.where(mask[:, :C].float() > 0, g, g * mask_slope)
+        dx[:, :C] = _bf(g)
+
+    return EmuLaunch("kair_upsample_nearest2_bwd", run)
+
+
+def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
+    def run():
+        Bn, _, Ho, Wo = dout.shape
+        g = F.pixel_unshuffle(dout * scale, r).permute(0, 2, 3, 1).reshape(-1, co * r * r)
+        dx[:, :co * r * r] = _bf(g)
+
+    return EmuLaunch("kair_pixel_shuffle_out_bwd", run)
