@@ -789,8 +789,9 @@ static int launch_res(const TnParams& p, bool bres, int grid, size_t smem, cudaS
 }
 
 // Instantiated configurations (kept explicit to bound compile time):
-//   dense: every epilogue at BN=192 (SwinIR-M, C=180 padded to 192) and BN=64 (SwinIR-S, C=60); LINEAR at BN 64/128/256
-//   conv : LINEAR at BN 64/128/192/256; RESID_LN at BN=192 and 64
+//   dense: every epilogue at BN=192 (SwinIR-M, C=180 padded to 192), BN=64 (SwinIR-S, C=60) and BN=256 (SwinIR-L,
+//          C=240); LINEAR at BN 64/128/256
+//   conv : LINEAR at BN 64/128/192/256; RESID_LN at BN=192, 64 and 256
 static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool bres, int grid, size_t smem,
                            cudaStream_t st) {
 #define KB_CASE(BN_, EPI_, CONV_) \
@@ -814,6 +815,11 @@ static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool b
   KB_CASE(64, KAIR_EPI_DGELU, false)
   KB_CASE(64, KAIR_EPI_LNBWD, false)
   KB_CASE(64, KAIR_EPI_RESID_LN, true)
+  KB_CASE(256, KAIR_EPI_GELU, false)
+  KB_CASE(256, KAIR_EPI_RESID_LN, false)
+  KB_CASE(256, KAIR_EPI_DGELU, false)
+  KB_CASE(256, KAIR_EPI_LNBWD, false)
+  KB_CASE(256, KAIR_EPI_RESID_LN, true)
 #undef KB_CASE
   set_error("kair_gemm_tn: configuration bn=%d mode=%d conv=%d is not instantiated", bn, epi, (int)conv);
   return -1;

@@ -23,7 +23,7 @@ def _tile(n, fused=False):
     """N tile of a GEMM with n output columns.  The fused epilogues (GELU, GELU', LayerNorm forward / backward) are
     instantiated at 192 (SwinIR-M, C=180) and 64 (SwinIR-S, C=60); plain LINEAR and the weight-gradient GEMMs at
     64 / 128 / 192 / 256."""
-    for bn in ((192, 64) if fused else (256, 192, 128, 64)):
+    for bn in ((256, 192, 64) if fused else (256, 192, 128, 64)):
         if n % bn == 0:
             return bn
     raise NotImplementedError("kair_b200 SwinIR: no GEMM tile for %d columns" % n)
@@ -66,10 +66,10 @@ class SwinIRSpec:
         hd = self.C // nH
         if hd >= 32:
             bad("head_dim=%d must be < 32 (one padded column carries the proj bias gradient)" % hd)
-        if _round_up(self.C + 1, 64) not in (64, 192):
-            bad("embed_dim=%d: the LayerNorm epilogues are instantiated for 64 and 192 padded channels "
-                "(embed_dim 1..63 and 128..191, e.g. SwinIR-S 60 and SwinIR-M 180)" % self.C)
-        if self.resi_connection != "1conv":
+        if _round_up(self.C + 1, 64) not in (64, 192, 256):
+            bad("embed_dim=%d: the LayerNorm epilogues are instantiated for 64, 192 and 256 padded channels "
+                "(embed_dim 1..63 and 128..255, e.g. SwinIR-S 60, SwinIR-M 180, SwinIR-L 240)" % self.C)
+        if self.resi_connection not in ("1conv", "3conv"):
             bad("resi_connection='%s'" % self.resi_connection)
         if self.upsampler not in ("", "pixelshuffle", "pixelshuffledirect", "nearest+conv"):
             bad("upsampler='%s'" % self.upsampler)
@@ -164,7 +164,10 @@ class SwinIREngine:
         W["proj"], W["projT"], W["bproj"] = bf(L, Cp, HP), (bf(L, HP, Cp) if train else None), f32(L, Cp)
         W["fc1"], W["fc1T"], W["bfc1"] = bf(L, Fp, Cp), (bf(L, Cp, Fp) if train else None), f32(L, Fp)
         W["fc2"], W["fc2T"], W["bfc2"] = bf(L, Cp, Fp), (bf(L, Fp, Cp) if train else None), f32(L, Cp)
-        W["conv"], W["convT"], W["bconv"] = bf(nl + 1, Cp, 9 * Cp), (bf(nl + 1, Cp, 9 * Cp) if train else None), \
+        three = self.spec.resi_connection == "3conv"
+        Cq, Cqp = C // 4, _round_up(C // 4 + 1, 64)
+        Kc = Cqp if three else Cp   # input channels of the convolution that closes an RSTB / the body
+        W["conv"], W["convT"], W["bconv"] = bf(nl + 1, Cp, 9 * Kc), (bf(nl + 1, Kc, 9 * Cp) if train else None), \
             f32(nl + 1, Cp)
         get = lambda suffix: [P[b + suffix] for b in blk]
         qb = get("attn.qkv.bias") if self.spec.qkv_bias else None
@@ -181,9 +184,23 @@ class SwinIREngine:
                                 out_f=self.spec.hidden, in_f=C),
             o.build_pack_linear(get("mlp.fc2.weight"), get("mlp.fc2.bias"), None, None, self.map_c, self.map_f,
                                 None, None, W["fc2"], W["fc2T"], W["bfc2"], out_f=C, in_f=self.spec.hidden),
-            o.build_pack_conv([P[n + ".weight"] for n in conv_names], [P[n + ".bias"] for n in conv_names],
-                              W["conv"], W["convT"], W["bconv"], O=C, I=C, I_pad=Cp),
         ]
+        pw = lambda sfx: [P[n + sfx + ".weight"] for n in conv_names]
+        pb = lambda sfx: [P[n + sfx + ".bias"] for n in conv_names]
+        if not three:
+            W["pack"].append(o.build_pack_conv(pw(""), pb(""), W["conv"], W["convT"], W["bconv"], O=C, I=C, I_pad=Cp))
+        else:
+            # '3conv' (network_swinir.py:467-471, 733-737): conv3x3 C -> C/4, LeakyReLU(0.2), conv1x1, LeakyReLU(0.2),
+            # conv3x3 C/4 -> C; the last one keeps the single-conv epilogues ("conv"), the first two are c3a / c3b
+            W["c3a"], W["c3aT"], W["bc3a"] = bf(nl + 1, Cqp, 9 * Cp), (bf(nl + 1, Cp, 9 * Cqp) if train else None), \
+                f32(nl + 1, Cqp)
+            W["c3b"], W["c3bT"], W["bc3b"] = bf(nl + 1, Cqp, Cqp), (bf(nl + 1, Cqp, Cqp) if train else None), \
+                f32(nl + 1, Cqp)
+            W["pack"] += [
+                o.build_pack_conv(pw(".0"), pb(".0"), W["c3a"], W["c3aT"], W["bc3a"], O=Cq, I=C, I_pad=Cp),
+                o.build_pack_conv(pw(".2"), pb(".2"), W["c3b"], W["c3bT"], W["bc3b"], O=Cq, I=Cq, I_pad=Cqp, taps=1),
+                o.build_pack_conv(pw(".4"), pb(".4"), W["conv"], W["convT"], W["bconv"], O=C, I=Cq, I_pad=Cqp),
+            ]
         # reconstruction heads (network_swinir.py:740-760): num_feat = 64
         up = self.spec.upsampler
         if up == "pixelshuffledirect":
@@ -283,6 +300,25 @@ class _Plan:
         dpa = lambda l: self.dp[l] if train else None
         dpm = lambda l: self.dp[L + l] if train else None
 
+        three = s.resi_connection == "3conv"
+        Cq, Cqp = C // 4, _round_up(C // 4 + 1, 64)
+        Kc = Cqp if three else Cp
+        mids = {}   # '3conv': conv index -> (a1, a2), the two LeakyReLU outputs (kept per conv when training)
+        mid_shared = (bf(T, Cqp), bf(T, Cqp)) if three and not train else None
+
+        def conv_operand(i, src, lst):
+            """bf16 input of the convolution that closes RSTB i (i == nl: conv_after_body); '3conv' runs its first two
+            layers here (the ones column Cq of a1 / a2 carries the next layer's bias gradient)"""
+            if not three:
+                return src
+            a1, a2 = mid_shared if mid_shared is not None else (bf(T, Cqp), bf(T, Cqp))
+            mids[i] = (a1, a2)
+            lst.append(o.build_gemm_tn(src, Wt["c3a"][i], N=Cqp, K=Cp, bn=_tile(Cqp), conv=geo, bias=Wt["bc3a"][i],
+                                       act=o.ACT_LRELU, act_slope=0.2, outB=a1, ones_col=Cq))
+            lst.append(o.build_gemm_tn(a1, Wt["c3b"][i], N=Cqp, K=Cqp, bn=_tile(Cqp), bias=Wt["bc3b"][i],
+                                       act=o.ACT_LRELU, act_slope=0.2, outB=a2, ones_col=Cq))
+            return a2
+
         cf_w, cf_b = P["conv_first.weight"], P["conv_first.bias"]
         cl_w, cl_b = (P["conv_last.weight"], P["conv_last.bias"]) if up != "pixelshuffledirect" else (None, None)
         tables = [P[b + "attn.relative_position_bias_table"] for b in eng._block_names()]
@@ -329,16 +365,16 @@ class _Plan:
             if i < nl - 1:
                 nxt = blocks[l]
                 t_next = tin[1] if t_cur is tin[0] else tin[0]
-                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_tile(Cp, True), conv=geo, mode=o.EPI_RESID_LN,
+                fwd.append(o.build_gemm_tn(conv_operand(i, x2b[i], fwd), Wt["conv"][i], N=Cp, K=Kc, bn=_tile(Cp, True), conv=geo, mode=o.EPI_RESID_LN,
                                            bias=Wt["bconv"][i], resid=t_cur, outF=t_next, outB=nxt.xh1,
                                            rowstat=nxt.r1, n_valid=C, ones_col=C))
                 t_cur = t_next
             else:
-                fwd.append(o.build_gemm_tn(x2b[i], Wt["conv"][i], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
+                fwd.append(o.build_gemm_tn(conv_operand(i, x2b[i], fwd), Wt["conv"][i], N=Cp, K=Kc, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
                                            bias=Wt["bconv"][i], resid=t_cur, outF=tfin))
         fwd.append(o.build_layernorm_fwd(tfin, P["norm.weight"], P["norm.bias"], C=C, y_bf16=yb, mean=meanF,
                                          rstd=rstdF, ones_col=C))
-        fwd.append(o.build_gemm_tn(yb, Wt["conv"][nl], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
+        fwd.append(o.build_gemm_tn(conv_operand(nl, yb, fwd), Wt["conv"][nl], N=Cp, K=Kc, bn=_tile(Cp), conv=geo, mode=o.EPI_LINEAR,
                                    bias=Wt["bconv"][nl], resid=first, outB=resb, ones_col=C))
         if not up:
             fwd.append(o.build_conv_out_fwd(resb, cl_w, cl_b, self.out, mean_t, C=C, pitch=Cp, out_scale=1.0 / rng,
@@ -399,14 +435,32 @@ class _Plan:
         self.G = G
         # packed weight gradients (fp32, accumulated by the token-contraction GEMMs)
         n_qkv, n_proj, n_fc = L * QP * Cp, L * Cp * HP, L * Fp * Cp
-        n_conv = (nl + 1) * Cp * 9 * Cp
+        n_conv = (nl + 1) * Cp * 9 * Kc
         self.dwflat = f32(n_qkv + n_proj + 2 * n_fc + n_conv)
         o0 = 0
         dWqkv = self.dwflat[o0:o0 + n_qkv].view(L, QP, Cp); o0 += n_qkv
         dWproj = self.dwflat[o0:o0 + n_proj].view(L, Cp, HP); o0 += n_proj
         dWfc1 = self.dwflat[o0:o0 + n_fc].view(L, Fp, Cp); o0 += n_fc
         dWfc2 = self.dwflat[o0:o0 + n_fc].view(L, Cp, Fp); o0 += n_fc
-        dWconv = self.dwflat[o0:o0 + n_conv].view(nl + 1, Cp, 9 * Cp)
+        dWconv = self.dwflat[o0:o0 + n_conv].view(nl + 1, Cp, 9 * Kc)
+        if three:
+            dWa, dWb = f32(nl + 1, Cqp, 9 * Cp), f32(nl + 1, Cqp, Cqp)
+            da1, da2 = bf(T, Cqp), bf(T, Cqp)
+
+        def conv_backward(i, g, src, **out):
+            """weight gradients of closing convolution i and its input gradient (epilogue outputs given by **out)"""
+            if not three:
+                bwd.append(o.build_gemm_nt(g, src, dWconv[i], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
+                bwd.append(o.build_gemm_tn(g, Wt["convT"][i], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, **out))
+                return
+            a1, a2 = mids[i]
+            bwd.append(o.build_gemm_nt(g, a2, dWconv[i], n1=Cp, n2=Cqp, bn=_tile(Cqp), conv=geo))
+            bwd.append(o.build_gemm_tn(g, Wt["convT"][i], N=Cqp, K=Cp, bn=_tile(Cqp), conv=geo, outB=da2, aux=a2,
+                                       act_slope=0.2))
+            bwd.append(o.build_gemm_nt(da2, a1, dWb[i], n1=Cqp, n2=Cqp, bn=_tile(Cqp)))
+            bwd.append(o.build_gemm_tn(da2, Wt["c3bT"][i], N=Cqp, K=Cqp, bn=_tile(Cqp), outB=da1, aux=a1, act_slope=0.2))
+            bwd.append(o.build_gemm_nt(da1, src, dWa[i], n1=Cqp, n2=Cp, bn=_tile(Cp), conv=geo))
+            bwd.append(o.build_gemm_tn(da1, Wt["c3aT"][i], N=Cp, K=Cqp, bn=_tile(Cp), conv=geo, **out))
         dresf, dresb, dyb = f32(T, Cp), bf(T, Cp), bf(T, Cp)
         R = [(f32(T, Cp), bf(T, Cp)) for _ in range(3)]  # rotating (fp32, bf16) gradient buffers
         du, datt, dqkv = bf(T, Fp), bf(T, HP), bf(T, QP)
@@ -491,8 +545,9 @@ class _Plan:
                                                         ones_col=C, center_tap=4))
             unpack_head.append(o.build_unpack_conv_grad(dWups, [G[n_ + ".weight"] for n_ in names], None, O=O_up, I=nf,
                                                         I_pad=nf))
-        bwd.append(o.build_gemm_nt(dresb, yb, dWconv[nl], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
-        bwd.append(o.build_gemm_tn(dresb, Wt["convT"][nl], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, outB=dyb))
+        if three:
+            self._thin += (dWa, dWb)
+        conv_backward(nl, dresb, yb, outB=dyb)
         dt = 2
         bwd.append(o.build_layernorm_bwd(tfin, meanF, rstdF, P["norm.weight"], G["norm.weight"], G["norm.bias"], C=C,
                                          dy_bf16=dyb, dx_f32=R[dt][0], dx_bf16=R[dt][1]))
@@ -500,9 +555,8 @@ class _Plan:
         for i in reversed(range(nl)):
             depth = s.depths[i]
             a, b = [k for k in range(3) if k != dt]
-            bwd.append(o.build_gemm_nt(R[dt][1], x2b[i], dWconv[i], n1=Cp, n2=Cp, bn=_tile(Cp), conv=geo))
-            bwd.append(o.build_gemm_tn(R[dt][1], Wt["convT"][i], N=Cp, K=Cp, bn=_tile(Cp), conv=geo, outF=R[a][0],
-                                       outB=R[a][1], outB_scale=dpm(l_end - 1), tokens_per_sample=tps))
+            conv_backward(i, R[dt][1], x2b[i], outF=R[a][0], outB=R[a][1], outB_scale=dpm(l_end - 1),
+                          tokens_per_sample=tps)
             cur, oth = a, b
             for j in reversed(range(depth)):
                 l = l_end - depth + j
@@ -563,8 +617,17 @@ class _Plan:
                                               gl("mlp.fc2.bias"), None, None, eng.map_c, eng.map_f, None, out_f=C,
                                               in_f=s.hidden, ones_col=s.hidden))
         cn = Wt["conv_names"]
-        bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
-                                            O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
+        if not three:
+            bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
+                                                O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
+        else:
+            gw = lambda sfx: [G[n + sfx + ".weight"] for n in cn]
+            gb = lambda sfx: [G[n + sfx + ".bias"] for n in cn]
+            bwd.append(o.build_unpack_conv_grad(dWa, gw(".0"), gb(".0"), O=Cq, I=C, I_pad=Cp, ones_col=C, center_tap=4))
+            bwd.append(o.build_unpack_conv_grad(dWb, gw(".2"), gb(".2"), O=Cq, I=Cq, I_pad=Cqp, taps=1, ones_col=Cq,
+                                                center_tap=0))
+            bwd.append(o.build_unpack_conv_grad(dWconv, gw(".4"), gb(".4"), O=C, I=Cq, I_pad=Cqp, ones_col=Cq,
+                                                center_tap=4))
         self.bwd = bwd + unpack_head
 
     # ------------------------------------------------------------------------------------------ execution

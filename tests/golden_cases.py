@@ -37,6 +37,11 @@ CASES = {
     "swinir_3conv": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=48, depths=[2], num_heads=[6],
                                       window_size=8, mlp_ratio=2, upscale=1, img_range=1.0, upsampler="",
                                       resi_connection="3conv"), x=(1, 3, 16, 16), seed=8, loss="l1"),
+    # SwinIR-L geometry at reduced depth (real-world SR large model, main_test_swinir.py:163-168): C=240, 8 heads,
+    # '3conv', nearest+conv x4
+    "swinir_l_small": dict(_SW, kw=dict(img_size=16, in_chans=3, embed_dim=240, depths=[2], num_heads=[8],
+                                        window_size=8, mlp_ratio=2, upscale=4, img_range=1.0, upsampler="nearest+conv",
+                                        resi_connection="3conv"), x=(1, 3, 16, 16), seed=14, loss="l1"),
     # JPEG-artifact model geometry: window 7, img_range 255
     "swinir_jpeg_ws7": dict(_SW, kw=dict(img_size=28, in_chans=1, embed_dim=180, depths=[2], num_heads=[6],
                                          window_size=7, mlp_ratio=2, upscale=1, img_range=255.0, upsampler="",

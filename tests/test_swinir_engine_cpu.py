@@ -116,21 +116,44 @@ def test_sr_heads_forward_vs_oracle(name):
     assert (y - y_ref).abs().max().item() < 2e-2
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2"])
+class _Fp32Buffers:
+    """Allocate fp32 wherever the engine / the emulation ask for bf16: what is left is pure host logic."""
+
+    def __enter__(self):
+        self.real = torch.bfloat16
+        torch.bfloat16 = torch.float32
+
+    def __exit__(self, *exc):
+        torch.bfloat16 = self.real
+
+
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small"])
 def test_sr_heads_backward_vs_oracle(name):
-    """Training through the reconstruction heads (options/swinir/train_swinir_sr_*.json): every parameter gradient of
-    the launch lists (emulated) against autograd through the oracle, smooth loss."""
+    """Training through the reconstruction heads and the '3conv' residual connection (options/swinir/train_swinir_sr_*.json,
+    SwinIR-L): every parameter gradient of the launch lists (emulated) against autograd through the oracle.  Checked
+    twice: with fp32 buffers (exact host logic, 1e-4) and with the real bf16 operands (rounding only)."""
     import golden_cases as gc
     case = gc.CASES[name]
     sd, x, tgt = gc.state_and_io(case)
-    mine = SwinIR(drop_path_rate=0.0, **case["kw"])
-    mine.load_state_dict(sd, strict=True)
     sdg = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point) for k, v in sd.items()}
     y_ref = gc.oracle_forward(case, sdg, x)
     _loss(y_ref, tgt).backward()
+
+    mine = SwinIR(drop_path_rate=0.0, **case["kw"])
+    mine.load_state_dict(sd, strict=True)
+    with _Fp32Buffers():
+        y, grads = _engine_step(mine, x, tgt)
+    assert (y - y_ref.detach()).abs().max().item() < 1e-4
+    bad = [(k, _rel_l2(grads[k], sdg[k].grad)) for k in grads if not _rel_l2(grads[k], sdg[k].grad) < 1e-4]
+    assert not bad, bad[:8]
+
+    mine = SwinIR(drop_path_rate=0.0, **case["kw"])
+    mine.load_state_dict(sd, strict=True)
     y, grads = _engine_step(mine, x, tgt)
     assert (y - y_ref.detach()).abs().max().item() < 2e-2
-    # the bias-table gradient is a sum over few windows here (6 in the 16x24 case) with heavy cancellation: 2x the bound
-    tol = lambda k: 1e-1 if k.endswith("relative_position_bias_table") else 5e-2
+    # bf16 operands: the bias-table gradient is a sum over few windows with heavy cancellation (2x the bound); the
+    # 12-channel LeakyReLU bottleneck of the C=48 '3conv' case amplifies rounding for everything upstream of it
+    wide = 2.5e-1 if name == "swinir_3conv" else 5e-2
+    tol = lambda k: max(wide, 1e-1) if k.endswith("relative_position_bias_table") else wide
     bad = [(k, _rel_l2(grads[k], sdg[k].grad)) for k in grads if not _rel_l2(grads[k], sdg[k].grad) < tol(k)]
     assert not bad, bad[:8]
