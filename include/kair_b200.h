@@ -115,7 +115,8 @@ typedef struct kair_gemm_nt_args {
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
- * kair_window_attn_fwd / _bwd: shifted-window multi-head attention core (8x8 windows, head_dim padded to 32).
+ * kair_window_attn_fwd / _bwd: shifted-window multi-head attention core (head_dim padded to 32).  window = 8 runs on
+ * tcgen05 / TMEM (shift 0 or 4); window = 2..7 (the 7x7 JPEG-artifact models) on a CUDA-core kernel (any shift < window).
  *   out[t, h*32+d] = sum_j softmax_j(q_i.k_j + table[rel(i,j)][h] + mask(i,j)) v_j
  * qkv holds [q | k | v] per token with columns [3][nH][32]; q is already multiplied by head_dim^-0.5.
  * Window partition / reverse (network_swinir.py:33-62), the cyclic shift (:249-252, 269-272) and the shifted-window

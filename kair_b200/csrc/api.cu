@@ -8,6 +8,8 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st);
 int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st);
 int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st);
 int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st);
+int window_attn_small_fwd_launch(const kair_window_attn_args& a, cudaStream_t st);
+int window_attn_small_bwd_launch(const kair_window_attn_args& a, cudaStream_t st);
 int pack_linear_launch(const kair_pack_linear_args& a, cudaStream_t st);
 int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st);
 int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st);
@@ -66,6 +68,8 @@ int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream) {
     kb::set_error("kair_window_attn_fwd: null args");
     return -1;
   }
+  // 8x8 windows: tcgen05 / TMEM kernel; smaller windows (7x7 JPEG models): CUDA-core kernel of attn_small.cu
+  if (args->window != 8) return kb::window_attn_small_fwd_launch(*args, (cudaStream_t)stream);
   return kb::window_attn_fwd_launch(*args, (cudaStream_t)stream);
 }
 
@@ -74,6 +78,7 @@ int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream) {
     kb::set_error("kair_window_attn_bwd: null args");
     return -1;
   }
+  if (args->window != 8) return kb::window_attn_small_bwd_launch(*args, (cudaStream_t)stream);
   return kb::window_attn_bwd_launch(*args, (cudaStream_t)stream);
 }
 

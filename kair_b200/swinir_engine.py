@@ -56,8 +56,8 @@ class SwinIRSpec:
         """Loud errors for configurations the sm_100a kernels do not cover yet (no fallback path exists)."""
         def bad(msg):
             raise NotImplementedError("kair_b200 SwinIR: " + msg + " (see DESIGN.md, 'coverage')")
-        if self.ws != 8:
-            bad("window_size=%d; the tcgen05 window-attention kernel is built for 8x8 windows" % self.ws)
+        if not 2 <= self.ws <= 8:
+            bad("window_size=%d; window attention kernels exist for 2..8 (8: tcgen05, smaller: CUDA cores)" % self.ws)
         if len(set(self.num_heads)) != 1:
             bad("num_heads must be the same in every RSTB")
         nH = self.num_heads[0]

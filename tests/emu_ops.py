@@ -203,7 +203,7 @@ def _attn_core(qkv, table, batch, H, W, nH, ws, shift):
 
 
 def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
-    assert window == 8 and shift in (0, 4)
+    assert 2 <= window <= 8 and 0 <= shift < window
 
     def run():
         w = 3 * num_heads * 32

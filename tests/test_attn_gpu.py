@@ -9,10 +9,9 @@ pytestmark = pytest.mark.gpu
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def _ref_attention(qkv, table, B, H, W, nH, shift, hd=32):
+def _ref_attention(qkv, table, B, H, W, nH, shift, hd=32, ws=8):
     """qkv: fp32 [B*H*W, 3*nH*hd] (q pre-scaled). Returns ([B*H*W, nH*hd], P) computed window by window."""
     from oracle import swinir_oracle as so
-    ws = 8
     N = ws * ws
     idx = so.window_token_index(H, W, ws, shift).to(qkv.device)            # (nW, N)
     nW = idx.shape[0]
@@ -34,7 +33,7 @@ def _ref_attention(qkv, table, B, H, W, nH, shift, hd=32):
     return out.view(B * H * W, nH * hd)
 
 
-def _make_qkv(B, H, W, nH, seed, dev):
+def _make_qkv(B, H, W, nH, seed, dev, ws=8):
     g = torch.Generator().manual_seed(seed)
     T = B * H * W
     qkv = torch.randn(T, 3 * nH * 32, generator=g) * 0.8
@@ -42,7 +41,7 @@ def _make_qkv(B, H, W, nH, seed, dev):
     qkv[..., 30:] = 0          # head_dim 30 padded to 32
     qkv[:, 2, 0, 30] = 1.0     # ones column of v (head 0) used for the proj bias gradient
     qkv = qkv.view(T, -1)
-    table = torch.randn(225, nH, generator=g) * 0.5
+    table = torch.randn((2 * ws - 1) ** 2, nH, generator=g) * 0.5
     return qkv.to(dev).bfloat16(), table.to(dev)
 
 
@@ -84,3 +83,44 @@ def test_window_attn_bwd(B, H, W, shift):
     e2 = (dtable - tf.grad).abs().max().item() / (tf.grad.abs().max().item() + 1e-9)
     assert e1 < 2e-2, ("dqkv", e1)
     assert e2 < 2e-2, ("dtable", e2)
+
+
+# ------------------------------------------------------------------ windows smaller than 8 (CUDA-core kernels, attn_small.cu)
+SMALL = [(7, 3, 2, 14, 21, 6), (7, 0, 1, 28, 28, 6), (7, 3, 1, 126, 126, 6), (4, 2, 2, 8, 12, 4), (5, 1, 1, 10, 15, 2)]
+
+
+@pytest.mark.parametrize("ws,shift,B,H,W,nH", SMALL)
+def test_small_window_attn_fwd(ws, shift, B, H, W, nH):
+    """7x7 windows of the JPEG-artifact models (main_test_swinir.py:170-175): shift 3 = ws // 2, 49 tokens / window."""
+    from kair_b200 import ops
+    dev = torch.device("cuda:0")
+    qkv, table = _make_qkv(B, H, W, nH, 500 + H + W + shift, dev, ws=ws)
+    out = torch.zeros(B * H * W, nH * 32, dtype=torch.bfloat16, device=dev)
+    ops.window_attn_fwd(qkv, table, out, batch=B, H=H, W=W, num_heads=nH, window=ws, shift=shift)
+    torch.cuda.synchronize()
+    ref = _ref_attention(qkv.float(), table, B, H, W, nH, shift, ws=ws)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2, err
+    assert (out.view(-1, nH, 32)[:, 0, 30].float() - 1.0).abs().max().item() < 1e-2
+
+
+@pytest.mark.parametrize("ws,shift,B,H,W,nH", SMALL)
+def test_small_window_attn_bwd(ws, shift, B, H, W, nH):
+    from kair_b200 import ops
+    dev = torch.device("cuda:0")
+    qkv, table = _make_qkv(B, H, W, nH, 700 + H + W + shift, dev, ws=ws)
+    g = torch.Generator().manual_seed(19)
+    dout = (torch.randn(B * H * W, nH * 32, generator=g) * 0.5).to(dev).bfloat16()
+    dqkv = torch.zeros_like(qkv)
+    dtable = torch.zeros_like(table)
+    ops.window_attn_bwd(qkv, table, dout, dqkv, dtable, batch=B, H=H, W=W, num_heads=nH, window=ws, shift=shift)
+    torch.cuda.synchronize()
+    qf = qkv.float().requires_grad_(True)
+    tf = table.clone().requires_grad_(True)
+    ref = _ref_attention(qf, tf, B, H, W, nH, shift, ws=ws)
+    (ref * dout.float()).sum().backward()
+    gq = qf.grad
+    e1 = (dqkv.float() - gq).abs().max().item() / (gq.abs().max().item() + 1e-9)
+    e2 = (dtable - tf.grad).abs().max().item() / (tf.grad.abs().max().item() + 1e-9)
+    assert e1 < 1e-2, ("dqkv", e1)
+    assert e2 < 1e-3, ("dtable", e2)

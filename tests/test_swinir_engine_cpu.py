@@ -127,7 +127,7 @@ class _Fp32Buffers:
         torch.bfloat16 = self.real
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small"])
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small", "swinir_jpeg_ws7"])
 def test_sr_heads_backward_vs_oracle(name):
     """Training through the reconstruction heads and the '3conv' residual connection (options/swinir/train_swinir_sr_*.json,
     SwinIR-L): every parameter gradient of the launch lists (emulated) against autograd through the oracle.  Checked

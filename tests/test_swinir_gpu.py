@@ -171,7 +171,7 @@ def test_golden_fixture_swinir_m_gray32():
     assert not bad, bad[:6]
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small"])
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small", "swinir_jpeg_ws7"])
 def test_golden_fixture_sr_heads(name):
     """cfg3 / cfg5 architectures (reduced depth): x4 pixelshuffle and nearest+conv heads under no_grad vs the golden
     output of the real reference module; bf16 result vs fp32 reference: 2e-2 max-abs and 0.02 dB PSNR (north_star)."""
@@ -207,7 +207,7 @@ def test_sr_x4_full_size_cfg3():
     assert torch.equal(y[4:8], y4)
 
 
-@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small"])
+@pytest.mark.parametrize("name", ["swinir_sr_ps4", "swinir_sr_nearest4", "swinir_s_psd2", "swinir_3conv", "swinir_l_small", "swinir_jpeg_ws7"])
 def test_sr_heads_training_vs_oracle(name):
     """Autograd through the reconstruction heads (classical / lightweight / real-world SR training,
     options/swinir/train_swinir_sr_*.json): output and every parameter gradient vs autograd through the oracle."""
