@@ -257,3 +257,48 @@ def test_sr_x2_training_step_cfg_classical():
         opt.step()
         losses.append(loss.item())
     assert losses[-1] < losses[0], losses
+
+
+# every model main_test_swinir.py:124-175 of the reference can construct (define_model), at its full architecture
+TASKS = {
+    "classical_sr_x2": dict(upscale=2, in_chans=3, img_size=48, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                            num_heads=[6] * 6, mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv"),
+    "classical_sr_x3": dict(upscale=3, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                            num_heads=[6] * 6, mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv"),
+    "classical_sr_x8": dict(upscale=8, in_chans=3, img_size=48, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                            num_heads=[6] * 6, mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv"),
+    "lightweight_sr_x3": dict(upscale=3, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 4, embed_dim=60,
+                              num_heads=[6] * 4, mlp_ratio=2, upsampler="pixelshuffledirect", resi_connection="1conv"),
+    "real_sr_x4_large": dict(upscale=4, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 9, embed_dim=240,
+                             num_heads=[8] * 9, mlp_ratio=2, upsampler="nearest+conv", resi_connection="3conv"),
+    "color_dn": dict(upscale=1, in_chans=3, img_size=128, window_size=8, img_range=1.0, depths=[6] * 6, embed_dim=180,
+                     num_heads=[6] * 6, mlp_ratio=2, upsampler="", resi_connection="1conv"),
+    "jpeg_car": dict(upscale=1, in_chans=1, img_size=126, window_size=7, img_range=255.0, depths=[6] * 6, embed_dim=180,
+                     num_heads=[6] * 6, mlp_ratio=2, upsampler="", resi_connection="1conv"),
+}
+
+
+@pytest.mark.parametrize("task", sorted(TASKS))
+def test_every_published_task_runs(task):
+    """Full-depth models of every task: inference on an input that is not a window multiple, batch-split invariance
+    (bit-exact: no cross-sample arithmetic), and one training step with finite gradients for all parameters."""
+    from kair_b200.network_swinir import SwinIR
+    kw = TASKS[task]
+    torch.manual_seed(0)
+    model = SwinIR(**kw).cuda().eval()
+    g = torch.Generator().manual_seed(2)
+    x = torch.rand(2, kw["in_chans"], 37, 45, generator=g).cuda()
+    with torch.no_grad():
+        y = model(x)
+        y0 = model(x[:1])
+    assert y.shape == (2, kw["in_chans"], 37 * kw["upscale"], 45 * kw["upscale"])
+    assert torch.isfinite(y).all().item()
+    assert torch.equal(y[:1], y0)
+    model.train()
+    ws = kw["window_size"]
+    xt = torch.rand(2, kw["in_chans"], 4 * ws, 4 * ws, generator=g).cuda()
+    out = model(xt)
+    out.abs().mean().backward()
+    for k, p in model.named_parameters():
+        assert p.grad is not None and torch.isfinite(p.grad).all().item(), k
+    assert sum(p.grad.abs().sum().item() for p in model.parameters()) > 0
