@@ -11,10 +11,9 @@ import math
 
 import torch
 import torch.nn as nn
-
-from . import parallel as _parallel
 import torch.nn.functional as F
 
+from . import parallel as _parallel
 from .swinir_engine import SwinIREngine, SwinIRFunction, SwinIRSpec
 
 
