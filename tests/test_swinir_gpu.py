@@ -302,3 +302,46 @@ def test_every_published_task_runs(task):
     for k, p in model.named_parameters():
         assert p.grad is not None and torch.isfinite(p.grad).all().item(), k
     assert sum(p.grad.abs().sum().item() for p in model.parameters()) > 0
+
+
+def test_amp_gradscaler_clip_and_frozen_params():
+    """The training loop of models/model_plain.py:273-300 of the reference around the drop-in module: autocast +
+    GradScaler (scaled loss -> unscale_ -> clip_grad_norm_ -> step), use_checkpoint=True accepted, and parameters with
+    requires_grad=False (main_test_dncnn.py:123-124) get no gradient while the rest match the unscaled run."""
+    from kair_b200.network_swinir import SwinIR
+    cfg = dict(CFG, depths=[2], num_heads=[6], use_checkpoint=True)
+    torch.manual_seed(0)
+    model = SwinIR(drop_path_rate=0.0, **cfg).cuda().train()
+    _randomize(model, 21)
+    g = torch.Generator().manual_seed(8)
+    x = torch.rand(2, 1, 32, 32, generator=g).cuda()
+    t = torch.rand(2, 1, 32, 32, generator=g).cuda()
+    charb = lambda a, b: torch.mean(torch.sqrt((a - b) ** 2 + 1e-9))
+
+    charb(model(x), t).backward()
+    plain = {k: p.grad.clone() for k, p in model.named_parameters()}
+    model.zero_grad(set_to_none=True)
+
+    frozen = [k for k in plain if "blocks.0.mlp" in k]
+    for k, p in model.named_parameters():
+        p.requires_grad_(k not in frozen)
+    opt = torch.optim.Adam([p for p in model.parameters() if p.requires_grad], lr=2e-4)
+    scaler = torch.amp.GradScaler("cuda", init_scale=1024.0)
+    before = {k: p.detach().clone() for k, p in model.named_parameters()}
+    with torch.autocast("cuda", dtype=torch.float16):
+        out = model(x)
+        loss = charb(out, t)
+    assert out.dtype == torch.float32
+    scaler.scale(loss).backward()
+    scaler.unscale_(opt)
+    total = torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=1e9)
+    assert torch.isfinite(total).item()
+    for k, p in model.named_parameters():
+        if k in frozen:
+            assert p.grad is None, k
+        else:
+            assert _rel_l2(p.grad, plain[k]) < 2e-2, (k, _rel_l2(p.grad, plain[k]))
+    scaler.step(opt)
+    scaler.update()
+    for k, p in model.named_parameters():
+        assert torch.equal(p.detach(), before[k]) == (k in frozen or plain[k].abs().max().item() == 0), k
