@@ -84,6 +84,8 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
+  pdl_wait();  // no global access above this point
+  pdl_launch_dependents();
   for (int i = threadIdx.x; i < 225 * nH; i += AB_THREADS) {
     int idx = i / nH, h = i - idx * nH;
     table_s[h * 225 + idx] = p.table[i];
@@ -471,8 +473,7 @@ int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
     attr_set[dev & 63] = true;
   }
   int grid = p.pairs < sm_count() ? p.pairs : sm_count();
-  window_attn_bwd_kernel<<<grid, AB_THREADS, smem, st>>>(p);
-  KB_CUDA(cudaGetLastError());
+  KB_CUDA(launch_pdl(window_attn_bwd_kernel, grid, AB_THREADS, smem, st, p));
   return 0;
 }
 

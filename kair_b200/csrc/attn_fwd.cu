@@ -106,6 +106,8 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
+  pdl_wait();  // no global access above this point
+  pdl_launch_dependents();
   // bias table -> smem as [h][idx]
   {
     // all loads of a thread are issued before the first store; values are pre-multiplied by log2(e) so that the
@@ -526,8 +528,7 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
     cudaMemset(ts_dev, 0, 3 * 256 * 8);
     p.ts = ts_dev;
   }
-  window_attn_fwd_kernel<<<grid, AF_THREADS, smem, st>>>(p);
-  KB_CUDA(cudaGetLastError());
+  KB_CUDA(launch_pdl(window_attn_fwd_kernel, grid, AF_THREADS, smem, st, p));
   if (want_ts) {
     static long long h[3 * 256];
     cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost);

@@ -68,6 +68,8 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
+  pdl_wait();  // no global access above this point
+  pdl_launch_dependents();
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -206,7 +208,7 @@ static int nt_launch_cfg(const NtParams& p, int grid, size_t smem, cudaStream_t 
     KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set[dev & 63] = true;
   }
-  kern<<<grid, NT_THREADS, smem, st>>>(p);
+  KB_CUDA(launch_pdl(kern, grid, NT_THREADS, smem, st, p));
   KB_CUDA(cudaGetLastError());
   return 0;
 }

@@ -191,6 +191,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
+  pdl_wait();  // everything above overlaps the previous kernel's tail; no global access before this point
+  pdl_launch_dependents();
   if (p.bias != nullptr && threadIdx.x >= 64 && threadIdx.x < 64 + BN) {
     bias_s[threadIdx.x - 64] = __ldg(p.bias + (blockIdx.x % p.n_tiles) * BN + (threadIdx.x - 64));
   }
@@ -777,8 +779,7 @@ static int launch_cfg(const TnParams& p, int grid, size_t smem, cudaStream_t st)
     KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set[dev & 63] = true;
   }
-  kern<<<grid, TN_THREADS, smem, st>>>(p);
-  KB_CUDA(cudaGetLastError());
+  KB_CUDA(launch_pdl(kern, grid, TN_THREADS, smem, st, p));
   return 0;
 }
 

@@ -63,6 +63,15 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* ba
   return 0;
 }
 
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("KB_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {

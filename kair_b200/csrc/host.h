@@ -35,6 +35,25 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* ba
               const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
               CUtensorMapSwizzle swizzle);
 
+// Programmatic dependent launch: the grid may become resident (barrier init, TMEM allocation, descriptor prefetch)
+// while the previous kernel of the stream drains; the kernel executes pdl_wait() before its first global access.
+// KB_PDL=0 in the environment launches with plain stream order.
+bool pdl_enabled();
+template <typename P>
+inline cudaError_t launch_pdl(void (*kern)(const P), int grid, int block, size_t smem, cudaStream_t st, const P& p) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
 int sm_count();
 int check_device();  // 0 if current device is sm_100; error otherwise
 
