@@ -7,7 +7,8 @@
 // written once, K-major, and consumed both as K-major and as MN-major operands), so no transposes are materialised.
 //
 //   warp 0      TMA producer: Q, K, V, dO tiles [2 windows x 64 tok][64 ch = 2 heads] per (window pair, head pair)
-//   warp 1      MMA issuer (UMMA M=64 per window; the two windows of a pair interleave in TMEM lanes)
+//   warp 1, 10  MMA issuers, one per group (UMMA M=64 per window; the two windows of a pair interleave in TMEM lanes);
+//               a single issuing thread was the critical path: ~85 cycles per tcgen05.mma, 32 of them per group
 //   warps 2..9  two groups (even / odd head of the pair), thread == query row: softmax recompute, delta, dS,
 //               P/dS -> swizzled smem, d_table partial sums kept in TMEM, dQ/dK/dV -> bf16 -> TMA scatter
 //
@@ -23,7 +24,7 @@
 
 namespace kb {
 
-constexpr int AB_THREADS = 320;
+constexpr int AB_THREADS = 352;   // producer, MMA issuer g0, 8 gradient warps, MMA issuer g1
 constexpr int AB_STAGE = 4 * 16384;   // Q, K, V, dO tiles of one head pair
 constexpr int AB_PDS = 32768;         // per group: P (16 KiB) + dS (16 KiB); reused as dq/dk/dv staging (24 KiB)
 
@@ -32,7 +33,14 @@ struct AttnBwdParams {
   const float* table;
   float* dtable;
   int nH, H, W, nWh, nWw, shift, total_windows, pairs;
+  long long* ts;  // development timeline buffer (env KB_AB_TS): [role][event] clock64 stamps of CTA 0
 };
+
+// timeline stamps: role 0 = MMA issuer, 1 = group 0 / thread 0, 2 = group 1 / thread 0; up to 256 events each
+#define AB_STAMP(role, cnt)                                                                    \
+  do {                                                                                         \
+    if (p.ts && blockIdx.x == 0 && (cnt) < 256) p.ts[(role) * 256 + (cnt)++] = clock64();      \
+  } while (0)
 
 __device__ __forceinline__ void ab_window_origin(const AttnBwdParams& p, int gw, int& b, int& wi, int& wj) {
   int nW = p.nWh * p.nWw;
@@ -56,7 +64,6 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
   uint64_t* w_free = grad_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_free + 2);
   float* table_s = reinterpret_cast<float*>(misc + 256);   // [nH][225]
-  float* dtab_s = table_s + p.nH * 225;                     // [2][225]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -72,7 +79,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     if (lane == 0) {
       for (int i = 0; i < 2; ++i) {
         mbar_init(&st_full[i], 1);
-        mbar_init(&st_empty[i], 1);
+        mbar_init(&st_empty[i], 2);   // one commit per MMA issuer
         mbar_init(&sdp_full[i], 1);
         mbar_init(&pds_full[i], 4);
         mbar_init(&grad_full[i], 1);
@@ -90,7 +97,6 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     int idx = i / nH, h = i - idx * nH;
     table_s[h * 225 + idx] = p.table[i];
   }
-  for (int i = threadIdx.x; i < 2 * 225; i += AB_THREADS) dtab_s[i] = 0.f;
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -131,25 +137,29 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // ================================ MMA issuer ================================
+  } else if (warp == 1 || warp == 10) {
+    // ================================ MMA issuers (warp 1: group 0, warp 10: group 1) ================================
     if (lane == 0) {
+      const int g = warp == 1 ? 0 : 1;
       constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);    // S, dP
       constexpr uint32_t idesc_dv = make_idesc_bf16(64, 32, 1, 1);   // P^T dO, dS^T Q
       constexpr uint32_t idesc_dq = make_idesc_bf16(64, 32, 0, 1);   // dS K
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
+      int tsc = 0;
+#define AB_MS() do { if (g == 0) AB_STAMP(0, tsc); } while (0)
       for (int hp = 0; hp < hpairs; ++hp) {
         for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++it) {
+          AB_MS();
           mbar_wait(&st_full[stage], phase);
           tcgen05_fence_after();
+          AB_MS();
           const uint32_t q_addr = smem_u32(stage_s + stage * AB_STAGE);
           const uint32_t k_addr = q_addr + 16384;
           const uint32_t v_addr = q_addr + 32768;
           const uint32_t do_addr = q_addr + 49152;
-#pragma unroll
-          for (int g = 0; g < 2; ++g) {
+          {
             mbar_wait(&w_free[g], (it & 1) ^ 1);
             tcgen05_fence_after();
             const uint32_t tw = tmem_base + g * 128;
@@ -168,9 +178,9 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
               }
             }
             umma_commit(&sdp_full[g]);
+            AB_MS();
           }
-#pragma unroll
-          for (int g = 0; g < 2; ++g) {
+          {
             mbar_wait(&pds_full[g], it & 1);
             tcgen05_fence_after();
             const uint32_t tw = tmem_base + g * 128;
@@ -196,6 +206,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
               }
             }
             umma_commit(&grad_full[g]);
+            AB_MS();
           }
           umma_commit(&st_empty[stage]);
           if (++stage == 2) {
@@ -224,6 +235,8 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     uint8_t* pds = pds_s + g * AB_PDS;
     const float LOG2E = 1.4426950408889634f;
     uint32_t it = 0;
+    int tsc = 0;
+#define AB_CS() do { if (gtid == 0) AB_STAMP(1 + g, tsc); } while (0)
 
     for (int hp = 0; hp < hpairs; ++hp) {
       const int h = hp * 2 + g;
@@ -253,8 +266,10 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         }
 
         // ---- A/B: S -> normalised P (fp32 registers)
+        AB_CS();
         mbar_wait(&sdp_full[g], it & 1);
         tcgen05_fence_after();
+        AB_CS();
         float pr[64];
         {
           uint32_t r0[32], r1[32];
@@ -291,6 +306,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         for (int j = 0; j < 64; ++j) pr[j] *= inv;
 
         // ---- C: delta = sum_j P_ij dP_ij
+        AB_CS();
         float dl4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -303,8 +319,10 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         const float delta = (dl4[0] + dl4[1]) + (dl4[2] + dl4[3]);
 
         // ---- D: the P/dS tiles double as the previous iteration's output staging: wait for its TMA reads
-        if (gtid == 0) tma_store_wait_read<0>();
+        AB_CS();
+        if (lane == 0) tma_store_wait_read<0>();   // every warp issued the stores of its own quadrant rows
         named_bar_sync(2 + g, 128);
+        AB_CS();
 
         // ---- E: dS, d_table partial sums, P/dS -> smem
         const float vmask = my_valid ? 1.0f : 0.0f;
@@ -344,10 +362,12 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&pds_full[g]);
+        AB_CS();
 
         // ---- G: dV | dQ | dK -> bf16 -> staging (64-byte rows, SWIZZLE_64B), tensor order dq, dk, dv
         mbar_wait(&grad_full[g], it & 1);
         tcgen05_fence_after();
+        AB_CS();
         {
           const uint32_t sw64 = (row >> 1) & 3;
 #pragma unroll
@@ -374,27 +394,33 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&w_free[g]);
-        named_bar_sync(2 + g, 128);
-        if (gtid == 0) {
+        AB_CS();
+        // the staging rows of quadrant q of both windows were written by this warp alone: its lane 0 stores them
+        // (6 TMA operations per warp instead of 24 from one thread, which took ~2600 cycles)
+        if (lane == 0) {
           for (int ws2 = 0; ws2 < (second_valid ? 2 : 1); ++ws2) {
             int b2, wi2, wj2;
             ab_window_origin(p, gw0 + ws2, b2, wi2, wj2);
-            for (int quad = 0; quad < 4; ++quad) {
-              const int hh2 = (wi2 * 8 + (quad >> 1) * 4 + p.shift) % p.H;
-              const int ww2 = (wj2 * 8 + (quad & 1) * 4 + p.shift) % p.W;
+            const int hh2 = (wi2 * 8 + (q >> 1) * 4 + p.shift) % p.H;
+            const int ww2 = (wj2 * 8 + (q & 1) * 4 + p.shift) % p.W;
 #pragma unroll
-              for (int t3 = 0; t3 < 3; ++t3)
-                tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws2 * 4 + quad) * 1024, t3 * nH * 32 + h * 32, ww2, hh2,
-                             b2);
-            }
+            for (int t3 = 0; t3 < 3; ++t3)
+              tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws2 * 4 + q) * 1024, t3 * nH * 32 + h * 32, ww2, hh2, b2);
           }
           tma_store_commit();
         }
+        __syncwarp();
+        AB_CS();
       }
 
-      // ---- end of pass: fold the per-row partial sums into d_table[:, h]
+      // ---- end of pass: fold the per-row partial sums into d_table[:, h].  The two windows of the pair are summed by a
+      // shuffle, the 64x64 (i, j) sums go to shared memory (the P/dS tiles are idle now) and each table entry gathers
+      // its (8-|dy|)(8-|dx|) contributions with plain loads: one global atomic per entry and pass.  (Shared-memory
+      // atomics per (i, j) cost ~21 000 cycles per pass: fp32 atomicAdd on shared memory is a CAS loop.)
       {
-        float* dt = dtab_s + g * 225;
+        if (lane == 0) tma_store_wait_read<0>();
+        named_bar_sync(2 + g, 128);
+        float* M = reinterpret_cast<float*>(pds);  // [64][65]
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t a[32];
@@ -402,23 +428,43 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int jj = c * 32 + j;
-            const int qj = jj >> 4;
-            const int jy = (qj >> 1) * 4 + ((jj & 15) >> 2);
-            const int jx = (qj & 1) * 4 + (jj & 3);
-            atomicAdd(&dt[base_i + (7 - jy) * 15 + (7 - jx)], __uint_as_float(a[j]));
+            float v = __uint_as_float(a[j]);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (lane < 16) M[i * 65 + c * 32 + j] = v;
           }
         }
         named_bar_sync(2 + g, 128);
         for (int idx = gtid; idx < 225; idx += 128) {
-          float v = dt[idx];
-          if (v != 0.f) atomicAdd(&p.dtable[idx * nH + h], v);
-          dt[idx] = 0.f;
+          const int dy = idx / 15 - 7, dx = idx % 15 - 7;
+          // fixed 8x8 trip counts with predicated loads: all 64 loads are independent (a variable-bound loop made
+          // this gather a ~7000-cycle dependent chain)
+          int fx[8];
+          bool vx[8];
+#pragma unroll
+          for (int xi = 0; xi < 8; ++xi) {
+            const int xj = xi - dx;
+            vx[xi] = (unsigned)xj < 8u;
+            fx[xi] = (xj >> 2) * 16 + (xj & 3);
+          }
+          float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int yi = 0; yi < 8; ++yi) {
+            const int yj = yi - dy;
+            const bool vy = (unsigned)yj < 8u;
+            const int fy = (yj >> 2) * 32 + (yj & 3) * 4;
+#pragma unroll
+            for (int xi = 0; xi < 8; ++xi) {
+              const int ii = ((yi >> 2) * 2 + (xi >> 2)) * 16 + (yi & 3) * 4 + (xi & 3);
+              s4[xi & 3] += (vy && vx[xi]) ? M[ii * 65 + fy + fx[xi]] : 0.f;
+            }
+          }
+          const float s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+          if (s != 0.f) atomicAdd(&p.dtable[idx * nH + h], s);
         }
         named_bar_sync(2 + g, 128);
       }
     }
-    if (gtid == 0) tma_store_wait_all<0>();
+    if (lane == 0) tma_store_wait_all<0>();
     __syncwarp();
   }
 
@@ -473,7 +519,25 @@ int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
     attr_set[dev & 63] = true;
   }
   int grid = p.pairs < sm_count() ? p.pairs : sm_count();
+  static long long* ts_dev = nullptr;
+  const bool want_ts = getenv("KB_AB_TS") != nullptr;
+  if (want_ts) {
+    if (!ts_dev) cudaMalloc(&ts_dev, 3 * 256 * 8);
+    cudaMemset(ts_dev, 0, 3 * 256 * 8);
+    p.ts = ts_dev;
+  }
   KB_CUDA(launch_pdl(window_attn_bwd_kernel, grid, AB_THREADS, smem, st, p));
+  if (want_ts) {
+    static long long h[3 * 256];
+    cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    const long long t0 = h[0];
+    const char* names[3] = {"mma", "group0", "group1"};
+    for (int r = 0; r < 3; ++r) {
+      fprintf(stderr, "%s:", names[r]);
+      for (int i = 0; i < 72 && h[r * 256 + i]; ++i) fprintf(stderr, " %lld", h[r * 256 + i] - t0);
+      fprintf(stderr, "\n");
+    }
+  }
   return 0;
 }
 
