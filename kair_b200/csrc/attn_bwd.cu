@@ -256,6 +256,13 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         const int gw = (wsel && second_valid) ? gw0 + 1 : gw0;
         int wb, wi, wj;
         ab_window_origin(p, gw, wb, wi, wj);
+        // output box coordinates of this warp's quadrant in both windows, for the lane that issues the TMA stores
+        // (computed here, off the critical path between grad_full and the stores; lane 16 holds the second window)
+        int sy = wi * 8 + (q >> 1) * 4 + p.shift, sx = wj * 8 + (q & 1) * 4 + p.shift;
+        if (sy >= p.H) sy -= p.H;
+        if (sx >= p.W) sx -= p.W;
+        const int sb1 = __shfl_sync(0xffffffffu, wb, 16), sy1 = __shfl_sync(0xffffffffu, sy, 16),
+                  sx1 = __shfl_sync(0xffffffffu, sx, 16);
         const bool lastrow = p.shift > 0 && wi == p.nWh - 1;
         const bool lastcol = p.shift > 0 && wj == p.nWw - 1;
         float madd[4];
@@ -398,14 +405,13 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         // the staging rows of quadrant q of both windows were written by this warp alone: its lane 0 stores them
         // (6 TMA operations per warp instead of 24 from one thread, which took ~2600 cycles)
         if (lane == 0) {
-          for (int ws2 = 0; ws2 < (second_valid ? 2 : 1); ++ws2) {
-            int b2, wi2, wj2;
-            ab_window_origin(p, gw0 + ws2, b2, wi2, wj2);
-            const int hh2 = (wi2 * 8 + (q >> 1) * 4 + p.shift) % p.H;
-            const int ww2 = (wj2 * 8 + (q & 1) * 4 + p.shift) % p.W;
+#pragma unroll
+          for (int t3 = 0; t3 < 3; ++t3)
+            tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + q * 1024, t3 * nH * 32 + h * 32, sx, sy, wb);
+          if (second_valid) {
 #pragma unroll
             for (int t3 = 0; t3 < 3; ++t3)
-              tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws2 * 4 + q) * 1024, t3 * nH * 32 + h * 32, ww2, hh2, b2);
+              tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (4 + q) * 1024, t3 * nH * 32 + h * 32, sx1, sy1, sb1);
           }
           tma_store_commit();
         }
