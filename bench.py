@@ -203,9 +203,11 @@ def _ncu_traffic(tag):
 
 
 def _group_table(groups):
+    """per kernel group: launches, total ms, algorithmic TFLOP/s, algorithmic GB/s and the written share of it"""
     return {k: {"n": v["count"], "ms": round(v["ms"], 4),
                 "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 1) if v["ms"] > 0 else 0.0,
-                "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 0) if v["ms"] > 0 else 0.0}
+                "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 0) if v["ms"] > 0 else 0.0,
+                "write_gbs": round(v.get("wbytes", 0.0) / (v["ms"] * 1e-3) / 1e9, 0) if v["ms"] > 0 else 0.0}
             for k, v in sorted(groups.items(), key=lambda kv: -kv[1]["ms"])}
 
 
@@ -340,6 +342,9 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": top["bytes"] / top["count"],
                 "algorithmic_flops_per_launch": top["flops"] / top["count"],
                 "peak_source": peak_src + " / hbm_gbs",
+                # pure-write ceiling of this GPU's HBM (fill kernel, measured live): write-heavy groups in `groups`
+                # (write_gbs close to this number) are at their roofline although `gbs` is far from `peak`
+                "hbm_write_peak": round(profiling.measure_fill_gbs(dev), 0),
                 "whole_step": {"tflops": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step,
                                "frac": 3 * FWD_GFLOP_PER_PATCH * BATCH_PER_GPU / ms_step / peak_tf,
                                "sum_kernel_ms": tot},
@@ -641,6 +646,7 @@ def run_b200_workload(args):
                      "algorithmic_bytes_per_launch": top["bytes"] / top["count"],
                      "algorithmic_flops_per_launch": top["flops"] / top["count"],
                      "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)",
+                     "hbm_write_peak": round(profiling.measure_fill_gbs(dev), 0),
                      "whole_step": {"tflops": fwd_gflop / ms_step, "frac": fwd_gflop / ms_step / peak_tf,
                                     "sum_kernel_ms": tot * passes},
                      "groups": _group_table(groups)})

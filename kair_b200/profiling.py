@@ -81,6 +81,22 @@ def describe(launch, real_dims):
     return name, 0.0, 0.0
 
 
+def write_bytes(launch, real_dims):
+    """Algorithmic HBM bytes WRITTEN by one launch (subset of describe()'s bytes) for the kernels that dominate a step.
+    B200 HBM3e sustains ~6.5 TB/s for mixed traffic but only ~3.9 TB/s for pure writes (measured with a fill kernel,
+    bench.py `hbm_write_peak`), so write-heavy epilogues (qkv, fc1+GELU: 75-80 % writes) have a lower ceiling."""
+    a = getattr(launch, "args", None)
+    name = launch.name.replace("kair_", "")
+    r = lambda n: real_dims.get(int(n), int(n))
+    if name == "gemm_tn":
+        return 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
+    if name in ("window_attn_fwd", "window_attn_bwd"):
+        T = a.batch * a.H * a.W
+        hd = real_dims.get("head_dim", 30)
+        return (3.0 if name.endswith("bwd") else 1.0) * T * a.num_heads * hd * 2
+    return 0.0
+
+
 def time_launches(launches, stream_handle, reps=1):
     """Run `launches` in order `reps` times on the current stream with a CUDA event between every pair of launches;
     returns per-launch mean milliseconds (list aligned with `launches`)."""
@@ -103,12 +119,29 @@ def summarize(launches, ms, real_dims):
     out = {}
     for l, t in zip(launches, ms):
         tag, fl, by = describe(l, real_dims)
-        d = out.setdefault(tag, dict(count=0, ms=0.0, flops=0.0, bytes=0.0))
+        d = out.setdefault(tag, dict(count=0, ms=0.0, flops=0.0, bytes=0.0, wbytes=0.0))
         d["count"] += 1
         d["ms"] += t
         d["flops"] += fl
         d["bytes"] += by
+        d["wbytes"] += write_bytes(l, real_dims)
     return out
+
+
+def measure_fill_gbs(device, mib=512, reps=5):
+    """Pure-write HBM bandwidth of this GPU (GB/s): best of `reps` fills of a `mib` MiB buffer (calibration only)."""
+    x = torch.empty(mib << 20, dtype=torch.uint8, device=device)
+    x.zero_()
+    torch.cuda.synchronize(device)
+    best = float("inf")
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        x.zero_()
+        b.record()
+        b.synchronize()
+        best = min(best, a.elapsed_time(b))
+    return (mib << 20) / (best * 1e-3) / 1e9
 
 
 def roofline_of(group, peak_tflops, peak_gbs):
