@@ -2,8 +2,12 @@
 //
 // Both operands are read in their natural token-major layout, i.e. "MN-major" UMMA operands: TMA brings
 // [64 tokens x 64 channels] SWIZZLE_128B atoms and tcgen05.mma consumes them with a_major = b_major = MN.
-// The token range is split across CTAs; every CTA keeps one 128 x BN accumulator tile in TMEM for its whole token
-// range and finally adds it into the fp32 result with a TMA reduce-add (cp.reduce.async.bulk.tensor ... .add).
+// The token range is split across CTAs; every CTA keeps a BM x BN accumulator (BM = 128, or 256 as two 128-row
+// accumulators that share each B tile) in TMEM for its whole token range and finally adds it into the fp32 result with a
+// TMA reduce-add (cp.reduce.async.bulk.tensor ... .add).  The kernel is bound by the L2 -> shared-memory fill rate
+// (cycle counters, KB_NT_TS: producer and MMA issuer each wait half of the time; ~38 B/clk per SM whatever the tile
+// shape), so BM = 256 is used when it makes n1 a single tile: every B tile is then read by half as many CTAs.  The
+// epilogue staging aliases the pipeline stages (all loads are consumed by then).
 // Conv mode: B is an NHWC image read through 9 shifted 4-D boxes (TMA zero fill = zero padding), the result column
 // block is tap*K2.
 //
@@ -19,7 +23,7 @@ namespace kb {
 
 constexpr int NT_THREADS = 320;
 constexpr int NT_BKT = 64;                    // tokens per pipeline stage
-constexpr int NT_A_STAGE = 128 * NT_BKT * 2;  // 16 KiB: two [64 tok x 64 ch] atoms
+constexpr int NT_A_ATOM2 = 128 * NT_BKT * 2;  // 16 KiB: two [64 tok x 64 ch] atoms = one 128-row A operand
 constexpr int NT_STG_PER_WARP = 8192;         // 2 x 4 KiB fp32 chunks
 constexpr int NT_STG_BYTES = 8 * NT_STG_PER_WARP;
 constexpr int NT_MAX_STAGES = 8;
@@ -30,17 +34,21 @@ struct NtParams {
   int T, kb_total, kb_per_split, splits, tiles1, tiles2, taps, stages;
   int H, W, TW, TH, tiles_w, tiles_h;  // conv: a k-block is a TW x TH pixel patch (TW*TH = 64)
   int k2;                              // channels of B per tap (conv: column block stride in D)
+  int ring;                            // bytes of the stage ring (>= the epilogue staging that aliases it)
+  long long* ts;                       // development aid (env KB_NT_TS): cycle counters of CTA 0
 };
 
-template <int BN, bool kConv>
+template <int BN, bool kConv, int BM>
 __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_constant__ NtParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   constexpr int B_STAGE = BN * NT_BKT * 2;
-  uint8_t* stg_base = smem;
-  uint8_t* a_base = smem + NT_STG_BYTES;
+  constexpr int NT_A_STAGE = (BM / 128) * NT_A_ATOM2;
+  constexpr int NACC = BM / 128;
+  uint8_t* stg_base = smem;   // aliases the pipeline stages: used only after the last MMA has completed
+  uint8_t* a_base = smem;
   uint8_t* b_base = a_base + p.stages * NT_A_STAGE;
-  uint8_t* misc = b_base + p.stages * B_STAGE;
+  uint8_t* misc = smem + p.ring;   // ring >= NT_STG_BYTES, so the aliased staging never reaches the barriers
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);
   uint64_t* empty_bar = full_bar + NT_MAX_STAGES;
   uint64_t* tfull_bar = empty_bar + NT_MAX_STAGES;
@@ -48,7 +56,8 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
+  constexpr int ACC_COLS = NACC * BN;
+  constexpr uint32_t TMEM_COLS = ACC_COLS <= 64 ? 64 : (ACC_COLS <= 128 ? 128 : (ACC_COLS <= 256 ? 256 : 512));
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -93,8 +102,11 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       const int dy = tap / 3, dx = tap - dy * 3;
+      long long t_wait = 0, t_begin = clock64();
       for (int kb = kb0; kb < kb1; ++kb) {
+        const long long tw0 = clock64();
         mbar_wait(&empty_bar[stage], phase ^ 1);
+        t_wait += clock64() - tw0;
         mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
         uint8_t* a_s = a_base + stage * NT_A_STAGE;
         uint8_t* b_s = b_base + stage * B_STAGE;
@@ -105,15 +117,15 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           int th = r / p.tiles_w;
           int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
 #pragma unroll
-          for (int i = 0; i < 2; ++i)
-            tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * 128 + i * 64, w0, h0, b);
+          for (int i = 0; i < BM / 64; ++i)
+            tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * BM + i * 64, w0, h0, b);
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
             tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0 + dx - 1, h0 + dy - 1, b);
         } else {
 #pragma unroll
-          for (int i = 0; i < 2; ++i)
-            tma_load_2d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * 128 + i * 64, kb * NT_BKT);
+          for (int i = 0; i < BM / 64; ++i)
+            tma_load_2d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * BM + i * 64, kb * NT_BKT);
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
             tma_load_2d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, kb * NT_BKT);
@@ -123,6 +135,11 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           phase ^= 1;
         }
       }
+      if (p.ts && blockIdx.x == 0) {
+        p.ts[0] = t_wait;
+        p.ts[1] = clock64() - t_begin;
+        p.ts[2] = nkb;
+      }
     }
     __syncwarp();
   } else if (warp == 1) {
@@ -130,15 +147,20 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
+      long long t_wait = 0, t_begin = clock64();
       for (int kb = 0; kb < nkb; ++kb) {
+        const long long tw0 = clock64();
         mbar_wait(&full_bar[stage], phase);
+        t_wait += clock64() - tw0;
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(a_base + stage * NT_A_STAGE);
         const uint32_t b_addr = smem_u32(b_base + stage * B_STAGE);
 #pragma unroll
         for (int k = 0; k < NT_BKT / 16; ++k) {
-          umma_f16_ss(tmem_base, make_desc_mnmajor_sw128(a_addr + k * 2048, NT_BKT),
-                      make_desc_mnmajor_sw128(b_addr + k * 2048, NT_BKT), idesc, (kb | k) != 0 ? 1u : 0u);
+#pragma unroll
+          for (int acc = 0; acc < NACC; ++acc)
+            umma_f16_ss(tmem_base + acc * BN, make_desc_mnmajor_sw128(a_addr + acc * NT_A_ATOM2 + k * 2048, NT_BKT),
+                        make_desc_mnmajor_sw128(b_addr + k * 2048, NT_BKT), idesc, (kb | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == p.stages) {
@@ -147,6 +169,10 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         }
       }
       umma_commit(tfull_bar);
+      if (p.ts && blockIdx.x == 0) {
+        p.ts[3] = t_wait;
+        p.ts[4] = clock64() - t_begin;
+      }
     }
     __syncwarp();
   } else if (nkb > 0) {
@@ -156,13 +182,16 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
     constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 32;
     uint8_t* stg = stg_base + ew * NT_STG_PER_WARP;
+    const long long te0 = clock64();
     mbar_wait(tfull_bar, 0);
+    const long long te1 = clock64();
     tcgen05_fence_after();
-    const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + hf * HALF;
     const int col_base = tap * p.k2 + tile2 * BN + hf * HALF;
     int sbuf = 0;
 #pragma unroll 1
-    for (int c = 0; c < NCH; ++c) {
+    for (int cc = 0; cc < NACC * NCH; ++cc) {
+      const int acc = cc / NCH, c = cc - acc * NCH;
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + hf * HALF;
       uint32_t r[32];
       tmem_ld32(tacc + c * 32, r);
       tmem_ld_wait();
@@ -181,13 +210,17 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        tma_reduce_add_2d(&p.tmD, buf, col_base + c * 32, tile1 * 128 + q * 32);
+        tma_reduce_add_2d(&p.tmD, buf, col_base + c * 32, tile1 * BM + acc * 128 + q * 32);
         tma_store_commit();
       }
       sbuf ^= 1;
     }
     if (lane == 0) tma_store_wait_all<0>();
     __syncwarp();
+    if (p.ts && blockIdx.x == 0 && ew == 0 && lane == 0) {
+      p.ts[5] = te1 - te0;
+      p.ts[6] = clock64() - te1;
+    }
   }
 
   tcgen05_fence_before();
@@ -198,9 +231,16 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
   }
 }
 
-template <int BN, bool kConv>
-static int nt_launch_cfg(const NtParams& p, int grid, size_t smem, cudaStream_t st) {
-  auto kern = gemm_nt_kernel<BN, kConv>;
+template <int BN, bool kConv, int BM>
+static int nt_launch_cfg(NtParams p, int grid, size_t smem, cudaStream_t st) {
+  auto kern = gemm_nt_kernel<BN, kConv, BM>;
+  static long long* ts_dev = nullptr;
+  const bool want_ts = getenv("KB_NT_TS") != nullptr;
+  if (want_ts) {
+    if (!ts_dev) cudaMalloc(&ts_dev, 8 * 8);
+    cudaMemset(ts_dev, 0, 8 * 8);
+    p.ts = ts_dev;
+  }
   static bool attr_set[64] = {false};
   int dev = 0;
   KB_CUDA(cudaGetDevice(&dev));
@@ -210,6 +250,13 @@ static int nt_launch_cfg(const NtParams& p, int grid, size_t smem, cudaStream_t 
   }
   KB_CUDA(launch_pdl(kern, grid, NT_THREADS, smem, st, p));
   KB_CUDA(cudaGetLastError());
+  if (want_ts) {
+    long long h[8];
+    cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "gemm_nt<%d,%d,%d> grid %d stages %d splits %d kb/split %d: producer wait %lld of %lld cycles (%lld k-blocks); "
+            "mma wait %lld of %lld; epilogue waited %lld, ran %lld\n", BN, (int)kConv, BM, grid, p.stages, p.splits,
+            p.kb_per_split, h[0], h[1], h[2], h[3], h[4], h[5], h[6]);
+  }
   return 0;
 }
 
@@ -226,7 +273,14 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   memset(&p, 0, sizeof(p));
   p.T = a.T;
   p.taps = a.conv ? 9 : 1;
-  p.tiles1 = (a.n1 + 127) / 128;
+  // measured at cfg2 sizes (tools/scratch/nt_ts.py): one 256-row tile beats two 128-row tiles by 13-14 % (n1 = 192);
+  // with more than one tile the uneven last tile and the doubled, un-overlapped epilogue cancel the gain (n1 = 384, 576)
+  int bm = (a.n1 > 128 && a.n1 <= 256) ? 256 : 128;
+  {
+    const char* e = getenv("KB_NT_BM");   // development aid: force the accumulator height
+    if (e && (atoi(e) == 128 || atoi(e) == 256)) bm = atoi(e);
+  }
+  p.tiles1 = (a.n1 + bm - 1) / bm;
   p.tiles2 = a.n2 / a.bn;
   p.k2 = a.n2;
   if (a.conv) {
@@ -283,11 +337,15 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   }
 
   const int b_stage = a.bn * NT_BKT * 2;
-  int stages = (232448 - 1024 - NT_STG_BYTES - NT_MISC_BYTES) / (NT_A_STAGE + b_stage);
+  const int a_stage = (bm / 128) * NT_A_ATOM2;
+  int stages = (232448 - 1024 - NT_MISC_BYTES) / (a_stage + b_stage);
   if (stages > NT_MAX_STAGES) stages = NT_MAX_STAGES;
   KB_CHECK(stages >= 2, "kair_gemm_nt: not enough shared memory");
   p.stages = stages;
-  size_t smem = 1024 + NT_STG_BYTES + (size_t)stages * (NT_A_STAGE + b_stage) + NT_MISC_BYTES;
+  size_t ring = (size_t)stages * (a_stage + b_stage);
+  if (ring < (size_t)NT_STG_BYTES) ring = NT_STG_BYTES;   // the epilogue staging aliases the ring
+  p.ring = (int)ring;
+  size_t smem = 1024 + ring + NT_MISC_BYTES;
 
   const int items = p.tiles1 * p.tiles2 * p.taps;
   int splits = a.splits > 0 ? a.splits : sm_count() / items;
@@ -298,21 +356,18 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   p.splits = splits;
   const int grid = items * splits;
 
-  if (a.conv) {
-    switch (a.bn) {
-      case 64: return nt_launch_cfg<64, true>(p, grid, smem, st);
-      case 128: return nt_launch_cfg<128, true>(p, grid, smem, st);
-      case 192: return nt_launch_cfg<192, true>(p, grid, smem, st);
-      case 256: return nt_launch_cfg<256, true>(p, grid, smem, st);
-    }
-  } else {
-    switch (a.bn) {
-      case 64: return nt_launch_cfg<64, false>(p, grid, smem, st);
-      case 128: return nt_launch_cfg<128, false>(p, grid, smem, st);
-      case 192: return nt_launch_cfg<192, false>(p, grid, smem, st);
-      case 256: return nt_launch_cfg<256, false>(p, grid, smem, st);
-    }
-  }
+#define KB_NT_CASE(BN_, CONV_)                                                              \
+  if (a.bn == BN_ && (a.conv != 0) == CONV_)                                                \
+    return bm == 256 ? nt_launch_cfg<BN_, CONV_, 256>(p, grid, smem, st) : nt_launch_cfg<BN_, CONV_, 128>(p, grid, smem, st);
+  KB_NT_CASE(64, true)
+  KB_NT_CASE(128, true)
+  KB_NT_CASE(192, true)
+  KB_NT_CASE(256, true)
+  KB_NT_CASE(64, false)
+  KB_NT_CASE(128, false)
+  KB_NT_CASE(192, false)
+  KB_NT_CASE(256, false)
+#undef KB_NT_CASE
   return -1;
 }
 
