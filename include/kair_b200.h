@@ -447,6 +447,42 @@ int kair_pixel_shuffle_out_bwd(const kair_shuffle_out_args* args, void* stream);
 /* y += x (fp32, n elements, n % 4 == 0); yb (bf16, optional) receives the updated y */
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * The serial tail of a training step.
+ *   kair_pixel_loss  CharbonnierLoss (models/loss.py:208-218; mode 0) or nn.L1Loss (mode 1) and its gradient in one pass:
+ *                    loss[0] = mean(sqrt((x-y)^2 + eps)),  dx = d(loss)/dx.  `scratch` is two zero-initialised 8-byte
+ *                    words owned by the caller (sum, arrival counter); the kernel re-arms them.
+ *   kair_adam_ema    torch.optim.Adam (L2 weight decay, no amsgrad; torch/optim/adam.py `_single_tensor_adam`) for L tensors
+ *                    in one launch + the EMA of ModelBase.update_E (models/model_base.py:247-252) on the updated values:
+ *                    e = e*ema_decay + p*(1-ema_decay).  step_size = lr / (1-beta1^t), bc2_sqrt = sqrt(1-beta2^t).
+ *                    chunk_tensor / chunk_offset list the (tensor, first element) of every 8192-element chunk.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_pixel_loss_args {
+  const float* x;
+  const float* y;
+  float* dx;         /* or NULL */
+  float* loss;       /* 1 element */
+  double* scratch;   /* 2 x 8 bytes, zero before the first call */
+  int64_t n;
+  float eps;
+  int32_t mode;      /* 0 Charbonnier, 1 L1 */
+} kair_pixel_loss_args;
+int kair_pixel_loss(const kair_pixel_loss_args* args, void* stream);
+
+typedef struct kair_adam_ema_args {
+  void* const* p;            /* [L] -> fp32 parameters (updated in place) */
+  const void* const* g;      /* [L] -> fp32 gradients */
+  void* const* m;            /* [L] -> exp_avg */
+  void* const* v;            /* [L] -> exp_avg_sq */
+  void* const* e;            /* [L] -> EMA copies, or NULL */
+  const int64_t* sizes;      /* [L] element counts */
+  const int32_t* chunk_tensor;
+  const int64_t* chunk_offset;
+  int32_t n_chunks, chunk_elems;  /* chunk_elems must be 8192 */
+  float step_size, beta1, beta2, eps, bc2_sqrt, weight_decay, ema_decay;
+} kair_adam_ema_args;
+int kair_adam_ema(const kair_adam_ema_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

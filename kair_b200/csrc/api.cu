@@ -35,6 +35,8 @@ int bn_fold_launch(const kair_bn_args& a, cudaStream_t st);
 int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st);
 int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st);
+int pixel_loss_launch(const kair_pixel_loss_args& a, cudaStream_t st);
+int adam_ema_launch(const kair_adam_ema_args& a, cudaStream_t st);
 int pixel_shuffle_out_bwd_launch(const kair_shuffle_out_args& a, cudaStream_t st);
 int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
@@ -115,6 +117,8 @@ KB_WRAP(kair_bn_fold, kair_bn_args, bn_fold_launch)
 KB_WRAP(kair_pixel_shuffle, kair_shuffle_args, pixel_shuffle_launch)
 KB_WRAP(kair_upsample_nearest2, kair_shuffle_args, upsample_nearest2_launch)
 KB_WRAP(kair_pixel_shuffle_out, kair_shuffle_out_args, pixel_shuffle_out_launch)
+KB_WRAP(kair_pixel_loss, kair_pixel_loss_args, pixel_loss_launch)
+KB_WRAP(kair_adam_ema, kair_adam_ema_args, adam_ema_launch)
 KB_WRAP(kair_pixel_shuffle_out_bwd, kair_shuffle_out_args, pixel_shuffle_out_bwd_launch)
 KB_WRAP(kair_pixel_shuffle_bwd, kair_shuffle_args, pixel_shuffle_bwd_launch)
 KB_WRAP(kair_upsample_nearest2_bwd, kair_shuffle_args, upsample_nearest2_bwd_launch)

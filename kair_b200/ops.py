@@ -530,6 +530,50 @@ def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
     return Launch("kair_pixel_shuffle_out", a)
 
 
+def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
+    """loss[0] = mean(sqrt((x-y)^2 + eps)) (mode 0, CharbonnierLoss) or mean|x-y| (mode 1) and dx = d(loss)/dx."""
+    _req(x, torch.float32, "x"); _req(y, torch.float32, "y"); _req(dx, torch.float32, "dx")
+    _req(loss, torch.float32, "loss"); _req(scratch, torch.float64, "scratch")
+    if not (x.is_contiguous() and y.is_contiguous() and (dx is None or dx.is_contiguous())) or x.shape != y.shape:
+        raise RuntimeError("kair_b200: pixel_loss needs contiguous x, y (and dx) of the same shape")
+    if scratch.numel() < 2:
+        raise RuntimeError("kair_b200: pixel_loss scratch must hold two 8-byte words")
+    a = _S["kair_pixel_loss_args"]()
+    a.x, a.y, a.dx, a.loss, a.scratch = _ptr(x), _ptr(y), _ptr(dx), _ptr(loss), _ptr(scratch)
+    a.n, a.eps, a.mode = x.numel(), eps, mode
+    return Launch("kair_pixel_loss", a)
+
+
+ADAM_CHUNK = 8192
+
+
+def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_decay=0.0):
+    """One launch of Adam (+ EMA when `e` is given) over the tensor lists.  The per-step scalars (step_size,
+    bc2_sqrt) are set on the returned launch's `args` before every run (see kair_b200/optim.py)."""
+    keep = []
+    dev = p[0].device
+    a = _S["kair_adam_ema_args"]()
+    a.p = _plist(p, p[0], keep); a.g = _plist(g, p[0], keep)
+    a.m = _plist(m, p[0], keep); a.v = _plist(v, p[0], keep)
+    a.e = _plist(e, p[0], keep)
+    for lst in (g, m, v) + ((e,) if e is not None else ()):
+        if [t.numel() for t in lst] != [t.numel() for t in p]:
+            raise RuntimeError("kair_b200: adam_ema tensor lists must match the parameters element for element")
+    sizes = torch.tensor([t.numel() for t in p], dtype=torch.int64, device=dev)
+    ct, co = [], []
+    for i, t in enumerate(p):
+        for off in range(0, t.numel(), ADAM_CHUNK):
+            ct.append(i); co.append(off)
+    chunk_tensor = torch.tensor(ct, dtype=torch.int32, device=dev)
+    chunk_offset = torch.tensor(co, dtype=torch.int64, device=dev)
+    keep += [sizes, chunk_tensor, chunk_offset]
+    a.sizes, a.chunk_tensor, a.chunk_offset = sizes.data_ptr(), chunk_tensor.data_ptr(), chunk_offset.data_ptr()
+    a.n_chunks, a.chunk_elems = len(ct), ADAM_CHUNK
+    a.beta1, a.beta2, a.eps, a.weight_decay, a.ema_decay = beta1, beta2, eps, weight_decay, ema_decay
+    a.step_size, a.bc2_sqrt = 0.0, 1.0
+    return Launch("kair_adam_ema", a, keep)
+
+
 def build_copy(dst, src):
     """dst <- src on the current stream (device-to-device plumbing for a handful of values, e.g. a bias gradient
     picked out of a column-sum vector); no kernel of ours is involved."""

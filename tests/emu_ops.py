@@ -669,3 +669,38 @@ def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
         dx[:, :co * r * r] = _bf(g)
 
     return EmuLaunch("kair_pixel_shuffle_out_bwd", run)
+
+
+def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
+    def run():
+        d = x - y
+        if mode == 0:
+            l = torch.sqrt(d * d + eps)
+            g = d / l
+        else:
+            l = d.abs()
+            g = torch.sign(d)
+        loss[0] = l.double().mean().float()
+        if dx is not None:
+            dx.copy_(g / x.numel())
+
+    return EmuLaunch("kair_pixel_loss", run)
+
+
+def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_decay=0.0):
+    import types
+    args = types.SimpleNamespace(step_size=0.0, bc2_sqrt=1.0)
+
+    def run():
+        for i in range(len(p)):
+            gi = g[i] + weight_decay * p[i] if weight_decay else g[i]
+            m[i].lerp_(gi, 1.0 - beta1)
+            v[i].mul_(beta2).addcmul_(gi, gi, value=1.0 - beta2)
+            denom = (v[i].sqrt() / args.bc2_sqrt).add_(eps)
+            p[i].addcdiv_(m[i], denom, value=-args.step_size)
+            if e is not None:
+                e[i].mul_(ema_decay).add_(p[i], alpha=1.0 - ema_decay)
+
+    l = EmuLaunch("kair_adam_ema", run)
+    l.args = args
+    return l

@@ -1,0 +1,96 @@
+"""SURVEY 8(f1) on the GPU: the fused loss + gradient kernel and the multi-tensor Adam + EMA kernel (through the C ABI)
+against torch.optim.Adam / the oracle on the same inputs; fp32 elementwise arithmetic: 1e-6 relative."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(7,), (3, 5), (1,), (33, 17, 3), (8192,), (8193,), (180, 180, 3, 3), (540, 180), (225, 6)]
+
+
+@pytest.mark.parametrize("wd", [0.0, 1e-2])
+def test_fused_adam_ema_matches_torch(wd):
+    from kair_b200.optim import FusedAdamEMA
+    g = torch.Generator().manual_seed(1)
+    init = [torch.randn(s, generator=g) for s in SHAPES]
+    mine = [torch.nn.Parameter(t.clone().cuda()) for t in init]
+    ref = [torch.nn.Parameter(t.clone()) for t in init]
+    ema = [t.clone().cuda() for t in init]
+    ema_ref = [t.clone() for t in init]
+    opt = FusedAdamEMA(mine, lr=2e-4, betas=(0.9, 0.999), weight_decay=wd, ema_params=ema, ema_decay=0.999)
+    opt_ref = torch.optim.Adam(ref, lr=2e-4, betas=(0.9, 0.999), weight_decay=wd, foreach=False)
+    for step in range(6):
+        for a, b in zip(mine, ref):
+            b.grad = torch.randn(b.shape, generator=g) * 0.05
+            a.grad = b.grad.cuda()
+        opt.step()
+        opt_ref.step()
+        for e, p in zip(ema_ref, ref):
+            e.mul_(0.999).add_(p.data, alpha=1 - 0.999)
+    torch.cuda.synchronize()
+    for a, b in zip(mine, ref):
+        assert torch.allclose(a.data.cpu(), b.data, rtol=2e-6, atol=1e-7)
+    for a, b in zip(ema, ema_ref):
+        assert torch.allclose(a.cpu(), b, rtol=2e-6, atol=1e-7)
+    for a, b in zip(mine, ref):
+        assert torch.allclose(opt.state[a]["exp_avg_sq"].cpu(), opt_ref.state[b]["exp_avg_sq"], rtol=2e-6, atol=1e-12)
+        assert float(opt.state[a]["step"]) == 6.0
+    assert len(opt._launches) == 1   # same gradient storage every step -> the pointer tables are built once
+
+
+@pytest.mark.parametrize("shape", [(8, 1, 128, 128), (3, 3, 37, 45), (1, 1, 1, 1)])
+@pytest.mark.parametrize("kind", ["charbonnier", "l1"])
+def test_fused_pixel_loss(shape, kind):
+    from kair_b200.loss import CharbonnierLoss, L1Loss
+    from oracle import train_step_oracle as to
+    g = torch.Generator().manual_seed(7)
+    x = torch.rand(shape, generator=g)
+    y = torch.rand(shape, generator=g)
+    y.view(-1)[0] = x.view(-1)[0]          # an exact zero difference: sqrt(eps) / sign(0) = 0
+    xr = x.clone().requires_grad_(True)
+    lr = to.charbonnier(xr, y) if kind == "charbonnier" else torch.mean(torch.abs(xr - y))
+    (3.0 * lr).backward()
+    mod = CharbonnierLoss() if kind == "charbonnier" else L1Loss()
+    xc = x.cuda().requires_grad_(True)
+    for _ in range(2):                     # twice: the kernel re-arms its scratch words
+        xc.grad = None
+        l = mod(xc, y.cuda())
+        (3.0 * l).backward()
+    torch.cuda.synchronize()
+    assert abs(l.item() - lr.item()) < 1e-6 * max(1.0, abs(lr.item()))
+    assert torch.allclose(xc.grad.cpu(), xr.grad, rtol=1e-5, atol=1e-9)
+
+
+def test_swinir_training_loop_with_fused_tail():
+    """model_plain.optimize_parameters with the three drop-ins: SwinIR module, fused Charbonnier, FusedAdamEMA (E_decay 0.999):
+    same losses as the torch loss + torch.optim.Adam + update_E loop on the same module, step for step."""
+    import copy
+    from kair_b200.network_swinir import SwinIR
+    from kair_b200.loss import CharbonnierLoss
+    from kair_b200.optim import FusedAdamEMA
+    cfg = dict(upscale=1, in_chans=1, img_size=32, window_size=8, img_range=1.0, depths=[2, 2], embed_dim=180,
+               num_heads=[6, 6], mlp_ratio=2, upsampler="", resi_connection="1conv", drop_path_rate=0.0)
+    torch.manual_seed(0)
+    netG = SwinIR(**cfg).cuda().train()
+    netG2 = copy.deepcopy(netG)
+    netE, netE2 = copy.deepcopy(netG).eval(), copy.deepcopy(netG).eval()
+    opt = FusedAdamEMA(netG.parameters(), lr=2e-4, ema_params=list(netE.parameters()), ema_decay=0.999)
+    opt2 = torch.optim.Adam(netG2.parameters(), lr=2e-4)
+    lossfn = CharbonnierLoss()
+    g = torch.Generator().manual_seed(4)
+    for step in range(3):
+        x = torch.rand(2, 1, 32, 32, generator=g).cuda()
+        t = torch.rand(2, 1, 32, 32, generator=g).cuda()
+        opt.zero_grad()
+        l = lossfn(netG(x), t)
+        l.backward()
+        opt.step()
+        opt2.zero_grad()
+        l2 = torch.mean(torch.sqrt((netG2(x) - t) ** 2 + 1e-9))
+        l2.backward()
+        opt2.step()
+        for e, p in zip(netE2.parameters(), netG2.parameters()):
+            e.data.mul_(0.999).add_(p.data, alpha=1 - 0.999)
+        assert abs(l.item() - l2.item()) < 1e-4 * abs(l2.item()) + 1e-6
+    for (k, a), b in zip(netE.named_parameters(), netE2.parameters()):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), k
