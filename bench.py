@@ -4,8 +4,9 @@
     python bench.py --gpus N --steps K --warmup W                 # this repo's sm_100a path
     python bench.py --impl reference --gpus N --steps K --warmup W # the reference arithmetic on the host CPU cores
 
-One step = zero_grad -> forward -> Charbonnier loss -> backward -> Adam (models/model_plain.py:270-302 of the
-reference) on 8 patches of 1x128x128 per GPU.  `value` is patches/s over all ranks with inputs resident in HBM;
+One step = zero_grad -> forward -> Charbonnier loss -> backward -> Adam -> update_E (EMA 0.999), i.e.
+`optimize_parameters` of the reference (models/model_plain.py:270-318 with options/swinir/train_swinir_denoising_gray.json)
+on 8 patches of 1x128x128 per GPU.  `value` is patches/s over all ranks with inputs resident in HBM;
 `e2e` is the same step fed from pinned host memory with the loss read back every step.  The roofline object
 describes the kernel group that takes the largest share of the step, timed per launch with CUDA events on the
 launching stream in an instrumented replay of the same launch lists right after the timed region.
@@ -137,6 +138,7 @@ def oracle_train_steps(steps, warmup, batch, seed=0, budget_s=240.0):
     for p in params:
         p.requires_grad_(True)
     opt = torch.optim.Adam(params, lr=2e-4, betas=(0.9, 0.999), weight_decay=0)
+    ema = [p.detach().clone() for p in params]       # netE; E_decay = 0.999 (train_swinir_denoising_gray.json:64)
     low, high = spect_batch(batch, PATCH, 1234)
     times = []
     t_begin = time.perf_counter()
@@ -147,6 +149,9 @@ def oracle_train_steps(steps, warmup, batch, seed=0, budget_s=240.0):
         loss = so.charbonnier(out, high)
         loss.backward()
         opt.step()
+        with torch.no_grad():                        # update_E, models/model_base.py:247-252
+            for e, p in zip(ema, params):
+                e.mul_(0.999).add_(p.data, alpha=1 - 0.999)
         dt = time.perf_counter() - t0
         if it >= warmup:
             times.append(dt)
@@ -236,7 +241,20 @@ def run_b200(args):
     net = model
     if world > 1:
         net = _wrap_dp(model, local_rank, args.ddp)
-    opt = torch.optim.Adam(model.parameters(), lr=2e-4, betas=(0.9, 0.999), weight_decay=0, fused=True)
+    # optimize_parameters (models/model_plain.py:270-318) with E_decay = 0.999: loss, Adam, update_E.  Default: the fused
+    # tail (kair_pixel_loss + kair_adam_ema, one launch each); --torch-tail: torch ops (fused Adam + foreach EMA).
+    import copy
+    from kair_b200.loss import CharbonnierLoss
+    from kair_b200.optim import FusedAdamEMA, update_ema
+    ema_params = [p.detach().clone() for p in model.parameters()]
+    if args.torch_tail:
+        opt = torch.optim.Adam(model.parameters(), lr=2e-4, betas=(0.9, 0.999), weight_decay=0, fused=True)
+        lossfn = charbonnier
+    else:
+        opt = FusedAdamEMA(model.parameters(), lr=2e-4, betas=(0.9, 0.999), weight_decay=0, ema_params=ema_params,
+                           ema_decay=0.999)
+        lossfn = CharbonnierLoss(eps=1e-9)
+    params_list = list(model.parameters())
 
     low_h, high_h = spect_batch(BATCH_PER_GPU, PATCH, 1234 + rank)
     low_h, high_h = low_h.pin_memory(), high_h.pin_memory()
@@ -245,9 +263,11 @@ def run_b200(args):
     def step(lo, hi):
         opt.zero_grad(set_to_none=True)
         out = net(lo)
-        loss = charbonnier(out, hi)
+        loss = lossfn(out, hi)
         loss.backward()
         opt.step()
+        if args.torch_tail:
+            update_ema(ema_params, params_list, 0.999)
         return loss
 
     def barrier():
@@ -355,7 +375,7 @@ def run_b200(args):
         sec, done, threads = oracle_train_steps(3, 1, 1, budget_s=60.0)
         cpu = {"value": 1.0 / sec, "unit": "patches/s", "cores": threads, "kind": "port",
                "sample": "1 patch (1x128x128) per step, %d timed steps after 1 warm-up, fp32 oracle port of the "
-                         "reference modules incl. Adam" % done}
+                         "reference modules incl. Adam and update_E" % done}
 
     if rank == 0:
         line = {
@@ -363,13 +383,14 @@ def run_b200(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": patches, "parallelism": _dp_name(world, args.ddp),
-                       "drop_path_rate": 0.1, "optimizer": "Adam lr 2e-4", "loss": "Charbonnier eps 1e-9",
+                       "drop_path_rate": 0.1, "optimizer": "Adam lr 2e-4 + EMA 0.999 (update_E)", "loss": "Charbonnier eps 1e-9",
+                       "step_tail": "torch" if args.torch_tail else "fused (kair_pixel_loss, kair_adam_ema)",
                        "l2": "per-step working set (~13 GB of activations) far exceeds the 126 MB L2; no flush needed"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "patches/s",
                     "h2d_bytes_per_step": (low_h.numel() + high_h.numel()) * 4 * world,
                     "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": (len(launches) + n_pack) * args.steps,
+            "gpu_launches": (len(launches) + n_pack + (0 if args.torch_tail else 2)) * args.steps,
             "roofline": roof, "cpu_baseline": cpu,
         }
         print(json.dumps(line), flush=True)
@@ -688,6 +709,8 @@ def main():
     ap.add_argument("--image", type=int, default=0, help="cfg5: image side (default 2048)")
     ap.add_argument("--ddp", action="store_true", help="N>1 training: wrap in torch DistributedDataParallel (the "
                     "reference's wrapper) instead of kair_b200.parallel.FlatDataParallel")
+    ap.add_argument("--torch-tail", action="store_true", help="cfg2: torch loss / fused Adam / foreach EMA instead of "
+                    "the fused kair_pixel_loss + kair_adam_ema tail")
     ap.add_argument("--ncu-slice", action="store_true", help="profiling aid: one launch per kernel group in a "
                     "cudaProfilerStart/Stop range")
     args = ap.parse_args()

@@ -479,7 +479,9 @@ typedef struct kair_adam_ema_args {
   const int32_t* chunk_tensor;
   const int64_t* chunk_offset;
   int32_t n_chunks, chunk_elems;  /* chunk_elems must be 8192 */
-  float step_size, beta1, beta2, eps, bc2_sqrt, weight_decay, ema_decay;
+  /* doubles: torch forms 1-beta1, 1-beta2 (and update_E 1-decay) in double before rounding to the fp32 compute type */
+  double beta1, beta2, ema_decay;
+  float step_size, eps, bc2_sqrt, weight_decay;
 } kair_adam_ema_args;
 int kair_adam_ema(const kair_adam_ema_args* args, void* stream);
 

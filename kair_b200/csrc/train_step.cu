@@ -64,21 +64,22 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(const kair_adam_ema_args 
   float* v = reinterpret_cast<float*>(a.v[t]);
   float* e = a.e ? reinterpret_cast<float*>(a.e[t]) : nullptr;
   const long long end = off + AE_CHUNK < n ? off + AE_CHUNK : n;
-  const float omb1 = 1.0f - a.beta1, omb2 = 1.0f - a.beta2, omd = 1.0f - a.ema_decay;
+  const float omb1 = (float)(1.0 - a.beta1), omb2 = (float)(1.0 - a.beta2), omd = (float)(1.0 - a.ema_decay);
+  const float beta2 = (float)a.beta2, decay = (float)a.ema_decay;
   for (long long i = off + threadIdx.x; i < end; i += blockDim.x) {
     float pi = p[i];
     float gi = g[i];
     if (a.weight_decay != 0.f) gi = fmaf(a.weight_decay, pi, gi);
     // exp_avg.lerp_(grad, 1 - beta1); exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
     const float mi = fmaf(omb1, gi - m[i], m[i]);
-    const float vi = fmaf(omb2 * gi, gi, a.beta2 * v[i]);
+    const float vi = fmaf(omb2 * gi, gi, beta2 * v[i]);
     // denom = exp_avg_sq.sqrt() / bias_correction2_sqrt + eps; param.addcdiv_(exp_avg, denom, value=-step_size)
     const float denom = sqrtf(vi) / a.bc2_sqrt + a.eps;
     pi = pi - a.step_size * (mi / denom);
     p[i] = pi;
     m[i] = mi;
     v[i] = vi;
-    if (e) e[i] = fmaf(omd, pi, e[i] * a.ema_decay);
+    if (e) e[i] = fmaf(omd, pi, e[i] * decay);
   }
 }
 
@@ -98,7 +99,7 @@ int pixel_loss_launch(const kair_pixel_loss_args& a, cudaStream_t st) {
 int adam_ema_launch(const kair_adam_ema_args& a, cudaStream_t st) {
   KB_CHECK(a.p && a.g && a.m && a.v && a.sizes && a.chunk_tensor && a.chunk_offset, "kair_adam_ema: null pointer");
   KB_CHECK(a.n_chunks > 0 && a.chunk_elems == AE_CHUNK, "kair_adam_ema: chunk table must use %d-element chunks", AE_CHUNK);
-  KB_CHECK(a.bc2_sqrt > 0.f && a.beta1 >= 0.f && a.beta1 < 1.f && a.beta2 >= 0.f && a.beta2 < 1.f,
+  KB_CHECK(a.bc2_sqrt > 0.f && a.beta1 >= 0.0 && a.beta1 < 1.0 && a.beta2 >= 0.0 && a.beta2 < 1.0,
            "kair_adam_ema: bad hyper-parameters");
   adam_ema_kernel<<<(unsigned)a.n_chunks, 256, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());

@@ -545,6 +545,7 @@ def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
 
 
 ADAM_CHUNK = 8192
+_ADAM_G_SLOT = 0
 
 
 def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_decay=0.0):
@@ -553,7 +554,8 @@ def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_de
     keep = []
     dev = p[0].device
     a = _S["kair_adam_ema_args"]()
-    a.p = _plist(p, p[0], keep); a.g = _plist(g, p[0], keep)
+    a.g = _plist(g, p[0], keep)            # first: adam_ema_set_grads() finds the table at keep[0], tensors behind it
+    a.p = _plist(p, p[0], keep)
     a.m = _plist(m, p[0], keep); a.v = _plist(v, p[0], keep)
     a.e = _plist(e, p[0], keep)
     for lst in (g, m, v) + ((e,) if e is not None else ()):
@@ -572,6 +574,21 @@ def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_de
     a.beta1, a.beta2, a.eps, a.weight_decay, a.ema_decay = beta1, beta2, eps, weight_decay, ema_decay
     a.step_size, a.bc2_sqrt = 0.0, 1.0
     return Launch("kair_adam_ema", a, keep)
+
+
+def adam_ema_set_grads(launch, g):
+    """Point a recorded kair_adam_ema launch at new gradient tensors (autograd hands out fresh ones every step unless
+    the caller keeps them): the pointer table is refreshed by a stream-ordered copy from pinned memory, no host sync."""
+    for t in g:
+        _req(t, torch.float32, "gradient")
+        if not t.is_contiguous():
+            raise RuntimeError("kair_b200: gradients must be contiguous")
+    keep = list(launch.keep)
+    arr = keep[_ADAM_G_SLOT]
+    host = torch.tensor([t.data_ptr() for t in g], dtype=torch.int64).pin_memory()
+    arr.copy_(host, non_blocking=True)
+    old = set(id(t) for t in keep[_ADAM_G_SLOT + 1:_ADAM_G_SLOT + 1 + len(g)])
+    launch.keep = tuple([arr] + list(g) + [x for x in keep[_ADAM_G_SLOT + 1 + len(g):] if id(x) not in old])
 
 
 def build_copy(dst, src):

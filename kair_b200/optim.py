@@ -9,6 +9,7 @@ parameters of netE, in the order of netG's) and `ema_decay` > 0 the call that `o
 import math
 
 import torch
+from torch.autograd.graph import increment_version
 
 from . import ops as _real_ops
 
@@ -65,19 +66,31 @@ class FusedAdamEMA(torch.optim.Optimizer):
                 ms = [self.state[p]["exp_avg"] for p in plist]
                 vs = [self.state[p]["exp_avg_sq"] for p in plist]
                 es = [self._ema[id(p)].data for p in plist] if self._ema is not None else None
-                key = (gi, tuple(x.data_ptr() for x in plist), tuple(x.data_ptr() for x in gs),
-                       tuple(x.data_ptr() for x in ms), tuple(x.data_ptr() for x in es) if es else None,
-                       b1, b2, group["eps"], group["weight_decay"])
-                l = self._launches.get(key)
-                if l is None:
+                key = (gi, tuple(x.data_ptr() for x in plist), tuple(x.data_ptr() for x in ms),
+                       tuple(x.data_ptr() for x in es) if es else None, b1, b2, group["eps"], group["weight_decay"])
+                gkey = tuple(x.data_ptr() for x in gs)
+                ent = self._launches.get(key)
+                if ent is None:
                     if len(self._launches) > 8:
                         self._launches.clear()
-                    l = self._launches[key] = o.build_adam_ema(
+                    ent = self._launches[key] = [o.build_adam_ema(
                         [p.data for p in plist], gs, ms, vs, es, beta1=b1, beta2=b2, eps=group["eps"],
-                        weight_decay=group["weight_decay"], ema_decay=self.ema_decay if es else 0.0)
+                        weight_decay=group["weight_decay"], ema_decay=self.ema_decay if es else 0.0), gkey]
+                elif ent[1] != gkey:
+                    # autograd handed out new gradient tensors: refresh that one pointer table (stream-ordered)
+                    o.adam_ema_set_grads(ent[0], gs)
+                    ent[1] = gkey
+                l = ent[0]
                 l.args.step_size = group["lr"] / (1.0 - b1 ** t)
                 l.args.bc2_sqrt = math.sqrt(1.0 - b2 ** t)
                 l.run(o.stream_handle())
+                # the kernel wrote through raw pointers: tell autograd (and the engines, which re-pack their bf16
+                # operands when a parameter's version changes) that these tensors were modified in place
+                increment_version(plist)
+                increment_version(ms)
+                increment_version(vs)
+                if es:
+                    increment_version([self._ema[id(p)] for p in plist])
                 for p in plist:
                     self.state[p]["step"] += 1.0
         return loss

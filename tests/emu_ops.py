@@ -703,4 +703,9 @@ def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_de
 
     l = EmuLaunch("kair_adam_ema", run)
     l.args = args
+    l.g = g
     return l
+
+
+def adam_ema_set_grads(launch, g):
+    launch.g[:] = list(g)

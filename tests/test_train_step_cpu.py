@@ -80,6 +80,7 @@ def test_fused_adam_ema_host_logic_and_state_dict():
         sch.step(); sch_ref.step()
     for a, b in zip(ps, ref):
         assert torch.allclose(a.data, b.data, rtol=1e-6, atol=1e-7)
+    assert all(p._version >= 3 for p in ps)   # the engines watch parameter versions to re-pack their operands
     for i, (a, b) in enumerate(zip(ema_mine, ema_ref)):
         if i != 3:   # update_E also averages parameters that got no gradient; the fused step leaves them alone
             assert torch.allclose(a, b, rtol=1e-6, atol=1e-7)

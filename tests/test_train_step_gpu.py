@@ -22,7 +22,10 @@ def test_fused_adam_ema_matches_torch(wd):
     for step in range(6):
         for a, b in zip(mine, ref):
             b.grad = torch.randn(b.shape, generator=g) * 0.05
-            a.grad = b.grad.cuda()
+            if a.grad is None:
+                a.grad = b.grad.cuda()
+            else:
+                a.grad.copy_(b.grad)       # gradient storage that persists across steps (as with zero_grad(False))
         opt.step()
         opt_ref.step()
         for e, p in zip(ema_ref, ref):
@@ -94,3 +97,5 @@ def test_swinir_training_loop_with_fused_tail():
         assert abs(l.item() - l2.item()) < 1e-4 * abs(l2.item()) + 1e-6
     for (k, a), b in zip(netE.named_parameters(), netE2.parameters()):
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), k
+    # new gradient tensors every step only refresh the gradient pointer table of the one recorded launch
+    assert len(opt._launches) == 1, len(opt._launches)
