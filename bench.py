@@ -557,7 +557,15 @@ def run_b200_workload(args):
         net = model
         if world > 1:
             net = _wrap_dp(model, local_rank, args.ddp)
-        opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)
+        # options/train_drunet.json: L1 loss, Adam 1e-4, no EMA (E_decay unset); fused tail unless --torch-tail
+        if args.torch_tail:
+            opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)
+            l1 = lambda a, b: torch.mean(torch.abs(a - b))
+        else:
+            from kair_b200.loss import L1Loss
+            from kair_b200.optim import FusedAdamEMA
+            opt = FusedAdamEMA(model.parameters(), lr=1e-4)
+            l1 = L1Loss()
         high = torch.rand(batch, 3, 128, 128, generator=g)
         sigma = torch.rand(batch, 1, 1, 1, generator=g) * 50.0 / 255.0
         low = torch.cat([high + torch.randn(high.shape, generator=g) * sigma, sigma.expand(batch, 1, 128, 128)], 1)
@@ -566,7 +574,7 @@ def run_b200_workload(args):
         plan_of = lambda: model.engine(dev).plan(batch, 128, 128, True)
         def step(lo, hi):
             opt.zero_grad(set_to_none=True)
-            loss = torch.mean(torch.abs(net(lo) - hi))
+            loss = l1(net(lo), hi)
             loss.backward()
             opt.step()
             return loss

@@ -33,7 +33,44 @@ class FusedAdamEMA(torch.optim.Optimizer):
             if len(ema) != len(flat) or any(e.shape != p.shape for e, p in zip(ema, flat)):
                 raise ValueError("ema_params must match the optimised parameters one to one (netE vs netG order)")
             self._ema = {id(p): e for p, e in zip(flat, ema)}
-        self._launches = {}
+        self._launches = {}   # group index -> list of recorded sub-launches (see _build)
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._launches.clear()   # the moment tensors were replaced
+
+    def _build(self, gi, group, ps):
+        """Slow path (first step, or the set / storage of the tensors changed): create the optimizer state, split the
+        parameters by step count (they all agree in KAIR's loop: every parameter gets a gradient every step) and record
+        one launch per distinct count."""
+        o = self._ops
+        for p in ps:
+            if p.grad.is_sparse or p.dtype != torch.float32:
+                raise RuntimeError("kair_b200 FusedAdamEMA: dense fp32 parameters only")
+            st = self.state[p]
+            if len(st) == 0:
+                st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        b1, b2 = group["betas"]
+        by_step = {}
+        for p in ps:
+            by_step.setdefault(float(self.state[p]["step"]), []).append(p)
+        subs = []
+        for step0, plist in by_step.items():
+            gs = [p.grad if p.grad.is_contiguous() else p.grad.contiguous() for p in plist]
+            ms = [self.state[p]["exp_avg"] for p in plist]
+            vs = [self.state[p]["exp_avg_sq"] for p in plist]
+            es = [self._ema[id(p)] for p in plist] if self._ema is not None else None
+            launch = o.build_adam_ema([p.data for p in plist], gs, ms, vs, [e.data for e in es] if es else None,
+                                      beta1=b1, beta2=b2, eps=group["eps"], weight_decay=group["weight_decay"],
+                                      ema_decay=self.ema_decay if es else 0.0)
+            subs.append(dict(launch=launch, params=plist, t=step0, gkey=tuple(g.data_ptr() for g in gs),
+                             steps=[self.state[p]["step"] for p in plist], bump=plist + ms + vs + (es or [])))
+        ent = dict(ids=tuple(map(id, ps)), pptr=[p.data_ptr() for p in ps], subs=subs,
+                   hyper=(b1, b2, group["eps"], group["weight_decay"]))
+        self._launches[gi] = ent
+        return ent
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -46,53 +83,28 @@ class FusedAdamEMA(torch.optim.Optimizer):
             ps = [p for p in group["params"] if p.grad is not None]
             if not ps:
                 continue
-            for p in ps:
-                if p.grad.is_sparse or p.dtype != torch.float32:
-                    raise RuntimeError("kair_b200 FusedAdamEMA: dense fp32 parameters only")
-                st = self.state[p]
-                if len(st) == 0:
-                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
-                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-            # all tensors of a group share the step count in KAIR's loop (every parameter gets a gradient every step);
-            # groups whose members disagree are split by step value
-            by_step = {}
-            for p in ps:
-                by_step.setdefault(float(self.state[p]["step"]), []).append(p)
-            for step0, plist in by_step.items():
-                t = step0 + 1.0
-                b1, b2 = group["betas"]
-                gs = [p.grad if p.grad.is_contiguous() else p.grad.contiguous() for p in plist]
-                ms = [self.state[p]["exp_avg"] for p in plist]
-                vs = [self.state[p]["exp_avg_sq"] for p in plist]
-                es = [self._ema[id(p)].data for p in plist] if self._ema is not None else None
-                key = (gi, tuple(x.data_ptr() for x in plist), tuple(x.data_ptr() for x in ms),
-                       tuple(x.data_ptr() for x in es) if es else None, b1, b2, group["eps"], group["weight_decay"])
-                gkey = tuple(x.data_ptr() for x in gs)
-                ent = self._launches.get(key)
-                if ent is None:
-                    if len(self._launches) > 8:
-                        self._launches.clear()
-                    ent = self._launches[key] = [o.build_adam_ema(
-                        [p.data for p in plist], gs, ms, vs, es, beta1=b1, beta2=b2, eps=group["eps"],
-                        weight_decay=group["weight_decay"], ema_decay=self.ema_decay if es else 0.0), gkey]
-                elif ent[1] != gkey:
+            b1, b2 = group["betas"]
+            ent = self._launches.get(gi)
+            if (ent is None or ent["ids"] != tuple(map(id, ps)) or len(ent["subs"]) != 1
+                    or ent["hyper"] != (b1, b2, group["eps"], group["weight_decay"])
+                    or any(p.data_ptr() != q for p, q in zip(ps, ent["pptr"]))):
+                ent = self._build(gi, group, ps)
+            for sub in ent["subs"]:
+                gs = [p.grad if p.grad.is_contiguous() else p.grad.contiguous() for p in sub["params"]]
+                gkey = tuple(g.data_ptr() for g in gs)
+                if gkey != sub["gkey"]:
                     # autograd handed out new gradient tensors: refresh that one pointer table (stream-ordered)
-                    o.adam_ema_set_grads(ent[0], gs)
-                    ent[1] = gkey
-                l = ent[0]
-                l.args.step_size = group["lr"] / (1.0 - b1 ** t)
-                l.args.bc2_sqrt = math.sqrt(1.0 - b2 ** t)
+                    o.adam_ema_set_grads(sub["launch"], gs)
+                    sub["gkey"] = gkey
+                sub["t"] += 1.0
+                l = sub["launch"]
+                l.args.step_size = group["lr"] / (1.0 - b1 ** sub["t"])
+                l.args.bc2_sqrt = math.sqrt(1.0 - b2 ** sub["t"])
                 l.run(o.stream_handle())
                 # the kernel wrote through raw pointers: tell autograd (and the engines, which re-pack their bf16
                 # operands when a parameter's version changes) that these tensors were modified in place
-                increment_version(plist)
-                increment_version(ms)
-                increment_version(vs)
-                if es:
-                    increment_version([self._ema[id(p)] for p in plist])
-                for p in plist:
-                    self.state[p]["step"] += 1.0
+                increment_version(sub["bump"])
+                torch._foreach_add_(sub["steps"], 1.0)
         return loss
 
 
