@@ -21,6 +21,7 @@ from collections import OrderedDict
 import torch
 import torch.nn as nn
 
+from . import _dirty
 from . import ops as _real_ops
 
 
@@ -90,7 +91,8 @@ class _EngineBase:
         return self._names[id(p)]
 
     def _versions(self, extra=()):
-        return tuple(p._version for p in self.P.values()) + tuple(b._version for b in extra)
+        # + the global optimizer-step epoch: fused optimizers do not touch the version counters (kair_b200/_dirty.py)
+        return (_dirty.optimizer_epoch(),) + tuple(p._version for p in self.P.values()) + tuple(b._version for b in extra)
 
     def _get_plan(self, key, make):
         p = self._plans.get(key)

@@ -65,7 +65,7 @@ class FusedAdamEMA(torch.optim.Optimizer):
             launch = o.build_adam_ema([p.data for p in plist], gs, ms, vs, [e.data for e in es] if es else None,
                                       beta1=b1, beta2=b2, eps=group["eps"], weight_decay=group["weight_decay"],
                                       ema_decay=self.ema_decay if es else 0.0)
-            subs.append(dict(launch=launch, params=plist, t=step0, gkey=tuple(g.data_ptr() for g in gs),
+            subs.append(dict(launch=launch, params=plist, t=step0, gkey=tuple(g.data_ptr() for g in gs), gtables={},
                              steps=[self.state[p]["step"] for p in plist], bump=plist + ms + vs + (es or [])))
         ent = dict(ids=tuple(map(id, ps)), pptr=[p.data_ptr() for p in ps], subs=subs,
                    hyper=(b1, b2, group["eps"], group["weight_decay"]))
@@ -94,8 +94,9 @@ class FusedAdamEMA(torch.optim.Optimizer):
                 gkey = tuple(g.data_ptr() for g in gs)
                 if gkey != sub["gkey"]:
                     # autograd handed out new gradient tensors: refresh that one pointer table (stream-ordered)
-                    o.adam_ema_set_grads(sub["launch"], gs)
+                    o.adam_ema_set_grads(sub["launch"], gs, sub["gtables"])
                     sub["gkey"] = gkey
+                    sub["grads"] = gs   # the table points into these
                 sub["t"] += 1.0
                 l = sub["launch"]
                 l.args.step_size = group["lr"] / (1.0 - b1 ** sub["t"])

@@ -17,6 +17,7 @@ import math
 
 import torch
 
+from . import _dirty
 from . import ops as _real_ops
 
 def _tile(n, fused=False):
@@ -234,7 +235,8 @@ class SwinIREngine:
         return W
 
     def _param_versions(self):
-        return tuple(p._version for p in self.P.values())
+        # + the global optimizer-step epoch: fused optimizers do not touch the version counters (kair_b200/_dirty.py)
+        return (_dirty.optimizer_epoch(),) + tuple(p._version for p in self.P.values())
 
     def refresh_weights(self, W, stream):
         """Re-pack when any master parameter changed (optimizer step, load_state_dict)."""

@@ -707,5 +707,5 @@ def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_de
     return l
 
 
-def adam_ema_set_grads(launch, g):
+def adam_ema_set_grads(launch, g, tables):
     launch.g[:] = list(g)

@@ -118,3 +118,34 @@ def test_loss_modules_host_logic(cls, ref):
         assert abs(mod(x, y).item() * 2.0 - lr.item()) < 1e-6
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         cls()(x, y)
+
+
+def test_engines_repack_after_an_optimizer_step_that_hides_from_version_counters():
+    """torch.optim.Adam(fused=True) (and apex) update parameters without bumping Tensor._version: the engines must still
+    see the new weights on their next forward (kair_b200/_dirty.py: global optimizer post-step hook)."""
+    from kair_b200.network_dncnn import DnCNN
+    from kair_b200 import _dirty
+    torch.manual_seed(0)
+    model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=4, act_mode="R")
+    model._ops = emu_ops
+    x = torch.rand(1, 1, 16, 16)
+    with torch.no_grad():
+        y0 = model(x)
+
+    class Sneaky(torch.optim.Optimizer):      # writes through .data views: no version bump on the parameters
+        def __init__(self, params):
+            super().__init__(params, {})
+
+        def step(self, closure=None):
+            for g in self.param_groups:
+                for p in g["params"]:
+                    torch.Tensor.add_(p.data, 0.05)
+
+    opt = Sneaky(model.parameters())
+    v = [p._version for p in model.parameters()]
+    e0 = _dirty.optimizer_epoch()
+    opt.step()
+    assert [p._version for p in model.parameters()] == v and _dirty.optimizer_epoch() == e0 + 1
+    with torch.no_grad():
+        y1 = model(x)
+    assert (y1 - y0).abs().max().item() > 1e-3

@@ -99,3 +99,26 @@ def test_swinir_training_loop_with_fused_tail():
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), k
     # new gradient tensors every step only refresh the gradient pointer table of the one recorded launch
     assert len(opt._launches) == 1, len(opt._launches)
+
+
+def test_torch_fused_adam_updates_reach_the_engine():
+    """Regression: torch.optim.Adam(fused=True) does not bump Tensor._version; the packed bf16 operands must still follow
+    the master weights (the loss of a fixed batch goes down and the output changes after every step)."""
+    from kair_b200.network_unet import UNetRes
+    torch.manual_seed(0)
+    model = UNetRes(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=1, act_mode="R", bias=False).cuda().train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+    g = torch.Generator().manual_seed(2)
+    x = torch.rand(2, 4, 32, 32, generator=g).cuda()
+    t = torch.rand(2, 3, 32, 32, generator=g).cuda()
+    losses, outs = [], []
+    for _ in range(4):
+        opt.zero_grad()
+        out = model(x)
+        loss = torch.mean(torch.abs(out - t))
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+        outs.append(out.detach().clone())
+    assert losses[-1] < losses[0], losses
+    assert all((outs[i + 1] - outs[i]).abs().max().item() > 0 for i in range(3))
