@@ -19,6 +19,15 @@ def install():
     un-vendored `timm` --, registering ours under its name in `sys.modules`) is all it takes.  Call it once, with the
     KAIR checkout on `sys.path`, before the model is built.  Returns {module name: "patched" | "registered"}."""
     done = {}
+    # the fused Charbonnier loss (SURVEY 8(f1)): model_plain.py imports the class by name from models.loss, so it must
+    # be swapped before model_plain is imported -- hence "call install() first"
+    try:
+        ref_loss = importlib.import_module("models.loss")
+        from .loss import CharbonnierLoss
+        ref_loss.CharbonnierLoss = CharbonnierLoss
+        done["models.loss"] = "patched"
+    except Exception:  # noqa: BLE001 - models.loss needs torchvision / other optional packages in some forks
+        done["models.loss"] = "skipped"
     for ref_name, cls, mine_name in _TARGETS:
         mine = importlib.import_module(mine_name)
         try:
