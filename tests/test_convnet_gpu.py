@@ -295,3 +295,31 @@ def test_cpu_tensor_is_rejected():
         DnCNN()(torch.rand(1, 1, 16, 16))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         UNetRes()(torch.rand(1, 3, 16, 16))
+
+
+@pytest.mark.parametrize("net", ["dncnn", "swinir"])
+def test_cuda_graph_replay_matches_eager(net):
+    """kair_b200.graphs.GraphedInference: one captured forward replayed on new inputs and after a weight change."""
+    from kair_b200.graphs import GraphedInference
+    torch.manual_seed(0)
+    if net == "dncnn":
+        from kair_b200.network_dncnn import DnCNN
+        model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=17, act_mode="R").cuda().eval()
+        shape = (1, 1, 64, 64)
+    else:
+        from kair_b200.network_swinir import SwinIR
+        model = SwinIR(upscale=2, in_chans=3, img_size=32, window_size=8, img_range=1.0, depths=[2, 2], embed_dim=60,
+                       num_heads=[6, 6], mlp_ratio=2, upsampler="pixelshuffledirect").cuda().eval()
+        shape = (2, 3, 32, 32)
+    g = torch.Generator().manual_seed(1)
+    x0, x1 = torch.rand(shape, generator=g).cuda(), torch.rand(shape, generator=g).cuda()
+    graphed = GraphedInference(model, x0)
+    with torch.no_grad():
+        assert torch.equal(graphed(x1).clone(), model(x1))
+        assert torch.equal(graphed(x0).clone(), model(x0))
+        for p in model.parameters():
+            p.mul_(1.01)                       # weights change: the packed operands must follow before the replay
+        y_new = model(x1)
+        assert torch.equal(graphed(x1).clone(), y_new)
+    with pytest.raises(RuntimeError, match="captured for shape"):
+        graphed(torch.rand(1, shape[1], 16, 16).cuda())
