@@ -535,9 +535,15 @@ def run_b200_workload(args):
         host = [(clean + torch.randn(clean.shape, generator=g) * (25.0 / 255.0)).pin_memory()]
         units = batch * 256 * 256 / 1e6
         plan_of = lambda: model.engine(dev).plan(batch, 256, 256, False, False)
-        def step(x):
-            with torch.no_grad():
-                return model(x)
+        if args.eager:
+            def step(x):
+                with torch.no_grad():
+                    return model(x)
+        else:
+            # launch-bound at batch 1 (17 kernels of ~16 us): replay the forward as one CUDA graph (kair_b200/graphs.py)
+            from kair_b200.graphs import GraphedInference
+            graphed = GraphedInference(model, host[0].to(dev))
+            step = lambda x: graphed(x)
         fwd_gflop = 72.63 * batch
         real_dims = {}
     elif name == "cfg3":
@@ -717,6 +723,8 @@ def main():
     ap.add_argument("--image", type=int, default=0, help="cfg5: image side (default 2048)")
     ap.add_argument("--ddp", action="store_true", help="N>1 training: wrap in torch DistributedDataParallel (the "
                     "reference's wrapper) instead of kair_b200.parallel.FlatDataParallel")
+    ap.add_argument("--eager", action="store_true", help="cfg1: launch the forward kernel by kernel instead of "
+                    "replaying the captured CUDA graph")
     ap.add_argument("--torch-tail", action="store_true", help="cfg2: torch loss / fused Adam / foreach EMA instead of "
                     "the fused kair_pixel_loss + kair_adam_ema tail")
     ap.add_argument("--ncu-slice", action="store_true", help="profiling aid: one launch per kernel group in a "
