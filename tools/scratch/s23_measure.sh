@@ -1,13 +1,13 @@
 set -x
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/s23_pytest_final.log
-python bench.py > gpurun_out/s23_bench.log 2>&1
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/s23_bench_ref.log 2>&1
-python bench.py --no-cpu-baseline --workload cfg1 > gpurun_out/s23_bench_cfg1.log 2>&1
-python bench.py --no-cpu-baseline --workload cfg1 --batch 64 > gpurun_out/s23_bench_cfg1_b64.log 2>&1
-python bench.py --no-cpu-baseline --workload cfg3 > gpurun_out/s23_bench_cfg3.log 2>&1
-python bench.py --no-cpu-baseline --workload cfg4 > gpurun_out/s23_bench_cfg4.log 2>&1
-python bench.py --no-cpu-baseline --workload cfg5 > gpurun_out/s23_bench_cfg5.log 2>&1
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/s23_smoke.log 2>&1
-python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/s23_launch_plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 1800 --csv --log-file gpurun_out/r1_s23_bench_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/s23_launch_ncu.log 2>&1
-for f in gpurun_out/s23_*.log; do echo "== $f"; tail -1 $f | cut -c1-260; done
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/s23f_pytest_final.log
+python bench.py > gpurun_out/s23f_bench.log 2>&1
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/s23f_bench_ref.log 2>&1
+python bench.py --no-cpu-baseline --workload cfg1 > gpurun_out/s23f_bench_cfg1.log 2>&1
+python bench.py --no-cpu-baseline --workload cfg1 --batch 64 > gpurun_out/s23f_bench_cfg1_b64.log 2>&1
+python bench.py --no-cpu-baseline --workload cfg3 > gpurun_out/s23f_bench_cfg3.log 2>&1
+python bench.py --no-cpu-baseline --workload cfg4 > gpurun_out/s23f_bench_cfg4.log 2>&1
+python bench.py --no-cpu-baseline --workload cfg5 > gpurun_out/s23f_bench_cfg5.log 2>&1
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/s23f_smoke.log 2>&1
+python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/s23f_launch_plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 1800 --csv --log-file gpurun_out/r1_s23f_bench_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/s23f_launch_ncu.log 2>&1
+for f in gpurun_out/s23f_*.log; do echo "== $f"; tail -1 $f | cut -c1-260; done
