@@ -7,6 +7,7 @@ __all__ = ["install"]
 
 _TARGETS = (("models.network_swinir", "SwinIR", "kair_b200.network_swinir"),
             ("models.network_dncnn", "DnCNN", "kair_b200.network_dncnn"),
+            ("models.network_dncnn", "FDnCNN", "kair_b200.network_dncnn"),
             ("models.network_unet", "UNetRes", "kair_b200.network_unet"))
 
 

@@ -200,9 +200,13 @@ def parse_dncnn(seq):
 
 
 class DnCNNEngine(_EngineBase):
-    def __init__(self, stages, P, device, ops=None):
+    def __init__(self, stages, P, device, ops=None, residual=True):
+        """residual: DnCNN returns x - model(x) (network_dncnn.py:69-71); FDnCNN returns model(x) (:146-148)."""
         super().__init__(P, device, ops)
         self.stages = stages
+        self.residual = bool(residual)
+        if self.residual and stages[0].conv.in_channels != stages[-1].conv.out_channels:
+            _unsupported("residual DnCNN output needs in_nc == out_nc")
         self.nc = stages[0].conv.out_channels
         self.Lb = len(stages) - 2
         self._w = {}
@@ -305,9 +309,13 @@ class _DnCNNPlan(_PlanBase):
             else:
                 fwd.append(o.build_gemm_tn(A(i), Wt["Wp"][i], N=nc, K=nc, bn=bn, conv=geo, bias=Wt["bp"][i], act=act,
                                            act_slope=slope, outB=A(i + 1)))
-        # x - n  ==  -(conv(feat) + b - x)
-        fwd.append(o.build_conv_out_fwd(A(Lb), tail.conv.weight, tail.conv.bias, self.out, zc_out, C=nc, pitch=nc,
-                                        out_scale=-1.0, skip=self.img, skip_mean=zc_out, skip_scale=-1.0))
+        if eng.residual:
+            # x - n  ==  -(conv(feat) + b - x)
+            fwd.append(o.build_conv_out_fwd(A(Lb), tail.conv.weight, tail.conv.bias, self.out, zc_out, C=nc, pitch=nc,
+                                            out_scale=-1.0, skip=self.img, skip_mean=zc_out, skip_scale=-1.0))
+        else:
+            fwd.append(o.build_conv_out_fwd(A(Lb), tail.conv.weight, tail.conv.bias, self.out, zc_out, C=nc, pitch=nc,
+                                            out_scale=1.0))
         self.fwd, self.bwd = fwd, None
         self.zero_before_bwd = []
         if not train:
@@ -331,7 +339,8 @@ class _DnCNNPlan(_PlanBase):
         dsh, clT, dWcl, csum = bf(T, 64), bf(nc, 64), f32(nc, 64), f32(64)
         xcol, dWcf = bf(T, 64), f32(1, nc, 64)
         self.zero_before_bwd += [dWcl, csum, dWcf]
-        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1, scale=-1.0))   # out = x - n
+        bwd.append(o.build_im2col3x3(self.dout, dsh, cpad=7, direction=-1,
+                                     scale=-1.0 if eng.residual else 1.0))   # out = x - n  /  out = n
         bwd.append(o.build_conv_out_pack(mode=0, co=cout, C=nc, cpad=7, W=tail.conv.weight, Wt=clT))
         bwd.append(o.build_gemm_nt(A(Lb), dsh, dWcl, n1=nc, n2=64, bn=64))
         bwd.append(o.build_conv_out_pack(mode=1, co=cout, C=nc, cpad=7, D=dWcl, dW=G(tail.conv.weight)))

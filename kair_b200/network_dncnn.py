@@ -1,4 +1,5 @@
-"""Drop-in `DnCNN` for models/network_dncnn.py:40-71 of the reference, computed by the sm_100a kernels.
+"""Drop-in `DnCNN` (models/network_dncnn.py:40-71 of the reference) and `FDnCNN` (:126-148), computed by the sm_100a
+kernels.
 
 Constructor, forward(x) contract (x - model(x)) and state_dict layout are the reference's: `self.model` is the
 flattened nn.Sequential of stock Conv2d / BatchNorm2d / ReLU children built by `basicblock.conv`, so
@@ -39,10 +40,13 @@ class DnCNN(nn.Module):
         self._engine_key = None
         self._ops = None   # test hook: tests/emu_ops.py replays the launch lists on CPU (host-logic / DDP tests)
 
+    _residual = True   # forward(x) = x - model(x)
+
     def engine(self, device):
         key = _tree_key(self, device)
         if self._engine is None or self._engine_key != key:
-            self._engine = DnCNNEngine(parse_dncnn(self.model), dict(self.named_parameters()), device, ops=self._ops)
+            self._engine = DnCNNEngine(parse_dncnn(self.model), dict(self.named_parameters()), device, ops=self._ops,
+                                       residual=self._residual)
             self._engine_key = key
         self._engine.grad_hook = (lambda flat: _parallel.allreduce_flat(self, flat))
         return self._engine
@@ -59,3 +63,12 @@ class DnCNN(nn.Module):
         if train:
             return ConvNetFunction.apply(x, plan, *params)
         return plan.run_forward(x)
+
+
+class FDnCNN(DnCNN):
+    """models/network_dncnn.py:126-148: DnCNN with a noise-level map as extra input channel, no BatchNorm by default
+    and no residual learning -- forward(x) = model(x).  Same engine, the tail writes n instead of x - n."""
+    _residual = False
+
+    def __init__(self, in_nc=2, out_nc=1, nc=64, nb=20, act_mode="R"):
+        super().__init__(in_nc=in_nc, out_nc=out_nc, nc=nc, nb=nb, act_mode=act_mode)

@@ -47,8 +47,9 @@ def _act(x, act_mode, slope=0.2):
     return F.relu(x) if act_mode[-1] == "R" else F.leaky_relu(x, slope)
 
 
-def dncnn_forward(sd, x, nb=17, act_mode="BR", training=False, momentum=0.9, eps=1e-4, new_stats=None):
-    """DnCNN.forward (network_dncnn.py:69-71): x - model(x); body layers conv -> [BN(eps 1e-4, momentum .9)] -> act
+def dncnn_forward(sd, x, nb=17, act_mode="BR", training=False, momentum=0.9, eps=1e-4, new_stats=None, residual=True):
+    """DnCNN.forward (network_dncnn.py:69-71): x - model(x) (residual=False: FDnCNN.forward, :146-148, model(x));
+    body layers conv -> [BN(eps 1e-4, momentum .9)] -> act
     (basicblock.py:65-71).  With training=True BatchNorm uses biased batch statistics; `new_stats` (dict) receives the
     running-stat updates PyTorch would make (running = (1-m)*running + m*batch, unbiased variance)."""
     has_bn = "B" in act_mode
@@ -79,7 +80,7 @@ def dncnn_forward(sd, x, nb=17, act_mode="BR", training=False, momentum=0.9, eps
         h = _act(h, act_mode)
         idx += 1
     n = F.conv2d(h, sd["model.%d.weight" % idx], sd["model.%d.bias" % idx], padding=1)
-    return x - n
+    return x - n if residual else n
 
 
 # ------------------------------------------------------------------------------------------------ UNetRes (DRUNet)

@@ -54,6 +54,9 @@ CASES = {
                            seed=11, loss="l1", train_mode=True),
     "dncnn_br_eval": dict(net="dncnn", kw=dict(in_nc=3, out_nc=3, nc=64, nb=5, act_mode="BR"), x=(2, 3, 24, 24),
                           seed=12, loss="l1"),
+    # FDnCNN (network_dncnn.py:126-148): noise-level map as second input channel, no residual learning
+    "fdncnn_r8": dict(net="fdncnn", kw=dict(in_nc=2, out_nc=1, nc=64, nb=8, act_mode="R"), x=(2, 2, 24, 32), seed=15,
+                      loss="l1"),
     # DRUNet (cfg4 architecture, nb reduced to 2)
     "unetres_nb2": dict(net="unetres", kw=dict(in_nc=4, out_nc=3, nc=[64, 128, 256, 512], nb=2, act_mode="R",
                                                downsample_mode="strideconv", upsample_mode="convtranspose",
@@ -82,7 +85,7 @@ def state_and_io(case):
         cfg = swinir_cfg(kw)
         sd = so.deterministic_state(so.state_spec(cfg), case["seed"], cfg)
         up = kw["upscale"]
-    elif net == "dncnn":
+    elif net in ("dncnn", "fdncnn"):
         sd = so.deterministic_state(co.dncnn_state_spec(**kw), case["seed"])
         up = 1
     else:
@@ -101,9 +104,9 @@ def oracle_forward(case, sd, x, new_stats=None):
     kw, net = case["kw"], case["net"]
     if net == "swinir":
         return so.swinir_forward(sd, x, swinir_cfg(kw))
-    if net == "dncnn":
+    if net in ("dncnn", "fdncnn"):
         return co.dncnn_forward(sd, x, nb=kw["nb"], act_mode=kw["act_mode"], training=case.get("train_mode", False),
-                                new_stats=new_stats)
+                                new_stats=new_stats, residual=net == "dncnn")
     return co.unetres_forward(sd, x, nb=kw["nb"])
 
 
@@ -115,6 +118,8 @@ def build_reference(case, ref_loader):
         model = ref_loader.load("network_swinir").SwinIR(drop_path_rate=0.0, **kw)
     elif net == "dncnn":
         model = ref_loader.load("network_dncnn").DnCNN(**kw)
+    elif net == "fdncnn":
+        model = ref_loader.load("network_dncnn").FDnCNN(**kw)
     else:
         model = ref_loader.load("network_unet").UNetRes(**kw)
     missing = model.load_state_dict(sd, strict=True)

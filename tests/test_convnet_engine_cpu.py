@@ -239,3 +239,27 @@ def test_install_routes_define_G_lookups():
         "print('ok')\n") % (ref_loader.REF, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
+
+
+def test_fdncnn_exact_with_fp32_buffers_and_state_dict():
+    """FDnCNN = the DnCNN engine without the residual: exact host logic (fp32 buffers) vs the oracle, reference layout."""
+    from kair_b200.network_dncnn import FDnCNN
+    import golden_cases as gc
+    case = gc.CASES["fdncnn_r8"]
+    sd, x, tgt = gc.state_and_io(case)
+    model = FDnCNN(**case["kw"])
+    assert list(model.state_dict().keys()) == list(sd.keys())
+    model.load_state_dict(sd, strict=True)
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    y_ref = gc.oracle_forward(case, sdg, x)
+    torch.mean(torch.abs(y_ref - tgt)).backward()
+    params = dict(model.named_parameters())
+    with _Fp32Buffers():
+        plan = DnCNNEngine(parse_dncnn(model.model), params, "cpu", ops=emu_ops, residual=False).plan(2, 24, 32, True, True)
+        y = ConvNetFunction.apply(x, plan, *params.values())
+        torch.mean(torch.abs(y - tgt)).backward()
+    assert y.shape == (2, 1, 24, 32)
+    assert (y.detach() - y_ref.detach()).abs().max().item() < 1e-4
+    gmax = max(sdg[k].grad.norm().item() for k in params)
+    for k, p in params.items():
+        assert (p.grad - sdg[k].grad).norm().item() < 1e-4 * gmax, k

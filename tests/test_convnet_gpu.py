@@ -140,10 +140,10 @@ def _rel_l2(a, b):
 
 
 def _build(case):
-    from kair_b200.network_dncnn import DnCNN
+    from kair_b200.network_dncnn import DnCNN, FDnCNN
     from kair_b200.network_unet import UNetRes
     kw = case["kw"]
-    model = DnCNN(**kw) if case["net"] == "dncnn" else UNetRes(**kw)
+    model = {"dncnn": DnCNN, "fdncnn": FDnCNN, "unetres": UNetRes}[case["net"]](**kw)
     sd, x, tgt = gc.state_and_io(case)
     model.load_state_dict(sd, strict=True)
     return model, sd, x, tgt
@@ -175,6 +175,11 @@ def _check_against_golden(name, grad_tol, out_tol=2e-2):
 
 def test_golden_dncnn_r17():
     _check_against_golden("dncnn_r17", 4e-2)
+
+
+def test_golden_fdncnn():
+    """FDnCNN (network_dncnn.py:126-148): 2 input channels (image + noise-level map), 1 output, no residual."""
+    _check_against_golden("fdncnn_r8", 4e-2)
 
 
 def test_golden_dncnn_br_train():
