@@ -59,3 +59,36 @@ def tiled_forward(model, img, tile, overlap, scale, window_size, tile_batch=4):
     """Single-process equivalent of main_test_swinir.test(img_lq, model, args, window_size) with args.tile set."""
     E, W, _ = tiled_partial(model, img, tile, overlap, scale, window_size, tile_batch)
     return E / W
+
+
+# ------------------------------------------------------------------------------------------------ x8 self-ensemble
+
+def dihedral(img, mode):
+    """The 8 flips / rotations of utils_image.augment_img_tensor4 (utils/utils_image.py:408-426) on (B, C, H, W)."""
+    if mode == 0:
+        return img
+    k, flip = {1: (1, True), 2: (0, True), 3: (3, False), 4: (2, True), 5: (1, False), 6: (2, False), 7: (3, True)}[mode]
+    out = img.rot90(k, [2, 3]) if k else img
+    return out.flip([2]) if flip else out
+
+
+def dihedral_inverse_mode(mode):
+    """utils_model.test_x8 (:178-182): modes 3 and 5 (pure quarter turns) are each other's inverse, the rest are
+    involutions."""
+    return 8 - mode if mode in (3, 5) else mode
+
+
+def test_x8(model, L, sf=1):
+    """`utils_model.test_x8(model, L, modulo=1, sf)` (utils/utils_model.py:176-185): mean over the 8 dihedral transforms of
+    model(transform(L)) mapped back.  Execution differs, not arithmetic: transforms of equal shape are stacked along the
+    batch into one forward (all 8 for square inputs, 2 x 4 otherwise), so one engine plan serves them."""
+    outs = [None] * 8
+    by_shape = {}
+    for i in range(8):
+        by_shape.setdefault(tuple(dihedral(L, i).shape), []).append(i)
+    b = L.shape[0]
+    for modes in by_shape.values():
+        y = model(torch.cat([dihedral(L, i) for i in modes], 0).contiguous())
+        for j, i in enumerate(modes):
+            outs[i] = dihedral(y[j * b:(j + 1) * b], dihedral_inverse_mode(i))
+    return torch.stack(outs, dim=0).mean(dim=0, keepdim=False)

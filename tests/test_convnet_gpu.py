@@ -328,3 +328,19 @@ def test_cuda_graph_replay_matches_eager(net):
         assert torch.equal(graphed(x1).clone(), y_new)
     with pytest.raises(RuntimeError, match="captured for shape"):
         graphed(torch.rand(1, shape[1], 16, 16).cuda())
+
+
+def test_x8_ensemble_on_the_gpu_path():
+    """tiling.test_x8 (utils_model.test_x8, :176-185) around the drop-in DnCNN: the batched 8-way ensemble equals the
+    one-transform-at-a-time evaluation bit for bit (no cross-sample arithmetic in the kernels)."""
+    from kair_b200 import tiling
+    from kair_b200.network_dncnn import DnCNN
+    torch.manual_seed(0)
+    model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=5, act_mode="R").cuda().eval()
+    for shape in [(1, 1, 48, 48), (2, 1, 32, 56)]:
+        L = torch.rand(shape, generator=torch.Generator().manual_seed(3)).cuda()
+        with torch.no_grad():
+            got = tiling.test_x8(model, L)
+            ref = torch.stack([tiling.dihedral(model(tiling.dihedral(L, i).contiguous()), tiling.dihedral_inverse_mode(i))
+                               for i in range(8)], 0).mean(0)
+        assert torch.equal(got, ref)

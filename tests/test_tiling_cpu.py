@@ -60,3 +60,32 @@ def test_rank_sharding_merges_to_the_same_image():
         parts = [tiling.tiled_partial(_model, padded, 16, 8, 2, 8, tile_batch=2, rank=r, world=world) for r in range(world)]
         assert sum(p[2] for p in parts) == len(tiling.tile_origins(padded.shape[2], padded.shape[3], 16, 8))
         assert torch.allclose(tiling.merge_partials(parts), want, atol=1e-6)
+
+
+def test_x8_ensemble_matches_the_sequential_definition():
+    """kair_b200.tiling.test_x8 vs utils_model.test_x8's definition evaluated one transform at a time (square and
+    non-square inputs; an un-equivariant conv so that every inverse transform matters)."""
+    import torch
+    from kair_b200 import tiling
+    torch.manual_seed(0)
+    conv = torch.nn.Conv2d(2, 2, 3, padding=1)
+    calls = []
+
+    def model(x):
+        calls.append(tuple(x.shape))
+        return conv(x)
+
+    for shape in [(2, 2, 12, 12), (1, 2, 8, 14)]:
+        L = torch.rand(shape)
+        for i in range(8):   # every transform is undone by the mode test_x8 pairs it with
+            assert torch.equal(tiling.dihedral(tiling.dihedral(L, i), tiling.dihedral_inverse_mode(i)), L)
+        with torch.no_grad():
+            calls.clear()
+            got = tiling.test_x8(model, L)
+            n_fwd = len(calls)
+            ref = torch.stack([tiling.dihedral(conv(tiling.dihedral(L, i)), tiling.dihedral_inverse_mode(i))
+                               for i in range(8)], 0).mean(0)
+        assert n_fwd == (1 if shape[2] == shape[3] else 2)
+        assert torch.allclose(got, ref, atol=1e-6)
+    ident = tiling.test_x8(lambda x: x, torch.arange(24.0).view(1, 1, 4, 6))
+    assert torch.allclose(ident, torch.arange(24.0).view(1, 1, 4, 6))
