@@ -24,8 +24,10 @@ def install():
     # be swapped before model_plain is imported -- hence "call install() first"
     try:
         ref_loss = importlib.import_module("models.loss")
-        from .loss import CharbonnierLoss
+        from .loss import CharbonnierLoss, PoissonLLLoss
         ref_loss.CharbonnierLoss = CharbonnierLoss
+        if hasattr(ref_loss, "PoissonLLLoss"):      # the SPECT fork's loss (models/loss.py:294-345)
+            ref_loss.PoissonLLLoss = PoissonLLLoss
         done["models.loss"] = "patched"
     except Exception:  # noqa: BLE001 - models.loss needs torchvision / other optional packages in some forks
         done["models.loss"] = "skipped"

@@ -20,14 +20,31 @@ __global__ void pixel_loss_kernel(const kair_pixel_loss_args a) {
   const float inv_n = 1.0f / (float)a.n;
   double acc = 0.0;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (long long)gridDim.x * blockDim.x) {
-    const float d = a.x[i] - a.y[i];
+    const float xv = a.x[i], yv = a.y[i];
+    const float d = xv - yv;
     float l, g;
-    if (a.mode == 0) {  // Charbonnier
+    if (a.mode == 0) {         // Charbonnier
       l = sqrtf(d * d + a.eps);
       g = d / l;
-    } else {            // L1 (sign(0) = 0 like torch)
+    } else if (a.mode == 1) {  // L1 (sign(0) = 0 like torch)
       l = fabsf(d);
       g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+    } else {                   // Poisson log-likelihood on de-normalised counts
+      float lam, k, dlam;      // dlam = d(lambda_raw)/dx
+      if (a.mode == 2) {
+        lam = xv * a.max_pixel; k = yv * a.max_pixel; dlam = a.max_pixel;
+      } else if (a.mode == 3) {
+        const float lg = logf(a.max_pixel + 1.0f);
+        lam = expf(xv * lg) - 1.0f; k = expf(yv * lg) - 1.0f; dlam = lg * (lam + 1.0f);
+      } else {
+        const float s2 = a.max_pixel + 0.375f;
+        lam = s2 * xv * xv - 0.375f; k = s2 * yv * yv - 0.375f; dlam = 2.0f * s2 * xv;
+      }
+      const bool live = lam >= a.eps;   // torch.clamp(min=eps) passes the gradient where the input is >= eps
+      lam = fmaxf(lam, a.eps);
+      k = fmaxf(k, 0.f);
+      l = lam - k * logf(lam);
+      g = live ? (1.0f - k / lam) * dlam : 0.f;
     }
     acc += (double)l;
     if (a.dx) a.dx[i] = g * inv_n;
@@ -87,7 +104,8 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(const kair_adam_ema_args 
 
 int pixel_loss_launch(const kair_pixel_loss_args& a, cudaStream_t st) {
   KB_CHECK(a.x && a.y && a.loss && a.scratch, "kair_pixel_loss: null pointer");
-  KB_CHECK(a.n > 0 && (a.mode == 0 || a.mode == 1), "kair_pixel_loss: empty input or unknown mode %d", a.mode);
+  KB_CHECK(a.n > 0 && a.mode >= 0 && a.mode <= 4, "kair_pixel_loss: empty input or unknown mode %d", a.mode);
+  KB_CHECK(a.mode < 2 || a.max_pixel > 0.f, "kair_pixel_loss: Poisson modes need max_pixel > 0");
   long long blocks = (a.n + 256 * 8 - 1) / (256 * 8);
   const long long cap = 4ll * sm_count();
   if (blocks > cap) blocks = cap;

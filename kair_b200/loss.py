@@ -18,8 +18,8 @@ class _PixelLossFn(torch.autograd.Function):
         need = x.requires_grad or y.requires_grad
         dx = torch.empty_like(xc) if need else None
         loss = torch.empty(1, dtype=torch.float32, device=x.device)
-        o.build_pixel_loss(xc, yc, dx, loss, owner._scratch_for(x.device), eps=owner.eps, mode=owner._mode).run(
-            o.stream_handle())
+        o.build_pixel_loss(xc, yc, dx, loss, owner._scratch_for(x.device), eps=owner.eps, mode=owner._mode,
+                           max_pixel=getattr(owner, "max_pixel", 0.0)).run(o.stream_handle())
         ctx.dx = dx
         ctx.needs = (x.requires_grad, y.requires_grad)
         return loss.view(())
@@ -61,3 +61,19 @@ class L1Loss(_PixelLoss):
     """nn.L1Loss() with the default 'mean' reduction (the DRUNet / DnCNN training loss, model_plain.py:117)."""
     _mode = 1
     eps = 0.0
+
+
+class PoissonLLLoss(_PixelLoss):
+    """Poisson negative log-likelihood on de-normalised SPECT counts (models/loss.py:294-345 of the reference; the fork's
+    `G_lossfn_type: poisson`, model_plain.py:193-202): lambda = clamp(denorm(pred), min=epsilon), k = clamp(denorm(target),
+    min=0), loss = -mean(k*log(lambda) - lambda); denorm per `normalization_method` as utils/utils_spect.py:21-35."""
+    _MODES = {"linear": 2, "log": 3, "anscombe": 4}
+
+    def __init__(self, normalization_method="linear", max_pixel=150.0, epsilon=1e-9):
+        super().__init__()
+        if normalization_method not in self._MODES:
+            raise ValueError(f"Unknown normalization method: {normalization_method}")
+        self.normalization_method = normalization_method
+        self.max_pixel = float(max_pixel)
+        self.epsilon = self.eps = epsilon
+        self._mode = self._MODES[normalization_method]

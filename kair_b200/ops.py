@@ -530,7 +530,7 @@ def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
     return Launch("kair_pixel_shuffle_out", a)
 
 
-def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
+def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0, max_pixel=0.0):
     """loss[0] = mean(sqrt((x-y)^2 + eps)) (mode 0, CharbonnierLoss) or mean|x-y| (mode 1) and dx = d(loss)/dx."""
     _req(x, torch.float32, "x"); _req(y, torch.float32, "y"); _req(dx, torch.float32, "dx")
     _req(loss, torch.float32, "loss"); _req(scratch, torch.float64, "scratch")
@@ -540,7 +540,7 @@ def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
         raise RuntimeError("kair_b200: pixel_loss scratch must hold two 8-byte words")
     a = _S["kair_pixel_loss_args"]()
     a.x, a.y, a.dx, a.loss, a.scratch = _ptr(x), _ptr(y), _ptr(dx), _ptr(loss), _ptr(scratch)
-    a.n, a.eps, a.mode = x.numel(), eps, mode
+    a.n, a.eps, a.mode, a.max_pixel = x.numel(), eps, mode, max_pixel
     return Launch("kair_pixel_loss", a)
 
 

@@ -2,6 +2,7 @@
 
 CPU restatement of the serial tail of the reference's training step:
   * CharbonnierLoss            models/loss.py:208-218      loss = mean(sqrt((x - y)^2 + eps)), eps = 1e-9
+  * PoissonLLLoss              models/loss.py:294-345      -mean(k log(lambda) - lambda) on de-normalised counts
   * Adam                       torch.optim.Adam as built by models/model_plain.py:139-152 (betas, weight decay = L2 added
                                to the gradient, no amsgrad); the published update rule, in torch's operation order
   * update_E                   models/model_base.py:247-252 e = e*decay + p*(1 - decay), after the optimizer step
@@ -20,6 +21,19 @@ def charbonnier(x, y, eps=1e-9):
 def charbonnier_grad(x, y, eps=1e-9):
     d = x - y
     return d / torch.sqrt(d * d + eps) / x.numel()
+
+
+def poisson_ll(pred, target, method="linear", max_pixel=150.0, eps=1e-9):
+    """PoissonLLLoss.forward (models/loss.py:320-345) with denormalize_spect (:308-318 == utils/utils_spect.py:21-35)."""
+    def den(v):
+        if method == "log":
+            return torch.exp(v * math.log(max_pixel + 1.0)) - 1.0
+        if method == "anscombe":
+            return (math.sqrt(max_pixel + 3 / 8) * v) ** 2 - 3 / 8
+        return v * max_pixel
+    lam = torch.clamp(den(pred), min=eps)
+    k = torch.clamp(den(target), min=0.0)
+    return -torch.mean(k * torch.log(lam) - lam)
 
 
 def adam_ema_step(params, grads, exp_avg, exp_avg_sq, ema, step, *, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,

@@ -671,15 +671,32 @@ def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
     return EmuLaunch("kair_pixel_shuffle_out_bwd", run)
 
 
-def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0):
+def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0, max_pixel=0.0):
     def run():
+        import math
         d = x - y
         if mode == 0:
             l = torch.sqrt(d * d + eps)
             g = d / l
-        else:
+        elif mode == 1:
             l = d.abs()
             g = torch.sign(d)
+        else:
+            if mode == 2:
+                den = lambda v: v * max_pixel
+                dlam = torch.full_like(x, max_pixel)
+            elif mode == 3:
+                lg = math.log(max_pixel + 1.0)
+                den = lambda v: torch.exp(v * lg) - 1.0
+                dlam = lg * torch.exp(x * lg)
+            else:
+                s2 = max_pixel + 0.375
+                den = lambda v: s2 * v * v - 0.375
+                dlam = 2.0 * s2 * x
+            raw = den(x)
+            lam, k = raw.clamp(min=eps), den(y).clamp(min=0.0)
+            l = lam - k * torch.log(lam)
+            g = torch.where(raw >= eps, (1.0 - k / lam) * dlam, torch.zeros_like(x))
         loss[0] = l.double().mean().float()
         if dx is not None:
             dx.copy_(g / x.numel())

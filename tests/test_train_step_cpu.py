@@ -149,3 +149,34 @@ def test_engines_repack_after_an_optimizer_step_that_hides_from_version_counters
     with torch.no_grad():
         y1 = model(x)
     assert (y1 - y0).abs().max().item() > 1e-3
+
+
+@pytest.mark.parametrize("method", ["linear", "log", "anscombe"])
+def test_poisson_ll_oracle_and_module(method):
+    """PoissonLLLoss (the SPECT fork's loss): oracle vs the reference module where mounted, drop-in module (emulated
+    kernel) vs the oracle incl. the gradient and the clamp at epsilon (negative predictions)."""
+    from kair_b200.loss import PoissonLLLoss
+    g = torch.Generator().manual_seed(11)
+    x = (torch.rand(2, 1, 16, 16, generator=g) * 0.6 - 0.05)     # some negative predictions -> clamped, zero gradient
+    y = torch.poisson(torch.rand(2, 1, 16, 16, generator=g) * 20.0) / 150.0
+    if method == "log":
+        y = torch.log(y * 150.0 + 1.0) / torch.log(torch.tensor(151.0))
+    xr = x.clone().requires_grad_(True)
+    lo = to.poisson_ll(xr, y, method)
+    lo.backward()
+    if ref_loader.have_reference():
+        ref = ref_loader.load("loss").PoissonLLLoss(method, 150.0, 1e-9)
+        xq = x.clone().requires_grad_(True)
+        lq = ref(xq, y)
+        lq.backward()
+        assert abs(lq.item() - lo.item()) < 1e-6 * max(1.0, abs(lq.item()))
+        assert torch.allclose(xq.grad, xr.grad, rtol=1e-5, atol=1e-8)
+    mod = PoissonLLLoss(method, 150.0, 1e-9)
+    mod._ops = emu_ops
+    xm = x.clone().requires_grad_(True)
+    lm = mod(xm, y)
+    lm.backward()
+    assert abs(lm.item() - lo.item()) < 1e-5 * max(1.0, abs(lo.item()))
+    assert torch.allclose(xm.grad, xr.grad, rtol=1e-4, atol=1e-7)
+    with pytest.raises(ValueError):
+        PoissonLLLoss("sqrt")

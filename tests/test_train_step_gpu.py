@@ -122,3 +122,21 @@ def test_torch_fused_adam_updates_reach_the_engine():
         outs.append(out.detach().clone())
     assert losses[-1] < losses[0], losses
     assert all((outs[i + 1] - outs[i]).abs().max().item() > 0 for i in range(3))
+
+
+@pytest.mark.parametrize("method", ["linear", "log", "anscombe"])
+def test_fused_poisson_ll(method):
+    from kair_b200.loss import PoissonLLLoss
+    from oracle import train_step_oracle as to
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(4, 2, 64, 64, generator=g) * 0.6 - 0.05
+    y = torch.poisson(torch.rand(4, 2, 64, 64, generator=g) * 20.0) / 150.0
+    xr = x.clone().requires_grad_(True)
+    lo = to.poisson_ll(xr, y, method)
+    lo.backward()
+    xc = x.cuda().requires_grad_(True)
+    l = PoissonLLLoss(method, 150.0, 1e-9)(xc, y.cuda())
+    l.backward()
+    torch.cuda.synchronize()
+    assert abs(l.item() - lo.item()) < 1e-5 * max(1.0, abs(lo.item()))
+    assert torch.allclose(xc.grad.cpu(), xr.grad, rtol=2e-4, atol=1e-7)
