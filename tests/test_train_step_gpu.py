@@ -139,4 +139,6 @@ def test_fused_poisson_ll(method):
     l.backward()
     torch.cuda.synchronize()
     assert abs(l.item() - lo.item()) < 1e-5 * max(1.0, abs(lo.item()))
-    assert torch.allclose(xc.grad.cpu(), xr.grad, rtol=2e-4, atol=1e-7)
+    # (1 - k/lambda) cancels where the prediction matches the counts: compare against the gradient's scale
+    err = (xc.grad.cpu() - xr.grad).abs().max().item()
+    assert err < 2e-5 * xr.grad.abs().max().item() + 1e-9, err
