@@ -37,8 +37,9 @@ __global__ void pixel_loss_kernel(const kair_pixel_loss_args a) {
         const float lg = logf(a.max_pixel + 1.0f);
         lam = expf(xv * lg) - 1.0f; k = expf(yv * lg) - 1.0f; dlam = lg * (lam + 1.0f);
       } else {
-        const float s2 = a.max_pixel + 0.375f;
-        lam = s2 * xv * xv - 0.375f; k = s2 * yv * yv - 0.375f; dlam = 2.0f * s2 * xv;
+        const float s = sqrtf(a.max_pixel + 0.375f);   // the reference's operation order: (sqrt(M + 3/8) * v)^2 - 3/8
+        const float tx = s * xv, ty = s * yv;
+        lam = tx * tx - 0.375f; k = ty * ty - 0.375f; dlam = 2.0f * s * tx;
       }
       const bool live = lam >= a.eps;   // torch.clamp(min=eps) passes the gradient where the input is >= eps
       lam = fmaxf(lam, a.eps);
