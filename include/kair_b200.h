@@ -465,7 +465,9 @@ typedef struct kair_pixel_loss_args {
   double* scratch;   /* 2 x 8 bytes, zero before the first call */
   int64_t n;
   float eps;
-  int32_t mode;      /* 0 Charbonnier, 1 L1, 2/3/4 Poisson log-likelihood with linear / log / anscombe de-normalisation */
+  int32_t mode;      /* 0 Charbonnier, 1 L1, 2/3/4 Poisson log-likelihood with linear / log / anscombe de-normalisation,
+                        5 mean squared difference of the uint8 images round(clamp(v,0,1)*255) (tensor2uint + calculate_psnr,
+                        utils/utils_image.py:296-300, 629-645; no gradient) */
   float max_pixel;   /* modes 2-4: PoissonLLLoss (models/loss.py:294-345): lambda = max(denorm(x), eps), k = max(denorm(y), 0),
                         loss = -mean(k log(lambda) - lambda); denorm as utils/utils_spect.py:21-35 */
 } kair_pixel_loss_args;

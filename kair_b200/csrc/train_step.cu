@@ -29,6 +29,10 @@ __global__ void pixel_loss_kernel(const kair_pixel_loss_args a) {
     } else if (a.mode == 1) {  // L1 (sign(0) = 0 like torch)
       l = fabsf(d);
       g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+    } else if (a.mode == 5) {  // uint8 MSE of tensor2uint(x), tensor2uint(y): np.round = round-half-even = rintf
+      const float qx = rintf(fminf(fmaxf(xv, 0.f), 1.f) * 255.0f), qy = rintf(fminf(fmaxf(yv, 0.f), 1.f) * 255.0f);
+      l = (qx - qy) * (qx - qy);
+      g = 0.f;
     } else {                   // Poisson log-likelihood on de-normalised counts
       float lam, k, dlam;      // dlam = d(lambda_raw)/dx
       if (a.mode == 2) {
@@ -105,8 +109,8 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(const kair_adam_ema_args 
 
 int pixel_loss_launch(const kair_pixel_loss_args& a, cudaStream_t st) {
   KB_CHECK(a.x && a.y && a.loss && a.scratch, "kair_pixel_loss: null pointer");
-  KB_CHECK(a.n > 0 && a.mode >= 0 && a.mode <= 4, "kair_pixel_loss: empty input or unknown mode %d", a.mode);
-  KB_CHECK(a.mode < 2 || a.max_pixel > 0.f, "kair_pixel_loss: Poisson modes need max_pixel > 0");
+  KB_CHECK(a.n > 0 && a.mode >= 0 && a.mode <= 5, "kair_pixel_loss: empty input or unknown mode %d", a.mode);
+  KB_CHECK(a.mode < 2 || a.mode == 5 || a.max_pixel > 0.f, "kair_pixel_loss: Poisson modes need max_pixel > 0");
   long long blocks = (a.n + 256 * 8 - 1) / (256 * 8);
   const long long cap = 4ll * sm_count();
   if (blocks > cap) blocks = cap;

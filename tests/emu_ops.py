@@ -681,6 +681,10 @@ def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0, max_pixel=0.0
         elif mode == 1:
             l = d.abs()
             g = torch.sign(d)
+        elif mode == 5:
+            q = lambda v: (v.clamp(0, 1) * 255.0).round()
+            l = (q(x) - q(y)) ** 2
+            g = torch.zeros_like(x)
         else:
             if mode == 2:
                 den = lambda v: v * max_pixel

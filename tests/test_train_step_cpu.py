@@ -180,3 +180,18 @@ def test_poisson_ll_oracle_and_module(method):
     assert torch.allclose(xm.grad, xr.grad, rtol=1e-4, atol=1e-7)
     with pytest.raises(ValueError):
         PoissonLLLoss("sqrt")
+
+
+def test_psnr_metric_host_logic():
+    """kair_b200.metrics.psnr_uint8 == golden_cases.psnr_uint8 (the oracle's restatement of tensor2uint +
+    calculate_psnr), incl. border cropping and identical images."""
+    import golden_cases as gc
+    from kair_b200 import metrics
+    g = torch.Generator().manual_seed(2)
+    a = torch.rand(1, 1, 20, 24, generator=g) * 1.2 - 0.1
+    b = a + torch.randn(a.shape, generator=g) * 0.05
+    assert abs(metrics.psnr_uint8(a, b, ops=emu_ops) - gc.psnr_uint8(a, b)) < 1e-4
+    assert abs(metrics.psnr_uint8(a, b, border=3, ops=emu_ops) - gc.psnr_uint8(a[..., 3:-3, 3:-3], b[..., 3:-3, 3:-3])) < 1e-4
+    assert metrics.psnr_uint8(a, a, ops=emu_ops) == float("inf")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        metrics.psnr_uint8(a, b)

@@ -145,3 +145,14 @@ def test_fused_poisson_ll(method):
     # the largest gradients: 1-ulp differences between CUDA's and the host's expf show up at 1e-3 of the scale
     err = (xc.grad.cpu() - xr.grad).abs().max().item()
     assert err < (2e-5 if method == "linear" else 5e-3) * xr.grad.abs().max().item() + 1e-9, err
+
+
+def test_psnr_metric_on_gpu():
+    import golden_cases as gc
+    from kair_b200 import metrics
+    g = torch.Generator().manual_seed(2)
+    a = torch.rand(2, 1, 1024, 256, generator=g) * 1.2 - 0.1       # the fork's full-frame SPECT validation shape
+    b = a + torch.randn(a.shape, generator=g) * 0.03
+    assert abs(metrics.psnr_uint8(a.cuda(), b.cuda()) - gc.psnr_uint8(a, b)) < 1e-4
+    assert abs(metrics.psnr_uint8(a.cuda(), b.cuda(), border=8) - gc.psnr_uint8(a[..., 8:-8, 8:-8], b[..., 8:-8, 8:-8])) < 1e-4
+    assert metrics.psnr_uint8(a.cuda(), a.cuda()) == float("inf")
