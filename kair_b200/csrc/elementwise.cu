@@ -393,9 +393,10 @@ constexpr int CI_MAX = 4;  // image-side channel count handled by the SIMT convo
 // every thread is independent (no reductions), its 9*ci image loads are issued together, the weights are read from
 // shared memory as float4 pairs and the result leaves as one 16-byte bf16 / two 16-byte fp32 stores.
 //   feat[t][o] = act( b[o] + sum_{c,tap} W[o][c][tap] * ((img[c][p+tap] - mean[c]) * range) )
+template <int CI>   // image channels as a compile-time constant: the 9*CI tap loads / index chains are the issue budget
 __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
   extern __shared__ float sw[];  // [ci*9][P8] weights, then [P8] bias; P8 = pitch rounded to 8
-  const int K = a.ci * 9;
+  const int K = CI * 9;
   const int P8 = a.pitch;        // launcher guarantees pitch % 8 == 0
   for (int e = threadIdx.x; e < K * P8; e += blockDim.x) {
     const int o = e % P8, k = e / P8;
@@ -411,15 +412,15 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
     const int g = (int)(e % og);
     const long long t = e / og;
     const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
-    float in[CI_MAX * 9];
+    float in[CI * 9];
 #pragma unroll
-    for (int c = 0; c < CI_MAX; ++c) {
+    for (int c = 0; c < CI; ++c) {
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
         float v = 0.f;
-        if (c < a.ci && hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
-          v = __ldg(a.img + (((size_t)b * a.ci + c) * a.H + hh) * a.Wd + ww);
+        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+          v = __ldg(a.img + (((size_t)b * CI + c) * a.H + hh) * a.Wd + ww);
           v = (v - a.mean[c]) * a.range;
         }
         in[c * 9 + tap] = v;
@@ -432,8 +433,7 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
       acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
     }
 #pragma unroll
-    for (int c = 0; c < CI_MAX; ++c) {
-      if (c >= a.ci) break;
+    for (int c = 0; c < CI; ++c) {
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const float x = in[c * 9 + tap];
@@ -476,7 +476,12 @@ int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st) {
   const long long n = (long long)a.batch * a.H * a.Wd * (a.pitch >> 3);
   long long blocks = (n + 255) / 256;
   if (blocks > (long long)sm_count() * 8) blocks = (long long)sm_count() * 8;
-  conv_in_fwd_kernel<<<(int)blocks, 256, smem, st>>>(a);
+  switch (a.ci) {
+    case 1: conv_in_fwd_kernel<1><<<(int)blocks, 256, smem, st>>>(a); break;
+    case 2: conv_in_fwd_kernel<2><<<(int)blocks, 256, smem, st>>>(a); break;
+    case 3: conv_in_fwd_kernel<3><<<(int)blocks, 256, smem, st>>>(a); break;
+    default: conv_in_fwd_kernel<4><<<(int)blocks, 256, smem, st>>>(a); break;
+  }
   KB_CUDA(cudaGetLastError());
   return 0;
 }
