@@ -612,7 +612,8 @@ __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
   }
 }
 
-int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
+// fallback of conv_thin.cu's tensor-core kernel (C > 192 or feature rows shorter than the k-padding)
+int conv_out_fwd_simt_launch(const kair_conv_out_args& a, cudaStream_t st) {
   KB_CHECK(a.feat && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
   KB_CHECK(a.co >= 1 && a.co <= CI_MAX, "kair_conv_out_fwd: co=%d unsupported (max %d)", a.co, CI_MAX);
   KB_CHECK(a.pitch % 8 == 0 && a.C <= a.pitch, "kair_conv_out_fwd: pitch must be a multiple of 8 channels, >= C");

@@ -72,20 +72,22 @@ def test_conv_in(ci, B, H, W):
     _run_both("conv_in_wgrad", kw2, ["dW", "db"], 1e-4)
 
 
-@pytest.mark.parametrize("co,B,H,W", [(1, 2, 16, 24), (3, 1, 9, 13)])
-def test_conv_out(co, B, H, W):
-    C, Cp = 180, 192
+@pytest.mark.parametrize("co,B,H,W,C,Cp", [(1, 2, 16, 24, 180, 192), (3, 1, 9, 13, 180, 192), (1, 1, 40, 70, 64, 64),
+                                           (3, 2, 33, 37, 60, 64), (4, 1, 8, 8, 48, 64), (2, 1, 5, 3, 200, 256)])
+def test_conv_out(co, B, H, W, C, Cp):
     g = _g(co * 5 + W)
     T = B * H * W
     feat = torch.zeros(T, Cp).bfloat16(); feat[:, :C] = torch.randn(T, C, generator=g).bfloat16()
-    feat[:, C] = 1.0
+    if Cp > C:
+        feat[:, C] = 1.0
     Wt = torch.randn(co, C, 3, 3, generator=g) * 0.1
     b = torch.randn(co, generator=g)
     skip = torch.rand(B, co, H, W, generator=g)
     mean = torch.rand(co, generator=g)
     kw = dict(feat=feat, W=Wt, b=b, out=torch.zeros(B, co, H, W), out_mean=mean, C=C, pitch=Cp, out_scale=0.5,
               skip=skip, skip_mean=mean, skip_scale=2.0)
-    _run_both("conv_out_fwd", kw, ["out"], 1e-5)
+    # tensor-core path: fp32 weights as two bf16 terms (~16 mantissa bits), fp32 accumulation in MMA order
+    _run_both("conv_out_fwd", kw, ["out"], 3e-5)
     dout = torch.randn(B, co, H, W, generator=g)
     kw2 = dict(dout=dout, W=Wt, C=C, pitch=Cp, out_scale=0.5, dfeat_f32=torch.zeros(T, Cp),
                dfeat_bf16=torch.zeros(T, Cp).bfloat16())
