@@ -31,8 +31,7 @@ constexpr int CO_HW = CO_TW + 2;   // halo width
 struct ConvOutTile {
   kair_conv_out_args a;
   int kc;                 // channels per tap, rounded up to 16 (<= pitch)
-  int th;                 // tile height = warps per CTA
-  int tiles_x, tiles_y;
+  int th;                 // tile height = warps per CTA; grid = (ceil(W / 32), ceil(H / th), batch)
 };
 
 __device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, bool pred) {
@@ -52,15 +51,7 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 
-// raw W[c][k][tap]; zero outside the real (co, C) extent
-__device__ __forceinline__ float w_raw(const kair_conv_out_args& a, int c, int k, int tap) {
-  return (c < a.co && k < a.C) ? __ldg(a.W + ((size_t)c * a.C + k) * 9 + tap) : 0.f;
-}
-// the bf16 term (0: hi, 1: lo) of an fp32 weight
-__device__ __forceinline__ float w_term(float w, int lo_term) {
-  const float hi = __bfloat162float(__float2bfloat16_rn(w));
-  return lo_term ? w - hi : hi;
-}
+__device__ __forceinline__ float bf16_round(float w) { return __bfloat162float(__float2bfloat16_rn(w)); }
 
 __global__ void __launch_bounds__(256) conv_out_fwd_mma_kernel(const ConvOutTile p) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -70,56 +61,52 @@ __global__ void __launch_bounds__(256) conv_out_fwd_mma_kernel(const ConvOutTile
   const uint32_t pitchB = 2u * p.kc + 16u;   // bytes per halo pixel
   uint2* frag = reinterpret_cast<uint2*>(smem);              // [ksteps][32 lanes]
   uint8_t* tile = smem + (size_t)ksteps * 32 * sizeof(uint2);
-  const int tid = threadIdx.x, lane = tid & 31, wrow = tid >> 5, nthr = blockDim.x;
-  const int tx = blockIdx.x % p.tiles_x, ty = (blockIdx.x / p.tiles_x) % p.tiles_y, b = blockIdx.x / (p.tiles_x * p.tiles_y);
-  const int x0 = tx * CO_TW, y0 = ty * p.th;
+  const int tid = threadIdx.x, lane = tid & 31, wrow = tid >> 5, nwarp = blockDim.x >> 5;
+  const int b = blockIdx.z;
+  const int x0 = blockIdx.x * CO_TW, y0 = blockIdx.y * p.th;
 
   pdl_wait();                 // the features come from the previous kernel of the stream
   pdl_launch_dependents();
 
-  {  // halo tile -> shared memory; (pixel, chunk) advance incrementally, one thread moves 16 bytes per step
-    const bf16* feat = reinterpret_cast<const bf16*>(a.feat);
+  {  // halo tile -> shared memory: a warp per halo row (row base and row validity are warp-uniform), lanes walk the
+     // row's 34 * cpp 16-byte chunks; (pixel, chunk) advance incrementally
+    const uint8_t* feat = reinterpret_cast<const uint8_t*>(a.feat);
     const int cpp = p.kc >> 3;               // 16-byte chunks per pixel
-    const int npix = (p.th + 2) * CO_HW;
-    const int dq = nthr / cpp, dr = nthr - dq * cpp;
-    const uint32_t tile_s = smem_u32(tile);
-    int pix = tid / cpp, ch = tid - pix * cpp;
-    while (pix < npix) {
-      const int hy = pix / CO_HW, hx = pix - hy * CO_HW;
-      const int y = y0 - 1 + hy, x = x0 - 1 + hx;
-      const bool in = y >= 0 && y < a.H && x >= 0 && x < a.Wd;
-      const bf16* src = in ? feat + (((size_t)b * a.H + y) * a.Wd + x) * a.pitch + ch * 8 : feat;
-      cp_async16_zfill(tile_s + pix * pitchB + ch * 16, src, in);
-      pix += dq; ch += dr;
-      if (ch >= cpp) { ch -= cpp; ++pix; }
+    const int dq = 32 / cpp, dr = 32 - dq * cpp;
+    const uint32_t gpitch = (uint32_t)a.pitch * 2u;
+    for (int hy = wrow; hy < p.th + 2; hy += nwarp) {
+      const int y = y0 - 1 + hy;
+      const bool yin = y >= 0 && y < a.H;
+      const uint8_t* grow = feat + ((size_t)b * a.H + (yin ? y : 0)) * a.Wd * gpitch;
+      const uint32_t srow = smem_u32(tile) + hy * CO_HW * pitchB;
+      int hx = lane / cpp, ch = lane - hx * cpp;
+      while (hx < CO_HW) {
+        const int x = x0 - 1 + hx;
+        const bool in = yin && x >= 0 && x < a.Wd;
+        cp_async16_zfill(srow + hx * pitchB + ch * 16, in ? grow + (size_t)x * gpitch + ch * 16 : feat, in);
+        hx += dq; ch += dr;
+        if (ch >= cpp) { ch -= cpp; ++hx; }
+      }
     }
   }
-  // B fragments while the copies fly: lane (g = lane/4, t = lane%4) of k-step s holds W^T[k = 2t, 2t+1 | 2t+8, 2t+9][n = g];
-  // four entries per thread per round so that the 16 weight gathers of a round are in flight together
-  for (int e0 = tid; e0 < ksteps * 32; e0 += 4 * nthr) {
-    float w[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int e = e0 + i * nthr;
-      const int s = e >> 5, l = e & 31;
+  // B fragments while the copies fly: lane (g = lane/4, t = lane%4) of k-step s holds W^T[k = 2t, 2t+1 | 2t+8, 2t+9][n = g],
+  // n = c: hi(W[c]), n = c + 4: lo(W[c]).  Zero everything, then one thread per real (k-step, t, c) writes both terms
+  // (disjoint addresses: no ordering needed between the two loops).
+  {
+    const int nthr = blockDim.x;
+    for (int e = tid; e < ksteps * 32; e += nthr)
+      if (((e >> 2) & 3) >= a.co) frag[e] = make_uint2(0u, 0u);
+    for (int e = tid; e < ksteps * 4 * a.co; e += nthr) {
+      const int t = e & 3, sc = e >> 2;
+      const int s = sc / a.co, c = sc - s * a.co;
       const int tap = s / kpt, kk = s - tap * kpt;
-      const int c = (l >> 2) & 3, k0 = kk * 16 + 2 * (l & 3);
-      const bool on = e < ksteps * 32;
-      w[i][0] = on ? w_raw(a, c, k0, tap) : 0.f;
-      w[i][1] = on ? w_raw(a, c, k0 + 1, tap) : 0.f;
-      w[i][2] = on ? w_raw(a, c, k0 + 8, tap) : 0.f;
-      w[i][3] = on ? w_raw(a, c, k0 + 9, tap) : 0.f;
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int e = e0 + i * nthr;
-      const int lo = (e & 31) >> 4;          // n = lane/4 >= 4: the low-order term
-      if (e < ksteps * 32) {
-        uint2 v;
-        v.x = pack_bf16x2(w_term(w[i][0], lo), w_term(w[i][1], lo));
-        v.y = pack_bf16x2(w_term(w[i][2], lo), w_term(w[i][3], lo));
-        frag[e] = v;
-      }
+      const int k0 = kk * 16 + 2 * t;
+      const float* wp = a.W + ((size_t)c * a.C + k0) * 9 + tap;
+      const float w0 = k0 < a.C ? __ldg(wp) : 0.f, w1 = k0 + 1 < a.C ? __ldg(wp + 9) : 0.f;
+      const float w2 = k0 + 8 < a.C ? __ldg(wp + 72) : 0.f, w3 = k0 + 9 < a.C ? __ldg(wp + 81) : 0.f;
+      const float h0 = bf16_round(w0), h1 = bf16_round(w1), h2 = bf16_round(w2), h3 = bf16_round(w3);
+      frag[s * 32 + c * 4 + t] = make_uint2(pack_bf16x2(h0, h1), pack_bf16x2(h2, h3));
+      frag[s * 32 + (c + 4) * 4 + t] = make_uint2(pack_bf16x2(w0 - h0, w1 - h1), pack_bf16x2(w2 - h2, w3 - h3));
     }
   }
   cp_async_wait_all();
@@ -198,10 +185,9 @@ int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
   p.kc = (a.C + 15) & ~15;
   if (p.kc > a.pitch || p.kc > 192) return conv_out_fwd_simt_launch(a, st);   // rows too short / too wide for the tile
   p.th = p.kc <= 64 ? 8 : 4;
-  p.tiles_x = (a.Wd + CO_TW - 1) / CO_TW;
-  p.tiles_y = (a.H + p.th - 1) / p.th;
-  const long long grid = (long long)p.tiles_x * p.tiles_y * a.batch;
-  KB_CHECK(grid > 0 && grid < (1ll << 31), "kair_conv_out_fwd: empty or oversized image batch");
+  const dim3 grid((unsigned)((a.Wd + CO_TW - 1) / CO_TW), (unsigned)((a.H + p.th - 1) / p.th), (unsigned)a.batch);
+  KB_CHECK(a.batch > 0 && a.H > 0 && a.Wd > 0 && grid.y < 65536u && grid.z < 65536u,
+           "kair_conv_out_fwd: empty or oversized image batch");
   const size_t smem = (size_t)9 * (p.kc >> 4) * 32 * sizeof(uint2) + (size_t)(p.th + 2) * CO_HW * (2 * p.kc + 16);
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -211,7 +197,7 @@ int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
     attr_set[dev & 63] = true;
   }
   KB_CHECK(smem <= 112 * 1024, "kair_conv_out_fwd: tile does not fit in shared memory");
-  KB_CUDA(launch_pdl(conv_out_fwd_mma_kernel, (int)grid, p.th * 32, smem, st, p));
+  KB_CUDA(launch_pdl(conv_out_fwd_mma_kernel, grid, p.th * 32, smem, st, p));
   return 0;
 }
 

@@ -40,9 +40,9 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* ba
 // KB_PDL=0 in the environment launches with plain stream order.
 bool pdl_enabled();
 template <typename P>
-inline cudaError_t launch_pdl(void (*kern)(const P), int grid, int block, size_t smem, cudaStream_t st, const P& p) {
+inline cudaError_t launch_pdl(void (*kern)(const P), dim3 grid, int block, size_t smem, cudaStream_t st, const P& p) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid);
+  cfg.gridDim = grid;
   cfg.blockDim = dim3((unsigned)block);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
@@ -52,6 +52,11 @@ inline cudaError_t launch_pdl(void (*kern)(const P), int grid, int block, size_t
   cfg.attrs = at;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
+template <typename P>
+inline cudaError_t launch_pdl(void (*kern)(const P), int grid, int block, size_t smem, cudaStream_t st, const P& p) {
+  return launch_pdl(kern, dim3((unsigned)grid), block, smem, st, p);
 }
 
 int sm_count();
