@@ -393,7 +393,9 @@ constexpr int CI_MAX = 4;  // image-side channel count handled by the SIMT convo
 // every thread is independent (no reductions), its 9*ci image loads are issued together, the weights are read from
 // shared memory as float4 pairs and the result leaves as one 16-byte bf16 / two 16-byte fp32 stores.
 //   feat[t][o] = act( b[o] + sum_{c,tap} W[o][c][tap] * ((img[c][p+tap] - mean[c]) * range) )
-template <int CI>   // image channels as a compile-time constant: the 9*CI tap loads / index chains are the issue budget
+// CI: image channels as a compile-time constant (the 9*CI tap loads / index chains are the issue budget);
+// idx_t: 32-bit element index whenever T * pitch/8 fits (the 64-bit div/mod chain cost more than the 72 FMAs)
+template <int CI, typename idx_t>
 __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
   extern __shared__ float sw[];  // [ci*9][P8] weights, then [P8] bias; P8 = pitch rounded to 8
   const int K = CI * 9;
@@ -405,13 +407,15 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
   float* sbias = sw + K * P8;
   for (int o = threadIdx.x; o < P8; o += blockDim.x) sbias[o] = (o < a.O && a.b) ? a.b[o] : 0.f;
   __syncthreads();
-  const int og = P8 >> 3;  // output groups per pixel
-  const long long T = (long long)a.batch * a.H * a.Wd;
-  const long long n = T * og;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(e % og);
-    const long long t = e / og;
-    const int w = (int)(t % a.Wd), h = (int)((t / a.Wd) % a.H), b = (int)(t / ((long long)a.Wd * a.H));
+  const idx_t og = (idx_t)(P8 >> 3);  // output groups per pixel
+  const idx_t T = (idx_t)a.batch * (idx_t)a.H * (idx_t)a.Wd;
+  const idx_t n = T * og;
+  for (idx_t e = (idx_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (idx_t)gridDim.x * blockDim.x) {
+    const idx_t t = e / og;
+    const int g = (int)(e - t * og);
+    const idx_t row = t / (idx_t)a.Wd;
+    const int w = (int)(t - row * (idx_t)a.Wd);
+    const int b = (int)(row / (idx_t)a.H), h = (int)(row - (idx_t)b * (idx_t)a.H);
     float in[CI * 9];
 #pragma unroll
     for (int c = 0; c < CI; ++c) {
@@ -450,7 +454,7 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
       if (o >= a.O) acc[i] = 0.f;
       else if (a.act == KAIR_ACT_LRELU) acc[i] = acc[i] > 0.f ? acc[i] : acc[i] * a.act_slope;
     }
-    const long long off = t * a.pitch + 8 * g;
+    const long long off = (long long)t * a.pitch + 8 * g;
     if (a.out_f32) {
       reinterpret_cast<float4*>(a.out_f32 + off)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
       reinterpret_cast<float4*>(a.out_f32 + off)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
@@ -476,12 +480,17 @@ int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st) {
   const long long n = (long long)a.batch * a.H * a.Wd * (a.pitch >> 3);
   long long blocks = (n + 255) / 256;
   if (blocks > (long long)sm_count() * 8) blocks = (long long)sm_count() * 8;
+  const bool small = n + (long long)blocks * 256 < (1ll << 32);   // the grid-stride index stays inside 32 bits
+#define KB_CONV_IN(CI_)                                                                       \
+  if (small) conv_in_fwd_kernel<CI_, unsigned><<<(int)blocks, 256, smem, st>>>(a);            \
+  else conv_in_fwd_kernel<CI_, long long><<<(int)blocks, 256, smem, st>>>(a)
   switch (a.ci) {
-    case 1: conv_in_fwd_kernel<1><<<(int)blocks, 256, smem, st>>>(a); break;
-    case 2: conv_in_fwd_kernel<2><<<(int)blocks, 256, smem, st>>>(a); break;
-    case 3: conv_in_fwd_kernel<3><<<(int)blocks, 256, smem, st>>>(a); break;
-    default: conv_in_fwd_kernel<4><<<(int)blocks, 256, smem, st>>>(a); break;
+    case 1: KB_CONV_IN(1); break;
+    case 2: KB_CONV_IN(2); break;
+    case 3: KB_CONV_IN(3); break;
+    default: KB_CONV_IN(4); break;
   }
+#undef KB_CONV_IN
   KB_CUDA(cudaGetLastError());
   return 0;
 }
