@@ -77,7 +77,7 @@ def test_batchnorm_kernels(T, C, slope):
                               eps=1e-4), ["scale", "shift"], 1e-5)
 
 
-@pytest.mark.parametrize("r,C", [(2, 64), (3, 64), (4, 4)])
+@pytest.mark.parametrize("r,C", [(2, 64), (2, 6), (3, 64), (4, 4)])
 def test_pixel_shuffle_and_nearest(r, C):
     B, H, W = 2, 6, 10
     x = torch.randn(B * H * W, C * r * r, generator=_g(r)).bfloat16()
