@@ -521,6 +521,29 @@ __global__ void pixel_shuffle_bwd_kernel(const kair_shuffle_args a) {
   }
 }
 
+// r = 2 fast path, the mirror of pixel_shuffle2_kernel: four coalesced bf16-pair reads (one per sub-pixel), one 16-byte write
+template <typename idx_t>
+__global__ void pixel_shuffle2_bwd_kernel(const kair_shuffle_args a) {
+  const idx_t cpp = (idx_t)(a.C >> 1);
+  const idx_t n = (idx_t)a.batch * (idx_t)a.H * (idx_t)a.W * cpp;
+  const idx_t Wi = (idx_t)a.W, Wo = Wi * 2;
+  const uint32_t* in = reinterpret_cast<const uint32_t*>(a.in);
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  const long long ip = a.in_pitch >> 1;
+  for (idx_t e = (idx_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (idx_t)gridDim.x * blockDim.x) {
+    const idx_t ti = e / cpp, q = e - ti * cpp;
+    const idx_t row = ti / Wi, w = ti - row * Wi;   // row = b * H + h
+    const long long i0 = ((long long)(2 * row) * Wo + 2 * w) * ip + q, i1 = i0 + (long long)Wo * ip;
+    const uint32_t s0 = __ldg(in + i0), s1 = __ldg(in + i0 + ip), s2 = __ldg(in + i1), s3 = __ldg(in + i1 + ip);
+    uint4 v;   // (c0 s0, c0 s1), (c0 s2, c0 s3), (c1 s0, c1 s1), (c1 s2, c1 s3)
+    v.x = __byte_perm(s0, s1, 0x5410);
+    v.y = __byte_perm(s2, s3, 0x5410);
+    v.z = __byte_perm(s0, s1, 0x7632);
+    v.w = __byte_perm(s2, s3, 0x7632);
+    reinterpret_cast<uint4*>(out + (long long)ti * a.out_pitch)[q] = v;
+  }
+}
+
 // adjoint of nearest x2: low-resolution gradient = sum of the 2x2 footprint (fp32), then the LeakyReLU mask
 __global__ void upsample_nearest2_bwd_kernel(const kair_shuffle_args a) {
   const int Wo = a.W * 2, vc = a.C >> 3;
@@ -599,6 +622,14 @@ int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st) {
                a.in_pitch >= a.C && !a.mask,
            "kair_pixel_shuffle_bwd: bad geometry (r=%d, C=%d) or mask given", a.r, a.C);
   const long long n = (long long)a.batch * a.H * a.W * a.r * a.r * (a.C >> 1);
+  if (a.r == 2 && a.out_pitch % 8 == 0 && a.in_pitch % 2 == 0) {
+    const long long n2 = n >> 2;   // 16-byte output chunks
+    const int grid = grid_for(n2, 256, 16);
+    if (n2 + (long long)grid * 256 < (1ll << 32)) pixel_shuffle2_bwd_kernel<unsigned><<<grid, 256, 0, st>>>(a);
+    else pixel_shuffle2_bwd_kernel<long long><<<grid, 256, 0, st>>>(a);
+    KB_CUDA(cudaGetLastError());
+    return 0;
+  }
   pixel_shuffle_bwd_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;

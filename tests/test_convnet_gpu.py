@@ -88,6 +88,9 @@ def test_pixel_shuffle_and_nearest(r, C):
     out = torch.zeros(B * H * r * W * r, C).bfloat16()
     emu_ops.build_pixel_shuffle(x, out, batch=B, H=H, W=W, C=C, r=r).run()
     assert torch.equal(out.float().view(B, H * r, W * r, C).permute(0, 3, 1, 2), ref)
+    dy = torch.randn(B * H * r * W * r, C, generator=_g(r + 10)).bfloat16()
+    _run_both("pixel_shuffle_bwd", dict(dy=dy, dx=torch.zeros(B * H * W, C * r * r).bfloat16(), batch=B, H=H, W=W, C=C, r=r),
+              ["dx"], 1e-6)
     if r == 2:
         x8 = torch.randn(B * H * W, 64, generator=_g(5)).bfloat16()
         _run_both("upsample_nearest2", dict(x=x8, out=torch.zeros(B * 4 * H * W, 64).bfloat16(), batch=B, H=H, W=W, C=64),
