@@ -53,12 +53,13 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 
 __device__ __forceinline__ float bf16_round(float w) { return __bfloat162float(__float2bfloat16_rn(w)); }
 
+template <int KPT>   // k-steps per tap as a compile-time constant (4: C = 49..64, every SR head / DnCNN / DRUNet); 0: run-time
 __global__ void __launch_bounds__(256) conv_out_fwd_mma_kernel(const ConvOutTile p) {
   extern __shared__ __align__(16) uint8_t smem[];
   const kair_conv_out_args& a = p.a;
-  const int kpt = p.kc >> 4;                 // k-steps per tap
+  const int kpt = KPT ? KPT : (p.kc >> 4);   // k-steps per tap
   const int ksteps = 9 * kpt;
-  const uint32_t pitchB = 2u * p.kc + 16u;   // bytes per halo pixel
+  const uint32_t pitchB = 32u * kpt + 16u;   // bytes per halo pixel (2 * kc + 16)
   uint2* frag = reinterpret_cast<uint2*>(smem);              // [ksteps][32 lanes]
   uint8_t* tile = smem + (size_t)ksteps * 32 * sizeof(uint2);
   const int tid = threadIdx.x, lane = tid & 31, wrow = tid >> 5, nwarp = blockDim.x >> 5;
@@ -147,6 +148,7 @@ __global__ void __launch_bounds__(256) conv_out_fwd_mma_kernel(const ConvOutTile
 #pragma unroll
     for (int tap = 0; tap < 9; ++tap) {
       const uint32_t toff = abase + ((tap / 3) * CO_HW + tap % 3) * pitchB;
+#pragma unroll
       for (int kk = 0; kk < kpt; ++kk) {
         const uint2 bw = fl[(tap * kpt + kk) * 32];
         uint32_t a0[4], a1[4];
@@ -193,11 +195,13 @@ int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
   int dev = 0;
   KB_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_mma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set[dev & 63] = true;
   }
   KB_CHECK(smem <= 112 * 1024, "kair_conv_out_fwd: tile does not fit in shared memory");
-  KB_CUDA(launch_pdl(conv_out_fwd_mma_kernel, grid, p.th * 32, smem, st, p));
+  if (p.kc == 64) KB_CUDA(launch_pdl(conv_out_fwd_mma_kernel<4>, grid, p.th * 32, smem, st, p));
+  else KB_CUDA(launch_pdl(conv_out_fwd_mma_kernel<0>, grid, p.th * 32, smem, st, p));
   return 0;
 }
 

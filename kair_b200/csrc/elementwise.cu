@@ -194,18 +194,20 @@ int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st) {
   return 0;
 }
 
+template <int TAPS>   // 0: run-time tap count; 1 / 4 / 9: compile-time (the index chain divides by it)
 __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
   const int l = blockIdx.y;
-  const int taps = a.taps;
-  const int rp = a.dwp_pitch > 0 ? a.dwp_pitch : taps * a.I_pad;  // row pitch of the packed gradient
+  const unsigned taps = TAPS ? TAPS : a.taps;
+  const int rp = a.dwp_pitch > 0 ? a.dwp_pitch : (int)taps * a.I_pad;  // row pitch of the packed gradient
   const float* dWp = a.dWp + (size_t)l * a.O_pad * rp;
   float* dW = reinterpret_cast<float*>(a.dW[l]);
-  const size_t n = (size_t)a.O * a.I * taps;
-  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
-    const int tap = (int)(e % taps);
-    const int i = (int)((e / taps) % a.I);
-    const int o = (int)(e / ((size_t)taps * a.I));
-    dW[e] = dWp[(size_t)o * rp + tap * a.I_pad + i];
+  // one layer's (O, I, taps) count fits 32 bits (launcher check): 32-bit div/mod chain, coalesced writes, the strided
+  // reads of a warp (taps rows x ~4 consecutive inputs) are served by L1
+  const unsigned n = (unsigned)a.O * (unsigned)a.I * taps, I = (unsigned)a.I;
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+    const unsigned oi = e / taps, tap = e - oi * taps;
+    const unsigned o = oi / I, i = oi - o * I;
+    dW[e] = __ldg(dWp + (size_t)o * rp + tap * a.I_pad + i);
   }
   if (a.db && a.ones_col >= 0 && blockIdx.x == 0) {
     float* db = reinterpret_cast<float*>(a.db[l]);
@@ -217,9 +219,14 @@ __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
 int unpack_conv_launch(const kair_unpack_conv_args& a, cudaStream_t st) {
   KB_CHECK(a.dWp && a.dW, "kair_unpack_conv_grad: null pointer");
   size_t n = (size_t)a.O * a.I * a.taps;
+  KB_CHECK(a.taps >= 1 && n < (1ull << 31), "kair_unpack_conv_grad: a layer's weight count must fit 31 bits");
   int blocks = (int)((n + 255) / 256);
   if (blocks > 1024) blocks = 1024;
-  unpack_conv_kernel<<<dim3(blocks, a.L), 256, 0, st>>>(a);
+  const dim3 grid(blocks, a.L);
+  if (a.taps == 9) unpack_conv_kernel<9><<<grid, 256, 0, st>>>(a);
+  else if (a.taps == 4) unpack_conv_kernel<4><<<grid, 256, 0, st>>>(a);
+  else if (a.taps == 1) unpack_conv_kernel<1><<<grid, 256, 0, st>>>(a);
+  else unpack_conv_kernel<0><<<grid, 256, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
 }
