@@ -3,7 +3,7 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this module.
 It restates, in functional PyTorch on plain state_dict tensors, the arithmetic of /root/reference
 models/network_swinir.py (file:line cited per function).  It is pinned against the real reference modules by
-tests/test_oracle_vs_reference.py (runs wherever /root/reference is mounted) and against the committed golden
+tests/test_oracle_golden_cpu.py (its live-reference cases run wherever /root/reference is mounted) and against the committed golden
 vectors in tests/golden/ (generated from the real reference by tests/golden/make_golden.py).
 
 Differences in *form* (not in arithmetic) from the reference: the shifted-window mask and the relative-position
