@@ -238,6 +238,9 @@ def run_b200(args):
 
     torch.manual_seed(0)
     model = SwinIR(**CFG2).to(dev).train()           # drop_path_rate: constructor default 0.1, as define_G leaves it
+    if args.precision == "fp32":
+        model.set_precision("fp32", args.terms)
+    plan_args = (BATCH_PER_GPU, PATCH, PATCH, True, args.precision, args.terms)
     net = model
     if world > 1:
         net = _wrap_dp(model, local_rank, args.ddp)
@@ -294,7 +297,7 @@ def run_b200(args):
         # profiling aid (never a bench value): replay ONE launch of every distinct kernel/shape group between
         # cudaProfilerStart/Stop so that `ncu --profile-from-start off --set full` captures ~30 launches, not 550
         import ctypes
-        plan = model.engine(dev).plan(BATCH_PER_GPU, PATCH, PATCH, True)
+        plan = model.engine(dev).plan(*plan_args)
         seen, pick = set(), []
         for l in list(plan.fwd) + list(plan.bwd):
             tag = profiling.describe(l, REAL_DIMS)[0]
@@ -325,13 +328,24 @@ def run_b200(args):
         e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
 
+    # host time per step: the CPU side of one step (Python + ctypes launch issue, no synchronisation inside) measured
+    # from a drained device, so it is not hidden behind -- nor inflated by -- queued GPU work
+    host_ms = []
+    for _ in range(5):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        step(low, high)
+        host_ms.append((time.perf_counter() - t0) * 1e3)
+    torch.cuda.synchronize()
+    host_ms_step = sorted(host_ms)[len(host_ms) // 2]
+
     patches = BATCH_PER_GPU * world
     ms_step = ms_total / args.steps
     value = patches / (ms_step * 1e-3)
     e2e_value = patches / (ms_e2e / args.steps * 1e-3)
 
     # ---- per-launch instrumented replay (rank 0): which kernel group dominates, and its achieved TFLOP/s
-    plan = model.engine(dev).plan(BATCH_PER_GPU, PATCH, PATCH, True)
+    plan = model.engine(dev).plan(*plan_args)
     launches = list(plan.fwd) + list(plan.bwd)
     n_pack = len(plan.Wt["pack"])
     roof, groups = None, None
@@ -377,12 +391,37 @@ def run_b200(args):
                "sample": "1 patch (1x128x128) per step, %d timed steps after 1 warm-up, fp32 oracle port of the "
                          "reference modules incl. Adam and update_E" % done}
 
+    # the inference half of BASELINE.json's metric ("... & DnCNN/SwinIR inference MPix/s") in the same process, about a
+    # second each: cfg1 (B=1 CUDA-graph replay, and B=64) and cfg3, each with value, e2e, dominant-kernel roofline
+    # fraction and its own CPU baseline (oracle port)
+    also = None
+    if rank == 0 and world == 1 and not args.no_also:
+        del plan, launches
+        also = {}
+        for key, wl, b_, st_ in (("cfg1", "cfg1", 1, 200), ("cfg1_b64", "cfg1", 64, 20), ("cfg3", "cfg3", 32, 10)):
+            sub = argparse.Namespace(**vars(args))
+            sub.workload, sub.batch, sub.steps, sub.warmup, sub.precision = wl, b_, st_, 3, "bf16"
+            sub.no_cpu_baseline = args.no_cpu_baseline or key == "cfg1_b64"
+            try:
+                l_ = run_b200_workload(sub, emit=False)
+                also[key] = {"metric": l_["metric"], "value": l_["value"], "unit": l_["unit"],
+                             "ms_per_step": l_["ms_per_step"], "steps": st_, "dtype": l_["dtype"],
+                             "workload": l_["config"]["workload"], "weights": l_["config"].get("weights"),
+                             "e2e": l_["e2e"], "gpu_launches": l_["gpu_launches"], "clocks": l_["clocks"],
+                             "roofline": {k: v for k, v in l_["roofline"].items() if k != "groups"},
+                             "cpu_baseline": l_["cpu_baseline"]}
+            except Exception as e:  # noqa: BLE001 -- the headline line must not be lost to a side measurement
+                also[key] = {"error": repr(e)}
+
     if rank == 0:
         line = {
             "metric": "SwinIR-M gray-DN train patches/s", "value": value, "unit": "patches/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "bf16x%d split operands, fp32 accumulate (fp32-accurate mode)" % args.terms,
+            "data": "synthetic", "host_ms_per_step": host_ms_step,
             "config": {"workload": WORKLOAD, "global_batch": patches, "parallelism": _dp_name(world, args.ddp),
+                       "precision": args.precision + (" (bf16 tensor-core operands, fp32 accumulate; 2e-2 contract)" if args.precision == "bf16" else " (split operands, terms=%d; 1e-4 / 1e-3 contract)" % args.terms),
                        "drop_path_rate": 0.1, "optimizer": "Adam lr 2e-4 + EMA 0.999 (update_E)", "loss": "Charbonnier eps 1e-9",
                        "step_tail": "torch" if args.torch_tail else "fused (kair_pixel_loss, kair_adam_ema)",
                        "l2": "per-step working set (~13 GB of activations) far exceeds the 126 MB L2; no flush needed"},
@@ -391,7 +430,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": (low_h.numel() + high_h.numel()) * 4 * world,
                     "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": (len(launches) + n_pack + (0 if args.torch_tail else 2)) * args.steps,
-            "roofline": roof, "cpu_baseline": cpu,
+            "roofline": roof, "cpu_baseline": cpu, "also": also,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -500,7 +539,7 @@ def run_reference_workload(args):
     }), flush=True)
 
 
-def run_b200_workload(args):
+def run_b200_workload(args, emit=True):
     import ctypes
     import torch
     import torch.distributed as dist
@@ -513,9 +552,12 @@ def run_b200_workload(args):
         raise RuntimeError("bench.py: no CUDA device; the sm_100a path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    if world > 1:
+    if world > 1 and emit:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+    prec = getattr(args, "precision", "bf16")
+    if prec == "fp32" and name not in ("cfg3", "cfg5"):
+        raise SystemExit("--precision fp32 covers the SwinIR workloads (cfg2, cfg3, cfg5)")
     batch = args.batch or DEFAULT_BATCH[name]
     torch.manual_seed(0)
     g = torch.Generator().manual_seed(1234 + rank)
@@ -548,10 +590,10 @@ def run_b200_workload(args):
         real_dims = {}
     elif name == "cfg3":
         from kair_b200.network_swinir import SwinIR
-        model = SwinIR(upsampler="pixelshuffle", **SWIN_SR).to(dev).eval()
+        model = SwinIR(upsampler="pixelshuffle", **SWIN_SR).to(dev).eval().set_precision(prec, args.terms)
         host = [torch.rand(batch, 3, 64, 64, generator=g).pin_memory()]
         units = batch * 64 * 64 / 1e6
-        plan_of = lambda: model.engine(dev).plan(batch, 64, 64, False)
+        plan_of = lambda: model.engine(dev).plan(batch, 64, 64, False, prec, args.terms)
         def step(x):
             with torch.no_grad():
                 return model(x)
@@ -588,7 +630,7 @@ def run_b200_workload(args):
         real_dims = {}
     elif name == "cfg5":
         from kair_b200.network_swinir import SwinIR
-        model = SwinIR(upsampler="nearest+conv", **SWIN_SR).to(dev).eval()
+        model = SwinIR(upsampler="nearest+conv", **SWIN_SR).to(dev).eval().set_precision(prec, args.terms)
         side = args.image or 2048
         img = tiling.pad_to_window(torch.rand(1, 3, side, side, generator=torch.Generator().manual_seed(1234)), 8)
         host = [img.pin_memory()]
@@ -596,7 +638,7 @@ def run_b200_workload(args):
         n_tiles = len(tiling.tile_origins(img.shape[2], img.shape[3], 256, 32))
         n_tiles_rank = len([i for i in range(n_tiles) if i % world == rank])
         extra_cfg = {"tiles": n_tiles, "tiles_on_rank0": n_tiles_rank, "padded": list(img.shape[2:])}
-        plan_of = lambda: model.engine(dev).plan(batch, 256, 256, False)
+        plan_of = lambda: model.engine(dev).plan(batch, 256, 256, False, prec, args.terms)
         def step(x):
             with torch.no_grad():
                 E, Wt, _ = tiling.tiled_partial(model, x, 256, 32, 4, 8, tile_batch=batch, rank=rank, world=world)
@@ -693,8 +735,10 @@ def run_b200_workload(args):
         line = {
             "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if name == "cfg5" else "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": dict({"workload": WORKLOADS[name] % batch, "parallelism": _dp_name(world, args.ddp) if name == "cfg4" else "replicas x%d, no collective" % world
+            "vs_baseline": None,
+            "dtype": "bf16" if prec == "bf16" else "bf16x%d split operands, fp32 accumulate (fp32-accurate mode)" % args.terms,
+            "data": "synthetic",
+            "config": dict({"workload": WORKLOADS[name] % batch, "precision": prec, "parallelism": _dp_name(world, args.ddp) if name == "cfg4" else "replicas x%d, no collective" % world
                             if name != "cfg5" else "tiles sharded over %d ranks, one reduce of the partial sums" % world,
                             "weights": weights,
                             "l2": "inputs/activations of a step exceed the 126 MB L2 except cfg1 at batch 1 "
@@ -705,9 +749,12 @@ def run_b200_workload(args):
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": n_launch * args.steps, "roofline": roof, "cpu_baseline": cpu,
         }
+        if not emit:
+            return line
         print(json.dumps(line), flush=True)
-    if world > 1:
+    if world > 1 and emit:
         dist.destroy_process_group()
+    return None
 
 
 def main():
@@ -729,6 +776,11 @@ def main():
                     "the fused kair_pixel_loss + kair_adam_ema tail")
     ap.add_argument("--ncu-slice", action="store_true", help="profiling aid: one launch per kernel group in a "
                     "cudaProfilerStart/Stop range")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"], help="bf16: tensor-core operands in bf16 "
+                    "(default, 2e-2 contract); fp32: the fp32-accurate split-operand mode (1e-4 / 1e-3 contract) of the "
+                    "SwinIR workloads")
+    ap.add_argument("--terms", type=int, default=3, choices=[3, 6], help="--precision fp32: component products per GEMM")
+    ap.add_argument("--no-also", action="store_true", help="cfg2: skip the cfg1 / cfg3 side measurements (`also`)")
     args = ap.parse_args()
     if args.workload != "cfg2":
         (run_reference_workload if args.impl == "reference" else run_b200_workload)(args)

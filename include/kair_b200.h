@@ -136,6 +136,9 @@ typedef struct kair_window_attn_args {
   float* dtable;     /* fp32 [(2*window-1)^2][num_heads], backward only, accumulated */
   int32_t batch, H, W;
   int32_t num_heads, window, shift;
+  /* fp32-accurate mode (SPLIT PRECISION below): qkv / out / dout / dqkv are fp32 arrays (same column layout and
+   * pitches in elements) and every window size runs on the CUDA-core fp32 kernel (expf, no bf16 rounding anywhere) */
+  int32_t fp32;
 } kair_window_attn_args;
 
 int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream);
@@ -164,6 +167,9 @@ typedef struct kair_pack_linear_args {
   void* WpT;                 /* bf16 [L][K_pad][N_pad] or NULL */
   float* bp;                 /* fp32 [L][N_pad] or NULL */
   int32_t L, N_pad, K_pad, out_f, in_f;
+  /* SPLIT PRECISION: terms = 0/1 packs plain bf16; terms = 3 / 6 packs the weight-side segments of a bf16 split,
+   * Wp [L][N_pad][terms*K_pad] and WpT [L][K_pad][terms*N_pad] (see kair_split_terms) */
+  int32_t terms;
 } kair_pack_linear_args;
 int kair_pack_linear(const kair_pack_linear_args* args, void* stream);
 
@@ -196,6 +202,9 @@ typedef struct kair_pack_conv_args {
    * basicblock.py:68-69; the arithmetic of utils/utils_bnorm.py:44-58): Wp = W * oscale[o], bp = b * oscale[o] + oshift[o] */
   const void* const* oscale; /* [L] -> fp32 (O) or NULL */
   const void* const* oshift; /* [L] -> fp32 (O) or NULL */
+  /* SPLIT PRECISION: terms = 3 / 6: Wp [L][O_pad][taps*terms*I_pad] with k = (tap*terms + seg)*I_pad + i and
+   * WpT [L][I_pad][taps*terms*O_pad] likewise (the activation carries terms*I_pad channels per pixel) */
+  int32_t terms;
 } kair_pack_conv_args;
 int kair_pack_conv(const kair_pack_conv_args* args, void* stream);
 
@@ -224,6 +233,8 @@ typedef struct kair_layernorm_args {
   int64_t T;
   int32_t C, pitch, ones_col;
   float eps;
+  /* SPLIT PRECISION: terms = 3 / 6: the bf16 outputs are split operands [T][terms*pitch] (kair_split_terms) */
+  int32_t terms;
 } kair_layernorm_args;
 int kair_layernorm_fwd(const kair_layernorm_args* args, void* stream);
 
@@ -289,10 +300,70 @@ typedef struct kair_conv_out_args {
    * multiplied by act'(u) = (mask > 0 ? 1 : mask_slope), mask = the saved bf16 feat */
   const void* mask;
   float mask_slope;
+  /* fp32-accurate mode: features as fp32 [T][pitch] instead of `feat` (forward and wgrad; CUDA-core fp32 kernels) */
+  const float* feat_f32;
 } kair_conv_out_args;
 int kair_conv_out_fwd(const kair_conv_out_args* args, void* stream);
 int kair_conv_out_dgrad(const kair_conv_out_args* args, void* stream);
 int kair_conv_out_wgrad(const kair_conv_out_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * SPLIT PRECISION -- the fp32-accurate mode (north_star: 1e-4 max-abs forward, 1e-3 relative gradients against the
+ * reference's fp32 arithmetic, models/network_swinir.py:114-145, 239-279).  The tensor cores only take bf16 (or
+ * narrower) operands, so an fp32 value x is carried as a sum of bf16 components c0 = bf16(x), c1 = bf16(x - c0),
+ * c2 = bf16(x - c0 - c1), and a product  X * W  becomes the sum of the significant component products, accumulated
+ * in fp32 (TMEM) by ONE ordinary kair_gemm_tn launch over a K axis that is `terms` times longer:
+ *     terms = 3:  activation segments [c0 | c1 | c0],            weight segments [C0 | C0 | C1]       (~2^-17)
+ *     terms = 6:  activation segments [c0 | c1 | c2 | c0 | c1 | c0], weight [C0 | C0 | C0 | C1 | C1 | C2] (~2^-24)
+ * kair_split_terms writes the activation side: fp32 rows -> bf16 rows of terms*n columns, optionally applying the
+ * element-wise stage that precedes the next GEMM in the reference (GELU network_swinir.py:26 and its derivative,
+ * LeakyReLU masks of the '3conv' / SR heads, DropPath row scales :204).  kair_pack_linear / kair_pack_conv with
+ * `terms` write the weight side.  Weight-gradient GEMMs (kair_gemm_nt) are launched once per component pair on
+ * column slices of the same buffers.
+ * ------------------------------------------------------------------------------------------------------------ */
+enum { KAIR_SPLIT_COPY = 0,      /* v = x                                   */
+       KAIR_SPLIT_GELU = 1,      /* v = gelu_erf(x)                         */
+       KAIR_SPLIT_DGELU = 2,     /* v = x * gelu_erf'(aux)                  */
+       KAIR_SPLIT_ACT_BWD = 3,   /* v = x * (aux > 0 ? 1 : slope)           */
+       KAIR_SPLIT_LRELU = 4      /* v = x > 0 ? x : x * slope               */ };
+typedef struct kair_split_args {
+  const float* x;        /* fp32 [T][x_pitch] */
+  int64_t x_pitch;
+  const float* aux;      /* fp32 [T][aux_pitch] or NULL */
+  int64_t aux_pitch;
+  void* out;             /* bf16 [T][out_pitch], out_pitch >= terms*n; segment s at columns [s*n, (s+1)*n) */
+  int64_t out_pitch;
+  float* out_f32;        /* optional fp32 copy of v, [T][out_f32_pitch] (may alias x) */
+  int64_t out_f32_pitch;
+  const float* row_scale;/* optional per-sample scale of v (DropPath), sample = row / rows_per_sample */
+  int64_t T;
+  int32_t n;             /* columns per segment (multiple of 8) */
+  int32_t terms;         /* 3 or 6 (1: a plain bf16 copy) */
+  int32_t op;            /* KAIR_SPLIT_* */
+  int32_t ones_col;      /* column of v forced to 1.0, or -1 */
+  int32_t rows_per_sample;
+  float slope;
+} kair_split_args;
+int kair_split_terms(const kair_split_args* args, void* stream);
+
+/* LayerNorm backward on split operands, fused with the residual gradient (the fp32-mode counterpart of
+ * KAIR_EPI_LNBWD; autograd of network_swinir.py:245, 277 with gamma / beta folded into the next linear layer):
+ *   dx = resid + rstd * (g - mean(g) - xhat * mean(g * xhat)),  xhat = the sum of the components stored in `xhat`
+ * outF = dx (fp32); out = split(dx * row_scale) for the next GEMMs (optional). */
+typedef struct kair_ln_bwd_split_args {
+  const float* g;        /* fp32 [T][pitch]: gradient w.r.t. the normalised activations */
+  const void* xhat;      /* bf16 split operand [T][xhat_pitch] written by kair_layernorm_fwd with the same terms */
+  int64_t xhat_pitch;
+  const float* rstd;     /* [T] */
+  const float* resid;    /* fp32 [T][pitch] or NULL */
+  float* outF;           /* fp32 [T][pitch] */
+  void* out;             /* bf16 split [T][out_pitch] or NULL */
+  int64_t out_pitch;
+  const float* row_scale;
+  int64_t T;
+  int32_t C, pitch, terms, rows_per_sample;
+} kair_ln_bwd_split_args;
+int kair_ln_bwd_split(const kair_ln_bwd_split_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Thin (<= 4 channel) convolutions expressed as GEMMs.  kair_im2col3x3 expands an NCHW fp32 image into a bf16 token
@@ -419,6 +490,8 @@ typedef struct kair_shuffle_args {
   const void* mask;        /* bf16, shaped like the backward output, or NULL */
   int64_t mask_pitch;
   float mask_slope;
+  /* fp32-accurate mode, forward entry points only: `in` / `out` hold fp32 elements (pitches in elements) */
+  int32_t fp32;
 } kair_shuffle_args;
 int kair_pixel_shuffle(const kair_shuffle_args* args, void* stream);
 int kair_upsample_nearest2(const kair_shuffle_args* args, void* stream);
@@ -437,6 +510,7 @@ typedef struct kair_shuffle_out_args {
   int64_t in_pitch;
   float scale;
   int32_t batch, H, W, co, r;
+  int32_t fp32;            /* kair_pixel_shuffle_out only: `in` holds fp32 elements (fp32-accurate mode) */
 } kair_shuffle_out_args;
 int kair_pixel_shuffle_out(const kair_shuffle_out_args* args, void* stream);
 /* adjoint of kair_pixel_shuffle_out: roles swap, `out` (the fp32 NCHW gradient of the image) is READ and `in`

@@ -41,6 +41,8 @@ int pixel_shuffle_out_bwd_launch(const kair_shuffle_out_args& a, cudaStream_t st
 int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
+int split_terms_launch(const kair_split_args& a, cudaStream_t st);
+int ln_bwd_split_launch(const kair_ln_bwd_split_args& a, cudaStream_t st);
 }
 
 extern "C" {
@@ -71,7 +73,7 @@ int kair_window_attn_fwd(const kair_window_attn_args* args, void* stream) {
     return -1;
   }
   // 8x8 windows: tcgen05 / TMEM kernel; smaller windows (7x7 JPEG models): CUDA-core kernel of attn_small.cu
-  if (args->window != 8) return kb::window_attn_small_fwd_launch(*args, (cudaStream_t)stream);
+  if (args->window != 8 || args->fp32) return kb::window_attn_small_fwd_launch(*args, (cudaStream_t)stream);
   return kb::window_attn_fwd_launch(*args, (cudaStream_t)stream);
 }
 
@@ -80,7 +82,7 @@ int kair_window_attn_bwd(const kair_window_attn_args* args, void* stream) {
     kb::set_error("kair_window_attn_bwd: null args");
     return -1;
   }
-  if (args->window != 8) return kb::window_attn_small_bwd_launch(*args, (cudaStream_t)stream);
+  if (args->window != 8 || args->fp32) return kb::window_attn_small_bwd_launch(*args, (cudaStream_t)stream);
   return kb::window_attn_bwd_launch(*args, (cudaStream_t)stream);
 }
 
@@ -122,6 +124,8 @@ KB_WRAP(kair_adam_ema, kair_adam_ema_args, adam_ema_launch)
 KB_WRAP(kair_pixel_shuffle_out_bwd, kair_shuffle_out_args, pixel_shuffle_out_bwd_launch)
 KB_WRAP(kair_pixel_shuffle_bwd, kair_shuffle_args, pixel_shuffle_bwd_launch)
 KB_WRAP(kair_upsample_nearest2_bwd, kair_shuffle_args, upsample_nearest2_bwd_launch)
+KB_WRAP(kair_split_terms, kair_split_args, split_terms_launch)
+KB_WRAP(kair_ln_bwd_split, kair_ln_bwd_split_args, ln_bwd_split_launch)
 #undef KB_WRAP
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {

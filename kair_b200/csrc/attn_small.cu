@@ -63,6 +63,26 @@ __device__ __forceinline__ void store_row32(bf16* p, const float (&f)[AS_HD]) {
   }
 }
 
+__device__ __forceinline__ void load_row32(const float* p, float (&f)[AS_HD]) {
+  const float4* v = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float4 u = __ldg(v + k);
+    f[4 * k] = u.x; f[4 * k + 1] = u.y; f[4 * k + 2] = u.z; f[4 * k + 3] = u.w;
+  }
+}
+
+__device__ __forceinline__ void store_row32(float* p, const float (&f)[AS_HD]) {
+  float4* v = reinterpret_cast<float4*>(p);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+}
+
+// fp32-accurate mode uses expf (<= 2 ulp); the bf16 path keeps the MUFU approximation
+template <typename IO> __device__ __forceinline__ float exp_io(float x);
+template <> __device__ __forceinline__ float exp_io<bf16>(float x) { return __expf(x); }
+template <> __device__ __forceinline__ float exp_io<float>(float x) { return expf(x); }
+
 __device__ __forceinline__ float dot32(const float (&a)[AS_HD], const float* b) {
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
@@ -80,6 +100,7 @@ __device__ __forceinline__ int rel_index(int i, int j, int ws) {
 }
 
 // ------------------------------------------------------------------------------------------------ forward
+template <typename IO>   // bf16 (window 2..7 of the bf16 mode) or float (every window of the fp32-accurate mode)
 __global__ void __launch_bounds__(AS_MAXN) attn_small_fwd_kernel(const kair_window_attn_args a, const SmallGeom g) {
   __shared__ float Ks[AS_MAXN][AS_HD];
   __shared__ float Vs[AS_MAXN][AS_HD];
@@ -90,7 +111,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_fwd_kernel(const kair_wind
   const int wj = win % g.nWw, wi = (win / g.nWw) % g.nWh, b = win / (g.nWw * g.nWh);
   const int i = threadIdx.x;
   const bool live = i < g.N;
-  const bf16* qkv = reinterpret_cast<const bf16*>(a.qkv);
+  const IO* qkv = reinterpret_cast<const IO*>(a.qkv);
   const int HP = g.nH * AS_HD;
 
   for (int e = i; e < g.tsz; e += AS_MAXN) tab[e] = __ldg(a.table + (long long)e * g.nH + head);
@@ -99,7 +120,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_fwd_kernel(const kair_wind
   long long tok = 0;
   if (live) {
     tok = token_of(g, b, wi, wj, i, rid);
-    const bf16* row = qkv + tok * a.qkv_pitch + head * AS_HD;
+    const IO* row = qkv + tok * a.qkv_pitch + head * AS_HD;
     float t[AS_HD];
     load_row32(row, q);
     load_row32(row + HP, t);
@@ -122,7 +143,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_fwd_kernel(const kair_wind
     float s = dot32(q, Ks[j]) + tab[rel_index(i, j, g.ws)];
     if (rids[j] != rid) s -= 100.0f;
     const float mn = fmaxf(m, s);
-    const float corr = __expf(m - mn), p = __expf(s - mn);
+    const float corr = exp_io<IO>(m - mn), p = exp_io<IO>(s - mn);
     l = l * corr + p;
 #pragma unroll
     for (int d = 0; d < AS_HD; ++d) o[d] = fmaf(o[d], corr, p * Vs[j][d]);
@@ -131,13 +152,14 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_fwd_kernel(const kair_wind
   const float inv = 1.0f / l;
 #pragma unroll
   for (int d = 0; d < AS_HD; ++d) o[d] *= inv;
-  store_row32(reinterpret_cast<bf16*>(a.out) + tok * a.out_pitch + head * AS_HD, o);
+  store_row32(reinterpret_cast<IO*>(a.out) + tok * a.out_pitch + head * AS_HD, o);
 }
 
 // ------------------------------------------------------------------------------------------------ backward
 // phase 1 (thread = query i): P_ij, dP_ij = dO_i . V_j, delta_i, dS_ij = P_ij (dP_ij - delta_i), dQ_i = sum_j dS_ij K_j;
 //                             P and dS are stored transposed ([j][i]) and d(table) is accumulated in shared memory
 // phase 2 (thread = key j):   dK_j = sum_i dS_ij Q_i,  dV_j = sum_i P_ij dO_i
+template <typename IO>
 __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_window_attn_args a, const SmallGeom g) {
   extern __shared__ float sm[];
   float* Qs = sm;                          // [64][32]
@@ -154,7 +176,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
   const int wj = win % g.nWw, wi = (win / g.nWw) % g.nWh, b = win / (g.nWw * g.nWh);
   const int i = threadIdx.x;
   const bool live = i < g.N;
-  const bf16* qkv = reinterpret_cast<const bf16*>(a.qkv);
+  const IO* qkv = reinterpret_cast<const IO*>(a.qkv);
   const int HP = g.nH * AS_HD;
 
   for (int e = i; e < g.tsz; e += AS_MAXN) {
@@ -166,7 +188,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
   long long tok = 0;
   if (live) {
     tok = token_of(g, b, wi, wj, i, rid);
-    const bf16* row = qkv + tok * a.qkv_pitch + head * AS_HD;
+    const IO* row = qkv + tok * a.qkv_pitch + head * AS_HD;
     float t[AS_HD];
     load_row32(row, q);
 #pragma unroll
@@ -177,7 +199,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
     load_row32(row + 2 * HP, t);
 #pragma unroll
     for (int d = 0; d < AS_HD; ++d) Vs[i * AS_HD + d] = t[d];
-    load_row32(reinterpret_cast<const bf16*>(a.dout) + tok * a.dout_pitch + head * AS_HD, go);
+    load_row32(reinterpret_cast<const IO*>(a.dout) + tok * a.dout_pitch + head * AS_HD, go);
 #pragma unroll
     for (int d = 0; d < AS_HD; ++d) Gs[i * AS_HD + d] = go[d];
     rids[i] = rid;
@@ -194,7 +216,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
     }
     float l = 0.f;
     for (int j = 0; j < g.N; ++j) {
-      const float p = __expf(Pt[j * AS_PS + i] - m);
+      const float p = exp_io<IO>(Pt[j * AS_PS + i] - m);
       Pt[j * AS_PS + i] = p;
       l += p;
     }
@@ -218,7 +240,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
 #pragma unroll
       for (int d = 0; d < AS_HD; ++d) dq[d] = fmaf(ds, kj[d], dq[d]);
     }
-    store_row32(reinterpret_cast<bf16*>(a.dqkv) + tok * a.dqkv_pitch + head * AS_HD, dq);
+    store_row32(reinterpret_cast<IO*>(a.dqkv) + tok * a.dqkv_pitch + head * AS_HD, dq);
   }
   __syncthreads();
 
@@ -237,7 +259,7 @@ __global__ void __launch_bounds__(AS_MAXN) attn_small_bwd_kernel(const kair_wind
         dv[d] = fmaf(p, gr[d], dv[d]);
       }
     }
-    bf16* drow = reinterpret_cast<bf16*>(a.dqkv) + tok * a.dqkv_pitch + head * AS_HD;
+    IO* drow = reinterpret_cast<IO*>(a.dqkv) + tok * a.dqkv_pitch + head * AS_HD;
     store_row32(drow + HP, dk);
     store_row32(drow + 2 * HP, dv);
   }
@@ -266,7 +288,8 @@ int window_attn_small_fwd_launch(const kair_window_attn_args& a, cudaStream_t st
   KB_CHECK(a.out_pitch % 8 == 0 && a.out_pitch >= a.num_heads * AS_HD, "kair_window_attn_fwd: bad out pitch");
   const long long blocks = (long long)a.batch * g.nWh * g.nWw * g.nH;
   KB_CHECK(blocks < (1ll << 31), "kair_window_attn_fwd: too many windows");
-  attn_small_fwd_kernel<<<(unsigned)blocks, AS_MAXN, 0, st>>>(a, g);
+  if (a.fp32) attn_small_fwd_kernel<float><<<(unsigned)blocks, AS_MAXN, 0, st>>>(a, g);
+  else attn_small_fwd_kernel<bf16><<<(unsigned)blocks, AS_MAXN, 0, st>>>(a, g);
   KB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -284,10 +307,12 @@ int window_attn_small_bwd_launch(const kair_window_attn_args& a, cudaStream_t st
   int dev = 0;
   KB_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    KB_CUDA(cudaFuncSetAttribute(attn_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KB_CUDA(cudaFuncSetAttribute(attn_small_bwd_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KB_CUDA(cudaFuncSetAttribute(attn_small_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set[dev & 63] = true;
   }
-  attn_small_bwd_kernel<<<(unsigned)blocks, AS_MAXN, smem, st>>>(a, g);
+  if (a.fp32) attn_small_bwd_kernel<float><<<(unsigned)blocks, AS_MAXN, smem, st>>>(a, g);
+  else attn_small_bwd_kernel<bf16><<<(unsigned)blocks, AS_MAXN, smem, st>>>(a, g);
   KB_CUDA(cudaGetLastError());
   return 0;
 }

@@ -257,6 +257,25 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
   const float e = ex2_approx(-0.72134752044448f * x * x);
   return fmaf(x * 0.3989422804014327f, e, gauss_cdf_from(x, e));
 }
+// SPLIT PRECISION (include/kair_b200.h): bf16 components of an fp32 value and the segment orders of the two operand
+// sides.  Component products c_i * C_j with i + j <= 1 (terms 3) / <= 2 (terms 6) are kept.
+__device__ __forceinline__ void split_components(float x, float& c0, float& c1, float& c2) {
+  c0 = __bfloat162float(__float2bfloat16(x));
+  const float r1 = x - c0;
+  c1 = __bfloat162float(__float2bfloat16(r1));
+  c2 = __bfloat162float(__float2bfloat16(r1 - c1));
+}
+__host__ __device__ constexpr int split_seg_act(int terms, int s) {
+  return terms == 3 ? (s == 1 ? 1 : 0) : (terms == 6 ? (s < 3 ? s : (s < 5 ? s - 3 : 0)) : 0);
+}
+__host__ __device__ constexpr int split_seg_w(int terms, int s) {
+  return terms == 3 ? (s == 2 ? 1 : 0) : (terms == 6 ? (s < 3 ? 0 : (s < 5 ? 1 : 2)) : 0);
+}
+__device__ __forceinline__ float split_pick(float x, int which) {
+  float c0, c1, c2;
+  split_components(x, c0, c1, c2);
+  return which == 0 ? c0 : (which == 1 ? c1 : c2);
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

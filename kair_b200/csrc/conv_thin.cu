@@ -178,6 +178,7 @@ __global__ void __launch_bounds__(256) conv_out_fwd_mma_kernel(const ConvOutTile
 }  // namespace
 
 int conv_out_fwd_launch(const kair_conv_out_args& a, cudaStream_t st) {
+  if (a.feat_f32) return conv_out_fwd_simt_launch(a, st);   // fp32-accurate mode: CUDA-core fp32 kernel
   KB_CHECK(a.feat && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
   KB_CHECK(a.co >= 1 && a.co <= 4, "kair_conv_out_fwd: co=%d unsupported (max 4)", a.co);
   KB_CHECK(a.pitch % 8 == 0 && a.C <= a.pitch, "kair_conv_out_fwd: pitch must be a multiple of 8 channels, >= C");

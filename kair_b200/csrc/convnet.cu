@@ -414,10 +414,11 @@ int bn_fold_launch(const kair_bn_args& a, cudaStream_t st) {
 
 // ------------------------------------------------------------------------------------------------ SR heads
 // PixelShuffle(r): out[(b, r*h+dy, r*w+dx)][c] = in[(b,h,w)][c*r*r + dy*r + dx]; one thread per output channel pair.
+template <typename E, typename E2>   // (bf16, __nv_bfloat162) or (float, float2)
 __global__ void pixel_shuffle_kernel(const kair_shuffle_args a) {
   const int r = a.r, Ho = a.H * r, Wo = a.W * r, rr = r * r;
-  const bf16* in = reinterpret_cast<const bf16*>(a.in);
-  bf16* out = reinterpret_cast<bf16*>(a.out);
+  const E* in = reinterpret_cast<const E*>(a.in);
+  E* out = reinterpret_cast<E*>(a.out);
   const int pc = a.C >> 1;
   const long long n = (long long)a.batch * Ho * Wo * pc;
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
@@ -427,10 +428,10 @@ __global__ void pixel_shuffle_kernel(const kair_shuffle_args a) {
     const long long b = to / ((long long)Wo * Ho);
     const long long ti = (b * a.H + ho / r) * a.W + wo / r;
     const int sub = (ho % r) * r + (wo % r);
-    __nv_bfloat162 v;
+    E2 v;
     v.x = in[ti * a.in_pitch + (long long)c * rr + sub];
     v.y = in[ti * a.in_pitch + (long long)(c + 1) * rr + sub];
-    *reinterpret_cast<__nv_bfloat162*>(out + to * a.out_pitch + c) = v;
+    *reinterpret_cast<E2*>(out + to * a.out_pitch + c) = v;
   }
 }
 
@@ -485,7 +486,8 @@ __global__ void pixel_shuffle_out_kernel(const kair_shuffle_out_args a) {
     const int c = (int)((e / ((long long)Wo * Ho)) % a.co);
     const long long b = e / ((long long)Wo * Ho * a.co);
     const long long ti = (b * a.H + ho / r) * a.W + wo / r;
-    const float v = __bfloat162float(in[ti * a.in_pitch + (long long)c * rr + (ho % r) * r + (wo % r)]);
+    const long long ii = ti * a.in_pitch + (long long)c * rr + (ho % r) * r + (wo % r);
+    const float v = a.fp32 ? reinterpret_cast<const float*>(a.in)[ii] : __bfloat162float(in[ii]);
     a.out[e] = v * a.scale + a.mean[c];
   }
 }
@@ -652,6 +654,11 @@ int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st) {
                a.out_pitch >= a.C,
            "kair_pixel_shuffle: bad geometry (r=%d, C=%d)", a.r, a.C);
   const long long n = (long long)a.batch * a.H * a.W * a.r * a.r * (a.C >> 1);
+  if (a.fp32) {
+    pixel_shuffle_kernel<float, float2><<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+    KB_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (a.r == 2 && a.in_pitch % 8 == 0) {
     const long long n2 = n >> 2;   // 16-byte input chunks
     const int grid = grid_for(n2, 256, 16);
@@ -660,12 +667,18 @@ int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st) {
     KB_CUDA(cudaGetLastError());
     return 0;
   }
-  pixel_shuffle_kernel<<<grid_for(n, 256, 16), 256, 0, st>>>(a);
+  pixel_shuffle_kernel<bf16, __nv_bfloat162><<<grid_for(n, 256, 16), 256, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
 }
 
-int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st) {
+int upsample_nearest2_launch(const kair_shuffle_args& a0, cudaStream_t st) {
+  kair_shuffle_args a = a0;
+  if (a.fp32) {   // a pure 16-byte mover: fp32 rows are twice as many 2-byte elements
+    a.C *= 2;
+    a.in_pitch *= 2;
+    a.out_pitch *= 2;
+  }
   KB_CHECK(a.in && a.out && a.batch > 0 && a.H > 0 && a.W > 0, "kair_upsample_nearest2: null pointer / empty");
   KB_CHECK(a.C % 8 == 0 && a.in_pitch % 8 == 0 && a.out_pitch % 8 == 0 && a.in_pitch >= a.C && a.out_pitch >= a.C,
            "kair_upsample_nearest2: C and pitches must be multiples of 8");

@@ -23,8 +23,9 @@ __global__ void pack_linear_kernel(const kair_pack_linear_args a) {
   const float* beta = a.beta ? reinterpret_cast<const float*>(a.beta[l]) : nullptr;
   const int src = a.row_map[r];
   const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
-  bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + ((size_t)l * a.N_pad + r) * a.K_pad;
-  bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * a.K_pad * a.N_pad : nullptr;
+  const int terms = a.terms > 1 ? a.terms : 1;   // SPLIT PRECISION: weight-side segments along K (Wp) / N (WpT)
+  bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + ((size_t)l * a.N_pad + r) * a.K_pad * terms;
+  bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * a.K_pad * a.N_pad * terms : nullptr;
   float bacc = 0.f;
   for (int c = threadIdx.x; c < a.K_pad; c += blockDim.x) {
     const int k = a.col_map[c];
@@ -34,8 +35,16 @@ __global__ void pack_linear_kernel(const kair_pack_linear_args a) {
       v = w * rs * (gamma ? gamma[k] : 1.0f);
       if (beta) bacc += w * beta[k];
     }
-    Wp[c] = __float2bfloat16(v);
-    if (WpT) WpT[(size_t)c * a.N_pad + r] = __float2bfloat16(v);
+    if (terms == 1) {
+      Wp[c] = __float2bfloat16(v);
+      if (WpT) WpT[(size_t)c * a.N_pad + r] = __float2bfloat16(v);
+    } else {
+      for (int sg = 0; sg < terms; ++sg) {
+        const bf16 comp = __float2bfloat16(split_pick(v, split_seg_w(terms, sg)));
+        Wp[(size_t)sg * a.K_pad + c] = comp;
+        if (WpT) WpT[((size_t)c * terms + sg) * a.N_pad + r] = comp;
+      }
+    }
   }
   if (a.bp) {
     __shared__ float red[32];
@@ -56,6 +65,7 @@ __global__ void pack_linear_kernel(const kair_pack_linear_args a) {
 int pack_linear_launch(const kair_pack_linear_args& a, cudaStream_t st) {
   KB_CHECK(a.W && a.row_map && a.col_map && a.Wp, "kair_pack_linear: null pointer");
   KB_CHECK(a.L > 0 && a.N_pad > 0 && a.K_pad > 0, "kair_pack_linear: bad sizes");
+  KB_CHECK(a.terms == 0 || a.terms == 1 || a.terms == 3 || a.terms == 6, "kair_pack_linear: terms=%d", a.terms);
   pack_linear_kernel<<<dim3(a.N_pad, a.L), 128, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
@@ -143,7 +153,8 @@ __global__ void __launch_bounds__(256) pack_conv_kernel(const kair_pack_conv_arg
   const int l = blockIdx.z;
   const float* W = reinterpret_cast<const float*>(a.W[l]);
   const int taps = TAPS ? TAPS : a.taps;
-  const size_t n = (size_t)a.O_pad * taps * a.I_pad;
+  const int terms = a.terms > 1 ? a.terms : 1;   // SPLIT PRECISION: weight-side segments inside every tap
+  const size_t n = (size_t)a.O_pad * taps * a.I_pad * terms;
   bf16* Wp = reinterpret_cast<bf16*>(a.Wp) + (size_t)l * n;
   bf16* WpT = a.WpT ? reinterpret_cast<bf16*>(a.WpT) + (size_t)l * n : nullptr;
   const float* osc = a.oscale ? reinterpret_cast<const float*>(a.oscale[l]) : nullptr;
@@ -161,14 +172,30 @@ __global__ void __launch_bounds__(256) pack_conv_kernel(const kair_pack_conv_arg
   for (int idx = threadIdx.x; idx < PC_T * run; idx += blockDim.x) {
     const int il = idx % PC_T, tap = (idx / PC_T) % taps, ol = idx / (PC_T * taps);
     const int o = o0 + ol, i = i0 + il;
-    if (o < a.O_pad && i < a.I_pad) Wp[((size_t)o * taps + tap) * a.I_pad + i] = __float2bfloat16(tile[ol][il * taps + tap]);
+    if (o < a.O_pad && i < a.I_pad) {
+      const float v = tile[ol][il * taps + tap];
+      if (terms == 1) {
+        Wp[((size_t)o * taps + tap) * a.I_pad + i] = __float2bfloat16(v);
+      } else {
+        for (int sg = 0; sg < terms; ++sg)
+          Wp[(((size_t)o * taps + tap) * terms + sg) * a.I_pad + i] = __float2bfloat16(split_pick(v, split_seg_w(terms, sg)));
+      }
+    }
   }
   if (WpT) {
     for (int idx = threadIdx.x; idx < PC_T * run; idx += blockDim.x) {
       const int ol = idx % PC_T, tap = (idx / PC_T) % taps, il = idx / (PC_T * taps);
       const int o = o0 + ol, i = i0 + il;
-      if (o < a.O_pad && i < a.I_pad)
-        WpT[((size_t)i * taps + (taps - 1 - tap)) * a.O_pad + o] = __float2bfloat16(tile[ol][il * taps + tap]);
+      if (o < a.O_pad && i < a.I_pad) {
+        const float v = tile[ol][il * taps + tap];
+        if (terms == 1) {
+          WpT[((size_t)i * taps + (taps - 1 - tap)) * a.O_pad + o] = __float2bfloat16(v);
+        } else {
+          for (int sg = 0; sg < terms; ++sg)
+            WpT[(((size_t)i * taps + (taps - 1 - tap)) * terms + sg) * a.O_pad + o] =
+                __float2bfloat16(split_pick(v, split_seg_w(terms, sg)));
+        }
+      }
     }
   }
   if (a.bp && blockIdx.x == 0 && blockIdx.y == 0) {
@@ -185,6 +212,7 @@ int pack_conv_launch(const kair_pack_conv_args& a, cudaStream_t st) {
   KB_CHECK(a.W && a.Wp, "kair_pack_conv: null pointer");
   KB_CHECK(a.taps >= 1 && a.taps <= PC_MAXTAPS, "kair_pack_conv: taps=%d must be in 1..%d", a.taps, PC_MAXTAPS);
   KB_CHECK(a.L >= 1 && a.L <= 65535, "kair_pack_conv: L=%d layers per launch", a.L);
+  KB_CHECK(a.terms == 0 || a.terms == 1 || a.terms == 3 || a.terms == 6, "kair_pack_conv: terms=%d", a.terms);
   dim3 grid((a.I_pad + PC_T - 1) / PC_T, (a.O_pad + PC_T - 1) / PC_T, a.L);
   if (a.taps == 9) pack_conv_kernel<9><<<grid, 256, 0, st>>>(a);
   else if (a.taps == 4) pack_conv_kernel<4><<<grid, 256, 0, st>>>(a);
@@ -266,8 +294,21 @@ __global__ void layernorm_fwd_kernel(const kair_layernorm_args a) {
     const int c = lane + 32 * i;
     if (c >= a.pitch) continue;
     const float xh = (c < a.C) ? (v[i] - mean) * rstd : 0.f;
-    const float y = (c < a.C) ? xh * a.gamma[c] + a.beta[c] : 0.f;
+    const float y = (c < a.C && a.gamma) ? xh * a.gamma[c] + a.beta[c] : 0.f;
     if (a.y_f32) a.y_f32[row * a.pitch + c] = y;
+    if (a.terms > 1) {   // SPLIT PRECISION: bf16 outputs are split operands [T][terms*pitch]
+      const size_t base = (size_t)row * a.pitch * a.terms + c;
+      for (int sg = 0; sg < a.terms; ++sg) {
+        const int w = split_seg_act(a.terms, sg);
+        if (a.y_bf16)
+          reinterpret_cast<bf16*>(a.y_bf16)[base + (size_t)sg * a.pitch] =
+              __float2bfloat16(split_pick(c == a.ones_col ? 1.0f : y, w));
+        if (a.xhat_bf16)
+          reinterpret_cast<bf16*>(a.xhat_bf16)[base + (size_t)sg * a.pitch] =
+              __float2bfloat16(split_pick(c == a.ones_col ? 1.0f : xh, w));
+      }
+      continue;
+    }
     if (a.y_bf16) reinterpret_cast<bf16*>(a.y_bf16)[row * a.pitch + c] = __float2bfloat16(c == a.ones_col ? 1.0f : y);
     if (a.xhat_bf16)
       reinterpret_cast<bf16*>(a.xhat_bf16)[row * a.pitch + c] = __float2bfloat16(c == a.ones_col ? 1.0f : xh);
@@ -277,6 +318,7 @@ __global__ void layernorm_fwd_kernel(const kair_layernorm_args a) {
 int layernorm_fwd_launch(const kair_layernorm_args& a, cudaStream_t st) {
   KB_CHECK(a.x && a.T > 0 && a.C > 0 && a.pitch >= a.C && a.pitch <= 256, "kair_layernorm_fwd: bad arguments");
   KB_CHECK((a.y_f32 == nullptr && a.y_bf16 == nullptr) || (a.gamma && a.beta), "kair_layernorm_fwd: affine output needs gamma/beta");
+  KB_CHECK(a.terms == 0 || a.terms == 1 || a.terms == 3 || a.terms == 6, "kair_layernorm_fwd: terms=%d", a.terms);
   const int warps = 8;
   layernorm_fwd_kernel<<<(unsigned)((a.T + warps - 1) / warps), warps * 32, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
@@ -559,6 +601,7 @@ int conv_in_wgrad_launch(const kair_conv_in_args& a, cudaStream_t st) {
 // j, j+8, ...; the 9 tap rows of a pixel are fetched with independent 16-byte loads issued before any arithmetic
 // (memory-level parallelism instead of one dependent load chain per warp), partial sums meet in 3 shuffle steps.
 //   out[c][p] = (b[c] + sum_{tap,k} W[c][k][tap] * feat[p+tap][k] + skip_scale * skip[c][p]) * out_scale + out_mean[c]
+template <bool kF32>   // kF32: fp32 features (a.feat_f32), 8 channels = two 16-byte loads
 __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
   extern __shared__ float sw[];  // [co][9][C_pad]
   const int Cp = a.pitch;
@@ -582,23 +625,38 @@ __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
 #pragma unroll
     for (int c = 0; c < CI_MAX; ++c) acc[c] = 0.f;
     for (int ch = sub; ch < chunks; ch += 8) {
-      uint4 v[9];
+      uint4 v[9], v2[9];
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
         v[tap] = make_uint4(0u, 0u, 0u, 0u);
-        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd)
-          v[tap] = __ldg(reinterpret_cast<const uint4*>(feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp + ch * 8));
+        v2[tap] = make_uint4(0u, 0u, 0u, 0u);
+        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+          const size_t off = (((size_t)b * a.H + hh) * a.Wd + ww) * Cp + ch * 8;
+          if (kF32) {
+            v[tap] = __ldg(reinterpret_cast<const uint4*>(a.feat_f32 + off));
+            v2[tap] = __ldg(reinterpret_cast<const uint4*>(a.feat_f32 + off + 4));
+          } else {
+            v[tap] = __ldg(reinterpret_cast<const uint4*>(feat + off));
+          }
+        }
       }
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
         const uint32_t wd[4] = {v[tap].x, v[tap].y, v[tap].z, v[tap].w};
         float f[8];
+        if (kF32) {
+          f[0] = __uint_as_float(v[tap].x); f[1] = __uint_as_float(v[tap].y);
+          f[2] = __uint_as_float(v[tap].z); f[3] = __uint_as_float(v[tap].w);
+          f[4] = __uint_as_float(v2[tap].x); f[5] = __uint_as_float(v2[tap].y);
+          f[6] = __uint_as_float(v2[tap].z); f[7] = __uint_as_float(v2[tap].w);
+        } else {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wd[i]));
-          f[2 * i] = f2.x;
-          f[2 * i + 1] = f2.y;
+          for (int i = 0; i < 4; ++i) {
+            const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wd[i]));
+            f[2 * i] = f2.x;
+            f[2 * i + 1] = f2.y;
+          }
         }
 #pragma unroll
         for (int c = 0; c < CI_MAX; ++c) {
@@ -630,7 +688,7 @@ __global__ void conv_out_fwd_kernel(const kair_conv_out_args a) {
 
 // fallback of conv_thin.cu's tensor-core kernel (C > 192 or feature rows shorter than the k-padding)
 int conv_out_fwd_simt_launch(const kair_conv_out_args& a, cudaStream_t st) {
-  KB_CHECK(a.feat && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
+  KB_CHECK((a.feat || a.feat_f32) && a.W && a.out && a.out_mean, "kair_conv_out_fwd: null pointer");
   KB_CHECK(a.co >= 1 && a.co <= CI_MAX, "kair_conv_out_fwd: co=%d unsupported (max %d)", a.co, CI_MAX);
   KB_CHECK(a.pitch % 8 == 0 && a.C <= a.pitch, "kair_conv_out_fwd: pitch must be a multiple of 8 channels, >= C");
   size_t smem = (size_t)a.co * 9 * a.pitch * 4;
@@ -639,14 +697,16 @@ int conv_out_fwd_simt_launch(const kair_conv_out_args& a, cudaStream_t st) {
   int dev = 0;
   KB_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    KB_CUDA(cudaFuncSetAttribute(conv_out_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
     attr_set[dev & 63] = true;
   }
   const long long groups = ((long long)a.batch * a.H * a.Wd + 3) / 4;
   long long blocks = (groups + 7) / 8;
   const long long cap = (long long)sm_count() * (smem > 32 * 1024 ? 2 : 6);
   if (blocks > cap) blocks = cap;
-  conv_out_fwd_kernel<<<(int)blocks, 256, smem, st>>>(a);
+  if (a.feat_f32) conv_out_fwd_kernel<true><<<(int)blocks, 256, smem, st>>>(a);
+  else conv_out_fwd_kernel<false><<<(int)blocks, 256, smem, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -731,12 +791,15 @@ __global__ void conv_out_wgrad_kernel(const kair_conv_out_args a) {
       for (int tap = 0; tap < 9; ++tap) {
         const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
         if (hh < 0 || hh >= a.H || ww < 0 || ww >= a.Wd) continue;
-        const bf16* row = feat + (((size_t)b * a.H + hh) * a.Wd + ww) * Cp;
+        const size_t roff = (((size_t)b * a.H + hh) * a.Wd + ww) * Cp;
+        const bf16* row = feat + roff;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int k = lane * 2 + 64 * j;
           if (k < a.C) {
-            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + k));
+            const float2 f = a.feat_f32
+                                 ? *reinterpret_cast<const float2*>(a.feat_f32 + roff + k)
+                                 : __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + k));
             acc[tap][2 * j] += d * f.x;
             acc[tap][2 * j + 1] += d * f.y;
           }
@@ -761,7 +824,7 @@ __global__ void conv_out_wgrad_kernel(const kair_conv_out_args a) {
 }
 
 int conv_out_wgrad_launch(const kair_conv_out_args& a, cudaStream_t st) {
-  KB_CHECK(a.dout && a.feat && a.dW, "kair_conv_out_wgrad: null pointer");
+  KB_CHECK(a.dout && (a.feat || a.feat_f32) && a.dW, "kair_conv_out_wgrad: null pointer");
   KB_CHECK(a.C <= 256, "kair_conv_out_wgrad: C=%d unsupported (max 256)", a.C);
   conv_out_wgrad_kernel<<<sm_count(), 256, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());

@@ -242,6 +242,7 @@ class SwinIR(nn.Module):
         self._drop_rates = dpr
         self._engine = None
         self._engine_key = None
+        self._precision, self._terms = "bf16", 3
         self._ops = None   # test hook: tests/emu_ops.py replays the launch lists on CPU (host-logic / DDP tests)
 
     def _init_weights(self, m):
@@ -268,6 +269,16 @@ class SwinIR(nn.Module):
         return F.pad(x, (0, pw, 0, ph), 'reflect') if (ph or pw) else x
 
     # ---------------------------------------------------------------------------------------------- engine
+    def set_precision(self, precision, terms=3):
+        """'bf16' (default): bf16 tensor-core operands, fp32 accumulation -- north_star's 2e-2 max-abs / 0.02 dB mode.
+        'fp32': the fp32-accurate mode (1e-4 max-abs forward, 1e-3 relative gradients): every operand is split into
+        `terms` = 3 (two bf16 components, ~2^-17) or 6 (three components, ~2^-24) tensor-core products accumulated in
+        fp32 (kair_b200/swinir_engine_fp32.py).  Not part of the reference's constructor; state_dict is unaffected."""
+        if precision not in ("bf16", "fp32") or terms not in (3, 6):
+            raise ValueError("precision must be 'bf16' or 'fp32' and terms 3 or 6")
+        self._precision, self._terms = precision, terms
+        return self
+
     def engine(self, device):
         """The kernel engine bound to the current parameter storage (rebuilt if parameters were re-allocated)."""
         params = dict(self.named_parameters())
@@ -288,7 +299,7 @@ class SwinIR(nn.Module):
         eng = self.engine(x.device)
         params = list(eng.P.values())
         train = torch.is_grad_enabled() and any(p.requires_grad for p in params)
-        plan = eng.plan(x.shape[0], x.shape[2], x.shape[3], train)
+        plan = eng.plan(x.shape[0], x.shape[2], x.shape[3], train, self._precision, self._terms)
         if train:
             plan.set_drop_path(self._drop_rates if self.training else [0.0] * len(self._drop_rates))
             out = SwinIRFunction.apply(x, plan, *params)

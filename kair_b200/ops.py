@@ -17,13 +17,14 @@ class Launch:
     Engines build these once per plan (all pointers are static workspace / parameter addresses) and replay them
     every step, so the per-step host cost is one ctypes call per kernel."""
 
-    __slots__ = ("name", "fn", "args", "keep")
+    __slots__ = ("name", "fn", "args", "keep", "meta")
 
     def __init__(self, name, args, keep=()):
         self.name = name
         self.fn = getattr(_lib.load(), name)
         self.args = args
         self.keep = keep  # tensors whose storage the struct points into
+        self.meta = None  # optional accounting hints for kair_b200.profiling (e.g. {"terms": 3} on split-operand GEMMs)
 
     def run(self, stream):
         rc = self.fn(ctypes.byref(self.args), stream)
@@ -137,7 +138,9 @@ def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
 # ------------------------------------------------------------------------------------------------ window attention
 
 def _attn_args(qkv, table, batch, H, W, num_heads, window, shift):
-    _req(qkv, torch.bfloat16, "qkv"); _req(table, torch.float32, "table")
+    _req(qkv, qkv.dtype, "qkv"); _req(table, torch.float32, "table")
+    if qkv.dtype not in (torch.bfloat16, torch.float32):
+        raise RuntimeError("kair_b200: qkv must be bf16 (tensor-core mode) or fp32 (fp32-accurate mode)")
     if not table.is_contiguous():
         raise RuntimeError("kair_b200: relative_position_bias_table must be contiguous")
     a = _S["kair_window_attn_args"]()
@@ -145,12 +148,13 @@ def _attn_args(qkv, table, batch, H, W, num_heads, window, shift):
     a.table = _ptr(table)
     a.batch, a.H, a.W = batch, H, W
     a.num_heads, a.window, a.shift = num_heads, window, shift
+    a.fp32 = 1 if qkv.dtype == torch.float32 else 0
     return a
 
 
 def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, shift=0):
     """out[t, h*32:(h+1)*32] = windowed softmax attention; qkv: bf16 [B*H*W, >=3*nH*32] in [3][nH][32] layout."""
-    _req(out, torch.bfloat16, "out")
+    _req(out, qkv.dtype, "out")
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.out = _ptr(out); a.out_pitch = _pitch(out)
     return Launch("kair_window_attn_fwd", a)
@@ -158,7 +162,7 @@ def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, 
 
 def build_window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_heads, window=8, shift=0):
     """Backward of window_attn_fwd: writes dqkv (bf16) and accumulates into dtable (fp32, caller zeroes)."""
-    _req(dout, torch.bfloat16, "dout"); _req(dqkv, torch.bfloat16, "dqkv"); _req(dtable, torch.float32, "dtable")
+    _req(dout, qkv.dtype, "dout"); _req(dqkv, qkv.dtype, "dqkv"); _req(dtable, torch.float32, "dtable")
     a = _attn_args(qkv, table, batch, H, W, num_heads, window, shift)
     a.dout = _ptr(dout); a.dout_pitch = _pitch(dout)
     a.dqkv = _ptr(dqkv); a.dqkv_pitch = _pitch(dqkv)
@@ -182,8 +186,9 @@ def _plist(tensors, like, keep):
     return arr.data_ptr()
 
 
-def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f):
-    """Pack L same-shaped nn.Linear layers (lists of fp32 tensors) into Wp [L,N_pad,K_pad] (+ WpT, bp)."""
+def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f, terms=1):
+    """Pack L same-shaped nn.Linear layers (lists of fp32 tensors) into Wp [L,N_pad,terms*K_pad] (+ WpT
+    [L,K_pad,terms*N_pad], bp).  terms > 1: weight-side segments of the fp32-accurate split (kair_b200.h)."""
     keep = []
     a = _S["kair_pack_linear_args"]()
     a.W = _plist(W, Wp, keep); a.b = _plist(b, Wp, keep)
@@ -191,7 +196,9 @@ def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const
     a.row_map = _ptr(row_map); a.col_map = _ptr(col_map)
     a.row_scale = _ptr(row_scale); a.bias_const = _ptr(bias_const)
     a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
-    a.L, a.N_pad, a.K_pad = Wp.shape
+    a.L, a.N_pad = Wp.shape[0], Wp.shape[1]
+    a.K_pad = Wp.shape[2] // terms
+    a.terms = terms
     a.out_f, a.in_f = out_f, in_f
     return Launch("kair_pack_linear", a, keep)
 
@@ -211,7 +218,7 @@ def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map
     return Launch("kair_unpack_linear_grad", a, keep)
 
 
-def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None):
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None, terms=1):
     """Pack L same-shaped conv weights (O,I,kh,kw) into Wp [L,O_pad,taps*I_pad] (+ flipped WpT [L,I_pad,taps*O_pad]).
     oscale / oshift: optional per-layer (O,) fp32 tensors folded in (Wp = W*oscale[o], bp = b*oscale[o] + oshift[o])."""
     keep = []
@@ -221,6 +228,7 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshi
     a.Wp = _ptr(Wp); a.WpT = _ptr(WpT); a.bp = _ptr(bp)
     a.L, a.O_pad = Wp.shape[0], Wp.shape[1]
     a.O, a.I, a.I_pad, a.taps = O, I, I_pad, taps
+    a.terms = terms
     return Launch("kair_pack_conv", a, keep)
 
 
@@ -237,13 +245,17 @@ def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, cen
 # ------------------------------------------------------------------------------------------------ LayerNorm
 
 def build_layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
-                  ones_col=-1):
+                  ones_col=-1, terms=1):
     _req(x, torch.float32, "x")
     a = _S["kair_layernorm_args"]()
     a.x = _ptr(x); a.gamma = _ptr(gamma); a.beta = _ptr(beta)
     a.y_f32 = _ptr(y_f32); a.y_bf16 = _ptr(y_bf16); a.xhat_bf16 = _ptr(xhat_bf16)
     a.mean = _ptr(mean); a.rstd = _ptr(rstd)
     a.T = x.shape[0]; a.C = C; a.pitch = x.stride(0); a.ones_col = ones_col; a.eps = eps
+    a.terms = terms
+    for t_ in (y_bf16, xhat_bf16):
+        if t_ is not None and (t_.stride(0) != terms * x.stride(0)):
+            raise RuntimeError("kair_b200: layernorm_fwd bf16 outputs must have pitch terms*pitch(x)")
     return Launch("kair_layernorm_fwd", a)
 
 
@@ -296,9 +308,15 @@ def _conv_out_args(W, shape, C, pitch, out_scale):
 
 
 def build_conv_out_fwd(feat, W, b, out, out_mean, *, C, pitch, out_scale=1.0, skip=None, skip_mean=None, skip_scale=0.0):
-    _req(feat, torch.bfloat16, "feat"); _req(out, torch.float32, "out")
+    _req(feat, feat.dtype, "feat"); _req(out, torch.float32, "out")
     a = _conv_out_args(W, out.shape, C, pitch, out_scale)
-    a.feat = _ptr(feat); a.b = _ptr(b); a.out = _ptr(out); a.out_mean = _ptr(out_mean)
+    if feat.dtype == torch.float32:   # fp32-accurate mode
+        a.feat_f32 = _ptr(feat)
+    elif feat.dtype == torch.bfloat16:
+        a.feat = _ptr(feat)
+    else:
+        raise RuntimeError("kair_b200: conv_out features must be bf16 or fp32")
+    a.b = _ptr(b); a.out = _ptr(out); a.out_mean = _ptr(out_mean)
     a.skip = _ptr(skip); a.skip_mean = _ptr(skip_mean); a.skip_scale = skip_scale
     return Launch("kair_conv_out_fwd", a)
 
@@ -313,9 +331,14 @@ def build_conv_out_dgrad(dout, W, *, C, pitch, out_scale=1.0, dfeat_f32=None, df
 
 
 def build_conv_out_wgrad(dout, feat, W, dW, db, *, C, pitch, out_scale=1.0):
-    _req(dout, torch.float32, "dout"); _req(feat, torch.bfloat16, "feat")
+    _req(dout, torch.float32, "dout"); _req(feat, feat.dtype, "feat")
     a = _conv_out_args(W, dout.shape, C, pitch, out_scale)
-    a.dout = _ptr(dout); a.feat = _ptr(feat); a.dW = _ptr(dW); a.db = _ptr(db)
+    if feat.dtype == torch.float32:
+        a.feat_f32 = _ptr(feat)
+    else:
+        _req(feat, torch.bfloat16, "feat")
+        a.feat = _ptr(feat)
+    a.dout = _ptr(dout); a.dW = _ptr(dW); a.db = _ptr(db)
     return Launch("kair_conv_out_wgrad", a)
 
 
@@ -340,6 +363,40 @@ def build_conv_out_pack(*, mode, co, C, cpad, W=None, Wt=None, D=None, dW=None, 
     ref = Wt if mode == 0 else D
     a.mode, a.co, a.C, a.C_pad, a.cpad, a.pitch, a.ones_row = mode, co, C, ref.shape[0], cpad, ref.stride(0), ones_row
     return Launch("kair_conv_out_pack", a)
+
+
+SPLIT_COPY, SPLIT_GELU, SPLIT_DGELU, SPLIT_ACT_BWD, SPLIT_LRELU = range(5)
+
+
+def build_split_terms(x, out, *, n, terms, op=SPLIT_COPY, aux=None, out_f32=None, row_scale=None, rows_per_sample=0,
+                      ones_col=-1, slope=0.0):
+    """fp32 rows -> split bf16 GEMM operand [T, terms*n] (fp32-accurate mode, kair_b200.h 'SPLIT PRECISION'), fused with
+    the element-wise stage `op`; out_f32 optionally receives the transformed fp32 values."""
+    _req(x, torch.float32, "x"); _req(out, torch.bfloat16, "out"); _req(aux, torch.float32, "aux")
+    _req(out_f32, torch.float32, "out_f32"); _req(row_scale, torch.float32, "row_scale")
+    a = _S["kair_split_args"]()
+    a.x = _ptr(x); a.x_pitch = _pitch(x)
+    a.aux = _ptr(aux); a.aux_pitch = _pitch(aux)
+    a.out = _ptr(out); a.out_pitch = _pitch(out)
+    a.out_f32 = _ptr(out_f32); a.out_f32_pitch = _pitch(out_f32)
+    a.row_scale = _ptr(row_scale)
+    a.T = x.shape[0]; a.n = n; a.terms = terms; a.op = op; a.ones_col = ones_col
+    a.rows_per_sample = rows_per_sample; a.slope = slope
+    return Launch("kair_split_terms", a)
+
+
+def build_ln_bwd_split(g, xhat, rstd, outF, *, C, terms, resid=None, out=None, row_scale=None, rows_per_sample=0):
+    """LayerNorm backward + residual gradient on split x-hat (fp32-accurate mode; counterpart of EPI_LNBWD)."""
+    _req(g, torch.float32, "g"); _req(xhat, torch.bfloat16, "xhat"); _req(rstd, torch.float32, "rstd")
+    _req(outF, torch.float32, "outF"); _req(resid, torch.float32, "resid"); _req(out, torch.bfloat16, "out")
+    _req(row_scale, torch.float32, "row_scale")
+    if _pitch(outF) != _pitch(g) or (resid is not None and _pitch(resid) != _pitch(g)):
+        raise RuntimeError("kair_b200: ln_bwd_split fp32 operands must share one pitch")
+    a = _S["kair_ln_bwd_split_args"]()
+    a.g = _ptr(g); a.xhat = _ptr(xhat); a.xhat_pitch = _pitch(xhat); a.rstd = _ptr(rstd); a.resid = _ptr(resid)
+    a.outF = _ptr(outF); a.out = _ptr(out); a.out_pitch = _pitch(out); a.row_scale = _ptr(row_scale)
+    a.T = g.shape[0]; a.C = C; a.pitch = _pitch(g); a.terms = terms; a.rows_per_sample = rows_per_sample
+    return Launch("kair_ln_bwd_split", a)
 
 
 def build_add_inplace(y, x, yb=None):
@@ -471,9 +528,13 @@ def build_bn_fold(gamma, beta, running_mean, running_var, scale, shift, *, C, ep
     return Launch("kair_bn_fold", a)
 
 
-def _shuffle_args(x, out, batch, H, W, C, r):
-    _req(x, torch.bfloat16, "in"); _req(out, torch.bfloat16, "out")
+def _shuffle_args(x, out, batch, H, W, C, r, allow_fp32=False):
+    if allow_fp32 and x.dtype == torch.float32:
+        _req(x, torch.float32, "in"); _req(out, torch.float32, "out")
+    else:
+        _req(x, torch.bfloat16, "in"); _req(out, torch.bfloat16, "out")
     a = _S["kair_shuffle_args"]()
+    a.fp32 = 1 if x.dtype == torch.float32 else 0
     setattr(a, "in", _ptr(x)); a.out = _ptr(out)
     a.in_pitch, a.out_pitch = _pitch(x), _pitch(out)
     a.batch, a.H, a.W, a.C, a.r = batch, H, W, C, r
@@ -482,12 +543,12 @@ def _shuffle_args(x, out, batch, H, W, C, r):
 
 def build_pixel_shuffle(x, out, *, batch, H, W, C, r):
     """nn.PixelShuffle(r) on token features: x [B*H*W, >= r*r*C] -> out [B*rH*rW, >= C] (bf16)."""
-    return Launch("kair_pixel_shuffle", _shuffle_args(x, out, batch, H, W, C, r))
+    return Launch("kair_pixel_shuffle", _shuffle_args(x, out, batch, H, W, C, r, allow_fp32=True))
 
 
 def build_upsample_nearest2(x, out, *, batch, H, W, C):
     """nearest-neighbour x2 of token features: x [B*H*W, >= C] -> out [B*2H*2W, >= C] (bf16)."""
-    return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2))
+    return Launch("kair_upsample_nearest2", _shuffle_args(x, out, batch, H, W, C, 2, allow_fp32=True))
 
 
 def build_pixel_shuffle_bwd(dy, dx, *, batch, H, W, C, r):
@@ -519,10 +580,13 @@ def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
 
 def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
     """out (B, co, r*H, r*W) fp32 = PixelShuffle(r)(x) * scale + mean[c]; x bf16 [B*H*W, >= co*r*r]."""
-    _req(x, torch.bfloat16, "in"); _req(out, torch.float32, "out"); _req(mean, torch.float32, "mean")
+    _req(x, x.dtype, "in"); _req(out, torch.float32, "out"); _req(mean, torch.float32, "mean")
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        raise RuntimeError("kair_b200: pixel_shuffle_out input must be bf16 or fp32")
     if not out.is_contiguous():
         raise RuntimeError("kair_b200: pixel_shuffle_out needs a contiguous NCHW output")
     a = _S["kair_shuffle_out_args"]()
+    a.fp32 = 1 if x.dtype == torch.float32 else 0
     setattr(a, "in", _ptr(x)); a.out = _ptr(out); a.mean = _ptr(mean)
     a.in_pitch = _pitch(x); a.scale = scale
     a.batch, a.co = out.shape[0], out.shape[1]

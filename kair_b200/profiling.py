@@ -17,15 +17,20 @@ def describe(launch, real_dims):
     r = lambda n: real_dims.get(int(n), int(n))
     if name == "gemm_tn":
         taps = 9 if a.conv else 1
+        terms = (getattr(launch, "meta", None) or {}).get("terms", 1)   # fp32-accurate mode: split operands along K
         tag = "gemm_tn[%s N%d K%d %s]" % ("conv3x3" if a.conv else "dense", a.N, a.K * taps, _EPI[a.mode])
+        if terms > 1:
+            tag = tag[:-1] + " split%d]" % terms
         if a.mode == 0 and a.aux:
             tag = tag[:-1] + "+actbwd]"
         # operand traffic of this launch on the unpadded extents: A once (the 9 taps re-read it from L2 / smem),
-        # fp32 residual in, bf16 aux in, every output once; weights are L2-resident
-        by = 2.0 * a.M * r(a.K)
+        # fp32 residual in, bf16 aux in, every output once; weights are L2-resident.  Split operands: the algorithmic
+        # FLOPs stay those of the reference's fp32 product (K / terms); the bytes are what the split layout moves.
+        kr = r(a.K // terms)
+        by = 2.0 * a.M * kr * terms
         by += 4.0 * a.M * r(a.N) * (1 if a.resid else 0) + 2.0 * a.M * r(a.N) * (1 if a.aux else 0)
         by += 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
-        return tag, 2.0 * a.M * r(a.N) * r(a.K) * taps, by
+        return tag, 2.0 * a.M * r(a.N) * kr * taps, by
     if name == "gemm_nt":
         taps = 9 if a.conv else 1
         tag = "gemm_nt[%s n1=%d n2=%d]" % ("conv3x3" if a.conv else "dense", a.n1, a.n2 * taps)
@@ -34,13 +39,22 @@ def describe(launch, real_dims):
         T = a.batch * a.H * a.W
         N = a.window * a.window
         hd = real_dims.get("head_dim", 30)
+        esz = 4 if a.fp32 else 2
+        sfx = "[fp32 cuda-core]" if a.fp32 else ""
         f = 4.0 * (T // N) * a.num_heads * N * N * hd          # QK^T + PV
-        by = 4.0 * T * a.num_heads * hd * 2                    # q, k, v, o in bf16 (15 360 B / window-head)
+        by = 4.0 * T * a.num_heads * hd * esz                  # q, k, v, o in bf16 (15 360 B / window-head)
         if name.endswith("bwd"):
             # autograd's dV, dP, dQ, dK contractions (the kernel's recomputation of S is not algorithmic work);
             # reads q, k, v, dO, writes dq, dk, dv
-            return "window_attn_bwd", 2.0 * f, 7.0 * T * a.num_heads * hd * 2
-        return "window_attn_fwd", f, by
+            return "window_attn_bwd" + sfx, 2.0 * f, 7.0 * T * a.num_heads * hd * esz
+        return "window_attn_fwd" + sfx, f, by
+    if name == "split_terms":
+        return name, 0.0, float(a.T) * a.n * (4.0 + (4.0 if a.aux else 0) + 2.0 * a.terms + (4.0 if a.out_f32 else 0))
+    if name == "ln_bwd_split":
+        return name, 0.0, float(a.T) * a.C * (4.0 + 2.0 * 2 + (4.0 if a.resid else 0) + 4.0 + (2.0 * a.terms if a.out else 0))
+    if name == "layernorm_fwd":
+        tm = a.terms if a.terms > 1 else 1
+        return name, 0.0, float(a.T) * a.C * (4.0 + (4.0 if a.y_f32 else 0) + 2.0 * tm * ((1 if a.y_bf16 else 0) + (1 if a.xhat_bf16 else 0)))
     T_ = lambda: int(a.T)
     if name in ("bn_stats",):
         return name, 0.0, 4.0 * T_() * a.C

@@ -119,6 +119,8 @@ class SwinIREngine:
                                  dtype=torch.float32, device=self.device)
         self._plans = {}
         self._weights = None
+        self._plans_fp32 = {}
+        self._weights_fp32 = None
         self.grad_hook = None   # callable(flat fp32 gradient buffer), e.g. parallel.allreduce_flat bound to the module
         self._build_maps()
 
@@ -247,7 +249,22 @@ class SwinIREngine:
             W["versions"] = v
 
     # ------------------------------------------------------------------------------------------ plans
-    def plan(self, B, H, W, train):
+    def plan(self, B, H, W, train, precision="bf16", terms=3):
+        """precision 'bf16': tensor-core operands in bf16 (2e-2 max-abs contract); 'fp32': the fp32-accurate split
+        mode of swinir_engine_fp32.py (1e-4 forward / 1e-3 gradient contract)."""
+        if precision == "fp32":
+            from . import swinir_engine_fp32 as f32m
+            Wt = f32m.weight_state_fp32(self, train, terms)
+            key = (B, H, W, bool(train), terms)
+            p = self._plans_fp32.get(key)
+            if p is None:
+                if len(self._plans_fp32) >= 2:
+                    self._plans_fp32.pop(next(iter(self._plans_fp32)))
+                p = f32m.PlanF32(self, Wt, B, H, W, bool(train), terms)
+                self._plans_fp32[key] = p
+            return p
+        if precision != "bf16":
+            raise ValueError("kair_b200: precision must be 'bf16' or 'fp32', got %r" % (precision,))
         key = (B, H, W, bool(train))
         Wt = self._weight_state(train)
         p = self._plans.get(key)

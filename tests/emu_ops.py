@@ -36,6 +36,32 @@ def _bf(x):
     return x.to(torch.bfloat16)
 
 
+SPLIT_COPY, SPLIT_GELU, SPLIT_DGELU, SPLIT_ACT_BWD, SPLIT_LRELU = range(5)
+
+
+def _components(x):
+    """bf16 components of an fp32 tensor (kair_b200.h 'SPLIT PRECISION'): c0 + c1 + c2 ~= x"""
+    c0 = x.to(torch.bfloat16).float()
+    r1 = x - c0
+    c1 = r1.to(torch.bfloat16).float()
+    c2 = (r1 - c1).to(torch.bfloat16).float()
+    return [c0, c1, c2]
+
+
+def _seg_act(terms):
+    return {1: [0], 3: [0, 1, 0], 6: [0, 1, 2, 0, 1, 0]}[terms]
+
+
+def _seg_w(terms):
+    return {1: [0], 3: [0, 0, 1], 6: [0, 0, 0, 1, 1, 2]}[terms]
+
+
+def _split_act(x, terms):
+    """[T, n] fp32 -> [T, terms*n] bf16 activation-side operand"""
+    c = _components(x)
+    return torch.cat([c[w] for w in _seg_act(terms)], dim=1).to(torch.bfloat16)
+
+
 def _gelu_grad(x):
     return 0.5 * (1.0 + torch.erf(x * 0.7071067811865476)) + x * torch.exp(-0.5 * x * x) * 0.3989422804014327
 
@@ -208,7 +234,7 @@ def build_window_attn_fwd(qkv, table, out, *, batch, H, W, num_heads, window=8, 
     def run():
         w = 3 * num_heads * 32
         o = _attn_core(qkv.reshape(batch * H * W, -1)[:, :w].float(), table.float(), batch, H, W, num_heads, window, shift)
-        out.reshape(batch * H * W, -1)[:, :num_heads * 32].copy_(_bf(o))
+        out.reshape(batch * H * W, -1)[:, :num_heads * 32].copy_(o.to(out.dtype))
 
     return EmuLaunch("kair_window_attn_fwd", run)
 
@@ -222,7 +248,7 @@ def build_window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_he
             t = table.float().detach().requires_grad_(True)
             o = _attn_core(q, t, batch, H, W, num_heads, window, shift)
             (o * dout.reshape(T, -1)[:, :num_heads * 32].float()).sum().backward()
-        dqkv.reshape(T, -1)[:, :w].copy_(_bf(q.grad))
+        dqkv.reshape(T, -1)[:, :w].copy_(q.grad.to(dqkv.dtype))
         dtable.add_(t.grad)
 
     return EmuLaunch("kair_window_attn_bwd", run)
@@ -230,9 +256,10 @@ def build_window_attn_bwd(qkv, table, dout, dqkv, dtable, *, batch, H, W, num_he
 
 # ------------------------------------------------------------------------------------------------ packing
 
-def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f):
+def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const, Wp, WpT, bp, *, out_f, in_f, terms=1):
     def run():
-        L, N_pad, K_pad = Wp.shape
+        L, N_pad = Wp.shape[0], Wp.shape[1]
+        K_pad = Wp.shape[2] // terms
         rm, cm = row_map.long(), col_map.long()
         for l in range(L):
             w = W[l].detach()
@@ -242,9 +269,15 @@ def build_pack_linear(W, b, gamma, beta, row_map, col_map, row_scale, bias_const
             rv, cv = rm >= 0, cm >= 0
             sub = w[rm[rv]][:, cm[cv]] * g[cm[cv]][None, :] * rs[rv][:, None]
             full[rv.nonzero()[:, 0][:, None], cv.nonzero()[:, 0][None, :]] = sub
-            Wp[l].copy_(_bf(full))
-            if WpT is not None:
-                WpT[l].copy_(_bf(full.t()))
+            if terms == 1:
+                Wp[l].copy_(_bf(full))
+                if WpT is not None:
+                    WpT[l].copy_(_bf(full.t()))
+            else:
+                c = _components(full)
+                Wp[l].copy_(_bf(torch.cat([c[w] for w in _seg_w(terms)], dim=1)))
+                if WpT is not None:
+                    WpT[l].copy_(_bf(torch.cat([c[w].t() for w in _seg_w(terms)], dim=1)))
             if bp is not None:
                 bias = torch.zeros(N_pad)
                 base = b[l].detach()[rm[rv]] if b is not None else torch.zeros(int(rv.sum()))
@@ -283,7 +316,7 @@ def build_unpack_linear_grad(dWp, W, gamma, beta, dW, db, dgamma, dbeta, row_map
     return EmuLaunch("kair_unpack_linear_grad", run)
 
 
-def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None):
+def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshift=None, terms=1):
     def run():
         L, O_pad = Wp.shape[0], Wp.shape[1]
         for l in range(L):
@@ -292,11 +325,16 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshi
                 w = w * oscale[l].view(O, 1, 1)
             full = torch.zeros(O_pad, taps, I_pad)
             full[:O, :, :I] = w.permute(0, 2, 1)
-            Wp[l].copy_(_bf(full.reshape(O_pad, taps * I_pad)))
+            def segs(m):   # [rows, taps, cols] -> [rows, taps * terms * cols] with k = (tap*terms + seg)*cols + i
+                if terms == 1:
+                    return _bf(m.reshape(m.shape[0], -1))
+                c = _components(m)
+                return _bf(torch.stack([c[w] for w in _seg_w(terms)], dim=2).reshape(m.shape[0], -1))
+            Wp[l].copy_(segs(full))
             if WpT is not None:
                 t = torch.zeros(I_pad, taps, O_pad)
                 t[:I, :, :O] = w.flip(2).permute(1, 2, 0)
-                WpT[l].copy_(_bf(t.reshape(I_pad, taps * O_pad)))
+                WpT[l].copy_(segs(t))
             if bp is not None:
                 bias = torch.zeros(O_pad)
                 if b is not None:
@@ -325,7 +363,7 @@ def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, cen
 # ------------------------------------------------------------------------------------------------ LayerNorm
 
 def build_layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None, xhat_bf16=None, mean=None, rstd=None,
-                        ones_col=-1):
+                        ones_col=-1, terms=1):
     def run():
         v = x[:, :C]
         m = v.mean(1, keepdim=True)
@@ -348,12 +386,12 @@ def build_layernorm_fwd(x, gamma, beta, *, C, eps=1e-5, y_f32=None, y_bf16=None,
             if y_bf16 is not None:
                 if ones_col >= 0:
                     y[:, ones_col] = 1.0
-                y_bf16.copy_(_bf(y))
+                y_bf16.copy_(_split_act(y, terms) if terms > 1 else _bf(y))
         if xhat_bf16 is not None:
             h = padded(xh)
             if ones_col >= 0:
                 h[:, ones_col] = 1.0
-            xhat_bf16.copy_(_bf(h))
+            xhat_bf16.copy_(_split_act(h, terms) if terms > 1 else _bf(h))
 
     return EmuLaunch("kair_layernorm_fwd", run)
 
@@ -495,6 +533,50 @@ def build_conv_out_pack(*, mode, co, C, cpad, W=None, Wt=None, D=None, dW=None, 
             if db is not None:
                 db.copy_(D[ones_row, 4 * cpad:4 * cpad + co])
     return EmuLaunch("kair_conv_out_pack", run)
+
+
+def build_split_terms(x, out, *, n, terms, op=SPLIT_COPY, aux=None, out_f32=None, row_scale=None, rows_per_sample=0,
+                      ones_col=-1, slope=0.0):
+    def run():
+        v = x[:, :n].float().clone()
+        if op == SPLIT_GELU:
+            v = F.gelu(v)
+        elif op == SPLIT_LRELU:
+            v = torch.where(v > 0, v, v * slope)
+        elif op == SPLIT_DGELU:
+            v = v * _gelu_grad(aux[:, :n].float())
+        elif op == SPLIT_ACT_BWD:
+            v = torch.where(aux[:, :n] > 0, v, v * slope)
+        if row_scale is not None:
+            v = v * row_scale.repeat_interleave(rows_per_sample)[:, None]
+        if ones_col >= 0:
+            v[:, ones_col] = 1.0
+        if out_f32 is not None:
+            out_f32[:, :n].copy_(v)
+        if out is not None:
+            out[:, :terms * n].copy_(_split_act(v, terms))
+
+    return EmuLaunch("kair_split_terms", run)
+
+
+def build_ln_bwd_split(g, xhat, rstd, outF, *, C, terms, resid=None, out=None, row_scale=None, rows_per_sample=0):
+    def run():
+        pitch = g.shape[1]
+        nc = {3: 2, 6: 3}[terms]
+        xh = sum(xhat[:, k * pitch:k * pitch + C].float() for k in reversed(range(nc)))
+        gg = g[:, :C]
+        m1 = gg.mean(1, keepdim=True)
+        m2 = (gg * xh).mean(1, keepdim=True)
+        dx = torch.zeros(g.shape[0], pitch)
+        dx[:, :C] = rstd[:, None] * (gg - m1 - xh * m2)
+        if resid is not None:
+            dx[:, :C] += resid[:, :C]
+        outF.copy_(dx)
+        if out is not None:
+            sc = row_scale.repeat_interleave(rows_per_sample)[:, None] if row_scale is not None else 1.0
+            out[:, :terms * pitch].copy_(_split_act(dx * sc, terms))
+
+    return EmuLaunch("kair_ln_bwd_split", run)
 
 
 def build_add_inplace(y, x, yb=None):
