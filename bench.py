@@ -394,6 +394,7 @@ def run_b200(args):
     # the inference half of BASELINE.json's metric ("... & DnCNN/SwinIR inference MPix/s") in the same process, about a
     # second each: cfg1 (B=1 CUDA-graph replay, and B=64) and cfg3, each with value, e2e, dominant-kernel roofline
     # fraction and its own CPU baseline (oracle port)
+    n_launches = len(launches)
     also = None
     if rank == 0 and world == 1 and not args.no_also:
         del plan, launches
@@ -429,7 +430,7 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": "patches/s",
                     "h2d_bytes_per_step": (low_h.numel() + high_h.numel()) * 4 * world,
                     "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": (len(launches) + n_pack + (0 if args.torch_tail else 2)) * args.steps,
+            "gpu_launches": (n_launches + n_pack + (0 if args.torch_tail else 2)) * args.steps,
             "roofline": roof, "cpu_baseline": cpu, "also": also,
         }
         print(json.dumps(line), flush=True)

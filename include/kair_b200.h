@@ -522,6 +522,39 @@ int kair_pixel_shuffle_out_bwd(const kair_shuffle_out_args* args, void* stream);
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Launch lists.  A plan (one forward or backward pass of a network at a fixed shape) is a static sequence of the entry
+ * points above with pre-filled argument structs; kair_run_list replays such a sequence in ONE call, so the host cost
+ * of a pass is one FFI crossing instead of one per kernel (SwinIR-M training: 558 kernels per step).
+ *   op   : kair_op_id("kair_gemm_tn") etc. -- the index of an entry point in the library's own table
+ *   args : the argument struct that entry point takes
+ * Returns 0, or the failing launch's return code with kair_last_error() naming its index.
+ * kair_add_inplace_s / kair_memcpy_d2d are struct-taking forms of the two scalar-argument helpers so that they can
+ * appear in lists.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_launch {
+  int32_t op;
+  int32_t reserved;
+  const void* args;
+} kair_launch;
+int kair_op_id(const char* name);   /* -1 if `name` is not a listable entry point */
+int kair_run_list(const kair_launch* list, int32_t n, void* stream);
+
+typedef struct kair_add_args {
+  float* y;          /* y += x */
+  const float* x;
+  void* yb;          /* bf16 shadow copy of the updated y, or NULL */
+  int64_t n;
+} kair_add_args;
+int kair_add_inplace_s(const kair_add_args* args, void* stream);
+
+typedef struct kair_memcpy_args {
+  void* dst;
+  const void* src;
+  int64_t bytes;
+} kair_memcpy_args;
+int kair_memcpy_d2d(const kair_memcpy_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * The serial tail of a training step.
  *   kair_pixel_loss  CharbonnierLoss (models/loss.py:208-218; mode 0) or nn.L1Loss (mode 1) and its gradient in one pass:
  *                    loss[0] = mean(sqrt((x-y)^2 + eps)),  dx = d(loss)/dx.  `scratch` is two zero-initialised 8-byte

@@ -67,7 +67,10 @@ def _compile_one(src, verbose):
     return obj, r.stderr
 
 
-def build(verbose=False, force=False):
+def build(verbose=False, force=False, devel=False):
+    """devel=True adds -DKB_DEVEL: the KB_*_DBG / KB_*_TS / KB_NT_BM development hooks (csrc/host.h) are compiled in."""
+    if devel and "-DKB_DEVEL" not in NVCC_FLAGS:
+        NVCC_FLAGS.append("-DKB_DEVEL")
     os.makedirs(OBJ_DIR, exist_ok=True)
     if force:
         for f in os.listdir(OBJ_DIR):
@@ -91,4 +94,4 @@ def build(verbose=False, force=False):
 
 
 if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv, devel="--devel" in sys.argv))

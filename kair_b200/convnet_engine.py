@@ -95,13 +95,8 @@ class _EngineBase:
         return (_dirty.optimizer_epoch(),) + tuple(p._version for p in self.P.values()) + tuple(b._version for b in extra)
 
     def _get_plan(self, key, make):
-        p = self._plans.get(key)
-        if p is None:
-            if len(self._plans) >= 4:
-                self._plans.pop(next(iter(self._plans)))
-            p = make()
-            self._plans[key] = p
-        return p
+        from .swinir_engine import pick_plan
+        return pick_plan(self._plans, key, 4, make)   # two activation sets per shape: see pick_plan
 
 
 class _PlanBase:
@@ -111,25 +106,40 @@ class _PlanBase:
         self.eng = eng
         self.generation = 0
 
+    def _lists(self):
+        """the launch lists as C arrays (one FFI call per pass), built on first use"""
+        ls = getattr(self, "_launch_lists", None)
+        if ls is None:
+            o = self.eng.ops
+            ls = self._launch_lists = (o.make_list(self.fwd), o.make_list(self.bwd) if self.bwd is not None else None)
+        return ls
+
     def run_forward(self, x):
-        st = self.eng.ops.stream_handle()
-        self.eng.refresh_weights(self, st)
-        self.img.copy_(x)
-        for l in self.fwd:
-            l.run(st)
+        o = self.eng.ops
+        with o.device_guard(self.img.device):   # the launchers use the current device and its current stream
+            st = o.stream_handle(self.img.device)
+            self.eng.refresh_weights(self, st)
+            self.img.copy_(x)
+            self._lists()[0].run(st)
+        # kair_bn_finalize wrote running_mean / running_var / num_batches_tracked through raw pointers: advance their
+        # version counters like an in-place torch op would, so that the folded eval-mode weights (keyed on these
+        # versions, refresh_weights) and GraphedInference see the change even when no optimizer step follows
+        for b in getattr(self, "bn_buffers", ()):
+            torch.autograd.graph.increment_version(b)
         self.generation += 1
         return self.out.clone()
 
     def run_backward(self, dout):
-        st = self.eng.ops.stream_handle()
-        self.dout.copy_(dout)
-        self.grads.flat.zero_()
-        for t in self.zero_before_bwd:
-            t.zero_()
-        for l in self.bwd:
-            l.run(st)
-        if self.eng.grad_hook is not None:
-            self.eng.grad_hook(self.grads.flat)
+        o = self.eng.ops
+        with o.device_guard(self.img.device):
+            st = o.stream_handle(self.img.device)
+            self.dout.copy_(dout)
+            self.grads.flat.zero_()
+            for t in self.zero_before_bwd:
+                t.zero_()
+            self._lists()[1].run(st)
+            if self.eng.grad_hook is not None:
+                self.eng.grad_hook(self.grads.flat)
         return self.grads.snapshot()
 
 
@@ -138,7 +148,9 @@ class ConvNetFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, plan, *params):
+        from .swinir_engine import mark_busy
         out = plan.run_forward(x)
+        mark_busy(plan)
         ctx.plan = plan
         ctx.generation = plan.generation
         return out
@@ -147,9 +159,15 @@ class ConvNetFunction(torch.autograd.Function):
     def backward(ctx, dout):
         plan = ctx.plan
         if plan.generation != ctx.generation:
-            raise RuntimeError("kair_b200: backward() called after another forward() of the same shape overwrote the "
-                               "saved activations; run forward and backward in pairs")
-        return (None, None) + tuple(plan.run_backward(dout.contiguous()))
+            raise RuntimeError("kair_b200: backward() called after two later forward() calls of the same shape "
+                               "overwrote the saved activations (two sets are kept per shape)")
+        plan.busy = False
+        grads = plan.run_backward(dout.contiguous())
+        dx = None
+        if ctx.needs_input_grad[0]:
+            from .swinir_engine import input_grad
+            dx = input_grad(plan, dout)
+        return (dx, None) + tuple(grads)
 
 
 # ====================================================================================================== DnCNN
@@ -293,6 +311,7 @@ class _DnCNNPlan(_PlanBase):
 
         fwd = []
         a0, s0 = act_of(head)
+        self.bn_buffers = []
         fwd.append(o.build_conv_in_fwd(self.img, head.conv.weight, head.conv.bias, zc_in, 1.0, O=nc, O_pad=nc, pitch=nc,
                                        out_bf16=A(0), act=a0, act_slope=s0))
         for i, s in enumerate(body):
@@ -304,6 +323,7 @@ class _DnCNNPlan(_PlanBase):
                 fwd.append(o.build_bn_finalize(self.bn_acc, self.bn_mean[i], self.bn_rstd[i], s.bn.running_mean,
                                                s.bn.running_var, s.bn.num_batches_tracked, C=nc, T=T, eps=s.bn.eps,
                                                momentum=s.bn.momentum))
+                self.bn_buffers += [s.bn.running_mean, s.bn.running_var, s.bn.num_batches_tracked]
                 fwd.append(o.build_bn_apply(z, self.bn_mean[i], self.bn_rstd[i], s.bn.weight, s.bn.bias, C=nc, act=act,
                                             act_slope=slope, out_bf16=A(i + 1)))
             else:
@@ -384,6 +404,7 @@ class _DnCNNPlan(_PlanBase):
                                             I_pad=7, ones_col=cin, center_tap=4, dwp_pitch=64))
         bwd.append(o.build_unpack_conv_grad(dWp, [G(s.conv.weight) for s in body], None, O=nc, I=nc, I_pad=nc))
         self.bwd = bwd
+        self._dx_spec = dict(dhead=d[cur], W=head.conv.weight, C=nc, pitch=nc, scale=1.0, skip=bool(eng.residual))
         self._finish(eng)
 
 
@@ -713,4 +734,5 @@ class _UNetResPlan(_PlanBase):
                                                   [G(U["conv"].weight).view(Co, Ci * 4)], None, None, None, U["rows"],
                                                   U["cols"], None, out_f=Co, in_f=4 * Ci, ones_col=-1))
         self.bwd = bwd
+        self._dx_spec = dict(dhead=cf, W=head.weight, C=nc[0], pitch=nc[0], scale=1.0, skip=False)
         self._finish(eng)

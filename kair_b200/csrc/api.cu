@@ -1,6 +1,8 @@
 // extern "C" entry points declared in include/kair_b200.h
 #include "../../include/kair_b200.h"
 
+#include <string.h>
+
 #include "host.h"
 
 namespace kb {
@@ -130,6 +132,79 @@ KB_WRAP(kair_ln_bwd_split, kair_ln_bwd_split_args, ln_bwd_split_launch)
 
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream) {
   return kb::add_inplace_launch(y, x, yb, (long long)n, (cudaStream_t)stream);
+}
+
+int kair_add_inplace_s(const kair_add_args* a, void* stream) {
+  if (!a) {
+    kb::set_error("kair_add_inplace_s: null args");
+    return -1;
+  }
+  return kb::add_inplace_launch(a->y, a->x, a->yb, (long long)a->n, (cudaStream_t)stream);
+}
+
+int kair_memcpy_d2d(const kair_memcpy_args* a, void* stream) {
+  if (!a || !a->dst || !a->src || a->bytes < 0) {
+    kb::set_error("kair_memcpy_d2d: bad arguments");
+    return -1;
+  }
+  cudaError_t e = cudaMemcpyAsync(a->dst, a->src, (size_t)a->bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    kb::set_error("kair_memcpy_d2d: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+// ---- launch lists: one table of (name, type-erased entry point); kair_op_id / kair_run_list index into it
+namespace {
+typedef int (*kb_entry)(const void*, void*);
+struct KbOp {
+  const char* name;
+  kb_entry fn;
+};
+#define KB_OP(NAME) {#NAME, reinterpret_cast<kb_entry>(&NAME)}
+const KbOp kb_ops[] = {
+    KB_OP(kair_gemm_tn), KB_OP(kair_gemm_nt), KB_OP(kair_window_attn_fwd), KB_OP(kair_window_attn_bwd),
+    KB_OP(kair_pack_linear), KB_OP(kair_unpack_linear_grad), KB_OP(kair_pack_conv), KB_OP(kair_unpack_conv_grad),
+    KB_OP(kair_layernorm_fwd), KB_OP(kair_layernorm_bwd), KB_OP(kair_conv_in_fwd), KB_OP(kair_conv_in_wgrad),
+    KB_OP(kair_conv_out_fwd), KB_OP(kair_conv_out_dgrad), KB_OP(kair_conv_out_wgrad), KB_OP(kair_im2col3x3),
+    KB_OP(kair_conv_out_pack), KB_OP(kair_space_to_depth), KB_OP(kair_depth_to_space), KB_OP(kair_colsum),
+    KB_OP(kair_bn_stats), KB_OP(kair_bn_finalize), KB_OP(kair_bn_apply), KB_OP(kair_bn_bwd_reduce),
+    KB_OP(kair_bn_bwd_apply), KB_OP(kair_bn_fold), KB_OP(kair_pixel_shuffle), KB_OP(kair_upsample_nearest2),
+    KB_OP(kair_pixel_shuffle_out), KB_OP(kair_pixel_loss), KB_OP(kair_adam_ema), KB_OP(kair_pixel_shuffle_out_bwd),
+    KB_OP(kair_pixel_shuffle_bwd), KB_OP(kair_upsample_nearest2_bwd), KB_OP(kair_split_terms),
+    KB_OP(kair_ln_bwd_split), KB_OP(kair_add_inplace_s), KB_OP(kair_memcpy_d2d),
+};
+#undef KB_OP
+constexpr int kb_n_ops = (int)(sizeof(kb_ops) / sizeof(kb_ops[0]));
+}  // namespace
+
+int kair_op_id(const char* name) {
+  if (!name) return -1;
+  for (int i = 0; i < kb_n_ops; ++i)
+    if (strcmp(kb_ops[i].name, name) == 0) return i;
+  return -1;
+}
+
+int kair_run_list(const kair_launch* list, int32_t n, void* stream) {
+  if (!list || n < 0) {
+    kb::set_error("kair_run_list: null list");
+    return -1;
+  }
+  for (int i = 0; i < n; ++i) {
+    const int op = list[i].op;
+    if (op < 0 || op >= kb_n_ops) {
+      kb::set_error("kair_run_list: launch %d has unknown op %d", i, op);
+      return -1;
+    }
+    const int rc = kb_ops[op].fn(list[i].args, stream);
+    if (rc != 0) {
+      std::string msg = kb::get_error();
+      kb::set_error("kair_run_list: launch %d (%s) failed: %s", i, kb_ops[op].name, msg.c_str());
+      return rc;
+    }
+  }
+  return 0;
 }
 
 }  // extern "C"

@@ -526,7 +526,7 @@ int window_attn_bwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
   }
   int grid = p.pairs < sm_count() ? p.pairs : sm_count();
   static long long* ts_dev = nullptr;
-  const bool want_ts = getenv("KB_AB_TS") != nullptr;
+  const bool want_ts = KB_DEV_ENV("KB_AB_TS") != nullptr;
   if (want_ts) {
     if (!ts_dev) cudaMalloc(&ts_dev, 3 * 256 * 8);
     cudaMemset(ts_dev, 0, 3 * 256 * 8);

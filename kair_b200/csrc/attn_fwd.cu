@@ -478,7 +478,7 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
   p.total_windows = a.batch * p.nWh * p.nWw;
   p.pairs = (p.total_windows + 1) / 2;
   {
-    const char* e = getenv("KB_AF_DBG");
+    const char* e = KB_DEV_ENV("KB_AF_DBG");
     p.dbg = e ? atoi(e) : 0;
   }
   uint32_t box[4] = {64, 4, 4, 1};
@@ -522,7 +522,7 @@ int window_attn_fwd_launch(const kair_window_attn_args& a, cudaStream_t st) {
   }
   int grid = p.pairs < sm_count() ? p.pairs : sm_count();
   static long long* ts_dev = nullptr;
-  const bool want_ts = getenv("KB_AF_TS") != nullptr;
+  const bool want_ts = KB_DEV_ENV("KB_AF_TS") != nullptr;
   if (want_ts) {
     if (!ts_dev) cudaMalloc(&ts_dev, 3 * 256 * 8);
     cudaMemset(ts_dev, 0, 3 * 256 * 8);

@@ -235,7 +235,7 @@ template <int BN, bool kConv, int BM>
 static int nt_launch_cfg(NtParams p, int grid, size_t smem, cudaStream_t st) {
   auto kern = gemm_nt_kernel<BN, kConv, BM>;
   static long long* ts_dev = nullptr;
-  const bool want_ts = getenv("KB_NT_TS") != nullptr;
+  const bool want_ts = KB_DEV_ENV("KB_NT_TS") != nullptr;
   if (want_ts) {
     if (!ts_dev) cudaMalloc(&ts_dev, 8 * 8);
     cudaMemset(ts_dev, 0, 8 * 8);
@@ -277,7 +277,7 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   // with more than one tile the uneven last tile and the doubled, un-overlapped epilogue cancel the gain (n1 = 384, 576)
   int bm = (a.n1 > 128 && a.n1 <= 256) ? 256 : 128;
   {
-    const char* e = getenv("KB_NT_BM");   // development aid: force the accumulator height
+    const char* e = KB_DEV_ENV("KB_NT_BM");   // development aid: force the accumulator height
     if (e && (atoi(e) == 128 || atoi(e) == 256)) bm = atoi(e);
   }
   p.tiles1 = (a.n1 + bm - 1) / bm;

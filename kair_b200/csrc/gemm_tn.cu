@@ -866,7 +866,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   p.has_outB2 = a.outB2 != nullptr;
   p.has_outF = a.outF != nullptr;
   {
-    const char* e = getenv("KB_TN_DBG");
+    const char* e = KB_DEV_ENV("KB_TN_DBG");
     p.dbg = e ? atoi(e) : 0;
   }
 

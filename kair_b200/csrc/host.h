@@ -59,6 +59,15 @@ inline cudaError_t launch_pdl(void (*kern)(const P), int grid, int block, size_t
   return launch_pdl(kern, dim3((unsigned)grid), block, smem, st, p);
 }
 
+// Development hooks (ablation masks KB_*_DBG, clock64 timelines KB_*_TS, KB_NT_BM) are compiled only into builds made
+// with -DKB_DEVEL (python -m kair_b200.build --devel): a stray environment variable must never change what a
+// production launch computes or insert a cudaMalloc / synchronous copy into it.
+#ifdef KB_DEVEL
+#define KB_DEV_ENV(name) getenv(name)
+#else
+#define KB_DEV_ENV(name) ((const char*)nullptr)
+#endif
+
 int sm_count();
 int check_device();  // 0 if current device is sm_100; error otherwise
 

@@ -58,7 +58,7 @@ class DnCNN(nn.Module):
         x = x.float().contiguous()
         eng = self.engine(x.device)
         params = list(eng.P.values())
-        train = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
         plan = eng.plan(x.shape[0], x.shape[2], x.shape[3], train, self.training)
         if train:
             return ConvNetFunction.apply(x, plan, *params)

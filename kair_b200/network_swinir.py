@@ -287,6 +287,7 @@ class SwinIR(nn.Module):
             self._engine = SwinIREngine(self._spec, params, device, ops=self._ops)
             self._engine_key = key
         self._engine.grad_hook = (lambda flat: _parallel.allreduce_flat(self, flat))
+        self._engine.grad_slice_hook = (lambda flat, lo, hi: _parallel.allreduce_slice(self, flat, lo, hi))
         return self._engine
 
     def forward(self, x):
@@ -298,7 +299,7 @@ class SwinIR(nn.Module):
         self.mean = self.mean.type_as(x)
         eng = self.engine(x.device)
         params = list(eng.P.values())
-        train = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        train = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in params))
         plan = eng.plan(x.shape[0], x.shape[2], x.shape[3], train, self._precision, self._terms)
         if train:
             plan.set_drop_path(self._drop_rates if self.training else [0.0] * len(self._drop_rates))

@@ -59,7 +59,7 @@ class UNetRes(nn.Module):
         x0 = x0.float().contiguous()
         eng = self.engine(x0.device)
         params = list(eng.P.values())
-        train = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        train = torch.is_grad_enabled() and (x0.requires_grad or any(p.requires_grad for p in params))
         plan = eng.plan(x0.shape[0], x0.shape[2], x0.shape[3], train)
         if train:
             return ConvNetFunction.apply(x0, plan, *params)

@@ -46,8 +46,50 @@ class _RawLaunch:
             _lib.check(rc, self.name)
 
 
-def stream_handle():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+class LaunchList:
+    """A whole pass (forward or backward list of a plan) replayed by ONE FFI call: kair_run_list walks a C array of
+    (entry point id, argument struct) pairs, so the per-pass host cost is one ctypes crossing instead of one per
+    kernel.  The Launch objects stay referenced (they own the argument structs and the tensors those point into)."""
+
+    __slots__ = ("launches", "array", "n", "fn")
+
+    def __init__(self, launches):
+        lib = _lib.load()
+        self.launches = list(launches)
+        self.n = len(self.launches)
+        self.array = (_S["kair_launch"] * max(self.n, 1))()
+        for i, l in enumerate(self.launches):
+            op = lib.kair_op_id(l.name.encode())
+            if op < 0:
+                raise RuntimeError("kair_b200: %s cannot be part of a launch list" % l.name)
+            self.array[i].op = op
+            self.array[i].args = ctypes.cast(ctypes.pointer(l.args), ctypes.c_void_p)
+        self.fn = lib.kair_run_list
+
+    def run(self, stream):
+        rc = self.fn(self.array, self.n, stream)
+        if rc != 0:
+            _lib.check(rc, "kair_run_list")
+
+    def __len__(self):
+        return self.n
+
+    def __iter__(self):
+        return iter(self.launches)
+
+
+def make_list(launches):
+    return LaunchList(launches)
+
+
+def stream_handle(device=None):
+    """the current stream of `device` (default: the current device) as the `void* stream` argument of the C ABI"""
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def device_guard(device):
+    """context manager that makes `device` current: the launchers use the current device (cudaGetDevice) and stream"""
+    return torch.cuda.device(device)
 
 
 def zeros(shape, dtype, device):
@@ -402,9 +444,11 @@ def build_ln_bwd_split(g, xhat, rstd, outF, *, C, terms, resid=None, out=None, r
 def build_add_inplace(y, x, yb=None):
     """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")
-    fn = _lib.load().kair_add_inplace
-    py, px, pyb, n = _ptr(y), _ptr(x), _ptr(yb), y.numel()
-    return _RawLaunch("kair_add_inplace", lambda stream: fn(py, px, pyb, n, stream), keep=(y, x, yb))
+    if not (y.is_contiguous() and x.is_contiguous() and (yb is None or yb.is_contiguous())):
+        raise RuntimeError("kair_b200: add_inplace operands must be contiguous")
+    a = _S["kair_add_args"]()
+    a.y, a.x, a.yb, a.n = _ptr(y), _ptr(x), _ptr(yb), y.numel()
+    return Launch("kair_add_inplace_s", a)
 
 
 # ------------------------------------------------------------------------------------------------ conv-net helpers
@@ -658,9 +702,13 @@ def adam_ema_set_grads(launch, g, tables):
 
 
 def build_copy(dst, src):
-    """dst <- src on the current stream (device-to-device plumbing for a handful of values, e.g. a bias gradient
-    picked out of a column-sum vector); no kernel of ours is involved."""
-    return _RawLaunch("copy", lambda stream: (dst.copy_(src), 0)[1], keep=(dst, src))
+    """dst <- src on the stream (cudaMemcpyAsync device-to-device: a handful of values, e.g. a bias gradient picked out of
+    a column-sum vector); listable like every other launch."""
+    if not (dst.is_contiguous() and src.is_contiguous()) or dst.dtype != src.dtype or dst.numel() != src.numel():
+        raise RuntimeError("kair_b200: copy needs contiguous tensors of one dtype and size")
+    a = _S["kair_memcpy_args"]()
+    a.dst, a.src, a.bytes = _ptr(dst), _ptr(src), dst.numel() * dst.element_size()
+    return Launch("kair_memcpy_d2d", a)
 
 
 # ------------------------------------------------------------------------------------------------ lifetimes

@@ -34,6 +34,36 @@ def _round_up(x, m):
     return (x + m - 1) // m * m
 
 
+_forward_clock = [0]
+
+
+def pick_plan(plans, key, max_shapes, make):
+    """The plan serving `key`.  A training plan owns ONE set of saved activations, so while its backward is pending
+    (`busy`, set by the autograd Function) a second forward of the same shape gets a second plan instance instead of
+    overwriting them: `y1 = m(x1); y2 = m(x2); (l(y1) + l(y2)).backward()` works like it does for the reference.  At
+    most two instances per shape are kept; a third pending forward reuses the older one, whose own backward then
+    raises (generation check) instead of returning gradients of the wrong activations."""
+    slots = plans.get(key)
+    if slots is None:
+        if len(plans) >= max_shapes:   # bound the workspace kept alive by stale shapes
+            plans.pop(next(iter(plans)))
+        slots = plans[key] = []
+    for p in slots:
+        if not getattr(p, "busy", False):
+            return p
+    if len(slots) < 2:
+        p = make()
+        p.busy = False
+        slots.append(p)
+        return p
+    return min(slots, key=lambda q: getattr(q, "busy_since", 0))
+
+
+def mark_busy(plan):
+    _forward_clock[0] += 1
+    plan.busy, plan.busy_since = True, _forward_clock[0]
+
+
 class SwinIRSpec:
     """The constructor arguments of models/network_swinir.py:646-652 that shape the computation."""
 
@@ -255,25 +285,12 @@ class SwinIREngine:
         if precision == "fp32":
             from . import swinir_engine_fp32 as f32m
             Wt = f32m.weight_state_fp32(self, train, terms)
-            key = (B, H, W, bool(train), terms)
-            p = self._plans_fp32.get(key)
-            if p is None:
-                if len(self._plans_fp32) >= 2:
-                    self._plans_fp32.pop(next(iter(self._plans_fp32)))
-                p = f32m.PlanF32(self, Wt, B, H, W, bool(train), terms)
-                self._plans_fp32[key] = p
-            return p
+            return pick_plan(self._plans_fp32, (B, H, W, bool(train), terms), 2,
+                             lambda: f32m.PlanF32(self, Wt, B, H, W, bool(train), terms))
         if precision != "bf16":
             raise ValueError("kair_b200: precision must be 'bf16' or 'fp32', got %r" % (precision,))
-        key = (B, H, W, bool(train))
         Wt = self._weight_state(train)
-        p = self._plans.get(key)
-        if p is None:
-            if len(self._plans) >= 4:  # bound the workspace kept alive by stale shapes
-                self._plans.pop(next(iter(self._plans)))
-            p = _Plan(self, Wt, B, H, W, bool(train))
-            self._plans[key] = p
-        return p
+        return pick_plan(self._plans, (B, H, W, bool(train)), 4, lambda: _Plan(self, Wt, B, H, W, bool(train)))
 
 
 class _Plan:
@@ -485,6 +502,55 @@ class _Plan:
         du, datt, dqkv = bf(T, Fp), bf(T, HP), bf(T, QP)
         blk_names = eng._block_names()
 
+        cn = Wt["conv_names"]
+        keys = list(P.keys())
+        offs, acc_ = {}, 0
+        for k_, n_ in zip(keys, sizes):
+            offs[k_] = (acc_, acc_ + n_)
+            acc_ += n_
+
+        def rstb_range(i):
+            """[lo, hi) of RSTB i's parameters in the flat gradient buffer (contiguous in state_dict order)"""
+            ks = [k_ for k_ in keys if k_.startswith("layers.%d." % i)]
+            lo, hi = offs[ks[0]][0], offs[ks[-1]][1]
+            assert hi - lo == sum(offs[k_][1] - offs[k_][0] for k_ in ks)
+            return lo, hi
+
+        def unpack_convs(c0, c1):
+            names_ = cn[c0:c1]
+            if not three:
+                return [o.build_unpack_conv_grad(dWconv[c0:c1], [G[n + ".weight"] for n in names_],
+                                                 [G[n + ".bias"] for n in names_], O=C, I=C, I_pad=Cp, ones_col=C,
+                                                 center_tap=4)]
+            gw = lambda sfx: [G[n + sfx + ".weight"] for n in names_]
+            gb = lambda sfx: [G[n + sfx + ".bias"] for n in names_]
+            return [o.build_unpack_conv_grad(dWa[c0:c1], gw(".0"), gb(".0"), O=Cq, I=C, I_pad=Cp, ones_col=C, center_tap=4),
+                    o.build_unpack_conv_grad(dWb[c0:c1], gw(".2"), gb(".2"), O=Cq, I=Cq, I_pad=Cqp, taps=1, ones_col=Cq,
+                                             center_tap=0),
+                    o.build_unpack_conv_grad(dWconv[c0:c1], gw(".4"), gb(".4"), O=C, I=Cq, I_pad=Cqp, ones_col=Cq,
+                                             center_tap=4)]
+
+        def unpack_rstb(i, l0, l1):
+            """packed weight gradients of blocks [l0, l1) and of the convolution closing RSTB i -> dW, db, dgamma, dbeta"""
+            names_ = blk_names[l0:l1]
+            gl = lambda suffix: [G[bn_ + suffix] for bn_ in names_]
+            pl = lambda suffix: [P[bn_ + suffix] for bn_ in names_]
+            return [
+                o.build_unpack_linear_grad(dWqkv[l0:l1], pl("attn.qkv.weight"), pl("norm1.weight"), pl("norm1.bias"),
+                                           gl("attn.qkv.weight"), gl("attn.qkv.bias") if s.qkv_bias else None,
+                                           gl("norm1.weight"), gl("norm1.bias"), eng.map_qkv, eng.map_c, eng.scale_qkv,
+                                           out_f=3 * C, in_f=C, ones_col=C),
+                o.build_unpack_linear_grad(dWproj[l0:l1], pl("attn.proj.weight"), None, None, gl("attn.proj.weight"),
+                                           gl("attn.proj.bias"), None, None, eng.map_c, eng.map_h, None, out_f=C, in_f=C,
+                                           ones_col=eng.hd),
+                o.build_unpack_linear_grad(dWfc1[l0:l1], pl("mlp.fc1.weight"), pl("norm2.weight"), pl("norm2.bias"),
+                                           gl("mlp.fc1.weight"), gl("mlp.fc1.bias"), gl("norm2.weight"), gl("norm2.bias"),
+                                           eng.map_f, eng.map_c, None, out_f=s.hidden, in_f=C, ones_col=C),
+                o.build_unpack_linear_grad(dWfc2[l0:l1], pl("mlp.fc2.weight"), None, None, gl("mlp.fc2.weight"),
+                                           gl("mlp.fc2.bias"), None, None, eng.map_c, eng.map_f, None, out_f=C,
+                                           in_f=s.hidden, ones_col=s.hidden)] + unpack_convs(i, i + 1)
+
+        marks = []   # (number of backward launches after which the slice is final, lo, hi) per RSTB
         bwd = []
         inv = 1.0 / rng
         ci = s.in_chans
@@ -603,14 +669,20 @@ class _Plan:
             bwd.append(o.build_add_inplace(R[cur][0], R[dt][0], R[cur][1]))
             dt = cur
             l_end -= depth
+            # every gradient of RSTB i is now complete in its packed form: map it onto the parameters' own layouts and
+            # mark the (contiguous) slice of the flat gradient buffer as ready, so that a data-parallel hook can start
+            # its all-reduce while the earlier RSTBs are still in their backward pass (model_base.py:113-119: DDP
+            # overlaps per bucket)
+            bwd += unpack_rstb(i, l_end, l_end + depth)
+            marks.append((len(bwd), ) + rstb_range(i))
         if s.patch_norm:
-            dfirst_b = R[(dt + 1) % 3][1]
+            dfirst_b, dfirst_f = R[(dt + 1) % 3][1], R[(dt + 1) % 3][0]
             bwd.append(o.build_layernorm_bwd(first, mean0, rstd0, P["patch_embed.norm.weight"],
                                              G["patch_embed.norm.weight"], G["patch_embed.norm.bias"], C=C,
-                                             dy_f32=R[dt][0], dx_add=dresf, dx_bf16=dfirst_b))
+                                             dy_f32=R[dt][0], dx_add=dresf, dx_f32=dfirst_f, dx_bf16=dfirst_b))
         else:
             bwd.append(o.build_add_inplace(R[dt][0], dresf, R[dt][1]))
-            dfirst_b = R[dt][1]
+            dfirst_b, dfirst_f = R[dt][1], R[dt][0]
         # conv_first weight gradient = d(first)^T . im2col(input) on the tensor cores (columns tap*7 + c, ones -> bias)
         xcol, dWcf = bf(T, 64), f32(1, Cp, 64)
         self._thin += (dWcf,)
@@ -618,36 +690,10 @@ class _Plan:
         bwd.append(o.build_gemm_nt(dfirst_b, xcol, dWcf[0], n1=Cp, n2=64, bn=64))
         bwd.append(o.build_unpack_conv_grad(dWcf, [G["conv_first.weight"]], [G["conv_first.bias"]], O=C, I=ci, I_pad=7,
                                             ones_col=ci, center_tap=4, dwp_pitch=64))
-        gl = lambda suffix: [G[bn_ + suffix] for bn_ in blk_names]
-        pl = lambda suffix: [P[bn_ + suffix] for bn_ in blk_names]
-        bwd.append(o.build_unpack_linear_grad(dWqkv, pl("attn.qkv.weight"), pl("norm1.weight"), pl("norm1.bias"),
-                                              gl("attn.qkv.weight"),
-                                              gl("attn.qkv.bias") if s.qkv_bias else None,
-                                              gl("norm1.weight"), gl("norm1.bias"), eng.map_qkv, eng.map_c,
-                                              eng.scale_qkv, out_f=3 * C, in_f=C, ones_col=C))
-        bwd.append(o.build_unpack_linear_grad(dWproj, pl("attn.proj.weight"), None, None, gl("attn.proj.weight"),
-                                              gl("attn.proj.bias"), None, None, eng.map_c, eng.map_h, None,
-                                              out_f=C, in_f=C, ones_col=eng.hd))
-        bwd.append(o.build_unpack_linear_grad(dWfc1, pl("mlp.fc1.weight"), pl("norm2.weight"), pl("norm2.bias"),
-                                              gl("mlp.fc1.weight"), gl("mlp.fc1.bias"), gl("norm2.weight"),
-                                              gl("norm2.bias"), eng.map_f, eng.map_c, None, out_f=s.hidden, in_f=C,
-                                              ones_col=C))
-        bwd.append(o.build_unpack_linear_grad(dWfc2, pl("mlp.fc2.weight"), None, None, gl("mlp.fc2.weight"),
-                                              gl("mlp.fc2.bias"), None, None, eng.map_c, eng.map_f, None, out_f=C,
-                                              in_f=s.hidden, ones_col=s.hidden))
-        cn = Wt["conv_names"]
-        if not three:
-            bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
-                                                O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
-        else:
-            gw = lambda sfx: [G[n + sfx + ".weight"] for n in cn]
-            gb = lambda sfx: [G[n + sfx + ".bias"] for n in cn]
-            bwd.append(o.build_unpack_conv_grad(dWa, gw(".0"), gb(".0"), O=Cq, I=C, I_pad=Cp, ones_col=C, center_tap=4))
-            bwd.append(o.build_unpack_conv_grad(dWb, gw(".2"), gb(".2"), O=Cq, I=Cq, I_pad=Cqp, taps=1, ones_col=Cq,
-                                                center_tap=0))
-            bwd.append(o.build_unpack_conv_grad(dWconv, gw(".4"), gb(".4"), O=C, I=Cq, I_pad=Cqp, ones_col=Cq,
-                                                center_tap=4))
+        bwd += unpack_convs(nl, nl + 1)     # conv_after_body
         self.bwd = bwd + unpack_head
+        self.bwd_marks = marks
+        self._dx_spec = dict(dhead=dfirst_f, W=cf_w, C=C, pitch=Cp, scale=rng, skip=not up)
 
     # ------------------------------------------------------------------------------------------ execution
     def set_drop_path(self, rates, generator=None):
@@ -664,26 +710,47 @@ class _Plan:
         self.dp.copy_((u < keep).float() / keep)
         self.dp_active = True
 
+    def _lists(self):
+        """the launch lists as C arrays (one FFI call per pass / per segment), built on first use"""
+        ls = getattr(self, "_launch_lists", None)
+        if ls is None:
+            o = self.eng.ops
+            segs = []
+            if self.bwd is not None:
+                start = 0
+                for end, lo, hi in getattr(self, "bwd_marks", []):
+                    segs.append((o.make_list(self.bwd[start:end]), (lo, hi)))
+                    start = end
+                segs.append((o.make_list(self.bwd[start:]), None))
+            ls = self._launch_lists = (o.make_list(self.fwd), segs)
+        return ls
+
     def run_forward(self, x):
-        st = self.eng.ops.stream_handle()
-        self.eng.refresh_weights(self.Wt, st)
-        self.img.copy_(x)
-        for l in self.fwd:
-            l.run(st)
+        o = self.eng.ops
+        with o.device_guard(self.img.device):   # the launchers use the current device and its current stream
+            st = o.stream_handle(self.img.device)
+            self.eng.refresh_weights(self.Wt, st)
+            self.img.copy_(x)
+            self._lists()[0].run(st)
         self.generation += 1
         return self.out.clone()
 
     def run_backward(self, dout):
-        st = self.eng.ops.stream_handle()
-        self.dout.copy_(dout)
-        self.gflat.zero_()
-        self.dwflat.zero_()
-        for t in self._thin:
-            t.zero_()
-        for l in self.bwd:
-            l.run(st)
-        if self.eng.grad_hook is not None:
-            self.eng.grad_hook(self.gflat)
+        o = self.eng.ops
+        with o.device_guard(self.img.device):
+            st = o.stream_handle(self.img.device)
+            self.dout.copy_(dout)
+            self.gflat.zero_()
+            self.dwflat.zero_()
+            for t in self._thin:
+                t.zero_()
+            slice_hook = getattr(self.eng, "grad_slice_hook", None)
+            for lst, ready in self._lists()[1]:
+                lst.run(st)
+                if ready is not None and slice_hook is not None:
+                    slice_hook(self.gflat, ready[0], ready[1])
+            if self.eng.grad_hook is not None:
+                self.eng.grad_hook(self.gflat)
         flat = self.gflat.clone()
         grads, off = [], 0
         for p in self.eng.P.values():
@@ -693,12 +760,38 @@ class _Plan:
         return grads
 
 
+def input_grad(plan, dout):
+    """d(loss)/d(input image) of a plan whose backward list has just run: the transposed first convolution applied to
+    the gradient of its output (kair_conv_out_fwd with the spatially flipped, channel-swapped conv_first weights --
+    autograd of network_swinir.py:809-813 / network_dncnn.py:63 / network_unet.py:25), times img_range, plus the global
+    skip `x + ...` (:835) where the network has one.  Built on first use: training loops do not need it."""
+    sp = plan._dx_spec
+    o, W = plan.eng.ops, sp["W"]
+    st = getattr(plan, "_dx_state", None)
+    if st is None:
+        dev = plan.img.device
+        ci = W.shape[1]
+        Wt = torch.zeros(ci, W.shape[0], 3, 3, dtype=torch.float32, device=dev)
+        zc = torch.zeros(ci, dtype=torch.float32, device=dev)
+        dimg = torch.zeros_like(plan.img)
+        skip = plan.dout if sp["skip"] else None
+        launch = o.build_conv_out_fwd(sp["dhead"], Wt, None, dimg, zc, C=sp["C"], pitch=sp["pitch"],
+                                      out_scale=sp["scale"], skip=skip, skip_mean=zc if skip is not None else None,
+                                      skip_scale=1.0 / sp["scale"])
+        st = plan._dx_state = (Wt, dimg, launch)
+    Wt, dimg, launch = st
+    Wt.copy_(W.detach().flip(2, 3).transpose(0, 1))
+    launch.run(o.stream_handle())
+    return dimg.clone()
+
+
 class SwinIRFunction(torch.autograd.Function):
     """forward/backward pair over the whole network (the reference's plugin convention, models/op/fused_act.py:21-72)."""
 
     @staticmethod
     def forward(ctx, x, plan, *params):
         out = plan.run_forward(x)
+        mark_busy(plan)
         ctx.plan = plan
         ctx.generation = plan.generation
         return out
@@ -707,7 +800,9 @@ class SwinIRFunction(torch.autograd.Function):
     def backward(ctx, dout):
         plan = ctx.plan
         if plan.generation != ctx.generation:
-            raise RuntimeError("kair_b200 SwinIR: backward() called after another forward() of the same shape "
-                               "overwrote the saved activations; run forward and backward in pairs")
+            raise RuntimeError("kair_b200 SwinIR: backward() called after two later forward() calls of the same shape "
+                               "overwrote the saved activations (two sets are kept per shape)")
+        plan.busy = False
         grads = plan.run_backward(dout.contiguous())
-        return (None, None) + tuple(grads)
+        dx = input_grad(plan, dout) if ctx.needs_input_grad[0] else None
+        return (dx, None) + tuple(grads)

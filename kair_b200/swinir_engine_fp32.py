@@ -380,3 +380,4 @@ class PlanF32(_Plan):
         bwd.append(o.build_unpack_conv_grad(dWconv, [G[n + ".weight"] for n in cn], [G[n + ".bias"] for n in cn],
                                             O=C, I=C, I_pad=Cp, ones_col=C, center_tap=4))
         self.bwd = bwd
+        self._dx_spec = dict(dhead=dfirst, W=cf_w, C=C, pitch=Cp, scale=rng, skip=True)

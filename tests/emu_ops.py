@@ -24,8 +24,32 @@ class EmuLaunch:
         self.fn()
 
 
-def stream_handle():
+def stream_handle(device=None):
     return None
+
+
+class _EmuList:
+    def __init__(self, launches):
+        self.launches = list(launches)
+
+    def run(self, stream=None):
+        for l in self.launches:
+            l.run(stream)
+
+    def __len__(self):
+        return len(self.launches)
+
+    def __iter__(self):
+        return iter(self.launches)
+
+
+def make_list(launches):
+    return _EmuList(launches)
+
+
+def device_guard(device):
+    import contextlib
+    return contextlib.nullcontext()
 
 
 def zeros(shape, dtype, device):

@@ -35,8 +35,8 @@ def _build(net):
         shape, out_c = (4, 1, 16, 16), 1
     else:
         from kair_b200.network_swinir import SwinIR
-        model = SwinIR(upscale=1, in_chans=1, img_size=16, window_size=8, img_range=1.0, depths=[2], embed_dim=180,
-                       num_heads=[6], mlp_ratio=2, upsampler="", resi_connection="1conv", drop_path_rate=0.0)
+        model = SwinIR(upscale=1, in_chans=1, img_size=16, window_size=8, img_range=1.0, depths=[2, 2], embed_dim=180,
+                       num_heads=[6, 6], mlp_ratio=2, upsampler="", resi_connection="1conv", drop_path_rate=0.0)
         shape, out_c = (2, 1, 16, 16), 1
     model._ops = emu_ops
     g = torch.Generator().manual_seed(11)

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 # bf16 mode: 2 x measured (profiles/parity_r2.json); fp32 mode: north_star's bounds
 TOL = {
-    ("cfg2", "bf16"): dict(fwd=2e-2, dpsnr=0.02, rel_all=1.1e-2, rel_worst=3.5e-2, cos_min=0.9997),
+    ("cfg2", "bf16"): dict(fwd=2e-2, dpsnr=0.02, rel_all=1.2e-2, rel_worst=2e-2, cos_min=0.9999),
     ("cfg3", "bf16"): dict(fwd=2e-2, dpsnr=0.02),
     ("cfg4", "bf16"): dict(fwd=2e-2, dpsnr=0.02, rel_all=7e-3, rel_worst=3.5e-2, cos_min=0.9997),
     ("cfg5", "bf16"): dict(fwd=2e-2, dpsnr=0.02),

@@ -345,3 +345,49 @@ def test_amp_gradscaler_clip_and_frozen_params():
     scaler.update()
     for k, p in model.named_parameters():
         assert torch.equal(p.detach(), before[k]) == (k in frozen or plain[k].abs().max().item() == 0), k
+
+
+@pytest.mark.parametrize("precision,tol", [("bf16", 1.5e-1), ("fp32", 1e-3)])
+def test_input_gradient_and_two_forwards(precision, tol):
+    """d(loss)/d(x) through the module (frozen net, plug-and-play use) vs autograd through the oracle, and two forwards
+    of one shape before a single backward (two activation sets per shape)."""
+    import golden_cases as gc
+    from kair_b200.network_swinir import SwinIR
+    case = gc.CASES["swinir_m_gray32"]
+    sd, x, tgt = gc.state_and_io(case)
+    xr = x.clone().requires_grad_(True)
+    gc.loss_fn(case)(gc.oracle_forward(case, sd, xr), tgt).backward()
+    model = SwinIR(drop_path_rate=0.0, **case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().set_precision(precision)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    xm = x.clone().cuda().requires_grad_(True)
+    gc.loss_fn(case)(model(xm), tgt.cuda()).backward()
+    assert _rel_l2(xm.grad.cpu(), xr.grad) < tol, _rel_l2(xm.grad.cpu(), xr.grad)
+    for p in model.parameters():
+        p.requires_grad_(True)
+    x2 = x.flip(3).contiguous()
+    sdg = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point) for k, v in sd.items()}
+    (gc.oracle_forward(case, sdg, x).square().mean() + gc.oracle_forward(case, sdg, x2).abs().mean()).backward()
+    y1, y2 = model(x.cuda()), model(x2.cuda())
+    (y1.square().mean() + y2.abs().mean()).backward()
+    worst = max(_rel_l2(p.grad.cpu(), sdg[k].grad) for k, p in model.named_parameters())
+    assert worst < (6e-2 if precision == "bf16" else 1e-3), worst
+
+
+def test_launch_list_is_one_ffi_call_and_reports_failures():
+    """kair_run_list replays a plan's pass in one call; a failing entry is reported with its index and name"""
+    import ctypes
+    from kair_b200 import _lib, ops
+    lib = _lib.load()
+    assert lib.kair_op_id(b"kair_gemm_tn") >= 0 and lib.kair_op_id(b"kair_last_error") == -1
+    y, xx = torch.ones(1024, device="cuda"), torch.full((1024,), 2.0, device="cuda")
+    lst = ops.make_list([ops.build_add_inplace(y, xx), ops.build_add_inplace(y, xx)])
+    lst.run(ops.stream_handle())
+    torch.cuda.synchronize()
+    assert torch.equal(y, torch.full((1024,), 5.0, device="cuda"))
+    bad = ops.build_add_inplace(y, xx)
+    bad.args.n = 3          # not a multiple of 4: the launcher refuses
+    with pytest.raises(RuntimeError, match="launch 1"):
+        ops.make_list([ops.build_add_inplace(y, xx), bad]).run(ops.stream_handle())
