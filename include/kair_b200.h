@@ -90,6 +90,49 @@ typedef struct kair_gemm_tn_args {
 int kair_gemm_tn(const kair_gemm_tn_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * kair_mlp_fused: the token-local MLP half of a Swin block in one launch (Mlp.forward, network_swinir.py:24-30, with the
+ * residual add / DropPath of :277 and, optionally, the LayerNorm that follows, :245):
+ *     u = X W1^T + b1;  g = gelu_erf(u);  v = (g W2^T + b2) * acc_scale[sample] + resid
+ *     ln != 0: outF = v, outB = bf16((v - mean) * rstd) (ones_col forced to 1), rowstat = rstd
+ *     ln == 0: exactly one of outF = v / outB = bf16(v) (ones_col forced to 1)
+ * The 2C-wide hidden activations stay in shared memory / TMEM (the unfused pair of kair_gemm_tn launches writes u and
+ * g to HBM and re-reads g); outU / outG (optional, training plans) receive bf16(u) and bf16(g) once for the backward
+ * pass.  X is the un-affine normalised input (norm2's affine folded into W1 / b1 by kair_pack_linear); W1 [F][N] and
+ * W2 [N][F] are packed bf16 operands; N = padded channels (64, 192 or 256), F = 2N.  Same rounding points and k-order
+ * as the unfused pair: results are bit-identical to it.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_mlp_fused_args {
+  const void* X;        /* bf16 [M][x_pitch] */
+  int64_t x_pitch;
+  const void* W1;       /* bf16 [F][w1_pitch] */
+  int64_t w1_pitch;
+  const void* W2;       /* bf16 [N][w2_pitch] */
+  int64_t w2_pitch;
+  const float* bias1;   /* [F] or NULL */
+  const float* bias2;   /* [N] or NULL */
+  const float* resid;   /* fp32 [M][resid_pitch] or NULL */
+  int64_t resid_pitch;
+  float* outF;          /* fp32 [M][outF_pitch] or NULL */
+  int64_t outF_pitch;
+  void* outB;           /* bf16 [M][outB_pitch] or NULL */
+  int64_t outB_pitch;
+  void* outU;           /* bf16 [M][outU_pitch] or NULL: pre-activation (training) */
+  int64_t outU_pitch;
+  void* outG;           /* bf16 [M][outG_pitch] or NULL: GELU output with ones_col_g forced to 1 (training) */
+  int64_t outG_pitch;
+  float* rowstat;       /* [M] rstd (ln != 0) or NULL */
+  const float* acc_scale; /* per-sample DropPath scale or NULL */
+  int32_t tokens_per_sample;
+  int32_t M, N, F;
+  int32_t ln;           /* apply LayerNorm to v */
+  int32_t n_valid;      /* real channels (LayerNorm statistics) */
+  int32_t ones_col;     /* column of outB forced to 1.0, -1 for none */
+  int32_t ones_col_g;   /* column of g forced to 1.0 (fc2 bias gradient of the backward pass), -1 for none */
+  float ln_eps;
+} kair_mlp_fused_args;
+int kair_mlp_fused(const kair_mlp_fused_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * kair_gemm_nt: D[n1][taps*n2] += sum_t A[t][n1] * B[t (+tap shift)][n2]   (fp32 accumulate into D, which the
  * caller zero-fills).  The weight-gradient GEMM of nn.Linear / nn.Conv2d 3x3 (autograd of
  * network_swinir.py:19-21, 105-107, 465, 729); with a ones column in B it also yields the bias gradient.

@@ -44,6 +44,7 @@ int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
 int add_inplace_launch(float* y, const float* x, void* yb, long long n, cudaStream_t st);
 int split_terms_launch(const kair_split_args& a, cudaStream_t st);
+int mlp_fused_launch(const kair_mlp_fused_args& a, cudaStream_t st);
 int ln_bwd_split_launch(const kair_ln_bwd_split_args& a, cudaStream_t st);
 }
 
@@ -127,6 +128,7 @@ KB_WRAP(kair_pixel_shuffle_out_bwd, kair_shuffle_out_args, pixel_shuffle_out_bwd
 KB_WRAP(kair_pixel_shuffle_bwd, kair_shuffle_args, pixel_shuffle_bwd_launch)
 KB_WRAP(kair_upsample_nearest2_bwd, kair_shuffle_args, upsample_nearest2_bwd_launch)
 KB_WRAP(kair_split_terms, kair_split_args, split_terms_launch)
+KB_WRAP(kair_mlp_fused, kair_mlp_fused_args, mlp_fused_launch)
 KB_WRAP(kair_ln_bwd_split, kair_ln_bwd_split_args, ln_bwd_split_launch)
 #undef KB_WRAP
 
@@ -173,7 +175,7 @@ const KbOp kb_ops[] = {
     KB_OP(kair_bn_bwd_apply), KB_OP(kair_bn_fold), KB_OP(kair_pixel_shuffle), KB_OP(kair_upsample_nearest2),
     KB_OP(kair_pixel_shuffle_out), KB_OP(kair_pixel_loss), KB_OP(kair_adam_ema), KB_OP(kair_pixel_shuffle_out_bwd),
     KB_OP(kair_pixel_shuffle_bwd), KB_OP(kair_upsample_nearest2_bwd), KB_OP(kair_split_terms),
-    KB_OP(kair_ln_bwd_split), KB_OP(kair_add_inplace_s), KB_OP(kair_memcpy_d2d),
+    KB_OP(kair_ln_bwd_split), KB_OP(kair_add_inplace_s), KB_OP(kair_memcpy_d2d), KB_OP(kair_mlp_fused),
 };
 #undef KB_OP
 constexpr int kb_n_ops = (int)(sizeof(kb_ops) / sizeof(kb_ops[0]));

@@ -159,6 +159,31 @@ def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.
     return Launch("kair_gemm_tn", a)
 
 
+def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF=None, outB=None, outU=None, outG=None,
+                    rowstat=None, acc_scale=None, tokens_per_sample=0, ln=True, n_valid=0, ones_col=-1, ones_col_g=-1,
+                    ln_eps=1e-5):
+    """fc1 + GELU + fc2 + DropPath + residual (+ LayerNorm) of a Swin block's MLP half in one launch; the hidden
+    activations stay on chip (outU / outG: optional bf16 copies for a backward pass).  See kair_b200.h."""
+    _req(X, torch.bfloat16, "X"); _req(W1, torch.bfloat16, "W1"); _req(W2, torch.bfloat16, "W2")
+    _req(bias1, torch.float32, "bias1"); _req(bias2, torch.float32, "bias2"); _req(resid, torch.float32, "resid")
+    _req(outF, torch.float32, "outF"); _req(outB, torch.bfloat16, "outB"); _req(outU, torch.bfloat16, "outU")
+    _req(outG, torch.bfloat16, "outG"); _req(rowstat, torch.float32, "rowstat"); _req(acc_scale, torch.float32, "acc_scale")
+    a = _S["kair_mlp_fused_args"]()
+    a.X = _ptr(X); a.x_pitch = _pitch(X)
+    a.W1 = _ptr(W1); a.w1_pitch = _pitch(W1)
+    a.W2 = _ptr(W2); a.w2_pitch = _pitch(W2)
+    a.bias1 = _ptr(bias1); a.bias2 = _ptr(bias2)
+    a.resid = _ptr(resid); a.resid_pitch = _pitch(resid)
+    a.outF = _ptr(outF); a.outF_pitch = _pitch(outF)
+    a.outB = _ptr(outB); a.outB_pitch = _pitch(outB)
+    a.outU = _ptr(outU); a.outU_pitch = _pitch(outU)
+    a.outG = _ptr(outG); a.outG_pitch = _pitch(outG)
+    a.rowstat = _ptr(rowstat); a.acc_scale = _ptr(acc_scale); a.tokens_per_sample = tokens_per_sample
+    a.M = X.shape[0]; a.N = N; a.F = F
+    a.ln = 1 if ln else 0; a.n_valid = n_valid; a.ones_col = ones_col; a.ones_col_g = ones_col_g; a.ln_eps = ln_eps
+    return Launch("kair_mlp_fused", a)
+
+
 def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B"); _req(D, torch.float32, "D")

@@ -31,6 +31,12 @@ def describe(launch, real_dims):
         by += 4.0 * a.M * r(a.N) * (1 if a.resid else 0) + 2.0 * a.M * r(a.N) * (1 if a.aux else 0)
         by += 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
         return tag, 2.0 * a.M * r(a.N) * kr * taps, by
+    if name == "mlp_fused":
+        tag = "mlp_fused[N%d F%d %s%s]" % (a.N, a.F, "resid_ln" if a.ln else "linear", " +u,g" if a.outU else "")
+        rn, rf = r(a.N), r(a.F)
+        by = 2.0 * a.M * rn + 4.0 * a.M * rn * ((1 if a.resid else 0) + (1 if a.outF else 0))
+        by += 2.0 * a.M * rn * (1 if a.outB else 0) + 2.0 * a.M * rf * ((1 if a.outU else 0) + (1 if a.outG else 0))
+        return tag, 4.0 * a.M * rn * rf, by
     if name == "gemm_nt":
         taps = 9 if a.conv else 1
         tag = "gemm_nt[%s n1=%d n2=%d]" % ("conv3x3" if a.conv else "dense", a.n1, a.n2 * taps)
@@ -102,6 +108,9 @@ def write_bytes(launch, real_dims):
     a = getattr(launch, "args", None)
     name = launch.name.replace("kair_", "")
     r = lambda n: real_dims.get(int(n), int(n))
+    if name == "mlp_fused":
+        return (4.0 * a.M * r(a.N) * (1 if a.outF else 0) + 2.0 * a.M * r(a.N) * (1 if a.outB else 0) +
+                2.0 * a.M * r(a.F) * ((1 if a.outU else 0) + (1 if a.outG else 0)))
     if name == "gemm_tn":
         return 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
     if name in ("window_attn_fwd", "window_attn_bwd"):

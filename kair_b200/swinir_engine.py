@@ -14,11 +14,17 @@ Reference arithmetic replaced (file:line in /root/reference): models/network_swi
 (WindowAttention.forward), :24-30 (Mlp.forward), and autograd's backward of all of them.
 """
 import math
+import os
 
 import torch
 
 from . import _dirty
 from . import ops as _real_ops
+
+# fc1 + GELU + fc2 + residual (+ LayerNorm) as one launch (kair_mlp_fused) instead of two kair_gemm_tn launches;
+# KAIR_B200_FUSE_MLP=0 keeps the unfused pair (A/B measurements; the results are bit-identical)
+FUSE_MLP = os.environ.get("KAIR_B200_FUSE_MLP", "1") != "0"
+
 
 def _tile(n, fused=False):
     """N tile of a GEMM with n output columns.  The fused epilogues (GELU, GELU', LayerNorm forward / backward) are
@@ -361,6 +367,9 @@ class _Plan:
         mean_t = eng.mean
         rng = s.img_range
 
+        fuse_mlp = FUSE_MLP and getattr(eng, "fuse_mlp", True) and Fp == 2 * Cp and Cp in (64, 192, 256)
+        self.fuse_mlp = fuse_mlp
+
         # ================================================================================ forward
         fwd = []
         fwd.append(o.build_conv_in_fwd(self.img, cf_w, cf_b, mean_t, rng, O=C, O_pad=Cp, pitch=Cp, out_f32=first))
@@ -384,6 +393,22 @@ class _Plan:
                 fwd.append(o.build_gemm_tn(S.att, Wt["proj"][l], N=Cp, K=HP, bn=_tile(Cp, True), mode=o.EPI_RESID_LN,
                                            bias=Wt["bproj"][l], resid=xin, outF=xs[0], outB=S.xh2, rowstat=S.r2,
                                            n_valid=C, ones_col=C, acc_scale=dpa(l), tokens_per_sample=tps))
+                if fuse_mlp:
+                    # the MLP half in one launch: u / g stay on chip (training plans keep one bf16 copy of each for
+                    # the backward pass), the epilogue is the residual add + the next block's LayerNorm
+                    nxt = blocks[l + 1] if j < depth - 1 else None
+                    fwd.append(o.build_mlp_fused(S.xh2, Wt["fc1"][l], Wt["fc2"][l], N=Cp, F=Fp, bias1=Wt["bfc1"][l],
+                                                 bias2=Wt["bfc2"][l], resid=xs[0],
+                                                 outF=xs[1] if nxt is not None else None,
+                                                 outB=nxt.xh1 if nxt is not None else x2b[i],
+                                                 outU=S.u if train else None, outG=S.g if train else None,
+                                                 rowstat=nxt.r1 if nxt is not None else None, acc_scale=dpm(l),
+                                                 tokens_per_sample=tps, ln=nxt is not None, n_valid=C, ones_col=C,
+                                                 ones_col_g=s.hidden))
+                    if nxt is not None:
+                        xin = xs[1]
+                    l += 1
+                    continue
                 fwd.append(o.build_gemm_tn(S.xh2, Wt["fc1"][l], N=Fp, K=Cp, bn=_tile(Fp, True), mode=o.EPI_GELU,
                                            bias=Wt["bfc1"][l], outB=S.g, outB2=S.u, ones_col=s.hidden))
                 if j < depth - 1:

@@ -186,6 +186,25 @@ def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.
     return EmuLaunch("kair_gemm_tn", run)
 
 
+def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF=None, outB=None, outU=None, outG=None,
+                    rowstat=None, acc_scale=None, tokens_per_sample=0, ln=True, n_valid=0, ones_col=-1, ones_col_g=-1,
+                    ln_eps=1e-5):
+    """stated as the unfused pair it replaces (kair_b200.h: bit-identical to it)"""
+    assert F == 2 * N and N in (64, 192, 256) and (outF is not None or outB is not None)
+    M = X.shape[0]
+    g = outG if outG is not None else torch.zeros(M, F, dtype=X.dtype)
+    first = build_gemm_tn(X, W1, N=F, K=N, bn=64, mode=EPI_GELU, bias=bias1, outB=g, outB2=outU, ones_col=ones_col_g)
+    second = build_gemm_tn(g, W2, N=N, K=F, bn=N, mode=EPI_RESID_LN if ln else EPI_LINEAR, bias=bias2, resid=resid,
+                           outF=outF, outB=outB, rowstat=rowstat if ln else None, n_valid=n_valid, ones_col=ones_col,
+                           acc_scale=acc_scale, tokens_per_sample=tokens_per_sample, ln_eps=ln_eps)
+
+    def run():
+        first.run()
+        second.run()
+
+    return EmuLaunch("kair_mlp_fused", run)
+
+
 def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
     assert n1 % 64 == 0 and n2 % bn == 0
 
