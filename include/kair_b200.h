@@ -565,6 +565,50 @@ int kair_pixel_shuffle_out_bwd(const kair_shuffle_out_args* args, void* stream);
 int kair_add_inplace(float* y, const float* x, void* yb, int64_t n, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * SPECT input pipeline and validation metrics (the fork's data path around the network: data/dataset_spect.py:57-132,
+ * utils/utils_spect.py:3-35, models/model_base.py:355-377, utils/utils_image.py:629-700, :833-865).
+ *   kair_spect_patches   one training batch from device-resident frame stacks [n_files][2][FH][FW] (the .dat layout:
+ *                        anterior, posterior): per sample (file, top, left, mode) -> posterior view mirrored
+ *                        (np.fliplr), P x P crop, augment_img mode 0..7, normalize_spect -> (B, 2, P, P) for L and H.
+ *   kair_spect_normalize normalize_spect (inverse = 0) / denormalize_spect (inverse = 1); method 0 log, 1 anscombe,
+ *                        2 linear, 3 identity.
+ *   kair_spect_metrics   one image (C, h, w) of de-normalised counts E (estimate) and H (reference):
+ *                        out[4c + 0] += sum (q(E) - q(H))^2 with q(x) = uint8(clip(x, 0, max_val) / max_val * 255)
+ *                        out[4c + 1] += sum over the valid region of the SSIM map of q(E), q(H) (11x11 Gaussian 1.5)
+ *                        out[4c + 2] += sum of the Poisson log-pmf of round(H) under mean max(E, 1e-9)
+ *                        (fp64 sums, caller zeroes `out` [C][4]; PSNR = 20 log10(255 / sqrt(out0 / (h w))),
+ *                         SSIM = out1 / ((h - 10)(w - 10)), pll = sum_c out2 / (C h w)).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_spect_patch_args {
+  const float* frames_L;  /* fp32 [n_files][2][FH][FW] or NULL */
+  const float* frames_H;
+  const int32_t* sample;  /* [B][4] = (file, top, left, mode) */
+  float* out_L;           /* (B, 2, P, P) or NULL */
+  float* out_H;
+  int32_t B, P, FH, FW, method;
+  float max_pixel;
+} kair_spect_patch_args;
+int kair_spect_patches(const kair_spect_patch_args* args, void* stream);
+
+typedef struct kair_spect_norm_args {
+  const float* x;
+  float* y;               /* may alias x */
+  int64_t n;
+  int32_t method, inverse;
+  float max_pixel;
+} kair_spect_norm_args;
+int kair_spect_normalize(const kair_spect_norm_args* args, void* stream);
+
+typedef struct kair_spect_metric_args {
+  const float* E;         /* (C, h, w) */
+  const float* H;
+  double* out;            /* [C][4], accumulated */
+  int32_t C, h, w;
+  float max_val;
+} kair_spect_metric_args;
+int kair_spect_metrics(const kair_spect_metric_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Launch lists.  A plan (one forward or backward pass of a network at a fixed shape) is a static sequence of the entry
  * points above with pre-filled argument structs; kair_run_list replays such a sequence in ONE call, so the host cost
  * of a pass is one FFI crossing instead of one per kernel (SwinIR-M training: 558 kernels per step).

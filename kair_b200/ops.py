@@ -466,6 +466,49 @@ def build_ln_bwd_split(g, xhat, rstd, outF, *, C, terms, resid=None, out=None, r
     return Launch("kair_ln_bwd_split", a)
 
 
+SPECT_METHODS = {"log": 0, "anscombe": 1, "linear": 2, "none": 3}
+
+
+def build_spect_patches(frames_L, frames_H, sample, out_L, out_H, *, patch, method, max_pixel):
+    """One SPECT training batch from device-resident frame stacks (see kair_b200.h)."""
+    ref = frames_L if frames_L is not None else frames_H
+    for t, n in ((frames_L, "frames_L"), (frames_H, "frames_H"), (out_L, "out_L"), (out_H, "out_H")):
+        _req(t, torch.float32, n)
+        if t is not None and not t.is_contiguous():
+            raise RuntimeError("kair_b200: spect_patches tensors must be contiguous")
+    _req(sample, torch.int32, "sample")
+    if ref.dim() != 4 or ref.shape[1] != 2 or sample.dim() != 2 or sample.shape[1] != 4 or not sample.is_contiguous():
+        raise RuntimeError("kair_b200: frames must be [n, 2, H, W] and sample [B, 4] int32")
+    a = _S["kair_spect_patch_args"]()
+    a.frames_L = _ptr(frames_L); a.frames_H = _ptr(frames_H); a.sample = _ptr(sample)
+    a.out_L = _ptr(out_L); a.out_H = _ptr(out_H)
+    a.B, a.P, a.FH, a.FW = sample.shape[0], patch, ref.shape[2], ref.shape[3]
+    a.method = SPECT_METHODS[method]; a.max_pixel = float(max_pixel)
+    return Launch("kair_spect_patches", a)
+
+
+def build_spect_normalize(x, y, *, method, max_pixel, inverse=False):
+    _req(x, torch.float32, "x"); _req(y, torch.float32, "y")
+    if not (x.is_contiguous() and y.is_contiguous()) or x.numel() != y.numel():
+        raise RuntimeError("kair_b200: spect_normalize needs contiguous tensors of one size")
+    a = _S["kair_spect_norm_args"]()
+    a.x = _ptr(x); a.y = _ptr(y); a.n = x.numel()
+    a.method = SPECT_METHODS[method]; a.inverse = 1 if inverse else 0; a.max_pixel = float(max_pixel)
+    return Launch("kair_spect_normalize", a)
+
+
+def build_spect_metrics(E, H, out, *, max_val):
+    """E, H: (C, h, w) de-normalised counts; out: fp64 [C, 4] (accumulated; zero it first)."""
+    _req(E, torch.float32, "E"); _req(H, torch.float32, "H"); _req(out, torch.float64, "out")
+    if not (E.is_contiguous() and H.is_contiguous() and out.is_contiguous()) or E.shape != H.shape or E.dim() != 3:
+        raise RuntimeError("kair_b200: spect_metrics needs contiguous (C, h, w) images of one shape")
+    a = _S["kair_spect_metric_args"]()
+    a.E = _ptr(E); a.H = _ptr(H); a.out = _ptr(out)
+    a.C, a.h, a.w = E.shape
+    a.max_val = float(max_val)
+    return Launch("kair_spect_metrics", a)
+
+
 def build_add_inplace(y, x, yb=None):
     """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")

@@ -855,3 +855,44 @@ def build_adam_ema(p, g, m, v, e, *, beta1, beta2, eps, weight_decay=0.0, ema_de
 
 def adam_ema_set_grads(launch, g, tables):
     launch.g[:] = list(g)
+
+
+# ------------------------------------------------------------------------------------------------ SPECT data path
+SPECT_METHODS = {"log": 0, "anscombe": 1, "linear": 2, "none": 3}
+
+
+def build_spect_patches(frames_L, frames_H, sample, out_L, out_H, *, patch, method, max_pixel):
+    from oracle import spect_oracle as spo
+
+    def run():
+        for b, (f, top, left, mode) in enumerate(sample.tolist()):
+            pl, ph = spo.train_patch(frames_L[f].numpy(), frames_H[f].numpy(), top, left, mode, patch, method, max_pixel)
+            out_L[b].copy_(torch.from_numpy(pl))
+            out_H[b].copy_(torch.from_numpy(ph))
+
+    return EmuLaunch("kair_spect_patches", run)
+
+
+def build_spect_normalize(x, y, *, method, max_pixel, inverse=False):
+    from oracle import spect_oracle as spo
+
+    def run():
+        fn = spo.denormalize_spect if inverse else spo.normalize_spect
+        y.copy_(torch.from_numpy(fn(x.numpy(), method, max_pixel).astype("float32")))
+
+    return EmuLaunch("kair_spect_normalize", run)
+
+
+def build_spect_metrics(E, H, out, *, max_val):
+    from oracle import spect_oracle as spo
+    import numpy as np
+
+    def run():
+        C, h, w = E.shape
+        for c in range(C):
+            e8, h8 = spo.quantize(E[c].numpy(), np.float32(max_val)), spo.quantize(H[c].numpy(), np.float32(max_val))
+            out[c, 0] += float(((e8.astype(np.float64) - h8.astype(np.float64)) ** 2).sum())
+            out[c, 1] += spo.ssim_uint8(e8, h8) * (h - 10) * (w - 10)
+            out[c, 2] += spo.pll(E[c].numpy(), H[c].numpy()) * h * w
+
+    return EmuLaunch("kair_spect_metrics", run)

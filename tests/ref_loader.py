@@ -56,3 +56,37 @@ def load(name):
         sys.path.append(REF)
     import importlib
     return importlib.import_module("models." + name)
+
+
+def _stub(name, **attrs):
+    if name not in sys.modules:
+        m = types.ModuleType(name)
+        for k, v in attrs.items():
+            setattr(m, k, v)
+        sys.modules[name] = m
+    return sys.modules[name]
+
+
+def load_utils():
+    """(utils.utils_image, utils.utils_spect, data.dataset_spect) of the reference.  utils_image.py:10-13 imports
+    matplotlib / mpl_toolkits / lpips at module level (plotting and the LPIPS metric, neither on the path tested here);
+    they are not installed in this image and are stubbed with empty modules -- no arithmetic lives in them."""
+    if not have_reference():
+        raise RuntimeError("reference tree not mounted")
+    sys.dont_write_bytecode = True
+    try:
+        import matplotlib  # noqa: F401
+    except ImportError:
+        mpl = _stub("matplotlib")
+        mpl.pyplot = _stub("matplotlib.pyplot")
+        tk = _stub("mpl_toolkits")
+        tk.mplot3d = _stub("mpl_toolkits.mplot3d", Axes3D=object)
+    try:
+        import lpips  # noqa: F401
+    except ImportError:
+        _stub("lpips")
+    if REF not in sys.path:
+        sys.path.append(REF)
+    import importlib
+    return (importlib.import_module("utils.utils_image"), importlib.import_module("utils.utils_spect"),
+            importlib.import_module("data.dataset_spect"))
