@@ -609,6 +609,27 @@ typedef struct kair_spect_metric_args {
 int kair_spect_metrics(const kair_spect_metric_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Tile / self-ensemble drivers (main_test_swinir.py:256-284 `test` with args.tile; utils/utils_model.py:127-185
+ * test_split_fn / test_x8; utils/utils_image.py:408-426 augment_img_tensor4).
+ *   kair_tiles_gather      tiles[n] = D_mode(img[:, y:y+h_src, x:x+w_src]), origins[n] = (y, x, mode); a stored tile is
+ *                          (C, th, tw), its source window (th, tw) or, for the quarter-turn modes 1/3/5/7, (tw, th)
+ *   kair_tiles_accumulate  E[:, y:y+.., x:x+..] += weight * D_mode^-1(tiles[n]); Wsum[y.., x..] += weight (optional):
+ *                          one thread per output pixel, tiles visited in index order (deterministic sums)
+ * img / E are single images (C, H, W) fp32; the batch dimension of the reference's loops is the tile index.
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_tiles_args {
+  const float* img;        /* gather: (C, H, W) source */
+  float* E;                /* accumulate: (C, H, W) sums */
+  float* Wsum;             /* accumulate: (H, W) weights or NULL */
+  float* tiles;            /* (n, C, th, tw): written by gather, read by accumulate */
+  const int32_t* origins;  /* [n][3] = (y, x, mode) in the coordinates of img / E */
+  int32_t n, C, th, tw, H, W;
+  float weight;
+} kair_tiles_args;
+int kair_tiles_gather(const kair_tiles_args* args, void* stream);
+int kair_tiles_accumulate(const kair_tiles_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Launch lists.  A plan (one forward or backward pass of a network at a fixed shape) is a static sequence of the entry
  * points above with pre-filled argument structs; kair_run_list replays such a sequence in ONE call, so the host cost
  * of a pass is one FFI crossing instead of one per kernel (SwinIR-M training: 558 kernels per step).

@@ -509,6 +509,38 @@ def build_spect_metrics(E, H, out, *, max_val):
     return Launch("kair_spect_metrics", a)
 
 
+def _tiles_args(tiles, origins, C, H, W):
+    _req(tiles, torch.float32, "tiles"); _req(origins, torch.int32, "origins")
+    if tiles.dim() != 4 or not tiles.is_contiguous() or origins.dim() != 2 or origins.shape[1] != 3 or \
+            not origins.is_contiguous() or origins.shape[0] != tiles.shape[0] or tiles.shape[1] != C:
+        raise RuntimeError("kair_b200: tiles must be contiguous (n, C, th, tw) and origins [n, 3] int32")
+    a = _S["kair_tiles_args"]()
+    a.tiles = _ptr(tiles); a.origins = _ptr(origins)
+    a.n, a.C, a.th, a.tw = tiles.shape
+    a.H, a.W = H, W
+    return a
+
+
+def build_tiles_gather(img, origins, tiles):
+    """tiles[n] = D_mode(img[:, y:y+.., x:x+..]) for origins[n] = (y, x, mode); img (C, H, W) fp32."""
+    _req(img, torch.float32, "img")
+    if img.dim() != 3 or not img.is_contiguous():
+        raise RuntimeError("kair_b200: tiles_gather needs a contiguous (C, H, W) image")
+    a = _tiles_args(tiles, origins, img.shape[0], img.shape[1], img.shape[2])
+    a.img = _ptr(img)
+    return Launch("kair_tiles_gather", a)
+
+
+def build_tiles_accumulate(tiles, origins, E, Wsum=None, *, weight=1.0):
+    """E[:, y.., x..] += weight * D_mode^-1(tiles[n]); Wsum[y.., x..] += weight.  E (C, H, W), Wsum (H, W) fp32."""
+    _req(E, torch.float32, "E"); _req(Wsum, torch.float32, "Wsum")
+    if E.dim() != 3 or not E.is_contiguous() or (Wsum is not None and (not Wsum.is_contiguous() or Wsum.shape != E.shape[1:])):
+        raise RuntimeError("kair_b200: tiles_accumulate needs contiguous E (C, H, W) and Wsum (H, W)")
+    a = _tiles_args(tiles, origins, E.shape[0], E.shape[1], E.shape[2])
+    a.E = _ptr(E); a.Wsum = _ptr(Wsum); a.weight = float(weight)
+    return Launch("kair_tiles_accumulate", a)
+
+
 def build_add_inplace(y, x, yb=None):
     """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")

@@ -896,3 +896,36 @@ def build_spect_metrics(E, H, out, *, max_val):
             out[c, 2] += spo.pll(E[c].numpy(), H[c].numpy()) * h * w
 
     return EmuLaunch("kair_spect_metrics", run)
+
+
+# ------------------------------------------------------------------------------------------------ tile drivers
+def _dihedral(img, mode):
+    """utils_image.augment_img_tensor4 on (..., H, W)"""
+    if mode == 0:
+        return img
+    k, flip = {1: (1, True), 2: (0, True), 3: (3, False), 4: (2, True), 5: (1, False), 6: (2, False), 7: (3, True)}[mode]
+    out = img.rot90(k, [-2, -1]) if k else img
+    return out.flip([-2]) if flip else out
+
+
+def build_tiles_gather(img, origins, tiles):
+    def run():
+        n, C, th, tw = tiles.shape
+        for i, (y, x, m) in enumerate(origins.tolist()):
+            hs, ws = (tw, th) if m % 2 == 1 else (th, tw)
+            tiles[i].copy_(_dihedral(img[:, y:y + hs, x:x + ws], m))
+
+    return EmuLaunch("kair_tiles_gather", run)
+
+
+def build_tiles_accumulate(tiles, origins, E, Wsum=None, *, weight=1.0):
+    def run():
+        for i, (y, x, m) in enumerate(origins.tolist()):
+            inv = 8 - m if m in (3, 5) else m
+            back = _dihedral(tiles[i], inv)
+            hb, wb = back.shape[-2:]
+            E[:, y:y + hb, x:x + wb] += weight * back
+            if Wsum is not None:
+                Wsum[y:y + hb, x:x + wb] += weight
+
+    return EmuLaunch("kair_tiles_accumulate", run)

@@ -334,16 +334,68 @@ def test_cuda_graph_replay_matches_eager(net):
 
 
 def test_x8_ensemble_on_the_gpu_path():
-    """tiling.test_x8 (utils_model.test_x8, :176-185) around the drop-in DnCNN: the batched 8-way ensemble equals the
-    one-transform-at-a-time evaluation bit for bit (no cross-sample arithmetic in the kernels)."""
+    """tiling.test_x8 (utils_model.test_x8, :176-185) around the drop-in DnCNN on the device kernels
+    (kair_tiles_gather / kair_tiles_accumulate): (i) against the ORACLE network evaluated one transform at a time with the
+    reference's definition (bf16 tolerance), (ii) against the one-at-a-time evaluation of the CUDA path itself (only the
+    order of the eight additions differs: 1e-6)."""
+    import golden_cases as gc
     from kair_b200 import tiling
     from kair_b200.network_dncnn import DnCNN
-    torch.manual_seed(0)
-    model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=5, act_mode="R").cuda().eval()
+    from oracle import convnets_oracle as co
+    case = gc.CASES["dncnn_r17"]
+    sd, _, _ = gc.state_and_io(case)
+    model = DnCNN(**case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().eval()
     for shape in [(1, 1, 48, 48), (2, 1, 32, 56)]:
-        L = torch.rand(shape, generator=torch.Generator().manual_seed(3)).cuda()
+        L = torch.rand(shape, generator=torch.Generator().manual_seed(3))
         with torch.no_grad():
-            got = tiling.test_x8(model, L)
-            ref = torch.stack([tiling.dihedral(model(tiling.dihedral(L, i).contiguous()), tiling.dihedral_inverse_mode(i))
+            got = tiling.test_x8(model, L.cuda())
+            seq = torch.stack([tiling.dihedral(model(tiling.dihedral(L.cuda(), i).contiguous()), tiling.dihedral_inverse_mode(i))
                                for i in range(8)], 0).mean(0)
-        assert torch.equal(got, ref)
+            want = torch.stack([tiling.dihedral(co.dncnn_forward(sd, tiling.dihedral(L, i).contiguous(), nb=17, act_mode="R"),
+                                                tiling.dihedral_inverse_mode(i)) for i in range(8)], 0).mean(0)
+        assert got.shape == want.shape
+        assert (got - seq).abs().max().item() < 1e-6
+        assert (got.cpu() - want).abs().max().item() < 2e-2
+
+
+def test_tile_kernels_match_their_statement():
+    """kair_tiles_gather / kair_tiles_accumulate vs tests/emu_ops.py: every dihedral mode, non-square tiles, overlaps"""
+    import emu_ops
+    from test_elementwise_gpu import _run_both
+    g = torch.Generator().manual_seed(9)
+    img = torch.rand(3, 40, 52, generator=g)
+    rows = [(m % 3, 2 * m, m) for m in range(8)]
+    for th, tw in ((16, 24), (20, 20)):
+        kw = dict(img=img, origins=torch.tensor(rows, dtype=torch.int32), tiles=torch.zeros(8, 3, th, tw))
+        _run_both("tiles_gather", kw, ["tiles"], 1e-12)
+        tiles = torch.rand(8, 3, th, tw, generator=g)
+        kw2 = dict(tiles=tiles, origins=torch.tensor(rows, dtype=torch.int32), E=torch.rand(3, 60, 60, generator=g),
+                   Wsum=torch.zeros(60, 60), weight=0.125)
+        _run_both("tiles_accumulate", kw2, ["E", "Wsum"], 1e-6)
+
+
+def test_tiled_forward_and_split_on_the_gpu_path():
+    """main_test_swinir.test (tiles + overlap-add) and utils_model.test_split_fn around the drop-in DnCNN vs the literal
+    reference loops on the oracle network"""
+    import golden_cases as gc
+    import parity_full as pf
+    from kair_b200 import tiling
+    from kair_b200.network_dncnn import DnCNN
+    from oracle import convnets_oracle as co
+    case = gc.CASES["dncnn_r17"]
+    sd, _, _ = gc.state_and_io(case)
+    model = DnCNN(**case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().eval()
+    oracle = lambda p: co.dncnn_forward(sd, p, nb=17, act_mode="R")
+    img = tiling.pad_to_window(torch.rand(1, 1, 70, 90, generator=torch.Generator().manual_seed(4)), 8)
+    with torch.no_grad():
+        got = tiling.tiled_forward(model, img.cuda(), 32, 8, 1, 8, tile_batch=3).cpu()
+        want = pf.reference_tiled_loop(img, oracle, 32, 8, 1)
+        assert (got - want).abs().max().item() < 2e-2
+        L = torch.rand(1, 1, 72, 88, generator=torch.Generator().manual_seed(5))
+        got2 = tiling.test_mode(model, L.cuda(), mode=2, refield=16, min_size=40, sf=1, modulo=8).cpu()
+        want2 = tiling.test_split_fn(oracle, L, refield=16, min_size=40, sf=1, modulo=8)   # host logic pinned on CPU
+        assert (got2 - want2).abs().max().item() < 2e-2

@@ -1,8 +1,11 @@
 """Host logic of kair_b200.tiling against a literal restatement of main_test_swinir.py:68-74, 256-284 (flip padding,
 tile origins, uniform overlap-add), with a stand-in model so that no GPU is needed; plus rank sharding: the partial
 sums of 1, 2 and 3 ranks merge to the same image (no collective on the data path)."""
+import pytest
 import torch
 
+import emu_ops
+import ref_loader
 from kair_b200 import tiling
 
 
@@ -40,7 +43,7 @@ def test_pad_and_tiles_match_reference_loop():
     assert torch.equal(padded, ref) and padded.shape[2] % ws == 0 and padded.shape[3] % ws == 0
     want = _reference_test(padded, _model, 24, 8, 2, ws)
     for tb in (1, 3, 64):
-        got = tiling.tiled_forward(_model, padded, 24, 8, 2, ws, tile_batch=tb)
+        got = tiling.tiled_forward(_model, padded, 24, 8, 2, ws, tile_batch=tb, ops=emu_ops)
         assert torch.allclose(got, want, atol=1e-6)
 
 
@@ -55,9 +58,9 @@ def test_cfg5_geometry():
 def test_rank_sharding_merges_to_the_same_image():
     g = torch.Generator().manual_seed(1)
     padded = tiling.pad_to_window(torch.rand(1, 1, 50, 70, generator=g), 8)
-    want = tiling.tiled_forward(_model, padded, 16, 8, 2, 8)
+    want = tiling.tiled_forward(_model, padded, 16, 8, 2, 8, ops=emu_ops)
     for world in (2, 3):
-        parts = [tiling.tiled_partial(_model, padded, 16, 8, 2, 8, tile_batch=2, rank=r, world=world) for r in range(world)]
+        parts = [tiling.tiled_partial(_model, padded, 16, 8, 2, 8, tile_batch=2, rank=r, world=world, ops=emu_ops) for r in range(world)]
         assert sum(p[2] for p in parts) == len(tiling.tile_origins(padded.shape[2], padded.shape[3], 16, 8))
         assert torch.allclose(tiling.merge_partials(parts), want, atol=1e-6)
 
@@ -81,11 +84,38 @@ def test_x8_ensemble_matches_the_sequential_definition():
             assert torch.equal(tiling.dihedral(tiling.dihedral(L, i), tiling.dihedral_inverse_mode(i)), L)
         with torch.no_grad():
             calls.clear()
-            got = tiling.test_x8(model, L)
+            got = tiling.test_x8(model, L, ops=emu_ops)
             n_fwd = len(calls)
             ref = torch.stack([tiling.dihedral(conv(tiling.dihedral(L, i)), tiling.dihedral_inverse_mode(i))
                                for i in range(8)], 0).mean(0)
         assert n_fwd == (1 if shape[2] == shape[3] else 2)
         assert torch.allclose(got, ref, atol=1e-6)
-    ident = tiling.test_x8(lambda x: x, torch.arange(24.0).view(1, 1, 4, 6))
+    ident = tiling.test_x8(lambda x: x, torch.arange(24.0).view(1, 1, 4, 6), ops=emu_ops)
     assert torch.allclose(ident, torch.arange(24.0).view(1, 1, 4, 6))
+
+
+@pytest.mark.skipif(not ref_loader.have_reference(), reason="reference tree not mounted")
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("shape,sf", [((1, 2, 70, 90), 1), ((2, 1, 64, 64), 2), ((1, 3, 45, 130), 1)])
+def test_test_mode_matches_the_reference_utils_model(mode, shape, sf):
+    """kair_b200.tiling.test_mode vs the UNMODIFIED utils/utils_model.test_mode (pad, recursive split, x8, split + x8)
+    around the same stand-in network (position dependent, not equivariant, so every index matters)"""
+    import importlib
+    ref_loader.load_utils()
+    um = importlib.import_module("utils.utils_model")
+    torch.manual_seed(0)
+    conv = torch.nn.Conv2d(shape[1], shape[1], 3, padding=1)
+
+    def model(x):
+        y = conv(x)
+        if sf > 1:
+            y = torch.nn.functional.interpolate(y, scale_factor=sf, mode="nearest")
+        ramp = torch.linspace(0, 1, y.shape[-1])[None, None, None, :] * torch.linspace(1, 2, y.shape[-2])[None, None, :, None]
+        return y * (1 + 0.1 * ramp)
+
+    L = torch.rand(shape, generator=torch.Generator().manual_seed(5))
+    with torch.no_grad():
+        want = um.test_mode(model, L, mode=mode, refield=16, min_size=40, sf=sf, modulo=8)
+        got = tiling.test_mode(model, L, mode=mode, refield=16, min_size=40, sf=sf, modulo=8, ops=emu_ops)
+    assert got.shape == want.shape
+    assert torch.allclose(got, want, atol=1e-6), (got - want).abs().max()
