@@ -630,6 +630,30 @@ int kair_tiles_gather(const kair_tiles_args* args, void* stream);
 int kair_tiles_accumulate(const kair_tiles_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * kair_axpby: v = a * x + b * y on fp32 token rows, optionally masked by a saved activation, with fp32 and / or bf16
+ * outputs -- the scaled residual adds of the dense blocks ("x5 * 0.2 + x", "out * 0.2 + x": models/network_rrdbnet.py:
+ * 49-56, 67-72) and the slice-and-mask step of their backward pass:
+ *     out_f32[t][c]  = a * x[t][c] + b * y[t][c]                                   c < n
+ *     out_bf16[t][c] = bf16(out * (mask ? (mask[t][c] > 0 ? 1 : mask_slope) : 1))   c < n;   0 for n <= c < n_pad
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_axpby_args {
+  const float* x;
+  int64_t x_pitch;
+  const float* y;        /* or NULL */
+  int64_t y_pitch;
+  float* out_f32;        /* or NULL; may alias x or y */
+  int64_t out_f32_pitch;
+  void* out_bf16;        /* or NULL */
+  int64_t out_bf16_pitch;
+  const void* mask;      /* bf16 or NULL */
+  int64_t mask_pitch;
+  int64_t T;
+  int32_t n, n_pad;      /* multiples of 8 */
+  float a, b, mask_slope;
+} kair_axpby_args;
+int kair_axpby(const kair_axpby_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Launch lists.  A plan (one forward or backward pass of a network at a fixed shape) is a static sequence of the entry
  * points above with pre-filled argument structs; kair_run_list replays such a sequence in ONE call, so the host cost
  * of a pass is one FFI crossing instead of one per kernel (SwinIR-M training: 558 kernels per step).

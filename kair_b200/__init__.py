@@ -1,4 +1,5 @@
-"""kair_b200: sm_100a (B200) kernels behind KAIR's SwinIR / DnCNN / UNetRes module API."""
+"""kair_b200: sm_100a (B200) kernels behind KAIR's SwinIR / DnCNN / FDnCNN / UNetRes / RRDBNet_noUp module API (see
+DESIGN.md)."""
 import importlib
 import sys
 
@@ -8,7 +9,8 @@ __all__ = ["install"]
 _TARGETS = (("models.network_swinir", "SwinIR", "kair_b200.network_swinir"),
             ("models.network_dncnn", "DnCNN", "kair_b200.network_dncnn"),
             ("models.network_dncnn", "FDnCNN", "kair_b200.network_dncnn"),
-            ("models.network_unet", "UNetRes", "kair_b200.network_unet"))
+            ("models.network_unet", "UNetRes", "kair_b200.network_unet"),
+            ("models.network_rrdbnet", "RRDBNet_noUp", "kair_b200.network_rrdbnet"))
 
 
 def install():

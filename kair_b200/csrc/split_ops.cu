@@ -137,7 +137,71 @@ __global__ void __launch_bounds__(256) ln_bwd_split_kernel(const kair_ln_bwd_spl
   }
 }
 
+__global__ void __launch_bounds__(256) axpby_kernel(const kair_axpby_args a) {
+  const int groups = a.n_pad >> 3;
+  const long long total = a.T * groups;
+  const bf16* mask = reinterpret_cast<const bf16*>(a.mask);
+  bf16* ob = reinterpret_cast<bf16*>(a.out_bf16);
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const long long t = e / groups;
+    const int c0 = (int)(e - t * groups) * 8;
+    float v[8];
+    if (c0 < a.n) {
+      const float4* xp = reinterpret_cast<const float4*>(a.x + t * a.x_pitch + c0);
+      const float4 x0 = xp[0], x1 = xp[1];
+      v[0] = a.a * x0.x; v[1] = a.a * x0.y; v[2] = a.a * x0.z; v[3] = a.a * x0.w;
+      v[4] = a.a * x1.x; v[5] = a.a * x1.y; v[6] = a.a * x1.z; v[7] = a.a * x1.w;
+      if (a.y) {
+        const float4* yp = reinterpret_cast<const float4*>(a.y + t * a.y_pitch + c0);
+        const float4 y0 = yp[0], y1 = yp[1];
+        v[0] = fmaf(a.b, y0.x, v[0]); v[1] = fmaf(a.b, y0.y, v[1]); v[2] = fmaf(a.b, y0.z, v[2]); v[3] = fmaf(a.b, y0.w, v[3]);
+        v[4] = fmaf(a.b, y1.x, v[4]); v[5] = fmaf(a.b, y1.y, v[5]); v[6] = fmaf(a.b, y1.z, v[6]); v[7] = fmaf(a.b, y1.w, v[7]);
+      }
+      if (a.out_f32) {
+        float4* op = reinterpret_cast<float4*>(a.out_f32 + t * a.out_f32_pitch + c0);
+        op[0] = make_float4(v[0], v[1], v[2], v[3]);
+        op[1] = make_float4(v[4], v[5], v[6], v[7]);
+      }
+      if (mask) {
+        const uint4 m = *reinterpret_cast<const uint4*>(mask + t * a.mask_pitch + c0);
+        const __nv_bfloat162* m2 = reinterpret_cast<const __nv_bfloat162*>(&m);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __bfloat1622float2(m2[i]);
+          if (!(f.x > 0.f)) v[2 * i] *= a.mask_slope;
+          if (!(f.y > 0.f)) v[2 * i + 1] *= a.mask_slope;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+    if (ob) {
+      const uint4 pk = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                  pack_bf16x2(v[6], v[7]));
+      *reinterpret_cast<uint4*>(ob + t * a.out_bf16_pitch + c0) = pk;
+    }
+  }
+}
+
 }  // namespace
+
+int axpby_launch(const kair_axpby_args& a, cudaStream_t st) {
+  KB_CHECK(a.x && (a.out_f32 || a.out_bf16) && a.T > 0, "kair_axpby: null pointer / empty input");
+  KB_CHECK(a.n > 0 && a.n % 8 == 0 && a.n_pad >= a.n && a.n_pad % 8 == 0, "kair_axpby: n=%d n_pad=%d", a.n, a.n_pad);
+  KB_CHECK(a.x_pitch % 4 == 0 && (!a.y || a.y_pitch % 4 == 0) && (!a.out_f32 || a.out_f32_pitch % 4 == 0) &&
+               (!a.out_bf16 || a.out_bf16_pitch % 8 == 0) && (!a.mask || a.mask_pitch % 8 == 0),
+           "kair_axpby: pitches must keep 16-byte alignment");
+  KB_CHECK(a.n_pad == a.n || a.out_bf16, "kair_axpby: n_pad > n only pads the bf16 output");
+  const long long total = a.T * (a.n_pad >> 3);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  axpby_kernel<<<(unsigned)blocks, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
 
 int split_terms_launch(const kair_split_args& a, cudaStream_t st) {
   KB_CHECK(a.x && (a.out || a.out_f32) && a.T > 0, "kair_split_terms: null pointer / empty input");

@@ -541,6 +541,21 @@ def build_tiles_accumulate(tiles, origins, E, Wsum=None, *, weight=1.0):
     return Launch("kair_tiles_accumulate", a)
 
 
+def build_axpby(x, *, n, a=1.0, y=None, b=0.0, out_f32=None, out_bf16=None, mask=None, mask_slope=0.0, n_pad=None):
+    """out = a*x + b*y on fp32 rows ([T, >= n]); bf16 copy optionally masked by a saved activation and zero-padded to
+    n_pad columns (kair_b200.h)."""
+    _req(x, torch.float32, "x"); _req(y, torch.float32, "y"); _req(out_f32, torch.float32, "out_f32")
+    _req(out_bf16, torch.bfloat16, "out_bf16"); _req(mask, torch.bfloat16, "mask")
+    g = _S["kair_axpby_args"]()
+    g.x = _ptr(x); g.x_pitch = _pitch(x); g.y = _ptr(y); g.y_pitch = _pitch(y)
+    g.out_f32 = _ptr(out_f32); g.out_f32_pitch = _pitch(out_f32)
+    g.out_bf16 = _ptr(out_bf16); g.out_bf16_pitch = _pitch(out_bf16)
+    g.mask = _ptr(mask); g.mask_pitch = _pitch(mask)
+    g.T = x.shape[0]; g.n = n; g.n_pad = n_pad if n_pad is not None else n
+    g.a, g.b, g.mask_slope = float(a), float(b), float(mask_slope)
+    return Launch("kair_axpby", g)
+
+
 def build_add_inplace(y, x, yb=None):
     """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")

@@ -168,3 +168,53 @@ def merge_bn_state(sd, nb=17, eps=1e-4):
             continue
         out[k] = sd[k].clone()
     return out
+
+
+# --------------------------------------------------------------------------------------------- RRDBNet_noUp
+
+def rrdbnet_state_spec(in_nc=3, out_nc=3, nf=64, nb=23, gc=32):
+    """Ordered [(key, shape, dtype)] of RRDBNet_noUp.state_dict() (models/network_rrdbnet.py:106-118)."""
+    spec = []
+
+    def conv(name, o, i):
+        spec.append((name + ".weight", (o, i, 3, 3), torch.float32))
+        spec.append((name + ".bias", (o,), torch.float32))
+    conv("conv_first", nf, in_nc)
+    for b in range(nb):
+        for r in (1, 2, 3):
+            p = "RRDB_trunk.%d.RDB%d." % (b, r)
+            for k in range(4):
+                conv(p + "conv%d" % (k + 1), gc, nf + k * gc)
+            conv(p + "conv5", nf, nf + 4 * gc)
+    conv("trunk_conv", nf, nf)
+    conv("HRconv", nf, nf)
+    conv("conv_last", out_nc, nf)
+    return spec
+
+
+def _rdb(x, sd, p):
+    """ResidualDenseBlock_5C.forward, models/network_rrdbnet.py:49-56."""
+    import torch.nn.functional as F
+    c = lambda name, t: F.conv2d(t, sd[p + name + ".weight"], sd[p + name + ".bias"], padding=1)
+    l = lambda t: F.leaky_relu(t, 0.2)
+    x1 = l(c("conv1", x))
+    x2 = l(c("conv2", torch.cat((x, x1), 1)))
+    x3 = l(c("conv3", torch.cat((x, x1, x2), 1)))
+    x4 = l(c("conv4", torch.cat((x, x1, x2, x3), 1)))
+    x5 = c("conv5", torch.cat((x, x1, x2, x3, x4), 1))
+    return x5 * 0.2 + x
+
+
+def rrdbnet_noup_forward(sd, x, nb=23):
+    """RRDBNet_noUp.forward, models/network_rrdbnet.py:120-125 (RRDB.forward :67-72)."""
+    import torch.nn.functional as F
+    c = lambda name, t: F.conv2d(t, sd[name + ".weight"], sd[name + ".bias"], padding=1)
+    fea = c("conv_first", x)
+    t = fea
+    for b in range(nb):
+        out = t
+        for r in (1, 2, 3):
+            out = _rdb(out, sd, "RRDB_trunk.%d.RDB%d." % (b, r))
+        t = out * 0.2 + t
+    fea = fea + c("trunk_conv", t)
+    return c("conv_last", F.leaky_relu(c("HRconv", fea), 0.2))

@@ -929,3 +929,21 @@ def build_tiles_accumulate(tiles, origins, E, Wsum=None, *, weight=1.0):
                 Wsum[y:y + hb, x:x + wb] += weight
 
     return EmuLaunch("kair_tiles_accumulate", run)
+
+
+def build_axpby(x, *, n, a=1.0, y=None, b=0.0, out_f32=None, out_bf16=None, mask=None, mask_slope=0.0, n_pad=None):
+    def run():
+        v = a * x[:, :n].float()
+        if y is not None:
+            v = v + b * y[:, :n].float()
+        if out_f32 is not None:
+            out_f32[:, :n].copy_(v)
+        if out_bf16 is not None:
+            vb = v
+            if mask is not None:
+                vb = torch.where(mask[:, :n].float() > 0, v, v * mask_slope)
+            out_bf16[:, :n].copy_(_bf(vb))
+            if n_pad is not None and n_pad > n:
+                out_bf16[:, n:n_pad].zero_()
+
+    return EmuLaunch("kair_axpby", run)

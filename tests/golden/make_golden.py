@@ -54,5 +54,7 @@ if __name__ == "__main__":
     if not ref_loader.have_reference():
         raise SystemExit("reference tree not mounted")
     torch.set_num_threads(8)
+    only = sys.argv[1:]
     for name, case in gc.CASES.items():
-        run_case(name, case)
+        if not only or name in only:
+            run_case(name, case)

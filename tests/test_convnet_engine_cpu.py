@@ -263,3 +263,40 @@ def test_fdncnn_exact_with_fp32_buffers_and_state_dict():
     gmax = max(sdg[k].grad.norm().item() for k in params)
     for k, p in params.items():
         assert (p.grad - sdg[k].grad).norm().item() < 1e-4 * gmax, k
+
+
+def test_rrdbnet_engine_vs_oracle_and_golden():
+    """RRDBNet_noUp (dense blocks without torch.cat) through emu_ops vs the oracle: forward, every parameter gradient,
+    the input gradient; the oracle itself vs the golden fixture of the real reference module."""
+    import json
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_rrdbnet import RRDBNet_noUp
+    case = gc.CASES["rrdbnet_nb2"]
+    sd, x, tgt = gc.state_and_io(case)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rrdbnet_nb2.npz"))
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    xr = x.clone().requires_grad_(True)
+    y_ref = gc.oracle_forward(case, sdg, xr)
+    loss = gc.loss_fn(case)(y_ref, tgt)
+    loss.backward()
+    assert np.abs(y_ref.detach().numpy() - z["y"]).max() < 2e-5 and abs(loss.item() - float(z["loss"])) < 1e-6
+    fp = json.loads(str(z["grads"]))
+    for k, v in sdg.items():
+        assert abs(v.grad.double().norm().item() - fp[k][0]) <= 1e-4 * fp[k][0] + 1e-9, k
+    model = RRDBNet_noUp(**case["kw"])
+    assert list(model.state_dict().keys()) == list(sd.keys())
+    model.load_state_dict(sd, strict=True)
+    model._ops = emu_ops
+    xm = x.clone().requires_grad_(True)
+    y = model(xm)
+    gc.loss_fn(case)(y, tgt).backward()
+    assert (y.detach() - y_ref.detach()).abs().max().item() < 2e-2
+    rel = lambda a, b: ((a - b).norm() / (b.norm() + 1e-30)).item()
+    bad = [(k, rel(p.grad, sdg[k].grad)) for k, p in model.named_parameters() if not rel(p.grad, sdg[k].grad) < 6e-2]
+    assert not bad, bad[:6]
+    assert rel(xm.grad, xr.grad) < 1.5e-1
+    model.eval()
+    with torch.no_grad():
+        assert (model(x) - y_ref.detach()).abs().max().item() < 2e-2

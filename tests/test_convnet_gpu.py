@@ -399,3 +399,47 @@ def test_tiled_forward_and_split_on_the_gpu_path():
         got2 = tiling.test_mode(model, L.cuda(), mode=2, refield=16, min_size=40, sf=1, modulo=8).cpu()
         want2 = tiling.test_split_fn(oracle, L, refield=16, min_size=40, sf=1, modulo=8)   # host logic pinned on CPU
         assert (got2 - want2).abs().max().item() < 2e-2
+
+
+def test_rrdbnet_noup_forward_backward_vs_oracle_and_golden():
+    """RRDBNet_noUp (the fork's `rrdbnet_no_up`) on the CUDA path: golden output of the real reference module, every
+    parameter gradient and the input gradient vs autograd through the oracle; eval plan == training plan forward."""
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_rrdbnet import RRDBNet_noUp
+    case = gc.CASES["rrdbnet_nb2"]
+    sd, x, tgt = gc.state_and_io(case)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rrdbnet_nb2.npz"))
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    xr = x.clone().requires_grad_(True)
+    gc.loss_fn(case)(gc.oracle_forward(case, sdg, xr), tgt).backward()
+    model = RRDBNet_noUp(**case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().train()
+    xm = x.clone().cuda().requires_grad_(True)
+    y = model(xm)
+    gc.loss_fn(case)(y, tgt.cuda()).backward()
+    assert np.abs(y.detach().cpu().numpy() - z["y"]).max() < 2e-2
+    bad = [(k, _rel_l2(p.grad.cpu(), sdg[k].grad)) for k, p in model.named_parameters()
+           if not _rel_l2(p.grad.cpu(), sdg[k].grad) < 6e-2]
+    assert not bad, bad[:6]
+    assert _rel_l2(xm.grad.cpu(), xr.grad) < 1.5e-1
+    model.eval()
+    with torch.no_grad():
+        y2 = model(x.cuda())
+    assert torch.equal(y2, y.detach())
+    # the fork's shape: 2 SPECT views, 64 x 64 patches, batch 4, full depth nb=20 -- finite, and one Adam step moves it
+    torch.manual_seed(0)
+    big = RRDBNet_noUp(in_nc=2, out_nc=2, nf=64, nb=20, gc=32).cuda().train()
+    opt = torch.optim.Adam(big.parameters(), lr=1e-4)
+    xb, tb = torch.rand(4, 2, 64, 64, device="cuda"), torch.rand(4, 2, 64, 64, device="cuda")
+    l0 = None
+    for _ in range(3):
+        opt.zero_grad()
+        loss = torch.mean(torch.abs(big(xb) - tb))
+        loss.backward()
+        assert all(torch.isfinite(p.grad).all().item() for p in big.parameters())
+        opt.step()
+        l0 = l0 if l0 is not None else loss.item()
+    assert loss.item() < l0
