@@ -4,7 +4,7 @@ SPECT data path and validation metrics of the reference fork.
 Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this module.  Pinned by
 tests/test_spect_cpu.py against the reference's own functions (data/dataset_spect.py, utils/utils_spect.py,
 utils/utils_image.py -- imported from /root/reference where it is mounted) and against the committed golden vectors
-tests/golden/spect_golden.npz generated from them by tests/golden/make_spect_golden.py.
+tests/golden/kat/spect_golden.npz generated from them by tests/golden/make_spect_golden.py.
 """
 import math
 

@@ -1,4 +1,4 @@
-"""Generate tests/golden/spect_golden.npz from the UNMODIFIED reference functions (run where /root/reference is
+"""Generate tests/golden/kat/spect_golden.npz from the UNMODIFIED reference functions (run where /root/reference is
 mounted): data/dataset_spect.py (DatasetSPECT on two temporary .dat frame pairs, seeded `random`), utils/utils_spect.py,
 utils/utils_image.py (calculate_psnr, calculate_ssim, pll) and the quantisation of models/model_base.py:358-366.
 
@@ -84,8 +84,8 @@ def main():
         out["denorm_" + method] = np.asarray(uspect.denormalize_spect(np.asarray(n, dtype=np.float32), method, 150), dtype=np.float64)
     out["norm_x"] = x
     del out["full_frames_L"], out["full_frames_H"]
-    np.savez_compressed(os.path.join(HERE, "spect_golden.npz"), **out)
-    print("wrote", os.path.join(HERE, "spect_golden.npz"), {k: v.shape for k, v in out.items()})
+    np.savez_compressed(os.path.join(HERE, "kat", "spect_golden.npz"), **out)
+    print("wrote", os.path.join(HERE, "kat", "spect_golden.npz"), {k: v.shape for k, v in out.items()})
 
 
 if __name__ == "__main__":

@@ -13,7 +13,7 @@ import ref_loader
 from oracle import spect_oracle as spo
 from spect_cases import synth_frames
 
-G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "spect_golden.npz"))
+G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kat", "spect_golden.npz"))
 
 
 @pytest.mark.parametrize("method", ["log", "anscombe", "linear"])

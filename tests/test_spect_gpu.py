@@ -12,7 +12,7 @@ from oracle import spect_oracle as spo
 from spect_cases import synth_frames
 
 pytestmark = pytest.mark.gpu
-G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "spect_golden.npz"))
+G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kat", "spect_golden.npz"))
 
 
 @pytest.mark.parametrize("method", ["log", "anscombe", "linear"])
