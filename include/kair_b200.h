@@ -85,6 +85,9 @@ typedef struct kair_gemm_tn_args {
   const float* acc_scale;
   const float* outB_scale;
   int32_t tokens_per_sample;
+  /* conv == 1: dilation of the 3x3 taps (tap (dy, dx) reads pixel p + dilation * (dy-1, dx-1), zero padding = dilation;
+   * IRCNN's nn.Conv2d(.., padding=d, dilation=d), models/network_dncnn.py:99-111); 0 or 1 = dense taps */
+  int32_t dilation;
 } kair_gemm_tn_args;
 
 int kair_gemm_tn(const kair_gemm_tn_args* args, void* stream);
@@ -153,6 +156,7 @@ typedef struct kair_gemm_nt_args {
   int32_t splits;   /* token-range splits, 0 = auto */
   int32_t conv;
   int32_t batch, H, W;
+  int32_t dilation;  /* conv == 1: tap (dy, dx) pairs A[p] with B[p + dilation * (dy-1, dx-1)]; 0 or 1 = dense taps */
 } kair_gemm_nt_args;
 
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);

@@ -9,6 +9,7 @@ __all__ = ["install"]
 _TARGETS = (("models.network_swinir", "SwinIR", "kair_b200.network_swinir"),
             ("models.network_dncnn", "DnCNN", "kair_b200.network_dncnn"),
             ("models.network_dncnn", "FDnCNN", "kair_b200.network_dncnn"),
+            ("models.network_dncnn", "IRCNN", "kair_b200.network_dncnn"),
             ("models.network_unet", "UNetRes", "kair_b200.network_unet"),
             ("models.network_rrdbnet", "RRDBNet_noUp", "kair_b200.network_rrdbnet"))
 

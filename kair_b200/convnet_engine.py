@@ -51,9 +51,15 @@ def _act_slope(m):
     return None
 
 
-def _is3x3(c):
-    return (isinstance(c, nn.Conv2d) and c.kernel_size == (3, 3) and c.stride == (1, 1) and c.padding == (1, 1)
-            and c.dilation == (1, 1) and c.groups == 1)
+def _is3x3(c, dilated=False):
+    """3x3, stride 1, 'same' zero padding; dilated=True also accepts nn.Conv2d(.., padding=d, dilation=d) (IRCNN,
+    models/network_dncnn.py:99-111)"""
+    if not (isinstance(c, nn.Conv2d) and c.kernel_size == (3, 3) and c.stride == (1, 1) and c.groups == 1):
+        return False
+    d = c.dilation[0]
+    if c.dilation != (d, d) or c.padding != (d, d):
+        return False
+    return d == 1 or (dilated and 1 <= d <= 8)
 
 
 class _GradStore:
@@ -175,6 +181,7 @@ class ConvNetFunction(torch.autograd.Function):
 class DnCNNStage:
     def __init__(self, conv):
         self.conv, self.bn, self.slope = conv, None, None
+        self.dil = conv.dilation[0]
 
 
 def parse_dncnn(seq):
@@ -184,8 +191,8 @@ def parse_dncnn(seq):
     stages = []
     for m in children:
         if isinstance(m, nn.Conv2d):
-            if not _is3x3(m):
-                _unsupported("DnCNN convolution %r is not 3x3 / stride 1 / pad 1" % (m,))
+            if not _is3x3(m, dilated=True):
+                _unsupported("DnCNN / IRCNN convolution %r is not 3x3 / stride 1 / padding == dilation" % (m,))
             stages.append(DnCNNStage(m))
         elif isinstance(m, nn.BatchNorm2d):
             if not stages or stages[-1].bn is not None or stages[-1].slope is not None:
@@ -207,6 +214,8 @@ def parse_dncnn(seq):
         _unsupported("DnCNN head with BatchNorm / tail with BatchNorm or activation")
     if head.conv.in_channels > 4 or tail.conv.out_channels > 4:
         _unsupported("DnCNN with more than 4 image channels")
+    if head.dil != 1 or tail.dil != 1:
+        _unsupported("dilated first / last convolution (the thin image-side kernels are dense 3x3)")
     if nc % 64 or nc > 256:
         _unsupported("DnCNN width nc=%d (must be 64, 128, 192 or 256)" % nc)
     for s in stages[1:-1]:
@@ -318,7 +327,8 @@ class _DnCNNPlan(_PlanBase):
             act, slope = act_of(s)
             if s.bn is not None and bn_live:
                 z = zs[i] if train else zshared
-                fwd.append(o.build_gemm_tn(A(i), Wt["Wp"][i], N=nc, K=nc, bn=bn, conv=geo, bias=Wt["bp"][i], outF=z))
+                fwd.append(o.build_gemm_tn(A(i), Wt["Wp"][i], N=nc, K=nc, bn=bn, conv=geo, bias=Wt["bp"][i], outF=z,
+                                           dilation=s.dil))
                 fwd.append(o.build_bn_stats(z, self.bn_acc, C=nc))
                 fwd.append(o.build_bn_finalize(self.bn_acc, self.bn_mean[i], self.bn_rstd[i], s.bn.running_mean,
                                                s.bn.running_var, s.bn.num_batches_tracked, C=nc, T=T, eps=s.bn.eps,
@@ -328,7 +338,7 @@ class _DnCNNPlan(_PlanBase):
                                             act_slope=slope, out_bf16=A(i + 1)))
             else:
                 fwd.append(o.build_gemm_tn(A(i), Wt["Wp"][i], N=nc, K=nc, bn=bn, conv=geo, bias=Wt["bp"][i], act=act,
-                                           act_slope=slope, outB=A(i + 1)))
+                                           act_slope=slope, outB=A(i + 1), dilation=s.dil))
         if eng.residual:
             # x - n  ==  -(conv(feat) + b - x)
             fwd.append(o.build_conv_out_fwd(A(Lb), tail.conv.weight, tail.conv.bias, self.out, zc_out, C=nc, pitch=nc,
@@ -389,13 +399,14 @@ class _DnCNNPlan(_PlanBase):
                 g = d[cur]
                 if s.conv.bias is not None:
                     bwd.append(o.build_colsum(g, G(s.conv.bias), C=nc))
-            bwd.append(o.build_gemm_nt(g, A(i), dWp[i], n1=nc, n2=nc, bn=bn, conv=geo))
+            bwd.append(o.build_gemm_nt(g, A(i), dWp[i], n1=nc, n2=nc, bn=bn, conv=geo, dilation=s.dil))
             prev = body[i - 1] if i > 0 else head
             if live(prev):
-                bwd.append(o.build_gemm_tn(g, Wt["WpT"][i], N=nc, K=nc, bn=bn, conv=geo, outF=df))
+                bwd.append(o.build_gemm_tn(g, Wt["WpT"][i], N=nc, K=nc, bn=bn, conv=geo, outF=df, dilation=s.dil))
             else:
                 bwd.append(o.build_gemm_tn(g, Wt["WpT"][i], N=nc, K=nc, bn=bn, conv=geo, outB=d[cur ^ 1],
-                                           aux=A(i) if prev.slope is not None else None, act_slope=prev.slope or 0.0))
+                                           aux=A(i) if prev.slope is not None else None, act_slope=prev.slope or 0.0,
+                                           dilation=s.dil))
             cur ^= 1
         bwd.append(o.build_im2col3x3(self.img, xcol, cpad=7, direction=1, mean=zc_in, scale=1.0, ones_col=4 * 7 + cin))
         bwd.append(o.build_gemm_nt(d[cur], xcol, dWcf[0], n1=nc, n2=64, bn=64))

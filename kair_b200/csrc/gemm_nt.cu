@@ -34,6 +34,7 @@ struct NtParams {
   int T, kb_total, kb_per_split, splits, tiles1, tiles2, taps, stages;
   int H, W, TW, TH, tiles_w, tiles_h;  // conv: a k-block is a TW x TH pixel patch (TW*TH = 64)
   int k2;                              // channels of B per tap (conv: column block stride in D)
+  int dil;                             // conv: tap dilation (1 = dense 3x3)
   int ring;                            // bytes of the stage ring (>= the epilogue staging that aliases it)
   long long* ts;                       // development aid (env KB_NT_TS): cycle counters of CTA 0
 };
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
             tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * BM + i * 64, w0, h0, b);
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
-            tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0 + dx - 1, h0 + dy - 1, b);
+            tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0 + (dx - 1) * p.dil, h0 + (dy - 1) * p.dil, b);
         } else {
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i)
@@ -273,6 +274,7 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   memset(&p, 0, sizeof(p));
   p.T = a.T;
   p.taps = a.conv ? 9 : 1;
+  p.dil = (a.conv && a.dilation > 1) ? a.dilation : 1;
   // measured at cfg2 sizes (tools/scratch/nt_ts.py): one 256-row tile beats two 128-row tiles by 13-14 % (n1 = 192);
   // with more than one tile the uneven last tile and the doubled, un-overlapped epilogue cancel the gain (n1 = 384, 576)
   int bm = (a.n1 > 128 && a.n1 <= 256) ? 256 : 128;

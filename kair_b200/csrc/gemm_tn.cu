@@ -51,6 +51,7 @@ struct TnParams {
   int has_outB, has_outB2, has_outF;
   // conv geometry
   int H, W, TW, TH, tiles_w, tiles_h;
+  int dil;  // tap dilation (1 = dense 3x3): halo of dil rows / columns, y taps are dil whole-atom offsets apart
 };
 
 struct TileCoord {
@@ -223,7 +224,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             const int kcc = kb / 3, dx = kb - kcc * 3;
             mbar_wait(&empty_bar[stage], phase ^ 1);
             mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)p.a_stage);
-            tma_load_4d(a_base + stage * p.a_stage, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + dx - 1, t.h0 - 1, t.b);
+            tma_load_4d(a_base + stage * p.a_stage, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + (dx - 1) * p.dil,
+                        t.h0 - p.dil, t.b);
             if (!kBRes) {
               for (int dy = 0; dy < 3; ++dy) {
                 mbar_wait(&emptyb_bar[stage_b], phase_b ^ 1);
@@ -299,7 +301,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll
               for (int k = 0; k < TN_BK / 16; ++k) {
                 if (p.dbg & 2) continue;
-                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + dy * 1024 + k * 32),
+                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + dy * p.dil * 1024 + k * 32),
                             make_desc_kmajor_sw128(b_addr + k * 32), idesc, (kb | dy | k) != 0 ? 1u : 0u);
               }
               if (!kBRes) {
@@ -870,6 +872,8 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
     p.dbg = e ? atoi(e) : 0;
   }
 
+  p.dil = (a.conv && a.dilation > 1) ? a.dilation : 1;
+  KB_CHECK(p.dil <= 8, "kair_gemm_tn: dilation=%d (max 8)", p.dil);
   if (a.conv) {
     KB_CHECK(a.batch > 0 && a.H > 0 && a.W > 0 && (long long)a.batch * a.H * a.W == a.M,
              "kair_gemm_tn: conv geometry %dx%dx%d does not match M=%d", a.batch, a.H, a.W, a.M);
@@ -882,7 +886,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
     p.m_tiles = a.batch * p.tiles_w * p.tiles_h;
     uint64_t dims[4] = {(uint64_t)a.K, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
     uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.a_pitch * 2 * a.W, (uint64_t)a.a_pitch * 2 * a.W * a.H};
-    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH + 2, 1};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)(p.TH + 2 * p.dil), 1};
     if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.A, dims, str, box, nullptr,
                   CU_TENSOR_MAP_SWIZZLE_128B))
       return -2;
@@ -943,7 +947,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   if (a.mode == KAIR_EPI_LINEAR && !loads_r && !a.outF && !lin_aux) { p.stg_warp = 6144; p.ringD = 3; p.ringS = 2048; p.ringDist = 0; }
   const int stg_bytes = 8 * p.stg_warp;
   const int budget = 232448 - 1024 - stg_bytes - TN_MISC_BYTES;
-  p.a_stage = a.conv ? (p.TH + 2) * p.TW * 128 : TN_A_STAGE;
+  p.a_stage = a.conv ? (p.TH + 2 * p.dil) * p.TW * 128 : TN_A_STAGE;
   bool bres = false;
   int stages = 0, stages_b = 0;
   {

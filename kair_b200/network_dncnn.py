@@ -72,3 +72,20 @@ class FDnCNN(DnCNN):
 
     def __init__(self, in_nc=2, out_nc=1, nc=64, nb=20, act_mode="R"):
         super().__init__(in_nc=in_nc, out_nc=out_nc, nc=nc, nb=nb, act_mode=act_mode)
+
+
+class IRCNN(DnCNN):
+    """models/network_dncnn.py:77-116: the 7-layer dilated-convolution denoiser prior (dilations 1, 2, 3, 4, 3, 2, 1,
+    ReLU, no BatchNorm), forward(x) = x - model(x).  Same engine as DnCNN: the dilated layers are the implicit-GEMM 3x3
+    with the taps `dilation` pixels apart (kair_gemm_tn / kair_gemm_nt `dilation`), forward and backward."""
+
+    def __init__(self, in_nc=1, out_nc=1, nc=64):
+        nn.Module.__init__(self)
+        L = [nn.Conv2d(in_nc, nc, 3, 1, 1, dilation=1, bias=True), nn.ReLU(inplace=True)]
+        for d in (2, 3, 4, 3, 2):
+            L += [nn.Conv2d(nc, nc, 3, 1, d, dilation=d, bias=True), nn.ReLU(inplace=True)]
+        L.append(nn.Conv2d(nc, out_nc, 3, 1, 1, dilation=1, bias=True))
+        self.model = B.sequential(*L)
+        self._engine = None
+        self._engine_key = None
+        self._ops = None

@@ -129,7 +129,7 @@ def ptr_array(tensors, device):
 
 def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
             aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None,
-            acc_scale=None, outB_scale=None, tokens_per_sample=0):
+            acc_scale=None, outB_scale=None, tokens_per_sample=0, dilation=1):
     """D = epilogue(A @ B^T).  A: bf16 [M, >=K] (or NHWC [B,H,W,>=K] with conv=(B,H,W)); B: bf16 [N, taps*K]."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
     _req(bias, torch.float32, "bias"); _req(resid, torch.float32, "resid")
@@ -156,6 +156,7 @@ def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.
     a.outF = _ptr(outF); a.outF_pitch = _pitch(outF)
     a.n_valid = n_valid; a.ones_col = ones_col
     a.acc_scale = _ptr(acc_scale); a.outB_scale = _ptr(outB_scale); a.tokens_per_sample = tokens_per_sample
+    a.dilation = dilation
     return Launch("kair_gemm_tn", a)
 
 
@@ -184,14 +185,14 @@ def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF
     return Launch("kair_mlp_fused", a)
 
 
-def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1):
     """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B"); _req(D, torch.float32, "D")
     a = _S["kair_gemm_nt_args"]()
     a.A = _ptr(A); a.a_pitch = _pitch(A)
     a.B = _ptr(B); a.b_pitch = _pitch(B)
     a.D = _ptr(D); a.d_pitch = _pitch(D)
-    a.n1 = n1; a.n2 = n2; a.bn = bn; a.splits = splits
+    a.n1 = n1; a.n2 = n2; a.bn = bn; a.splits = splits; a.dilation = dilation
     if conv is not None:
         a.conv = 1
         a.batch, a.H, a.W = conv

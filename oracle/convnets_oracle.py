@@ -218,3 +218,25 @@ def rrdbnet_noup_forward(sd, x, nb=23):
         t = out * 0.2 + t
     fea = fea + c("trunk_conv", t)
     return c("conv_last", F.leaky_relu(c("HRconv", fea), 0.2))
+
+
+# --------------------------------------------------------------------------------------------- IRCNN
+
+def ircnn_state_spec(in_nc=1, out_nc=1, nc=64):
+    """Ordered [(key, shape, dtype)] of IRCNN.state_dict() (models/network_dncnn.py:97-112: model.0, .2, .., .12)."""
+    spec = []
+    chans = [(nc, in_nc)] + [(nc, nc)] * 5 + [(out_nc, nc)]
+    for i, (o, c) in enumerate(chans):
+        spec.append(("model.%d.weight" % (2 * i), (o, c, 3, 3), torch.float32))
+        spec.append(("model.%d.bias" % (2 * i), (o,), torch.float32))
+    return spec
+
+
+def ircnn_forward(sd, x):
+    """IRCNN.forward, models/network_dncnn.py:114-116 with the layers of :99-111 (dilations 1,2,3,4,3,2,1)."""
+    h = x
+    for i, d in enumerate((1, 2, 3, 4, 3, 2, 1)):
+        h = F.conv2d(h, sd["model.%d.weight" % (2 * i)], sd["model.%d.bias" % (2 * i)], padding=d, dilation=d)
+        if i < 6:
+            h = F.relu(h)
+    return x - h

@@ -90,18 +90,18 @@ def _gelu_grad(x):
     return 0.5 * (1.0 + torch.erf(x * 0.7071067811865476)) + x * torch.exp(-0.5 * x * x) * 0.3989422804014327
 
 
-def _conv_acc(A, Bw, conv, K, N):
+def _conv_acc(A, Bw, conv, K, N, dilation=1):
     """implicit-GEMM 3x3: A NHWC [B,H,W,>=K] bf16, Bw [N, 9*K] with k = tap*K + ci."""
     Bn, H, W = conv
     x = A.reshape(Bn, H, W, -1)[..., :K].float().permute(0, 3, 1, 2)
     w = Bw[:N, :9 * K].float().reshape(N, 9, K).permute(0, 2, 1).reshape(N, K, 3, 3)
-    y = F.conv2d(x, w, padding=1)
+    y = F.conv2d(x, w, padding=dilation, dilation=dilation)
     return y.permute(0, 2, 3, 1).reshape(Bn * H * W, N)
 
 
 def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.0, ln_eps=1e-5, bias=None, resid=None,
                   aux=None, rowstat=None, outB=None, outB2=None, outF=None, n_valid=0, ones_col=-1, conv=None,
-                  acc_scale=None, outB_scale=None, tokens_per_sample=0):
+                  acc_scale=None, outB_scale=None, tokens_per_sample=0, dilation=1):
     assert K % 64 == 0 and N % bn == 0 and bn in (64, 128, 192, 256)
     if mode in (EPI_RESID_LN, EPI_LNBWD):
         assert N == bn
@@ -109,7 +109,7 @@ def build_gemm_tn(A, B, *, N, K, bn, mode=EPI_LINEAR, act=ACT_NONE, act_slope=0.
     def run():
         M = conv[0] * conv[1] * conv[2] if conv is not None else A.shape[0]
         if conv is not None:
-            acc = _conv_acc(A, B, conv, K, N)
+            acc = _conv_acc(A, B, conv, K, N, dilation)
         else:
             acc = A[:, :K].float() @ B[:N, :K].float().t()
         nv = n_valid if n_valid > 0 else N
@@ -205,8 +205,9 @@ def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF
     return EmuLaunch("kair_mlp_fused", run)
 
 
-def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1):
     assert n1 % 64 == 0 and n2 % bn == 0
+    d = dilation
 
     def run():
         if conv is None:
@@ -215,10 +216,10 @@ def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None):
         Bn, H, W = conv
         a = A.reshape(Bn, H, W, -1)[..., :n1].float()
         b = B.reshape(Bn, H, W, -1)[..., :n2].float()
-        bp = F.pad(b, (0, 0, 1, 1, 1, 1))
+        bp = F.pad(b, (0, 0, d, d, d, d))
         for tap in range(9):
             dy, dx = tap // 3, tap % 3
-            bs = bp[:, dy:dy + H, dx:dx + W, :]
+            bs = bp[:, dy * d:dy * d + H, dx * d:dx * d + W, :]
             D[:n1, tap * n2:(tap + 1) * n2] += torch.einsum("bhwi,bhwj->ij", a, bs)
 
     return EmuLaunch("kair_gemm_nt", run)

@@ -57,6 +57,8 @@ CASES = {
     # FDnCNN (network_dncnn.py:126-148): noise-level map as second input channel, no residual learning
     "fdncnn_r8": dict(net="fdncnn", kw=dict(in_nc=2, out_nc=1, nc=64, nb=8, act_mode="R"), x=(2, 2, 24, 32), seed=15,
                       loss="l1"),
+    # IRCNN (network_dncnn.py:77-116): dilated 3x3 stack 1-2-3-4-3-2-1, the plug-and-play denoiser prior
+    "ircnn": dict(net="ircnn", kw=dict(in_nc=3, out_nc=3, nc=64), x=(2, 3, 24, 40), seed=17, loss="l1"),
     # RRDBNet_noUp (the fork's `rrdbnet_no_up`, SPECToptions/network_configs.json:16-31: 2 SPECT views in / out), nb reduced
     "rrdbnet_nb2": dict(net="rrdbnet", kw=dict(in_nc=2, out_nc=2, nf=64, nb=2, gc=32), x=(1, 2, 24, 32), seed=16, loss="l1"),
     # DRUNet (cfg4 architecture, nb reduced to 2)
@@ -93,6 +95,9 @@ def state_and_io(case):
     elif net == "rrdbnet":
         sd = so.deterministic_state(co.rrdbnet_state_spec(**kw), case["seed"])
         up = 1
+    elif net == "ircnn":
+        sd = so.deterministic_state(co.ircnn_state_spec(**kw), case["seed"])
+        up = 1
     else:
         sd = so.deterministic_state(co.unetres_state_spec(kw["in_nc"], kw["out_nc"], tuple(kw["nc"]), kw["nb"],
                                                           kw["bias"]), case["seed"])
@@ -114,6 +119,8 @@ def oracle_forward(case, sd, x, new_stats=None):
                                 new_stats=new_stats, residual=net == "dncnn")
     if net == "rrdbnet":
         return co.rrdbnet_noup_forward(sd, x, nb=kw["nb"])
+    if net == "ircnn":
+        return co.ircnn_forward(sd, x)
     return co.unetres_forward(sd, x, nb=kw["nb"])
 
 
@@ -129,6 +136,8 @@ def build_reference(case, ref_loader):
         model = ref_loader.load("network_dncnn").FDnCNN(**kw)
     elif net == "rrdbnet":
         model = ref_loader.load("network_rrdbnet").RRDBNet_noUp(**kw)
+    elif net == "ircnn":
+        model = ref_loader.load("network_dncnn").IRCNN(**kw)
     else:
         model = ref_loader.load("network_unet").UNetRes(**kw)
     missing = model.load_state_dict(sd, strict=True)

@@ -443,3 +443,47 @@ def test_rrdbnet_noup_forward_backward_vs_oracle_and_golden():
         opt.step()
         l0 = l0 if l0 is not None else loss.item()
     assert loss.item() < l0
+
+
+@pytest.mark.parametrize("d", [2, 3, 4])
+def test_dilated_conv_kernels(d):
+    """kair_gemm_tn / kair_gemm_nt conv mode with `dilation` vs their statement (F.conv2d with dilation = padding = d)"""
+    import emu_ops
+    from test_elementwise_gpu import _run_both
+    g = torch.Generator().manual_seed(40 + d)
+    B, H, W, C = 2, 20, 28, 64
+    T = B * H * W
+    x = (torch.randn(T, C, generator=g)).bfloat16()
+    Wm = (torch.randn(C, 9 * C, generator=g) * 0.05).bfloat16()
+    bias = torch.randn(C, generator=g) * 0.1
+    kw = dict(A=x, B=Wm, N=C, K=C, bn=64, conv=(B, H, W), bias=bias, act=emu_ops.ACT_LRELU, act_slope=0.0,
+              outB=torch.zeros(T, C).bfloat16(), outF=torch.zeros(T, C), dilation=d)
+    _run_both("gemm_tn", kw, ["outF"], 2e-3)
+    gy = (torch.randn(T, C, generator=g)).bfloat16()
+    kw2 = dict(A=gy, B=x, D=torch.zeros(C, 9 * C), n1=C, n2=C, bn=64, conv=(B, H, W), dilation=d)
+    _run_both("gemm_nt", kw2, ["D"], 2e-3)
+
+
+def test_ircnn_forward_backward_vs_oracle_and_golden():
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_dncnn import IRCNN
+    case = gc.CASES["ircnn"]
+    sd, x, tgt = gc.state_and_io(case)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ircnn.npz"))
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    gc.loss_fn(case)(gc.oracle_forward(case, sdg, x), tgt).backward()
+    model = IRCNN(**case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().train()
+    y = model(x.cuda())
+    gc.loss_fn(case)(y, tgt.cuda()).backward()
+    assert np.abs(y.detach().cpu().numpy() - z["y"]).max() < 2e-2
+    bad = [(k, _rel_l2(p.grad.cpu(), sdg[k].grad)) for k, p in model.named_parameters()
+           if not _rel_l2(p.grad.cpu(), sdg[k].grad) < 6e-2]
+    assert not bad, bad[:6]
+    model.eval()
+    with torch.no_grad():
+        big = model(torch.rand(1, 3, 250, 190, device="cuda"))     # not a tile multiple: TMA out-of-bounds fill at dilation 4
+    assert big.shape == (1, 3, 250, 190) and torch.isfinite(big).all()
