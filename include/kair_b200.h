@@ -658,6 +658,21 @@ typedef struct kair_axpby_args {
 int kair_axpby(const kair_axpby_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * kair_ffd_pack: the input side of FFDNet.forward (models/network_ffdnet.py:54-64) as one gather: ReplicationPad2d to
+ * even H, W -> PixelUnShuffle(2) (models/basicblock.py:100-127: channel c*4 + dy*2 + dx) -> torch.cat with the noise
+ * level map sigma.repeat(1, 1, H/2, W/2) -> bf16 token rows for the first convolution (implicit-GEMM, K padded to 64):
+ *   out[(b, y, x)][c*4 + dy*2 + dx] = img[b][c][min(2y+dy, h-1)][min(2x+dx, w-1)],  out[..][4C] = sigma[b],  0 beyond
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct kair_ffd_pack_args {
+  const float* img;      /* (B, C, h, w) */
+  const float* sigma;    /* (B) */
+  void* out;             /* bf16 [B * H2 * W2][pitch], H2 = ceil(h / 2), W2 = ceil(w / 2) */
+  int64_t pitch;         /* multiple of 8, >= 4C + 1 */
+  int32_t batch, C, h, w;
+} kair_ffd_pack_args;
+int kair_ffd_pack(const kair_ffd_pack_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Launch lists.  A plan (one forward or backward pass of a network at a fixed shape) is a static sequence of the entry
  * points above with pre-filled argument structs; kair_run_list replays such a sequence in ONE call, so the host cost
  * of a pass is one FFI crossing instead of one per kernel (SwinIR-M training: 558 kernels per step).

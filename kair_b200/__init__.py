@@ -11,7 +11,8 @@ _TARGETS = (("models.network_swinir", "SwinIR", "kair_b200.network_swinir"),
             ("models.network_dncnn", "FDnCNN", "kair_b200.network_dncnn"),
             ("models.network_dncnn", "IRCNN", "kair_b200.network_dncnn"),
             ("models.network_unet", "UNetRes", "kair_b200.network_unet"),
-            ("models.network_rrdbnet", "RRDBNet_noUp", "kair_b200.network_rrdbnet"))
+            ("models.network_rrdbnet", "RRDBNet_noUp", "kair_b200.network_rrdbnet"),
+            ("models.network_ffdnet", "FFDNet", "kair_b200.network_ffdnet"))
 
 
 def install():

@@ -50,6 +50,7 @@ int spect_normalize_launch(const kair_spect_norm_args& a, cudaStream_t st);
 int spect_metrics_launch(const kair_spect_metric_args& a, cudaStream_t st);
 int tiles_gather_launch(const kair_tiles_args& a, cudaStream_t st);
 int axpby_launch(const kair_axpby_args& a, cudaStream_t st);
+int ffd_pack_launch(const kair_ffd_pack_args& a, cudaStream_t st);
 int tiles_accumulate_launch(const kair_tiles_args& a, cudaStream_t st);
 int ln_bwd_split_launch(const kair_ln_bwd_split_args& a, cudaStream_t st);
 }
@@ -140,6 +141,7 @@ KB_WRAP(kair_spect_normalize, kair_spect_norm_args, spect_normalize_launch)
 KB_WRAP(kair_spect_metrics, kair_spect_metric_args, spect_metrics_launch)
 KB_WRAP(kair_tiles_gather, kair_tiles_args, tiles_gather_launch)
 KB_WRAP(kair_axpby, kair_axpby_args, axpby_launch)
+KB_WRAP(kair_ffd_pack, kair_ffd_pack_args, ffd_pack_launch)
 KB_WRAP(kair_tiles_accumulate, kair_tiles_args, tiles_accumulate_launch)
 KB_WRAP(kair_ln_bwd_split, kair_ln_bwd_split_args, ln_bwd_split_launch)
 #undef KB_WRAP
@@ -189,7 +191,7 @@ const KbOp kb_ops[] = {
     KB_OP(kair_pixel_shuffle_bwd), KB_OP(kair_upsample_nearest2_bwd), KB_OP(kair_split_terms),
     KB_OP(kair_ln_bwd_split), KB_OP(kair_add_inplace_s), KB_OP(kair_memcpy_d2d), KB_OP(kair_mlp_fused),
     KB_OP(kair_spect_patches), KB_OP(kair_spect_normalize), KB_OP(kair_spect_metrics),
-    KB_OP(kair_tiles_gather), KB_OP(kair_tiles_accumulate), KB_OP(kair_axpby),
+    KB_OP(kair_tiles_gather), KB_OP(kair_tiles_accumulate), KB_OP(kair_axpby), KB_OP(kair_ffd_pack),
 };
 #undef KB_OP
 constexpr int kb_n_ops = (int)(sizeof(kb_ops) / sizeof(kb_ops[0]));

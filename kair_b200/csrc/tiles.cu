@@ -86,6 +86,50 @@ __global__ void tiles_accumulate_kernel(const kair_tiles_args a) {
 
 }  // namespace
 
+namespace {
+__global__ void ffd_pack_kernel(const kair_ffd_pack_args a) {
+  const int H2 = (a.h + 1) >> 1, W2 = (a.w + 1) >> 1;
+  const int groups = (int)(a.pitch >> 3);
+  const long long total = (long long)a.batch * H2 * W2 * groups;
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const long long t = e / groups;
+    const int g = (int)(e - t * groups);
+    const int x = (int)(t % W2), y = (int)((t / W2) % H2), b = (int)(t / ((long long)W2 * H2));
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int col = g * 8 + i;
+      float val = 0.f;
+      if (col < 4 * a.C) {
+        const int c = col >> 2, dy = (col >> 1) & 1, dx = col & 1;
+        const int yy = min(2 * y + dy, a.h - 1), xx = min(2 * x + dx, a.w - 1);   // ReplicationPad2d bottom / right
+        val = __ldg(a.img + (((size_t)b * a.C + c) * a.h + yy) * a.w + xx);
+      } else if (col == 4 * a.C) {
+        val = __ldg(a.sigma + b);
+      }
+      v[i] = val;
+    }
+    *reinterpret_cast<uint4*>(out + t * a.pitch + g * 8) =
+        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+}  // namespace
+
+int ffd_pack_launch(const kair_ffd_pack_args& a, cudaStream_t st) {
+  KB_CHECK(a.img && a.sigma && a.out, "kair_ffd_pack: null pointer");
+  KB_CHECK(a.batch > 0 && a.C > 0 && a.h > 0 && a.w > 0 && a.pitch % 8 == 0 && a.pitch >= 4 * a.C + 1,
+           "kair_ffd_pack: bad geometry (C=%d, pitch=%lld)", a.C, (long long)a.pitch);
+  const long long total = (long long)a.batch * ((a.h + 1) / 2) * ((a.w + 1) / 2) * (a.pitch >> 3);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  ffd_pack_kernel<<<(unsigned)blocks, 256, 0, st>>>(a);
+  KB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 static int tiles_check(const kair_tiles_args& a, const char* who) {
   KB_CHECK(a.origins && a.tiles && a.n > 0 && a.C > 0 && a.th > 0 && a.tw > 0 && a.H > 0 && a.W > 0, "%s: bad arguments", who);
   return 0;

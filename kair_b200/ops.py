@@ -557,6 +557,18 @@ def build_axpby(x, *, n, a=1.0, y=None, b=0.0, out_f32=None, out_bf16=None, mask
     return Launch("kair_axpby", g)
 
 
+def build_ffd_pack(img, sigma, out):
+    """FFDNet input: replicate-pad to even size, PixelUnShuffle(2), noise-level map as an extra channel -> bf16 token
+    rows [B*H2*W2, pitch] (kair_b200.h)."""
+    _req(img, torch.float32, "img"); _req(sigma, torch.float32, "sigma"); _req(out, torch.bfloat16, "out")
+    if not img.is_contiguous() or img.dim() != 4 or sigma.numel() != img.shape[0] or not sigma.is_contiguous():
+        raise RuntimeError("kair_b200: ffd_pack needs a contiguous (B, C, h, w) image and B noise levels")
+    a = _S["kair_ffd_pack_args"]()
+    a.img = _ptr(img); a.sigma = _ptr(sigma); a.out = _ptr(out); a.pitch = _pitch(out)
+    a.batch, a.C, a.h, a.w = img.shape
+    return Launch("kair_ffd_pack", a)
+
+
 def build_add_inplace(y, x, yb=None):
     """y += x (fp32, in place); yb (bf16, optional) receives the updated y."""
     _req(y, torch.float32, "y"); _req(x, torch.float32, "x"); _req(yb, torch.bfloat16, "yb")

@@ -240,3 +240,29 @@ def ircnn_forward(sd, x):
         if i < 6:
             h = F.relu(h)
     return x - h
+
+
+# --------------------------------------------------------------------------------------------- FFDNet
+
+def ffdnet_state_spec(in_nc=1, out_nc=1, nc=64, nb=15, act_mode="R"):
+    """Ordered [(key, shape, dtype)] of FFDNet.state_dict() (models/network_ffdnet.py:45-49: model.0, .2, ..)."""
+    spec = []
+    chans = [(nc, in_nc * 4 + 1)] + [(nc, nc)] * (nb - 2) + [(out_nc * 4, nc)]
+    for i, (o, c) in enumerate(chans):
+        spec.append(("model.%d.weight" % (2 * i), (o, c, 3, 3), torch.float32))
+        spec.append(("model.%d.bias" % (2 * i), (o,), torch.float32))
+    return spec
+
+
+def ffdnet_forward(sd, x, sigma, nb=15):
+    """FFDNet.forward, models/network_ffdnet.py:54-69 (ReLU stages; PixelUnShuffle of basicblock.py:104-126)."""
+    h, w = x.shape[-2:]
+    x = F.pad(x, (0, int(-(-w // 2) * 2 - w), 0, int(-(-h // 2) * 2 - h)), mode="replicate")
+    x = F.pixel_unshuffle(x, 2)
+    m = sigma.repeat(1, 1, x.shape[-2], x.shape[-1])
+    t = torch.cat((x, m), 1)
+    for i in range(nb):
+        t = F.conv2d(t, sd["model.%d.weight" % (2 * i)], sd["model.%d.bias" % (2 * i)], padding=1)
+        if i < nb - 1:
+            t = F.relu(t)
+    return F.pixel_shuffle(t, 2)[..., :h, :w]

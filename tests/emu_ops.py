@@ -948,3 +948,16 @@ def build_axpby(x, *, n, a=1.0, y=None, b=0.0, out_f32=None, out_bf16=None, mask
                 out_bf16[:, n:n_pad].zero_()
 
     return EmuLaunch("kair_axpby", run)
+
+
+def build_ffd_pack(img, sigma, out):
+    def run():
+        Bn, C, h, w = img.shape
+        x = F.pad(img, (0, (w + 1) // 2 * 2 - w, 0, (h + 1) // 2 * 2 - h), mode="replicate")
+        u = F.pixel_unshuffle(x, 2)                                         # channel c*4 + dy*2 + dx
+        m = sigma.view(Bn, 1, 1, 1).expand(Bn, 1, u.shape[2], u.shape[3])
+        t = torch.cat((u, m), 1).permute(0, 2, 3, 1).reshape(-1, 4 * C + 1)
+        out.zero_()
+        out[:, :4 * C + 1].copy_(_bf(t))
+
+    return EmuLaunch("kair_ffd_pack", run)

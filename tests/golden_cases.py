@@ -59,6 +59,9 @@ CASES = {
                       loss="l1"),
     # IRCNN (network_dncnn.py:77-116): dilated 3x3 stack 1-2-3-4-3-2-1, the plug-and-play denoiser prior
     "ircnn": dict(net="ircnn", kw=dict(in_nc=3, out_nc=3, nc=64), x=(2, 3, 24, 40), seed=17, loss="l1"),
+    # FFDNet colour geometry (network_ffdnet.py:27-72: nc=96 -> 128 padded channels), odd image size (replicate pad)
+    "ffdnet_c96": dict(net="ffdnet", kw=dict(in_nc=3, out_nc=3, nc=96, nb=5, act_mode="R"), x=(2, 3, 23, 30), seed=18,
+                       loss="l1"),
     # RRDBNet_noUp (the fork's `rrdbnet_no_up`, SPECToptions/network_configs.json:16-31: 2 SPECT views in / out), nb reduced
     "rrdbnet_nb2": dict(net="rrdbnet", kw=dict(in_nc=2, out_nc=2, nf=64, nb=2, gc=32), x=(1, 2, 24, 32), seed=16, loss="l1"),
     # DRUNet (cfg4 architecture, nb reduced to 2)
@@ -66,6 +69,12 @@ CASES = {
                                                downsample_mode="strideconv", upsample_mode="convtranspose",
                                                bias=False), x=(1, 4, 32, 32), seed=13, loss="l1"),
 }
+
+
+def sigma_of(case):
+    """noise levels (B, 1, 1, 1) of an FFDNet case: 15/255 .. 50/255, one per sample"""
+    B = case["x"][0]
+    return (torch.linspace(15.0, 50.0, B) / 255.0).view(B, 1, 1, 1)
 
 
 def loss_fn(case):
@@ -98,6 +107,9 @@ def state_and_io(case):
     elif net == "ircnn":
         sd = so.deterministic_state(co.ircnn_state_spec(**kw), case["seed"])
         up = 1
+    elif net == "ffdnet":
+        sd = so.deterministic_state(co.ffdnet_state_spec(**kw), case["seed"])
+        up = 1
     else:
         sd = so.deterministic_state(co.unetres_state_spec(kw["in_nc"], kw["out_nc"], tuple(kw["nc"]), kw["nb"],
                                                           kw["bias"]), case["seed"])
@@ -121,6 +133,8 @@ def oracle_forward(case, sd, x, new_stats=None):
         return co.rrdbnet_noup_forward(sd, x, nb=kw["nb"])
     if net == "ircnn":
         return co.ircnn_forward(sd, x)
+    if net == "ffdnet":
+        return co.ffdnet_forward(sd, x, sigma_of(case), nb=kw["nb"])
     return co.unetres_forward(sd, x, nb=kw["nb"])
 
 
@@ -138,6 +152,27 @@ def build_reference(case, ref_loader):
         model = ref_loader.load("network_rrdbnet").RRDBNet_noUp(**kw)
     elif net == "ircnn":
         model = ref_loader.load("network_dncnn").IRCNN(**kw)
+    elif net == "ffdnet":
+        ffd = ref_loader.load("network_ffdnet").FFDNet(**kw)
+        sig = sigma_of(case)
+
+        class _WithSigma(torch.nn.Module):      # the golden harness calls model(x)
+            def __init__(self):
+                super().__init__()
+                self.net = ffd
+
+            def forward(self, x):
+                return self.net(x, sig)
+
+            def load_state_dict(self, sd, strict=True):
+                return self.net.load_state_dict(sd, strict=strict)
+
+            def named_parameters(self, *a, **k):
+                return self.net.named_parameters(*a, **k)
+
+            def state_dict(self, *a, **k):
+                return self.net.state_dict(*a, **k)
+        model = _WithSigma()
     else:
         model = ref_loader.load("network_unet").UNetRes(**kw)
     missing = model.load_state_dict(sd, strict=True)

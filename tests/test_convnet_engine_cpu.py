@@ -325,3 +325,33 @@ def test_ircnn_engine_vs_oracle_and_golden():
     rel = lambda a, b: ((a - b).norm() / (b.norm() + 1e-30)).item()
     bad = [(k, rel(p.grad, sdg[k].grad)) for k, p in model.named_parameters() if not rel(p.grad, sdg[k].grad) < 6e-2]
     assert not bad, bad[:6]
+
+
+def test_ffdnet_engine_vs_oracle_and_golden():
+    """FFDNet (pad + PixelUnShuffle + noise map as one gather, padded 96 -> 128 channels, PixelShuffle + crop) through
+    emu_ops vs the oracle and the golden fixture of the real reference module"""
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_ffdnet import FFDNet
+    case = gc.CASES["ffdnet_c96"]
+    sd, x, tgt = gc.state_and_io(case)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ffdnet_c96.npz"))
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    y_ref = gc.oracle_forward(case, sdg, x)
+    gc.loss_fn(case)(y_ref, tgt).backward()
+    assert np.abs(y_ref.detach().numpy() - z["y"]).max() < 2e-5
+    model = FFDNet(**case["kw"])
+    assert list(model.state_dict().keys()) == list(sd.keys())
+    model.load_state_dict(sd, strict=True)
+    model._ops = emu_ops
+    y = model(x, gc.sigma_of(case))
+    assert y.shape == y_ref.shape
+    gc.loss_fn(case)(y, tgt).backward()
+    assert (y.detach() - y_ref.detach()).abs().max().item() < 2e-2
+    rel = lambda a, b: ((a - b).norm() / (b.norm() + 1e-30)).item()
+    bad = [(k, rel(p.grad, sdg[k].grad)) for k, p in model.named_parameters() if not rel(p.grad, sdg[k].grad) < 6e-2]
+    assert not bad, bad[:6]
+    model.eval()
+    with torch.no_grad():
+        assert (model(x, gc.sigma_of(case)) - y_ref.detach()).abs().max().item() < 2e-2

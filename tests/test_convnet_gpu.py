@@ -487,3 +487,31 @@ def test_ircnn_forward_backward_vs_oracle_and_golden():
     with torch.no_grad():
         big = model(torch.rand(1, 3, 250, 190, device="cuda"))     # not a tile multiple: TMA out-of-bounds fill at dilation 4
     assert big.shape == (1, 3, 250, 190) and torch.isfinite(big).all()
+
+
+def test_ffdnet_forward_backward_vs_oracle_and_golden():
+    import os
+    import numpy as np
+    import golden_cases as gc
+    from kair_b200.network_ffdnet import FFDNet
+    case = gc.CASES["ffdnet_c96"]
+    sd, x, tgt = gc.state_and_io(case)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ffdnet_c96.npz"))
+    sdg = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    gc.loss_fn(case)(gc.oracle_forward(case, sdg, x), tgt).backward()
+    model = FFDNet(**case["kw"])
+    model.load_state_dict(sd, strict=True)
+    model = model.cuda().train()
+    sig = gc.sigma_of(case).cuda()
+    y = model(x.cuda(), sig)
+    gc.loss_fn(case)(y, tgt.cuda()).backward()
+    assert y.shape == tuple(z["y"].shape) and np.abs(y.detach().cpu().numpy() - z["y"]).max() < 2e-2
+    bad = [(k, _rel_l2(p.grad.cpu(), sdg[k].grad)) for k, p in model.named_parameters()
+           if not _rel_l2(p.grad.cpu(), sdg[k].grad) < 6e-2]
+    assert not bad, bad[:6]
+    # the gray model at its published depth (nc=64, nb=15) on an even-sized image: inference, finite, right shape
+    torch.manual_seed(0)
+    gray = FFDNet(in_nc=1, out_nc=1, nc=64, nb=15, act_mode="R").cuda().eval()
+    with torch.no_grad():
+        out = gray(torch.rand(2, 1, 240, 240, device="cuda"), torch.full((2, 1, 1, 1), 25 / 255.0, device="cuda"))
+    assert out.shape == (2, 1, 240, 240) and torch.isfinite(out).all()
