@@ -187,14 +187,15 @@ def _wrap_dp(model, local_rank, use_ddp):
         from torch.nn.parallel import DistributedDataParallel as DDP
         return DDP(model, device_ids=[local_rank], broadcast_buffers=False, gradient_as_bucket_view=True)
     from kair_b200.parallel import FlatDataParallel
-    return FlatDataParallel(model)
+    return FlatDataParallel(model, overlap=not os.environ.get("KAIR_B200_NO_OVERLAP"))
 
 
 def _dp_name(world, use_ddp):
     if world == 1:
         return "dp1"
-    return "dp%d (%s)" % (world, "torch DDP" if use_ddp else "FlatDataParallel: one NCCL all-reduce of the flat "
-                          "gradient buffer per step")
+    return "dp%d (%s)" % (world, "torch DDP" if use_ddp else "FlatDataParallel: NCCL all-reduce of the flat gradient "
+                          "buffer, per-RSTB slices overlapped with the backward pass"
+                          + (" [overlap off]" if os.environ.get("KAIR_B200_NO_OVERLAP") else ""))
 
 
 def _ncu_traffic(tag):
