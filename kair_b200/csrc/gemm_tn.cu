@@ -3,6 +3,10 @@
 //   warp 0      TMA producer   (A tiles [128 x 64] bf16, SWIZZLE_128B; conv mode: 9 shifted 4-D boxes per k-slice,
 //                                zero padding comes from TMA out-of-bounds fill)
 //   warp 1      MMA issuer     (one lane issues tcgen05.mma 128 x BN x 16, accumulators double-buffered in TMEM)
+//   warp 10     second issuer  (narrow tiles only, BN <= 64: a 128 x 64 x 16 UMMA costs its issuing thread ~85 cycles but
+//                                the tensor pipe ~48, so ONE thread cannot keep the pipe busy; the two issuers take
+//                                alternate tiles -- issuer i owns TMEM accumulator stage i -- and walk the same operand
+//                                rings with independently computed stage / phase sequences)
 //   warps 2..9  epilogue       (tcgen05.ld -> registers -> fused bias / GELU / residual / LayerNorm /
 //                                LayerNorm-backward -> swizzled smem staging -> TMA store)
 //
@@ -21,7 +25,7 @@
 
 namespace kb {
 
-constexpr int TN_THREADS = 320;       // 10 warps
+constexpr int TN_THREADS = 352;       // 11 warps: TMA, MMA issuer 0, 8 epilogue, MMA issuer 1
 constexpr int TN_BM = 128;
 constexpr int TN_BK = 64;
 constexpr int TN_A_STAGE = TN_BM * TN_BK * 2;  // 16 KiB
@@ -45,6 +49,9 @@ struct TnParams {
   int a_stage;  // bytes of one A stage: 16 KiB (dense), 18 KiB (conv: 8 x 18 pixel halo column of one 64-channel slice)
   int n_valid, ones_col, act;
   int stg_warp, ringD, ringS, ringDist;
+  int issuers;  // MMA issuer warps in use (1 or 2); the block has 320 + 32 * (issuers - 1) threads
+  int ring_split;  // 2 issuers: 1 = each issuer owns one half of the operand rings, 0 = one shared ring (needs
+                   // stages > stages per tile so that the parity waits of the issuer that runs ahead stay unambiguous)
   int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs,
             // 4 = LINEAR epilogue does the barrier handshake only, 8 = dense producer moves no A tiles
   float act_slope, ln_eps;
@@ -127,6 +134,12 @@ __device__ __forceinline__ void tma_store_chunk(const TnParams& p, const CUtenso
     tma_store_2d(tm, buf, col, t.w0 + q * 32);
   }
 }
+
+#ifdef KB_DEVEL
+#define TN_DBG(p) ((p).dbg)
+#else
+#define TN_DBG(p) 0
+#endif
 
 template <int BN, int EPI, bool kConv, bool kBRes>
 __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_constant__ TnParams p) {
@@ -215,69 +228,103 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         for (int kb = 0; kb < k_total; ++kb)
           tma_load_2d(b_base + kb * B_STAGE, &p.tmB, bres_bar, kb * TN_BK, n_tile * BN);
       }
-      int stage = 0, stage_b = 0;
-      uint32_t phase = 0, phase_b = 0;
-      for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride) {
+      // With two MMA issuers the operand rings are split in halves: tiles alternate between the halves, each half is
+      // consumed by one issuer in order, so the mbarrier parity protocol stays single-producer / single-consumer.
+      const int nr = p.ring_split ? 2 : 1;
+      const int sh = p.stages / nr, shb = (kConv && !kBRes) ? p.stages_b / nr : 0;   // stages per sub-ring
+      int stage_r[2] = {0, 0}, stage_br[2] = {0, 0};
+      uint32_t phase_r[2] = {0, 0}, phase_br[2] = {0, 0};
+      int it = 0;
+      for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
         const TileCoord t = tile_coord<kConv>(p, m_tile);
+        const int r = nr == 2 ? (it & 1) : 0;
+        int stage = stage_r[r], stage_b = stage_br[r];
+        uint32_t phase = phase_r[r], phase_b = phase_br[r];
+        const int s0 = r * sh, sb0 = r * shb;
         if (kConv) {
           for (int kb = 0; kb < p.kc * 3; ++kb) {
             const int kcc = kb / 3, dx = kb - kcc * 3;
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)p.a_stage);
-            tma_load_4d(a_base + stage * p.a_stage, &p.tmA, &full_bar[stage], kcc * TN_BK, t.w0 + (dx - 1) * p.dil,
-                        t.h0 - p.dil, t.b);
+            mbar_wait(&empty_bar[s0 + stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)p.a_stage);
+            tma_load_4d(a_base + (s0 + stage) * p.a_stage, &p.tmA, &full_bar[s0 + stage], kcc * TN_BK,
+                        t.w0 + (dx - 1) * p.dil, t.h0 - p.dil, t.b);
             if (!kBRes) {
               for (int dy = 0; dy < 3; ++dy) {
-                mbar_wait(&emptyb_bar[stage_b], phase_b ^ 1);
-                mbar_arrive_expect_tx(&fullb_bar[stage_b], (uint32_t)B_STAGE);
-                tma_load_2d(b_base + stage_b * B_STAGE, &p.tmB, &fullb_bar[stage_b],
+                mbar_wait(&emptyb_bar[sb0 + stage_b], phase_b ^ 1);
+                mbar_arrive_expect_tx(&fullb_bar[sb0 + stage_b], (uint32_t)B_STAGE);
+                tma_load_2d(b_base + (sb0 + stage_b) * B_STAGE, &p.tmB, &fullb_bar[sb0 + stage_b],
                             ((dy * 3 + dx) * p.kc + kcc) * TN_BK, n_tile * BN);
-                if (++stage_b == p.stages_b) {
+                if (++stage_b == shb) {
                   stage_b = 0;
                   phase_b ^= 1;
                 }
               }
             }
-            if (++stage == p.stages) {
+            if (++stage == sh) {
               stage = 0;
               phase ^= 1;
             }
           }
         } else {
           for (int kb = 0; kb < k_total; ++kb) {
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            if (p.dbg & 8) {  // ablation: no A traffic
-              mbar_arrive(&full_bar[stage]);
-              if (++stage == p.stages) {
+            mbar_wait(&empty_bar[s0 + stage], phase ^ 1);
+            if (TN_DBG(p) & 8) {  // ablation: no A traffic
+              mbar_arrive(&full_bar[s0 + stage]);
+              if (++stage == sh) {
                 stage = 0;
                 phase ^= 1;
               }
               continue;
             }
-            mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
-            tma_load_2d(a_base + stage * TN_A_STAGE, &p.tmA, &full_bar[stage], kb * TN_BK, t.w0);
-            if (!kBRes) tma_load_2d(b_base + stage * B_STAGE, &p.tmB, &full_bar[stage], kb * TN_BK, n_tile * BN);
-            if (++stage == p.stages) {
+            mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
+            tma_load_2d(a_base + (s0 + stage) * TN_A_STAGE, &p.tmA, &full_bar[s0 + stage], kb * TN_BK, t.w0);
+            if (!kBRes) tma_load_2d(b_base + (s0 + stage) * B_STAGE, &p.tmB, &full_bar[s0 + stage], kb * TN_BK, n_tile * BN);
+            if (++stage == sh) {
               stage = 0;
               phase ^= 1;
             }
           }
         }
+        stage_r[r] = stage; stage_br[r] = stage_b;
+        phase_r[r] = phase; phase_br[r] = phase_b;
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // ================================ MMA issuer ================================
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 10) {
+    // ================================ MMA issuers ================================
+    const int issuer = warp == 1 ? 0 : 1;
+    if (lane == 0 && issuer < p.issuers) {
       constexpr uint32_t idesc = make_idesc_bf16(TN_BM, BN, 0, 0);
       if (kBRes) {
         mbar_wait(bres_bar, 0);
         tcgen05_fence_after();
       }
+      const int nr = p.ring_split ? 2 : 1;
+      const int sh = p.stages / nr, shb = (kConv && !kBRes) ? p.stages_b / nr : 0;
+      const int s0 = p.ring_split ? issuer * sh : 0, sb0 = p.ring_split ? issuer * shb : 0;
+      const int a_per_tile = kConv ? p.kc * 3 : k_total;       // A ring stages of one tile
+      const int b_per_tile = (kConv && !kBRes) ? p.kc * 9 : 0; // B ring stages of one tile (streamed conv weights)
+      const bool shared2 = p.issuers == 2 && !p.ring_split;    // shared ring: step over the other issuer's tiles
+      const uint32_t dil_bytes = (uint32_t)p.dil * 1024u;      // y taps: dil whole 8-pixel atoms apart
       int stage = 0, stage_b = 0;
       uint32_t phase = 0, phase_b = 0;
-      int it = 0;
-      for (int m_tile = m_first; m_tile < p.m_tiles; m_tile += m_stride, ++it) {
+      auto skip_tile = [&]() {
+        stage += a_per_tile;
+        while (stage >= sh) {
+          stage -= sh;
+          phase ^= 1;
+        }
+        if (shb) {
+          stage_b += b_per_tile;
+          while (stage_b >= shb) {
+            stage_b -= shb;
+            phase_b ^= 1;
+          }
+        }
+      };
+      if (shared2 && issuer == 1) skip_tile();
+      for (int it = issuer, m_tile = m_first + issuer * m_stride; m_tile < p.m_tiles;
+           it += p.issuers, m_tile += p.issuers * m_stride) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -286,62 +333,65 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         if (kConv) {
           for (int kb = 0; kb < p.kc * 3; ++kb) {
             const int kcc = kb / 3, dx = kb - kcc * 3;
-            mbar_wait(&full_bar[stage], phase);
+            mbar_wait(&full_bar[s0 + stage], phase);
             tcgen05_fence_after();
-            const uint32_t a_addr = smem_u32(a_base + stage * p.a_stage);
+            const uint32_t a_addr = smem_u32(a_base + (s0 + stage) * p.a_stage);
+#pragma unroll
             for (int dy = 0; dy < 3; ++dy) {
+              const uint32_t a_dy = a_addr + dy * dil_bytes;
               uint32_t b_addr;
               if (kBRes) {
                 b_addr = smem_u32(b_base + ((dy * 3 + dx) * p.kc + kcc) * B_STAGE);
               } else {
-                mbar_wait(&fullb_bar[stage_b], phase_b);
+                mbar_wait(&fullb_bar[sb0 + stage_b], phase_b);
                 tcgen05_fence_after();
-                b_addr = smem_u32(b_base + stage_b * B_STAGE);
+                b_addr = smem_u32(b_base + (sb0 + stage_b) * B_STAGE);
               }
 #pragma unroll
               for (int k = 0; k < TN_BK / 16; ++k) {
-                if (p.dbg & 2) continue;
-                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + dy * p.dil * 1024 + k * 32),
+                if (TN_DBG(p) & 2) continue;
+                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_dy + k * 32),
                             make_desc_kmajor_sw128(b_addr + k * 32), idesc, (kb | dy | k) != 0 ? 1u : 0u);
               }
               if (!kBRes) {
-                umma_commit(&emptyb_bar[stage_b]);
-                if (++stage_b == p.stages_b) {
+                umma_commit(&emptyb_bar[sb0 + stage_b]);
+                if (++stage_b == shb) {
                   stage_b = 0;
                   phase_b ^= 1;
                 }
               }
             }
-            umma_commit(&empty_bar[stage]);
-            if (++stage == p.stages) {
+            umma_commit(&empty_bar[s0 + stage]);
+            if (++stage == sh) {
               stage = 0;
               phase ^= 1;
             }
           }
         } else {
           for (int kb = 0; kb < k_total; ++kb) {
-            mbar_wait(&full_bar[stage], phase);
+            mbar_wait(&full_bar[s0 + stage], phase);
             tcgen05_fence_after();
-            const uint32_t a_addr = smem_u32(a_base + stage * TN_A_STAGE);
-            const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : stage) * B_STAGE);
+            const uint32_t a_addr = smem_u32(a_base + (s0 + stage) * TN_A_STAGE);
+            const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : s0 + stage) * B_STAGE);
 #pragma unroll
             for (int k = 0; k < TN_BK / 16; ++k) {
-              if (p.dbg & 2) continue;
+              if (TN_DBG(p) & 2) continue;
               umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
                           (kb | k) != 0 ? 1u : 0u);
             }
-            umma_commit(&empty_bar[stage]);
-            if (++stage == p.stages) {
+            umma_commit(&empty_bar[s0 + stage]);
+            if (++stage == sh) {
               stage = 0;
               phase ^= 1;
             }
           }
         }
         umma_commit(&tfull_bar[as]);
+        if (shared2) skip_tile();
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp < 10) {
     // ================================ epilogue ================================
     // Each epilogue warp owns two 6 KiB staging sets (4 KiB fp32 chunk + 2 KiB bf16 chunk of 32 rows x 32 columns).
     // Global operands of the epilogue (fp32 residual rows, bf16 aux rows) are TMA-loaded into the set one chunk
@@ -502,13 +552,13 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 
       if (EPI == KAIR_EPI_LINEAR) {
 #pragma unroll 1
-        for (int c = 0; c < ((p.dbg & 4) ? 0 : NCH); ++c) {  // dbg 4: ablation, epilogue = barrier handshake only
+        for (int c = 0; c < ((TN_DBG(p) & 4) ? 0 : NCH); ++c) {  // dbg 4: ablation, epilogue = barrier handshake only
           const int col = col_half + c * 32;
           const bool last = (c == NCH - 1);
           uint8_t* buf = slot_begin(!last || more_tiles, use_r, use_a, last ? t_next : t, last ? col_half : col + 32,
                                     use_r || use_a);
           float v[32];
-          if (p.dbg & 1) {
+          if (TN_DBG(p) & 1) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = 0.f;
           } else {
@@ -781,7 +831,7 @@ static int launch_cfg(const TnParams& p, int grid, size_t smem, cudaStream_t st)
     KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set[dev & 63] = true;
   }
-  KB_CUDA(launch_pdl(kern, grid, TN_THREADS, smem, st, p));
+  KB_CUDA(launch_pdl(kern, grid, p.issuers == 2 ? TN_THREADS : TN_THREADS - 32, smem, st, p));
   return 0;
 }
 
@@ -871,6 +921,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
     const char* e = KB_DEV_ENV("KB_TN_DBG");
     p.dbg = e ? atoi(e) : 0;
   }
+
 
   p.dil = (a.conv && a.dilation > 1) ? a.dilation : 1;
   KB_CHECK(p.dil <= 8, "kair_gemm_tn: dilation=%d (max 8)", p.dil);
@@ -974,6 +1025,29 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   KB_CHECK(stages >= 2, "kair_gemm_tn: not enough shared memory for bn=%d", a.bn);
   p.stages = stages;
   p.stages_b = stages_b;
+  // narrow tiles are bound by the issue rate of a single thread: a second issuer warp on its own halves of the rings
+  p.issuers = 1;
+  p.ring_split = 0;
+  if (a.bn <= 64) {
+    const int a_tile = a.conv ? p.kc * 3 : k_total, b_tile = (a.conv && !bres) ? p.kc * 9 : 0;
+    if (stages > a_tile && (!b_tile || stages_b > b_tile)) {
+      p.issuers = 2;                                   // one shared ring, deeper prefetch per issuer
+    } else if (stages >= 4 && (!b_tile || stages_b >= 4)) {
+      p.issuers = 2;
+      p.ring_split = 1;
+      p.stages &= ~1;                                  // equal halves
+      p.stages_b &= ~1;
+    }
+  }
+  {
+    const char* e = KB_DEV_ENV("KB_TN_ISSUERS");
+    if (e && atoi(e) == 1) {
+      p.issuers = 1;
+      p.ring_split = 0;
+      p.stages = stages;
+      p.stages_b = stages_b;
+    }
+  }
   size_t smem = 1024 + stg_bytes + (size_t)stages * p.a_stage +
                 (size_t)(bres ? k_total : (a.conv ? stages_b : stages)) * b_stage + TN_MISC_BYTES;
 
