@@ -37,10 +37,17 @@ struct AttnBwdParams {
 };
 
 // timeline stamps: role 0 = MMA issuer, 1 = group 0 / thread 0, 2 = group 1 / thread 0; up to 256 events each
+#ifdef KB_DEVEL
 #define AB_STAMP(role, cnt)                                                                    \
   do {                                                                                         \
     if (p.ts && blockIdx.x == 0 && (cnt) < 256) p.ts[(role) * 256 + (cnt)++] = clock64();      \
   } while (0)
+#else   // production builds carry no timeline stamps inside the pipelines
+#define AB_STAMP(role, cnt) \
+  do {                      \
+    (void)(cnt);            \
+  } while (0)
+#endif
 
 __device__ __forceinline__ void ab_window_origin(const AttnBwdParams& p, int gw, int& b, int& wi, int& wj) {
   int nW = p.nWh * p.nWw;

@@ -28,10 +28,19 @@
 namespace kb {
 
 // timeline stamps: role r (0 producer, 1 mma, 2 softmax warp 2 lane 0), up to 256 events each
+#ifdef KB_DEVEL
 #define AF_TS(role, cnt)                                                              \
   do {                                                                                \
     if (p.ts && blockIdx.x == 0 && (cnt) < 256) p.ts[(role) * 256 + (cnt)++] = clock64(); \
   } while (0)
+#define AF_DBG(p) ((p).dbg)
+#else   // production builds carry no timeline stamps / ablation branches inside the pipelines
+#define AF_TS(role, cnt) \
+  do {                   \
+    (void)(cnt);         \
+  } while (0)
+#define AF_DBG(p) 0
+#endif
 
 constexpr int AF_THREADS = 320;
 constexpr int AF_STAGE = 3 * 16384;     // Q, K, V tiles of one head pair
@@ -394,7 +403,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       if (lane == 0) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
       named_bar_sync(2, 256);
       for (int hh = 0; hh < nH / 2; ++hh) {
-        if (p.dbg & 4) break;
+        if (AF_DBG(p) & 4) break;
         const int h = hh * 2 + g;
         uint32_t r[32];
         tmem_ld32(tmem_O + lane_sel + h * 32, r);

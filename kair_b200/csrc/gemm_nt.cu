@@ -19,6 +19,14 @@
 #include "host.h"
 #include "../../include/kair_b200.h"
 
+#ifdef KB_DEVEL
+#define NT_CLOCK() clock64()
+#define NT_TS(p) ((p).ts)
+#else   // production builds: no clock reads / timeline stores in the pipelines
+#define NT_CLOCK() 0ll
+#define NT_TS(p) ((long long*)nullptr)
+#endif
+
 namespace kb {
 
 constexpr int NT_THREADS = 320;
@@ -103,11 +111,11 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       const int dy = tap / 3, dx = tap - dy * 3;
-      long long t_wait = 0, t_begin = clock64();
+      long long t_wait = 0, t_begin = NT_CLOCK();
       for (int kb = kb0; kb < kb1; ++kb) {
-        const long long tw0 = clock64();
+        const long long tw0 = NT_CLOCK();
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        t_wait += clock64() - tw0;
+        t_wait += NT_CLOCK() - tw0;
         mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
         uint8_t* a_s = a_base + stage * NT_A_STAGE;
         uint8_t* b_s = b_base + stage * B_STAGE;
@@ -136,9 +144,9 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           phase ^= 1;
         }
       }
-      if (p.ts && blockIdx.x == 0) {
+      if (NT_TS(p) && blockIdx.x == 0) {
         p.ts[0] = t_wait;
-        p.ts[1] = clock64() - t_begin;
+        p.ts[1] = NT_CLOCK() - t_begin;
         p.ts[2] = nkb;
       }
     }
@@ -148,11 +156,11 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
-      long long t_wait = 0, t_begin = clock64();
+      long long t_wait = 0, t_begin = NT_CLOCK();
       for (int kb = 0; kb < nkb; ++kb) {
-        const long long tw0 = clock64();
+        const long long tw0 = NT_CLOCK();
         mbar_wait(&full_bar[stage], phase);
-        t_wait += clock64() - tw0;
+        t_wait += NT_CLOCK() - tw0;
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(a_base + stage * NT_A_STAGE);
         const uint32_t b_addr = smem_u32(b_base + stage * B_STAGE);
@@ -170,9 +178,9 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         }
       }
       umma_commit(tfull_bar);
-      if (p.ts && blockIdx.x == 0) {
+      if (NT_TS(p) && blockIdx.x == 0) {
         p.ts[3] = t_wait;
-        p.ts[4] = clock64() - t_begin;
+        p.ts[4] = NT_CLOCK() - t_begin;
       }
     }
     __syncwarp();
@@ -183,9 +191,9 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
     constexpr int HALF = BN / 2;
     constexpr int NCH = HALF / 32;
     uint8_t* stg = stg_base + ew * NT_STG_PER_WARP;
-    const long long te0 = clock64();
+    const long long te0 = NT_CLOCK();
     mbar_wait(tfull_bar, 0);
-    const long long te1 = clock64();
+    const long long te1 = NT_CLOCK();
     tcgen05_fence_after();
     const int col_base = tap * p.k2 + tile2 * BN + hf * HALF;
     int sbuf = 0;
@@ -218,9 +226,9 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
     }
     if (lane == 0) tma_store_wait_all<0>();
     __syncwarp();
-    if (p.ts && blockIdx.x == 0 && ew == 0 && lane == 0) {
+    if (NT_TS(p) && blockIdx.x == 0 && ew == 0 && lane == 0) {
       p.ts[5] = te1 - te0;
-      p.ts[6] = clock64() - te1;
+      p.ts[6] = NT_CLOCK() - te1;
     }
   }
 
