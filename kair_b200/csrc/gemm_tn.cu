@@ -32,6 +32,7 @@ constexpr int TN_A_STAGE = TN_BM * TN_BK * 2;  // 16 KiB
 // per-epilogue-warp staging ring (runtime, TnParams::stg_warp): 12 KiB = 2 x (4 KiB fp32 + 2 KiB bf16 chunk) for the
 // epilogues with in-place residual traffic, 6-8 KiB for the light ones so that more A stages fit
 constexpr int TN_MAX_STAGES = 8;
+constexpr int TN_EPI_LEAN = 5;                 // internal epilogue id (see the epilogue section)
 constexpr int TN_MISC_BYTES = 6144;            // 1 KiB barriers + tmem ptr, 4 KiB row-exchange buffer
 
 struct TnParams {
@@ -410,9 +411,13 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     int xslot = 0;
     const float inv_n = 1.0f / (float)p.n_valid;
     const int col_half = n_tile * BN + hf * HALF;
-    const bool use_r = p.resid != nullptr && (EPI == KAIR_EPI_LINEAR || EPI == KAIR_EPI_RESID_LN || EPI == KAIR_EPI_LNBWD);
+    // TN_EPI_LEAN: LINEAR with bias / ReLU (optional) and the bf16 output only -- qkv, the proj input gradient, the
+    // DnCNN body convolutions: the option tests below fold away at compile time (the epilogue is instruction / branch bound:
+    // ncu showed 14 % branch_resolving + 12 % no_inst stalls in the generic LINEAR loop)
+    constexpr bool kLean = (EPI == TN_EPI_LEAN);
+    const bool use_r = !kLean && p.resid != nullptr && (EPI == KAIR_EPI_LINEAR || EPI == KAIR_EPI_RESID_LN || EPI == KAIR_EPI_LNBWD);
     // LINEAR with aux: activation backward, v *= (aux > 0 ? 1 : act_slope) with aux = the saved activation output
-    const bool use_a = (EPI == KAIR_EPI_DGELU || EPI == KAIR_EPI_LNBWD || (EPI == KAIR_EPI_LINEAR && p.aux != nullptr));
+    const bool use_a = !kLean && (EPI == KAIR_EPI_DGELU || EPI == KAIR_EPI_LNBWD || (EPI == KAIR_EPI_LINEAR && p.aux != nullptr));
     const bool has_ld = use_r || use_a;
     // The warp's 12 KiB of staging memory is a ring of ringD buffers of ringS bytes; slot k uses buffer k % ringD and
     // its operands are TMA-prefetched ringDist slots ahead.
@@ -542,7 +547,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       const bool more_tiles = (m_tile + m_stride) < p.m_tiles;
       const TileCoord t_next = tile_coord<kConv>(p, more_tiles ? m_tile + m_stride : m_tile);
       float sa = 1.0f, sb = 1.0f;  // DropPath per-sample scales
-      if (tok >= 0) {
+      if (!kLean && tok >= 0) {
         if (p.acc_scale) sa = __ldg(p.acc_scale + tok / p.tokens_per_sample);
         if (p.outB_scale) sb = __ldg(p.outB_scale + tok / p.tokens_per_sample);
       }
@@ -550,7 +555,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       tcgen05_fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * HALF;
 
-      if (EPI == KAIR_EPI_LINEAR) {
+      if (EPI == KAIR_EPI_LINEAR || kLean) {
 #pragma unroll 1
         for (int c = 0; c < ((TN_DBG(p) & 4) ? 0 : NCH); ++c) {  // dbg 4: ablation, epilogue = barrier handshake only
           const int col = col_half + c * 32;
@@ -565,7 +570,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             load_acc(tacc + c * 32, v);
           }
           add_bias(v, col);
-          if (p.acc_scale) {
+          if (!kLean && p.acc_scale) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] *= sa;
           }
@@ -580,13 +585,13 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.act_slope;
           }
-          if (p.has_outF) stage_f32(buf, lane, v);
-          if (p.has_outB) {
-            if (p.outB_scale) {
+          if (!kLean && p.has_outF) stage_f32(buf, lane, v);
+          if (kLean || p.has_outB) {
+            if (!kLean && p.outB_scale) {
 #pragma unroll
               for (int i = 0; i < 32; ++i) v[i] *= sb;
             }
-            if (p.ones_col >= col && p.ones_col < col + 32) {
+            if (!kLean && p.ones_col >= col && p.ones_col < col + 32) {
 #pragma unroll
               for (int i = 0; i < 32; ++i)
                 if (col + i == p.ones_col) v[i] = 1.0f;
@@ -596,8 +601,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
-            if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + boff, t, q, col);
+            if (!kLean && p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
+            if (kLean || p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + boff, t, q, col);
           }
           slot_end(true);
         }
@@ -849,6 +854,10 @@ static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool b
                            cudaStream_t st) {
 #define KB_CASE(BN_, EPI_, CONV_) \
   if (bn == BN_ && epi == EPI_ && conv == CONV_) return launch_res<BN_, EPI_, CONV_>(p, bres, grid, smem, st);
+  KB_CASE(192, TN_EPI_LEAN, false)
+  KB_CASE(64, TN_EPI_LEAN, false)
+  KB_CASE(192, TN_EPI_LEAN, true)
+  KB_CASE(64, TN_EPI_LEAN, true)
   KB_CASE(192, KAIR_EPI_LINEAR, false)
   KB_CASE(192, KAIR_EPI_GELU, false)
   KB_CASE(192, KAIR_EPI_RESID_LN, false)
@@ -876,6 +885,11 @@ static int launch_dispatch(const TnParams& p, int bn, int epi, bool conv, bool b
 #undef KB_CASE
   set_error("kair_gemm_tn: configuration bn=%d mode=%d conv=%d is not instantiated", bn, epi, (int)conv);
   return -1;
+}
+
+static bool tn_is_lean(const kair_gemm_tn_args& a) {
+  return a.mode == KAIR_EPI_LINEAR && a.outB && !a.outF && !a.resid && !a.aux && !a.acc_scale && !a.outB_scale &&
+         a.ones_col < 0 && (a.bn == 192 || a.bn == 64);
 }
 
 int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
@@ -1057,7 +1071,7 @@ int gemm_tn_launch(const kair_gemm_tn_args& a, cudaStream_t st) {
   grid = (grid / p.n_tiles) * p.n_tiles;
   KB_CHECK(grid >= p.n_tiles, "kair_gemm_tn: n_tiles=%d exceeds the SM count", p.n_tiles);
 
-  return launch_dispatch(p, a.bn, a.mode, a.conv != 0, bres, grid, smem, st);
+  return launch_dispatch(p, a.bn, tn_is_lean(a) ? TN_EPI_LEAN : a.mode, a.conv != 0, bres, grid, smem, st);
 }
 
 }  // namespace kb
