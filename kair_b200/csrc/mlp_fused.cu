@@ -85,7 +85,9 @@ __device__ __forceinline__ void mf_stage_f32(uint8_t* buf, int lane, const float
   }
 }
 
-template <int N>
+// kTrain: u and g are written for the backward pass; kLN: LayerNorm epilogue.  Compile-time, because the epilogue loops
+// are instruction / branch bound (the same finding as gemm_tn's lean LINEAR instantiation).
+template <int N, bool kTrain, bool kLN>
 __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_constant__ MfParams p) {
   constexpr int KS1 = N / 64;              // k-slices of the first GEMM
   constexpr int F = 2 * N;                 // hidden width (mlp_ratio 2, padded)
@@ -129,8 +131,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
     if (p.has_resid) tma_prefetch_desc(&p.tmResid);
     if (p.has_outF) tma_prefetch_desc(&p.tmOutF);
     if (p.has_outB) tma_prefetch_desc(&p.tmOutB);
-    if (p.has_u) tma_prefetch_desc(&p.tmU);
-    if (p.has_g) tma_prefetch_desc(&p.tmG);
+    if (kTrain) tma_prefetch_desc(&p.tmU);
+    if (kTrain) tma_prefetch_desc(&p.tmG);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -227,7 +229,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         auto gemm2 = [&](int cc) {
           mbar_wait(g_full, gq & 1);
           tcgen05_fence_after();
-          if (p.has_g) {   // the hidden activations of a training plan leave from the operand tile itself
+          if (kTrain) {   // the hidden activations of a training plan leave from the operand tile itself
             tma_store_2d(&p.tmG, g_base, (cc * 2) * 64, tile * MF_BM);
             tma_store_2d(&p.tmG, g_base + MF_BM * 128, (cc * 2 + 1) * 64, tile * MF_BM);
             tma_store_commit();
@@ -249,7 +251,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
               umma_commit(&w_empty[stage]);
               next_stage();
             }
-          if (p.has_g) tma_store_wait_read<0>();   // the G tile is re-written once both its readers are done
+          if (kTrain) tma_store_wait_read<0>();   // the G tile is re-written once both its readers are done
           umma_commit(g_empty);
           ++gq;
         };
@@ -278,7 +280,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         gemm2(NC - 1);
         umma_commit(acc2_full);
       }
-      if (p.has_g) tma_store_wait_all<0>();
+      if (kTrain) tma_store_wait_all<0>();
     }
     __syncwarp();
   } else {
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
 
     // training plans stage u through the same per-warp buffers during the hidden chunks, so the residual chunk of the
     // NEXT tile cannot be prefetched across the tile boundary there; it is requested when the output phase begins
-    const bool xprefetch = !p.has_u;
+    const bool xprefetch = !kTrain;
     int tile = blockIdx.x;
     if (use_r && xprefetch && lane == 0 && tile < p.m_tiles) issue_load(0, tile, col_half);
     __syncwarp();
@@ -387,7 +389,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
               v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + b4.w;
             }
           }
-          if (p.has_u) {   // pre-activation of a training plan: 2 KiB sub-buffers of this warp's staging, round robin
+          if (kTrain) {   // pre-activation of a training plan: 2 KiB sub-buffers of this warp's staging, round robin
             uint8_t* ub = stg + ((gc * 2 + g2) & 3) * 2048;
             if (lane == 0) tma_store_wait_read<3>();
             __syncwarp();
@@ -431,7 +433,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         __syncwarp();
         if (lane == 0) mbar_arrive(g_full);
       }
-      if (p.has_u) {   // the staging buffers are about to hold residual chunks again
+      if (kTrain) {   // the staging buffers are about to hold residual chunks again
         if (lane == 0) {
           tma_store_wait_read<0>();
           if (use_r) issue_load(ridx, tile, col_half);
@@ -465,7 +467,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           }
         }
         if (use_r) add_row_f32(v, buf);
-        if (p.ln) {
+        if (kLN) {
           float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
@@ -485,7 +487,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           __syncwarp();
           if (lane == 0) tma_store_2d(&p.tmOutF, buf, col, row0);
           stored = true;
-        } else if (!p.ln && p.has_outB) {
+        } else if (!kLN && p.has_outB) {
           // no LayerNorm (the block that closes an RSTB): v itself goes out as the bf16 operand of the next convolution
           if (p.ones_col >= col && p.ones_col < col + 32) {
 #pragma unroll
@@ -501,7 +503,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         }
         slot_end(stored);
       }
-      if (p.ln) {
+      if (kLN) {
         tmem_st_wait();
         float tot, dummy;
         exchange2(s1, 0.f, tot, dummy);
@@ -559,7 +561,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           }
         }
       }
-      if (p.has_u) {   // the next tile stages u through these buffers with a relaxed wait: drain this tile's stores first
+      if (kTrain) {   // the next tile stages u through these buffers with a relaxed wait: drain this tile's stores first
         if (lane == 0) tma_store_wait_read<0>();
         __syncwarp();
       }
@@ -579,9 +581,9 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
   }
 }
 
-template <int N>
-int mf_launch(const MfParams& p, int grid, size_t smem, cudaStream_t st) {
-  auto kern = mlp_fused_kernel<N>;
+template <int N, bool kTrain, bool kLN>
+int mf_launch_cfg(const MfParams& p, int grid, size_t smem, cudaStream_t st) {
+  auto kern = mlp_fused_kernel<N, kTrain, kLN>;
   static bool attr_set[64] = {false};
   int dev = 0;
   KB_CUDA(cudaGetDevice(&dev));
@@ -591,6 +593,15 @@ int mf_launch(const MfParams& p, int grid, size_t smem, cudaStream_t st) {
   }
   KB_CUDA(launch_pdl(kern, grid, MF_THREADS, smem, st, p));
   return 0;
+}
+
+template <int N>
+int mf_launch(const MfParams& p, int grid, size_t smem, cudaStream_t st) {
+  const bool train = p.has_u != 0;
+  if (train && p.ln) return mf_launch_cfg<N, true, true>(p, grid, smem, st);
+  if (train) return mf_launch_cfg<N, true, false>(p, grid, smem, st);
+  if (p.ln) return mf_launch_cfg<N, false, true>(p, grid, smem, st);
+  return mf_launch_cfg<N, false, false>(p, grid, smem, st);
 }
 
 }  // namespace
@@ -605,6 +616,7 @@ int mlp_fused_launch(const kair_mlp_fused_args& a, cudaStream_t st) {
   KB_CHECK(a.outF || a.outB, "kair_mlp_fused: no output");
   KB_CHECK(a.ln || !(a.outF && a.outB), "kair_mlp_fused: without LayerNorm exactly one of outF / outB is written");
   KB_CHECK(!a.acc_scale || a.tokens_per_sample > 0, "kair_mlp_fused: tokens_per_sample required");
+  KB_CHECK((a.outU != nullptr) == (a.outG != nullptr), "kair_mlp_fused: outU and outG come together (training plans)");
   if (check_device() != 0) return -3;
 
   MfParams p;
