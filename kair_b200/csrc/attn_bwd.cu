@@ -296,28 +296,41 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
             pr[32 + j] = __uint_as_float(r1[j]);
           }
         }
-        // four independent max / sum / delta chains (a 64-long dependent chain costs 64 x 4 cycles per row)
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        // bias, mask (only the windows on the shifted border carry one), softmax.  All fp32 arithmetic of this phase is
+        // packed two lanes per instruction (FADD2 / FFMA2 / FMUL2): the phase was issue bound (two gradient warps per
+        // scheduler, ~15 issue slots per element).  Four independent max / sum / delta chains.
 #pragma unroll
-        for (int j = 0; j < 64; ++j) {
+        for (int j = 0; j < 64; j += 2) {
           const int qj = j >> 4;
           const int jy = (qj >> 1) * 4 + ((j & 15) >> 2);
           const int jx = (qj & 1) * 4 + (j & 3);
-          pr[j] = pr[j] + tb[(7 - jy) * 15 + (7 - jx)] + madd[qj];
-          mx4[j & 3] = fmaxf(mx4[j & 3], pr[j]);
+          const int o = (7 - jy) * 15 + (7 - jx);   // column j + 1 sits one step to the right: table offset o - 1
+          add2(pr[j], pr[j + 1], pr[j], pr[j + 1], tb[o], tb[o - 1]);
         }
+        if (lastrow || lastcol) {
+#pragma unroll
+          for (int j = 0; j < 64; j += 2) add2(pr[j], pr[j + 1], pr[j], pr[j + 1], madd[j >> 4], madd[j >> 4]);
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int j = 0; j < 64; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], pr[j]);
         const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
         float sum4[4] = {0.f, 0.f, 0.f, 0.f};
-        const float mb = mx * LOG2E;
+        const float nmb = -mx * LOG2E;
 #pragma unroll
-        for (int j = 0; j < 64; ++j) {
-          pr[j] = ex2_approx(fmaf(pr[j], LOG2E, -mb));
-          sum4[j & 3] += pr[j];
+        for (int j = 0; j < 64; j += 4) {
+          fma2(pr[j], pr[j + 1], pr[j], pr[j + 1], LOG2E, LOG2E, nmb, nmb);
+          fma2(pr[j + 2], pr[j + 3], pr[j + 2], pr[j + 3], LOG2E, LOG2E, nmb, nmb);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) pr[j + u] = ex2_approx(pr[j + u]);
+          add2(sum4[0], sum4[1], sum4[0], sum4[1], pr[j], pr[j + 1]);
+          add2(sum4[2], sum4[3], sum4[2], sum4[3], pr[j + 2], pr[j + 3]);
         }
         const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
-        const float inv = 1.0f / sum;
+        // rows of the padding window of an odd window count get P = 0, hence dS = 0 and no d_table contribution
+        const float inv = my_valid ? 1.0f / sum : 0.0f;
 #pragma unroll
-        for (int j = 0; j < 64; ++j) pr[j] *= inv;
+        for (int j = 0; j < 64; j += 2) mul2(pr[j], pr[j + 1], pr[j], pr[j + 1], inv, inv);
 
         // ---- C: delta = sum_j P_ij dP_ij
         AB_CS();
@@ -328,18 +341,22 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
           tmem_ld32(tW + 64 + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) dl4[j & 3] = fmaf(pr[c * 32 + j], __uint_as_float(r[j]), dl4[j & 3]);
+          for (int j = 0; j < 32; j += 4) {
+            fma2(dl4[0], dl4[1], pr[c * 32 + j], pr[c * 32 + j + 1], __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                 dl4[0], dl4[1]);
+            fma2(dl4[2], dl4[3], pr[c * 32 + j + 2], pr[c * 32 + j + 3], __uint_as_float(r[j + 2]),
+                 __uint_as_float(r[j + 3]), dl4[2], dl4[3]);
+          }
         }
-        const float delta = (dl4[0] + dl4[1]) + (dl4[2] + dl4[3]);
+        const float ndelta = -((dl4[0] + dl4[1]) + (dl4[2] + dl4[3]));
 
         // ---- D: the P/dS tiles double as the previous iteration's output staging: wait for its TMA reads
         AB_CS();
-        if (lane == 0) tma_store_wait_read<0>();   // every warp issued the stores of its own quadrant rows
+        if (lane < 6) tma_store_wait_read<0>();   // every warp issued the stores of its own quadrant rows
         named_bar_sync(2 + g, 128);
         AB_CS();
 
         // ---- E: dS, d_table partial sums, P/dS -> smem
-        const float vmask = my_valid ? 1.0f : 0.0f;
         const uint32_t prow = smem_u32(pds) + row * 128;
         const uint32_t dsrow = prow + 16384;
         const uint32_t sw = row & 7;
@@ -351,9 +368,13 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
           tmem_ld_wait();
           float ds[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            ds[j] = pr[c * 32 + j] * (__uint_as_float(r[j]) - delta) * vmask;
-            a[j] = __float_as_uint(__uint_as_float(a[j]) + ds[j]);
+          for (int j = 0; j < 32; j += 2) {
+            float t0, t1, a0, a1;
+            add2(t0, t1, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), ndelta, ndelta);
+            mul2(ds[j], ds[j + 1], pr[c * 32 + j], pr[c * 32 + j + 1], t0, t1);
+            add2(a0, a1, __uint_as_float(a[j]), __uint_as_float(a[j + 1]), ds[j], ds[j + 1]);
+            a[j] = __float_as_uint(a0);
+            a[j + 1] = __float_as_uint(a1);
           }
           tmem_st32(tACC + c * 32, a);
 #pragma unroll
@@ -409,17 +430,14 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         __syncwarp();
         if (lane == 0) mbar_arrive(&w_free[g]);
         AB_CS();
-        // the staging rows of quadrant q of both windows were written by this warp alone: its lane 0 stores them
-        // (6 TMA operations per warp instead of 24 from one thread, which took ~2600 cycles)
-        if (lane == 0) {
-#pragma unroll
-          for (int t3 = 0; t3 < 3; ++t3)
-            tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + q * 1024, t3 * nH * 32 + h * 32, sx, sy, wb);
-          if (second_valid) {
-#pragma unroll
-            for (int t3 = 0; t3 < 3; ++t3)
-              tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (4 + q) * 1024, t3 * nH * 32 + h * 32, sx1, sy1, sb1);
-          }
+        // the staging rows of quadrant q of both windows were written by this warp alone.  A TMA store costs the
+        // issuing THREAD 130-300 cycles, so the six boxes (dq, dk, dv of two windows) go out from six lanes at once
+        // (one thread issuing 24 took ~2600 cycles, lane 0 of each warp issuing 6 took ~1300)
+        if (lane < 6) {
+          const int t3 = lane % 3, ws = lane / 3;
+          if (ws == 0 || second_valid)
+            tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws * 4 + q) * 1024, t3 * nH * 32 + h * 32, ws ? sx1 : sx,
+                         ws ? sy1 : sy, ws ? sb1 : wb);
           tma_store_commit();
         }
         __syncwarp();
@@ -431,7 +449,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
       // its (8-|dy|)(8-|dx|) contributions with plain loads: one global atomic per entry and pass.  (Shared-memory
       // atomics per (i, j) cost ~21 000 cycles per pass: fp32 atomicAdd on shared memory is a CAS loop.)
       {
-        if (lane == 0) tma_store_wait_read<0>();
+        if (lane < 6) tma_store_wait_read<0>();
         named_bar_sync(2 + g, 128);
         float* M = reinterpret_cast<float*>(pds);  // [64][65]
 #pragma unroll
@@ -477,7 +495,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         named_bar_sync(2 + g, 128);
       }
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    if (lane < 6) tma_store_wait_all<0>();
     __syncwarp();
   }
 

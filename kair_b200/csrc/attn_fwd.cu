@@ -350,29 +350,38 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         if (lane == 0) mbar_arrive(&s_empty[g]);
         if (tsw) AF_TS(2, tsn);
         // scores in the exp2 domain: t = s*log2(e) + bias*log2(e) (+ mask); 4-way split max / sum chains for ILP
+        // (fp32 math packed two lanes per instruction: FFMA2 / FADD2; the phase is issue bound)
         const bool masked = lastrow || lastcol;
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int j = 0; j < 64; ++j) {
+        for (int j = 0; j < 64; j += 2) {
           const int qj = j >> 4;
           const int jy = (qj & 1) * 4 + ((j & 15) >> 2);
           const int jx = (qj >> 1) * 4 + (j & 3);
-          s[j] = fmaf(s[j], LOG2E, tb[(7 - jy) * 15 + (7 - jx)]);
-          if (masked) s[j] += madd[qj];
-          mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
+          const int o = (7 - jy) * 15 + (7 - jx);   // column j + 1 is one pixel to the right: table offset o - 1
+          fma2(s[j], s[j + 1], s[j], s[j + 1], LOG2E, LOG2E, tb[o], tb[o - 1]);
         }
-        const float mb = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        if (masked) {
+#pragma unroll
+          for (int j = 0; j < 64; j += 2) add2(s[j], s[j + 1], s[j], s[j + 1], madd[j >> 4], madd[j >> 4]);
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int j = 0; j < 64; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
+        const float nmb = -fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
         float sum4[4] = {0.f, 0.f, 0.f, 0.f};
         uint32_t pk[32];
 #pragma unroll
-        for (int j = 0; j < 64; j += 2) {
-          float e0, e1;
-          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(s[j] - mb));
-          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(s[j + 1] - mb));
-          __nv_bfloat162 b2 = __floats2bfloat162_rn(e0, e1);
-          float2 f2 = __bfloat1622float2(b2);
-          sum4[(j >> 1) & 3] += f2.x + f2.y;  // normalise by the sum of the values the tensor core will actually see
-          pk[j >> 1] = *reinterpret_cast<uint32_t*>(&b2);
+        for (int j = 0; j < 64; j += 4) {
+          add2(s[j], s[j + 1], s[j], s[j + 1], nmb, nmb);
+          add2(s[j + 2], s[j + 3], s[j + 2], s[j + 3], nmb, nmb);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) s[j + u] = ex2_approx(s[j + u]);
+          pk[j >> 1] = pack_bf16x2(s[j], s[j + 1]);
+          pk[(j >> 1) + 1] = pack_bf16x2(s[j + 2], s[j + 3]);
+          // the row sum is taken over the unrounded exponentials: against the sum of the bf16 values the tensor core
+          // sees it differs by ~2^-9 / sqrt(64) relative, an order below the bf16 rounding of the output itself
+          add2(sum4[0], sum4[1], sum4[0], sum4[1], s[j], s[j + 1]);
+          add2(sum4[2], sum4[3], sum4[2], sum4[3], s[j + 2], s[j + 3]);
         }
         const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
         inv_sum[hh] = 1.0f / sum;
@@ -411,7 +420,8 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         const float sc = inv_sum[hh];
         float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * sc;
+        for (int j = 0; j < 32; j += 2)
+          mul2(v[j], v[j + 1], __uint_as_float(r[j]), __uint_as_float(r[j + 1]), sc, sc);
         const uint32_t base = smem_u32(out_s + (h >> 1) * 16384) + row * 128;
         const uint32_t sw = row & 7;
 #pragma unroll

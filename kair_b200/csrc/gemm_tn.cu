@@ -456,7 +456,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           float4 b4 = bp[i];  // warp-uniform address: shared-memory broadcast
-          v[4 * i] += b4.x; v[4 * i + 1] += b4.y; v[4 * i + 2] += b4.z; v[4 * i + 3] += b4.w;
+          add2(v[4 * i], v[4 * i + 1], v[4 * i], v[4 * i + 1], b4.x, b4.y);
+          add2(v[4 * i + 2], v[4 * i + 3], v[4 * i + 2], v[4 * i + 3], b4.z, b4.w);
         }
       }
     };
@@ -505,7 +506,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(r4.x), "=f"(r4.y), "=f"(r4.z), "=f"(r4.w)
                      : "r"(base + ((j ^ sw) << 4)));
-        v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+        add2(v[4 * j], v[4 * j + 1], v[4 * j], v[4 * j + 1], r4.x, r4.y);
+        add2(v[4 * j + 2], v[4 * j + 3], v[4 * j + 2], v[4 * j + 3], r4.z, r4.w);
       }
     };
     auto read_row_bf16 = [&](float (&x)[32], const uint8_t* buf) {
@@ -572,7 +574,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           add_bias(v, col);
           if (!kLean && p.acc_scale) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] *= sa;
+            for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], v[i], v[i + 1], sa, sa);
           }
           if (use_a) {
             float u[32];
@@ -589,7 +591,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           if (kLean || p.has_outB) {
             if (!kLean && p.outB_scale) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] *= sb;
+              for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], v[i], v[i + 1], sb, sb);
             }
             if (!kLean && p.ones_col >= col && p.ones_col < col + 32) {
 #pragma unroll
@@ -616,7 +618,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           add_bias(v, col);
           if (p.has_outB2) stage_bf16(buf, lane, v);  // pre-activation u
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+          for (int i = 0; i < 32; i += 2) gelu_erf2(v[i], v[i + 1]);
           if (p.ones_col >= col && p.ones_col < col + 32) {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
@@ -645,14 +647,15 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           add_bias(v, col);
           if (p.acc_scale) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] *= sa;
+            for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], v[i], v[i + 1], sa, sa);
           }
           if (use_r) add_row_f32(v, buf);
           {  // four independent partial sums: a single 32-long FADD chain costs 32 x 4 dependent cycles
             float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
-              p0 += v[i]; p1 += v[i + 1]; p2 += v[i + 2]; p3 += v[i + 3];
+              add2(p0, p1, p0, p1, v[i], v[i + 1]);
+              add2(p2, p3, p2, p3, v[i + 2], v[i + 3]);
             }
             s1 += (p0 + p1) + (p2 + p3);
           }
@@ -684,9 +687,11 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            const float d0 = __uint_as_float(r[i]) - mean, d1 = __uint_as_float(r[i + 1]) - mean;
-            const float d2 = __uint_as_float(r[i + 2]) - mean, d3 = __uint_as_float(r[i + 3]) - mean;
-            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2); q3 = fmaf(d3, d3, q3);
+            float d0, d1, d2, d3;
+            add2(d0, d1, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), -mean, -mean);
+            add2(d2, d3, __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]), -mean, -mean);
+            fma2(q0, q1, d0, d1, d0, d1, q0, q1);
+            fma2(q2, q3, d2, d3, d2, d3, q2, q3);
           }
           s2 += (q0 + q1) + (q2 + q3);
         }
@@ -706,10 +711,16 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             tmem_ld32(tacc + c * 32, r);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              float x = (__uint_as_float(r[i]) - mean) * rstd;
-              int cg = col + i;
-              v[i] = cg < p.n_valid ? x : (cg == p.ones_col ? 1.0f : 0.0f);
+            for (int i = 0; i < 32; i += 2) {
+              add2(v[i], v[i + 1], __uint_as_float(r[i]), __uint_as_float(r[i + 1]), -mean, -mean);
+              mul2(v[i], v[i + 1], v[i], v[i + 1], rstd, rstd);
+            }
+            if (col + 32 > p.n_valid) {   // only the chunk that holds the padding columns pays for the selects
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const int cg = col + i;
+                if (cg >= p.n_valid) v[i] = cg == p.ones_col ? 1.0f : 0.0f;
+              }
             }
           }
           uint8_t* bb = stg + (c & 1) * 6144 + 4096;
@@ -735,7 +746,11 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           load_acc(tacc + c * 32, v);
           read_row_bf16(u, buf);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] *= gelu_erf_grad(u[i]);
+          for (int i = 0; i < 32; i += 2) {
+            float g0, g1;
+            gelu_erf_grad2(u[i], u[i + 1], g0, g1);
+            mul2(v[i], v[i + 1], v[i], v[i + 1], g0, g1);
+          }
           stage_bf16(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
@@ -759,8 +774,8 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             const float a0 = __uint_as_float(r[i]), a1 = __uint_as_float(r[i + 1]);
-            p0 += a0; p1 += a1;
-            q0 = fmaf(a0, x[i], q0); q1 = fmaf(a1, x[i + 1], q1);
+            add2(p0, p1, p0, p1, a0, a1);
+            fma2(q0, q1, a0, a1, x[i], x[i + 1], q0, q1);
           }
           s1 += p0 + p1;
           s2 += q0 + q1;
@@ -784,17 +799,25 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             tmem_ld32(tacc + c * 32, r);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = rstd * (__uint_as_float(r[i]) - m1 - x[i] * m2);
+            for (int i = 0; i < 32; i += 2) {   // rstd * fma(-x, m2, dy - m1)
+              float a0, a1;
+              add2(a0, a1, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), -m1, -m1);
+              fma2(a0, a1, x[i], x[i + 1], -m2, -m2, a0, a1);
+              mul2(v[i], v[i + 1], a0, a1, rstd, rstd);
+            }
           }
           if (use_r) add_row_f32(v, buf);
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (col + i >= p.n_valid) v[i] = 0.f;
+          if (col + 32 > p.n_valid) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col + i >= p.n_valid) v[i] = 0.f;
+          }
           if (p.has_outF) stage_f32(buf, lane, v);
           if (p.has_outB) {
             if (p.outB_scale) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] *= sb;
+              for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], v[i], v[i + 1], sb, sb);
             }
             stage_bf16(buf + 4096, lane, v);
           }

@@ -343,7 +343,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(r4.x), "=f"(r4.y), "=f"(r4.z), "=f"(r4.w)
                      : "r"(base + ((j ^ sw) << 4)));
-        v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+        add2(v[4 * j], v[4 * j + 1], v[4 * j], v[4 * j + 1], r4.x, r4.y);
+        add2(v[4 * j + 2], v[4 * j + 3], v[4 * j + 2], v[4 * j + 3], r4.z, r4.w);
       }
     };
 
@@ -383,10 +384,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const float4 b4 = bp[i];
-              v[4 * i] = __uint_as_float(r[4 * i]) + b4.x;
-              v[4 * i + 1] = __uint_as_float(r[4 * i + 1]) + b4.y;
-              v[4 * i + 2] = __uint_as_float(r[4 * i + 2]) + b4.z;
-              v[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + b4.w;
+              add2(v[4 * i], v[4 * i + 1], __uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), b4.x, b4.y);
+              add2(v[4 * i + 2], v[4 * i + 3], __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]), b4.z, b4.w);
             }
           }
           if (kTrain) {   // pre-activation of a training plan: 2 KiB sub-buffers of this warp's staging, round robin
@@ -402,7 +401,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
             }
           }
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+          for (int i = 0; i < 32; i += 2) gelu_erf2(v[i], v[i + 1]);
           if (p.ones_col_g >= hcol && p.ones_col_g < hcol + 32) {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
@@ -460,10 +459,10 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float4 b4 = bp[i];
-            v[4 * i] = (__uint_as_float(r[4 * i]) + b4.x) * sa;
-            v[4 * i + 1] = (__uint_as_float(r[4 * i + 1]) + b4.y) * sa;
-            v[4 * i + 2] = (__uint_as_float(r[4 * i + 2]) + b4.z) * sa;
-            v[4 * i + 3] = (__uint_as_float(r[4 * i + 3]) + b4.w) * sa;
+            add2(v[4 * i], v[4 * i + 1], __uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), b4.x, b4.y);
+            add2(v[4 * i + 2], v[4 * i + 3], __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]), b4.z, b4.w);
+            mul2(v[4 * i], v[4 * i + 1], v[4 * i], v[4 * i + 1], sa, sa);
+            mul2(v[4 * i + 2], v[4 * i + 3], v[4 * i + 2], v[4 * i + 3], sa, sa);
           }
         }
         if (use_r) add_row_f32(v, buf);
@@ -471,7 +470,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            p0 += v[i]; p1 += v[i + 1]; p2 += v[i + 2]; p3 += v[i + 3];
+            add2(p0, p1, p0, p1, v[i], v[i + 1]);
+            add2(p2, p3, p2, p3, v[i + 2], v[i + 3]);
           }
           s1 += (p0 + p1) + (p2 + p3);
           uint32_t r[32];
@@ -517,9 +517,11 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            const float d0 = __uint_as_float(r[i]) - mean, d1 = __uint_as_float(r[i + 1]) - mean;
-            const float d2 = __uint_as_float(r[i + 2]) - mean, d3 = __uint_as_float(r[i + 3]) - mean;
-            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2); q3 = fmaf(d3, d3, q3);
+            float d0, d1, d2, d3;
+            add2(d0, d1, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), -mean, -mean);
+            add2(d2, d3, __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]), -mean, -mean);
+            fma2(q0, q1, d0, d1, d0, d1, q0, q1);
+            fma2(q2, q3, d2, d3, d2, d3, q2, q3);
           }
           s2 += (q0 + q1) + (q2 + q3);
         }
@@ -542,10 +544,16 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
               tmem_ld32(tacc + c * 32, r);
               tmem_ld_wait();
 #pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                const float x = (__uint_as_float(r[i]) - mean) * rstd;
-                const int cg = col + i;
-                v[i] = cg < p.n_valid ? x : (cg == p.ones_col ? 1.0f : 0.0f);
+              for (int i = 0; i < 32; i += 2) {
+                add2(v[i], v[i + 1], __uint_as_float(r[i]), __uint_as_float(r[i + 1]), -mean, -mean);
+                mul2(v[i], v[i + 1], v[i], v[i + 1], rstd, rstd);
+              }
+              if (col + 32 > p.n_valid) {   // only the chunk that holds the padding columns pays for the selects
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                  const int cg = col + i;
+                  if (cg >= p.n_valid) v[i] = cg == p.ones_col ? 1.0f : 0.0f;
+                }
               }
             }
             uint8_t* bb = free_buf + (c & 1) * 2048;
