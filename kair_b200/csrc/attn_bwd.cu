@@ -112,7 +112,10 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // The whole warp runs the loop and one ELECTED thread issues: under `if (lane == 0)` the compiler cannot prove a
+    // single active thread and wraps every UTMALDG / UTCHMMA / UTMASTG (uniform-datapath operands) in an
+    // ELECT / R2UR / BRA.U.ANY waterfall loop, ~100-300 cycles per instruction; under elect.sync they issue back to back.
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int hp = 0; hp < hpairs; ++hp) {
@@ -123,19 +126,22 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
           ab_window_origin(p, gw0, wb[0], wi[0], wj[0]);
           ab_window_origin(p, gw1, wb[1], wi[1], wj[1]);
           mbar_wait(&st_empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&st_full[stage], AB_STAGE);
-          uint8_t* st = stage_s + stage * AB_STAGE;
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&st_full[stage], AB_STAGE);
+            uint8_t* st = stage_s + stage * AB_STAGE;
 #pragma unroll
-          for (int wq = 0; wq < 8; ++wq) {
-            const int wsel = wq >> 2, quad = wq & 3;
-            const int hh = (wi[wsel] * 8 + (quad >> 1) * 4 + p.shift) % p.H;
-            const int ww = (wj[wsel] * 8 + (quad & 1) * 4 + p.shift) % p.W;
+            for (int wq = 0; wq < 8; ++wq) {
+              const int wsel = wq >> 2, quad = wq & 3;
+              const int hh = (wi[wsel] * 8 + (quad >> 1) * 4 + p.shift) % p.H;
+              const int ww = (wj[wsel] * 8 + (quad & 1) * 4 + p.shift) % p.W;
 #pragma unroll
-            for (int t3 = 0; t3 < 3; ++t3)
-              tma_load_4d(st + t3 * 16384 + wq * 2048, &p.tmQKV, &st_full[stage], t3 * nH * 32 + hp * 64, ww, hh,
-                          wb[wsel]);
-            tma_load_4d(st + 3 * 16384 + wq * 2048, &p.tmDO, &st_full[stage], hp * 64, ww, hh, wb[wsel]);
+              for (int t3 = 0; t3 < 3; ++t3)
+                tma_load_4d(st + t3 * 16384 + wq * 2048, &p.tmQKV, &st_full[stage], t3 * nH * 32 + hp * 64, ww, hh,
+                            wb[wsel]);
+              tma_load_4d(st + 3 * 16384 + wq * 2048, &p.tmDO, &st_full[stage], hp * 64, ww, hh, wb[wsel]);
+            }
           }
+          __syncwarp();
           if (++stage == 2) {
             stage = 0;
             phase ^= 1;
@@ -146,7 +152,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     __syncwarp();
   } else if (warp == 1 || warp == 10) {
     // ================================ MMA issuers (warp 1: group 0, warp 10: group 1) ================================
-    if (lane == 0) {
+    {
       const int g = warp == 1 ? 0 : 1;
       constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);    // S, dP
       constexpr uint32_t idesc_dv = make_idesc_bf16(64, 32, 1, 1);   // P^T dO, dS^T Q
@@ -170,6 +176,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
             mbar_wait(&w_free[g], (it & 1) ^ 1);
             tcgen05_fence_after();
             const uint32_t tw = tmem_base + g * 128;
+            if (elect_one()) {
 #pragma unroll
             for (int w = 0; w < 2; ++w) {
               const uint32_t lo = (uint32_t)(w * 16) << 16;
@@ -185,6 +192,8 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
               }
             }
             umma_commit(&sdp_full[g]);
+            }
+            __syncwarp();
             AB_MS();
           }
           {
@@ -193,6 +202,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
             const uint32_t tw = tmem_base + g * 128;
             const uint32_t p_addr = smem_u32(pds_s + g * AB_PDS);
             const uint32_t ds_addr = p_addr + 16384;
+            if (elect_one()) {
 #pragma unroll
             for (int w = 0; w < 2; ++w) {
               const uint32_t lo = (uint32_t)(w * 16) << 16;
@@ -213,9 +223,11 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
               }
             }
             umma_commit(&grad_full[g]);
+            umma_commit(&st_empty[stage]);
+            }
+            __syncwarp();
             AB_MS();
           }
-          umma_commit(&st_empty[stage]);
           if (++stage == 2) {
             stage = 0;
             phase ^= 1;
@@ -352,7 +364,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
 
         // ---- D: the P/dS tiles double as the previous iteration's output staging: wait for its TMA reads
         AB_CS();
-        if (lane < 6) tma_store_wait_read<0>();   // every warp issued the stores of its own quadrant rows
+        if (elect_one()) tma_store_wait_read<0>();   // every warp issued the stores of its own quadrant rows
         named_bar_sync(2 + g, 128);
         AB_CS();
 
@@ -430,14 +442,16 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         __syncwarp();
         if (lane == 0) mbar_arrive(&w_free[g]);
         AB_CS();
-        // the staging rows of quadrant q of both windows were written by this warp alone.  A TMA store costs the
-        // issuing THREAD 130-300 cycles, so the six boxes (dq, dk, dv of two windows) go out from six lanes at once
-        // (one thread issuing 24 took ~2600 cycles, lane 0 of each warp issuing 6 took ~1300)
-        if (lane < 6) {
-          const int t3 = lane % 3, ws = lane / 3;
-          if (ws == 0 || second_valid)
-            tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (ws * 4 + q) * 1024, t3 * nH * 32 + h * 32, ws ? sx1 : sx,
-                         ws ? sy1 : sy, ws ? sb1 : wb);
+        // the staging rows of quadrant q of both windows were written by this warp alone: its elected thread stores them
+        if (elect_one()) {
+#pragma unroll
+          for (int t3 = 0; t3 < 3; ++t3)
+            tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + q * 1024, t3 * nH * 32 + h * 32, sx, sy, wb);
+          if (second_valid) {
+#pragma unroll
+            for (int t3 = 0; t3 < 3; ++t3)
+              tma_store_4d(&p.tmDQKV, pds + t3 * 8192 + (4 + q) * 1024, t3 * nH * 32 + h * 32, sx1, sy1, sb1);
+          }
           tma_store_commit();
         }
         __syncwarp();
@@ -449,7 +463,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
       // its (8-|dy|)(8-|dx|) contributions with plain loads: one global atomic per entry and pass.  (Shared-memory
       // atomics per (i, j) cost ~21 000 cycles per pass: fp32 atomicAdd on shared memory is a CAS loop.)
       {
-        if (lane < 6) tma_store_wait_read<0>();
+        if (elect_one()) tma_store_wait_read<0>();
         named_bar_sync(2 + g, 128);
         float* M = reinterpret_cast<float*>(pds);  // [64][65]
 #pragma unroll
@@ -495,7 +509,7 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
         named_bar_sync(2 + g, 128);
       }
     }
-    if (lane < 6) tma_store_wait_all<0>();
+    if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
   }
 

@@ -145,7 +145,8 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // whole warp runs the loops; the elected thread issues (elect_one, common.cuh)
+    {
       int stage = 0;
       uint32_t phase = 0;
       int tsn = 0;
@@ -185,12 +186,16 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
           uint8_t* st = qkv_s + stage * AF_STAGE;
           mbar_wait(&qk_empty[stage], phase ^ 1);
           AF_TS(0, tsn);
-          mbar_arrive_expect_tx(&qk_full[stage], 32768);
-          load_tile(st, &qk_full[stage], hp * 64);
-          load_tile(st + 16384, &qk_full[stage], nH * 32 + hp * 64);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&qk_full[stage], 32768);
+            load_tile(st, &qk_full[stage], hp * 64);
+            load_tile(st + 16384, &qk_full[stage], nH * 32 + hp * 64);
+          }
           mbar_wait(&v_empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&v_full[stage], 16384);
-          load_tile(st + 32768, &v_full[stage], 2 * nH * 32 + hp * 64);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&v_full[stage], 16384);
+            load_tile(st + 32768, &v_full[stage], 2 * nH * 32 + hp * 64);
+          }
           AF_TS(0, tsn);
           if (++stage == 2) {
             stage = 0;
@@ -204,7 +209,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     // ================================ MMA issuer ================================
     // Software-pipelined by one head-pair step: S(n+1) = Q K^T is issued before waiting for the probabilities of step
     // n, so the softmax warps always find their next score tile ready while O(n) = P V is still being accumulated.
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc_s = make_idesc_bf16(64, 64, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(64, 32, 0, 1);
       uint32_t s_use[2] = {0, 0}, p_use[2] = {0, 0};  // per S / P buffer use counters
@@ -221,19 +226,21 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         for (int b = 0; b < 2; ++b) {
           mbar_wait(&s_empty[b], (s_use[b] & 1) ^ 1);
           tcgen05_fence_after();
+          if (elect_one()) {
 #pragma unroll
-          for (int w = 0; w < 2; ++w) {
+            for (int w = 0; w < 2; ++w) {
 #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-              umma_f16_ss(tmem_S + b * 64 + ((uint32_t)(w * 16) << 16),
-                          make_desc_kmajor_sw128(q_addr + w * 8192 + b * 64 + k * 32),
-                          make_desc_kmajor_sw128(k_addr + w * 8192 + b * 64 + k * 32), idesc_s, k);
+              for (int k = 0; k < 2; ++k) {
+                umma_f16_ss(tmem_S + b * 64 + ((uint32_t)(w * 16) << 16),
+                            make_desc_kmajor_sw128(q_addr + w * 8192 + b * 64 + k * 32),
+                            make_desc_kmajor_sw128(k_addr + w * 8192 + b * 64 + k * 32), idesc_s, k);
+              }
             }
+            umma_commit(&s_full[b]);
+            if (b == 1) umma_commit(&qk_empty[s_stage]);  // Q and K of this stage may be overwritten once S is done
           }
-          umma_commit(&s_full[b]);
           s_use[b]++;
         }
-        umma_commit(&qk_empty[s_stage]);  // Q and K of this stage may be overwritten as soon as S is done
         AF_TS(1, tsn);
         if (++s_stage == 2) {
           s_stage = 0;
@@ -250,7 +257,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
           // issue the next step's S now if its Q/K have landed, otherwise after this step's P V
           const bool more = !(last_pair && hp == hpairs - 1);
           bool s_done = !more;
-          if (more && mbar_try_wait(&qk_full[s_stage], s_phase)) {
+          if (more && __any_sync(0xffffffffu, mbar_try_wait(&qk_full[s_stage], s_phase))) {
             issue_S();
             s_done = true;
           }
@@ -268,20 +275,24 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
               tcgen05_fence_after();
             }
             const uint32_t pa = smem_u32(p_s + b * AF_P_BYTES);
+            if (elect_one()) {
 #pragma unroll
-            for (int w = 0; w < 2; ++w) {
+              for (int w = 0; w < 2; ++w) {
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk) {
-                umma_f16_ss(tmem_O + h * 32 + ((uint32_t)(w * 16) << 16),
-                            make_desc_kmajor_sw128(pa + w * 8192 + kk * 32),
-                            make_desc_mnmajor_sw128(v_addr + w * 8192 + kk * 2048 + b * 64, 64), idesc_pv, kk);
+                for (int kk = 0; kk < 4; ++kk) {
+                  umma_f16_ss(tmem_O + h * 32 + ((uint32_t)(w * 16) << 16),
+                              make_desc_kmajor_sw128(pa + w * 8192 + kk * 32),
+                              make_desc_mnmajor_sw128(v_addr + w * 8192 + kk * 2048 + b * 64, 64), idesc_pv, kk);
+                }
+              }
+              umma_commit(&p_empty[b]);
+              if (b == 1) {
+                umma_commit(&v_empty[stage]);
+                if (hp == hpairs - 1) umma_commit(o_full);  // before a possibly blocking wait for the next pair's Q/K
               }
             }
-            umma_commit(&p_empty[b]);
             p_use[b]++;
           }
-          umma_commit(&v_empty[stage]);
-          if (hp == hpairs - 1) umma_commit(o_full);  // before a possibly blocking wait for the next pair's Q/K
           AF_TS(1, tsn);
           if (!s_done) issue_S();
           if (++stage == 2) {
@@ -409,7 +420,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       mbar_wait(o_full, pair_it & 1);
       if (tsw) AF_TS(2, tsn);
       tcgen05_fence_after();
-      if (lane == 0) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
+      if (elect_one()) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
       named_bar_sync(2, 256);
       for (int hh = 0; hh < nH / 2; ++hh) {
         if (AF_DBG(p) & 4) break;
@@ -438,7 +449,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       __syncwarp();
       if (lane == 0) mbar_arrive(o_empty);
       named_bar_sync(2, 256);
-      if (lane == 0) {
+      if (elect_one()) {
         // the pair's (window, half, head-pair) output boxes are spread over the eight epilogue warps
         const int ew = warp - 2;
         const int nops = (second_valid ? 2 : 1) * 2 * hpairs;
@@ -462,7 +473,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       }
       if (tsw) AF_TS(2, tsn);
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
   }
 

@@ -20,7 +20,13 @@ typedef __nv_bfloat16 bf16;
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
+// One elected thread of a CONVERGED warp.  Single-thread issue of TMA / tcgen05 instructions must be guarded by this,
+// not by `lane == 0`: their operands live in uniform registers, and only under elect.sync does the compiler know that
+// one thread is active -- otherwise every such instruction is wrapped in an ELECT / R2UR / BRA.U.ANY waterfall loop
+// (measured: ~95 cycles per tcgen05.mma, 130-300 per TMA operation).  The leader is the same thread on every call
+// (same member mask), which the per-thread bulk-group and tcgen05.commit bookkeeping rely on.
 __device__ __forceinline__ bool elect_one() {
+  __syncwarp();
   uint32_t pred = 0;
   asm volatile(
       "{\n\t.reg .pred P;\n\t"

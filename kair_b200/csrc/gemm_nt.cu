@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
   const int nkb = kb1 - kb0;  // may be <= 0 for trailing splits
 
   if (warp == 0) {
-    if (lane == 0) {
+    {   // whole warp; the elected thread issues (elect_one, common.cuh)
       int stage = 0;
       uint32_t phase = 0;
       const int dy = tap / 3, dx = tap - dy * 3;
@@ -116,6 +116,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         const long long tw0 = NT_CLOCK();
         mbar_wait(&empty_bar[stage], phase ^ 1);
         t_wait += NT_CLOCK() - tw0;
+        if (elect_one()) {
         mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
         uint8_t* a_s = a_base + stage * NT_A_STAGE;
         uint8_t* b_s = b_base + stage * B_STAGE;
@@ -139,12 +140,13 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           for (int i = 0; i < BN / 64; ++i)
             tma_load_2d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, kb * NT_BKT);
         }
+        }
         if (++stage == p.stages) {
           stage = 0;
           phase ^= 1;
         }
       }
-      if (NT_TS(p) && blockIdx.x == 0) {
+      if (NT_TS(p) && blockIdx.x == 0 && lane == 0) {
         p.ts[0] = t_wait;
         p.ts[1] = NT_CLOCK() - t_begin;
         p.ts[2] = nkb;
@@ -152,7 +154,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && nkb > 0) {
+    if (nkb > 0) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
@@ -164,21 +166,23 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(a_base + stage * NT_A_STAGE);
         const uint32_t b_addr = smem_u32(b_base + stage * B_STAGE);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < NT_BKT / 16; ++k) {
+          for (int k = 0; k < NT_BKT / 16; ++k) {
 #pragma unroll
-          for (int acc = 0; acc < NACC; ++acc)
-            umma_f16_ss(tmem_base + acc * BN, make_desc_mnmajor_sw128(a_addr + acc * NT_A_ATOM2 + k * 2048, NT_BKT),
-                        make_desc_mnmajor_sw128(b_addr + k * 2048, NT_BKT), idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int acc = 0; acc < NACC; ++acc)
+              umma_f16_ss(tmem_base + acc * BN, make_desc_mnmajor_sw128(a_addr + acc * NT_A_ATOM2 + k * 2048, NT_BKT),
+                          make_desc_mnmajor_sw128(b_addr + k * 2048, NT_BKT), idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == nkb - 1) umma_commit(tfull_bar);
         }
-        umma_commit(&empty_bar[stage]);
         if (++stage == p.stages) {
           stage = 0;
           phase ^= 1;
         }
       }
-      umma_commit(tfull_bar);
-      if (NT_TS(p) && blockIdx.x == 0) {
+      if (NT_TS(p) && blockIdx.x == 0 && lane == 0) {
         p.ts[3] = t_wait;
         p.ts[4] = NT_CLOCK() - t_begin;
       }
@@ -204,7 +208,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       uint32_t r[32];
       tmem_ld32(tacc + c * 32, r);
       tmem_ld_wait();
-      if (lane == 0) tma_store_wait_read<1>();
+      if (elect_one()) tma_store_wait_read<1>();
       __syncwarp();
       uint8_t* buf = stg + sbuf * 4096;
       uint32_t base = smem_u32(buf) + lane * 128;
@@ -218,13 +222,13 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
+      if (elect_one()) {
         tma_reduce_add_2d(&p.tmD, buf, col_base + c * 32, tile1 * BM + acc * 128 + q * 32);
         tma_store_commit();
       }
       sbuf ^= 1;
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
     if (NT_TS(p) && blockIdx.x == 0 && ew == 0 && lane == 0) {
       p.ts[5] = te1 - te0;

@@ -223,8 +223,10 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
-      if (kBRes) {
+    // the whole warp runs the loops, one elected thread issues (see elect_one in common.cuh: `lane == 0` costs a
+    // waterfall loop per TMA / MMA instruction)
+    {
+      if (kBRes && elect_one()) {
         mbar_arrive_expect_tx(bres_bar, (uint32_t)(k_total * B_STAGE));
         for (int kb = 0; kb < k_total; ++kb)
           tma_load_2d(b_base + kb * B_STAGE, &p.tmB, bres_bar, kb * TN_BK, n_tile * BN);
@@ -246,15 +248,19 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           for (int kb = 0; kb < p.kc * 3; ++kb) {
             const int kcc = kb / 3, dx = kb - kcc * 3;
             mbar_wait(&empty_bar[s0 + stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)p.a_stage);
-            tma_load_4d(a_base + (s0 + stage) * p.a_stage, &p.tmA, &full_bar[s0 + stage], kcc * TN_BK,
-                        t.w0 + (dx - 1) * p.dil, t.h0 - p.dil, t.b);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)p.a_stage);
+              tma_load_4d(a_base + (s0 + stage) * p.a_stage, &p.tmA, &full_bar[s0 + stage], kcc * TN_BK,
+                          t.w0 + (dx - 1) * p.dil, t.h0 - p.dil, t.b);
+            }
             if (!kBRes) {
               for (int dy = 0; dy < 3; ++dy) {
                 mbar_wait(&emptyb_bar[sb0 + stage_b], phase_b ^ 1);
-                mbar_arrive_expect_tx(&fullb_bar[sb0 + stage_b], (uint32_t)B_STAGE);
-                tma_load_2d(b_base + (sb0 + stage_b) * B_STAGE, &p.tmB, &fullb_bar[sb0 + stage_b],
-                            ((dy * 3 + dx) * p.kc + kcc) * TN_BK, n_tile * BN);
+                if (elect_one()) {
+                  mbar_arrive_expect_tx(&fullb_bar[sb0 + stage_b], (uint32_t)B_STAGE);
+                  tma_load_2d(b_base + (sb0 + stage_b) * B_STAGE, &p.tmB, &fullb_bar[sb0 + stage_b],
+                              ((dy * 3 + dx) * p.kc + kcc) * TN_BK, n_tile * BN);
+                }
                 if (++stage_b == shb) {
                   stage_b = 0;
                   phase_b ^= 1;
@@ -270,16 +276,19 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           for (int kb = 0; kb < k_total; ++kb) {
             mbar_wait(&empty_bar[s0 + stage], phase ^ 1);
             if (TN_DBG(p) & 8) {  // ablation: no A traffic
-              mbar_arrive(&full_bar[s0 + stage]);
+              if (elect_one()) mbar_arrive(&full_bar[s0 + stage]);
               if (++stage == sh) {
                 stage = 0;
                 phase ^= 1;
               }
               continue;
             }
-            mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
-            tma_load_2d(a_base + (s0 + stage) * TN_A_STAGE, &p.tmA, &full_bar[s0 + stage], kb * TN_BK, t.w0);
-            if (!kBRes) tma_load_2d(b_base + (s0 + stage) * B_STAGE, &p.tmB, &full_bar[s0 + stage], kb * TN_BK, n_tile * BN);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&full_bar[s0 + stage], (uint32_t)(TN_A_STAGE + (kBRes ? 0 : B_STAGE)));
+              tma_load_2d(a_base + (s0 + stage) * TN_A_STAGE, &p.tmA, &full_bar[s0 + stage], kb * TN_BK, t.w0);
+              if (!kBRes)
+                tma_load_2d(b_base + (s0 + stage) * B_STAGE, &p.tmB, &full_bar[s0 + stage], kb * TN_BK, n_tile * BN);
+            }
             if (++stage == sh) {
               stage = 0;
               phase ^= 1;
@@ -294,7 +303,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
   } else if (warp == 1 || warp == 10) {
     // ================================ MMA issuers ================================
     const int issuer = warp == 1 ? 0 : 1;
-    if (lane == 0 && issuer < p.issuers) {
+    if (issuer < p.issuers) {   // whole warp; the elected thread issues
       constexpr uint32_t idesc = make_idesc_bf16(TN_BM, BN, 0, 0);
       if (kBRes) {
         mbar_wait(bres_bar, 0);
@@ -348,21 +357,23 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
                 tcgen05_fence_after();
                 b_addr = smem_u32(b_base + (sb0 + stage_b) * B_STAGE);
               }
+              if (elect_one()) {
 #pragma unroll
-              for (int k = 0; k < TN_BK / 16; ++k) {
-                if (TN_DBG(p) & 2) continue;
-                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_dy + k * 32),
-                            make_desc_kmajor_sw128(b_addr + k * 32), idesc, (kb | dy | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < TN_BK / 16; ++k) {
+                  if (TN_DBG(p) & 2) continue;
+                  umma_f16_ss(tacc, make_desc_kmajor_sw128(a_dy + k * 32),
+                              make_desc_kmajor_sw128(b_addr + k * 32), idesc, (kb | dy | k) != 0 ? 1u : 0u);
+                }
+                if (!kBRes) umma_commit(&emptyb_bar[sb0 + stage_b]);
+                if (dy == 2) umma_commit(&empty_bar[s0 + stage]);
               }
               if (!kBRes) {
-                umma_commit(&emptyb_bar[sb0 + stage_b]);
                 if (++stage_b == shb) {
                   stage_b = 0;
                   phase_b ^= 1;
                 }
               }
             }
-            umma_commit(&empty_bar[s0 + stage]);
             if (++stage == sh) {
               stage = 0;
               phase ^= 1;
@@ -374,20 +385,23 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             tcgen05_fence_after();
             const uint32_t a_addr = smem_u32(a_base + (s0 + stage) * TN_A_STAGE);
             const uint32_t b_addr = smem_u32(b_base + (kBRes ? kb : s0 + stage) * B_STAGE);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < TN_BK / 16; ++k) {
-              if (TN_DBG(p) & 2) continue;
-              umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
-                          (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < TN_BK / 16; ++k) {
+                if (TN_DBG(p) & 2) continue;
+                umma_f16_ss(tacc, make_desc_kmajor_sw128(a_addr + k * 32), make_desc_kmajor_sw128(b_addr + k * 32), idesc,
+                            (kb | k) != 0 ? 1u : 0u);
+              }
+              umma_commit(&empty_bar[s0 + stage]);
+              if (kb == k_total - 1) umma_commit(&tfull_bar[as]);
             }
-            umma_commit(&empty_bar[s0 + stage]);
             if (++stage == sh) {
               stage = 0;
               phase ^= 1;
             }
           }
         }
-        umma_commit(&tfull_bar[as]);
+        if (kConv && elect_one()) umma_commit(&tfull_bar[as]);
         if (shared2) skip_tile();
       }
     }
@@ -477,7 +491,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     // Begin a slot: make sure the buffer that is about to be (re)filled is free (the TMA store that last used it has
     // been read out), prefetch the slot ringDist ahead into it, then wait for this slot's operands.
     auto slot_begin = [&](bool have_next, bool nr, bool na, const TileCoord& nt, int ncol, bool wait_mine) -> uint8_t* {
-      if (lane == 0) {
+      if (elect_one()) {
         if (have_next && (nr || na)) {
           wait_stores(ringD - ringDist - 1);
           issue_load(ring_at(ringDist), nr, na, nt, ncol);
@@ -493,7 +507,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       return stg + ridx * ringS;
     };
     auto slot_end = [&](bool stored) {
-      if (stored && lane == 0) tma_store_commit();
+      if (stored && elect_one()) tma_store_commit();
       ridx = ring_at(1);
     };
     // this thread's row of a landed fp32 / bf16 chunk (same swizzles as stage_f32 / stage_bf16)
@@ -531,7 +545,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
 
     int it = 0;
     int m_tile = m_first;
-    if (has_ld && lane == 0 && m_tile < p.m_tiles) {
+    if (has_ld && m_tile < p.m_tiles && elect_one()) {
       const TileCoord t0 = tile_coord<kConv>(p, m_tile);
       if (EPI == KAIR_EPI_DGELU) {
         for (int c = 0; c < ringDist; ++c) issue_load(c, false, true, t0, col_half + c * 32);  // needs ringDist <= NCH
@@ -602,7 +616,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {
             if (!kLean && p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
             if (kLean || p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + boff, t, q, col);
           }
@@ -627,7 +641,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           stage_bf16(buf + 2048, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {
             if (p.has_outB2) tma_store_chunk<kConv>(p, &p.tmOutB2, buf, t, q, col);
             tma_store_chunk<kConv>(p, &p.tmOutB, buf + 2048, t, q, col);
           }
@@ -669,7 +683,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             stage_f32(buf, lane, v);
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
+            if (elect_one()) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
           }
           slot_end(p.has_outF);
         }
@@ -724,12 +738,12 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
             }
           }
           uint8_t* bb = stg + (c & 1) * 6144 + 4096;
-          if (lane == 0) tma_store_wait_read<1>();
+          if (elect_one()) tma_store_wait_read<1>();
           __syncwarp();
           stage_bf16(bb, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {
             tma_store_chunk<kConv>(p, &p.tmOutB, bb, t, q, col);
             tma_store_commit();
           }
@@ -754,7 +768,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           stage_bf16(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) tma_store_chunk<kConv>(p, &p.tmOutB, buf, t, q, col);
+          if (elect_one()) tma_store_chunk<kConv>(p, &p.tmOutB, buf, t, q, col);
           slot_end(true);
         }
       } else if (EPI == KAIR_EPI_LNBWD) {
@@ -823,7 +837,7 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {
             if (p.has_outF) tma_store_chunk<kConv>(p, &p.tmOutF, buf, t, q, col);
             if (p.has_outB) tma_store_chunk<kConv>(p, &p.tmOutB, buf + 4096, t, q, col);
           }
@@ -833,9 +847,9 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
       // release the accumulator stage back to the MMA warp
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);  // plain SYNCS, no uniform operands
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
   }
 

@@ -172,7 +172,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // whole warp runs the loops; the elected thread issues (elect_one, common.cuh)
+    {
       int stage = 0;
       uint32_t phase = 0;
       auto next_stage = [&]() {
@@ -183,24 +184,31 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
       };
       auto load_w1 = [&](int c, int ks) {
         mbar_wait(&w_empty[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&w_full[stage], (uint32_t)(MF_HC * 128));
-        tma_load_2d(w_base + stage * MF_STAGE, &p.tmW1, &w_full[stage], ks * 64, c * MF_HC);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&w_full[stage], (uint32_t)(MF_HC * 128));
+          tma_load_2d(w_base + stage * MF_STAGE, &p.tmW1, &w_full[stage], ks * 64, c * MF_HC);
+        }
         next_stage();
       };
       auto load_w2 = [&](int c) {
         for (int hs = 0; hs < 2; ++hs)
           for (int nh = 0; nh < 2; ++nh) {
             mbar_wait(&w_empty[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&w_full[stage], (uint32_t)(NH * 128));
-            tma_load_2d(w_base + stage * MF_STAGE, &p.tmW2, &w_full[stage], (c * 2 + hs) * 64, nh * NH);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&w_full[stage], (uint32_t)(NH * 128));
+              tma_load_2d(w_base + stage * MF_STAGE, &p.tmW2, &w_full[stage], (c * 2 + hs) * 64, nh * NH);
+            }
             next_stage();
           }
       };
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < p.m_tiles; tile += gridDim.x, ++it) {
         mbar_wait(a_empty, (it & 1) ^ 1);
-        mbar_arrive_expect_tx(a_full, (uint32_t)A_BYTES);
-        for (int ks = 0; ks < KS1; ++ks) tma_load_2d(a_base + ks * (MF_BM * 128), &p.tmA, a_full, ks * 64, tile * MF_BM);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(a_full, (uint32_t)A_BYTES);
+          for (int ks = 0; ks < KS1; ++ks)
+            tma_load_2d(a_base + ks * (MF_BM * 128), &p.tmA, a_full, ks * 64, tile * MF_BM);
+        }
         for (int c = 0; c < NC; ++c) {
           for (int ks = 0; ks < KS1; ++ks) load_w1(c, ks);
           if (c >= 1) load_w2(c - 1);
@@ -211,7 +219,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
     __syncwarp();
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc1 = make_idesc_bf16(MF_BM, MF_HC, 0, 0);
       constexpr uint32_t idesc2 = make_idesc_bf16(MF_BM, NH, 0, 0);
       int stage = 0;
@@ -229,7 +237,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         auto gemm2 = [&](int cc) {
           mbar_wait(g_full, gq & 1);
           tcgen05_fence_after();
-          if (kTrain) {   // the hidden activations of a training plan leave from the operand tile itself
+          if (kTrain && elect_one()) {   // the hidden activations of a training plan leave from the operand tile itself
             tma_store_2d(&p.tmG, g_base, (cc * 2) * 64, tile * MF_BM);
             tma_store_2d(&p.tmG, g_base + MF_BM * 128, (cc * 2 + 1) * 64, tile * MF_BM);
             tma_store_commit();
@@ -244,15 +252,19 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
               tcgen05_fence_after();
               const uint32_t a_addr = smem_u32(g_base + hs * (MF_BM * 128));
               const uint32_t b_addr = smem_u32(w_base + stage * MF_STAGE);
+              if (elect_one()) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_f16_ss(tmem_acc2 + nh * NH, make_desc_kmajor_sw128(a_addr + k * 32),
-                            make_desc_kmajor_sw128(b_addr + k * 32), idesc2, (cc | hs | k) != 0 ? 1u : 0u);
-              umma_commit(&w_empty[stage]);
+                for (int k = 0; k < 4; ++k)
+                  umma_f16_ss(tmem_acc2 + nh * NH, make_desc_kmajor_sw128(a_addr + k * 32),
+                              make_desc_kmajor_sw128(b_addr + k * 32), idesc2, (cc | hs | k) != 0 ? 1u : 0u);
+                umma_commit(&w_empty[stage]);
+              }
               next_stage();
             }
-          if (kTrain) tma_store_wait_read<0>();   // the G tile is re-written once both its readers are done
-          umma_commit(g_empty);
+          if (elect_one()) {
+            if (kTrain) tma_store_wait_read<0>();   // the G tile is re-written once both its readers are done
+            umma_commit(g_empty);
+          }
           ++gq;
         };
         mbar_wait(a_full, it & 1);
@@ -266,21 +278,25 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
             tcgen05_fence_after();
             const uint32_t a_addr = smem_u32(a_base + ks * (MF_BM * 128));
             const uint32_t b_addr = smem_u32(w_base + stage * MF_STAGE);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_f16_ss(tmem_acc1 + b1 * MF_HC, make_desc_kmajor_sw128(a_addr + k * 32),
-                          make_desc_kmajor_sw128(b_addr + k * 32), idesc1, (ks | k) != 0 ? 1u : 0u);
-            umma_commit(&w_empty[stage]);
+              for (int k = 0; k < 4; ++k)
+                umma_f16_ss(tmem_acc1 + b1 * MF_HC, make_desc_kmajor_sw128(a_addr + k * 32),
+                            make_desc_kmajor_sw128(b_addr + k * 32), idesc1, (ks | k) != 0 ? 1u : 0u);
+              umma_commit(&w_empty[stage]);
+              if (ks == KS1 - 1) {
+                umma_commit(&acc1_full[b1]);
+                if (c == NC - 1) umma_commit(a_empty);   // the X tile may be replaced once the last first-GEMM has read it
+              }
+            }
             next_stage();
           }
-          umma_commit(&acc1_full[b1]);
-          if (c == NC - 1) umma_commit(a_empty);   // the X tile may be replaced once the last first-GEMM has read it
           if (c >= 1) gemm2(c - 1);
         }
         gemm2(NC - 1);
-        umma_commit(acc2_full);
+        if (elect_one()) umma_commit(acc2_full);
       }
-      if (kTrain) tma_store_wait_all<0>();
+      if (kTrain && elect_one()) tma_store_wait_all<0>();
     }
     __syncwarp();
   } else {
@@ -315,7 +331,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
     // begin a slot of the 2-buffer ring: free the other buffer (its TMA store must have been read out), prefetch the
     // next slot's residual chunk into it, then wait for this slot's chunk
     auto slot_begin = [&](bool have_next, int ntile, int ncol) -> uint8_t* {
-      if (lane == 0) {
+      if (elect_one()) {
         if (have_next && use_r) {
           tma_store_wait_read<0>();
           issue_load(ridx ^ 1, ntile, ncol);
@@ -331,7 +347,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
       return stg + ridx * 4096;
     };
     auto slot_end = [&](bool stored) {
-      if (stored && lane == 0) tma_store_commit();
+      if (stored && elect_one()) tma_store_commit();
       ridx ^= 1;
     };
     auto add_row_f32 = [&](float (&v)[32], const uint8_t* buf) {
@@ -352,7 +368,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
     // NEXT tile cannot be prefetched across the tile boundary there; it is requested when the output phase begins
     const bool xprefetch = !kTrain;
     int tile = blockIdx.x;
-    if (use_r && xprefetch && lane == 0 && tile < p.m_tiles) issue_load(0, tile, col_half);
+    if (use_r && xprefetch && tile < p.m_tiles && elect_one()) issue_load(0, tile, col_half);
     __syncwarp();
     uint32_t it = 0, gc = 0;
     for (; tile < p.m_tiles; tile += gridDim.x, ++it) {
@@ -390,12 +406,12 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           }
           if (kTrain) {   // pre-activation of a training plan: 2 KiB sub-buffers of this warp's staging, round robin
             uint8_t* ub = stg + ((gc * 2 + g2) & 3) * 2048;
-            if (lane == 0) tma_store_wait_read<3>();
+            if (elect_one()) tma_store_wait_read<3>();
             __syncwarp();
             mf_stage_bf16(ub, lane, v);
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
+            if (elect_one()) {
               tma_store_2d(&p.tmU, ub, hcol, row0);
               tma_store_commit();
             }
@@ -433,7 +449,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         if (lane == 0) mbar_arrive(g_full);
       }
       if (kTrain) {   // the staging buffers are about to hold residual chunks again
-        if (lane == 0) {
+        if (elect_one()) {
           tma_store_wait_read<0>();
           if (use_r) issue_load(ridx, tile, col_half);
         }
@@ -485,7 +501,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           mf_stage_f32(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) tma_store_2d(&p.tmOutF, buf, col, row0);
+          if (elect_one()) tma_store_2d(&p.tmOutF, buf, col, row0);
           stored = true;
         } else if (!kLN && p.has_outB) {
           // no LayerNorm (the block that closes an RSTB): v itself goes out as the bf16 operand of the next convolution
@@ -498,7 +514,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           mf_stage_bf16(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) tma_store_2d(&p.tmOutB, buf, col, row0);
+          if (elect_one()) tma_store_2d(&p.tmOutB, buf, col, row0);
           stored = true;
         }
         slot_end(stored);
@@ -533,7 +549,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         if (p.has_outB) {
           // x-hat -> bf16 through the two 2 KiB halves of the ring buffer that is NOT receiving the next tile's residual
           uint8_t* free_buf = stg + (ridx ^ 1) * 4096;
-          if (lane == 0) tma_store_wait_read<0>();
+          if (elect_one()) tma_store_wait_read<0>();
           __syncwarp();
 #pragma unroll 1
           for (int c = 0; c < NCH; ++c) {
@@ -557,12 +573,12 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
               }
             }
             uint8_t* bb = free_buf + (c & 1) * 2048;
-            if (lane == 0) tma_store_wait_read<1>();
+            if (elect_one()) tma_store_wait_read<1>();
             __syncwarp();
             mf_stage_bf16(bb, lane, v);
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
+            if (elect_one()) {
               tma_store_2d(&p.tmOutB, bb, col, row0);
               tma_store_commit();
             }
@@ -570,14 +586,14 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         }
       }
       if (kTrain) {   // the next tile stages u through these buffers with a relaxed wait: drain this tile's stores first
-        if (lane == 0) tma_store_wait_read<0>();
+        if (elect_one()) tma_store_wait_read<0>();
         __syncwarp();
       }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc2_empty);
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
   }
 
