@@ -98,16 +98,21 @@ __global__ void __launch_bounds__(AB_THREADS, 1) window_attn_bwd_kernel(const __
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
-  pdl_wait();  // no global access above this point
-  pdl_launch_dependents();
-  for (int i = threadIdx.x; i < 225 * nH; i += AB_THREADS) {
-    int idx = i / nH, h = i - idx * nH;
-    table_s[h * 225 + idx] = p.table[i];
-  }
+  // barriers / TMEM slot visible before the dependency wait; after it the producer and the issuers start at once and
+  // only the gradient warps (the table's sole readers) wait for its global load
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // no global access above this point
+  pdl_launch_dependents();
+  if (warp >= 2 && warp < 10) {
+    for (int i = threadIdx.x - 64; i < 225 * nH; i += 256) {
+      int idx = i / nH, h = i - idx * nH;
+      table_s[h * 225 + idx] = __ldg(p.table + i);
+    }
+    named_bar_sync(6, 256);
+  }
   // per group g: W_g = tmem_base + g*128 (S | dP, later dV | dQ | dK), ACC_g = tmem_base + 256 + g*64
 
   if (warp == 0) {

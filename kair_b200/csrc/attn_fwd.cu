@@ -115,31 +115,34 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
+  // barriers / TMEM slot visible before the dependency wait; after it the producer and the issuer start at once and
+  // only the softmax warps (the table's sole readers) wait for its global load
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // no global access above this point
   pdl_launch_dependents();
-  // bias table -> smem as [h][idx]
-  {
-    // all loads of a thread are issued before the first store; values are pre-multiplied by log2(e) so that the
-    // softmax works in the exp2 domain with a single FFMA per score
-    float tv[6];
+  if (warp >= 2) {
+    // bias table -> smem as [h][idx].  All loads of a thread are issued before the first store; values are
+    // pre-multiplied by log2(e) so that the softmax works in the exp2 domain with a single FFMA per score
+    const int tid = threadIdx.x - 64;
+    float tv[8];
 #pragma unroll
-    for (int u = 0; u < 6; ++u) {
-      const int i = threadIdx.x + u * AF_THREADS;
+    for (int u = 0; u < 8; ++u) {
+      const int i = tid + u * 256;
       tv[u] = i < 225 * nH ? __ldg(p.table + i) : 0.f;
     }
 #pragma unroll
-    for (int u = 0; u < 6; ++u) {
-      const int i = threadIdx.x + u * AF_THREADS;
+    for (int u = 0; u < 8; ++u) {
+      const int i = tid + u * 256;
       if (i < 225 * nH) {
         const int idx = i / nH, h = i - idx * nH;
         table_s[h * 225 + idx] = tv[u] * 1.4426950408889634f;
       }
     }
+    named_bar_sync(3, 256);
   }
-  tcgen05_fence_before();
-  __syncthreads();
-  tcgen05_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S = tmem_base;         // 2 x 64 columns
   const uint32_t tmem_O = tmem_base + 128;   // nH x 32 columns
 

@@ -92,9 +92,10 @@ __global__ void unpack_linear_dw_kernel(const kair_unpack_linear_args a) {
   if (threadIdx.x == 0 && a.db && a.ones_col >= 0) reinterpret_cast<float*>(a.db[l])[src] = dWp[a.ones_col] * rs;
 }
 
-__global__ void unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
-  // block = 32 columns x 8 row groups; dgamma[k] = sum_r rs*W[src][k] * dWp[r][c], dbeta[k] = sum_r rs*W[src][k] * dbp[r]
-  __shared__ float sg[8][33], sb[8][33];
+__global__ void __launch_bounds__(1024) unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
+  // block = 32 columns x 32 row groups; dgamma[k] = sum_r rs*W[src][k] * dWp[r][c], dbeta[k] = sum_r rs*W[src][k] * dbp[r]
+  // (8 row groups made this a 72-deep chain of dependent global loads on a 36-block grid: ~20 us per launch)
+  __shared__ float sg[32][33], sb[32][33];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5, l = blockIdx.y;
   const int c = blockIdx.x * 32 + cx;
   const int k = c < a.K_pad ? a.col_map[c] : -1;
@@ -102,7 +103,7 @@ __global__ void unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
   const float* dWp = a.dWp + (size_t)l * a.N_pad * a.K_pad;
   float dg = 0.f, db = 0.f;
   if (k >= 0) {
-    for (int r = ry; r < a.N_pad; r += 8) {
+    for (int r = ry; r < a.N_pad; r += 32) {
       const int src = a.row_map[r];
       if (src < 0) continue;
       const float rs = a.row_scale ? a.row_scale[r] : 1.0f;
@@ -114,14 +115,18 @@ __global__ void unpack_linear_dln_kernel(const kair_unpack_linear_args a) {
   sg[ry][cx] = dg;
   sb[ry][cx] = db;
   __syncthreads();
-  if (ry == 0 && k >= 0) {
+  // warp ry reduces column ry: lane i holds row group i of that column
+  float g = sg[cx][ry], b = sb[cx][ry];
 #pragma unroll
-    for (int i = 1; i < 8; ++i) {
-      dg += sg[i][cx];
-      db += sb[i][cx];
-    }
-    reinterpret_cast<float*>(a.dgamma[l])[k] = dg;
-    reinterpret_cast<float*>(a.dbeta[l])[k] = db;
+  for (int o = 16; o > 0; o >>= 1) {
+    g += __shfl_xor_sync(0xffffffffu, g, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
+  const int c2 = blockIdx.x * 32 + ry;
+  const int k2 = c2 < a.K_pad ? a.col_map[c2] : -1;
+  if (cx == 0 && k2 >= 0) {
+    reinterpret_cast<float*>(a.dgamma[l])[k2] = g;
+    reinterpret_cast<float*>(a.dbeta[l])[k2] = b;
   }
 }
 
@@ -131,7 +136,7 @@ int unpack_linear_launch(const kair_unpack_linear_args& a, cudaStream_t st) {
   KB_CUDA(cudaGetLastError());
   if (a.dgamma && a.dbeta) {
     KB_CHECK(a.W && a.ones_col >= 0, "kair_unpack_linear_grad: LayerNorm gradients need W and ones_col");
-    unpack_linear_dln_kernel<<<dim3((a.K_pad + 31) / 32, a.L), 256, 0, st>>>(a);
+    unpack_linear_dln_kernel<<<dim3((a.K_pad + 31) / 32, a.L), 1024, 0, st>>>(a);
     KB_CUDA(cudaGetLastError());
   }
   return 0;

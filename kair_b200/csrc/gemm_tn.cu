@@ -206,15 +206,20 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
-  pdl_wait();  // everything above overlaps the previous kernel's tail; no global access before this point
-  pdl_launch_dependents();
-  if (p.bias != nullptr && threadIdx.x >= 64 && threadIdx.x < 64 + BN) {
-    bias_s[threadIdx.x - 64] = __ldg(p.bias + (blockIdx.x % p.n_tiles) * BN + (threadIdx.x - 64));
-  }
+  // barriers and the TMEM slot become visible here, BEFORE the wait on the previous kernel: the producer and the
+  // issuers then start the moment the dependency resolves, and only the epilogue warps (the bias' sole readers) wait
+  // for its global load (it used to sit in front of this barrier and delayed the first TMA load by a DRAM round trip)
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlaps the previous kernel's tail; no global access before this point
+  pdl_launch_dependents();
+  if (threadIdx.x >= 64 && threadIdx.x < 320) {
+    if (p.bias != nullptr && threadIdx.x < 64 + BN)
+      bias_s[threadIdx.x - 64] = __ldg(p.bias + (blockIdx.x % p.n_tiles) * BN + (threadIdx.x - 64));
+    named_bar_sync(4, 256);
+  }
 
   // static persistent schedule: this CTA keeps one n-tile and walks m-tiles with a fixed stride
   const int n_tile = blockIdx.x % p.n_tiles;

@@ -157,16 +157,21 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
-  pdl_wait();  // no global access above this point
-  pdl_launch_dependents();
-  for (int i = threadIdx.x; i < F + N; i += MF_THREADS) {
-    const float* src = i < F ? p.bias1 : p.bias2;
-    bias1_s[i] = src ? __ldg(src + (i < F ? i : i - F)) : 0.f;
-  }
+  // barriers / TMEM slot visible before the dependency wait; after it the producer and the issuer start at once and
+  // only the epilogue warps (the biases' sole readers) wait for their global load
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // no global access above this point
+  pdl_launch_dependents();
+  if (warp >= 2) {
+    for (int i = threadIdx.x - 64; i < F + N; i += 256) {
+      const float* src = i < F ? p.bias1 : p.bias2;
+      bias1_s[i] = src ? __ldg(src + (i < F ? i : i - F)) : 0.f;
+    }
+    named_bar_sync(4, 256);
+  }
   const uint32_t tmem_acc1 = tmem_base;          // 2 x 128 columns
   const uint32_t tmem_acc2 = tmem_base + 256;    // N columns
 
