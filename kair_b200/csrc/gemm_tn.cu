@@ -54,7 +54,8 @@ struct TnParams {
   int ring_split;  // 2 issuers: 1 = each issuer owns one half of the operand rings, 0 = one shared ring (needs
                    // stages > stages per tile so that the parity waits of the issuer that runs ahead stay unambiguous)
   int dbg;  // development ablations (env KB_TN_DBG): 1 = skip tcgen05.ld in LINEAR, 2 = skip the MMAs,
-            // 4 = LINEAR epilogue does the barrier handshake only, 8 = dense producer moves no A tiles
+            // 4 = LINEAR epilogue does the barrier handshake only, 8 = dense producer moves no A tiles,
+            // 16 = DGELU without the gelu' arithmetic, 32 = DGELU without its stores
   float act_slope, ln_eps;
   int has_outB, has_outB2, has_outF;
   // conv geometry
@@ -765,15 +766,21 @@ __global__ void __launch_bounds__(TN_THREADS, 1) gemm_tn_kernel(const __grid_con
           load_acc(tacc + c * 32, v);
           read_row_bf16(u, buf);
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float g0, g1;
-            gelu_erf_grad2(u[i], u[i + 1], g0, g1);
-            mul2(v[i], v[i + 1], v[i], v[i + 1], g0, g1);
+          if (TN_DBG(p) & 16) {   // ablation: no gelu' arithmetic
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) mul2(v[i], v[i + 1], v[i], v[i + 1], u[i], u[i + 1]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float g0, g1;
+              gelu_erf_grad2(u[i], u[i + 1], g0, g1);
+              mul2(v[i], v[i + 1], v[i], v[i + 1], g0, g1);
+            }
           }
           stage_bf16(buf, lane, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (elect_one()) tma_store_chunk<kConv>(p, &p.tmOutB, buf, t, q, col);
+          if (!(TN_DBG(p) & 32) && elect_one()) tma_store_chunk<kConv>(p, &p.tmOutB, buf, t, q, col);   // 32: no store
           slot_end(true);
         }
       } else if (EPI == KAIR_EPI_LNBWD) {
