@@ -731,6 +731,22 @@ typedef struct kair_pixel_loss_args {
 } kair_pixel_loss_args;
 int kair_pixel_loss(const kair_pixel_loss_args* args, void* stream);
 
+/* kair_pixel_loss_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers
+ * that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments, modes and results as kair_pixel_loss, but `scratch` must be NULL: the partial sums live in a
+ * file-scope __device__ array inside the library (8192 fp64 slots + a counter, 64.25 KiB, held by every GPU that loads
+ * the library until exit).  The call itself allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   - limit: n <= KAIR_PIXEL_LOSS_NOALLOC_MAX_N (one slot per 8192 elements); larger n returns an error, use
+ *     kair_pixel_loss with caller-owned scratch instead;
+ *   - the loss is summed in a fixed order (no floating-point atomics): bit-identical from call to call; against
+ *     kair_pixel_loss it differs by the fp64 summation order only (<= 1 ulp of the fp32 result);
+ *   - every call on a device shares the array: calls that OVERLAP on the GPU (two streams, concurrently replayed graphs)
+ *     race on it -- serialise them.  Nothing has to be cleared between calls (the kernel re-arms its counter);
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress): make it before stream
+ *     capture begins. */
+#define KAIR_PIXEL_LOSS_NOALLOC_MAX_N 67108864LL   /* 8192 slots x 8192 elements */
+int kair_pixel_loss_noalloc(const kair_pixel_loss_args* args, void* stream);
+
 typedef struct kair_adam_ema_args {
   void* const* p;            /* [L] -> fp32 parameters (updated in place) */
   const void* const* g;      /* [L] -> fp32 gradients */
