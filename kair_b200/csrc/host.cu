@@ -34,7 +34,7 @@ static EncodeTiledFn get_encode() {
 
 int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
               const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
-              CUtensorMapSwizzle swizzle) {
+              CUtensorMapSwizzle swizzle, int l2_promotion) {
   EncodeTiledFn fn = get_encode();
   KB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
   cuuint64_t d[5];
@@ -48,7 +48,10 @@ int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* ba
   }
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
   CUresult r = fn(out, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swizzle,
+                  l2_promotion == 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                      : (l2_promotion == 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B),
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error(
         "cuTensorMapEncodeTiled failed (%d): rank %d base %p dims [%llu %llu %llu %llu] strides [%llu %llu %llu] box "

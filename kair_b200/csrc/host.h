@@ -31,9 +31,12 @@ const char* get_error();
 
 // Encode a tiled tensor map. dims/box are innermost-first; strides_bytes has rank-1 entries (dims 1..rank-1).
 // elem_strides may be null (all 1). Returns 0 on success.
+// l2_promotion: bytes the L2 fetches from DRAM around every accessed 128-byte line.  256 (default) pays when the
+// neighbouring line is consumed soon after; a kernel that comes back for the neighbour much later (window_attn_bwd walks
+// the channel dimension in its OUTER loop) must ask for 128, or half of what it pulls from DRAM is thrown away.
 int make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
               const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
-              CUtensorMapSwizzle swizzle);
+              CUtensorMapSwizzle swizzle, int l2_promotion = 256);
 
 // Programmatic dependent launch: the grid may become resident (barrier init, TMEM allocation, descriptor prefetch)
 // while the previous kernel of the stream drains; the kernel executes pdl_wait() before its first global access.
