@@ -36,16 +36,24 @@ def tile_origins(h, w, tile, overlap):
     return [(y, x) for y in hs for x in ws]
 
 
+def _rows(rows, device):
+    """[(y, x, mode)] -> int32 device tensor.  Building it is a pageable host-to-device copy, which makes the host wait
+    for everything queued on the stream: loops build ONE table up front and pass slices of it."""
+    if isinstance(rows, torch.Tensor):
+        return rows
+    return torch.tensor(rows, dtype=torch.int32, device=device)
+
+
 def _gather(o, img3, rows, th, tw):
-    """(n, C, th, tw) patches of the (C, H, W) image for rows = [(y, x, mode)]"""
-    org = torch.tensor(rows, dtype=torch.int32, device=img3.device)
-    out = torch.empty(len(rows), img3.shape[0], th, tw, dtype=torch.float32, device=img3.device)
+    """(n, C, th, tw) patches of the (C, H, W) image for rows = [(y, x, mode)] (list, or int32 device tensor [n, 3])"""
+    org = _rows(rows, img3.device)
+    out = torch.empty(org.shape[0], img3.shape[0], th, tw, dtype=torch.float32, device=img3.device)
     o.build_tiles_gather(img3, org, out).run(o.stream_handle(img3.device))
     return out
 
 
 def _accumulate(o, tiles, rows, E3, W2, weight=1.0):
-    org = torch.tensor(rows, dtype=torch.int32, device=E3.device)
+    org = _rows(rows, E3.device)
     o.build_tiles_accumulate(tiles.float().contiguous(), org, E3, W2, weight=weight).run(o.stream_handle(E3.device))
 
 
@@ -61,11 +69,16 @@ def tiled_partial(model, img, tile, overlap, scale, window_size, tile_batch=4, r
     img3 = img[0].float().contiguous()
     E = torch.zeros(c, h * scale, w * scale, dtype=torch.float32, device=img.device)
     W = torch.zeros(h * scale, w * scale, dtype=torch.float32, device=img.device)
+    if not origins:
+        return E[None], W[None, None], 0
+    # both origin tables go to the device once, before the loop: the host then queues gather -> network -> overlap-add
+    # of every chunk without ever waiting for the GPU (a per-chunk table upload drained the stream 25 times per image)
+    src = _rows([(y, x, 0) for y, x in origins], img.device)
+    dst = _rows([(y * scale, x * scale, 0) for y, x in origins], img.device)
     for i in range(0, len(origins), tile_batch):
-        chunk = origins[i:i + tile_batch]
-        patches = _gather(o, img3, [(y, x, 0) for y, x in chunk], tile, tile)
+        patches = _gather(o, img3, src[i:i + tile_batch], tile, tile)
         out = model(patches)
-        _accumulate(o, out, [(y * scale, x * scale, 0) for y, x in chunk], E, W)
+        _accumulate(o, out, dst[i:i + tile_batch], E, W)
     return E[None], W[None, None], len(origins)
 
 
