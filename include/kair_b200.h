@@ -162,6 +162,30 @@ typedef struct kair_gemm_nt_args {
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * kair_conv_chain -- L consecutive 3x3 convolutions, 64 -> 64 channels, padding 1, + bias, + leaky-ReLU, as ONE
+ * persistent cooperative launch (one CTA per SM, weights of the running layer resident in shared memory, a grid-wide
+ * barrier between layers).  Replaces the body loop of the reference's plain conv stacks at inference:
+ * models/network_dncnn.py:40-71 (`sequential(m_head, *m_body, m_tail)`, body entries 'CR' / 'CBR' with the eval-mode
+ * BatchNorm folded by kair_pack_conv), models/network_dncnn.py:103-148 (FDnCNN).  Results are bit-identical to L
+ * launches of kair_gemm_tn (conv = 1, bn = 64, bias, act) over the same ping-pong buffers.
+ *   layer l reads act(l & 1) and writes act((l + 1) & 1); the input is act0, the result is in act(L & 1).
+ * `sync`: two zero-initialised 32-bit words owned by the caller (barrier arrivals, exit arrivals); the kernel leaves
+ * them at zero.  Launches that share `sync` (or the activation buffers) must not overlap on the GPU.
+ * ------------------------------------------------------------------------------------------------------------ */
+#define KAIR_CONV_CHAIN_MAX_LAYERS 32
+typedef struct kair_conv_chain_args {
+  void* act0;           /* bf16 [batch*H*W][pitch], channels 0..63 used */
+  void* act1;
+  const void* Wp;       /* bf16 [L][64][9*64]: kair_pack_conv layout, k = tap*64 + input channel */
+  const float* bias;    /* [L][64] or NULL */
+  const float* slope;   /* [L] device: out = v > 0 ? v : v * slope  (0 = ReLU, 1 = no activation) */
+  int32_t* sync;        /* 2 words, zero before the first launch */
+  int64_t pitch;        /* elements per pixel row of act0 / act1 (>= 64, multiple of 8) */
+  int32_t L, batch, H, W;
+} kair_conv_chain_args;
+int kair_conv_chain(const kair_conv_chain_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * kair_window_attn_fwd / _bwd: shifted-window multi-head attention core (head_dim padded to 32).  window = 8 runs on
  * tcgen05 / TMEM (shift 0 or 4); window = 2..7 (the 7x7 JPEG-artifact models) on a CUDA-core kernel (any shift < window).
  *   out[t, h*32+d] = sum_j softmax_j(q_i.k_j + table[rel(i,j)][h] + mask(i,j)) v_j

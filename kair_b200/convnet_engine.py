@@ -16,6 +16,7 @@ The strided conv / transposed conv are dense GEMMs over 2x2-regrouped rows (kair
 Reference arithmetic replaced (file:line in /root/reference): models/network_dncnn.py:61-71,
 models/network_unet.py:25-76, models/basicblock.py:61-98, 211-223, 471-477, 495-501 and autograd's backward of them.
 """
+import os
 from collections import OrderedDict
 
 import torch
@@ -23,6 +24,14 @@ import torch.nn as nn
 
 from . import _dirty
 from . import ops as _real_ops
+
+
+# kair_conv_chain (the whole conv body as one persistent launch with grid barriers) serves inference plans of at most this
+# many 8 x 16 pixel tiles (env KAIR_B200_CHAIN_MAX_TILES).  Default 0 = OFF: measured on B200 it does not beat the per-layer
+# launches -- 151 vs 148 us for the 15 body layers of DnCNN at batch 1, 1316 vs 1270 us at batch 16 -- because a
+# 128 x 64 x 16 UMMA costs ~77 cycles whatever feeds it (1.45 us per tile with the fill, the epilogue and the stores
+# ablated away), and PDL + graph replay already hide the launch gaps the chain was meant to remove.
+CHAIN_MAX_TILES = int(os.environ.get("KAIR_B200_CHAIN_MAX_TILES", "0"))
 
 
 def _conv_tile(n):
@@ -323,7 +332,19 @@ class _DnCNNPlan(_PlanBase):
         self.bn_buffers = []
         fwd.append(o.build_conv_in_fwd(self.img, head.conv.weight, head.conv.bias, zc_in, 1.0, O=nc, O_pad=nc, pitch=nc,
                                        out_bf16=A(0), act=a0, act_slope=s0))
-        for i, s in enumerate(body):
+        # opt-in (CHAIN_MAX_TILES): the whole body as ONE persistent launch with a grid barrier between layers
+        # (kair_conv_chain) instead of one launch per layer
+        tiles = B * ((H + 15) // 16) * ((W + 7) // 8)
+        chain = (not train and not bn_live and nc == 64 and 1 <= Lb <= 32 and all(s.dil == 1 for s in body)
+                 and tiles <= CHAIN_MAX_TILES and hasattr(o, "build_conv_chain"))
+        self.chain = chain
+        if chain:
+            self.chain_slope = torch.tensor([1.0 if s.slope is None else float(s.slope) for s in body],
+                                            dtype=torch.float32, device=dev)
+            self.chain_sync = torch.zeros(2, dtype=torch.int32, device=dev)
+            fwd.append(o.build_conv_chain(acts[0], acts[1], Wt["Wp"], Wt["bp"], self.chain_slope, self.chain_sync,
+                                          L=Lb, conv=geo))
+        for i, s in enumerate(body if not chain else ()):
             act, slope = act_of(s)
             if s.bn is not None and bn_live:
                 z = zs[i] if train else zshared

@@ -38,6 +38,7 @@ int pixel_shuffle_launch(const kair_shuffle_args& a, cudaStream_t st);
 int upsample_nearest2_launch(const kair_shuffle_args& a, cudaStream_t st);
 int pixel_shuffle_out_launch(const kair_shuffle_out_args& a, cudaStream_t st);
 int pixel_loss_launch(const kair_pixel_loss_args& a, cudaStream_t st);
+int conv_chain_launch(const kair_conv_chain_args& a, cudaStream_t st);
 int adam_ema_launch(const kair_adam_ema_args& a, cudaStream_t st);
 int pixel_shuffle_out_bwd_launch(const kair_shuffle_out_args& a, cudaStream_t st);
 int pixel_shuffle_bwd_launch(const kair_shuffle_args& a, cudaStream_t st);
@@ -130,6 +131,7 @@ KB_WRAP(kair_pixel_shuffle, kair_shuffle_args, pixel_shuffle_launch)
 KB_WRAP(kair_upsample_nearest2, kair_shuffle_args, upsample_nearest2_launch)
 KB_WRAP(kair_pixel_shuffle_out, kair_shuffle_out_args, pixel_shuffle_out_launch)
 KB_WRAP(kair_pixel_loss, kair_pixel_loss_args, pixel_loss_launch)
+KB_WRAP(kair_conv_chain, kair_conv_chain_args, conv_chain_launch)
 KB_WRAP(kair_adam_ema, kair_adam_ema_args, adam_ema_launch)
 KB_WRAP(kair_pixel_shuffle_out_bwd, kair_shuffle_out_args, pixel_shuffle_out_bwd_launch)
 KB_WRAP(kair_pixel_shuffle_bwd, kair_shuffle_args, pixel_shuffle_bwd_launch)
@@ -191,7 +193,7 @@ const KbOp kb_ops[] = {
     KB_OP(kair_pixel_shuffle_bwd), KB_OP(kair_upsample_nearest2_bwd), KB_OP(kair_split_terms),
     KB_OP(kair_ln_bwd_split), KB_OP(kair_add_inplace_s), KB_OP(kair_memcpy_d2d), KB_OP(kair_mlp_fused),
     KB_OP(kair_spect_patches), KB_OP(kair_spect_normalize), KB_OP(kair_spect_metrics),
-    KB_OP(kair_tiles_gather), KB_OP(kair_tiles_accumulate), KB_OP(kair_axpby), KB_OP(kair_ffd_pack),
+    KB_OP(kair_tiles_gather), KB_OP(kair_tiles_accumulate), KB_OP(kair_axpby), KB_OP(kair_ffd_pack), KB_OP(kair_conv_chain),
 };
 #undef KB_OP
 constexpr int kb_n_ops = (int)(sizeof(kb_ops) / sizeof(kb_ops[0]));

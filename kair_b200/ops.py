@@ -766,6 +766,24 @@ def build_pixel_shuffle_out(x, out, mean, *, r, scale=1.0):
     return Launch("kair_pixel_shuffle_out", a)
 
 
+def build_conv_chain(act0, act1, Wp, bias, slope, sync, *, L, conv):
+    """L 3x3 convolutions 64 -> 64 (+ bias, leaky-ReLU slope[l]) in one persistent launch; layer l reads act(l & 1) and
+    writes act((l + 1) & 1).  Wp bf16 [L, 64, 576], bias f32 [L, 64] or None, slope f32 [L], sync int32 [2] (zero)."""
+    _req(act0, torch.bfloat16, "act0"); _req(act1, torch.bfloat16, "act1"); _req(Wp, torch.bfloat16, "Wp")
+    _req(bias, torch.float32, "bias"); _req(slope, torch.float32, "slope"); _req(sync, torch.int32, "sync")
+    B, H, W = conv
+    if Wp.dim() != 3 or tuple(Wp.shape[1:]) != (64, 576) or Wp.shape[0] < L or not Wp.is_contiguous():
+        raise RuntimeError("kair_b200: conv_chain needs contiguous packed weights [L, 64, 576]")
+    if (bias is not None and (not bias.is_contiguous() or bias.numel() < L * 64)) or slope.numel() < L or sync.numel() < 2:
+        raise RuntimeError("kair_b200: conv_chain needs bias [L, 64], slope [L] and two sync words")
+    if _pitch(act0) != _pitch(act1) or act0.numel() < B * H * W * 64 or act1.numel() < B * H * W * 64:
+        raise RuntimeError("kair_b200: conv_chain needs two [B*H*W, >= 64] activation buffers of one pitch")
+    a = _S["kair_conv_chain_args"]()
+    a.act0, a.act1, a.Wp, a.bias, a.slope, a.sync = _ptr(act0), _ptr(act1), _ptr(Wp), _ptr(bias), _ptr(slope), _ptr(sync)
+    a.pitch, a.L, a.batch, a.H, a.W = _pitch(act0), L, B, H, W
+    return Launch("kair_conv_chain", a, keep=(act0, act1, Wp, bias, slope, sync))
+
+
 def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0, max_pixel=0.0):
     """loss[0] = mean(sqrt((x-y)^2 + eps)) (mode 0, CharbonnierLoss) or mean|x-y| (mode 1) and dx = d(loss)/dx."""
     _req(x, torch.float32, "x"); _req(y, torch.float32, "y"); _req(dx, torch.float32, "dx")

@@ -31,6 +31,10 @@ def describe(launch, real_dims):
         by += 4.0 * a.M * r(a.N) * (1 if a.resid else 0) + 2.0 * a.M * r(a.N) * (1 if a.aux else 0)
         by += 2.0 * a.M * r(a.N) * ((1 if a.outB else 0) + (1 if a.outB2 else 0)) + 4.0 * a.M * r(a.N) * (1 if a.outF else 0)
         return tag, 2.0 * a.M * r(a.N) * kr * taps, by
+    if name == "conv_chain":
+        M = float(a.batch) * a.H * a.W
+        # per layer: the activation is read and written once (bf16, 64 channels); FLOPs of L 3x3 convolutions 64 -> 64
+        return "conv_chain[L%d conv3x3 N64 K576]" % a.L, 2.0 * M * 64 * 576 * a.L, 2.0 * M * 64 * 2 * a.L
     if name == "mlp_fused":
         tag = "mlp_fused[N%d F%d %s%s]" % (a.N, a.F, "resid_ln" if a.ln else "linear", " +u,g" if a.outU else "")
         rn, rf = r(a.N), r(a.F)

@@ -797,6 +797,20 @@ def build_pixel_shuffle_out_bwd(dout, dx, *, r, co, scale=1.0):
     return EmuLaunch("kair_pixel_shuffle_out_bwd", run)
 
 
+def build_conv_chain(act0, act1, Wp, bias, slope, sync, *, L, conv):
+    """kair_conv_chain = L runs of the conv-mode gemm_tn emulation over the ping-pong buffers (the slope is a device
+    value in the real op, so it is read when the launch runs)"""
+    acts = (act0, act1)
+
+    def run():
+        sl = slope.tolist()
+        for l in range(L):
+            build_gemm_tn(acts[l & 1], Wp[l], N=64, K=64, bn=64, conv=conv, bias=None if bias is None else bias[l],
+                          act=ACT_LRELU, act_slope=sl[l], outB=acts[(l + 1) & 1]).run(None)
+
+    return EmuLaunch("kair_conv_chain", run)
+
+
 def build_pixel_loss(x, y, dx, loss, scratch, *, eps=1e-9, mode=0, max_pixel=0.0):
     def run():
         import math

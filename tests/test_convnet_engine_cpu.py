@@ -355,3 +355,24 @@ def test_ffdnet_engine_vs_oracle_and_golden():
     model.eval()
     with torch.no_grad():
         assert (model(x, gc.sigma_of(case)) - y_ref.detach()).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("act_mode", ["R", "BR"])
+def test_dncnn_inference_plan_with_conv_chain(monkeypatch, act_mode):
+    """opt-in kair_conv_chain routing (one persistent launch for the conv body): same result as the per-layer plan, one
+    launch instead of nb - 2, eval-mode BatchNorm folded into the chain's weights"""
+    import kair_b200.convnet_engine as ce
+    model = DnCNN(in_nc=1, out_nc=1, nc=64, nb=6, act_mode=act_mode)
+    _seed_params(model, 9)
+    model.eval()
+    x = torch.rand(2, 1, 24, 16, generator=torch.Generator().manual_seed(2))
+    outs, n_launch = [], []
+    for limit in (0, 4096):
+        monkeypatch.setattr(ce, "CHAIN_MAX_TILES", limit)
+        eng = DnCNNEngine(parse_dncnn(model.model), dict(model.named_parameters()), "cpu", ops=emu_ops)
+        plan = eng.plan(2, 24, 16, False, False)
+        assert plan.chain == (limit > 0)
+        outs.append(plan.run_forward(x).clone())
+        n_launch.append(len(plan.fwd))
+    assert torch.equal(outs[0], outs[1])
+    assert n_launch[0] - n_launch[1] == 4 - 1
