@@ -80,8 +80,8 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
   uint64_t* p_full = s_empty + 2;
   uint64_t* p_empty = p_full + 2;
   uint64_t* o_full = p_empty + 2;
-  uint64_t* o_empty = o_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 1);
+  uint64_t* o_empty = o_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_empty + 2);
   float* table_s = reinterpret_cast<float*>(misc + 256);  // [nH][225]
 
   const int warp = threadIdx.x >> 5;
@@ -107,8 +107,10 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         mbar_init(&p_full[i], 4);
         mbar_init(&p_empty[i], 1);
       }
-      mbar_init(o_full, 1);
-      mbar_init(o_empty, 8);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&o_full[i], 1);
+        mbar_init(&o_empty[i], 8);
+      }
       fence_barrier_init();
     }
     __syncwarp();
@@ -144,7 +146,11 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     named_bar_sync(3, 256);
   }
   const uint32_t tmem_S = tmem_base;         // 2 x 64 columns
-  const uint32_t tmem_O = tmem_base + 128;   // nH x 32 columns
+  const uint32_t tmem_O = tmem_base + 128;   // nH x 32 columns, twice when they fit (nH <= 6)
+  // O is double-buffered by window-pair parity when 128 + 2 * nH * 32 <= 512 TMEM columns: the softmax warps then run
+  // the output epilogue of pair n-1 AFTER the first softmax of pair n, i.e. while the tensor pipe finishes P V of pair
+  // n-1 and computes the next scores -- they used to sit ~3800 cycles per pair in the o_full wait (clock64 timeline)
+  const bool o_dbl = 128 + 2 * nH * 32 <= 512;
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -256,6 +262,9 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
       if (blockIdx.x < p.pairs) issue_S();
       for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
         const bool last_pair = pair + (int)gridDim.x >= p.pairs;
+        const int ob = o_dbl ? (int)(pair_it & 1) : 0;                       // O buffer of this pair
+        const uint32_t oph = o_dbl ? ((pair_it >> 1) & 1) : (pair_it & 1);   // its barrier phase
+        const uint32_t tO = tmem_O + ob * nH * 32;
         for (int hp = 0; hp < hpairs; ++hp) {
           // issue the next step's S now if its Q/K have landed, otherwise after this step's P V
           const bool more = !(last_pair && hp == hpairs - 1);
@@ -274,7 +283,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
             AF_TS(1, tsn);
             tcgen05_fence_after();
             if (h == 0) {
-              mbar_wait(o_empty, (pair_it & 1) ^ 1);
+              mbar_wait(&o_empty[ob], oph ^ 1);
               tcgen05_fence_after();
             }
             const uint32_t pa = smem_u32(p_s + b * AF_P_BYTES);
@@ -283,7 +292,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
               for (int w = 0; w < 2; ++w) {
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
-                  umma_f16_ss(tmem_O + h * 32 + ((uint32_t)(w * 16) << 16),
+                  umma_f16_ss(tO + h * 32 + ((uint32_t)(w * 16) << 16),
                               make_desc_kmajor_sw128(pa + w * 8192 + kk * 32),
                               make_desc_mnmajor_sw128(v_addr + w * 8192 + kk * 2048 + b * 64, 64), idesc_pv, kk);
                 }
@@ -291,7 +300,7 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
               umma_commit(&p_empty[b]);
               if (b == 1) {
                 umma_commit(&v_empty[stage]);
-                if (hp == hpairs - 1) umma_commit(o_full);  // before a possibly blocking wait for the next pair's Q/K
+                if (hp == hpairs - 1) umma_commit(&o_full[ob]);  // before a possibly blocking wait for the next pair's Q/K
               }
             }
             p_use[b]++;
@@ -324,6 +333,72 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
     int tsn = 0;
     const bool tsw = (warp == 2 && lane == 0);
     const float LOG2E = 1.4426950408889634f;
+
+    // ---- epilogue of one window pair: O * 1/rowsum -> bf16 -> staging -> TMA scatter to the windows' pixels
+    auto epilogue = [&](int e_pair, uint32_t e_it, const float (&inv)[AF_MAX_HEADS / 2]) {
+      const int gw0 = e_pair * 2;
+      const bool second_valid = gw0 + 1 < p.total_windows;
+      const int ob = o_dbl ? (int)(e_it & 1) : 0;
+      const uint32_t tO = tmem_O + ob * nH * 32;
+      mbar_wait(&o_full[ob], o_dbl ? ((e_it >> 1) & 1) : (e_it & 1));
+      if (tsw) AF_TS(2, tsn);
+      tcgen05_fence_after();
+      if (elect_one()) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
+      named_bar_sync(2, 256);
+      for (int hh = 0; hh < nH / 2; ++hh) {
+        if (AF_DBG(p) & 4) break;
+        const int h = hh * 2 + g;
+        uint32_t r[32];
+        tmem_ld32(tO + lane_sel + h * 32, r);
+        tmem_ld_wait();
+        const float sc = inv[hh];
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 2)
+          mul2(v[j], v[j + 1], __uint_as_float(r[j]), __uint_as_float(r[j + 1]), sc, sc);
+        const uint32_t base = smem_u32(out_s + (h >> 1) * 16384) + row * 128;
+        const uint32_t sw = row & 7;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t a = base + ((((h & 1) * 4 + c) ^ sw) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(v[8 * c], v[8 * c + 1])),
+                       "r"(pack_bf16x2(v[8 * c + 2], v[8 * c + 3])), "r"(pack_bf16x2(v[8 * c + 4], v[8 * c + 5])),
+                       "r"(pack_bf16x2(v[8 * c + 6], v[8 * c + 7]))
+                       : "memory");
+        }
+      }
+      fence_proxy_async_smem();
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&o_empty[ob]);
+      named_bar_sync(2, 256);
+      if (elect_one()) {
+        // the pair's (window, half, head-pair) output boxes are spread over the eight epilogue warps
+        const int ew = warp - 2;
+        const int nops = (second_valid ? 2 : 1) * 2 * hpairs;
+        for (int op = ew; op < nops; op += 8) {
+          const int a = op % hpairs, hq = op / hpairs;
+          const int ws2 = hq >> 1, qx = hq & 1;
+          int b2, wi2, wj2;
+          window_origin(p, gw0 + ws2, b2, wi2, wj2);
+          const bool hwrap = p.shift > 0 && wi2 == p.nWh - 1;
+          const int h0 = (wi2 * 8 + p.shift) % p.H;
+          const int ww2 = (wj2 * 8 + qx * 4 + p.shift) % p.W;
+          const uint8_t* src = out_s + a * 16384 + (ws2 * 4 + qx * 2) * 2048;
+          if (!hwrap) {
+            tma_store_4d(&p.tmOut2, src, a * 64, ww2, h0, b2);
+          } else {
+            tma_store_4d(&p.tmOut, src, a * 64, ww2, h0, b2);
+            tma_store_4d(&p.tmOut, src + 2048, a * 64, ww2, (h0 + 4) % p.H, b2);
+          }
+        }
+        tma_store_commit();
+      }
+      if (tsw) AF_TS(2, tsn);
+    };
+    float inv_prev[AF_MAX_HEADS / 2];
+    int prev_pair = -1;
+    uint32_t prev_it = 0;
 
     for (int pair = blockIdx.x; pair < p.pairs; pair += gridDim.x, ++pair_it) {
       const int gw0 = pair * 2;
@@ -417,65 +492,22 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[g]);
         if (tsw) AF_TS(2, tsn);
+        if (hh == 0 && prev_pair >= 0) {   // the previous pair's output, under this pair's tensor work
+          epilogue(prev_pair, prev_it, inv_prev);
+          prev_pair = -1;
+        }
       }
 
-      // ---- epilogue: O * 1/rowsum -> bf16 -> staging -> TMA scatter to the windows' pixels
-      mbar_wait(o_full, pair_it & 1);
-      if (tsw) AF_TS(2, tsn);
-      tcgen05_fence_after();
-      if (elect_one()) tma_store_wait_read<0>();  // this warp's share of the previous pair's output stores
-      named_bar_sync(2, 256);
-      for (int hh = 0; hh < nH / 2; ++hh) {
-        if (AF_DBG(p) & 4) break;
-        const int h = hh * 2 + g;
-        uint32_t r[32];
-        tmem_ld32(tmem_O + lane_sel + h * 32, r);
-        tmem_ld_wait();
-        const float sc = inv_sum[hh];
-        float v[32];
+      if (!o_dbl) {
+        epilogue(pair, pair_it, inv_sum);
+      } else {   // deferred: runs after the first softmax of the next pair (or after the loop)
 #pragma unroll
-        for (int j = 0; j < 32; j += 2)
-          mul2(v[j], v[j + 1], __uint_as_float(r[j]), __uint_as_float(r[j + 1]), sc, sc);
-        const uint32_t base = smem_u32(out_s + (h >> 1) * 16384) + row * 128;
-        const uint32_t sw = row & 7;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t a = base + ((((h & 1) * 4 + c) ^ sw) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(v[8 * c], v[8 * c + 1])),
-                       "r"(pack_bf16x2(v[8 * c + 2], v[8 * c + 3])), "r"(pack_bf16x2(v[8 * c + 4], v[8 * c + 5])),
-                       "r"(pack_bf16x2(v[8 * c + 6], v[8 * c + 7]))
-                       : "memory");
-        }
+        for (int u = 0; u < AF_MAX_HEADS / 2; ++u) inv_prev[u] = inv_sum[u];
+        prev_pair = pair;
+        prev_it = pair_it;
       }
-      fence_proxy_async_smem();
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(o_empty);
-      named_bar_sync(2, 256);
-      if (elect_one()) {
-        // the pair's (window, half, head-pair) output boxes are spread over the eight epilogue warps
-        const int ew = warp - 2;
-        const int nops = (second_valid ? 2 : 1) * 2 * hpairs;
-        for (int op = ew; op < nops; op += 8) {
-          const int a = op % hpairs, hq = op / hpairs;
-          const int ws2 = hq >> 1, qx = hq & 1;
-          int b2, wi2, wj2;
-          window_origin(p, gw0 + ws2, b2, wi2, wj2);
-          const bool hwrap = p.shift > 0 && wi2 == p.nWh - 1;
-          const int h0 = (wi2 * 8 + p.shift) % p.H;
-          const int ww2 = (wj2 * 8 + qx * 4 + p.shift) % p.W;
-          const uint8_t* src = out_s + a * 16384 + (ws2 * 4 + qx * 2) * 2048;
-          if (!hwrap) {
-            tma_store_4d(&p.tmOut2, src, a * 64, ww2, h0, b2);
-          } else {
-            tma_store_4d(&p.tmOut, src, a * 64, ww2, h0, b2);
-            tma_store_4d(&p.tmOut, src + 2048, a * 64, ww2, (h0 + 4) % p.H, b2);
-          }
-        }
-        tma_store_commit();
-      }
-      if (tsw) AF_TS(2, tsn);
     }
+    if (prev_pair >= 0) epilogue(prev_pair, prev_it, inv_prev);
     if (elect_one()) tma_store_wait_all<0>();
     __syncwarp();
   }
