@@ -157,6 +157,10 @@ typedef struct kair_gemm_nt_args {
   int32_t conv;
   int32_t batch, H, W;
   int32_t dilation;  /* conv == 1: tap (dy, dx) pairs A[p] with B[p + dilation * (dy-1, dx-1)]; 0 or 1 = dense taps */
+  int32_t swap;      /* conv == 1, n2 == 64 only: the same products, written TRANSPOSED -- D is fp32 [9*n2][d_pitch] with
+                        D[tap*n2 + i][o] (kair_unpack_conv_grad `transposed`).  The tap-shifted input is then the M
+                        operand (two taps fill a 128-row UMMA) and the n1 output channels the N operand: for 64 -> 64
+                        layers every MMA row is useful, where the plain order wastes half of a 128-row accumulator */
 } kair_gemm_nt_args;
 
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);
@@ -284,7 +288,8 @@ typedef struct kair_unpack_conv_args {
   void* const* dW;           /* [L] -> fp32 (O, I, kh, kw) */
   void* const* db;           /* [L] -> fp32 (O) or NULL; taken from column ones_col of the centre tap */
   int32_t L, O, I, O_pad, I_pad, taps, ones_col, center_tap;
-  int32_t dwp_pitch;         /* row pitch of dWp in elements; 0 = taps*I_pad */
+  int32_t dwp_pitch;         /* row pitch of dWp in elements; 0 = taps*I_pad (transposed: 0 = O_pad) */
+  int32_t transposed;        /* dWp is fp32 [L][taps*I_pad][O_pad] (kair_gemm_nt `swap`); db is not available then */
 } kair_unpack_conv_args;
 int kair_unpack_conv_grad(const kair_unpack_conv_args* args, void* stream);
 

@@ -377,7 +377,10 @@ class _DnCNNPlan(_PlanBase):
         self.dout = f32(B, cout, H, W)
         self.grads = _GradStore(eng.P, dev)
         G = lambda p: self.grads.G[eng.name_of(p)]
-        dWp = f32(Lb, nc, 9 * nc)
+        # 64 -> 64 layers: weight gradients with the operand roles swapped (kair_gemm_nt `swap`: every row of the 128-row
+        # UMMA is useful), which leaves the packed gradient transposed, [9*nc, nc]
+        swap = nc == 64
+        dWp = f32(Lb, 9 * nc, nc) if swap else f32(Lb, nc, 9 * nc)
         self.zero_before_bwd = [dWp]
         d = [bf(T, nc), bf(T, nc)]   # ping-pong gradients w.r.t. stage outputs / pre-activations
         # the gradient entering a live BatchNorm stays fp32: its backward subtracts projections of dy, which would
@@ -420,7 +423,7 @@ class _DnCNNPlan(_PlanBase):
                 g = d[cur]
                 if s.conv.bias is not None:
                     bwd.append(o.build_colsum(g, G(s.conv.bias), C=nc))
-            bwd.append(o.build_gemm_nt(g, A(i), dWp[i], n1=nc, n2=nc, bn=bn, conv=geo, dilation=s.dil))
+            bwd.append(o.build_gemm_nt(g, A(i), dWp[i], n1=nc, n2=nc, bn=bn, conv=geo, dilation=s.dil, swap=swap))
             prev = body[i - 1] if i > 0 else head
             if live(prev):
                 bwd.append(o.build_gemm_tn(g, Wt["WpT"][i], N=nc, K=nc, bn=bn, conv=geo, outF=df, dilation=s.dil))
@@ -434,7 +437,8 @@ class _DnCNNPlan(_PlanBase):
         bwd.append(o.build_unpack_conv_grad(dWcf, [G(head.conv.weight)],
                                             [G(head.conv.bias)] if head.conv.bias is not None else None, O=nc, I=cin,
                                             I_pad=7, ones_col=cin, center_tap=4, dwp_pitch=64))
-        bwd.append(o.build_unpack_conv_grad(dWp, [G(s.conv.weight) for s in body], None, O=nc, I=nc, I_pad=nc))
+        bwd.append(o.build_unpack_conv_grad(dWp, [G(s.conv.weight) for s in body], None, O=nc, I=nc, I_pad=nc,
+                                            transposed=swap))
         self.bwd = bwd
         self._dx_spec = dict(dhead=d[cur], W=head.conv.weight, C=nc, pitch=nc, scale=1.0, skip=bool(eng.residual))
         self._finish(eng)
@@ -666,7 +670,9 @@ class _UNetResPlan(_PlanBase):
         self.dout = f32(B, cout, H, W)
         self.grads = _GradStore(eng.P, dev)
         G = lambda p: self.grads.G[eng.name_of(p)] if p is not None else None
-        dWres = [f32(len(Wt["res"][l]["convs"]), nc[l], 9 * nc[l]) for l in range(4)]
+        swp = [nc[l] == 64 for l in range(4)]   # 64-channel levels: swapped-role weight gradients (see _DnCNNPlan)
+        dWres = [f32(len(Wt["res"][l]["convs"]), 9 * nc[l], nc[l]) if swp[l] else f32(len(Wt["res"][l]["convs"]), nc[l], 9 * nc[l])
+                 for l in range(4)]
         dWdown = [f32(1, nc[l + 1], 4 * nc[l]) for l in range(3)]
         dWup = [f32(1, nc[l + 1], 4 * nc[l]) for l in range(3)]
         self.zero_before_bwd = dWres + dWdown + dWup
@@ -684,12 +690,14 @@ class _UNetResPlan(_PlanBase):
             c1, c2 = R["convs"][k], R["convs"][k + 1]
             nf = gf[l][0] if cf is not gf[l][0] else gf[l][1]
             nb2 = gb[l][0] if cb is not gb[l][0] else gb[l][1]
-            bwd.append(o.build_gemm_nt(cb, hb_, dWres[l][k + 1], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l]))
+            bwd.append(o.build_gemm_nt(cb, hb_, dWres[l][k + 1], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l],
+                                       swap=swp[l]))
             if c2.bias is not None:
                 bwd.append(o.build_colsum(cb, G(c2.bias), C=nc[l]))
             bwd.append(o.build_gemm_tn(cb, R["WpT"][k + 1], N=nc[l], K=nc[l], bn=bns[l], conv=geos[l], outB=dh[l],
                                        aux=hb_, act_slope=spec.slope))
-            bwd.append(o.build_gemm_nt(dh[l], xb_, dWres[l][k], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l]))
+            bwd.append(o.build_gemm_nt(dh[l], xb_, dWres[l][k], n1=nc[l], n2=nc[l], bn=_bn_tile(nc[l]), conv=geos[l],
+                                       swap=swp[l]))
             if c1.bias is not None:
                 bwd.append(o.build_colsum(dh[l], G(c1.bias), C=nc[l]))
             bwd.append(o.build_gemm_tn(dh[l], R["WpT"][k], N=nc[l], K=nc[l], bn=bns[l], conv=geos[l], resid=cf, outF=nf,
@@ -755,7 +763,7 @@ class _UNetResPlan(_PlanBase):
             convs = Wt["res"][l]["convs"]
             if convs:
                 bwd.append(o.build_unpack_conv_grad(dWres[l], [G(c.weight) for c in convs], None, O=nc[l], I=nc[l],
-                                                    I_pad=nc[l]))
+                                                    I_pad=nc[l], transposed=swp[l]))
         for l in range(3):
             D, U = Wt["down"][l], Wt["up"][l]
             Ci, Co = nc[l], nc[l + 1]

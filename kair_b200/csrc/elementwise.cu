@@ -231,8 +231,8 @@ template <int TAPS>   // 0: run-time tap count; 1 / 4 / 9: compile-time (the ind
 __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
   const int l = blockIdx.y;
   const unsigned taps = TAPS ? TAPS : a.taps;
-  const int rp = a.dwp_pitch > 0 ? a.dwp_pitch : (int)taps * a.I_pad;  // row pitch of the packed gradient
-  const float* dWp = a.dWp + (size_t)l * a.O_pad * rp;
+  const int rp = a.dwp_pitch > 0 ? a.dwp_pitch : (a.transposed ? a.O_pad : (int)taps * a.I_pad);  // row pitch
+  const float* dWp = a.dWp + (size_t)l * (a.transposed ? (size_t)taps * a.I_pad : (size_t)a.O_pad) * rp;
   float* dW = reinterpret_cast<float*>(a.dW[l]);
   // one layer's (O, I, taps) count fits 32 bits (launcher check): 32-bit div/mod chain, coalesced writes, the strided
   // reads of a warp (taps rows x ~4 consecutive inputs) are served by L1
@@ -240,7 +240,7 @@ __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
   for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
     const unsigned oi = e / taps, tap = e - oi * taps;
     const unsigned o = oi / I, i = oi - o * I;
-    dW[e] = __ldg(dWp + (size_t)o * rp + tap * a.I_pad + i);
+    dW[e] = a.transposed ? __ldg(dWp + (size_t)(tap * a.I_pad + i) * rp + o) : __ldg(dWp + (size_t)o * rp + tap * a.I_pad + i);
   }
   if (a.db && a.ones_col >= 0 && blockIdx.x == 0) {
     float* db = reinterpret_cast<float*>(a.db[l]);
@@ -251,6 +251,7 @@ __global__ void unpack_conv_kernel(const kair_unpack_conv_args a) {
 
 int unpack_conv_launch(const kair_unpack_conv_args& a, cudaStream_t st) {
   KB_CHECK(a.dWp && a.dW, "kair_unpack_conv_grad: null pointer");
+  KB_CHECK(!a.transposed || !a.db, "kair_unpack_conv_grad: the transposed layout carries no bias column");
   size_t n = (size_t)a.O * a.I * a.taps;
   KB_CHECK(a.taps >= 1 && n < (1ull << 31), "kair_unpack_conv_grad: a layer's weight count must fit 31 bits");
   int blocks = (int)((n + 255) / 256);

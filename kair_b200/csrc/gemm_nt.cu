@@ -43,6 +43,8 @@ struct NtParams {
   int H, W, TW, TH, tiles_w, tiles_h;  // conv: a k-block is a TW x TH pixel patch (TW*TH = 64)
   int k2;                              // channels of B per tap (conv: column block stride in D)
   int dil;                             // conv: tap dilation (1 = dense 3x3)
+  int swap;                            // conv, 64 input channels: tmA = the INPUT image (one tap-shifted atom per 64 rows of
+                                       // the M operand, tap = tile1 * BM / 64 + atom), tmB = the output gradient; D transposed
   int ring;                            // bytes of the stage ring (>= the epilogue staging that aliases it)
   long long* ts;                       // development aid (env KB_NT_TS): cycle counters of CTA 0
 };
@@ -117,10 +119,30 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         mbar_wait(&empty_bar[stage], phase ^ 1);
         t_wait += NT_CLOCK() - tw0;
         if (elect_one()) {
-        mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
         uint8_t* a_s = a_base + stage * NT_A_STAGE;
         uint8_t* b_s = b_base + stage * B_STAGE;
-        if (kConv) {
+        if (kConv && p.swap) {
+          // swapped roles: M rows = (tap, input channel); atoms past the ninth tap are not loaded (their rows of D are
+          // outside the result tensor and clipped by the TMA store)
+          int per_img = p.tiles_w * p.tiles_h;
+          int b = kb / per_img;
+          int r = kb - b * per_img;
+          int th = r / p.tiles_w;
+          int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
+          const int tap0 = tile1 * (BM / 64);
+          const int n_at = 9 - tap0 < BM / 64 ? 9 - tap0 : BM / 64;
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(n_at * 8192 + B_STAGE));
+#pragma unroll
+          for (int i = 0; i < BM / 64; ++i) {
+            const int tp = tap0 + i, ty = tp / 3, tx = tp - ty * 3;
+            if (i < n_at)
+              tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], 0, w0 + (tx - 1) * p.dil, h0 + (ty - 1) * p.dil, b);
+          }
+#pragma unroll
+          for (int i = 0; i < BN / 64; ++i)
+            tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0, h0, b);
+        } else if (kConv) {
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
           int per_img = p.tiles_w * p.tiles_h;
           int b = kb / per_img;
           int r = kb - b * per_img;
@@ -133,6 +155,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           for (int i = 0; i < BN / 64; ++i)
             tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0 + (dx - 1) * p.dil, h0 + (dy - 1) * p.dil, b);
         } else {
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i)
             tma_load_2d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * BM + i * 64, kb * NT_BKT);
@@ -276,7 +299,12 @@ static int nt_launch_cfg(NtParams p, int grid, size_t smem, cudaStream_t st) {
 int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   KB_CHECK(a.A && a.B && a.D, "kair_gemm_nt: null pointer");
   KB_CHECK(a.bn == 64 || a.bn == 128 || a.bn == 192 || a.bn == 256, "kair_gemm_nt: bn=%d unsupported", a.bn);
-  KB_CHECK(a.n2 > 0 && a.n2 % a.bn == 0, "kair_gemm_nt: n2=%d must be a multiple of bn=%d", a.n2, a.bn);
+  if (a.swap) {
+    KB_CHECK(a.conv && a.n2 == 64, "kair_gemm_nt: swap needs conv = 1 and n2 = 64 input channels (got n2=%d)", a.n2);
+    KB_CHECK(a.n1 % a.bn == 0, "kair_gemm_nt: swap: n1=%d must be a multiple of bn=%d", a.n1, a.bn);
+  } else {
+    KB_CHECK(a.n2 > 0 && a.n2 % a.bn == 0, "kair_gemm_nt: n2=%d must be a multiple of bn=%d", a.n2, a.bn);
+  }
   KB_CHECK(a.n1 > 0 && a.n1 % 64 == 0, "kair_gemm_nt: n1=%d must be a multiple of 64", a.n1);
   KB_CHECK(a.a_pitch % 8 == 0 && a.b_pitch % 8 == 0 && a.d_pitch % 4 == 0, "kair_gemm_nt: misaligned pitch");
   KB_CHECK(a.T > 0, "kair_gemm_nt: empty token range");
@@ -297,6 +325,21 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   p.tiles1 = (a.n1 + bm - 1) / bm;
   p.tiles2 = a.n2 / a.bn;
   p.k2 = a.n2;
+  // swapped roles (64 input channels): M = (tap, input channel) = 576 rows in 128-row tiles, N = output channels
+  const void* opA = a.A;
+  const void* opB = a.B;
+  long long pitchA = a.a_pitch, pitchB = a.b_pitch;
+  int chA = a.n1, chB = a.n2;
+  if (a.swap) {
+    p.swap = 1;
+    bm = 128;
+    p.taps = 1;
+    p.tiles1 = (9 * 64 + bm - 1) / bm;
+    p.tiles2 = a.n1 / a.bn;
+    p.k2 = 0;
+    opA = a.B; pitchA = a.b_pitch; chA = a.n2;
+    opB = a.A; pitchB = a.a_pitch; chB = a.n1;
+  }
   if (a.conv) {
     KB_CHECK((long long)a.batch * a.H * a.W == a.T, "kair_gemm_nt: conv geometry does not match T");
     p.H = a.H;
@@ -310,16 +353,16 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
     p.kb_total = a.batch * p.tiles_w * p.tiles_h;
     uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH, 1};
     {
-      uint64_t dims[4] = {(uint64_t)a.n1, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
-      uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.a_pitch * 2 * a.W, (uint64_t)a.a_pitch * 2 * a.W * a.H};
-      if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.A, dims, str, box, nullptr,
+      uint64_t dims[4] = {(uint64_t)chA, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+      uint64_t str[3] = {(uint64_t)pitchA * 2, (uint64_t)pitchA * 2 * a.W, (uint64_t)pitchA * 2 * a.W * a.H};
+      if (make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, opA, dims, str, box, nullptr,
                     CU_TENSOR_MAP_SWIZZLE_128B))
         return -2;
     }
     {
-      uint64_t dims[4] = {(uint64_t)a.n2, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
-      uint64_t str[3] = {(uint64_t)a.b_pitch * 2, (uint64_t)a.b_pitch * 2 * a.W, (uint64_t)a.b_pitch * 2 * a.W * a.H};
-      if (make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a.B, dims, str, box, nullptr,
+      uint64_t dims[4] = {(uint64_t)chB, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.batch};
+      uint64_t str[3] = {(uint64_t)pitchB * 2, (uint64_t)pitchB * 2 * a.W, (uint64_t)pitchB * 2 * a.W * a.H};
+      if (make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, opB, dims, str, box, nullptr,
                     CU_TENSOR_MAP_SWIZZLE_128B))
         return -2;
     }
@@ -342,7 +385,7 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
     }
   }
   {
-    uint64_t dims[2] = {(uint64_t)a.n2 * p.taps, (uint64_t)a.n1};
+    uint64_t dims[2] = {a.swap ? (uint64_t)a.n1 : (uint64_t)a.n2 * p.taps, a.swap ? (uint64_t)9 * a.n2 : (uint64_t)a.n1};
     uint64_t str[1] = {(uint64_t)a.d_pitch * 4};
     uint32_t box[2] = {32, 32};
     if (make_tmap(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, a.D, dims, str, box, nullptr,

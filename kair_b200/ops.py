@@ -185,14 +185,17 @@ def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF
     return Launch("kair_mlp_fused", a)
 
 
-def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1):
-    """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed."""
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1, swap=False):
+    """D[n1, taps*n2] += A[:, :n1]^T @ B[:, :n2] (token contraction).  D is fp32 and must be pre-zeroed.
+    swap (conv, n2 == 64): the same products written transposed, D[9*n2, n1] (rows tap*n2 + input channel)."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B"); _req(D, torch.float32, "D")
     a = _S["kair_gemm_nt_args"]()
     a.A = _ptr(A); a.a_pitch = _pitch(A)
     a.B = _ptr(B); a.b_pitch = _pitch(B)
     a.D = _ptr(D); a.d_pitch = _pitch(D)
-    a.n1 = n1; a.n2 = n2; a.bn = bn; a.splits = splits; a.dilation = dilation
+    a.n1 = n1; a.n2 = n2; a.bn = bn; a.splits = splits; a.dilation = dilation; a.swap = 1 if swap else 0
+    if swap and (conv is None or n2 != 64 or D.shape[-2] < 9 * n2 or D.shape[-1] < n1):
+        raise RuntimeError("kair_b200: gemm_nt swap needs a 3x3 convolution with 64 input channels and D [9*64, >= n1]")
     if conv is not None:
         a.conv = 1
         a.batch, a.H, a.W = conv
@@ -300,13 +303,16 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshi
     return Launch("kair_pack_conv", a, keep)
 
 
-def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0):
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0, transposed=False):
     keep = []
     a = _S["kair_unpack_conv_args"]()
     a.dWp = _ptr(dWp); a.dW = _plist(dW, dWp, keep); a.db = _plist(db, dWp, keep)
-    a.L, a.O_pad = dWp.shape[0], dWp.shape[1]
+    a.L, a.O_pad = dWp.shape[0], (dWp.shape[2] if transposed else dWp.shape[1])
     a.O, a.I, a.I_pad, a.taps, a.ones_col, a.center_tap = O, I, I_pad, taps, ones_col, center_tap
     a.dwp_pitch = dwp_pitch
+    a.transposed = 1 if transposed else 0
+    if transposed and (db is not None or dWp.shape[1] != taps * I_pad):
+        raise RuntimeError("kair_b200: transposed packed gradients are [L, taps*I_pad, O_pad] and carry no bias column")
     return Launch("kair_unpack_conv_grad", a, keep)
 
 

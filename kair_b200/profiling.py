@@ -43,7 +43,7 @@ def describe(launch, real_dims):
         return tag, 4.0 * a.M * rn * rf, by
     if name == "gemm_nt":
         taps = 9 if a.conv else 1
-        tag = "gemm_nt[%s n1=%d n2=%d]" % ("conv3x3" if a.conv else "dense", a.n1, a.n2 * taps)
+        tag = "gemm_nt[%s n1=%d n2=%d%s]" % ("conv3x3" if a.conv else "dense", a.n1, a.n2 * taps, " swap" if a.swap else "")
         return tag, 2.0 * a.T * r(a.n1) * r(a.n2) * taps, 2.0 * a.T * (r(a.n1) + r(a.n2))
     if name in ("window_attn_fwd", "window_attn_bwd"):
         T = a.batch * a.H * a.W

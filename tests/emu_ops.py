@@ -205,8 +205,8 @@ def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF
     return EmuLaunch("kair_mlp_fused", run)
 
 
-def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1):
-    assert n1 % 64 == 0 and n2 % bn == 0
+def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1, swap=False):
+    assert n1 % 64 == 0 and (n1 % bn == 0 and n2 == 64 and conv is not None if swap else n2 % bn == 0)
     d = dilation
 
     def run():
@@ -220,7 +220,10 @@ def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1):
         for tap in range(9):
             dy, dx = tap // 3, tap % 3
             bs = bp[:, dy * d:dy * d + H, dx * d:dx * d + W, :]
-            D[:n1, tap * n2:(tap + 1) * n2] += torch.einsum("bhwi,bhwj->ij", a, bs)
+            if swap:   # transposed result: rows tap*n2 + input channel, columns output channel
+                D[tap * n2:(tap + 1) * n2, :n1] += torch.einsum("bhwi,bhwj->ji", a, bs)
+            else:
+                D[:n1, tap * n2:(tap + 1) * n2] += torch.einsum("bhwi,bhwj->ij", a, bs)
 
     return EmuLaunch("kair_gemm_nt", run)
 
@@ -392,10 +395,15 @@ def build_pack_conv(W, b, Wp, WpT, bp, *, O, I, I_pad, taps=9, oscale=None, oshi
     return EmuLaunch("kair_pack_conv", run)
 
 
-def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0):
+def build_unpack_conv_grad(dWp, dW, db, *, O, I, I_pad, taps=9, ones_col=-1, center_tap=4, dwp_pitch=0, transposed=False):
     def run():
         L, O_pad = dWp.shape[0], dWp.shape[1]
         for l in range(L):
+            if transposed:   # [taps*I_pad, O_pad] -> (O, I, taps)
+                assert db is None
+                d = dWp[l].reshape(taps, I_pad, -1)
+                dW[l].copy_(d[:, :I, :O].permute(2, 1, 0).reshape(dW[l].shape))
+                continue
             d = dWp[l].reshape(O_pad, -1)[:, :taps * I_pad].reshape(O_pad, taps, I_pad)
             dW[l].copy_(d[:O, :, :I].permute(0, 2, 1).reshape(dW[l].shape))
             if db is not None and ones_col >= 0:
