@@ -56,7 +56,19 @@ struct MfParams {
   int n_valid, ones_col, ones_col_g, ln;
   int has_resid, has_outF, has_outB, has_u, has_g;
   float ln_eps;
+  long long* ts;   // development timeline (devel build, env KB_MF_TS): clock64 stamps of epilogue warp 2 / lane 0 of CTA 0
 };
+
+#ifdef KB_DEVEL
+#define MF_STAMP()                                                                                   \
+  do {                                                                                               \
+    if (p.ts && blockIdx.x == 0 && threadIdx.x == 64 && tsn < 512) p.ts[tsn++] = clock64();          \
+  } while (0)
+#else
+#define MF_STAMP() \
+  do {             \
+  } while (0)
+#endif
 
 __device__ __forceinline__ void mf_stage_bf16(uint8_t* buf, int lane, const float (&v)[32]) {
   // 32 rows x 32 bf16 (64-byte rows), SWIZZLE_64B: 16-byte unit j of row r lives at unit j ^ ((r >> 1) & 3)
@@ -307,6 +319,8 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
   } else {
     // ================================ epilogue ================================
     const int ew = warp - 2;
+    int tsn = 0;
+    (void)tsn;
     const int q = warp & 3;    // TMEM lane quarter this warp may access
     const int hf = ew >> 2;    // column half
     const int row = q * 32 + lane;
@@ -389,8 +403,10 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
 #pragma unroll 1
       for (int c = 0; c < NC; ++c, ++gc) {
         const uint32_t b1 = gc & 1;
+        MF_STAMP();   // 0: chunk start
         mbar_wait(&acc1_full[b1], (gc >> 1) & 1);
         tcgen05_fence_after();
+        MF_STAMP();   // 1: acc1 ready
         uint32_t pk[2][16];
 #pragma unroll
         for (int g2 = 0; g2 < 2; ++g2) {
@@ -423,11 +439,6 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
           }
 #pragma unroll
           for (int i = 0; i < 32; i += 2) gelu_erf2(v[i], v[i + 1]);
-          if (p.ones_col_g >= hcol && p.ones_col_g < hcol + 32) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (hcol + i == p.ones_col_g) v[i] = 1.0f;
-          }
 #pragma unroll
           for (int i = 0; i < 16; ++i) pk[g2][i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
         }
@@ -435,7 +446,9 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         __syncwarp();
         if (lane == 0) mbar_arrive(&acc1_empty[b1]);
         // G tile: K-major slice `hf` (64 hidden columns), 128-byte rows in 8-row SWIZZLE_128B atoms
+        MF_STAMP();   // 2: bias + u + GELU done
         mbar_wait(g_empty, (gc & 1) ^ 1);
+        MF_STAMP();   // 3: G tile free
         {
           const uint32_t base = smem_u32(g_base + hf * (MF_BM * 128)) + row * 128;
           const uint32_t sw = row & 7;
@@ -448,6 +461,17 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
                            "r"(pk[g2][4 * j + 1]), "r"(pk[g2][4 * j + 2]), "r"(pk[g2][4 * j + 3])
                            : "memory");
             }
+        }
+        {
+          // the ones column of g (it carries fc2's bias gradient through the weight-gradient GEMM): one 2-byte store into
+          // the operand tile by the thread that owns the row, after its own vector stores.  (As `if (col == ones) v = 1`
+          // over the registers the compiler emitted 64 compare + select pairs per chunk: 12 % of an issue-bound loop.)
+          const int oc = p.ones_col_g - (c * MF_HC + hf * 64);   // column inside this thread's 64-column slice
+          if (oc >= 0 && oc < 64) {
+            const uint32_t a = smem_u32(g_base + hf * (MF_BM * 128)) + row * 128 + ((((uint32_t)oc >> 3) ^ (row & 7)) << 4) +
+                               ((uint32_t)oc & 7) * 2;
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)0x3F80) : "memory");
+          }
         }
         fence_proxy_async_smem();
         __syncwarp();
@@ -462,8 +486,10 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
       }
 
       // ---------------- output: acc2 -> +b2, DropPath, residual, [LayerNorm] ----------------
+      MF_STAMP();   // 12: hidden chunks done
       mbar_wait(acc2_full, it & 1);
       tcgen05_fence_after();
+      MF_STAMP();   // 13: acc2 ready
       const uint32_t tacc = tmem_acc2 + lane_sel + col_half;
       float s1 = 0.f;
 #pragma unroll 1
@@ -526,8 +552,10 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
       }
       if (kLN) {
         tmem_st_wait();
+        MF_STAMP();   // 14: pass A done
         float tot, dummy;
         exchange2(s1, 0.f, tot, dummy);
+        MF_STAMP();   // 15: first exchange
         const float mean = tot * inv_n;
         float s2 = 0.f;
 #pragma unroll 1
@@ -594,6 +622,7 @@ __global__ void __launch_bounds__(MF_THREADS, 1) mlp_fused_kernel(const __grid_c
         if (elect_one()) tma_store_wait_read<0>();
         __syncwarp();
       }
+      MF_STAMP();   // 16: output phase done
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc2_empty);
@@ -620,7 +649,22 @@ int mf_launch_cfg(const MfParams& p, int grid, size_t smem, cudaStream_t st) {
     KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     attr_set[dev & 63] = true;
   }
-  KB_CUDA(launch_pdl(kern, grid, MF_THREADS, smem, st, p));
+  static long long* ts_dev = nullptr;
+  MfParams q = p;
+  const bool want_ts = KB_DEV_ENV("KB_MF_TS") != nullptr;
+  if (want_ts) {
+    if (!ts_dev) cudaMalloc(&ts_dev, 512 * 8);
+    cudaMemset(ts_dev, 0, 512 * 8);
+    q.ts = ts_dev;
+  }
+  KB_CUDA(launch_pdl(kern, grid, MF_THREADS, smem, st, q));
+  if (want_ts) {
+    static long long h[512];
+    cudaMemcpy(h, ts_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "mlp_fused:");
+    for (int i = 0; i < 120 && h[i]; ++i) fprintf(stderr, " %lld", h[i] - h[0]);
+    fprintf(stderr, "\n");
+  }
   return 0;
 }
 
