@@ -90,7 +90,41 @@ def build(verbose=False, force=False, devel=False):
         for _, log in results:
             if log:
                 sys.stderr.write(log)
+    build_torch_ext(force=force)
     return LIB_PATH
+
+
+TORCH_SRC = os.path.join(HERE, "csrc_torch", "kair_b200_torch.cpp")
+TORCH_LIB_PATH = os.path.join(HERE, "libkair_b200_torch.so")
+
+
+def build_torch_ext(force=False):
+    """The thin torch C++ extension (csrc_torch/kair_b200_torch.cpp: TORCH_LIBRARY ops over the C ABI), compiled with
+    plain g++ against the installed torch and linked to libkair_b200.so next to it ($ORIGIN rpath)."""
+    import torch
+    from torch.utils import cpp_extension as ce
+    stamp = os.path.join(OBJ_DIR, "kair_b200_torch.stamp")
+    h = hashlib.sha256()
+    for f in (TORCH_SRC, os.path.join(HERE, "..", "include", "kair_b200.h")):
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    h.update(torch.__version__.encode())
+    dig = h.hexdigest()
+    if (not force and os.path.exists(TORCH_LIB_PATH) and os.path.exists(stamp) and open(stamp).read() == dig
+            and os.path.getmtime(TORCH_LIB_PATH) >= os.path.getmtime(LIB_PATH)):
+        return TORCH_LIB_PATH
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", TORCH_SRC]
+    cmd += ["-I" + p for p in ce.include_paths()] + ["-I" + os.path.join(cuda_home, "include")]
+    cmd += ["-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI)]
+    cmd += ["-L" + p for p in ce.library_paths()] + ["-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda"]
+    cmd += ["-L" + HERE, "-lkair_b200", "-Wl,-rpath,$ORIGIN", "-o", TORCH_LIB_PATH]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building the torch extension failed:\n%s\n%s" % (r.stdout, r.stderr))
+    with open(stamp, "w") as fh:
+        fh.write(dig)
+    return TORCH_LIB_PATH
 
 
 if __name__ == "__main__":

@@ -1,5 +1,6 @@
 """Thin tensor-level wrappers over the C-ABI kernels.  PyTorch supplies device memory and streams only."""
 import ctypes
+import os
 
 import torch
 
@@ -9,6 +10,11 @@ EPI_LINEAR, EPI_GELU, EPI_RESID_LN, EPI_DGELU, EPI_LNBWD = range(5)
 ACT_NONE, ACT_LRELU = 0, 1
 
 _S = _lib.STRUCTS
+
+
+# KAIR_B200_TORCH_OPS=1: launch lists are replayed through torch.ops.kair_b200.run_list (kair_b200/torch_ext.py) instead
+# of the ctypes call -- the second binding of the same C ABI
+USE_TORCH_OPS = os.environ.get("KAIR_B200_TORCH_OPS") == "1"
 
 
 class Launch:
@@ -67,9 +73,17 @@ class LaunchList:
         self.fn = lib.kair_run_list
 
     def run(self, stream):
+        if USE_TORCH_OPS:   # same C entry point, reached through the torch C++ extension (current device / stream)
+            return self.run_torch(torch.empty(0, device="cuda"))
         rc = self.fn(self.array, self.n, stream)
         if rc != 0:
             _lib.check(rc, "kair_run_list")
+
+    def run_torch(self, anchor):
+        """the same replay through the torch C++ extension (`torch.ops.kair_b200.run_list`, kair_b200/torch_ext.py) on
+        the current stream of `anchor`'s device"""
+        from . import torch_ext
+        torch_ext.load().run_list(anchor, ctypes.addressof(self.array), self.n)
 
     def __len__(self):
         return self.n
