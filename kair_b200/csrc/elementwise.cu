@@ -321,11 +321,85 @@ __global__ void layernorm_fwd_kernel(const kair_layernorm_args a) {
   }
 }
 
+// Fast path (terms <= 1, even pitch): a lane owns column PAIRS c = 2 * lane + 64 * i, so every warp access is one
+// 256-byte (fp32) or 128-byte (bf16) contiguous run instead of 128 / 64 bytes, and a warp keeps two rows in flight.
+// Same arithmetic and summation order per row as layernorm_fwd_kernel up to the pairing of the partial sums.
+__global__ void __launch_bounds__(256) layernorm_fwd_pairs_kernel(const kair_layernorm_args a) {
+  const int warps = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nv = (a.pitch + 63) >> 6;   // float2 per lane and row (<= 4)
+  const long long row0 = ((long long)blockIdx.x * warps + (threadIdx.x >> 5)) * 2;
+  float2 v[2][4];
+  float s[2] = {0.f, 0.f};
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const long long row = row0 + r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = 2 * lane + 64 * i;
+      v[r][i] = make_float2(0.f, 0.f);
+      if (i < nv && row < a.T && c < a.C) {
+        const float2 t = *reinterpret_cast<const float2*>(a.x + row * a.pitch + c);
+        v[r][i].x = t.x;
+        v[r][i].y = (c + 1 < a.C) ? t.y : 0.f;
+      }
+      s[r] += v[r][i].x + v[r][i].y;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const long long row = row0 + r;
+    if (row >= a.T) return;   // rows come in order: nothing follows an absent row (warp-uniform)
+    const float mean = warp_sum(s[r]) / a.C;
+    float s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = 2 * lane + 64 * i;
+      const float d0 = (i < nv && c < a.C) ? v[r][i].x - mean : 0.f;
+      const float d1 = (i < nv && c + 1 < a.C) ? v[r][i].y - mean : 0.f;
+      s2 += d0 * d0 + d1 * d1;
+    }
+    const float rstd = rsqrtf(warp_sum(s2) / a.C + a.eps);
+    if (lane == 0) {
+      if (a.mean) a.mean[row] = mean;
+      if (a.rstd) a.rstd[row] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = 2 * lane + 64 * i;
+      if (i >= nv || c >= a.pitch) continue;
+      float xh[2], y[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int ce = c + e;
+        const float xv = e ? v[r][i].y : v[r][i].x;
+        xh[e] = (ce < a.C) ? (xv - mean) * rstd : 0.f;
+        y[e] = (ce < a.C && a.gamma) ? xh[e] * a.gamma[ce] + a.beta[ce] : 0.f;
+      }
+      if (a.y_f32) *reinterpret_cast<float2*>(a.y_f32 + row * a.pitch + c) = make_float2(y[0], y[1]);
+      if (a.y_bf16)
+        *reinterpret_cast<uint32_t*>(reinterpret_cast<bf16*>(a.y_bf16) + row * a.pitch + c) =
+            pack_bf16x2(c == a.ones_col ? 1.0f : y[0], c + 1 == a.ones_col ? 1.0f : y[1]);
+      if (a.xhat_bf16)
+        *reinterpret_cast<uint32_t*>(reinterpret_cast<bf16*>(a.xhat_bf16) + row * a.pitch + c) =
+            pack_bf16x2(c == a.ones_col ? 1.0f : xh[0], c + 1 == a.ones_col ? 1.0f : xh[1]);
+    }
+  }
+}
+
 int layernorm_fwd_launch(const kair_layernorm_args& a, cudaStream_t st) {
   KB_CHECK(a.x && a.T > 0 && a.C > 0 && a.pitch >= a.C && a.pitch <= 256, "kair_layernorm_fwd: bad arguments");
   KB_CHECK((a.y_f32 == nullptr && a.y_bf16 == nullptr) || (a.gamma && a.beta), "kair_layernorm_fwd: affine output needs gamma/beta");
   KB_CHECK(a.terms == 0 || a.terms == 1 || a.terms == 3 || a.terms == 6, "kair_layernorm_fwd: terms=%d", a.terms);
   const int warps = 8;
+  const bool aligned = (reinterpret_cast<uintptr_t>(a.x) % 8 == 0) && (!a.y_f32 || reinterpret_cast<uintptr_t>(a.y_f32) % 8 == 0) &&
+                       (!a.y_bf16 || reinterpret_cast<uintptr_t>(a.y_bf16) % 4 == 0) &&
+                       (!a.xhat_bf16 || reinterpret_cast<uintptr_t>(a.xhat_bf16) % 4 == 0);
+  if (a.terms <= 1 && a.pitch % 2 == 0 && aligned) {
+    layernorm_fwd_pairs_kernel<<<(unsigned)((a.T + 2 * warps - 1) / (2 * warps)), warps * 32, 0, st>>>(a);
+    KB_CUDA(cudaGetLastError());
+    return 0;
+  }
   layernorm_fwd_kernel<<<(unsigned)((a.T + warps - 1) / warps), warps * 32, 0, st>>>(a);
   KB_CUDA(cudaGetLastError());
   return 0;
