@@ -517,6 +517,7 @@ int layernorm_bwd_launch(const kair_layernorm_bwd_args& a, cudaStream_t st) {
 
 // ------------------------------------------------------------------------------------------------ thin convolutions
 constexpr int CI_MAX = 4;  // image-side channel count handled by the SIMT convolutions
+constexpr int CI_PIX = 4;  // conv_in: pixels (along a row) per thread
 
 // conv_in: NCHW fp32 image (B, ci, H, W) -> token features [T][pitch]; one thread per (pixel, 8 consecutive outputs):
 // every thread is independent (no reductions), its 9*ci image loads are issued together, the weights are read from
@@ -536,66 +537,86 @@ __global__ void conv_in_fwd_kernel(const kair_conv_in_args a) {
   float* sbias = sw + K * P8;
   for (int o = threadIdx.x; o < P8; o += blockDim.x) sbias[o] = (o < a.O && a.b) ? a.b[o] : 0.f;
   __syncthreads();
+  // one thread = 8 consecutive outputs of CI_PIX consecutive pixels of a row: the 18 float4 weight reads per tap set are
+  // amortised over four pixels (one pixel per thread was bound by the shared-memory bandwidth of those reads: every
+  // warp-wide LDS.128 is 8 wavefronts), and the 3 x (CI_PIX + 2) image window is loaded once
   const idx_t og = (idx_t)(P8 >> 3);  // output groups per pixel
-  const idx_t T = (idx_t)a.batch * (idx_t)a.H * (idx_t)a.Wd;
-  const idx_t n = T * og;
+  const idx_t Wq = (idx_t)((a.Wd + CI_PIX - 1) / CI_PIX);
+  const idx_t rows = (idx_t)a.batch * (idx_t)a.H;
+  const idx_t n = rows * Wq * og;
   for (idx_t e = (idx_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (idx_t)gridDim.x * blockDim.x) {
-    const idx_t t = e / og;
-    const int g = (int)(e - t * og);
-    const idx_t row = t / (idx_t)a.Wd;
-    const int w = (int)(t - row * (idx_t)a.Wd);
+    const idx_t tq = e / og;
+    const int g = (int)(e - tq * og);
+    const idx_t row = tq / Wq;
+    const int w0 = (int)(tq - row * Wq) * CI_PIX;
     const int b = (int)(row / (idx_t)a.H), h = (int)(row - (idx_t)b * (idx_t)a.H);
-    float in[CI * 9];
+    float in[CI][3][CI_PIX + 2];
 #pragma unroll
     for (int c = 0; c < CI; ++c) {
 #pragma unroll
-      for (int tap = 0; tap < 9; ++tap) {
-        const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
-        float v = 0.f;
-        if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
-          v = __ldg(a.img + (((size_t)b * CI + c) * a.H + hh) * a.Wd + ww);
-          v = (v - a.mean[c]) * a.range;
+      for (int dy = 0; dy < 3; ++dy) {
+        const int hh = h + dy - 1;
+#pragma unroll
+        for (int x = 0; x < CI_PIX + 2; ++x) {
+          const int ww = w0 + x - 1;
+          float v = 0.f;
+          if (hh >= 0 && hh < a.H && ww >= 0 && ww < a.Wd) {
+            v = __ldg(a.img + (((size_t)b * CI + c) * a.H + hh) * a.Wd + ww);
+            v = (v - a.mean[c]) * a.range;
+          }
+          in[c][dy][x] = v;
         }
-        in[c * 9 + tap] = v;
       }
     }
-    float acc[8];
+    float acc[CI_PIX][8];
     {
       const float4 b0 = *reinterpret_cast<const float4*>(sbias + 8 * g);
       const float4 b1 = *reinterpret_cast<const float4*>(sbias + 8 * g + 4);
-      acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+#pragma unroll
+      for (int j = 0; j < CI_PIX; ++j) {
+        acc[j][0] = b0.x; acc[j][1] = b0.y; acc[j][2] = b0.z; acc[j][3] = b0.w;
+        acc[j][4] = b1.x; acc[j][5] = b1.y; acc[j][6] = b1.z; acc[j][7] = b1.w;
+      }
     }
+    // same accumulation order per output as before: channels outer, taps in (dy, dx) order
 #pragma unroll
     for (int c = 0; c < CI; ++c) {
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
-        const float x = in[c * 9 + tap];
         const float* wr = sw + (c * 9 + tap) * P8 + 8 * g;
-        const float4 w0 = *reinterpret_cast<const float4*>(wr);
-        const float4 w1 = *reinterpret_cast<const float4*>(wr + 4);
-        acc[0] += w0.x * x; acc[1] += w0.y * x; acc[2] += w0.z * x; acc[3] += w0.w * x;
-        acc[4] += w1.x * x; acc[5] += w1.y * x; acc[6] += w1.z * x; acc[7] += w1.w * x;
+        const float4 w0v = *reinterpret_cast<const float4*>(wr);
+        const float4 w1v = *reinterpret_cast<const float4*>(wr + 4);
+#pragma unroll
+        for (int j = 0; j < CI_PIX; ++j) {
+          const float x = in[c][tap / 3][j + tap % 3];
+          acc[j][0] += w0v.x * x; acc[j][1] += w0v.y * x; acc[j][2] += w0v.z * x; acc[j][3] += w0v.w * x;
+          acc[j][4] += w1v.x * x; acc[j][5] += w1v.y * x; acc[j][6] += w1v.z * x; acc[j][7] += w1v.w * x;
+        }
       }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int o = 8 * g + i;
-      if (o >= a.O) acc[i] = 0.f;
-      else if (a.act == KAIR_ACT_LRELU) acc[i] = acc[i] > 0.f ? acc[i] : acc[i] * a.act_slope;
-    }
-    const long long off = (long long)t * a.pitch + 8 * g;
-    if (a.out_f32) {
-      reinterpret_cast<float4*>(a.out_f32 + off)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      reinterpret_cast<float4*>(a.out_f32 + off)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    }
-    if (a.out_bf16) {
+    for (int j = 0; j < CI_PIX; ++j) {
+      if (w0 + j >= a.Wd) break;
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
-        if (8 * g + i == a.ones_col) acc[i] = 1.0f;
-      uint4 o4;
-      o4.x = pack_bf16x2(acc[0], acc[1]); o4.y = pack_bf16x2(acc[2], acc[3]);
-      o4.z = pack_bf16x2(acc[4], acc[5]); o4.w = pack_bf16x2(acc[6], acc[7]);
-      *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.out_bf16) + off) = o4;
+      for (int i = 0; i < 8; ++i) {
+        const int o = 8 * g + i;
+        if (o >= a.O) acc[j][i] = 0.f;
+        else if (a.act == KAIR_ACT_LRELU) acc[j][i] = acc[j][i] > 0.f ? acc[j][i] : acc[j][i] * a.act_slope;
+      }
+      const long long off = ((long long)row * a.Wd + w0 + j) * a.pitch + 8 * g;
+      if (a.out_f32) {
+        reinterpret_cast<float4*>(a.out_f32 + off)[0] = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+        reinterpret_cast<float4*>(a.out_f32 + off)[1] = make_float4(acc[j][4], acc[j][5], acc[j][6], acc[j][7]);
+      }
+      if (a.out_bf16) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (8 * g + i == a.ones_col) acc[j][i] = 1.0f;
+        uint4 o4;
+        o4.x = pack_bf16x2(acc[j][0], acc[j][1]); o4.y = pack_bf16x2(acc[j][2], acc[j][3]);
+        o4.z = pack_bf16x2(acc[j][4], acc[j][5]); o4.w = pack_bf16x2(acc[j][6], acc[j][7]);
+        *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.out_bf16) + off) = o4;
+      }
     }
   }
 }
@@ -606,7 +627,7 @@ int conv_in_fwd_launch(const kair_conv_in_args& a, cudaStream_t st) {
   KB_CHECK(a.O_pad >= a.O && a.pitch >= a.O && a.pitch % 8 == 0, "kair_conv_in_fwd: pitch must be a multiple of 8, >= O");
   size_t smem = ((size_t)a.ci * 9 * a.pitch + a.pitch) * 4;
   KB_CHECK(smem <= 48 * 1024, "kair_conv_in_fwd: weights do not fit in shared memory");
-  const long long n = (long long)a.batch * a.H * a.Wd * (a.pitch >> 3);
+  const long long n = (long long)a.batch * a.H * ((a.Wd + CI_PIX - 1) / CI_PIX) * (a.pitch >> 3);
   long long blocks = (n + 255) / 256;
   if (blocks > (long long)sm_count() * 8) blocks = (long long)sm_count() * 8;
   const bool small = n + (long long)blocks * 256 < (1ll << 32);   // the grid-stride index stays inside 32 bits
