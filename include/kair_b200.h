@@ -157,10 +157,10 @@ typedef struct kair_gemm_nt_args {
   int32_t conv;
   int32_t batch, H, W;
   int32_t dilation;  /* conv == 1: tap (dy, dx) pairs A[p] with B[p + dilation * (dy-1, dx-1)]; 0 or 1 = dense taps */
-  int32_t swap;      /* conv == 1, n2 == 64 only: the same products, written TRANSPOSED -- D is fp32 [9*n2][d_pitch] with
+  int32_t swap;      /* conv == 1, n2 a multiple of 64: the same products, written TRANSPOSED -- D is fp32 [9*n2][d_pitch] with
                         D[tap*n2 + i][o] (kair_unpack_conv_grad `transposed`).  The tap-shifted input is then the M
-                        operand (two taps fill a 128-row UMMA) and the n1 output channels the N operand: for 64 -> 64
-                        layers every MMA row is useful, where the plain order wastes half of a 128-row accumulator */
+                        operand (9*n2 rows in 128-row tiles) and the n1 output channels the N operand: for layers with 64
+                        output channels every MMA row is useful, where the plain order wastes half of a 128-row accumulator */
 } kair_gemm_nt_args;
 
 int kair_gemm_nt(const kair_gemm_nt_args* args, void* stream);

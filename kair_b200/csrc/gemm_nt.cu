@@ -43,8 +43,8 @@ struct NtParams {
   int H, W, TW, TH, tiles_w, tiles_h;  // conv: a k-block is a TW x TH pixel patch (TW*TH = 64)
   int k2;                              // channels of B per tap (conv: column block stride in D)
   int dil;                             // conv: tap dilation (1 = dense 3x3)
-  int swap;                            // conv, 64 input channels: tmA = the INPUT image (one tap-shifted atom per 64 rows of
-                                       // the M operand, tap = tile1 * BM / 64 + atom), tmB = the output gradient; D transposed
+  int swap;                            // conv: tmA = the INPUT image (M rows = (tap, input channel): one tap-shifted
+                                       // [64 tok x 64 ch] atom per 64 rows), tmB = the output gradient; D transposed; k2 = n2 / 64
   int ring;                            // bytes of the stage ring (>= the epilogue staging that aliases it)
   long long* ts;                       // development aid (env KB_NT_TS): cycle counters of CTA 0
 };
@@ -129,14 +129,15 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           int r = kb - b * per_img;
           int th = r / p.tiles_w;
           int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
-          const int tap0 = tile1 * (BM / 64);
-          const int n_at = 9 - tap0 < BM / 64 ? 9 - tap0 : BM / 64;
+          // row atom r of the M side = (tap r / cpt, input channels 64 (r % cpt) ..), cpt = n2 / 64 atoms per tap
+          const int at0 = tile1 * (BM / 64);
+          const int n_at = 9 * p.k2 - at0 < BM / 64 ? 9 * p.k2 - at0 : BM / 64;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(n_at * 8192 + B_STAGE));
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i) {
-            const int tp = tap0 + i, ty = tp / 3, tx = tp - ty * 3;
+            const int at = at0 + i, tp = at / p.k2, ch = (at - tp * p.k2) * 64, ty = tp / 3, tx = tp - ty * 3;
             if (i < n_at)
-              tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], 0, w0 + (tx - 1) * p.dil, h0 + (ty - 1) * p.dil, b);
+              tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], ch, w0 + (tx - 1) * p.dil, h0 + (ty - 1) * p.dil, b);
           }
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
@@ -300,7 +301,7 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
   KB_CHECK(a.A && a.B && a.D, "kair_gemm_nt: null pointer");
   KB_CHECK(a.bn == 64 || a.bn == 128 || a.bn == 192 || a.bn == 256, "kair_gemm_nt: bn=%d unsupported", a.bn);
   if (a.swap) {
-    KB_CHECK(a.conv && a.n2 == 64, "kair_gemm_nt: swap needs conv = 1 and n2 = 64 input channels (got n2=%d)", a.n2);
+    KB_CHECK(a.conv && a.n2 > 0 && a.n2 % 64 == 0, "kair_gemm_nt: swap needs conv = 1 and n2 a multiple of 64 (got n2=%d)", a.n2);
     KB_CHECK(a.n1 % a.bn == 0, "kair_gemm_nt: swap: n1=%d must be a multiple of bn=%d", a.n1, a.bn);
   } else {
     KB_CHECK(a.n2 > 0 && a.n2 % a.bn == 0, "kair_gemm_nt: n2=%d must be a multiple of bn=%d", a.n2, a.bn);
@@ -334,9 +335,9 @@ int gemm_nt_launch(const kair_gemm_nt_args& a, cudaStream_t st) {
     p.swap = 1;
     bm = 128;
     p.taps = 1;
-    p.tiles1 = (9 * 64 + bm - 1) / bm;
+    p.tiles1 = (9 * a.n2 + bm - 1) / bm;
     p.tiles2 = a.n1 / a.bn;
-    p.k2 = 0;
+    p.k2 = a.n2 / 64;   // swap: atoms of 64 input channels per tap (the epilogue's tap * k2 column term is 0: taps = 1)
     opA = a.B; pitchA = a.b_pitch; chA = a.n2;
     opB = a.A; pitchB = a.a_pitch; chB = a.n1;
   }

@@ -208,8 +208,8 @@ def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1, swap=
     a.B = _ptr(B); a.b_pitch = _pitch(B)
     a.D = _ptr(D); a.d_pitch = _pitch(D)
     a.n1 = n1; a.n2 = n2; a.bn = bn; a.splits = splits; a.dilation = dilation; a.swap = 1 if swap else 0
-    if swap and (conv is None or n2 != 64 or D.shape[-2] < 9 * n2 or D.shape[-1] < n1):
-        raise RuntimeError("kair_b200: gemm_nt swap needs a 3x3 convolution with 64 input channels and D [9*64, >= n1]")
+    if swap and (conv is None or n2 % 64 or D.shape[-2] < 9 * n2 or D.shape[-1] < n1):
+        raise RuntimeError("kair_b200: gemm_nt swap needs a 3x3 convolution, n2 a multiple of 64 and D [9*n2, >= n1]")
     if conv is not None:
         a.conv = 1
         a.batch, a.H, a.W = conv

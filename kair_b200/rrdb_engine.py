@@ -148,8 +148,10 @@ class _RRDBPlan(_PlanBase):
         self.dout = f32(B, cout, H, W)
         self.grads = _GradStore(eng.P, dev)
         G = lambda p: self.grads.G[eng.name_of(p)]
-        dW = [f32(L, 64, 9 * KPAD[k]) for k in range(5)]
-        dWt = f32(2, 64, 9 * 64)
+        # every convolution here has 64 (padded) output channels: weight gradients with the operand roles swapped
+        # (kair_gemm_nt `swap`: M = (tap, input channel)), packed gradients transposed [9 * I_pad, 64]
+        dW = [f32(L, 9 * KPAD[k], 64) for k in range(5)]
+        dWt = f32(2, 9 * 64, 64)
         dsh, clT, dWcl, csum = bf(T, 64), bf(NF, 64), f32(NF, 64), f32(64)
         xcol, dWcf = bf(T, 64), f32(1, NF, 64)
         self.zero_before_bwd = dW + [dWt, dWcl, csum, dWcf]
@@ -165,7 +167,7 @@ class _RRDBPlan(_PlanBase):
         bwd.append(o.build_gemm_tn(dsh, clT, N=NF, K=64, bn=64, outB=g_hr, aux=hrb, act_slope=0.2))   # * lrelu'(HRconv)
         # HRconv
         bwd.append(o.build_colsum(g_hr, G(hr.bias), C=NF))
-        bwd.append(o.build_gemm_nt(g_hr, feat2, dWt[1], n1=NF, n2=NF, bn=64, conv=geo))
+        bwd.append(o.build_gemm_nt(g_hr, feat2, dWt[1], n1=NF, n2=NF, bn=64, conv=geo, swap=True))
         # d(feat2) = d(fea + trunk): fp32 copy in Z (gradient of the residual stream, [T][192] with zero upper columns)
         Z = [f32(T, 192), f32(T, 192)]
         dDs = [f32(T, 192), f32(T, 192)]
@@ -174,7 +176,7 @@ class _RRDBPlan(_PlanBase):
         bwd.append(o.build_gemm_tn(g_hr, Wt["WtT"][1], N=NF, K=NF, bn=64, conv=geo, outF=dfea, outB=g_f2))
         # trunk_conv: fea receives d(feat2) directly (dfea) and, at the very end, the gradient through the trunk
         bwd.append(o.build_colsum(g_f2, G(trunk.bias), C=NF))
-        bwd.append(o.build_gemm_nt(g_f2, D(L), dWt[0], n1=NF, n2=NF, bn=64, conv=geo))
+        bwd.append(o.build_gemm_nt(g_f2, D(L), dWt[0], n1=NF, n2=NF, bn=64, conv=geo, swap=True))
         z = 0
         bwd.append(o.build_gemm_tn(g_f2, Wt["WtT"][0], N=NF, K=NF, bn=64, conv=geo, outF=Z[z][:, :NF]))
         for i in reversed(range(L)):
@@ -186,14 +188,14 @@ class _RRDBPlan(_PlanBase):
             # out = 0.2 * x5 + x:  d(x5) = 0.2 * g,  the skip stays in Z[z][:, :64]
             bwd.append(o.build_axpby(Z[z], n=NF, a=0.2, out_bf16=g5))
             bwd.append(o.build_colsum(g5, G(blocks[i][4].bias), C=NF))
-            bwd.append(o.build_gemm_nt(g5, Di, dW[4][i], n1=64, n2=KPAD[4], bn=KPAD[4], conv=geo))
+            bwd.append(o.build_gemm_nt(g5, Di, dW[4][i], n1=64, n2=KPAD[4], bn=64, conv=geo, swap=True))
             d = 0
             bwd.append(o.build_gemm_tn(g5, Wt["WpT4"][i], N=KPAD[4], K=64, bn=KPAD[4], conv=geo, resid=Z[z], outF=dDs[d]))
             for k in (3, 2, 1, 0):
                 # gradient of x_{k+1}'s pre-activation: its slot of dD times LeakyReLU'
                 bwd.append(o.build_axpby(dDs[d][:, SLOT[k]:], n=GC, out_bf16=gk, mask=Di[:, SLOT[k]:], mask_slope=0.2, n_pad=NF))
                 bwd.append(o.build_colsum(gk, G(blocks[i][k].bias), C=GC))
-                bwd.append(o.build_gemm_nt(gk, Di, dW[k][i], n1=64, n2=KPAD[k], bn=KPAD[k], conv=geo))
+                bwd.append(o.build_gemm_nt(gk, Di, dW[k][i], n1=64, n2=KPAD[k], bn=64, conv=geo, swap=True))
                 if k > 0:
                     bwd.append(o.build_gemm_tn(gk, Wt["WpT%d" % k][i], N=KPAD[k], K=64, bn=KPAD[k], conv=geo, resid=dDs[d],
                                                outF=dDs[d ^ 1]))
@@ -215,8 +217,9 @@ class _RRDBPlan(_PlanBase):
         for k in range(5):
             cs = [blk[k] for blk in blocks]
             bwd.append(o.build_unpack_conv_grad(dW[k], [G(c.weight) for c in cs], None, O=GC if k < 4 else NF,
-                                                I=NF + GC * k, I_pad=KPAD[k]))
-        bwd.append(o.build_unpack_conv_grad(dWt, [G(trunk.weight), G(hr.weight)], None, O=NF, I=NF, I_pad=NF))
+                                                I=NF + GC * k, I_pad=KPAD[k], transposed=True))
+        bwd.append(o.build_unpack_conv_grad(dWt, [G(trunk.weight), G(hr.weight)], None, O=NF, I=NF, I_pad=NF,
+                                            transposed=True))
         self.bwd = bwd
         self._dx_spec = dict(dhead=dfea, W=head.weight, C=NF, pitch=NF, scale=1.0, skip=False)
         self._finish(eng)

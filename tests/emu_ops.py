@@ -206,7 +206,7 @@ def build_mlp_fused(X, W1, W2, *, N, F, bias1=None, bias2=None, resid=None, outF
 
 
 def build_gemm_nt(A, B, D, *, n1, n2, bn, splits=0, conv=None, dilation=1, swap=False):
-    assert n1 % 64 == 0 and (n1 % bn == 0 and n2 == 64 and conv is not None if swap else n2 % bn == 0)
+    assert n1 % 64 == 0 and (n1 % bn == 0 and n2 % 64 == 0 and conv is not None if swap else n2 % bn == 0)
     d = dilation
 
     def run():
