@@ -113,6 +113,21 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       const int dy = tap / 3, dx = tap - dy * 3;
+      // swap mode: channel offset and pixel shift of every row atom of this CTA's M tile, computed once (inside the
+      // k-block loop the divisions sat on the producer's critical path: +35 % on a fill-bound kernel)
+      int sw_ch[BM / 64], sw_dx[BM / 64], sw_dy[BM / 64];
+      int sw_n = 0;
+      if (kConv && p.swap) {
+        const int at0 = tile1 * (BM / 64);
+        sw_n = 9 * p.k2 - at0 < BM / 64 ? 9 * p.k2 - at0 : BM / 64;
+#pragma unroll
+        for (int i = 0; i < BM / 64; ++i) {
+          const int at = at0 + i, tp = at / p.k2, ty = tp / 3;
+          sw_ch[i] = (at - tp * p.k2) * 64;
+          sw_dx[i] = (tp - ty * 3 - 1) * p.dil;
+          sw_dy[i] = (ty - 1) * p.dil;
+        }
+      }
       long long t_wait = 0, t_begin = NT_CLOCK();
       for (int kb = kb0; kb < kb1; ++kb) {
         const long long tw0 = NT_CLOCK();
@@ -130,14 +145,10 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           int th = r / p.tiles_w;
           int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
           // row atom r of the M side = (tap r / cpt, input channels 64 (r % cpt) ..), cpt = n2 / 64 atoms per tap
-          const int at0 = tile1 * (BM / 64);
-          const int n_at = 9 * p.k2 - at0 < BM / 64 ? 9 * p.k2 - at0 : BM / 64;
-          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(n_at * 8192 + B_STAGE));
+          mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(sw_n * 8192 + B_STAGE));
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i) {
-            const int at = at0 + i, tp = at / p.k2, ch = (at - tp * p.k2) * 64, ty = tp / 3, tx = tp - ty * 3;
-            if (i < n_at)
-              tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], ch, w0 + (tx - 1) * p.dil, h0 + (ty - 1) * p.dil, b);
+            if (i < sw_n) tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], sw_ch[i], w0 + sw_dx[i], h0 + sw_dy[i], b);
           }
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
