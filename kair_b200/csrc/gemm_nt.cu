@@ -128,6 +128,16 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           sw_dy[i] = (ty - 1) * p.dil;
         }
       }
+      // conv: (image, tile row, tile column) of the k-block, walked incrementally -- the producer thread is a serial chain
+      // (wait, coordinates, issue) in a fill-bound kernel and two integer divisions per k-block were a visible part of it
+      int cb = 0, cth = 0, ctw = 0;
+      if (kConv) {
+        const int per_img = p.tiles_w * p.tiles_h;
+        cb = kb0 / per_img;
+        const int r = kb0 - cb * per_img;
+        cth = r / p.tiles_w;
+        ctw = r - cth * p.tiles_w;
+      }
       long long t_wait = 0, t_begin = NT_CLOCK();
       for (int kb = kb0; kb < kb1; ++kb) {
         const long long tw0 = NT_CLOCK();
@@ -139,11 +149,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
         if (kConv && p.swap) {
           // swapped roles: M rows = (tap, input channel); atoms past the ninth tap are not loaded (their rows of D are
           // outside the result tensor and clipped by the TMA store)
-          int per_img = p.tiles_w * p.tiles_h;
-          int b = kb / per_img;
-          int r = kb - b * per_img;
-          int th = r / p.tiles_w;
-          int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
+          const int b = cb, h0 = cth * p.TH, w0 = ctw * p.TW;
           // row atom r of the M side = (tap r / cpt, input channels 64 (r % cpt) ..), cpt = n2 / 64 atoms per tap
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(sw_n * 8192 + B_STAGE));
 #pragma unroll
@@ -155,11 +161,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
             tma_load_4d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, w0, h0, b);
         } else if (kConv) {
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)(NT_A_STAGE + B_STAGE));
-          int per_img = p.tiles_w * p.tiles_h;
-          int b = kb / per_img;
-          int r = kb - b * per_img;
-          int th = r / p.tiles_w;
-          int h0 = th * p.TH, w0 = (r - th * p.tiles_w) * p.TW;
+          const int b = cb, h0 = cth * p.TH, w0 = ctw * p.TW;
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i)
             tma_load_4d(a_s + i * 8192, &p.tmA, &full_bar[stage], tile1 * BM + i * 64, w0, h0, b);
@@ -175,6 +177,13 @@ __global__ void __launch_bounds__(NT_THREADS, 1) gemm_nt_kernel(const __grid_con
           for (int i = 0; i < BN / 64; ++i)
             tma_load_2d(b_s + i * 8192, &p.tmB, &full_bar[stage], tile2 * BN + i * 64, kb * NT_BKT);
         }
+        }
+        if (kConv && ++ctw == p.tiles_w) {
+          ctw = 0;
+          if (++cth == p.tiles_h) {
+            cth = 0;
+            ++cb;
+          }
         }
         if (++stage == p.stages) {
           stage = 0;
