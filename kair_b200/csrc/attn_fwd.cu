@@ -171,10 +171,12 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
           int wi, wj;
           window_origin(p, wsel ? gw1 : gw0, wb[wsel], wi, wj);
           hw[wsel] = p.shift > 0 && wi == p.nWh - 1;
-          h0[wsel] = (wi * 8 + p.shift) % p.H;
-          h1[wsel] = (h0[wsel] + 4) % p.H;
-          ww[wsel][0] = (wj * 8 + p.shift) % p.W;
-          ww[wsel][1] = (wj * 8 + 4 + p.shift) % p.W;
+          // (conditional subtraction instead of a run-time `%`: the shifted coordinates are below 2 H / 2 W)
+          auto wrap = [](int v, int n) { return v >= n ? v - n : v; };
+          h0[wsel] = wrap(wi * 8 + p.shift, p.H);
+          h1[wsel] = wrap(h0[wsel] + 4, p.H);
+          ww[wsel][0] = wrap(wj * 8 + p.shift, p.W);
+          ww[wsel][1] = wrap(wj * 8 + 4 + p.shift, p.W);
         }
         auto load_tile = [&](uint8_t* dst, uint64_t* bar, int col) {
 #pragma unroll
@@ -382,14 +384,15 @@ __global__ void __launch_bounds__(AF_THREADS, 1) window_attn_fwd_kernel(const __
           int b2, wi2, wj2;
           window_origin(p, gw0 + ws2, b2, wi2, wj2);
           const bool hwrap = p.shift > 0 && wi2 == p.nWh - 1;
-          const int h0 = (wi2 * 8 + p.shift) % p.H;
-          const int ww2 = (wj2 * 8 + qx * 4 + p.shift) % p.W;
+          int h0 = wi2 * 8 + p.shift, ww2 = wj2 * 8 + qx * 4 + p.shift;
+          if (h0 >= p.H) h0 -= p.H;
+          if (ww2 >= p.W) ww2 -= p.W;
           const uint8_t* src = out_s + a * 16384 + (ws2 * 4 + qx * 2) * 2048;
           if (!hwrap) {
             tma_store_4d(&p.tmOut2, src, a * 64, ww2, h0, b2);
           } else {
             tma_store_4d(&p.tmOut, src, a * 64, ww2, h0, b2);
-            tma_store_4d(&p.tmOut, src + 2048, a * 64, ww2, (h0 + 4) % p.H, b2);
+            tma_store_4d(&p.tmOut, src + 2048, a * 64, ww2, h0 + 4 >= p.H ? h0 + 4 - p.H : h0 + 4, b2);
           }
         }
         tma_store_commit();
